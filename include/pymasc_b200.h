@@ -1,0 +1,156 @@
+/*
+ * pymasc_b200.h -- C ABI of libpymasc_b200.so, the sm_100a replacement for the
+ * native layer under PyMaSC's bit-array calculator.
+ *
+ * Plain pointers and sizes only; no Python, torch or C++ types cross this boundary.
+ * Every function returns PMB_OK (0) or a negative pmb_status; nothing aborts or throws.
+ * Input arrays are borrowed for the duration of the call.  A pmb_ctx owns one CUDA
+ * device, one stream and a device arena; it is not thread-safe, but different contexts
+ * (devices) may be driven from different host threads (ctypes drops the GIL).
+ *
+ * There is NO CPU fallback behind this ABI: without a usable CUDA device pmb_create
+ * fails with PMB_ERR_CUDA.
+ *
+ * Reference interfaces replaced (paths relative to the PyMaSC checkout):
+ *   pmb_run_chrom / pmb_run_batch .... CCBitArrayCalculator._calc_correlation,
+ *                                      PyMaSC/core/bitarray/mscc.pyx:217-325, i.e. the
+ *                                      bit_array_* calls it makes through
+ *                                      PyMaSC/core/bitarray/bitarray.pxd:20-36:
+ *        fwd_pos / rev_pos scatter ... bit_array_set_bit        external/BitArray/bit_array.c:668
+ *                                      (bitarray.__setitem__,   bitarray.pyx:72-79)
+ *        map_begin / map_end fill .... bit_array_set_region     bit_array.c:823 (-> :423-479)
+ *                                      (_load_mappability,      mscc.pyx:327-349)
+ *        fwd_total / rev_total ....... bit_array_num_bits_set   bit_array.c:962-978
+ *        ncc[k] ...................... bitarray.acount + rshift bitarray.pyx:109-133, bit_array.c:1993-2011
+ *        dmp/mfwd/mrev/mscc[k] ....... bit_array_and x3, count x3, acount, lshift
+ *                                      mscc.pyx:291-310, bit_array.c:1614-1636, :1953-1970
+ *   PMB_FLAG_AUTOCORR ................ _fill_result's mappable-length loop, mscc.pyx:207-215
+ *   popcount ......................... popcnt macro, external/bitcnt.h:23-44
+ */
+#ifndef PYMASC_B200_H
+#define PYMASC_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct pmb_ctx pmb_ctx;
+typedef struct pmb_batch pmb_batch;
+
+typedef enum {
+    PMB_OK = 0,
+    PMB_ERR_CUDA = -1,      /* CUDA runtime error; text in pmb_last_error            */
+    PMB_ERR_RANGE = -2,     /* a position / interval lies beyond the bit array       */
+                            /* (the reference aborts on a BitArray assert here)      */
+    PMB_ERR_ARG = -3,       /* invalid argument                                      */
+    PMB_ERR_NOMEM = -4      /* device or pinned-host allocation failed               */
+} pmb_status;
+
+/* flags of pmb_chrom_args */
+#define PMB_FLAG_NCC      1u  /* compute ncc[k] and the strand totals (not skip_ncc)   */
+#define PMB_FLAG_MSCC     2u  /* compute dmp/mfwd/mrev/mscc[k]; needs intervals        */
+#define PMB_FLAG_AUTOCORR 4u  /* read-less chromosome: dmp[k] = sum_j M[j] M[j+k]      */
+                              /* (mscc.pyx:207-215); other outputs untouched           */
+
+#define PMB_EXTRA_ALLOCATE_SIZE 100 /* mscc.pyx:118 */
+
+/*
+ * One chromosome (or one position shard of it).
+ * Bit array length, as in the reference (mscc.pyx:134,:165):
+ *     nbits = chrom_len + read_len + max_shift + 100
+ * Positions are 1-based bit indices: fwd_pos = leftmost base of a forward read,
+ * rev_pos = pos + query_length - 1 of a reverse read (mscc.pyx:416-417).  Duplicates
+ * are allowed and collapse (a bit is set once).  Order is free.
+ * Intervals are BigWig-style 0-based half-open (begin, end) with value >= 1.0 already
+ * selected by the host; bits begin+1 .. end are set (mscc.pyx:343-344).
+ * Counts are taken over j in [range_lo, range_hi); range_hi == 0 means the whole
+ * array [0, nbits).  A shard still receives every read/interval (or at least those
+ * within max_shift + read_len of its range): halos are built on the device.
+ * All chromosomes of one batch must share read_len and max_shift.
+ */
+typedef struct {
+    uint64_t chrom_len;
+    uint32_t read_len;
+    uint32_t max_shift;
+    uint32_t flags;
+    uint32_t reserved;
+    const uint32_t *fwd_pos;   uint64_t n_fwd;
+    const uint32_t *rev_pos;   uint64_t n_rev;
+    const uint32_t *map_begin; const uint32_t *map_end; uint64_t n_intervals;
+    uint64_t range_lo, range_hi;
+} pmb_chrom_args;
+
+/* Caller-allocated outputs; each vector holds max_shift+1 int64.  Vectors that the
+ * flags do not request may be NULL. */
+typedef struct {
+    int64_t fwd_total;   /* popcount(F) over the range   (mscc.pyx:236) */
+    int64_t rev_total;   /* popcount(R) over the range   (mscc.pyx:237) */
+    int64_t *ncc;        /* sum_j F[j] R[j+k]                     (:314) */
+    int64_t *mscc;       /* sum_j F[j] R[j+k] D_k[j]              (:305) */
+    int64_t *mfwd;       /* sum_j F[j] D_k[j]                     (:303) */
+    int64_t *mrev;       /* sum_j R[j+k] D_k[j]                   (:304) */
+    int64_t *dmp;        /* sum_j D_k[j], D_k[j] = M[j] M[j+read_len-1-k]  (:291-298);
+                            with PMB_FLAG_AUTOCORR: sum_j M[j] M[j+k]            */
+} pmb_chrom_out;
+
+/* Device-side timings of the last pmb_batch_execute, CUDA events on the ctx stream. */
+typedef struct {
+    float build_ms;     /* memset + scatter + interval fill + prep           */
+    float window_ms;    /* shift-window kernel(s)                            */
+    float total_ms;     /* first launch to last launch of the execute        */
+    uint32_t launches;  /* kernels launched by the execute                   */
+    uint32_t window_launches;
+    uint64_t window_word_shift_pairs; /* 32-bit word x shift pairs evaluated  */
+} pmb_timing;
+
+int  pmb_create(pmb_ctx **out, int device_ordinal);
+void pmb_destroy(pmb_ctx *ctx);
+const char *pmb_last_error(pmb_ctx *ctx);   /* ctx may be NULL: last create error */
+
+/* Whole path for one chromosome / a list of chromosomes from HOST arrays:
+ * H2D, bit-array build, shift-window kernel, D2H.  Synchronous. */
+int pmb_run_chrom(pmb_ctx *ctx, const pmb_chrom_args *a, pmb_chrom_out *o);
+int pmb_run_batch(pmb_ctx *ctx, const pmb_chrom_args *a, pmb_chrom_out *o, uint32_t n);
+
+/* The same path in three steps, so that inputs can stay resident in HBM and the
+ * counters can be reduced across GPUs before they leave the device:
+ *   prepare : copy positions/intervals to the device (H2D), plan tiles
+ *   execute : build bit arrays + shift-window kernel; counters stay on the device;
+ *             may be called repeatedly (each call recomputes from the resident inputs)
+ *   fetch   : D2H of the counters into caller-allocated outputs
+ * pmb_batch_counters exposes the device counter block for an NCCL all-reduce:
+ * int64[n_chroms][PMB_NCOUNTERS][stride], counter order ncc, dmp, mfwd, mrev, mscc,
+ * followed by int64[n_chroms][2] strand totals (fwd, rev). */
+#define PMB_NCOUNTERS 5
+int  pmb_batch_prepare(pmb_ctx *ctx, const pmb_chrom_args *a, uint32_t n, pmb_batch **out);
+int  pmb_batch_execute(pmb_ctx *ctx, pmb_batch *b);
+int  pmb_batch_fetch(pmb_ctx *ctx, pmb_batch *b, pmb_chrom_out *o);
+int  pmb_batch_counters(pmb_ctx *ctx, pmb_batch *b, void **dev_ptr, uint64_t *n_int64,
+                        uint32_t *stride);
+void pmb_batch_free(pmb_ctx *ctx, pmb_batch *b);
+int  pmb_get_timing(pmb_ctx *ctx, pmb_timing *t);
+
+/* Stream of the context (cudaStream_t as void*), for callers that order their own
+ * work (e.g. an NCCL all-reduce issued through torch) after pmb_batch_execute. */
+void *pmb_stream(pmb_ctx *ctx);
+int   pmb_synchronize(pmb_ctx *ctx);
+
+/* Pinned host memory for callers without another way to get it. */
+int  pmb_host_alloc(void **out, uint64_t bytes);
+void pmb_host_free(void *p);
+
+/* Tuning knobs (0 = default): variant selects the carry-save depth of the
+ * shift-window kernel's counters, tile_words its tile size. */
+int  pmb_set_option(pmb_ctx *ctx, const char *name, int64_t value);
+
+/* Integer-pipe calibration on the device: runs a dependent-free loop of `what`
+ * (0 = POPC, 1 = LOP3, 2 = POPC+LOP3 interleaved, 3 = SHF, 4 = IADD3, 5 = POPC+IMAD)
+ * and returns executed thread-level ops per second. */
+int  pmb_pipe_probe(pmb_ctx *ctx, int what, double *ops_per_sec, float *ms);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* PYMASC_B200_H */

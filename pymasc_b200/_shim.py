@@ -1,0 +1,285 @@
+"""ctypes binding of libpymasc_b200.so (include/pymasc_b200.h).
+
+The library is the only compute path of this package.  If it is missing, or no sm_100
+device can be opened, the calls here raise -- there is deliberately no CPU fallback.
+"""
+import ctypes
+import os
+
+import numpy as np
+
+from .exceptions import DeviceError, PositionOutOfRange
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libpymasc_b200.so")
+
+PMB_OK, PMB_ERR_CUDA, PMB_ERR_RANGE, PMB_ERR_ARG, PMB_ERR_NOMEM = 0, -1, -2, -3, -4
+FLAG_NCC, FLAG_MSCC, FLAG_AUTOCORR = 1, 2, 4
+NCOUNTERS = 5
+COUNTER_ORDER = ("ncc", "dmp", "mfwd", "mrev", "mscc")
+
+_u32p = ctypes.POINTER(ctypes.c_uint32)
+_i64p = ctypes.POINTER(ctypes.c_int64)
+
+
+class ChromArgs(ctypes.Structure):
+    _fields_ = [
+        ("chrom_len", ctypes.c_uint64),
+        ("read_len", ctypes.c_uint32),
+        ("max_shift", ctypes.c_uint32),
+        ("flags", ctypes.c_uint32),
+        ("reserved", ctypes.c_uint32),
+        ("fwd_pos", ctypes.c_void_p), ("n_fwd", ctypes.c_uint64),
+        ("rev_pos", ctypes.c_void_p), ("n_rev", ctypes.c_uint64),
+        ("map_begin", ctypes.c_void_p), ("map_end", ctypes.c_void_p),
+        ("n_intervals", ctypes.c_uint64),
+        ("range_lo", ctypes.c_uint64), ("range_hi", ctypes.c_uint64),
+    ]
+
+
+class ChromOut(ctypes.Structure):
+    _fields_ = [
+        ("fwd_total", ctypes.c_int64), ("rev_total", ctypes.c_int64),
+        ("ncc", ctypes.c_void_p), ("mscc", ctypes.c_void_p), ("mfwd", ctypes.c_void_p),
+        ("mrev", ctypes.c_void_p), ("dmp", ctypes.c_void_p),
+    ]
+
+
+class Timing(ctypes.Structure):
+    _fields_ = [
+        ("build_ms", ctypes.c_float), ("window_ms", ctypes.c_float), ("total_ms", ctypes.c_float),
+        ("launches", ctypes.c_uint32), ("window_launches", ctypes.c_uint32),
+        ("window_word_shift_pairs", ctypes.c_uint64),
+    ]
+
+
+EXPORTS = (
+    "pmb_create", "pmb_destroy", "pmb_last_error", "pmb_run_chrom", "pmb_run_batch",
+    "pmb_batch_prepare", "pmb_batch_execute", "pmb_batch_fetch", "pmb_batch_counters",
+    "pmb_batch_free", "pmb_get_timing", "pmb_stream", "pmb_synchronize", "pmb_host_alloc",
+    "pmb_host_free", "pmb_set_option", "pmb_pipe_probe",
+)
+
+_lib = None
+
+
+def load_library():
+    """dlopen the shim (needs libcudart, not a GPU).  Raises DeviceError if it was not built."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise DeviceError(
+            "libpymasc_b200.so is missing (%s). Build it with `python -m pymasc_b200.build`; "
+            "pymasc_b200 has no CPU fallback." % LIB_PATH)
+    L = ctypes.CDLL(LIB_PATH)
+    vp, vpp = ctypes.c_void_p, ctypes.POINTER(ctypes.c_void_p)
+    L.pmb_create.argtypes = [vpp, ctypes.c_int]
+    L.pmb_create.restype = ctypes.c_int
+    L.pmb_destroy.argtypes = [vp]
+    L.pmb_destroy.restype = None
+    L.pmb_last_error.argtypes = [vp]
+    L.pmb_last_error.restype = ctypes.c_char_p
+    L.pmb_run_chrom.argtypes = [vp, ctypes.POINTER(ChromArgs), ctypes.POINTER(ChromOut)]
+    L.pmb_run_chrom.restype = ctypes.c_int
+    L.pmb_run_batch.argtypes = [vp, ctypes.POINTER(ChromArgs), ctypes.POINTER(ChromOut), ctypes.c_uint32]
+    L.pmb_run_batch.restype = ctypes.c_int
+    L.pmb_batch_prepare.argtypes = [vp, ctypes.POINTER(ChromArgs), ctypes.c_uint32, vpp]
+    L.pmb_batch_prepare.restype = ctypes.c_int
+    L.pmb_batch_execute.argtypes = [vp, vp]
+    L.pmb_batch_execute.restype = ctypes.c_int
+    L.pmb_batch_fetch.argtypes = [vp, vp, ctypes.POINTER(ChromOut)]
+    L.pmb_batch_fetch.restype = ctypes.c_int
+    L.pmb_batch_counters.argtypes = [vp, vp, vpp, ctypes.POINTER(ctypes.c_uint64),
+                                     ctypes.POINTER(ctypes.c_uint32)]
+    L.pmb_batch_counters.restype = ctypes.c_int
+    L.pmb_batch_free.argtypes = [vp, vp]
+    L.pmb_batch_free.restype = None
+    L.pmb_get_timing.argtypes = [vp, ctypes.POINTER(Timing)]
+    L.pmb_get_timing.restype = ctypes.c_int
+    L.pmb_stream.argtypes = [vp]
+    L.pmb_stream.restype = vp
+    L.pmb_synchronize.argtypes = [vp]
+    L.pmb_synchronize.restype = ctypes.c_int
+    L.pmb_host_alloc.argtypes = [vpp, ctypes.c_uint64]
+    L.pmb_host_alloc.restype = ctypes.c_int
+    L.pmb_host_free.argtypes = [vp]
+    L.pmb_host_free.restype = None
+    L.pmb_set_option.argtypes = [vp, ctypes.c_char_p, ctypes.c_int64]
+    L.pmb_set_option.restype = ctypes.c_int
+    L.pmb_pipe_probe.argtypes = [vp, ctypes.c_int, ctypes.POINTER(ctypes.c_double),
+                                 ctypes.POINTER(ctypes.c_float)]
+    L.pmb_pipe_probe.restype = ctypes.c_int
+    _lib = L
+    return L
+
+
+def _as_u32(a):
+    if a is None:
+        return np.zeros(0, dtype=np.uint32)
+    a = np.asarray(a)
+    if a.dtype != np.uint32 or not a.flags.c_contiguous:
+        a = np.ascontiguousarray(a, dtype=np.uint32)
+    return a
+
+
+class Job(object):
+    """One chromosome (or position shard) handed to the device."""
+
+    __slots__ = ("chrom_len", "read_len", "max_shift", "flags", "fwd_pos", "rev_pos",
+                 "map_begins", "map_ends", "lo", "hi")
+
+    def __init__(self, chrom_len, read_len, max_shift, flags, fwd_pos=None, rev_pos=None,
+                 map_begins=None, map_ends=None, lo=0, hi=0):
+        self.chrom_len, self.read_len, self.max_shift, self.flags = (
+            int(chrom_len), int(read_len), int(max_shift), int(flags))
+        self.fwd_pos, self.rev_pos = _as_u32(fwd_pos), _as_u32(rev_pos)
+        self.map_begins, self.map_ends = _as_u32(map_begins), _as_u32(map_ends)
+        self.lo, self.hi = int(lo), int(hi)
+
+
+class Device(object):
+    """A pmb_ctx: one CUDA device, one stream."""
+
+    def __init__(self, ordinal=None):
+        self._L = load_library()
+        if ordinal is None:
+            ordinal = int(os.environ.get("PYMASC_B200_DEVICE", os.environ.get("LOCAL_RANK", "0")))
+        h = ctypes.c_void_p()
+        rc = self._L.pmb_create(ctypes.byref(h), int(ordinal))
+        if rc != PMB_OK:
+            raise DeviceError("pmb_create(device %d) failed (%d): %s -- pymasc_b200 needs an sm_100 "
+                              "GPU and has no CPU fallback" %
+                              (ordinal, rc, self._L.pmb_last_error(None).decode()))
+        self._h = h
+        self.ordinal = int(ordinal)
+
+    def close(self):
+        if getattr(self, "_h", None):
+            self._L.pmb_destroy(self._h)
+            self._h = None
+
+    __del__ = close
+
+    def _check(self, rc):
+        if rc == PMB_OK:
+            return
+        msg = self._L.pmb_last_error(self._h).decode()
+        if rc == PMB_ERR_RANGE:
+            raise PositionOutOfRange(msg)
+        if rc == PMB_ERR_ARG:
+            raise ValueError(msg)
+        raise DeviceError("libpymasc_b200 error %d: %s" % (rc, msg))
+
+    def set_option(self, name, value):
+        self._check(self._L.pmb_set_option(self._h, name.encode(), int(value)))
+
+    def synchronize(self):
+        self._check(self._L.pmb_synchronize(self._h))
+
+    @property
+    def stream(self):
+        return self._L.pmb_stream(self._h)
+
+    # ---- argument marshalling
+    @staticmethod
+    def _marshal(jobs):
+        n = len(jobs)
+        args = (ChromArgs * n)()
+        for a, j in zip(args, jobs):
+            a.chrom_len, a.read_len, a.max_shift, a.flags = j.chrom_len, j.read_len, j.max_shift, j.flags
+            a.fwd_pos, a.n_fwd = j.fwd_pos.ctypes.data, j.fwd_pos.size
+            a.rev_pos, a.n_rev = j.rev_pos.ctypes.data, j.rev_pos.size
+            a.map_begin, a.map_end = j.map_begins.ctypes.data, j.map_ends.ctypes.data
+            a.n_intervals = j.map_begins.size
+            a.range_lo, a.range_hi = j.lo, j.hi
+        return args
+
+    @staticmethod
+    def _outputs(jobs):
+        n = len(jobs)
+        outs = (ChromOut * n)()
+        arrays = []
+        for o, j in zip(outs, jobs):
+            S = j.max_shift + 1
+            d = {}
+            if j.flags & FLAG_AUTOCORR:
+                d["dmp"] = np.zeros(S, np.int64)
+            else:
+                if j.flags & FLAG_NCC:
+                    d["ncc"] = np.zeros(S, np.int64)
+                if j.flags & FLAG_MSCC:
+                    for k in ("dmp", "mfwd", "mrev", "mscc"):
+                        d[k] = np.zeros(S, np.int64)
+            for k, v in d.items():
+                setattr(o, k, v.ctypes.data)
+            arrays.append(d)
+        return outs, arrays
+
+    @staticmethod
+    def _collect(jobs, outs, arrays):
+        res = []
+        for o, d, j in zip(outs, arrays, jobs):
+            d = dict(d)
+            if not j.flags & FLAG_AUTOCORR:
+                d["fwd_total"], d["rev_total"] = int(o.fwd_total), int(o.rev_total)
+            res.append(d)
+        return res
+
+    # ---- the hot path
+    def run_batch(self, jobs):
+        """Host arrays in, per-shift int64 counters out (H2D + build + window + D2H)."""
+        if not jobs:
+            return []
+        args = self._marshal(jobs)
+        outs, arrays = self._outputs(jobs)
+        self._check(self._L.pmb_run_batch(self._h, args, outs, len(jobs)))
+        return self._collect(jobs, outs, arrays)
+
+    def prepare(self, jobs):
+        return Batch(self, jobs)
+
+    def timing(self):
+        t = Timing()
+        self._check(self._L.pmb_get_timing(self._h, ctypes.byref(t)))
+        return {"build_ms": t.build_ms, "window_ms": t.window_ms, "total_ms": t.total_ms,
+                "launches": t.launches, "window_launches": t.window_launches,
+                "window_word_shift_pairs": t.window_word_shift_pairs}
+
+    def pipe_probe(self, what):
+        ops, ms = ctypes.c_double(), ctypes.c_float()
+        self._check(self._L.pmb_pipe_probe(self._h, int(what), ctypes.byref(ops), ctypes.byref(ms)))
+        return ops.value, ms.value
+
+
+class Batch(object):
+    """Inputs resident on the device: prepare once, execute (repeatedly), fetch."""
+
+    def __init__(self, device, jobs):
+        self.dev, self.jobs = device, list(jobs)
+        args = device._marshal(self.jobs)
+        h = ctypes.c_void_p()
+        device._check(device._L.pmb_batch_prepare(device._h, args, len(self.jobs), ctypes.byref(h)))
+        self._h = h
+
+    def execute(self):
+        self.dev._check(self.dev._L.pmb_batch_execute(self.dev._h, self._h))
+
+    def fetch(self):
+        outs, arrays = self.dev._outputs(self.jobs)
+        self.dev._check(self.dev._L.pmb_batch_fetch(self.dev._h, self._h, outs))
+        return self.dev._collect(self.jobs, outs, arrays)
+
+    def counters(self):
+        """(device pointer, number of int64, per-counter stride) of the counter block."""
+        p, n, s = ctypes.c_void_p(), ctypes.c_uint64(), ctypes.c_uint32()
+        self.dev._check(self.dev._L.pmb_batch_counters(self.dev._h, self._h, ctypes.byref(p),
+                                                       ctypes.byref(n), ctypes.byref(s)))
+        return p.value, n.value, s.value
+
+    def free(self):
+        if getattr(self, "_h", None) and getattr(self.dev, "_h", None):
+            self.dev._L.pmb_batch_free(self.dev._h, self._h)
+        self._h = None
+
+    __del__ = free

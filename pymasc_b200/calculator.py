@@ -1,0 +1,361 @@
+"""B200 drop-in for PyMaSC's bit-array calculator.
+
+``CCBitArrayCalculator`` here has the constructor, attributes, methods, error behaviour and
+result objects of the reference class of the same name
+(PyMaSC/core/bitarray/mscc.pyx:41-483; interface PyMaSC/interfaces/calculator.py:15-124), so it
+can be constructed at PyMaSC/handler/factory.py:247 in its place and everything downstream
+(result.py, stats.py, output/*) runs unchanged.
+
+What differs is where the work happens.  The reference sets one bit per ``feed_*`` call in a
+host BitArray and, at every chromosome switch, runs (max_shift+1) x ~10 whole-array passes on
+one CPU core.  Here ``feed_*`` only appends the 5' position to a packed uint32 buffer and keeps
+the reference's host-side bookkeeping (sort check, duplicate rules, read-length sums); closed
+chromosomes are queued and handed to the device in ONE batch -- bit-array build and the
+shift-window kernel run in libpymasc_b200.so (pymasc_b200/csrc) -- when results are needed
+(``flush``, ``finishup_calculation``, ``get_result``, ``get_whole_result``).
+
+There is no CPU fallback: without the CUDA library and an sm_100 device the first batch raises
+``DeviceError``.
+"""
+import logging
+from array import array
+
+import numpy as np
+
+from . import _shim
+from .exceptions import PositionOutOfRange, ReadUnsortedError
+from .result import (
+    BothChromResult, BothGenomeWideResult, EmptyMSCCResult, EmptyNCCResult, MSCCGenomeWideResult,
+    MSCCResult, NCCGenomeWideResult, NCCResult,
+)
+
+logger = logging.getLogger(__name__)
+
+
+class DeviceEngine(object):
+    """Runs batches of chromosome jobs on one B200 through the C ABI."""
+
+    def __init__(self, device=None):
+        self._device = device
+        self._ordinal = None if device is None or isinstance(device, _shim.Device) else int(device)
+        if not isinstance(device, _shim.Device):
+            self._device = None
+
+    @property
+    def device(self):
+        if self._device is None:      # opened lazily: spawned workers pick their own GPU
+            self._device = _shim.Device(self._ordinal)
+        return self._device
+
+    def run(self, jobs):
+        return self.device.run_batch(jobs)
+
+
+class _Pending(object):
+    __slots__ = ("chrom", "fwd", "rev", "intervals", "fwd_len_sum", "rev_len_sum")
+
+
+class CCBitArrayCalculator(object):
+    """Naive and mappability-sensitive strand cross-correlation counts on a B200.
+
+    Args (same order and meaning as mscc.pyx:97-98):
+        max_shift, read_len, references, lengths, bwfeeder=None, skip_ncc=False,
+        logger_lock=None, progress_bar=None
+    Extra keyword (not in the reference): ``engine`` -- object with ``run(jobs)``; defaults to
+    ``DeviceEngine()``.  Tests inject a checker engine here; the product never does.
+    """
+
+    def __init__(self, max_shift, read_len, references, lengths, bwfeeder=None, skip_ncc=False,
+                 logger_lock=None, progress_bar=None, engine=None):
+        self.MAPPABILITY_THRESHOLD = 1.         # mscc.pyx:116
+        self.EXTRA_ALLOCATE_SIZE = 100          # mscc.pyx:118
+        self._max_shift = int(max_shift)
+        self._read_len = int(read_len)
+        self.references = references
+        self.ref2genomelen = dict(zip(references, lengths))
+        self.genomelen = sum(lengths)
+        self.ref2ncc_result = {}
+        self.ref2mscc_result = {}
+        self.forward_sum = self.reverse_sum = 0
+        self.forward_read_len_sum = self.reverse_read_len_sum = 0
+
+        self._chr = ''
+        self._solved_chr = []
+        self._buff_flashed = False
+        self._array_extend_size = self._read_len + self._max_shift + self.EXTRA_ALLOCATE_SIZE
+
+        self._bwfeeder = bwfeeder
+        self._skip_ncc = bool(skip_ncc)
+        self._logger_lock = logger_lock
+        self._progress = progress_bar           # accepted; per-shift ticks do not exist here
+        self._engine = engine if engine is not None else DeviceEngine()
+
+        self._pending = []                      # closed chromosomes awaiting the device
+        self._fwd = self._rev_end = self._rev_len = None
+        self._nbits = 0
+        self._last_pos = self._last_forward_pos = 0
+        self._forward_read_len_sum = 0
+
+    # readonly attributes of the reference (mscc.pyx:75-79)
+    max_shift = property(lambda self: self._max_shift)
+    read_len = property(lambda self: self._read_len)
+    skip_ncc = property(lambda self: self._skip_ncc)
+    logger_lock = property(lambda self: self._logger_lock)
+
+    # ------------------------------------------------------------------ logging
+    def _logging_info(self, msg):
+        if self._logger_lock:
+            self._logger_lock.acquire()
+        logger.info(msg)
+        if self._logger_lock:
+            self._logger_lock.release()
+
+    # ------------------------------------------------------------------ feeding (host)
+    def _init_buff(self):
+        # mscc.pyx:161-171 -- the bit arrays become packed position buffers
+        self._nbits = self.ref2genomelen[self._chr] + self._array_extend_size
+        self._fwd = array('I')
+        self._rev_end = array('I')
+        self._rev_len = array('I')
+        self._last_pos = 0
+        self._last_forward_pos = 0
+        self._forward_read_len_sum = 0
+
+    def _check_pos(self, chrom, pos):
+        # mscc.pyx:351-366
+        if chrom != self._chr:
+            if self._chr != '':
+                if chrom in self._solved_chr:
+                    raise ReadUnsortedError
+                self._solved_chr.append(self._chr)
+                self._close_chromosome()
+                self._buff_flashed = False
+            self._chr = chrom
+            self._init_buff()
+            self._logging_info("Loading {} reads to bit array...".format(chrom))
+        if pos < self._last_pos:
+            raise ReadUnsortedError
+        self._last_pos = pos
+
+    def feed_forward_read(self, chrom, pos, readlen):
+        """pos: 1-based leftmost base.  mscc.pyx:370-393."""
+        self._check_pos(chrom, pos)
+        if self._last_forward_pos == pos:
+            return None                         # duplicated read
+        self._last_forward_pos = pos
+        if not 0 <= pos < self._nbits:
+            raise PositionOutOfRange("forward read at %s:%d beyond the bit array" % (chrom, pos))
+        self._forward_read_len_sum += readlen
+        self._fwd.append(pos)
+
+    def feed_reverse_read(self, chrom, pos, readlen):
+        """The bit set is pos + readlen - 1, the 5' end of the reverse read.  mscc.pyx:397-418."""
+        self._check_pos(chrom, pos)
+        end = pos + readlen - 1
+        if not 0 <= end < self._nbits:
+            raise PositionOutOfRange("reverse read end at %s:%d beyond the bit array" % (chrom, end))
+        # first-occurrence rule for the read-length sum is applied when the chromosome closes
+        self._rev_end.append(end)
+        self._rev_len.append(readlen)
+
+    def feed_batch(self, chrom, pos, readlen, is_reverse):
+        """Vectorised feed of one chromosome's reads in coordinate order (numpy arrays).
+        Equivalent to calling feed_forward_read / feed_reverse_read per read."""
+        pos = np.asarray(pos, dtype=np.int64)
+        readlen = np.asarray(readlen, dtype=np.int64)
+        is_reverse = np.asarray(is_reverse, dtype=bool)
+        if pos.size == 0:
+            return
+        self._check_pos(chrom, int(pos[0]))
+        if pos.size > 1 and np.any(pos[1:] < pos[:-1]):
+            raise ReadUnsortedError
+        self._last_pos = int(pos[-1])
+        fpos, flen = pos[~is_reverse], readlen[~is_reverse]
+        if fpos.size:
+            keep = np.ones(fpos.size, dtype=bool)
+            keep[1:] = fpos[1:] != fpos[:-1]
+            keep[0] = fpos[0] != self._last_forward_pos
+            fpos, flen = fpos[keep], flen[keep]
+            if fpos.size:
+                if fpos[0] < 0 or fpos[-1] >= self._nbits:
+                    raise PositionOutOfRange("forward read on %s beyond the bit array" % chrom)
+                self._last_forward_pos = int(fpos[-1])
+                self._forward_read_len_sum += int(flen.sum())
+                self._fwd.frombytes(fpos.astype(np.uint32).tobytes())
+        rend = pos[is_reverse] + readlen[is_reverse] - 1
+        if rend.size:
+            if rend.min() < 0 or rend.max() >= self._nbits:
+                raise PositionOutOfRange("reverse read end on %s beyond the bit array" % chrom)
+            self._rev_end.frombytes(rend.astype(np.uint32).tobytes())
+            self._rev_len.frombytes(readlen[is_reverse].astype(np.uint32).tobytes())
+
+    # ------------------------------------------------------------------ mappability (host)
+    def _load_intervals(self, chrom):
+        """(begins, ends) uint32 arrays of the intervals with value >= 1.0, or None without a
+        feeder.  KeyError when the track lacks the chromosome.  mscc.pyx:327-349."""
+        if not self._bwfeeder:
+            return None
+        if hasattr(self._bwfeeder, "fetch_arrays"):          # packed fast path
+            b, e = self._bwfeeder.fetch_arrays(self.MAPPABILITY_THRESHOLD, chrom)
+        else:
+            feeder = self._bwfeeder.fetch(self.MAPPABILITY_THRESHOLD, chrom)
+            rows = [(iv[0], iv[1]) for iv in feeder]
+            arr = np.asarray(rows, dtype=np.int64).reshape(-1, 2)
+            b, e = arr[:, 0], arr[:, 1]
+        self._logging_info("Loading {} mappability to bit array...".format(chrom))
+        b = np.ascontiguousarray(b, dtype=np.int64)
+        e = np.ascontiguousarray(e, dtype=np.int64)
+        nbits = self.ref2genomelen[chrom] + self._array_extend_size
+        if b.size and (b.min() < 0 or e.max() >= nbits):
+            # the reference aborts on a BitArray assert here (bit_array.c:825)
+            raise PositionOutOfRange("mappability interval on %s beyond the bit array" % chrom)
+        return b.astype(np.uint32), e.astype(np.uint32)
+
+    # ------------------------------------------------------------------ closing a chromosome
+    def _close_chromosome(self):
+        """The host half of _calc_correlation (mscc.pyx:217-282): settle the read-length sums,
+        reserve the result slots in the reference's insertion order, queue the device job."""
+        if self._chr == '' or self._buff_flashed:
+            return
+        chrom = self._chr
+        p = _Pending()
+        p.chrom = chrom
+        p.fwd = np.frombuffer(self._fwd, dtype=np.uint32).copy() if len(self._fwd) else np.zeros(0, np.uint32)
+        rev_end = np.frombuffer(self._rev_end, dtype=np.uint32) if len(self._rev_end) else np.zeros(0, np.uint32)
+        rev_len = np.frombuffer(self._rev_len, dtype=np.uint32) if len(self._rev_len) else np.zeros(0, np.uint32)
+        # reverse duplicate rule (mscc.pyx:416-418): only the first read to set a bit counts
+        uniq, first = np.unique(rev_end, return_index=True)
+        p.rev = uniq.astype(np.uint32)
+        p.fwd_len_sum = int(self._forward_read_len_sum)
+        p.rev_len_sum = int(rev_len[first].sum()) if first.size else 0
+        self.forward_read_len_sum += p.fwd_len_sum
+        self.reverse_read_len_sum += p.rev_len_sum
+        if not self._skip_ncc:
+            self.ref2ncc_result[chrom] = None          # reserved; filled by _compute_pending
+        try:
+            p.intervals = self._load_intervals(chrom)
+        except KeyError as e:
+            self._logging_info("Mappability for '{}' not found. "
+                               "Skip calc mappability sensitive CC.".format(e.args[0]))
+            p.intervals = None
+        if p.intervals is not None:
+            self.ref2mscc_result[chrom] = None
+        self._logging_info("Calculate cross-correlation for {}...".format(chrom))
+        if not self._skip_ncc or p.intervals is not None:
+            self._pending.append(p)
+        self._fwd = self._rev_end = self._rev_len = None
+
+    def _job_of(self, p):
+        flags = (0 if self._skip_ncc else _shim.FLAG_NCC) | \
+                (_shim.FLAG_MSCC if p.intervals is not None else 0)
+        b, e = p.intervals if p.intervals is not None else (None, None)
+        return _shim.Job(self.ref2genomelen[p.chrom], self._read_len, self._max_shift, flags,
+                         p.fwd, p.rev, b, e)
+
+    def _mappable_len_list(self, dmp):
+        # mscc.pyx:271, :292-298 -- popc(D_k) re-indexed by |read_len-1-k|
+        rl = self._read_len
+        ml = [None] * rl
+        for k in range(self._max_shift + 1):
+            if k < rl:
+                ml[rl - k - 1] = int(dmp[k])
+            elif k >= rl * 2 - 1:
+                ml.append(int(dmp[k]))
+        return ml
+
+    def _store(self, p, out):
+        chrom, L = p.chrom, self.ref2genomelen[p.chrom]
+        if not self._skip_ncc:
+            self.forward_sum += out["fwd_total"]
+            self.reverse_sum += out["rev_total"]
+            r = NCCResult(max_shift=self._max_shift, read_len=self._read_len, genomelen=L,
+                          forward_sum=out["fwd_total"], reverse_sum=out["rev_total"],
+                          forward_read_len_sum=p.fwd_len_sum, reverse_read_len_sum=p.rev_len_sum,
+                          ccbins=[int(x) for x in out["ncc"]])
+            r.calc_cc()
+            self.ref2ncc_result[chrom] = r
+        if p.intervals is not None:
+            r = MSCCResult(max_shift=self._max_shift, read_len=self._read_len, genomelen=L,
+                           forward_sum=[int(x) for x in out["mfwd"]],
+                           reverse_sum=[int(x) for x in out["mrev"]],
+                           forward_read_len_sum=p.fwd_len_sum, reverse_read_len_sum=p.rev_len_sum,
+                           ccbins=[int(x) for x in out["mscc"]],
+                           mappable_len=self._mappable_len_list(out["dmp"]))
+            r.calc_cc()
+            self.ref2mscc_result[chrom] = r
+
+    def _compute_pending(self, fill=()):
+        """One device batch: every queued chromosome plus the mappable-length
+        autocorrelation of the read-less chromosomes in `fill` (mscc.pyx:181-215)."""
+        jobs = [self._job_of(p) for p in self._pending]
+        fills = []
+        for chrom in fill:
+            self._chr = chrom                                   # side effect of _fill_result
+            if chrom not in self.ref2ncc_result:
+                self.ref2ncc_result[chrom] = EmptyNCCResult.create_empty(
+                    self.ref2genomelen[chrom], self._max_shift, self._read_len)
+            if not self._bwfeeder or chrom in self.ref2mscc_result:
+                continue
+            res = self.ref2mscc_result[chrom] = EmptyMSCCResult.create_empty(
+                self.ref2genomelen[chrom], self._max_shift, self._read_len)
+            try:
+                iv = self._load_intervals(chrom)
+            except KeyError:
+                continue
+            self._logging_info("Calc {} mappable length...".format(chrom))
+            jobs.append(_shim.Job(self.ref2genomelen[chrom], self._read_len, self._max_shift,
+                                  _shim.FLAG_AUTOCORR, None, None, iv[0], iv[1]))
+            fills.append(res)
+        if not jobs:
+            return
+        outs = self._engine.run(jobs)
+        for p, out in zip(self._pending, outs):
+            self._store(p, out)
+        for res, out in zip(fills, outs[len(self._pending):]):
+            res.mappable_len = tuple(int(x) for x in out["dmp"])
+        self._pending = []
+
+    # ------------------------------------------------------------------ public protocol
+    def flush(self, chrom=None):
+        """mscc.pyx:173-179."""
+        if self._chr != '' and not self._buff_flashed:
+            self._close_chromosome()
+        self._compute_pending(fill=() if chrom is None else (chrom,))
+        self._buff_flashed = True
+
+    def finishup_calculation(self):
+        """mscc.pyx:420-439: flush the last chromosome, then fill every reference."""
+        if self._chr != '' and not self._buff_flashed:
+            self._close_chromosome()
+        last = self._chr
+        self._compute_pending(fill=[last] + list(self.references))
+        self._buff_flashed = True
+
+    def get_result(self, chrom):
+        """mscc.pyx:441-447."""
+        if chrom not in self.ref2ncc_result and chrom not in self.ref2mscc_result:
+            raise KeyError(chrom)
+        self._compute_pending()
+        return BothChromResult(chrom=self.ref2ncc_result.get(chrom),
+                               mappable_chrom=self.ref2mscc_result.get(chrom))
+
+    def get_whole_result(self):
+        """mscc.pyx:449-483."""
+        self._compute_pending()
+        if not self.ref2mscc_result:
+            assert self.ref2ncc_result, "No results available for either NCC or MSCC."
+            return NCCGenomeWideResult(
+                genomelen=self.genomelen, forward_sum=self.forward_sum, reverse_sum=self.reverse_sum,
+                chroms=self.ref2ncc_result.copy(),
+                forward_read_len_sum=self.forward_read_len_sum,
+                reverse_read_len_sum=self.reverse_read_len_sum)
+        elif not self.ref2ncc_result:
+            return MSCCGenomeWideResult(
+                genomelen=self.genomelen, chroms=self.ref2mscc_result.copy(),
+                forward_read_len_sum=self.forward_read_len_sum,
+                reverse_read_len_sum=self.reverse_read_len_sum)
+        return BothGenomeWideResult(
+            genomelen=self.genomelen, forward_sum=self.forward_sum, reverse_sum=self.reverse_sum,
+            chroms=self.ref2ncc_result.copy(), mappable_chroms=self.ref2mscc_result.copy(),
+            forward_read_len_sum=self.forward_read_len_sum,
+            reverse_read_len_sum=self.reverse_read_len_sum)

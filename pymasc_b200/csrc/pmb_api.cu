@@ -1,0 +1,641 @@
+// pmb_api.cu -- C ABI of libpymasc_b200.so (see include/pymasc_b200.h).
+// Host-side planning + launches for the bit-array build and shift-window kernels.
+// sm_100a only; there is no CPU path in this library.
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <string.h>
+
+#include <algorithm>
+#include <string>
+#include <vector>
+
+#include "../../include/pymasc_b200.h"
+#include "pmb_build.cuh"
+#include "pmb_probe.cuh"
+#include "pmb_window.cuh"
+
+using namespace pmb;
+
+static thread_local std::string g_create_error;
+
+struct pmb_ctx {
+    int device = 0;
+    int num_sms = 148;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
+    std::string err;
+    pmb_timing timing{};
+    // options
+    int variant = -1;        // -1: default per mode
+    int tile_words = 0;      // 0: automatic
+    int grid_blocks = 0;     // 0: one per SM
+    int block_warps = 16;
+    // pinned staging for counters
+    void* h_stage = nullptr;
+    size_t h_stage_bytes = 0;
+};
+
+#define CU_TRY(ctx, call)                                                                   \
+    do {                                                                                    \
+        cudaError_t e__ = (call);                                                           \
+        if (e__ != cudaSuccess) {                                                           \
+            char buf__[512];                                                                \
+            snprintf(buf__, sizeof buf__, "%s failed: %s (%s:%d)", #call,                   \
+                     cudaGetErrorString(e__), __FILE__, __LINE__);                          \
+            (ctx)->err = buf__;                                                             \
+            return (e__ == cudaErrorMemoryAllocation) ? PMB_ERR_NOMEM : PMB_ERR_CUDA;       \
+        }                                                                                   \
+    } while (0)
+
+struct JobPlan {
+    pmb_chrom_args a;          // host pointers are only valid during prepare
+    uint64_t nbits = 0;
+    int64_t lo = 0, hi = 0;
+    int64_t origin_word = 0;   // ow
+    uint64_t body_words = 0;   // Wpad = n_tiles * T
+    uint32_t n_tiles = 0;
+    int mode = 0;              // MODE_NCC / MODE_MSCC / MODE_BOTH; autocorr -> MODE_NCC on M
+    bool autocorr = false;
+    // offsets (in uint32 words) into the batch's device buffers
+    size_t in_fwd = 0, in_rev = 0, in_mb = 0, in_me = 0;
+    size_t bits = 0;           // start of this job's arrays; each array_words long
+    size_t array_words = 0;    // 2H + Wpad
+};
+
+struct WinLaunch {
+    int mode;
+    WindowParams P;
+    uint32_t blocks, warps;
+    size_t smem;
+    uint64_t pairs;   // 32-bit word x shift pairs evaluated by this launch
+};
+
+struct pmb_batch {
+    std::vector<JobPlan> jobs;
+    std::vector<WinLaunch> launches;
+    uint32_t read_len = 0, max_shift = 0, n_shifts = 0;
+    uint32_t n_units = 0, stride = 0, halo_words = 0, tile_words = 0;
+    uint32_t* d_in = nullptr;  size_t in_words = 0;
+    uint32_t* d_bits = nullptr; size_t bits_words = 0;
+    unsigned long long* d_counters = nullptr; size_t counter_words = 0;  // + totals at the end
+    WindowJob* d_jobs = nullptr; size_t d_jobs_count = 0;
+    int* d_err = nullptr;
+    uint32_t* d_long = nullptr; size_t long_cap = 0;   // [0] = count, [1..] = list
+};
+
+// ------------------------------------------------------------------ context
+extern "C" int pmb_create(pmb_ctx** out, int device_ordinal)
+{
+    if (!out) return PMB_ERR_ARG;
+    *out = nullptr;
+    int n = 0;
+    cudaError_t e = cudaGetDeviceCount(&n);
+    if (e != cudaSuccess || n <= 0) {
+        g_create_error = std::string("no usable CUDA device: ") +
+                         (e != cudaSuccess ? cudaGetErrorString(e) : "device count is 0");
+        return PMB_ERR_CUDA;
+    }
+    if (device_ordinal < 0 || device_ordinal >= n) {
+        g_create_error = "device ordinal out of range";
+        return PMB_ERR_ARG;
+    }
+    pmb_ctx* c = new pmb_ctx();
+    c->device = device_ordinal;
+    auto fail = [&](const char* what, cudaError_t err) {
+        g_create_error = std::string(what) + ": " + cudaGetErrorString(err);
+        delete c;
+        return PMB_ERR_CUDA;
+    };
+    if ((e = cudaSetDevice(device_ordinal)) != cudaSuccess) return fail("cudaSetDevice", e);
+    cudaDeviceProp prop;
+    if ((e = cudaGetDeviceProperties(&prop, device_ordinal)) != cudaSuccess)
+        return fail("cudaGetDeviceProperties", e);
+    if (prop.major != 10) {
+        g_create_error = "libpymasc_b200 is built for sm_100a only; device is sm_" +
+                         std::to_string(prop.major) + std::to_string(prop.minor);
+        delete c;
+        return PMB_ERR_CUDA;
+    }
+    c->num_sms = prop.multiProcessorCount;
+    if ((e = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking)) != cudaSuccess)
+        return fail("cudaStreamCreate", e);
+    for (auto& ev : c->ev)
+        if ((e = cudaEventCreate(&ev)) != cudaSuccess) return fail("cudaEventCreate", e);
+    // keep freed blocks cached in the stream-ordered pool (arena behaviour)
+    cudaMemPool_t pool;
+    if (cudaDeviceGetDefaultMemPool(&pool, device_ordinal) == cudaSuccess) {
+        uint64_t thr = UINT64_MAX;
+        cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &thr);
+    }
+    *out = c;
+    return PMB_OK;
+}
+
+extern "C" void pmb_destroy(pmb_ctx* c)
+{
+    if (!c) return;
+    cudaSetDevice(c->device);
+    if (c->stream) cudaStreamSynchronize(c->stream);
+    for (auto& ev : c->ev)
+        if (ev) cudaEventDestroy(ev);
+    if (c->h_stage) cudaFreeHost(c->h_stage);
+    if (c->stream) cudaStreamDestroy(c->stream);
+    delete c;
+}
+
+extern "C" const char* pmb_last_error(pmb_ctx* c)
+{
+    return c ? c->err.c_str() : g_create_error.c_str();
+}
+
+extern "C" void* pmb_stream(pmb_ctx* c) { return c ? (void*)c->stream : nullptr; }
+
+extern "C" int pmb_synchronize(pmb_ctx* c)
+{
+    if (!c) return PMB_ERR_ARG;
+    CU_TRY(c, cudaSetDevice(c->device));
+    CU_TRY(c, cudaStreamSynchronize(c->stream));
+    return PMB_OK;
+}
+
+extern "C" int pmb_host_alloc(void** out, uint64_t bytes)
+{
+    if (!out) return PMB_ERR_ARG;
+    return cudaHostAlloc(out, bytes ? bytes : 1, cudaHostAllocDefault) == cudaSuccess ? PMB_OK
+                                                                                      : PMB_ERR_NOMEM;
+}
+extern "C" void pmb_host_free(void* p)
+{
+    if (p) cudaFreeHost(p);
+}
+
+extern "C" int pmb_set_option(pmb_ctx* c, const char* name, int64_t value)
+{
+    if (!c || !name) return PMB_ERR_ARG;
+    if (!strcmp(name, "variant")) c->variant = (int)value;
+    else if (!strcmp(name, "tile_words")) c->tile_words = (int)value;
+    else if (!strcmp(name, "grid_blocks")) c->grid_blocks = (int)value;
+    else if (!strcmp(name, "block_warps")) c->block_warps = (int)value;
+    else { c->err = std::string("unknown option ") + name; return PMB_ERR_ARG; }
+    return PMB_OK;
+}
+
+extern "C" int pmb_get_timing(pmb_ctx* c, pmb_timing* t)
+{
+    if (!c || !t) return PMB_ERR_ARG;
+    if (c->timing.total_ms < 0.f && c->timing.launches) {   // events of the last execute
+        CU_TRY(c, cudaSetDevice(c->device));
+        CU_TRY(c, cudaEventSynchronize(c->ev[2]));
+        CU_TRY(c, cudaEventElapsedTime(&c->timing.build_ms, c->ev[0], c->ev[1]));
+        CU_TRY(c, cudaEventElapsedTime(&c->timing.window_ms, c->ev[1], c->ev[2]));
+        CU_TRY(c, cudaEventElapsedTime(&c->timing.total_ms, c->ev[0], c->ev[2]));
+    }
+    *t = c->timing;
+    return PMB_OK;
+}
+
+// ------------------------------------------------------------------ batch: prepare
+static uint32_t gcd_u32(uint32_t a, uint32_t b) { return b ? gcd_u32(b, a % b) : a; }
+
+enum { A_F = 0, A_R = 1, A_M = 2, A_MP = 3, A_FM = 4 };
+
+static int arrays_of(const JobPlan& j)
+{
+    if (j.autocorr) return 1;                 // M only (stored in slot 0)
+    return (j.mode & MODE_MSCC) ? 5 : 2;      // F, R [, M, Mp, FM]
+}
+
+extern "C" void pmb_batch_free(pmb_ctx* c, pmb_batch* b)
+{
+    if (!b) return;
+    if (c) {
+        cudaSetDevice(c->device);
+        if (b->d_in) cudaFreeAsync(b->d_in, c->stream);
+        if (b->d_bits) cudaFreeAsync(b->d_bits, c->stream);
+        if (b->d_counters) cudaFreeAsync(b->d_counters, c->stream);
+        if (b->d_jobs) cudaFreeAsync(b->d_jobs, c->stream);
+        if (b->d_err) cudaFreeAsync(b->d_err, c->stream);
+        if (b->d_long) cudaFreeAsync(b->d_long, c->stream);
+        cudaStreamSynchronize(c->stream);
+    }
+    delete b;
+}
+
+// One shift-window launch per (mode present in the batch) x (chunk of <= 64 units).
+// A unit chunk starting at unit u0 is the same kernel on moved base pointers:
+// R + 4*u0 words, Mp - 4*u0 words, counters + 128*u0.
+static int plan_windows(pmb_ctx* c, pmb_batch* b)
+{
+    const size_t n = b->jobs.size();
+    const uint32_t H = b->halo_words, T = b->tile_words;
+    const uint32_t UNIT_CHUNK = 64;
+    std::vector<WindowJob> table;
+    size_t jobs_used = 0;
+    for (int mode = 1; mode <= 3; mode++) {
+        std::vector<size_t> members;
+        for (size_t i = 0; i < n; i++)
+            if (b->jobs[i].mode == mode) members.push_back(i);
+        if (members.empty()) continue;
+        for (uint32_t u0 = 0; u0 < b->n_units; u0 += UNIT_CHUNK) {
+            const uint32_t nu = std::min(UNIT_CHUNK, b->n_units - u0);
+            table.clear();
+            uint32_t tiles = 0;
+            for (size_t i : members) {
+                JobPlan& j = b->jobs[i];
+                uint32_t* base = b->d_bits + j.bits;
+                auto arr = [&](int slot) { return base + (size_t)slot * j.array_words + H; };
+                WindowJob w{};
+                if (j.autocorr) {   // sum_j M[j] M[j+k]: the NCC kernel on F = R = M, into the dmp slot
+                    w.F = arr(0);
+                    w.R = arr(0) + 4 * u0;
+                    w.counters = b->d_counters + (i * PMB_NCOUNTERS + C_DMP) * b->stride + 128 * u0;
+                } else {
+                    w.F = arr(A_F);
+                    w.R = arr(A_R) + 4 * u0;
+                    if (j.mode & MODE_MSCC) {
+                        w.FM = arr(A_FM);
+                        w.M = arr(A_M);
+                        w.Mp = arr(A_MP) - 4 * u0;
+                    }
+                    w.counters = b->d_counters + i * PMB_NCOUNTERS * b->stride + 128 * u0;
+                }
+                w.tile_begin = tiles;
+                w.n_tiles = j.n_tiles;
+                tiles += j.n_tiles;
+                table.push_back(w);
+            }
+            if (jobs_used + table.size() > b->d_jobs_count) { c->err = "job table overflow"; return PMB_ERR_ARG; }
+            WindowJob* d_tab = b->d_jobs + jobs_used;
+            jobs_used += table.size();
+            // pageable source: staged before the call returns, so `table` can be reused
+            CU_TRY(c, cudaMemcpyAsync(d_tab, table.data(), table.size() * sizeof(WindowJob),
+                                      cudaMemcpyHostToDevice, c->stream));
+            WinLaunch L{};
+            L.mode = mode;
+            L.P.jobs = d_tab;
+            L.P.n_jobs = (uint32_t)table.size();
+            L.P.total_tiles = tiles;
+            L.P.tile_words = T;
+            L.P.n_units = nu;
+            L.warps = (uint32_t)std::max(1, std::min(c->block_warps, 16));
+            L.P.n_parts = L.warps / gcd_u32(nu, L.warps);
+            L.P.n_shifts = b->n_shifts;
+            L.P.stride = b->stride;
+            L.P.halo_words = 4 * nu + 4;
+            uint32_t blocks = c->grid_blocks > 0 ? (uint32_t)c->grid_blocks : (uint32_t)c->num_sms;
+            L.blocks = std::max(1u, std::min(blocks, tiles));
+            L.smem = window_smem_bytes(T, L.P.halo_words, nu);
+            L.pairs = (uint64_t)tiles * T * nu * 128;
+            b->launches.push_back(L);
+        }
+    }
+    return PMB_OK;
+}
+
+extern "C" int pmb_batch_prepare(pmb_ctx* c, const pmb_chrom_args* a, uint32_t n, pmb_batch** out)
+{
+    if (!c || !a || !out || n == 0) return PMB_ERR_ARG;
+    *out = nullptr;
+    CU_TRY(c, cudaSetDevice(c->device));
+    pmb_batch* b = new pmb_batch();
+    struct Guard {   // frees the batch on any early return
+        pmb_ctx* c; pmb_batch* b; bool armed = true;
+        ~Guard() { if (armed) pmb_batch_free(c, b); }
+    } guard{c, b};
+
+    b->read_len = a[0].read_len;
+    b->max_shift = a[0].max_shift;
+    b->n_shifts = b->max_shift + 1;
+    b->n_units = (b->n_shifts + 127) / 128;
+    b->stride = 128 * b->n_units;
+    b->halo_words = 4 * b->n_units + 4;
+    if (b->read_len == 0) { c->err = "read_len must be >= 1"; return PMB_ERR_ARG; }
+
+    // pass 1: ranges and the total amount of work, to pick the tile size
+    uint64_t total_words = 0;
+    b->jobs.resize(n);
+    for (uint32_t i = 0; i < n; i++) {
+        JobPlan& j = b->jobs[i];
+        j.a = a[i];
+        if (a[i].read_len != b->read_len || a[i].max_shift != b->max_shift) {
+            c->err = "all chromosomes of a batch must share read_len and max_shift";
+            return PMB_ERR_ARG;
+        }
+        j.nbits = a[i].chrom_len + a[i].read_len + a[i].max_shift + PMB_EXTRA_ALLOCATE_SIZE;
+        if (j.nbits >= (1ull << 32)) {
+            c->err = "chromosome too long for 32-bit positions";
+            return PMB_ERR_ARG;
+        }
+        j.autocorr = (a[i].flags & PMB_FLAG_AUTOCORR) != 0;
+        j.mode = (a[i].flags & PMB_FLAG_NCC ? MODE_NCC : 0) | (a[i].flags & PMB_FLAG_MSCC ? MODE_MSCC : 0);
+        if (j.autocorr) j.mode = MODE_NCC;
+        if (j.mode == 0) { c->err = "flags select nothing to compute"; return PMB_ERR_ARG; }
+        if ((j.mode & MODE_MSCC) && a[i].n_intervals && (!a[i].map_begin || !a[i].map_end)) {
+            c->err = "interval arrays missing"; return PMB_ERR_ARG;
+        }
+        if ((a[i].n_fwd && !a[i].fwd_pos) || (a[i].n_rev && !a[i].rev_pos)) {
+            c->err = "position arrays missing"; return PMB_ERR_ARG;
+        }
+        j.lo = (int64_t)a[i].range_lo;
+        j.hi = a[i].range_hi ? (int64_t)a[i].range_hi : (int64_t)j.nbits;
+        if (j.hi > (int64_t)j.nbits) j.hi = (int64_t)j.nbits;
+        if (j.lo > j.hi) j.lo = j.hi;
+        if (j.autocorr && (j.lo != 0 || j.hi != (int64_t)j.nbits)) {
+            c->err = "PMB_FLAG_AUTOCORR needs the whole chromosome range"; return PMB_ERR_ARG;
+        }
+        j.origin_word = (j.lo >> 5) & ~(int64_t)3;
+        total_words += (uint64_t)(((j.hi + 31) >> 5) - j.origin_word);
+    }
+    const uint32_t blocks = c->grid_blocks > 0 ? (uint32_t)c->grid_blocks : (uint32_t)c->num_sms;
+    uint32_t T = 1024;
+    if (c->tile_words > 0) T = (uint32_t)c->tile_words;
+    else while (T > 64 && total_words / T < 8ull * blocks) T >>= 1;
+    if (T < 64 || (T & 63)) { c->err = "tile_words must be a multiple of 64"; return PMB_ERR_ARG; }
+    b->tile_words = T;
+
+    // pass 2: layout
+    size_t in_words = 0, bits_words = 0;
+    for (uint32_t i = 0; i < n; i++) {
+        JobPlan& j = b->jobs[i];
+        uint64_t body = (uint64_t)(((j.hi + 31) >> 5) - j.origin_word);
+        j.n_tiles = (uint32_t)((body + T - 1) / T);
+        if (j.n_tiles == 0) j.n_tiles = 1;
+        j.body_words = (uint64_t)j.n_tiles * T;
+        j.array_words = 2 * (size_t)b->halo_words + j.body_words;
+        j.bits = bits_words;
+        bits_words += (size_t)arrays_of(j) * j.array_words;
+        auto take = [&](uint64_t cnt) { size_t o = in_words; in_words += (cnt + 3) & ~3ull; return o; };
+        if (!j.autocorr) { j.in_fwd = take(j.a.n_fwd); j.in_rev = take(j.a.n_rev); }
+        if ((j.mode & MODE_MSCC) || j.autocorr) { j.in_mb = take(j.a.n_intervals); j.in_me = take(j.a.n_intervals); }
+    }
+    b->in_words = in_words;
+    b->bits_words = bits_words;
+    b->counter_words = (size_t)n * PMB_NCOUNTERS * b->stride + (size_t)n * 2;
+
+    CU_TRY(c, cudaMallocAsync((void**)&b->d_in, std::max<size_t>(in_words, 4) * 4, c->stream));
+    CU_TRY(c, cudaMallocAsync((void**)&b->d_bits, std::max<size_t>(bits_words, 4) * 4, c->stream));
+    CU_TRY(c, cudaMallocAsync((void**)&b->d_counters, b->counter_words * 8, c->stream));
+    CU_TRY(c, cudaMallocAsync((void**)&b->d_err, 16, c->stream));
+    uint64_t max_iv = 0;
+    for (auto& j : b->jobs) max_iv = std::max<uint64_t>(max_iv, j.a.n_intervals);
+    b->long_cap = (size_t)max_iv + 4;
+    CU_TRY(c, cudaMallocAsync((void**)&b->d_long, b->long_cap * 4, c->stream));
+    // window job tables: one per unit chunk (filled in execute)
+    b->d_jobs_count = (size_t)n * ((b->n_units + 63) / 64 + 1) * 3;
+    CU_TRY(c, cudaMallocAsync((void**)&b->d_jobs, b->d_jobs_count * sizeof(WindowJob), c->stream));
+
+    // H2D of the packed inputs
+    for (auto& j : b->jobs) {
+        auto up = [&](size_t off, const uint32_t* src, uint64_t cnt) -> cudaError_t {
+            if (!cnt) return cudaSuccess;
+            return cudaMemcpyAsync(b->d_in + off, src, cnt * 4, cudaMemcpyHostToDevice, c->stream);
+        };
+        if (!j.autocorr) {
+            CU_TRY(c, up(j.in_fwd, j.a.fwd_pos, j.a.n_fwd));
+            CU_TRY(c, up(j.in_rev, j.a.rev_pos, j.a.n_rev));
+        }
+        if ((j.mode & MODE_MSCC) || j.autocorr) {
+            CU_TRY(c, up(j.in_mb, j.a.map_begin, j.a.n_intervals));
+            CU_TRY(c, up(j.in_me, j.a.map_end, j.a.n_intervals));
+        }
+        j.a.fwd_pos = j.a.rev_pos = j.a.map_begin = j.a.map_end = nullptr;   // borrowed no longer
+    }
+    {
+        int rc = plan_windows(c, b);
+        if (rc != PMB_OK) return rc;
+    }
+    CU_TRY(c, cudaStreamSynchronize(c->stream));   // host arrays may be released by the caller
+    guard.armed = false;
+    *out = b;
+    return PMB_OK;
+}
+
+// ------------------------------------------------------------------ batch: execute
+template <int MODE>
+static cudaError_t launch_window(pmb_ctx* c, int variant, const WindowParams& P, dim3 grid, dim3 block,
+                                 size_t smem)
+{
+    // variant -> carry-save level of (ncc, dmp, mfwd, mrev, mscc)
+#define PMB_LAUNCH(LV)                                                                            \
+    do {                                                                                          \
+        auto k = shift_window_kernel<MODE, LV>;                                                   \
+        cudaError_t e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize,      \
+                                             (int)smem);                                          \
+        if (e != cudaSuccess) return e;                                                           \
+        k<<<grid, block, smem, c->stream>>>(P);                                                   \
+        return cudaGetLastError();                                                                \
+    } while (0)
+    using V0 = Levels<0, 0, 0, 0, 0>;   // plain popc everywhere (POPC-pipe bound)
+    using V1 = Levels<1, 1, 1, 1, 1>;   // pair carry-save everywhere
+    using V2 = Levels<2, 2, 2, 2, 2>;   // quad carry-save everywhere
+    using V3 = Levels<1, 0, 1, 1, 1>;   // mixes, to balance the ALU and POPC pipes
+    using V4 = Levels<1, 0, 0, 1, 1>;
+    using V5 = Levels<0, 1, 1, 0, 0>;
+    switch (variant) {
+        case 0: PMB_LAUNCH(V0);
+        case 2: PMB_LAUNCH(V2);
+        case 3: PMB_LAUNCH(V3);
+        case 4: PMB_LAUNCH(V4);
+        case 5: PMB_LAUNCH(V5);
+        case 1:
+        default: PMB_LAUNCH(V1);
+    }
+#undef PMB_LAUNCH
+}
+
+extern "C" int pmb_batch_execute(pmb_ctx* c, pmb_batch* b)
+{
+    if (!c || !b) return PMB_ERR_ARG;
+    CU_TRY(c, cudaSetDevice(c->device));
+    cudaStream_t st = c->stream;
+    const uint32_t H = b->halo_words;
+    const int64_t NEG = -(1ll << 40), POS = (1ll << 40);
+    uint32_t launches = 0;
+
+    CU_TRY(c, cudaEventRecord(c->ev[0], st));
+    CU_TRY(c, cudaMemsetAsync(b->d_bits, 0, std::max<size_t>(b->bits_words, 4) * 4, st));
+    CU_TRY(c, cudaMemsetAsync(b->d_counters, 0, b->counter_words * 8, st));
+    CU_TRY(c, cudaMemsetAsync(b->d_err, 0, 16, st));
+    const size_t n = b->jobs.size();
+    unsigned long long* d_totals = b->d_counters + n * PMB_NCOUNTERS * b->stride;
+
+    auto blocks_for = [&](uint64_t items, int per_block) {
+        uint64_t g = (items + per_block - 1) / per_block;
+        return (unsigned)std::min<uint64_t>(std::max<uint64_t>(g, 1), (uint64_t)c->num_sms * 16);
+    };
+
+    for (size_t i = 0; i < n; i++) {
+        JobPlan& j = b->jobs[i];
+        Geometry g;
+        g.origin_bit = j.origin_word * 32;
+        g.halo_bits = (int64_t)H * 32;
+        g.total_bits = (int64_t)j.array_words * 32;
+        uint32_t* base = b->d_bits + j.bits;
+        auto arr = [&](int slot) { return base + (size_t)slot * j.array_words; };
+
+        if (j.autocorr) {
+            uint32_t* M = arr(0);
+            if (j.a.n_intervals) {
+                CU_TRY(c, cudaMemsetAsync(b->d_long, 0, 4, st));
+                fill_intervals_kernel<<<blocks_for(j.a.n_intervals, 8), 256, 0, st>>>(
+                    M, g, b->d_in + j.in_mb, b->d_in + j.in_me, j.a.n_intervals, 0, NEG, POS, j.nbits,
+                    b->d_err, b->d_long + 1, b->d_long);
+                fill_long_kernel<<<c->num_sms * 4, 256, 0, st>>>(M, g, b->d_in + j.in_mb,
+                                                                 b->d_in + j.in_me, 0, NEG, POS,
+                                                                 b->d_long + 1, b->d_long);
+                launches += 2;
+            }
+            continue;
+        }
+        if (j.a.n_fwd) {
+            scatter_bits_kernel<<<blocks_for(j.a.n_fwd, 256), 256, 0, st>>>(
+                arr(A_F), g, b->d_in + j.in_fwd, j.a.n_fwd, j.lo, j.hi, j.nbits, b->d_err);
+            launches++;
+        }
+        if (j.a.n_rev) {
+            scatter_bits_kernel<<<blocks_for(j.a.n_rev, 256), 256, 0, st>>>(
+                arr(A_R), g, b->d_in + j.in_rev, j.a.n_rev, NEG, POS, j.nbits, b->d_err);
+            launches++;
+        }
+        if ((j.mode & MODE_MSCC) && j.a.n_intervals) {
+            for (int pass = 0; pass < 2; pass++) {
+                uint32_t* dst = arr(pass == 0 ? A_M : A_MP);
+                int64_t down = pass == 0 ? 0 : (int64_t)b->read_len - 1;
+                int64_t clo = pass == 0 ? j.lo : NEG, chi = pass == 0 ? j.hi : POS;
+                CU_TRY(c, cudaMemsetAsync(b->d_long, 0, 4, st));
+                fill_intervals_kernel<<<blocks_for(j.a.n_intervals, 8), 256, 0, st>>>(
+                    dst, g, b->d_in + j.in_mb, b->d_in + j.in_me, j.a.n_intervals, down, clo, chi,
+                    j.nbits, b->d_err, b->d_long + 1, b->d_long);
+                fill_long_kernel<<<c->num_sms * 4, 256, 0, st>>>(dst, g, b->d_in + j.in_mb,
+                                                                 b->d_in + j.in_me, down, clo, chi,
+                                                                 b->d_long + 1, b->d_long);
+                launches += 2;
+            }
+        }
+        const bool mscc = (j.mode & MODE_MSCC) != 0;
+        prep_kernel<<<blocks_for(j.body_words, 1024), 256, 0, st>>>(
+            arr(A_F) + H, mscc ? arr(A_M) + H : nullptr, mscc ? arr(A_FM) + H : nullptr, arr(A_R) + H,
+            j.body_words, g.origin_bit, j.lo, j.hi, d_totals + 2 * i);
+        launches++;
+    }
+    CU_TRY(c, cudaGetLastError());
+    CU_TRY(c, cudaEventRecord(c->ev[1], st));
+
+    // shift-window launches planned by pmb_batch_prepare
+    uint32_t window_launches = 0;
+    uint64_t pairs = 0;
+    for (const WinLaunch& L : b->launches) {
+        cudaError_t e;
+        int variant = c->variant < 0 ? 1 : c->variant;
+        dim3 grid(L.blocks), block(L.warps * 32);
+        if (L.mode == MODE_NCC) e = launch_window<MODE_NCC>(c, variant, L.P, grid, block, L.smem);
+        else if (L.mode == MODE_MSCC) e = launch_window<MODE_MSCC>(c, variant, L.P, grid, block, L.smem);
+        else e = launch_window<MODE_BOTH>(c, variant, L.P, grid, block, L.smem);
+        CU_TRY(c, e);
+        window_launches++;
+        pairs += L.pairs;
+    }
+    CU_TRY(c, cudaEventRecord(c->ev[2], st));
+    c->timing.launches = launches + window_launches;
+    c->timing.window_launches = window_launches;
+    c->timing.window_word_shift_pairs = pairs;
+    c->timing.build_ms = c->timing.window_ms = c->timing.total_ms = -1.f;   // resolved lazily
+    return PMB_OK;
+}
+
+// ------------------------------------------------------------------ batch: fetch
+extern "C" int pmb_batch_counters(pmb_ctx* c, pmb_batch* b, void** dev_ptr, uint64_t* n_int64,
+                                  uint32_t* stride)
+{
+    if (!c || !b) return PMB_ERR_ARG;
+    if (dev_ptr) *dev_ptr = (void*)b->d_counters;
+    if (n_int64) *n_int64 = (uint64_t)b->counter_words;
+    if (stride) *stride = b->stride;
+    return PMB_OK;
+}
+
+extern "C" int pmb_batch_fetch(pmb_ctx* c, pmb_batch* b, pmb_chrom_out* o)
+{
+    if (!c || !b || !o) return PMB_ERR_ARG;
+    CU_TRY(c, cudaSetDevice(c->device));
+    const size_t bytes = b->counter_words * 8 + 16;
+    if (c->h_stage_bytes < bytes) {
+        if (c->h_stage) cudaFreeHost(c->h_stage);
+        c->h_stage = nullptr;
+        c->h_stage_bytes = 0;
+        CU_TRY(c, cudaHostAlloc(&c->h_stage, bytes, cudaHostAllocDefault));
+        c->h_stage_bytes = bytes;
+    }
+    int64_t* h = (int64_t*)c->h_stage;
+    int* h_err = (int*)((char*)c->h_stage + b->counter_words * 8);
+    CU_TRY(c, cudaMemcpyAsync(h, b->d_counters, b->counter_words * 8, cudaMemcpyDeviceToHost, c->stream));
+    CU_TRY(c, cudaMemcpyAsync(h_err, b->d_err, 4, cudaMemcpyDeviceToHost, c->stream));
+    CU_TRY(c, cudaStreamSynchronize(c->stream));
+    if (*h_err) {
+        c->err = "a read position or mappability interval lies beyond chrom_len + read_len + "
+                 "max_shift + 100 bits";
+        return PMB_ERR_RANGE;
+    }
+    const size_t n = b->jobs.size(), S = b->n_shifts;
+    const int64_t* totals = h + n * PMB_NCOUNTERS * b->stride;
+    for (size_t i = 0; i < n; i++) {
+        const int64_t* base = h + i * PMB_NCOUNTERS * b->stride;
+        const JobPlan& j = b->jobs[i];
+        o[i].fwd_total = totals[2 * i];
+        o[i].rev_total = totals[2 * i + 1];
+        auto put = [&](int64_t* dst, int slot) {
+            if (dst) memcpy(dst, base + (size_t)slot * b->stride, S * sizeof(int64_t));
+        };
+        if (j.autocorr) { put(o[i].dmp, C_DMP); continue; }
+        if (j.mode & MODE_NCC) put(o[i].ncc, C_NCC);
+        if (j.mode & MODE_MSCC) {
+            put(o[i].dmp, C_DMP); put(o[i].mfwd, C_MFWD); put(o[i].mrev, C_MREV); put(o[i].mscc, C_MSCC);
+        }
+    }
+    return PMB_OK;
+}
+
+// ------------------------------------------------------------------ one-call forms
+extern "C" int pmb_run_batch(pmb_ctx* c, const pmb_chrom_args* a, pmb_chrom_out* o, uint32_t n)
+{
+    pmb_batch* b = nullptr;
+    int rc = pmb_batch_prepare(c, a, n, &b);
+    if (rc != PMB_OK) return rc;
+    rc = pmb_batch_execute(c, b);
+    if (rc == PMB_OK) rc = pmb_batch_fetch(c, b, o);
+    pmb_batch_free(c, b);
+    return rc;
+}
+
+extern "C" int pmb_run_chrom(pmb_ctx* c, const pmb_chrom_args* a, pmb_chrom_out* o)
+{
+    return pmb_run_batch(c, a, o, 1);
+}
+
+// ------------------------------------------------------------------ pipe calibration
+extern "C" int pmb_pipe_probe(pmb_ctx* c, int what, double* ops_per_sec, float* ms_out)
+{
+    if (!c || !ops_per_sec) return PMB_ERR_ARG;
+    CU_TRY(c, cudaSetDevice(c->device));
+    uint32_t* d_sink = nullptr;
+    CU_TRY(c, cudaMallocAsync((void**)&d_sink, 4096, c->stream));
+    const int blocks = c->num_sms * 4, threads = 512, iters = 4096;
+    double ops_per_thread = 0;
+    float best = 1e30f;
+    for (int rep = 0; rep < 4; rep++) {
+        CU_TRY(c, cudaEventRecord(c->ev[0], c->stream));
+        ops_per_thread = launch_probe(what, blocks, threads, iters, d_sink, c->stream);
+        CU_TRY(c, cudaGetLastError());
+        CU_TRY(c, cudaEventRecord(c->ev[3], c->stream));
+        CU_TRY(c, cudaEventSynchronize(c->ev[3]));
+        float ms = 0;
+        CU_TRY(c, cudaEventElapsedTime(&ms, c->ev[0], c->ev[3]));
+        if (rep > 0) best = std::min(best, ms);
+    }
+    CU_TRY(c, cudaFreeAsync(d_sink, c->stream));
+    if (ops_per_thread <= 0) { c->err = "unknown probe"; return PMB_ERR_ARG; }
+    *ops_per_sec = ops_per_thread * (double)blocks * threads / (best * 1e-3);
+    if (ms_out) *ms_out = best;
+    return PMB_OK;
+}

@@ -1,0 +1,168 @@
+// pmb_build.cuh -- bit-array build kernels (sm_100a).
+//
+// Device layout of one chromosome job (all five arrays share one geometry):
+//
+//     [ halo H words | body Wpad words | halo H words ]      32-bit words, LSB-first,
+//                    ^ origin word `ow` of the chromosome     bit j of the reference's
+//                                                             64-bit array == bit j here
+// "array bit index" a = (chromosome bit) - 32*ow + 32*H.
+//   F   forward 5' ends, only bits inside the counted range [lo, hi)
+//   R   reverse 5' ends, whole window (halo included: R[j+k] is read up to hi+max_shift)
+//   M   mappable positions, only bits inside [lo, hi)
+//   Mp  M moved down by read_len-1 bits: Mp[x] = M[x + read_len-1], whole window
+//       (so that D_k[j] = M[j] & Mp[j-k], a plain "shift by k" like R)
+//   FM  F & M (written by prep)
+// Halos are zero, which is exactly the reference's zero-fill when it shifts arrays
+// (external/BitArray/bit_array.c:1953-2011).
+#pragma once
+#include <stdint.h>
+
+namespace pmb {
+
+struct Geometry {
+    int64_t origin_bit;   // 32*ow: chromosome bit of body word 0
+    int64_t halo_bits;    // 32*H
+    int64_t total_bits;   // 32*(H + Wpad + H)
+};
+
+// chromosome bit -> array bit, or -1 when outside the allocated window
+__device__ __forceinline__ int64_t to_array_bit(const Geometry& g, int64_t chrom_bit)
+{
+    int64_t a = chrom_bit - g.origin_bit + g.halo_bits;
+    return (a < 0 || a >= g.total_bits) ? -1 : a;
+}
+
+// K1: one thread per read position.  bit_array_set_bit (bit_array.c:668) as an
+// idempotent atomicOr: duplicates collapse exactly like mscc.pyx:388-393, :416-418.
+// Positions are sorted, so neighbouring threads hit the same or adjacent words.
+// Only positions with clip_lo <= p < clip_hi are set (F: the counted range;
+// R: everything that falls in the window).  p >= nbits raises the error flag
+// (the reference would abort on its assert).
+__global__ void scatter_bits_kernel(uint32_t* __restrict__ arr, Geometry g,
+                                    const uint32_t* __restrict__ pos, uint64_t n,
+                                    int64_t clip_lo, int64_t clip_hi, uint64_t nbits,
+                                    int* __restrict__ err_flag)
+{
+    uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+    for (; i < n; i += stride) {
+        int64_t p = pos[i];
+        if ((uint64_t)p >= nbits) { atomicExch(err_flag, 1); continue; }
+        if (p < clip_lo || p >= clip_hi) continue;
+        int64_t a = to_array_bit(g, p);
+        if (a < 0) continue;
+        atomicOr(arr + (a >> 5), 1u << (a & 31));
+    }
+}
+
+// K2: one warp per mappable interval (begin, end): chromosome bits begin+1 .. end
+// (mscc.pyx:343-344 -> bit_array_set_region, bit_array.c:423-479), moved down by
+// `shift_down` bits (0 for M, read_len-1 for Mp) and clipped to [clip_lo, clip_hi).
+// Edge words use atomicOr with the partial mask, interior words a plain store.
+// Intervals longer than LONG_WORDS only write their two edge words here and are
+// queued for fill_long_kernel, which spreads the interior over the whole grid.
+constexpr int LONG_WORDS = 4096;
+
+__device__ __forceinline__ bool interval_span(const Geometry& g, uint32_t begin, uint32_t end,
+                                              int64_t shift_down, int64_t clip_lo, int64_t clip_hi,
+                                              int64_t& a0, int64_t& a1)
+{
+    int64_t s = (int64_t)begin + 1 - shift_down;   // first bit (inclusive)
+    int64_t e = (int64_t)end - shift_down;         // last bit (inclusive)
+    if (s < clip_lo) s = clip_lo;
+    if (e >= clip_hi) e = clip_hi - 1;
+    if (e < s) return false;
+    a0 = s - g.origin_bit + g.halo_bits;
+    a1 = e - g.origin_bit + g.halo_bits;
+    if (a0 < 0) a0 = 0;
+    if (a1 >= g.total_bits) a1 = g.total_bits - 1;
+    return a1 >= a0;
+}
+
+__global__ void fill_intervals_kernel(uint32_t* __restrict__ arr, Geometry g,
+                                      const uint32_t* __restrict__ begins,
+                                      const uint32_t* __restrict__ ends, uint64_t n,
+                                      int64_t shift_down, int64_t clip_lo, int64_t clip_hi,
+                                      uint64_t nbits, int* __restrict__ err_flag,
+                                      uint32_t* __restrict__ long_list, uint32_t* __restrict__ long_count)
+{
+    const int lane = threadIdx.x & 31;
+    uint64_t warp = ((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    uint64_t nwarps = ((uint64_t)gridDim.x * blockDim.x) >> 5;
+    for (uint64_t i = warp; i < n; i += nwarps) {
+        uint32_t b = begins[i], e = ends[i];
+        if (e <= b) continue;                       // zero-length region
+        if ((uint64_t)e >= nbits) { if (lane == 0) atomicExch(err_flag, 1); continue; }
+        int64_t a0, a1;
+        if (!interval_span(g, b, e, shift_down, clip_lo, clip_hi, a0, a1)) continue;
+        int64_t fw = a0 >> 5, lw = a1 >> 5;
+        uint32_t fmask = 0xFFFFFFFFu << (a0 & 31);
+        uint32_t lmask = 0xFFFFFFFFu >> (31 - (a1 & 31));
+        if (fw == lw) {
+            if (lane == 0) atomicOr(arr + fw, fmask & lmask);
+            continue;
+        }
+        if (lane == 0) atomicOr(arr + fw, fmask);
+        if (lane == 1) atomicOr(arr + lw, lmask);
+        if (lw - fw - 1 > LONG_WORDS) {
+            if (lane == 0) long_list[atomicAdd(long_count, 1u)] = (uint32_t)i;
+            continue;
+        }
+        for (int64_t w = fw + 1 + lane; w < lw; w += 32) arr[w] = 0xFFFFFFFFu;
+    }
+}
+
+__global__ void fill_long_kernel(uint32_t* __restrict__ arr, Geometry g,
+                                 const uint32_t* __restrict__ begins,
+                                 const uint32_t* __restrict__ ends,
+                                 int64_t shift_down, int64_t clip_lo, int64_t clip_hi,
+                                 const uint32_t* __restrict__ long_list,
+                                 const uint32_t* __restrict__ long_count)
+{
+    uint32_t n = *long_count;
+    uint64_t tid = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    uint64_t nth = (uint64_t)gridDim.x * blockDim.x;
+    for (uint32_t q = 0; q < n; q++) {
+        uint32_t i = long_list[q];
+        int64_t a0, a1;
+        if (!interval_span(g, begins[i], ends[i], shift_down, clip_lo, clip_hi, a0, a1)) continue;
+        int64_t fw = a0 >> 5, lw = a1 >> 5;
+        for (int64_t w = fw + 1 + (int64_t)tid; w < lw; w += (int64_t)nth) arr[w] = 0xFFFFFFFFu;
+    }
+}
+
+// prep: FM = F & M over the body, strand totals over the counted range
+// (bit_array_num_bits_set, bit_array.c:962-978 -> __popc).  F is already clipped to
+// the range; R is masked here so that halo bits are not counted twice across shards.
+__global__ void prep_kernel(const uint32_t* __restrict__ F, const uint32_t* __restrict__ M,
+                            uint32_t* __restrict__ FM, const uint32_t* __restrict__ R,
+                            uint64_t body_words, int64_t origin_bit, int64_t lo, int64_t hi,
+                            unsigned long long* __restrict__ totals /* [2]: fwd, rev */)
+{
+    uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+    unsigned int cf = 0, cr = 0;
+    for (; i < body_words; i += stride) {
+        uint32_t f = F[i];
+        if (M) FM[i] = f & M[i];
+        cf += __popc(f);
+        int64_t b0 = origin_bit + (int64_t)(i << 5);   // chromosome bit of this word's bit 0
+        uint32_t mask = 0xFFFFFFFFu;
+        if (b0 + 32 <= lo || b0 >= hi) mask = 0;
+        else {
+            if (b0 < lo) mask &= 0xFFFFFFFFu << (lo - b0);
+            if (b0 + 32 > hi) mask &= 0xFFFFFFFFu >> (b0 + 32 - hi);
+        }
+        cr += __popc(R[i] & mask);
+    }
+    for (int o = 16; o; o >>= 1) {
+        cf += __shfl_xor_sync(0xFFFFFFFFu, cf, o);
+        cr += __shfl_xor_sync(0xFFFFFFFFu, cr, o);
+    }
+    if ((threadIdx.x & 31) == 0) {
+        if (cf) atomicAdd(totals, (unsigned long long)cf);
+        if (cr) atomicAdd(totals + 1, (unsigned long long)cr);
+    }
+}
+
+}  // namespace pmb

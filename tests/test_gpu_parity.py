@@ -1,0 +1,241 @@
+"""Parity of the CUDA path (through the C ABI) against the CPU oracle and the reference's
+vectors.  Integer counts must be bit-exact; the derived float64 curves are checked against
+the reference's golden tables with the north_star tolerance (1e-9 relative, written below).
+"""
+import numpy as np
+import pytest
+
+import helpers
+from oracle import cc_oracle
+from pymasc_b200 import CCBitArrayCalculator, _shim, synth
+from pymasc_b200.exceptions import PositionOutOfRange
+
+pytestmark = pytest.mark.gpu
+RTOL = 1e-9
+
+
+@pytest.fixture(scope="module")
+def dev():
+    d = _shim.Device(0)
+    yield d
+    d.close()
+
+
+def check_job(dev, L, rl, D, fwd, rev, b=None, e=None, flags=None, lo=0, hi=0):
+    if flags is None:
+        flags = _shim.FLAG_NCC | (_shim.FLAG_MSCC if b is not None else 0)
+    got = dev.run_batch([_shim.Job(L, rl, D, flags, fwd, rev, b, e, lo, hi)])[0]
+    mscc = bool(flags & _shim.FLAG_MSCC)
+    want = cc_oracle.chrom_counts(L, rl, D, fwd, rev, b if mscc else None, e if mscc else None,
+                                  skip_ncc=not flags & _shim.FLAG_NCC, lo=lo, hi=hi or None)
+    assert sorted(got) == sorted(want)
+    for k in want:
+        assert np.array_equal(np.asarray(got[k]), np.asarray(want[k])), k
+    return got
+
+
+def random_case(seed, L, rl, n_reads, with_track=True):
+    rng = np.random.default_rng(seed)
+    fwd = np.unique(rng.integers(1, L, size=n_reads)).astype(np.uint32)
+    rev = np.unique(rng.integers(rl, L + rl - 1, size=n_reads)).astype(np.uint32)
+    b = e = None
+    if with_track:
+        edges = np.sort(rng.choice(np.arange(0, L), size=2 * max(2, L // 700), replace=False))
+        b, e = edges[0::2].astype(np.uint32), edges[1::2].astype(np.uint32)
+    return fwd, rev, b, e
+
+
+@pytest.mark.parametrize("L,rl,D", [
+    (5000, 20, 100), (4097, 36, 127), (4096 - 36 - 128 - 100, 36, 128),   # word / unit edges
+    (70001, 36, 300), (131072, 50, 30), (131072, 50, 80), (99999, 25, 49),
+    (250000, 36, 1000), (60000, 101, 1300), (33, 5, 3),
+])
+def test_random_chromosomes_bit_exact(dev, L, rl, D):
+    fwd, rev, b, e = random_case(L + D, L, rl, max(10, L // 20))
+    check_job(dev, L, rl, D, fwd, rev, b, e)
+    check_job(dev, L, rl, D, fwd, rev)                                   # NCC only
+    check_job(dev, L, rl, D, fwd, rev, b, e, flags=_shim.FLAG_MSCC)      # skip_ncc
+
+
+def test_all_kernel_variants_agree(dev):
+    L, rl, D = 300000, 36, 500
+    fwd, rev, b, e = random_case(5, L, rl, 40000)
+    try:
+        for v in range(6):
+            dev.set_option("variant", v)
+            check_job(dev, L, rl, D, fwd, rev, b, e)
+            check_job(dev, L, rl, D, fwd, rev)
+    finally:
+        dev.set_option("variant", -1)
+
+
+@pytest.mark.parametrize("tile", [64, 256, 2048])
+def test_tile_sizes_agree(dev, tile):
+    L, rl, D = 500000, 36, 700
+    fwd, rev, b, e = random_case(6, L, rl, 30000)
+    try:
+        dev.set_option("tile_words", tile)
+        check_job(dev, L, rl, D, fwd, rev, b, e)
+    finally:
+        dev.set_option("tile_words", 0)
+
+
+def test_edge_inputs(dev):
+    L, rl, D = 10000, 36, 200
+    fwd, rev, b, e = random_case(9, L, rl, 500)
+    empty = np.zeros(0, np.uint32)
+    check_job(dev, L, rl, D, empty, rev, b, e)                 # no forward reads
+    check_job(dev, L, rl, D, fwd, empty, b, e)                 # no reverse reads
+    check_job(dev, L, rl, D, empty, empty, b, e)
+    check_job(dev, L, rl, D, fwd, rev, empty, empty)           # track without intervals
+    nbits = L + rl + D + 100
+    # reads and intervals in the very last positions of the array; fully mappable chromosome
+    check_job(dev, L, rl, D, np.array([1, L, nbits - 1], np.uint32),
+              np.array([rl, L + rl - 1, nbits - 1], np.uint32),
+              np.array([0], np.uint32), np.array([nbits - 1], np.uint32))
+    # duplicates collapse
+    check_job(dev, L, rl, D, np.array([5, 5, 5, 900], np.uint32), np.array([40, 40], np.uint32), b, e)
+    # a long interval (interior handled by the long-fill kernel)
+    check_job(dev, 400000, rl, D, fwd, rev, np.array([3, 300000], np.uint32),
+              np.array([290000, 399000], np.uint32))
+
+
+def test_out_of_range_is_an_error_code(dev):
+    L, rl, D = 1000, 20, 50
+    with pytest.raises(PositionOutOfRange):
+        dev.run_batch([_shim.Job(L, rl, D, _shim.FLAG_NCC, [5], [L + rl + D + 100])])
+    with pytest.raises(PositionOutOfRange):
+        dev.run_batch([_shim.Job(L, rl, D, _shim.FLAG_NCC | _shim.FLAG_MSCC, [5], [30], [1], [5000])])
+
+
+def test_position_shards_with_halos_add_up(dev):
+    """Shards [lo, hi) with device-built halos sum to the whole (config 4's decomposition)."""
+    L, rl, D = 600000, 36, 1000
+    fwd, rev, b, e = random_case(11, L, rl, 60000)
+    whole = check_job(dev, L, rl, D, fwd, rev, b, e)
+    nbits = L + rl + D + 100
+    cuts = [0, 150001, 300032, 449999, nbits]
+    parts = [check_job(dev, L, rl, D, fwd, rev, b, e, lo=a, hi=z) for a, z in zip(cuts[:-1], cuts[1:])]
+    for k in whole:
+        assert np.array_equal(np.asarray(whole[k]), sum(np.asarray(p[k]) for p in parts)), k
+
+
+def test_batch_of_mixed_jobs_and_autocorrelation(dev):
+    rl, D = 36, 300
+    jobs, wants = [], []
+    for i, L in enumerate([50000, 120000, 80000]):
+        fwd, rev, b, e = random_case(20 + i, L, rl, 4000)
+        if i == 1:
+            jobs.append(_shim.Job(L, rl, D, _shim.FLAG_NCC, fwd, rev))
+            wants.append(cc_oracle.chrom_counts(L, rl, D, fwd, rev))
+        else:
+            jobs.append(_shim.Job(L, rl, D, _shim.FLAG_NCC | _shim.FLAG_MSCC, fwd, rev, b, e))
+            wants.append(cc_oracle.chrom_counts(L, rl, D, fwd, rev, b, e))
+    _, _, b, e = random_case(30, 90000, rl, 10)
+    jobs.append(_shim.Job(90000, rl, D, _shim.FLAG_AUTOCORR, None, None, b, e))
+    wants.append({"dmp": cc_oracle.mappable_autocorr(90000, rl, D, b, e)})
+    outs = dev.run_batch(jobs)
+    for got, want in zip(outs, wants):
+        assert sorted(got) == sorted(want)
+        for k in want:
+            assert np.array_equal(np.asarray(got[k]), np.asarray(want[k])), k
+
+
+def test_large_max_shift_unit_chunks(dev):
+    """max_shift 9000 -> 71 units -> two unit-chunk launches on moved base pointers."""
+    L, rl, D = 200000, 36, 9000
+    fwd, rev, b, e = random_case(40, L, rl, 20000)
+    check_job(dev, L, rl, D, fwd, rev, b, e)
+
+
+def test_prepare_execute_fetch_is_repeatable(dev):
+    L, rl, D = 200000, 36, 400
+    fwd, rev, b, e = random_case(41, L, rl, 20000)
+    want = cc_oracle.chrom_counts(L, rl, D, fwd, rev, b, e)
+    batch = dev.prepare([_shim.Job(L, rl, D, 3, fwd, rev, b, e)])
+    for _ in range(3):
+        batch.execute()
+        got = batch.fetch()[0]
+        for k in want:
+            assert np.array_equal(np.asarray(got[k]), np.asarray(want[k])), k
+    t = dev.timing()
+    assert t["window_ms"] > 0 and t["launches"] >= 6
+    batch.free()
+
+
+# ----------------------------------------------------------------- the reference's own pins
+def test_fixture_golden_tables_through_the_calculator():
+    """configs[0]: tests/data ChIP-seq fixture, -d 300 -q 10 -r 36, against tests/golden."""
+    fx = helpers.load_fixture()
+    gold = helpers.load_golden_tables()
+    vec = helpers.load_ref_vectors()
+    feeder = helpers.ListFeeder({"chr1": (fx["map_begins"], fx["map_ends"])})
+    calc = CCBitArrayCalculator(300, 36, fx["references"], fx["lengths"], feeder)
+    calc.feed_batch("chr1", fx["pos"], fx["readlen"], fx["is_reverse"])
+    calc.finishup_calculation()
+    whole = calc.get_whole_result()
+    assert (whole.forward_sum, whole.reverse_sum, whole.genomelen) == (622, 670, 3137454505)
+    ncc, mscc = whole.chroms["chr1"], whole.mappable_chroms["chr1"]
+    rows = gold["nreads"]["chr1"][1:]
+    assert [int(x) for x in mscc.forward_sum] == [int(r.split("-")[0]) for r in rows]
+    assert [int(x) for x in mscc.reverse_sum] == [int(r.split("-")[1]) for r in rows]
+    assert mscc.mappable_len[35] == 19906
+    for got, want in ((ncc.cc, gold["cc"]["chr1"]), (mscc.cc, gold["mscc"]["chr1"])):
+        want = np.array(want)
+        assert np.max(np.abs(np.asarray(got) - want) / np.abs(want)) <= RTOL
+    got = helpers.snapshot_whole(whole)
+    want = vec["fixture_both"]
+    for k in ("chroms", "mappable_chroms"):
+        got[k] = {c: v for c, v in got[k].items() if c in want[k]}
+    helpers.assert_snapshots_equal(got, want, rtol=RTOL)
+
+
+@pytest.mark.parametrize("spec", helpers.TOY_SPECS, ids=lambda s: s["name"])
+def test_toy_cases_through_the_calculator(spec):
+    toy = helpers.make_toy(spec)
+    feeder = helpers.ListFeeder(toy["tracks"]) if toy["tracks"] is not None else None
+    calc = CCBitArrayCalculator(spec["D"], spec["rl"], toy["references"], toy["lengths"], feeder,
+                                spec["skip_ncc"])
+    for chrom, r in toy["reads"].items():
+        for p, l, rev in zip(r["pos"].tolist(), r["readlen"].tolist(), r["is_reverse"].tolist()):
+            (calc.feed_reverse_read if rev else calc.feed_forward_read)(chrom, p, l)
+    calc.finishup_calculation()
+    helpers.assert_snapshots_equal(helpers.snapshot_whole(calc.get_whole_result()),
+                                   helpers.load_ref_vectors()["toy_" + spec["name"]], rtol=RTOL)
+
+
+# ----------------------------------------------------------------- full-size properties
+def test_hg38_chr21_properties(dev):
+    """BASELINE config 2/3 shapes at full chromosome size (chr21 + chr22, max_shift 1000),
+    through size-independent properties: dmp symmetry (popc(D_k) depends on |rl-1-k| only),
+    k = 0 identities, shard additivity, and an oracle check on a window of shifts."""
+    rl, D = 36, 1000
+    # same read density as the 20 M-read genome
+    share = (46709983 + 50818468) / 3088269832.0
+    wl = synth.workload(n_reads=int(20_000_000 * share), chroms=["chr21", "chr22"], read_len=rl)
+    jobs = [_shim.Job(w["length"], rl, D, 3, w["fwd"], w["rev"], w["begins"], w["ends"]) for w in wl]
+    outs = dev.run_batch(jobs)
+    for w, o in zip(wl, outs):
+        dmp = o["dmp"]
+        for k in range(0, 2 * rl - 1):
+            assert dmp[k] == dmp[2 * (rl - 1) - k]                # |rl-1-k| symmetry
+        assert o["fwd_total"] == np.unique(w["fwd"]).size
+        assert o["rev_total"] == np.unique(w["rev"]).size
+        assert np.all(o["mscc"] <= np.minimum(o["mfwd"], o["mrev"]))
+        assert np.all(o["mscc"] <= o["ncc"]) and np.all(o["mfwd"] <= o["fwd_total"])
+        # k = 0: ncc[0] = |F & R| computed independently on the host
+        assert o["ncc"][0] == np.intersect1d(w["fwd"], w["rev"]).size
+    # shard additivity at full size, 3 uneven shards of chr21
+    w = wl[0]
+    nbits = w["length"] + rl + D + 100
+    cuts = [0, nbits // 3 + 5, 2 * nbits // 3 - 17, nbits]
+    parts = dev.run_batch([_shim.Job(w["length"], rl, D, 3, w["fwd"], w["rev"], w["begins"], w["ends"], a, z)
+                           for a, z in zip(cuts[:-1], cuts[1:])])
+    for k in ("ncc", "dmp", "mfwd", "mrev", "mscc", "fwd_total", "rev_total"):
+        assert np.array_equal(np.asarray(outs[0][k]), sum(np.asarray(p[k]) for p in parts)), k
+    # oracle on the same full-size chromosome, restricted to a 2 Mb range so it takes seconds
+    lo, hi = 10_000_000, 12_000_000
+    got = dev.run_batch([_shim.Job(w["length"], rl, D, 3, w["fwd"], w["rev"], w["begins"], w["ends"], lo, hi)])[0]
+    want = cc_oracle.chrom_counts(w["length"], rl, D, w["fwd"], w["rev"], w["begins"], w["ends"], lo=lo, hi=hi)
+    for k in want:
+        assert np.array_equal(np.asarray(got[k]), np.asarray(want[k])), k
