@@ -1,0 +1,480 @@
+#!/usr/bin/env python
+"""bench.py -- the correlation stage of PyMaSC's bit-array path on B200s (and the reference
+CPU arm beside it).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--mode both|ncc]
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N ... bench.py --gpus N ...
+
+Workload (BASELINE.json configs[2]/[1]): synthetic hg38-shaped genome -- 24
+chromosomes with the real hg38 lengths, 20 M single-end 36 bp ChIP-like reads, synthetic
+36-mer mappability track (~79 % mappable, ~1.6 M intervals), max_shift 1000, NCC+MSCC
+(``--mode ncc``: NCC only, configs[1]).  One STEP = the whole correlation stage of that genome:
+bit-array build (scatter + interval fill) and the shift-window kernel for all chromosomes, and
+for N > 1 the NCCL all-reduce of the per-shift counters.  N ranks cut the genome into N equal
+position ranges (pymasc_b200/sharding.py), so total work is fixed: strong scaling.
+
+metric   bit-position x shift evals/s: sum_chrom (L + read_len + max_shift + 100) x (max_shift+1)
+         evals per step / step time.
+value    inputs (packed uint32 positions / intervals) resident in HBM; device time by CUDA
+         events on the launching stream, max over ranks.
+e2e      same step through the C ABI from pinned HOST arrays: H2D + build + window
+         (+ all-reduce) + D2H of the counters inside the timed region.
+roofline popc pipe (the kernel is an integer AND+popcount reduction, not HBM- or tensor-bound):
+         algorithmic popc32 = evals x P / 32 (P = 5 NCC+MSCC, 1 NCC) / window-kernel time,
+         against the POPC issue rate measured live on the device (pmb_pipe_probe).
+cpu_baseline / --impl reference: the UNMODIFIED reference calculator compiled into oracle/_ref
+         (CCBitArrayCalculator, fed read by read as handler/read.py does), on a bounded sample.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+READ_LEN = 36
+MAX_SHIFT = 1000
+N_READS = 20_000_000
+METRIC = "bit-position x shift evals/s"
+UNIT = "evals/s"
+
+
+# ---------------------------------------------------------------------------- helpers
+def env_int(name, default):
+    try:
+        return int(os.environ.get(name, default))
+    except ValueError:
+        return default
+
+
+class ClockSampler(object):
+    """nvidia-smi clocks / throttle reasons DURING the timed region (B200_PROFILING.md)."""
+    FIELDS = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+              "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+              "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.proc, self.lines = index, None, []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.FIELDS,
+                 "--format=csv,noheader,nounits", "-lms", "100"],
+                stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._pump, daemon=True)
+            self.thread.start()
+        except OSError:
+            self.proc = None
+        return self
+
+    def _pump(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except subprocess.TimeoutExpired:
+            self.proc.kill()
+        self.thread.join(timeout=2)
+        sm, mx, pw, reasons = [], [], [], set()
+        names = ("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap")
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 7:
+                continue
+            try:
+                sm.append(float(f[0])); mx.append(float(f[1])); pw.append(float(f[2]))
+            except ValueError:
+                continue
+            for name, v in zip(names, f[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": float(np.median(sm)) if sm else None,
+                "sm_max_mhz": max(mx) if mx else None,
+                "power_w_max": max(pw) if pw else None,
+                "samples": len(sm), "reasons": sorted(reasons)}
+
+
+def pinned_u32(a):
+    """Copy of `a` in page-locked host memory, as a numpy uint32 view (torch owns the pages)."""
+    import torch
+    a = np.ascontiguousarray(a, dtype=np.uint32)
+    t = torch.empty(max(a.size, 1), dtype=torch.int32).pin_memory()
+    v = t.numpy().view(np.uint32)[:a.size]
+    v[:] = a
+    v_base = v
+    _PINNED.append(t)
+    return v_base
+
+
+_PINNED = []
+
+
+def build_workload(mode, chrom_indices=None):
+    from pymasc_b200 import synth
+    names = [n for n, _ in synth.HG38]
+    chroms = None if chrom_indices is None else [names[i] for i in sorted(chrom_indices)]
+    t0 = time.time()
+    # read counts are allotted against the WHOLE genome, whichever chromosomes are generated
+    total = float(sum(L for _, L in synth.HG38))
+    out = []
+    for i, (name, L) in enumerate(synth.HG38):
+        if chroms is not None and name not in chroms:
+            out.append({"name": name, "length": L, "fwd": np.zeros(0, np.uint32),
+                        "rev": np.zeros(0, np.uint32),
+                        "begins": np.zeros(0, np.uint32) if mode == "both" else None,
+                        "ends": np.zeros(0, np.uint32) if mode == "both" else None})
+            continue
+        n = max(8, int(round(N_READS * L / total)))
+        fwd, rev = synth.chip_reads(i, L, n, READ_LEN)
+        b = e = None
+        if mode == "both":
+            b, e = synth.mappability(i, L)
+        out.append({"name": name, "length": L, "fwd": fwd, "rev": rev, "begins": b, "ends": e})
+    return out, time.time() - t0
+
+
+# ---------------------------------------------------------------------------- CPU arms
+def _ref_task(args):
+    """One worker task of the reference arm: a chromosome-shaped sample through the
+    unmodified reference calculator (feed read by read, then finishup).  Returns
+    (evals, seconds, ncc ccbins[:4]) -- runs in a spawned process like a CalcWorker."""
+    (name, L, fwd, rev, begins, ends, mode) = args
+    if ROOT not in sys.path:
+        sys.path.insert(0, ROOT)
+    from oracle import ref_runner
+    pos, ln, is_rev = ref_runner.merged_feed_order(
+        fwd, np.full(len(fwd), READ_LEN), np.asarray(rev, np.int64) - READ_LEN + 1,
+        np.full(len(rev), READ_LEN))
+    tracks = {name: (begins, ends)} if mode == "both" else None
+    t0 = time.perf_counter()
+    calc = ref_runner.run_reference(MAX_SHIFT, READ_LEN, [name], [L], {name: (pos, ln, is_rev)},
+                                    tracks=tracks)
+    dt = time.perf_counter() - t0
+    res = calc.get_result(name)
+    evals = (L + READ_LEN + MAX_SHIFT + 100) * (MAX_SHIFT + 1)
+    return evals, dt, [int(x) for x in res.chrom.ccbins[:4]]
+
+
+def sample_chromosome(chrom, length):
+    """The leading `length` bp of a workload chromosome as a stand-alone chromosome."""
+    fwd = chrom["fwd"][chrom["fwd"] < length]
+    rev = chrom["rev"][chrom["rev"] < length + READ_LEN - 1]
+    b = e = None
+    if chrom["begins"] is not None:
+        keep = chrom["ends"] <= length
+        b, e = chrom["begins"][keep], chrom["ends"][keep]
+    return (chrom["name"], int(length), fwd, rev, b, e)
+
+
+def cpu_baseline_leg(workload, mode, sample_bp, check_device=None):
+    """Reference calculator on ONE core over a bounded sample (rank 0, N = 1 only)."""
+    from oracle import ref_runner
+    if not ref_runner.available():
+        return {"value": None, "unit": UNIT, "cores": 0, "kind": "reference",
+                "sample": "oracle/_ref missing (build it where /root/reference exists)"}
+    chrom = workload[20]   # chr21
+    task = sample_chromosome(chrom, min(sample_bp, chrom["length"]))
+    evals, dt, head = _ref_task(task + (mode,))
+    out = {"value": evals / dt, "unit": UNIT, "cores": 1, "kind": "reference",
+           "seconds": round(dt, 2),
+           "sample": "first %d bp of %s of this workload (%d fwd + %d rev reads, %s intervals), all %d "
+                     "shifts, feed_*_read per read + finishup_calculation, %s" %
+                     (task[1], task[0], len(task[2]), len(task[3]),
+                      "no" if task[4] is None else len(task[4]), MAX_SHIFT + 1,
+                      "NCC+MSCC" if mode == "both" else "NCC")}
+    if check_device is not None:   # the same sample through the CUDA path must agree
+        from pymasc_b200 import _shim
+        flags = _shim.FLAG_NCC | (_shim.FLAG_MSCC if mode == "both" else 0)
+        got = check_device.run_batch([_shim.Job(task[1], READ_LEN, MAX_SHIFT, flags, task[2],
+                                                task[3], task[4], task[5])])[0]
+        out["gpu_matches_reference_on_sample"] = [int(x) for x in got["ncc"][:4]] == head
+    return out
+
+
+def reference_arm(args):
+    """--impl reference: the reference's own `-p N` scheme (one spawned process per task pulled
+    from a pool, handler/calc.py:163-192) on all host cores; each step = `cores` chromosome-
+    shaped samples of the workload."""
+    import multiprocessing as mp
+    from oracle import ref_runner
+    mode = args.mode
+    if not ref_runner.available():
+        print(json.dumps({"impl": "reference", "unavailable": "oracle/_ref (compiled reference) missing"}))
+        return
+    cores = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
+    if args.ref_cores:
+        cores = args.ref_cores
+    n_steps = args.steps + args.warmup
+    # size the sample so that the whole run stays within ~4 minutes: calibrate on 1 Mb
+    workload, _ = build_workload(mode, chrom_indices=list(range(24))[-min(24, cores):] if cores < 24 else None)
+    live = [c for c in workload if len(c["fwd"])]
+    ev, dt, _ = _ref_task(sample_chromosome(live[-1], 1_000_000) + (mode,))
+    per_bp = dt / 1_000_000
+    budget = min(25.0, 200.0 / max(1, n_steps))
+    sample_bp = int(max(2_000_000, min(40_000_000, budget / per_bp)))
+    tasks = []
+    for i in range(cores):
+        c = live[i % len(live)]
+        tasks.append(sample_chromosome(c, min(sample_bp, c["length"])) + (mode,))
+    ctx = mp.get_context("spawn")
+    times = []
+    with ctx.Pool(processes=cores) as pool:
+        pool.map(_ref_task, [sample_chromosome(live[0], 200_000) + (mode,)] * cores)  # import warm-up
+        for s in range(n_steps):
+            t0 = time.perf_counter()
+            res = pool.map(_ref_task, tasks, chunksize=1)
+            dt = time.perf_counter() - t0
+            if s >= args.warmup:
+                times.append((sum(r[0] for r in res), dt))
+    evals = sum(t[0] for t in times)
+    secs = sum(t[1] for t in times)
+    value = evals / secs
+    sample = ("%d tasks per step (one per core), each the first %d bp of a workload chromosome as a "
+              "stand-alone chromosome, all %d shifts, feed per read + finishup, %s" %
+              (cores, sample_bp, MAX_SHIFT + 1, "NCC+MSCC" if mode == "both" else "NCC"))
+    line = {
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * secs / max(1, len(times)),
+        "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "u64",
+        "data": "synthetic", "config": workload_config(mode),
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "reference",
+                         "sample": sample},
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line))
+
+
+def workload_config(mode):
+    return {"workload": "synthetic hg38-shaped genome (24 chromosomes, 3.09 Gb), 20M single-end 36 bp "
+                        "reads%s, max_shift 1000, %s" %
+                        (", synthetic 36-mer mappability track" if mode == "both" else "",
+                         "NCC+MSCC" if mode == "both" else "NCC only"),
+            "read_len": READ_LEN, "max_shift": MAX_SHIFT, "n_reads": N_READS,
+            "mode": "ncc+mscc" if mode == "both" else "ncc",
+            "l2": "inputs larger than L2: 5 bit arrays x 386 MB per step vs 126 MB L2; no explicit flush"}
+
+
+# ---------------------------------------------------------------------------- GPU arm
+def gpu_arm(args):
+    import torch
+    import torch.distributed as dist
+    from pymasc_b200 import _shim, sharding, synth
+    from pymasc_b200.distributed import counters_tensor
+
+    world = env_int("WORLD_SIZE", 1)
+    rank = env_int("RANK", 0)
+    local = env_int("LOCAL_RANK", 0)
+    if world != args.gpus and world > 1:
+        raise SystemExit("--gpus %d but WORLD_SIZE=%d" % (args.gpus, world))
+    if args.gpus > 1 and world == 1:
+        raise SystemExit("launch with torch.distributed.run --nproc-per-node %d" % args.gpus)
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    mode = args.mode
+
+    lengths = [L for _, L in synth.HG38]
+    pieces = sharding.plan(lengths, READ_LEN, MAX_SHIFT, world)[rank]
+    mine = sorted({ci for ci, _, _ in pieces})
+    need = set(mine)
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        need.add(20)
+    workload, gen_s = build_workload(mode, chrom_indices=need)
+    jobs = sharding.jobs_for_rank(workload, pieces, READ_LEN, MAX_SHIFT)
+    # page-locked copies of the packed inputs: what the host side hands to the C ABI
+    h2d = 0
+    for j in jobs:
+        for name in ("fwd_pos", "rev_pos", "map_begins", "map_ends"):
+            a = getattr(j, name)
+            if a is not None and a.size:
+                setattr(j, name, pinned_u32(a))
+                h2d += a.size * 4
+    evals_total = synth.evals(lengths, READ_LEN, MAX_SHIFT)
+    P = 5 if mode == "both" else 1
+
+    dev = _shim.Device(local)
+    stream = torch.cuda.Stream(device=local)
+    dev.set_stream(stream.cuda_stream)
+    if args.variant is not None:
+        dev.set_option("variant", args.variant)
+    if args.tile_words:
+        dev.set_option("tile_words", args.tile_words)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(x):
+        if world == 1:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    with torch.cuda.stream(stream):
+        # ---- resident-input arm
+        batch = dev.prepare(jobs)
+        ctr = counters_tensor(batch) if world > 1 else None
+
+        def step():
+            batch.execute()
+            if world > 1:
+                dist.all_reduce(ctr)
+
+        for _ in range(args.warmup):
+            step()
+        barrier()
+        sampler = ClockSampler(local).start() if rank == 0 else None
+        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        ev0.record(stream)
+        for _ in range(args.steps):
+            step()
+        ev1.record(stream)
+        barrier()
+        clocks = sampler.stop() if sampler else None
+        dev_ms = max_over_ranks(ev0.elapsed_time(ev1))
+        ms_per_step = dev_ms / args.steps
+        launches_per_step = dev.timing()["launches"]
+
+        # ---- per-kernel times of the same step (library CUDA events on the same stream)
+        win_ms, build_ms = [], []
+        for _ in range(max(3, min(args.steps, 10))):
+            batch.execute()
+            t = dev.timing()
+            win_ms.append(t["window_ms"]); build_ms.append(t["build_ms"])
+        pairs = t["window_word_shift_pairs"]
+        win_launches = t["window_launches"]
+        resident = batch.fetch()
+        batch.free()
+
+        # ---- end-to-end arm: pinned host arrays in, counters on the host out
+        def e2e_step():
+            b = dev.prepare(jobs)                      # H2D
+            try:
+                b.execute()
+                if world > 1:
+                    dist.all_reduce(counters_tensor(b))
+                return b.fetch()                       # D2H + sync
+            finally:
+                b.free()
+
+        for _ in range(min(args.warmup, 3)):
+            e2e_out = e2e_step()
+        barrier()
+        t0 = time.perf_counter()
+        ev0.record(stream)
+        for _ in range(args.steps):
+            e2e_out = e2e_step()
+        ev1.record(stream)
+        barrier()
+        wall_ms = (time.perf_counter() - t0) * 1e3
+        e2e_ms = max_over_ranks(max(wall_ms, ev0.elapsed_time(ev1))) / args.steps
+        d2h = sum(sum(v.size * 8 for v in o.values() if isinstance(v, np.ndarray)) + 16 for o in e2e_out)
+
+        # resident and e2e arms must agree with each other (full-size consistency check)
+        same = all(np.array_equal(np.asarray(a[k]), np.asarray(b[k]))
+                   for a, b in zip(resident, e2e_out) for k in a)
+
+        popc_peak, _ = dev.pipe_probe(0)
+        lop3_peak, _ = dev.pipe_probe(1)
+
+    line = None
+    if rank == 0:
+        win_s = float(np.mean(win_ms)) * 1e-3
+        # this rank's share of the algorithmic work (ranks are balanced to 128 bits)
+        evals_rank = evals_total / world
+        popc_alg = evals_rank * P / 32.0
+        arrays = 5 if mode == "both" else 2
+        alg_bytes = arrays * sum(L + READ_LEN + MAX_SHIFT + 100 for L in lengths) / 8.0 / world
+        peaks = {}
+        try:
+            with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as fh:
+                peaks = json.load(fh)
+        except OSError:
+            pass
+        hbm_peak = peaks.get("hbm_gbs", 6650.0)
+        line = {
+            "metric": METRIC, "value": evals_total / (ms_per_step * 1e-3), "unit": UNIT,
+            "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_per_step,
+            "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "u32",
+            "data": "synthetic", "config": dict(workload_config(mode),
+                                                parallelism="position ranges x%d + NCCL all-reduce" % world
+                                                if world > 1 else "1 GPU"),
+            "e2e": {"value": evals_total / (e2e_ms * 1e-3), "unit": UNIT, "ms_per_step": e2e_ms,
+                    "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
+                    "api": "pmb_batch_prepare/execute/fetch via ctypes (pymasc_b200._shim)"},
+            "gpu_launches": int(launches_per_step * args.steps),
+            "launches_per_step": int(launches_per_step),
+            "clocks": clocks,
+            "roofline": {
+                "bound": "popc", "kernel": "shift_window_kernel",
+                "achieved": popc_alg / win_s / 1e9, "peak": popc_peak / 1e9, "unit": "Gpopc32/s",
+                "frac": popc_alg / win_s / popc_peak,
+                "peak_source": "pmb_pipe_probe(POPC) measured in this run (MEASURED_PEAKS.json has no "
+                               "integer-pipe figure); LOP3 rate %.0f Gop/s" % (lop3_peak / 1e9),
+                "algorithmic_popc_per_eval": P / 32.0,
+                "kernel_ms": win_s * 1e3, "kernel_launches_per_step": int(win_launches),
+                "build_ms": float(np.mean(build_ms)),
+                "executed_word_shift_pairs": int(pairs),
+                "traffic": None,
+                "hbm": {"algorithmic_bytes": alg_bytes, "achieved_gbs": alg_bytes / win_s / 1e9,
+                        "peak_gbs": hbm_peak,
+                        "peak_source": "MEASURED_PEAKS.json" if peaks else "fallback",
+                        "frac": alg_bytes / win_s / 1e9 / hbm_peak},
+            },
+            "resident_equals_e2e": bool(same),
+            "synthetic_generation_s": round(gen_s, 1),
+        }
+        if world == 1 and not args.no_cpu_baseline:
+            dev.set_stream(None)
+            line["cpu_baseline"] = cpu_baseline_leg(workload, mode, args.cpu_sample_bp, check_device=dev)
+        else:
+            line["cpu_baseline"] = None
+        print(json.dumps(line), flush=True)
+    dev.set_stream(None)
+    dev.close()
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--mode", default="both", choices=["both", "ncc"])
+    ap.add_argument("--variant", type=int, default=None, help="shift-window kernel variant (tuning)")
+    ap.add_argument("--tile-words", type=int, default=0)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--cpu-sample-bp", type=int, default=20_000_000)
+    ap.add_argument("--ref-cores", type=int, default=0)
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 0)
+    if args.impl == "reference":
+        if env_int("RANK", 0) == 0:
+            reference_arm(args)
+        return
+    if args.warmup < 3:
+        args.warmup = 3      # timing rule: at least 3 warm-up steps
+    gpu_arm(args)
+
+
+if __name__ == "__main__":
+    main()

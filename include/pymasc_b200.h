@@ -136,6 +136,9 @@ int  pmb_get_timing(pmb_ctx *ctx, pmb_timing *t);
  * work (e.g. an NCCL all-reduce issued through torch) after pmb_batch_execute. */
 void *pmb_stream(pmb_ctx *ctx);
 int   pmb_synchronize(pmb_ctx *ctx);
+/* Run on a stream the caller owns (cudaStream_t as void*; NULL = back to the context's
+ * own stream).  The caller keeps the stream alive while the context uses it. */
+int   pmb_set_stream(pmb_ctx *ctx, void *stream);
 
 /* Pinned host memory for callers without another way to get it. */
 int  pmb_host_alloc(void **out, uint64_t bytes);

@@ -123,12 +123,19 @@ def chrom_counts(chrom_len, read_len, max_shift, fwd_pos, rev_pos,
     return out
 
 
-def mappable_autocorr(chrom_len, read_len, max_shift, map_begins, map_ends):
-    """mappable_len tuple of a read-less chromosome (mscc.pyx:207-215)."""
+def mappable_autocorr(chrom_len, read_len, max_shift, map_begins, map_ends, lo=0, hi=None):
+    """mappable_len tuple of a read-less chromosome (mscc.pyx:207-215); with lo/hi the
+    partial sums over j in [lo, hi) of a position shard (they add up to the whole)."""
     nbits = array_bits(chrom_len, read_len, max_shift)
     M = make_mappability(nbits, map_begins, map_ends)
     out = np.zeros(max_shift + 1, dtype=np.int64)
-    lib().orc_mappable_autocorr(_p(M, ctypes.c_uint64), nbits, max_shift, _p(out, ctypes.c_int64))
+    if lo == 0 and (hi is None or hi >= nbits):
+        lib().orc_mappable_autocorr(_p(M, ctypes.c_uint64), nbits, max_shift, _p(out, ctypes.c_int64))
+    else:   # sum_j M[j] M[j+k] is the NCC count of F = R = M
+        rc = lib().orc_cc_counts(_p(M, ctypes.c_uint64), _p(M, ctypes.c_uint64), None, nbits,
+                                 read_len, max_shift, lo, min(hi, nbits), _p(out, ctypes.c_int64),
+                                 None, None, None, None)
+        assert rc == 0
     return out
 
 

@@ -57,7 +57,7 @@ EXPORTS = (
     "pmb_create", "pmb_destroy", "pmb_last_error", "pmb_run_chrom", "pmb_run_batch",
     "pmb_batch_prepare", "pmb_batch_execute", "pmb_batch_fetch", "pmb_batch_counters",
     "pmb_batch_free", "pmb_get_timing", "pmb_stream", "pmb_synchronize", "pmb_host_alloc",
-    "pmb_host_free", "pmb_set_option", "pmb_pipe_probe",
+    "pmb_host_free", "pmb_set_option", "pmb_pipe_probe", "pmb_set_stream",
 )
 
 _lib = None
@@ -101,6 +101,8 @@ def load_library():
     L.pmb_stream.restype = vp
     L.pmb_synchronize.argtypes = [vp]
     L.pmb_synchronize.restype = ctypes.c_int
+    L.pmb_set_stream.argtypes = [vp, vp]
+    L.pmb_set_stream.restype = ctypes.c_int
     L.pmb_host_alloc.argtypes = [vpp, ctypes.c_uint64]
     L.pmb_host_alloc.restype = ctypes.c_int
     L.pmb_host_free.argtypes = [vp]
@@ -180,6 +182,10 @@ class Device(object):
     @property
     def stream(self):
         return self._L.pmb_stream(self._h)
+
+    def set_stream(self, stream):
+        """Adopt a caller-owned cudaStream_t (integer handle; None/0 = the context's own)."""
+        self._check(self._L.pmb_set_stream(self._h, ctypes.c_void_p(int(stream) if stream else None)))
 
     # ---- argument marshalling
     @staticmethod

@@ -23,6 +23,7 @@ struct pmb_ctx {
     int device = 0;
     int num_sms = 148;
     cudaStream_t stream = nullptr;
+    cudaStream_t own_stream = nullptr;   // created by pmb_create; `stream` may be borrowed
     cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
     std::string err;
     pmb_timing timing{};
@@ -118,8 +119,9 @@ extern "C" int pmb_create(pmb_ctx** out, int device_ordinal)
         return PMB_ERR_CUDA;
     }
     c->num_sms = prop.multiProcessorCount;
-    if ((e = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking)) != cudaSuccess)
+    if ((e = cudaStreamCreateWithFlags(&c->own_stream, cudaStreamNonBlocking)) != cudaSuccess)
         return fail("cudaStreamCreate", e);
+    c->stream = c->own_stream;
     for (auto& ev : c->ev)
         if ((e = cudaEventCreate(&ev)) != cudaSuccess) return fail("cudaEventCreate", e);
     // keep freed blocks cached in the stream-ordered pool (arena behaviour)
@@ -140,7 +142,7 @@ extern "C" void pmb_destroy(pmb_ctx* c)
     for (auto& ev : c->ev)
         if (ev) cudaEventDestroy(ev);
     if (c->h_stage) cudaFreeHost(c->h_stage);
-    if (c->stream) cudaStreamDestroy(c->stream);
+    if (c->own_stream) cudaStreamDestroy(c->own_stream);
     delete c;
 }
 
@@ -150,6 +152,15 @@ extern "C" const char* pmb_last_error(pmb_ctx* c)
 }
 
 extern "C" void* pmb_stream(pmb_ctx* c) { return c ? (void*)c->stream : nullptr; }
+
+extern "C" int pmb_set_stream(pmb_ctx* c, void* stream)
+{
+    if (!c) return PMB_ERR_ARG;
+    CU_TRY(c, cudaSetDevice(c->device));
+    CU_TRY(c, cudaStreamSynchronize(c->stream));   // nothing of ours is left on the old stream
+    c->stream = stream ? (cudaStream_t)stream : c->own_stream;
+    return PMB_OK;
+}
 
 extern "C" int pmb_synchronize(pmb_ctx* c)
 {
@@ -200,9 +211,12 @@ static uint32_t gcd_u32(uint32_t a, uint32_t b) { return b ? gcd_u32(b, a % b) :
 
 enum { A_F = 0, A_R = 1, A_M = 2, A_MP = 3, A_FM = 4 };
 
+static bool whole_range(const JobPlan& j) { return j.lo == 0 && j.hi == (int64_t)j.nbits; }
+
 static int arrays_of(const JobPlan& j)
 {
-    if (j.autocorr) return 1;                 // M only (stored in slot 0)
+    // autocorrelation: M (whole window, the "R" role) [+ M clipped to the shard, the "F" role]
+    if (j.autocorr) return whole_range(j) ? 1 : 2;
     return (j.mode & MODE_MSCC) ? 5 : 2;      // F, R [, M, Mp, FM]
 }
 
@@ -247,7 +261,7 @@ static int plan_windows(pmb_ctx* c, pmb_batch* b)
                 auto arr = [&](int slot) { return base + (size_t)slot * j.array_words + H; };
                 WindowJob w{};
                 if (j.autocorr) {   // sum_j M[j] M[j+k]: the NCC kernel on F = R = M, into the dmp slot
-                    w.F = arr(0);
+                    w.F = arr(whole_range(j) ? 0 : 1);
                     w.R = arr(0) + 4 * u0;
                     w.counters = b->d_counters + (i * PMB_NCOUNTERS + C_DMP) * b->stride + 128 * u0;
                 } else {
@@ -341,9 +355,6 @@ extern "C" int pmb_batch_prepare(pmb_ctx* c, const pmb_chrom_args* a, uint32_t n
         j.hi = a[i].range_hi ? (int64_t)a[i].range_hi : (int64_t)j.nbits;
         if (j.hi > (int64_t)j.nbits) j.hi = (int64_t)j.nbits;
         if (j.lo > j.hi) j.lo = j.hi;
-        if (j.autocorr && (j.lo != 0 || j.hi != (int64_t)j.nbits)) {
-            c->err = "PMB_FLAG_AUTOCORR needs the whole chromosome range"; return PMB_ERR_ARG;
-        }
         j.origin_word = (j.lo >> 5) & ~(int64_t)3;
         total_words += (uint64_t)(((j.hi + 31) >> 5) - j.origin_word);
     }
@@ -475,14 +486,16 @@ extern "C" int pmb_batch_execute(pmb_ctx* c, pmb_batch* b)
         auto arr = [&](int slot) { return base + (size_t)slot * j.array_words; };
 
         if (j.autocorr) {
-            uint32_t* M = arr(0);
-            if (j.a.n_intervals) {
+            const int n_arr = arrays_of(j);
+            for (int pass = 0; pass < n_arr && j.a.n_intervals; pass++) {
+                uint32_t* M = arr(pass);
+                int64_t clo = pass == 0 ? NEG : j.lo, chi = pass == 0 ? POS : j.hi;
                 CU_TRY(c, cudaMemsetAsync(b->d_long, 0, 4, st));
                 fill_intervals_kernel<<<blocks_for(j.a.n_intervals, 8), 256, 0, st>>>(
-                    M, g, b->d_in + j.in_mb, b->d_in + j.in_me, j.a.n_intervals, 0, NEG, POS, j.nbits,
+                    M, g, b->d_in + j.in_mb, b->d_in + j.in_me, j.a.n_intervals, 0, clo, chi, j.nbits,
                     b->d_err, b->d_long + 1, b->d_long);
                 fill_long_kernel<<<c->num_sms * 4, 256, 0, st>>>(M, g, b->d_in + j.in_mb,
-                                                                 b->d_in + j.in_me, 0, NEG, POS,
+                                                                 b->d_in + j.in_me, 0, clo, chi,
                                                                  b->d_long + 1, b->d_long);
                 launches += 2;
             }

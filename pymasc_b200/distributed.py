@@ -1,0 +1,118 @@
+"""One process per GPU: position-sharded counts + one all-reduce (torch.distributed).
+
+``ShardedEngine`` is an engine for ``CCBitArrayCalculator`` (``engine=`` keyword).  Every rank
+of the process group feeds the same reads (or at least closes the same chromosomes) and calls
+``run(jobs)`` with the same job list; each rank counts its position shard of every chromosome
+(``sharding.plan``), the (max_shift+1)-long int64 count vectors are summed across ranks with a
+single ``all_reduce`` -- NCCL over NVLink/NVSwitch when the local engine is a device, on the
+device counter block itself (no host round trip) -- and every rank returns the full result.
+
+torch is used for the process group only; the counts come from libpymasc_b200.so.
+"""
+import numpy as np
+
+from . import _shim, sharding
+
+_KEYS = ("ncc", "dmp", "mfwd", "mrev", "mscc")
+
+
+class _DevicePointer(object):
+    """__cuda_array_interface__ view of a device int64 block owned by a pmb_batch."""
+
+    def __init__(self, ptr, n):
+        self.__cuda_array_interface__ = {
+            "shape": (int(n),), "typestr": "<i8", "data": (int(ptr), False), "version": 3,
+            "strides": None,
+        }
+
+
+def counters_tensor(batch):
+    """torch int64 CUDA tensor aliasing the batch's device counter block
+    (int64[n_jobs][5][stride] followed by int64[n_jobs][2] strand totals)."""
+    import torch
+    ptr, n, _ = batch.counters()
+    return torch.as_tensor(_DevicePointer(ptr, n), device="cuda:%d" % batch.dev.ordinal)
+
+
+def job_chroms(jobs):
+    """The sharding module's chromosome dicts from whole-chromosome jobs."""
+    return [{"length": j.chrom_len, "fwd": j.fwd_pos, "rev": j.rev_pos,
+             "begins": j.map_begins if j.flags & (_shim.FLAG_MSCC | _shim.FLAG_AUTOCORR) else None,
+             "ends": j.map_ends if j.flags & (_shim.FLAG_MSCC | _shim.FLAG_AUTOCORR) else None,
+             "flags": j.flags} for j in jobs]
+
+
+def shard_jobs(jobs, rank, world):
+    """This rank's position shards of `jobs` (same length and order as `jobs`)."""
+    if not jobs:
+        return []
+    rl, D = jobs[0].read_len, jobs[0].max_shift
+    chroms = job_chroms(jobs)
+    pieces = sharding.plan([c["length"] for c in chroms], rl, D, world)[rank]
+    mine = sharding.jobs_for_rank(chroms, pieces, rl, D, flags_of=lambda c: c["flags"])
+    for j in mine:   # read-less autocorrelation jobs carry no reads
+        if j.flags & _shim.FLAG_AUTOCORR:
+            j.fwd_pos = j.rev_pos = np.zeros(0, np.uint32)
+    return mine
+
+
+class ShardedEngine(object):
+    """Engine that splits every batch across the ranks of a torch.distributed group.
+
+    local: a ``_shim.Device`` (product: NCCL all-reduce of the device counters) or any object
+    with ``run(jobs)`` returning host dicts (tests: gloo all-reduce of host vectors)."""
+
+    def __init__(self, local=None, group=None):
+        import torch.distributed as dist
+        self._dist = dist
+        self._group = group
+        self._local = local
+        self.rank = dist.get_rank(group)
+        self.world = dist.get_world_size(group)
+
+    @property
+    def local(self):
+        if self._local is None:
+            self._local = _shim.Device()      # LOCAL_RANK / PYMASC_B200_DEVICE
+        return self._local
+
+    def run(self, jobs):
+        if not jobs:
+            return []
+        mine = shard_jobs(jobs, self.rank, self.world)
+        if isinstance(self.local, _shim.Device):
+            return self._run_device(mine)
+        return self._run_host(mine)
+
+    # NCCL path: reduce the device counter block in place, then one D2H
+    def _run_device(self, mine):
+        import torch
+        dev = self.local
+        with torch.cuda.device(dev.ordinal):
+            dev.set_stream(torch.cuda.current_stream().cuda_stream)
+            batch = dev.prepare(mine)
+            try:
+                batch.execute()
+                self._dist.all_reduce(counters_tensor(batch), group=self._group)
+                return batch.fetch()
+            finally:
+                batch.free()
+                dev.set_stream(None)
+
+    # host path (gloo): used by the CPU tests of the sharding logic
+    def _run_host(self, mine):
+        import torch
+        outs = self.local.run(mine)
+        flat, index = [], []
+        for i, o in enumerate(outs):
+            for k in sorted(o):
+                v = np.atleast_1d(np.asarray(o[k], dtype=np.int64))
+                index.append((i, k, v.size, np.isscalar(o[k]) or isinstance(o[k], int)))
+                flat.append(v)
+        t = torch.from_numpy(np.concatenate(flat))
+        self._dist.all_reduce(t, group=self._group)
+        red, off, res = t.numpy(), 0, [dict() for _ in outs]
+        for i, k, n, scalar in index:
+            res[i][k] = int(red[off]) if scalar else red[off:off + n].copy()
+            off += n
+        return res

@@ -18,7 +18,8 @@ class OracleEngine(object):
         for j in jobs:
             if j.flags & _shim.FLAG_AUTOCORR:
                 outs.append({"dmp": cc_oracle.mappable_autocorr(
-                    j.chrom_len, j.read_len, j.max_shift, j.map_begins, j.map_ends)})
+                    j.chrom_len, j.read_len, j.max_shift, j.map_begins, j.map_ends,
+                    lo=j.lo, hi=j.hi if j.hi else None)})
                 continue
             mscc = bool(j.flags & _shim.FLAG_MSCC)
             outs.append(cc_oracle.chrom_counts(

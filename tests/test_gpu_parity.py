@@ -239,3 +239,31 @@ def test_hg38_chr21_properties(dev):
     want = cc_oracle.chrom_counts(w["length"], rl, D, w["fwd"], w["rev"], w["begins"], w["ends"], lo=lo, hi=hi)
     for k in want:
         assert np.array_equal(np.asarray(got[k]), np.asarray(want[k])), k
+
+
+# ----------------------------------------------------------------- the N > 1 decomposition
+@pytest.mark.parametrize("world", [2, 8])
+def test_rank_jobs_from_the_sharding_plan_add_up(dev, world):
+    """What bench.py / ShardedEngine run per rank: identical job lists with clipped inputs and
+    empty ranges, executed here rank after rank on one device; the per-rank counter blocks
+    must sum to the whole-genome result (the all-reduce is a plain int64 sum)."""
+    from pymasc_b200 import sharding
+    from pymasc_b200.distributed import shard_jobs
+    rl, D = 36, 400
+    chroms = []
+    for i, L in enumerate([300000, 41000, 170000]):
+        fwd, rev, b, e = random_case(50 + i, L, rl, L // 12)
+        chroms.append({"length": L, "fwd": fwd, "rev": rev, "begins": b, "ends": e})
+    lengths = [c["length"] for c in chroms]
+    whole_jobs = sharding.jobs_for_rank(chroms, sharding.plan(lengths, rl, D, 1)[0], rl, D)
+    _, _, b, e = random_case(60, 90000, rl, 10)
+    whole_jobs.append(_shim.Job(90000, rl, D, _shim.FLAG_AUTOCORR, None, None, b, e))
+    whole = dev.run_batch(whole_jobs)
+    want_auto = cc_oracle.mappable_autocorr(90000, rl, D, b, e)
+    assert np.array_equal(whole[-1]["dmp"], want_auto)
+    parts = [dev.run_batch(shard_jobs(whole_jobs, r, world)) for r in range(world)]
+    merged = sharding.sum_outputs(parts)
+    for a, m in zip(whole, merged):
+        assert sorted(a) == sorted(m)
+        for k in a:
+            assert np.array_equal(np.asarray(a[k]), np.asarray(m[k])), k
