@@ -1,0 +1,433 @@
+// pmb_events.cuh -- the event-window path (sm_100a): the same per-shift counts as the
+// shift-window kernel, computed from the SET BITS of the sparse arrays instead of from every
+// bit position.
+//
+// The reference's loop (PyMaSC/core/bitarray/mscc.pyx:288-317) and the dense shift-window
+// kernel (pmb_window.cuh) cost  L x (max_shift+1)  whatever the data.  But F and R hold one
+// bit per read (0.3 % of the positions at 20 M reads on hg38) and M is a union of runs, so
+// every count is a sum over few "events", each contributing one (max_shift+1)-bit WINDOW of a
+// bit array (bit b of the window <-> shift k = b):
+//
+//   forward read at p:   ncc  += R[p .. p+D]                                   (:314)
+//     and, if M[p]:      mfwd += M[p+rl-1-k], k = 0..D   = Mr[N-p-rl .. +D]    (:303)
+//                        mscc += R[p+k] & M[p+rl-1-k]                          (:305)
+//   reverse read at q:   mrev += M[q-k] & M[q+rl-1-2k]   (j = q-k in range)    (:304)
+//                             =  Mr[N-1-q .. +D] & {Er|Or}[N/2-1-((q+rl-1)>>1) .. +D]
+//   mappable-run edges:  popc(D_k) = A[rl-1-k],  A[s] = sum_j Mc[j] M[j+s]     (:291-298)
+//                        2A[s] - A[s-1] - A[s+1] = sum_j dMc[j] dM[j+s]  (dX = starts - ends),
+//                        so every run edge of the (range-clipped) M adds the windows of the
+//                        start/end edge arrays Sb/Eb; two directly counted lags anchor the
+//                        recurrence (finalize_dmp_kernel).  Exact integer arithmetic.
+//
+// Mr is M bit-reversed, Er/Or are the even/odd bits of M bit-reversed (so that the
+// descending and the stride-2 descending windows become ascending ones); derive_kernel
+// writes them, Sb and Eb in one streaming pass over M.
+//
+// Mapping.  A warp scans 32 words of the event source at a time (coalesced), and handles the
+// events one after the other: lane <-> window column (32 shifts), so one event is a 128-byte
+// coalesced, unaligned window load per array + one funnel shift per lane.  The per-shift
+// counts are kept BIT-SLICED in registers: a carry-save binary counter (acc/pend word per
+// level, ~1 CSA = 2 LOP3 per event and counter, independent of the window's density); a
+// carry out of the top level and the final residue go to a per-block shared-memory
+// histogram, which is flushed to the 64-bit global counters when the block changes
+// chromosome or ends.  No data-dependent approximation: counts are bit-exact.
+#pragma once
+#include <stdint.h>
+#include <cuda_runtime.h>
+
+#include "pmb_window.cuh"   // xor3 / maj3, counter slots
+
+namespace pmb {
+
+enum { EV_FWD = 0, EV_REV = 1, EV_EDGE = 2 };
+enum { EVF_NCC = 1u, EVF_MSCC = 2u, EVF_AUTOCORR = 4u };
+
+struct EventJob {
+    const uint32_t* F;    // array word 0 of each array (halo included)
+    const uint32_t* R;
+    const uint32_t* M;
+    const uint32_t* Mr;
+    const uint32_t* Er;
+    const uint32_t* Or;
+    const uint32_t* Sb;
+    const uint32_t* Eb;
+    unsigned long long* counters;   // [5][stride]
+    unsigned long long* aux;        // [2][stride]: edge products, + then - (window-bit indexed)
+    unsigned long long* adirect;    // [2]: the two directly counted lags
+    long long a_lo, a_hi;           // counted range in array bits
+    uint32_t array_words;
+    uint32_t tile_begin, n_tiles;
+    int32_t edge_off;               // window start relative to an edge: rl-1-D, or 0 (autocorr)
+    uint32_t flags;
+    uint32_t reserved;
+};
+
+struct EventParams {
+    const EventJob* jobs;
+    uint32_t n_jobs;
+    uint32_t total_tiles;
+    uint32_t tile_words;    // multiple of 32 * warps per block
+    uint32_t col0;          // first window column of this launch
+    uint32_t n_cols;        // <= 32
+    uint32_t max_shift;
+    uint32_t read_len;
+    uint32_t stride;
+};
+
+constexpr int EV_LEVELS = 6;          // carry-save levels: a top-level carry every 64 events
+constexpr int EV_HIST_STRIDE = 33;    // padded: lane l, bit b -> bank (l + b) % 32
+
+// NC bit-sliced counters sharing one event count (all warp-uniform control flow).
+template <int NC>
+struct Slices {
+    uint32_t acc[NC][EV_LEVELS];
+    uint32_t pend[NC][EV_LEVELS];
+    uint32_t m;
+
+    __device__ __forceinline__ void reset()
+    {
+#pragma unroll
+        for (int n = 0; n < NC; ++n)
+#pragma unroll
+            for (int i = 0; i < EV_LEVELS; ++i) { acc[n][i] = 0; pend[n][i] = 0; }
+        m = 0;
+    }
+    static __device__ __forceinline__ void sink(uint32_t* hist, int lane, uint32_t c, uint32_t weight)
+    {
+        while (c) {
+            const int b = __ffs(c) - 1;
+            c &= c - 1;
+            atomicAdd(hist + lane * EV_HIST_STRIDE + b, weight);
+        }
+    }
+    // add one window word per counter
+    __device__ __forceinline__ void add(const uint32_t (&x)[NC], uint32_t* hist, int lane)
+    {
+        ++m;
+        uint32_t mm = m;
+        uint32_t c[NC];
+#pragma unroll
+        for (int n = 0; n < NC; ++n) c[n] = x[n];
+        bool go = true;
+#pragma unroll
+        for (int i = 0; i < EV_LEVELS; ++i) {
+            if (go) {
+                if (mm & 1u) {
+#pragma unroll
+                    for (int n = 0; n < NC; ++n) pend[n][i] = c[n];
+                    go = false;
+                } else {
+#pragma unroll
+                    for (int n = 0; n < NC; ++n) {
+                        const uint32_t t = maj3(acc[n][i], pend[n][i], c[n]);
+                        acc[n][i] = xor3(acc[n][i], pend[n][i], c[n]);
+                        c[n] = t;
+                    }
+                    mm >>= 1;
+                }
+            }
+        }
+        if (go) {
+#pragma unroll
+            for (int n = 0; n < NC; ++n) sink(hist + n * 32 * EV_HIST_STRIDE, lane, c[n], 1u << EV_LEVELS);
+        }
+    }
+    __device__ __forceinline__ void flush(uint32_t* hist, int lane)
+    {
+#pragma unroll
+        for (int n = 0; n < NC; ++n) {
+#pragma unroll
+            for (int i = 0; i < EV_LEVELS; ++i) {
+                sink(hist + n * 32 * EV_HIST_STRIDE, lane, acc[n][i], 1u << i);
+                if ((m >> i) & 1u) sink(hist + n * 32 * EV_HIST_STRIDE, lane, pend[n][i], 1u << i);
+            }
+        }
+        reset();
+    }
+};
+
+// Window column `col` (32 bits) of array A starting at bit `st`: every lane loads one word,
+// the upper neighbour comes by shuffle (lane 31 loads its own).
+__device__ __forceinline__ uint32_t window_word(const uint32_t* __restrict__ A, long long st, uint32_t col,
+                                                int lane)
+{
+    const long long w = (st >> 5) + col;
+    const uint32_t lo = __ldg(A + w);
+    uint32_t hi = __shfl_down_sync(0xFFFFFFFFu, lo, 1);
+    if (lane == 31) hi = __ldg(A + w + 1);
+    return __funnelshift_r(lo, hi, (uint32_t)(st & 31));
+}
+
+__device__ __forceinline__ uint32_t range_mask(long long bit0, long long lo, long long hi)
+{
+    if (bit0 + 32 <= lo || bit0 >= hi) return 0u;
+    uint32_t mask = 0xFFFFFFFFu;
+    if (bit0 < lo) mask &= 0xFFFFFFFFu << (lo - bit0);
+    if (bit0 + 32 > hi) mask &= 0xFFFFFFFFu >> (bit0 + 32 - hi);
+    return mask;
+}
+
+template <int KIND>
+struct EvTraits;
+template <> struct EvTraits<EV_FWD> { static constexpr int NC = 3; };    // ncc, mfwd, mscc
+template <> struct EvTraits<EV_REV> { static constexpr int NC = 1; };    // mrev
+template <> struct EvTraits<EV_EDGE> { static constexpr int NC = 2; };   // + and - edge products
+
+// KIND: which events; NCC / MSCC: which counters the batch asked for.
+template <int KIND, bool NCC, bool MSCC>
+__global__ void __launch_bounds__(256) event_window_kernel(const EventParams P)
+{
+    constexpr int NC = EvTraits<KIND>::NC;
+    __shared__ uint32_t hist[NC * 32 * EV_HIST_STRIDE];
+
+    const int lane = threadIdx.x & 31;
+    const int warp = threadIdx.x >> 5;
+    const int n_warps = blockDim.x >> 5;
+
+    const uint32_t t_lo = (uint32_t)(((uint64_t)P.total_tiles * blockIdx.x) / gridDim.x);
+    const uint32_t t_hi = (uint32_t)(((uint64_t)P.total_tiles * (blockIdx.x + 1)) / gridDim.x);
+    if (t_lo >= t_hi) return;
+
+    for (uint32_t i = threadIdx.x; i < NC * 32 * EV_HIST_STRIDE; i += blockDim.x) hist[i] = 0;
+    __syncthreads();
+
+    Slices<NC> sl;
+    sl.reset();
+    const uint32_t col = P.col0 + lane;          // this lane's window column
+    const bool col_on = lane < (int)P.n_cols;
+    const long long D = P.max_shift;
+
+    uint32_t cur_job = 0;
+    while (cur_job + 1 < P.n_jobs && P.jobs[cur_job + 1].tile_begin <= t_lo) cur_job++;
+
+    auto flush_block = [&](uint32_t job) {
+        sl.flush(hist, lane);
+        __syncthreads();
+        const EventJob& J = P.jobs[job];
+        for (uint32_t i = threadIdx.x; i < NC * 32 * EV_HIST_STRIDE; i += blockDim.x) {
+            const uint32_t v = hist[i];
+            if (!v) continue;
+            hist[i] = 0;
+            const uint32_t n = i / (32 * EV_HIST_STRIDE);
+            const uint32_t r = i % (32 * EV_HIST_STRIDE);
+            const uint32_t c = r / EV_HIST_STRIDE, b = r % EV_HIST_STRIDE;
+            if (b >= 32 || c >= P.n_cols) continue;
+            const uint32_t k = 32 * (P.col0 + c) + b;     // window bit index
+            unsigned long long* dst;
+            if (KIND == EV_FWD) dst = J.counters + (size_t)(n == 0 ? C_NCC : n == 1 ? C_MFWD : C_MSCC) * P.stride;
+            else if (KIND == EV_REV) dst = J.counters + (size_t)C_MREV * P.stride;
+            else dst = J.aux + (size_t)n * P.stride;
+            atomicAdd(dst + k, (unsigned long long)v);
+        }
+        __syncthreads();
+    };
+
+    const uint32_t words_per_warp = P.tile_words / n_warps;
+    for (uint32_t t = t_lo; t < t_hi; ++t) {
+        uint32_t job = cur_job;
+        while (job + 1 < P.n_jobs && P.jobs[job + 1].tile_begin <= t) job++;
+        if (job != cur_job) {
+            flush_block(cur_job);
+            cur_job = job;
+        }
+        const EventJob& J = P.jobs[job];
+        if (KIND != EV_EDGE && (J.flags & EVF_AUTOCORR)) continue;      // no reads in such a job
+        if (KIND == EV_REV && !(J.flags & EVF_MSCC)) continue;
+        if (KIND == EV_EDGE && !(J.flags & (EVF_MSCC | EVF_AUTOCORR))) continue;
+        const long long N = (long long)J.array_words * 32;
+        const uint32_t w_begin = (t - J.tile_begin) * P.tile_words + warp * words_per_warp;
+
+        for (uint32_t g = w_begin; g < w_begin + words_per_warp; g += 32) {
+            if (g >= J.array_words) break;
+            const uint32_t i = g + lane;
+            uint32_t ev = 0, ev2 = 0;     // ev: reads / run starts; ev2: run ends
+            if (i < J.array_words) {
+                if (KIND == EV_FWD) ev = __ldg(J.F + i);
+                else if (KIND == EV_REV) ev = __ldg(J.R + i);
+                else {
+                    const uint32_t m = __ldg(J.M + i) & range_mask((long long)i * 32, J.a_lo, J.a_hi);
+                    uint32_t prev = 0;
+                    if (i > 0) prev = (__ldg(J.M + i - 1) & range_mask((long long)(i - 1) * 32, J.a_lo, J.a_hi)) >> 31;
+                    const uint32_t up = (m << 1) | prev;     // Mc[a-1]
+                    ev = m & ~up;
+                    ev2 = ~m & up;
+                }
+            }
+            uint32_t nz = __ballot_sync(0xFFFFFFFFu, (ev | ev2) != 0);
+            while (nz) {
+                const int src = __ffs(nz) - 1;
+                nz &= nz - 1;
+                uint32_t e1 = __shfl_sync(0xFFFFFFFFu, ev, src);
+                uint32_t e2 = (KIND == EV_EDGE) ? __shfl_sync(0xFFFFFFFFu, ev2, src) : 0u;
+                const long long base = (long long)(g + src) * 32;
+                while (e1 | e2) {
+                    const bool is_end = (e1 == 0);
+                    uint32_t& e = is_end ? e2 : e1;
+                    const int bit = __ffs(e) - 1;
+                    e &= e - 1;
+                    const long long a = base + bit;          // array bit of the event
+                    if (KIND == EV_FWD) {
+                        uint32_t x[3] = {0u, 0u, 0u};
+                        uint32_t w1 = 0;
+                        if (col_on) w1 = window_word(J.R, a, col, lane);
+                        else (void)__shfl_down_sync(0xFFFFFFFFu, 0u, 1);
+                        if (NCC) x[0] = w1;
+                        if (MSCC) {
+                            const uint32_t mp = (__ldg(J.M + (a >> 5)) >> (a & 31)) & 1u;   // M[p]
+                            if (mp) {     // warp-uniform
+                                uint32_t w2 = 0;
+                                if (col_on) w2 = window_word(J.Mr, N - a - (long long)P.read_len, col, lane);
+                                else (void)__shfl_down_sync(0xFFFFFFFFu, 0u, 1);
+                                x[1] = w2;
+                                x[2] = w1 & w2;
+                            }
+                        }
+                        sl.add(x, hist, lane);
+                    } else if (KIND == EV_REV) {
+                        // shifts k with j = q - k inside the counted range
+                        long long kmin = a - J.a_hi + 1, kmax = a - J.a_lo;
+                        if (kmin < 0) kmin = 0;
+                        if (kmax > D) kmax = D;
+                        if (kmin > kmax) continue;           // warp-uniform
+                        const long long tpos = a + (long long)P.read_len - 1;
+                        const uint32_t* dec = (tpos & 1) ? J.Or : J.Er;
+                        uint32_t x[1] = {0u};
+                        uint32_t w3 = 0, w4 = 0;
+                        if (col_on) {
+                            w3 = window_word(J.Mr, N - 1 - a, col, lane);
+                            w4 = window_word(dec, (N >> 1) - 1 - (tpos >> 1), col, lane);
+                        } else {
+                            (void)__shfl_down_sync(0xFFFFFFFFu, 0u, 1);
+                            (void)__shfl_down_sync(0xFFFFFFFFu, 0u, 1);
+                        }
+                        x[0] = w3 & w4 & range_mask((long long)col * 32, kmin, kmax + 1);
+                        sl.add(x, hist, lane);
+                    } else {
+                        const long long st = a + (long long)J.edge_off;
+                        uint32_t ws = 0, we = 0;
+                        if (col_on) {
+                            ws = window_word(J.Sb, st, col, lane);
+                            we = window_word(J.Eb, st, col, lane);
+                        } else {
+                            (void)__shfl_down_sync(0xFFFFFFFFu, 0u, 1);
+                            (void)__shfl_down_sync(0xFFFFFFFFu, 0u, 1);
+                        }
+                        uint32_t x[2];
+                        x[0] = is_end ? we : ws;     // start.start + end.end
+                        x[1] = is_end ? ws : we;     // start.end + end.start
+                        sl.add(x, hist, lane);
+                    }
+                }
+            }
+        }
+    }
+    flush_block(cur_job);
+}
+
+// ---------------------------------------------------------------- derive
+// One streaming pass over the (unclipped) M window of a job:
+//   Mr[w]  = brev(M[W-1-w])                    reversed
+//   Er/Or  = even / odd bits of M, reversed    (W/2 words each)
+//   Sb/Eb  = run starts M[a] & ~M[a-1] / run ends ~M[a] & M[a-1]
+//   adirect[0..1] += sum_j Mc[j] M[j + lag0/lag1]   (Mc = M clipped to [a_lo, a_hi))
+__device__ __forceinline__ uint32_t compress_even(uint64_t x)
+{
+    x &= 0x5555555555555555ull;
+    x = (x | (x >> 1)) & 0x3333333333333333ull;
+    x = (x | (x >> 2)) & 0x0f0f0f0f0f0f0f0full;
+    x = (x | (x >> 4)) & 0x00ff00ff00ff00ffull;
+    x = (x | (x >> 8)) & 0x0000ffff0000ffffull;
+    x = (x | (x >> 16)) & 0x00000000ffffffffull;
+    return (uint32_t)x;
+}
+
+__device__ __forceinline__ uint32_t word_at_lag(const uint32_t* __restrict__ M, long long i, long long lag,
+                                                long long W)
+{
+    // bits 32i + lag .. +31 of M (zero outside the array)
+    const long long q = lag >> 5;               // floor
+    const uint32_t r = (uint32_t)(lag & 31);
+    const long long w = i + q;
+    const uint32_t lo = (w >= 0 && w < W) ? M[w] : 0u;
+    const uint32_t hi = (w + 1 >= 0 && w + 1 < W) ? M[w + 1] : 0u;
+    return __funnelshift_r(lo, hi, r);
+}
+
+__global__ void derive_kernel(const uint32_t* __restrict__ M, uint32_t* __restrict__ Mr,
+                              uint32_t* __restrict__ Er, uint32_t* __restrict__ Or,
+                              uint32_t* __restrict__ Sb, uint32_t* __restrict__ Eb,
+                              uint32_t array_words, long long a_lo, long long a_hi,
+                              long long lag0, long long lag1, int n_lags,
+                              unsigned long long* __restrict__ adirect)
+{
+    const uint32_t pairs = array_words >> 1;
+    const long long W = array_words;
+    unsigned int c0 = 0, c1 = 0;
+    for (uint32_t v = blockIdx.x * blockDim.x + threadIdx.x; v < pairs; v += gridDim.x * blockDim.x) {
+        const uint32_t i = 2 * v;
+        const uint32_t m0 = M[i], m1 = M[i + 1];
+        const uint32_t prev = i ? (M[i - 1] >> 31) : 0u;
+        const uint32_t up0 = (m0 << 1) | prev, up1 = (m1 << 1) | (m0 >> 31);
+        Sb[i] = m0 & ~up0;
+        Sb[i + 1] = m1 & ~up1;
+        Eb[i] = ~m0 & up0;
+        Eb[i + 1] = ~m1 & up1;
+        if (Mr) {
+            Mr[array_words - 1 - i] = __brev(m0);
+            Mr[array_words - 2 - i] = __brev(m1);
+            const uint64_t x = ((uint64_t)m1 << 32) | m0;
+            Er[pairs - 1 - v] = __brev(compress_even(x));
+            Or[pairs - 1 - v] = __brev(compress_even(x >> 1));
+        }
+        const uint32_t mc0 = m0 & range_mask((long long)i * 32, a_lo, a_hi);
+        const uint32_t mc1 = m1 & range_mask((long long)(i + 1) * 32, a_lo, a_hi);
+        if (mc0) {
+            c0 += __popc(mc0 & word_at_lag(M, i, lag0, W));
+            if (n_lags > 1) c1 += __popc(mc0 & word_at_lag(M, i, lag1, W));
+        }
+        if (mc1) {
+            c0 += __popc(mc1 & word_at_lag(M, i + 1, lag0, W));
+            if (n_lags > 1) c1 += __popc(mc1 & word_at_lag(M, i + 1, lag1, W));
+        }
+    }
+    for (int o = 16; o; o >>= 1) {
+        c0 += __shfl_xor_sync(0xFFFFFFFFu, c0, o);
+        c1 += __shfl_xor_sync(0xFFFFFFFFu, c1, o);
+    }
+    if ((threadIdx.x & 31) == 0) {
+        if (c0) atomicAdd(adirect, (unsigned long long)c0);
+        if (c1) atomicAdd(adirect + 1, (unsigned long long)c1);
+    }
+}
+
+// ---------------------------------------------------------------- finalize
+// dmp from the two direct lags and the edge products C[b] = aux[0][b] - aux[1][b]:
+//   MSCC      dmp[0] = A[rl-1], dmp[1] = A[rl-2], dmp[k+1] = 2 dmp[k] - dmp[k-1] - C[D-k]
+//   AUTOCORR  out[0] = A[0],    out[1] = A[1],    out[s+1] = 2 out[s] - out[s-1] - C[s]
+// One thread per job (the chain is (max_shift+1) long and serial; it is tiny).
+__global__ void finalize_dmp_kernel(const EventJob* __restrict__ jobs, uint32_t n_jobs, uint32_t stride,
+                                    uint32_t max_shift)
+{
+    const uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= n_jobs) return;
+    const EventJob& J = jobs[j];
+    if (!(J.flags & (EVF_MSCC | EVF_AUTOCORR))) return;
+    const bool autocorr = (J.flags & EVF_AUTOCORR) != 0;
+    long long* out = (long long*)(J.counters + (size_t)C_DMP * stride);
+    const long long* plus = (const long long*)J.aux;
+    const long long* minus = plus + stride;
+    long long prev = (long long)J.adirect[0];
+    out[0] = prev;
+    if (max_shift == 0) return;
+    long long cur = (long long)J.adirect[1];
+    out[1] = cur;
+    for (uint32_t k = 1; k < max_shift; ++k) {
+        const uint32_t b = autocorr ? k : max_shift - k;
+        const long long nxt = 2 * cur - prev - (plus[b] - minus[b]);
+        out[k + 1] = nxt;
+        prev = cur;
+        cur = nxt;
+    }
+}
+
+}  // namespace pmb
