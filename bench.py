@@ -313,6 +313,10 @@ def gpu_arm(args):
         dev.set_option("variant", args.variant)
     if args.tile_words:
         dev.set_option("tile_words", args.tile_words)
+    dev.set_option("path", {"auto": 0, "dense": 1, "events": 2}[args.path])
+    for kv in args.opt:
+        k, v = kv.split("=")
+        dev.set_option(k, int(v))
 
     def barrier():
         if world > 1:
@@ -462,6 +466,9 @@ def main():
     ap.add_argument("--mode", default="both", choices=["both", "ncc"])
     ap.add_argument("--variant", type=int, default=None, help="shift-window kernel variant (tuning)")
     ap.add_argument("--tile-words", type=int, default=0)
+    ap.add_argument("--path", default="dense", choices=["auto", "dense", "events"],
+                    help="device algorithm: dense shift-window kernel or event-window kernels")
+    ap.add_argument("--opt", action="append", default=[], help="pmb_set_option name=value (tuning)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--cpu-sample-bp", type=int, default=20_000_000)
     ap.add_argument("--ref-cores", type=int, default=0)

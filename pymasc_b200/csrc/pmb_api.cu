@@ -14,6 +14,7 @@
 #include "pmb_build.cuh"
 #include "pmb_probe.cuh"
 #include "pmb_window.cuh"
+#include "pmb_events.cuh"
 
 using namespace pmb;
 
@@ -32,6 +33,9 @@ struct pmb_ctx {
     int tile_words = 0;      // 0: automatic
     int grid_blocks = 0;     // 0: one per SM
     int block_warps = 16;
+    int path = 0;            // 0 auto, 1 dense shift-window, 2 event-window
+    int event_tile_words = 0;
+    int event_blocks_per_sm = 0;
     // pinned staging for counters
     void* h_stage = nullptr;
     size_t h_stage_bytes = 0;
@@ -83,6 +87,12 @@ struct pmb_batch {
     WindowJob* d_jobs = nullptr; size_t d_jobs_count = 0;
     int* d_err = nullptr;
     uint32_t* d_long = nullptr; size_t long_cap = 0;   // [0] = count, [1..] = list
+    // event-window path
+    int path = 1;                       // 1 dense, 2 events
+    unsigned long long* d_aux = nullptr; size_t aux_words = 0;   // [n][2][stride] + [n][2]
+    EventJob* d_evjobs = nullptr;
+    uint32_t ev_total_tiles = 0, ev_tile_words = 0;
+    bool any_ncc = false, any_mscc = false, any_autocorr = false;
 };
 
 // ------------------------------------------------------------------ context
@@ -188,6 +198,9 @@ extern "C" int pmb_set_option(pmb_ctx* c, const char* name, int64_t value)
     else if (!strcmp(name, "tile_words")) c->tile_words = (int)value;
     else if (!strcmp(name, "grid_blocks")) c->grid_blocks = (int)value;
     else if (!strcmp(name, "block_warps")) c->block_warps = (int)value;
+    else if (!strcmp(name, "path")) c->path = (int)value;
+    else if (!strcmp(name, "event_tile_words")) c->event_tile_words = (int)value;
+    else if (!strcmp(name, "event_blocks_per_sm")) c->event_blocks_per_sm = (int)value;
     else { c->err = std::string("unknown option ") + name; return PMB_ERR_ARG; }
     return PMB_OK;
 }
@@ -213,6 +226,14 @@ enum { A_F = 0, A_R = 1, A_M = 2, A_MP = 3, A_FM = 4 };
 
 static bool whole_range(const JobPlan& j) { return j.lo == 0 && j.hi == (int64_t)j.nbits; }
 
+// event-window path: array slots, in units of array_words (Er and Or are half arrays)
+enum { E_F = 0, E_R = 1, E_M = 2, E_MR = 3, E_SB = 4, E_EB = 5, E_ER = 6 };
+static size_t event_words_of(const JobPlan& j)
+{
+    if (j.autocorr) return 3 * j.array_words;                       // M, Sb, Eb (slots 0..2)
+    return ((j.mode & MODE_MSCC) ? 7 : 2) * j.array_words;          // F, R [, M, Mr, Sb, Eb, Er|Or]
+}
+
 static int arrays_of(const JobPlan& j)
 {
     // autocorrelation: M (whole window, the "R" role) [+ M clipped to the shard, the "F" role]
@@ -231,6 +252,8 @@ extern "C" void pmb_batch_free(pmb_ctx* c, pmb_batch* b)
         if (b->d_jobs) cudaFreeAsync(b->d_jobs, c->stream);
         if (b->d_err) cudaFreeAsync(b->d_err, c->stream);
         if (b->d_long) cudaFreeAsync(b->d_long, c->stream);
+        if (b->d_aux) cudaFreeAsync(b->d_aux, c->stream);
+        if (b->d_evjobs) cudaFreeAsync(b->d_evjobs, c->stream);
         cudaStreamSynchronize(c->stream);
     }
     delete b;
@@ -307,6 +330,57 @@ static int plan_windows(pmb_ctx* c, pmb_batch* b)
     return PMB_OK;
 }
 
+// Event-window path: one job table for the three event kernels; tiles cover the WHOLE array of
+// every job (halos included: reverse reads in the halo contribute to in-range positions).
+static int plan_events(pmb_ctx* c, pmb_batch* b)
+{
+    const size_t n = b->jobs.size();
+    const uint32_t TW = c->event_tile_words > 0 ? (uint32_t)c->event_tile_words : 2048;
+    if (TW % 256) { c->err = "event_tile_words must be a multiple of 256"; return PMB_ERR_ARG; }
+    b->ev_tile_words = TW;
+    b->aux_words = n * (2 * (size_t)b->stride + 2);
+    CU_TRY(c, cudaMallocAsync((void**)&b->d_aux, b->aux_words * 8, c->stream));
+    CU_TRY(c, cudaMallocAsync((void**)&b->d_evjobs, n * sizeof(EventJob), c->stream));
+    std::vector<EventJob> table(n);
+    uint32_t tiles = 0;
+    unsigned long long* adirect0 = b->d_aux + n * 2 * (size_t)b->stride;
+    for (size_t i = 0; i < n; i++) {
+        JobPlan& j = b->jobs[i];
+        uint32_t* base = b->d_bits + j.bits;
+        auto arr = [&](int slot) { return base + (size_t)slot * j.array_words; };
+        EventJob e{};
+        if (j.autocorr) {
+            e.M = arr(0); e.Sb = arr(1); e.Eb = arr(2);
+            e.flags = EVF_AUTOCORR;
+            e.edge_off = 0;
+        } else {
+            e.F = arr(E_F); e.R = arr(E_R);
+            e.flags = (j.mode & MODE_NCC ? EVF_NCC : 0) | (j.mode & MODE_MSCC ? EVF_MSCC : 0);
+            if (j.mode & MODE_MSCC) {
+                e.M = arr(E_M); e.Mr = arr(E_MR); e.Sb = arr(E_SB); e.Eb = arr(E_EB);
+                e.Er = arr(E_ER); e.Or = arr(E_ER) + j.array_words / 2;
+            }
+            e.edge_off = (int32_t)b->read_len - 1 - (int32_t)b->max_shift;
+        }
+        e.counters = b->d_counters + i * PMB_NCOUNTERS * b->stride;
+        e.aux = b->d_aux + i * 2 * (size_t)b->stride;
+        e.adirect = adirect0 + 2 * i;
+        const int64_t off = (int64_t)b->halo_words * 32 - j.origin_word * 32;   // chrom bit -> array bit
+        e.a_lo = j.lo + off;
+        e.a_hi = j.hi + off;
+        e.array_words = (uint32_t)j.array_words;
+        e.tile_begin = tiles;
+        e.n_tiles = (uint32_t)((j.array_words + TW - 1) / TW);
+        tiles += e.n_tiles;
+        table[i] = e;
+    }
+    b->ev_total_tiles = tiles;
+    CU_TRY(c, cudaMemcpyAsync(b->d_evjobs, table.data(), n * sizeof(EventJob), cudaMemcpyHostToDevice,
+                              c->stream));
+    CU_TRY(c, cudaStreamSynchronize(c->stream));   // `table` is a local
+    return PMB_OK;
+}
+
 extern "C" int pmb_batch_prepare(pmb_ctx* c, const pmb_chrom_args* a, uint32_t n, pmb_batch** out)
 {
     if (!c || !a || !out || n == 0) return PMB_ERR_ARG;
@@ -358,11 +432,29 @@ extern "C" int pmb_batch_prepare(pmb_ctx* c, const pmb_chrom_args* a, uint32_t n
         j.origin_word = (j.lo >> 5) & ~(int64_t)3;
         total_words += (uint64_t)(((j.hi + 31) >> 5) - j.origin_word);
     }
+    // Which algorithm?  The event-window path costs ~ (reads + run edges) x shifts/32, the dense
+    // shift-window path ~ words x shifts; both give identical counts.  auto: events unless the
+    // inputs are so dense that there are more than 4 events per 32-bit word.
+    uint64_t total_events = 0;
+    for (uint32_t i = 0; i < n; i++) {
+        total_events += a[i].n_fwd + a[i].n_rev + 2 * a[i].n_intervals;
+        b->any_ncc |= (a[i].flags & PMB_FLAG_NCC) && !(a[i].flags & PMB_FLAG_AUTOCORR);
+        b->any_mscc |= (a[i].flags & PMB_FLAG_MSCC) && !(a[i].flags & PMB_FLAG_AUTOCORR);
+        b->any_autocorr |= (a[i].flags & PMB_FLAG_AUTOCORR) != 0;
+    }
+    b->path = c->path == 1 || c->path == 2 ? c->path : (total_events <= 4 * total_words ? 2 : 1);
     const uint32_t blocks = c->grid_blocks > 0 ? (uint32_t)c->grid_blocks : (uint32_t)c->num_sms;
     uint32_t T = 1024;
-    if (c->tile_words > 0) T = (uint32_t)c->tile_words;
-    else while (T > 64 && total_words / T < 8ull * blocks) T >>= 1;
-    if (T < 64 || (T & 63)) { c->err = "tile_words must be a multiple of 64"; return PMB_ERR_ARG; }
+    if (b->path == 2) {
+        T = 64;   // body granule only; the event kernels tile the whole array themselves
+        // windows reach 2*max_shift + read_len beyond the counted range (the stride-2 window of
+        // the reverse reads), plus the idle-lane / upper-neighbour words
+        b->halo_words = ((2 * b->max_shift + b->read_len + 192 + 31) / 32 + 3) & ~3u;
+    } else {
+        if (c->tile_words > 0) T = (uint32_t)c->tile_words;
+        else while (T > 64 && total_words / T < 8ull * blocks) T >>= 1;
+        if (T < 64 || (T & 63)) { c->err = "tile_words must be a multiple of 64"; return PMB_ERR_ARG; }
+    }
     b->tile_words = T;
 
     // pass 2: layout
@@ -375,7 +467,7 @@ extern "C" int pmb_batch_prepare(pmb_ctx* c, const pmb_chrom_args* a, uint32_t n
         j.body_words = (uint64_t)j.n_tiles * T;
         j.array_words = 2 * (size_t)b->halo_words + j.body_words;
         j.bits = bits_words;
-        bits_words += (size_t)arrays_of(j) * j.array_words;
+        bits_words += b->path == 2 ? event_words_of(j) : (size_t)arrays_of(j) * j.array_words;
         auto take = [&](uint64_t cnt) { size_t o = in_words; in_words += (cnt + 3) & ~3ull; return o; };
         if (!j.autocorr) { j.in_fwd = take(j.a.n_fwd); j.in_rev = take(j.a.n_rev); }
         if ((j.mode & MODE_MSCC) || j.autocorr) { j.in_mb = take(j.a.n_intervals); j.in_me = take(j.a.n_intervals); }
@@ -413,7 +505,7 @@ extern "C" int pmb_batch_prepare(pmb_ctx* c, const pmb_chrom_args* a, uint32_t n
         j.a.fwd_pos = j.a.rev_pos = j.a.map_begin = j.a.map_end = nullptr;   // borrowed no longer
     }
     {
-        int rc = plan_windows(c, b);
+        int rc = b->path == 2 ? plan_events(c, b) : plan_windows(c, b);
         if (rc != PMB_OK) return rc;
     }
     CU_TRY(c, cudaStreamSynchronize(c->stream));   // host arrays may be released by the caller
@@ -455,10 +547,129 @@ static cudaError_t launch_window(pmb_ctx* c, int variant, const WindowParams& P,
 #undef PMB_LAUNCH
 }
 
+// ------------------------------------------------------------------ batch: execute (event path)
+static int execute_events(pmb_ctx* c, pmb_batch* b)
+{
+    cudaStream_t st = c->stream;
+    const uint32_t H = b->halo_words;
+    const int64_t NEG = -(1ll << 40), POS = (1ll << 40);
+    uint32_t launches = 0;
+    const size_t n = b->jobs.size();
+
+    CU_TRY(c, cudaEventRecord(c->ev[0], st));
+    CU_TRY(c, cudaMemsetAsync(b->d_bits, 0, std::max<size_t>(b->bits_words, 4) * 4, st));
+    CU_TRY(c, cudaMemsetAsync(b->d_counters, 0, b->counter_words * 8, st));
+    CU_TRY(c, cudaMemsetAsync(b->d_aux, 0, b->aux_words * 8, st));
+    CU_TRY(c, cudaMemsetAsync(b->d_err, 0, 16, st));
+    unsigned long long* d_totals = b->d_counters + n * PMB_NCOUNTERS * b->stride;
+    unsigned long long* adirect0 = b->d_aux + n * 2 * (size_t)b->stride;
+
+    auto blocks_for = [&](uint64_t items, int per_block) {
+        uint64_t g = (items + per_block - 1) / per_block;
+        return (unsigned)std::min<uint64_t>(std::max<uint64_t>(g, 1), (uint64_t)c->num_sms * 16);
+    };
+    for (size_t i = 0; i < n; i++) {
+        JobPlan& j = b->jobs[i];
+        Geometry g;
+        g.origin_bit = j.origin_word * 32;
+        g.halo_bits = (int64_t)H * 32;
+        g.total_bits = (int64_t)j.array_words * 32;
+        uint32_t* base = b->d_bits + j.bits;
+        auto arr = [&](int slot) { return base + (size_t)slot * j.array_words; };
+        const int64_t off = g.halo_bits - g.origin_bit;
+        const bool mscc = !j.autocorr && (j.mode & MODE_MSCC);
+        uint32_t* M = j.autocorr ? arr(0) : (mscc ? arr(E_M) : nullptr);
+
+        if (!j.autocorr) {
+            if (j.a.n_fwd) {
+                scatter_bits_kernel<<<blocks_for(j.a.n_fwd, 256), 256, 0, st>>>(
+                    arr(E_F), g, b->d_in + j.in_fwd, j.a.n_fwd, j.lo, j.hi, j.nbits, b->d_err);
+                launches++;
+            }
+            if (j.a.n_rev) {
+                scatter_bits_kernel<<<blocks_for(j.a.n_rev, 256), 256, 0, st>>>(
+                    arr(E_R), g, b->d_in + j.in_rev, j.a.n_rev, NEG, POS, j.nbits, b->d_err);
+                launches++;
+            }
+            prep_kernel<<<blocks_for(j.body_words, 1024), 256, 0, st>>>(
+                arr(E_F) + H, nullptr, nullptr, arr(E_R) + H, j.body_words, g.origin_bit, j.lo, j.hi,
+                d_totals + 2 * i);
+            launches++;
+        }
+        if (M) {
+            if (j.a.n_intervals) {
+                CU_TRY(c, cudaMemsetAsync(b->d_long, 0, 4, st));
+                fill_intervals_kernel<<<blocks_for(j.a.n_intervals, 8), 256, 0, st>>>(
+                    M, g, b->d_in + j.in_mb, b->d_in + j.in_me, j.a.n_intervals, 0, NEG, POS, j.nbits,
+                    b->d_err, b->d_long + 1, b->d_long);
+                fill_long_kernel<<<c->num_sms * 4, 256, 0, st>>>(M, g, b->d_in + j.in_mb,
+                                                                 b->d_in + j.in_me, 0, NEG, POS,
+                                                                 b->d_long + 1, b->d_long);
+                launches += 2;
+            }
+            const long long lag0 = j.autocorr ? 0 : (long long)b->read_len - 1;
+            const long long lag1 = j.autocorr ? 1 : (long long)b->read_len - 2;
+            derive_kernel<<<blocks_for(j.array_words / 2, 256), 256, 0, st>>>(
+                M, j.autocorr ? nullptr : arr(E_MR), j.autocorr ? nullptr : arr(E_ER),
+                j.autocorr ? nullptr : arr(E_ER) + j.array_words / 2,
+                j.autocorr ? arr(1) : arr(E_SB), j.autocorr ? arr(2) : arr(E_EB),
+                (uint32_t)j.array_words, j.lo + off, j.hi + off, lag0, lag1, b->max_shift ? 2 : 1,
+                adirect0 + 2 * i);
+            launches++;
+        }
+    }
+    CU_TRY(c, cudaGetLastError());
+    CU_TRY(c, cudaEventRecord(c->ev[1], st));
+
+    EventParams P{};
+    P.jobs = b->d_evjobs;
+    P.n_jobs = (uint32_t)n;
+    P.total_tiles = b->ev_total_tiles;
+    P.tile_words = b->ev_tile_words;
+    P.max_shift = b->max_shift;
+    P.read_len = b->read_len;
+    P.stride = b->stride;
+    const uint32_t n_cols_total = (b->n_shifts + 31) / 32;
+    const uint32_t bps = c->event_blocks_per_sm > 0 ? (uint32_t)c->event_blocks_per_sm : 8;
+    const uint32_t grid = std::max(1u, std::min(b->ev_total_tiles, (uint32_t)c->num_sms * bps));
+    uint32_t window_launches = 0;
+    for (uint32_t col0 = 0; col0 < n_cols_total; col0 += 32) {
+        P.col0 = col0;
+        P.n_cols = std::min(32u, n_cols_total - col0);
+        if (b->any_ncc || b->any_mscc) {
+            if (b->any_ncc && b->any_mscc) event_window_kernel<EV_FWD, true, true><<<grid, 256, 0, st>>>(P);
+            else if (b->any_ncc) event_window_kernel<EV_FWD, true, false><<<grid, 256, 0, st>>>(P);
+            else event_window_kernel<EV_FWD, false, true><<<grid, 256, 0, st>>>(P);
+            window_launches++;
+        }
+        if (b->any_mscc) {
+            event_window_kernel<EV_REV, false, true><<<grid, 256, 0, st>>>(P);
+            window_launches++;
+        }
+        if (b->any_mscc || b->any_autocorr) {
+            event_window_kernel<EV_EDGE, false, true><<<grid, 256, 0, st>>>(P);
+            window_launches++;
+        }
+    }
+    if (b->any_mscc || b->any_autocorr) {
+        finalize_dmp_kernel<<<(unsigned)((n + 63) / 64), 64, 0, st>>>(b->d_evjobs, (uint32_t)n, b->stride,
+                                                                     b->max_shift);
+        window_launches++;
+    }
+    CU_TRY(c, cudaGetLastError());
+    CU_TRY(c, cudaEventRecord(c->ev[2], st));
+    c->timing.launches = launches + window_launches;
+    c->timing.window_launches = window_launches;
+    c->timing.window_word_shift_pairs = 0;
+    c->timing.build_ms = c->timing.window_ms = c->timing.total_ms = -1.f;
+    return PMB_OK;
+}
+
 extern "C" int pmb_batch_execute(pmb_ctx* c, pmb_batch* b)
 {
     if (!c || !b) return PMB_ERR_ARG;
     CU_TRY(c, cudaSetDevice(c->device));
+    if (b->path == 2) return execute_events(c, b);
     cudaStream_t st = c->stream;
     const uint32_t H = b->halo_words;
     const int64_t NEG = -(1ll << 40), POS = (1ll << 40);

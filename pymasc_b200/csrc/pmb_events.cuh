@@ -193,8 +193,11 @@ __global__ void __launch_bounds__(256) event_window_kernel(const EventParams P)
 
     Slices<NC> sl;
     sl.reset();
-    const uint32_t col = P.col0 + lane;          // this lane's window column
+    // this lane's window column; idle lanes (n_cols < 32) load the word after the last column,
+    // which is what the last active lane needs as its upper neighbour (always inside the halo)
     const bool col_on = lane < (int)P.n_cols;
+    const uint32_t col = P.col0 + (col_on ? (uint32_t)lane : P.n_cols);
+    const uint32_t col_mask = col_on ? 0xFFFFFFFFu : 0u;
     const long long D = P.max_shift;
 
     uint32_t cur_job = 0;
@@ -266,24 +269,20 @@ __global__ void __launch_bounds__(256) event_window_kernel(const EventParams P)
                     const int bit = __ffs(e) - 1;
                     e &= e - 1;
                     const long long a = base + bit;          // array bit of the event
-                    if (KIND == EV_FWD) {
+                    if constexpr (KIND == EV_FWD) {
                         uint32_t x[3] = {0u, 0u, 0u};
-                        uint32_t w1 = 0;
-                        if (col_on) w1 = window_word(J.R, a, col, lane);
-                        else (void)__shfl_down_sync(0xFFFFFFFFu, 0u, 1);
-                        if (NCC) x[0] = w1;
-                        if (MSCC) {
+                        const uint32_t w1 = window_word(J.R, a, col, lane) & col_mask;
+                        if (NCC && (J.flags & EVF_NCC)) x[0] = w1;
+                        if (MSCC && (J.flags & EVF_MSCC)) {
                             const uint32_t mp = (__ldg(J.M + (a >> 5)) >> (a & 31)) & 1u;   // M[p]
                             if (mp) {     // warp-uniform
-                                uint32_t w2 = 0;
-                                if (col_on) w2 = window_word(J.Mr, N - a - (long long)P.read_len, col, lane);
-                                else (void)__shfl_down_sync(0xFFFFFFFFu, 0u, 1);
+                                const uint32_t w2 = window_word(J.Mr, N - a - (long long)P.read_len, col, lane) & col_mask;
                                 x[1] = w2;
                                 x[2] = w1 & w2;
                             }
                         }
                         sl.add(x, hist, lane);
-                    } else if (KIND == EV_REV) {
+                    } else if constexpr (KIND == EV_REV) {
                         // shifts k with j = q - k inside the counted range
                         long long kmin = a - J.a_hi + 1, kmax = a - J.a_lo;
                         if (kmin < 0) kmin = 0;
@@ -292,26 +291,14 @@ __global__ void __launch_bounds__(256) event_window_kernel(const EventParams P)
                         const long long tpos = a + (long long)P.read_len - 1;
                         const uint32_t* dec = (tpos & 1) ? J.Or : J.Er;
                         uint32_t x[1] = {0u};
-                        uint32_t w3 = 0, w4 = 0;
-                        if (col_on) {
-                            w3 = window_word(J.Mr, N - 1 - a, col, lane);
-                            w4 = window_word(dec, (N >> 1) - 1 - (tpos >> 1), col, lane);
-                        } else {
-                            (void)__shfl_down_sync(0xFFFFFFFFu, 0u, 1);
-                            (void)__shfl_down_sync(0xFFFFFFFFu, 0u, 1);
-                        }
-                        x[0] = w3 & w4 & range_mask((long long)col * 32, kmin, kmax + 1);
+                        const uint32_t w3 = window_word(J.Mr, N - 1 - a, col, lane);
+                        const uint32_t w4 = window_word(dec, (N >> 1) - 1 - (tpos >> 1), col, lane);
+                        x[0] = w3 & w4 & col_mask & range_mask((long long)col * 32, kmin, kmax + 1);
                         sl.add(x, hist, lane);
                     } else {
                         const long long st = a + (long long)J.edge_off;
-                        uint32_t ws = 0, we = 0;
-                        if (col_on) {
-                            ws = window_word(J.Sb, st, col, lane);
-                            we = window_word(J.Eb, st, col, lane);
-                        } else {
-                            (void)__shfl_down_sync(0xFFFFFFFFu, 0u, 1);
-                            (void)__shfl_down_sync(0xFFFFFFFFu, 0u, 1);
-                        }
+                        const uint32_t ws = window_word(J.Sb, st, col, lane) & col_mask;
+                        const uint32_t we = window_word(J.Eb, st, col, lane) & col_mask;
                         uint32_t x[2];
                         x[0] = is_end ? we : ws;     // start.start + end.end
                         x[1] = is_end ? ws : we;     // start.end + end.start

@@ -12,6 +12,7 @@ from pymasc_b200.exceptions import PositionOutOfRange
 
 pytestmark = pytest.mark.gpu
 RTOL = 1e-9
+PATHS = (1, 2)      # 1 dense shift-window, 2 event-window (0 = auto picks one of them)
 
 
 @pytest.fixture(scope="module")
@@ -22,16 +23,31 @@ def dev():
 
 
 def check_job(dev, L, rl, D, fwd, rev, b=None, e=None, flags=None, lo=0, hi=0):
+    """Both device algorithms -- the dense shift-window kernel (path 1) and the event-window
+    kernels (path 2) -- against the oracle, bit for bit."""
     if flags is None:
         flags = _shim.FLAG_NCC | (_shim.FLAG_MSCC if b is not None else 0)
-    got = dev.run_batch([_shim.Job(L, rl, D, flags, fwd, rev, b, e, lo, hi)])[0]
     mscc = bool(flags & _shim.FLAG_MSCC)
     want = cc_oracle.chrom_counts(L, rl, D, fwd, rev, b if mscc else None, e if mscc else None,
                                   skip_ncc=not flags & _shim.FLAG_NCC, lo=lo, hi=hi or None)
-    assert sorted(got) == sorted(want)
-    for k in want:
-        assert np.array_equal(np.asarray(got[k]), np.asarray(want[k])), k
+    try:
+        for path in PATHS:
+            dev.set_option("path", path)
+            got = dev.run_batch([_shim.Job(L, rl, D, flags, fwd, rev, b, e, lo, hi)])[0]
+            assert sorted(got) == sorted(want)
+            for k in want:
+                assert np.array_equal(np.asarray(got[k]), np.asarray(want[k])), (k, "path %d" % path)
+    finally:
+        dev.set_option("path", 0)
     return got
+
+
+@pytest.fixture(params=PATHS, ids=lambda p: "dense" if p == 1 else "events")
+def pdev(dev, request):
+    """The device pinned to one algorithm for the whole test."""
+    dev.set_option("path", request.param)
+    yield dev
+    dev.set_option("path", 0)
 
 
 def random_case(seed, L, rl, n_reads, with_track=True):
@@ -120,7 +136,8 @@ def test_position_shards_with_halos_add_up(dev):
         assert np.array_equal(np.asarray(whole[k]), sum(np.asarray(p[k]) for p in parts)), k
 
 
-def test_batch_of_mixed_jobs_and_autocorrelation(dev):
+def test_batch_of_mixed_jobs_and_autocorrelation(pdev):
+    dev = pdev
     rl, D = 36, 300
     jobs, wants = [], []
     for i, L in enumerate([50000, 120000, 80000]):
@@ -205,7 +222,8 @@ def test_toy_cases_through_the_calculator(spec):
 
 
 # ----------------------------------------------------------------- full-size properties
-def test_hg38_chr21_properties(dev):
+def test_hg38_chr21_properties(pdev):
+    dev = pdev
     """BASELINE config 2/3 shapes at full chromosome size (chr21 + chr22, max_shift 1000),
     through size-independent properties: dmp symmetry (popc(D_k) depends on |rl-1-k| only),
     k = 0 identities, shard additivity, and an oracle check on a window of shifts."""
@@ -243,7 +261,8 @@ def test_hg38_chr21_properties(dev):
 
 # ----------------------------------------------------------------- the N > 1 decomposition
 @pytest.mark.parametrize("world", [2, 8])
-def test_rank_jobs_from_the_sharding_plan_add_up(dev, world):
+def test_rank_jobs_from_the_sharding_plan_add_up(pdev, world):
+    dev = pdev
     """What bench.py / ShardedEngine run per rank: identical job lists with clipped inputs and
     empty ranges, executed here rank after rank on one device; the per-rank counter blocks
     must sum to the whole-genome result (the all-reduce is a plain int64 sum)."""
