@@ -356,15 +356,36 @@ def gpu_arm(args):
         launches_per_step = dev.timing()["launches"]
 
         # ---- per-kernel times of the same step (library CUDA events on the same stream)
-        win_ms, build_ms = [], []
+        win_ms, build_ms, fwd_ms, rev_ms, edge_ms = [], [], [], [], []
         for _ in range(max(3, min(args.steps, 10))):
             batch.execute()
             t = dev.timing()
             win_ms.append(t["window_ms"]); build_ms.append(t["build_ms"])
+            fwd_ms.append(t["ev_fwd_ms"]); rev_ms.append(t["ev_rev_ms"]); edge_ms.append(t["ev_edge_ms"])
         pairs = t["window_word_shift_pairs"]
         win_launches = t["window_launches"]
+        used_path = t["path"]
         resident = batch.fetch()
         batch.free()
+
+        # ---- the other algorithm on the same inputs: must give identical counters; the dense
+        #      shift-window kernel is the one the popc-pipe roofline is quoted on
+        other = None
+        if not args.single_path:
+            dev.set_option("path", 1 if used_path == 2 else 2)
+            ob = dev.prepare(jobs)
+            o_win, o_build = [], []
+            for _ in range(4):
+                ob.execute()
+                t2 = dev.timing()
+                o_win.append(t2["window_ms"]); o_build.append(t2["build_ms"])
+            o_out = ob.fetch()
+            ob.free()
+            dev.set_option("path", {"auto": 0, "dense": 1, "events": 2}[args.path])
+            other = {"path": t2["path"], "window_ms": float(np.mean(o_win[1:])),
+                     "build_ms": float(np.mean(o_build[1:])), "pairs": t2["window_word_shift_pairs"],
+                     "same": all(np.array_equal(np.asarray(a[k]), np.asarray(b2[k]))
+                                 for a, b2 in zip(resident, o_out) for k in a)}
 
         # ---- end-to-end arm: pinned host arrays in, counters on the host out
         def e2e_step():
@@ -412,35 +433,71 @@ def gpu_arm(args):
         except OSError:
             pass
         hbm_peak = peaks.get("hbm_gbs", 6650.0)
+        peak_src = "MEASURED_PEAKS.json hbm_gbs (of measured)" if peaks else "6650 GB/s (of fallback)"
+        bits_bytes = sum(L + READ_LEN + MAX_SHIFT + 100 for L in lengths) / 8.0 / world   # one bit array
+
+        def dense_roofline(window_s, word_pairs):
+            """Shift-window kernel: integer AND+popcount, bound by the POPC/ALU pipes."""
+            return {"bound": "popc", "kernel": "shift_window_kernel",
+                    "achieved": popc_alg / window_s / 1e9, "peak": popc_peak / 1e9, "unit": "Gpopc32/s",
+                    "frac": popc_alg / window_s / popc_peak,
+                    "peak_source": "pmb_pipe_probe(POPC) measured in this run (MEASURED_PEAKS.json has no "
+                                   "integer-pipe figure); LOP3 rate %.0f Gop/s. frac > 1 is possible: "
+                                   "carry-save counters execute 0.5 POPC per algorithmic popc32"
+                                   % (lop3_peak / 1e9),
+                    "algorithmic_popc_per_eval": P / 32.0, "kernel_ms": window_s * 1e3,
+                    "executed_word_shift_pairs": int(word_pairs),
+                    "traffic": 1.954e9 / world if mode == "both" else None,
+                    "traffic_source": "profiles/r01_ncu_shift_window_dense_v1.txt (ncu --set full, N=1)",
+                    "hbm": {"algorithmic_bytes": alg_bytes, "achieved_gbs": alg_bytes / window_s / 1e9,
+                            "peak_gbs": hbm_peak, "frac": alg_bytes / window_s / 1e9 / hbm_peak}}
+
+        def events_roofline(fwd_s, all_s):
+            """Event-window kernels: every array is streamed once, windows come from L1/L2; the
+            floor is HBM.  Dominant kernel: the forward-read kernel (F, R [, M, Mr])."""
+            nbytes = (4 if mode == "both" else 2) * bits_bytes
+            return {"bound": "hbm", "kernel": "event_window_kernel<EV_FWD>",
+                    "achieved": nbytes / fwd_s / 1e9, "peak": hbm_peak, "unit": "GB/s",
+                    "frac": nbytes / fwd_s / 1e9 / hbm_peak, "peak_source": peak_src,
+                    "algorithmic_bytes": nbytes, "kernel_ms": fwd_s * 1e3,
+                    "all_event_kernels_ms": all_s * 1e3,
+                    "traffic": None,
+                    "note": "latency/issue-bound today (see profiles/); evals/s of this path are "
+                            "delivered evals: the counts equal the dense kernel's bit for bit"}
+
+        paths = {}
+        if used_path == 2:
+            roof = events_roofline(float(np.mean(fwd_ms)) * 1e-3, win_s)
+            roof.update(rev_kernel_ms=float(np.mean(rev_ms)), edge_kernel_ms=float(np.mean(edge_ms)),
+                        build_ms=float(np.mean(build_ms)), kernel_launches_per_step=int(win_launches))
+            paths["events"] = {"window_ms": win_s * 1e3, "build_ms": float(np.mean(build_ms))}
+            if other:
+                paths["dense"] = {"window_ms": other["window_ms"], "build_ms": other["build_ms"],
+                                  "roofline": dense_roofline(other["window_ms"] * 1e-3, other["pairs"]),
+                                  "counters_equal_events_path": other["same"]}
+        else:
+            roof = dense_roofline(win_s, pairs)
+            roof.update(build_ms=float(np.mean(build_ms)), kernel_launches_per_step=int(win_launches))
+            paths["dense"] = {"window_ms": win_s * 1e3, "build_ms": float(np.mean(build_ms))}
+            if other:
+                paths["events"] = {"window_ms": other["window_ms"], "build_ms": other["build_ms"],
+                                   "counters_equal_dense_path": other["same"]}
         line = {
             "metric": METRIC, "value": evals_total / (ms_per_step * 1e-3), "unit": UNIT,
             "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_per_step,
             "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "u32",
             "data": "synthetic", "config": dict(workload_config(mode),
                                                 parallelism="position ranges x%d + NCCL all-reduce" % world
-                                                if world > 1 else "1 GPU"),
+                                                if world > 1 else "1 GPU",
+                                                path="events" if used_path == 2 else "dense"),
             "e2e": {"value": evals_total / (e2e_ms * 1e-3), "unit": UNIT, "ms_per_step": e2e_ms,
                     "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
                     "api": "pmb_batch_prepare/execute/fetch via ctypes (pymasc_b200._shim)"},
             "gpu_launches": int(launches_per_step * args.steps),
             "launches_per_step": int(launches_per_step),
             "clocks": clocks,
-            "roofline": {
-                "bound": "popc", "kernel": "shift_window_kernel",
-                "achieved": popc_alg / win_s / 1e9, "peak": popc_peak / 1e9, "unit": "Gpopc32/s",
-                "frac": popc_alg / win_s / popc_peak,
-                "peak_source": "pmb_pipe_probe(POPC) measured in this run (MEASURED_PEAKS.json has no "
-                               "integer-pipe figure); LOP3 rate %.0f Gop/s" % (lop3_peak / 1e9),
-                "algorithmic_popc_per_eval": P / 32.0,
-                "kernel_ms": win_s * 1e3, "kernel_launches_per_step": int(win_launches),
-                "build_ms": float(np.mean(build_ms)),
-                "executed_word_shift_pairs": int(pairs),
-                "traffic": None,
-                "hbm": {"algorithmic_bytes": alg_bytes, "achieved_gbs": alg_bytes / win_s / 1e9,
-                        "peak_gbs": hbm_peak,
-                        "peak_source": "MEASURED_PEAKS.json" if peaks else "fallback",
-                        "frac": alg_bytes / win_s / 1e9 / hbm_peak},
-            },
+            "roofline": roof,
+            "paths": paths,
             "resident_equals_e2e": bool(same),
             "synthetic_generation_s": round(gen_s, 1),
         }
@@ -466,7 +523,8 @@ def main():
     ap.add_argument("--mode", default="both", choices=["both", "ncc"])
     ap.add_argument("--variant", type=int, default=None, help="shift-window kernel variant (tuning)")
     ap.add_argument("--tile-words", type=int, default=0)
-    ap.add_argument("--path", default="dense", choices=["auto", "dense", "events"],
+    ap.add_argument("--single-path", action="store_true", help="skip the cross-check pass of the other algorithm")
+    ap.add_argument("--path", default="auto", choices=["auto", "dense", "events"],
                     help="device algorithm: dense shift-window kernel or event-window kernels")
     ap.add_argument("--opt", action="append", default=[], help="pmb_set_option name=value (tuning)")
     ap.add_argument("--no-cpu-baseline", action="store_true")

@@ -102,7 +102,11 @@ typedef struct {
     float total_ms;     /* first launch to last launch of the execute        */
     uint32_t launches;  /* kernels launched by the execute                   */
     uint32_t window_launches;
-    uint64_t window_word_shift_pairs; /* 32-bit word x shift pairs evaluated  */
+    uint64_t window_word_shift_pairs; /* 32-bit word x shift pairs evaluated (dense path) */
+    uint32_t path;      /* algorithm the execute used: 1 dense shift-window, 2 event-window */
+    float ev_fwd_ms;    /* event path: forward-read kernel(s)                 */
+    float ev_rev_ms;    /* event path: reverse-read kernel(s)                 */
+    float ev_edge_ms;   /* event path: run-edge kernel(s) + finalize          */
 } pmb_timing;
 
 int  pmb_create(pmb_ctx **out, int device_ordinal);
@@ -144,8 +148,11 @@ int   pmb_set_stream(pmb_ctx *ctx, void *stream);
 int  pmb_host_alloc(void **out, uint64_t bytes);
 void pmb_host_free(void *p);
 
-/* Tuning knobs (0 = default): variant selects the carry-save depth of the
- * shift-window kernel's counters, tile_words its tile size. */
+/* Options (0 = default).  "path": 0 auto, 1 dense shift-window kernel, 2 event-window
+ * kernels -- two algorithms for the same counts (identical results); auto takes the
+ * event path unless the inputs hold more than 4 events (reads + run edges) per 32-bit
+ * word.  Tuning: "variant" (carry-save depth of the shift-window counters), "tile_words",
+ * "grid_blocks", "block_warps", "event_tile_words", "event_blocks_per_sm". */
 int  pmb_set_option(pmb_ctx *ctx, const char *name, int64_t value);
 
 /* Integer-pipe calibration on the device: runs a dependent-free loop of `what`

@@ -50,6 +50,8 @@ class Timing(ctypes.Structure):
         ("build_ms", ctypes.c_float), ("window_ms", ctypes.c_float), ("total_ms", ctypes.c_float),
         ("launches", ctypes.c_uint32), ("window_launches", ctypes.c_uint32),
         ("window_word_shift_pairs", ctypes.c_uint64),
+        ("path", ctypes.c_uint32), ("ev_fwd_ms", ctypes.c_float), ("ev_rev_ms", ctypes.c_float),
+        ("ev_edge_ms", ctypes.c_float),
     ]
 
 
@@ -250,7 +252,8 @@ class Device(object):
         self._check(self._L.pmb_get_timing(self._h, ctypes.byref(t)))
         return {"build_ms": t.build_ms, "window_ms": t.window_ms, "total_ms": t.total_ms,
                 "launches": t.launches, "window_launches": t.window_launches,
-                "window_word_shift_pairs": t.window_word_shift_pairs}
+                "window_word_shift_pairs": t.window_word_shift_pairs, "path": t.path,
+                "ev_fwd_ms": t.ev_fwd_ms, "ev_rev_ms": t.ev_rev_ms, "ev_edge_ms": t.ev_edge_ms}
 
     def pipe_probe(self, what):
         ops, ms = ctypes.c_double(), ctypes.c_float()

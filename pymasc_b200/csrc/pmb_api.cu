@@ -26,6 +26,7 @@ struct pmb_ctx {
     cudaStream_t stream = nullptr;
     cudaStream_t own_stream = nullptr;   // created by pmb_create; `stream` may be borrowed
     cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
+    cudaEvent_t evk[2] = {nullptr, nullptr};   // event path: after the fwd / rev kernels
     std::string err;
     pmb_timing timing{};
     // options
@@ -134,6 +135,8 @@ extern "C" int pmb_create(pmb_ctx** out, int device_ordinal)
     c->stream = c->own_stream;
     for (auto& ev : c->ev)
         if ((e = cudaEventCreate(&ev)) != cudaSuccess) return fail("cudaEventCreate", e);
+    for (auto& ev : c->evk)
+        if ((e = cudaEventCreate(&ev)) != cudaSuccess) return fail("cudaEventCreate", e);
     // keep freed blocks cached in the stream-ordered pool (arena behaviour)
     cudaMemPool_t pool;
     if (cudaDeviceGetDefaultMemPool(&pool, device_ordinal) == cudaSuccess) {
@@ -150,6 +153,8 @@ extern "C" void pmb_destroy(pmb_ctx* c)
     cudaSetDevice(c->device);
     if (c->stream) cudaStreamSynchronize(c->stream);
     for (auto& ev : c->ev)
+        if (ev) cudaEventDestroy(ev);
+    for (auto& ev : c->evk)
         if (ev) cudaEventDestroy(ev);
     if (c->h_stage) cudaFreeHost(c->h_stage);
     if (c->own_stream) cudaStreamDestroy(c->own_stream);
@@ -214,6 +219,11 @@ extern "C" int pmb_get_timing(pmb_ctx* c, pmb_timing* t)
         CU_TRY(c, cudaEventElapsedTime(&c->timing.build_ms, c->ev[0], c->ev[1]));
         CU_TRY(c, cudaEventElapsedTime(&c->timing.window_ms, c->ev[1], c->ev[2]));
         CU_TRY(c, cudaEventElapsedTime(&c->timing.total_ms, c->ev[0], c->ev[2]));
+        if (c->timing.path == 2) {
+            CU_TRY(c, cudaEventElapsedTime(&c->timing.ev_fwd_ms, c->ev[1], c->evk[0]));
+            CU_TRY(c, cudaEventElapsedTime(&c->timing.ev_rev_ms, c->evk[0], c->evk[1]));
+            CU_TRY(c, cudaEventElapsedTime(&c->timing.ev_edge_ms, c->evk[1], c->ev[2]));
+        }
     }
     *t = c->timing;
     return PMB_OK;
@@ -633,24 +643,24 @@ static int execute_events(pmb_ctx* c, pmb_batch* b)
     const uint32_t bps = c->event_blocks_per_sm > 0 ? (uint32_t)c->event_blocks_per_sm : 8;
     const uint32_t grid = std::max(1u, std::min(b->ev_total_tiles, (uint32_t)c->num_sms * bps));
     uint32_t window_launches = 0;
-    for (uint32_t col0 = 0; col0 < n_cols_total; col0 += 32) {
-        P.col0 = col0;
-        P.n_cols = std::min(32u, n_cols_total - col0);
-        if (b->any_ncc || b->any_mscc) {
-            if (b->any_ncc && b->any_mscc) event_window_kernel<EV_FWD, true, true><<<grid, 256, 0, st>>>(P);
-            else if (b->any_ncc) event_window_kernel<EV_FWD, true, false><<<grid, 256, 0, st>>>(P);
-            else event_window_kernel<EV_FWD, false, true><<<grid, 256, 0, st>>>(P);
+    auto chunks = [&](auto&& launch) {
+        for (uint32_t col0 = 0; col0 < n_cols_total; col0 += 32) {
+            P.col0 = col0;
+            P.n_cols = std::min(32u, n_cols_total - col0);
+            launch();
             window_launches++;
         }
-        if (b->any_mscc) {
-            event_window_kernel<EV_REV, false, true><<<grid, 256, 0, st>>>(P);
-            window_launches++;
-        }
-        if (b->any_mscc || b->any_autocorr) {
-            event_window_kernel<EV_EDGE, false, true><<<grid, 256, 0, st>>>(P);
-            window_launches++;
-        }
-    }
+    };
+    if (b->any_ncc || b->any_mscc) chunks([&] {
+        if (b->any_ncc && b->any_mscc) event_window_kernel<EV_FWD, true, true><<<grid, 256, 0, st>>>(P);
+        else if (b->any_ncc) event_window_kernel<EV_FWD, true, false><<<grid, 256, 0, st>>>(P);
+        else event_window_kernel<EV_FWD, false, true><<<grid, 256, 0, st>>>(P);
+    });
+    CU_TRY(c, cudaEventRecord(c->evk[0], st));
+    if (b->any_mscc) chunks([&] { event_window_kernel<EV_REV, false, true><<<grid, 256, 0, st>>>(P); });
+    CU_TRY(c, cudaEventRecord(c->evk[1], st));
+    if (b->any_mscc || b->any_autocorr)
+        chunks([&] { event_window_kernel<EV_EDGE, false, true><<<grid, 256, 0, st>>>(P); });
     if (b->any_mscc || b->any_autocorr) {
         finalize_dmp_kernel<<<(unsigned)((n + 63) / 64), 64, 0, st>>>(b->d_evjobs, (uint32_t)n, b->stride,
                                                                      b->max_shift);
@@ -661,6 +671,7 @@ static int execute_events(pmb_ctx* c, pmb_batch* b)
     c->timing.launches = launches + window_launches;
     c->timing.window_launches = window_launches;
     c->timing.window_word_shift_pairs = 0;
+    c->timing.path = 2;
     c->timing.build_ms = c->timing.window_ms = c->timing.total_ms = -1.f;
     return PMB_OK;
 }
@@ -764,6 +775,8 @@ extern "C" int pmb_batch_execute(pmb_ctx* c, pmb_batch* b)
     c->timing.launches = launches + window_launches;
     c->timing.window_launches = window_launches;
     c->timing.window_word_shift_pairs = pairs;
+    c->timing.path = 1;
+    c->timing.ev_fwd_ms = c->timing.ev_rev_ms = c->timing.ev_edge_ms = 0.f;
     c->timing.build_ms = c->timing.window_ms = c->timing.total_ms = -1.f;   // resolved lazily
     return PMB_OK;
 }

@@ -30,7 +30,7 @@ def test_struct_layouts_match_the_header():
     # 64-bit fields first, no implicit padding surprises
     assert ctypes.sizeof(_shim.ChromArgs) == 8 + 4 * 4 + 8 * 9
     assert ctypes.sizeof(_shim.ChromOut) == 8 * 7
-    assert ctypes.sizeof(_shim.Timing) == 4 * 3 + 4 * 2 + 4 + 8   # one pad word before the u64
+    assert ctypes.sizeof(_shim.Timing) == 4 * 3 + 4 * 2 + 4 + 8 + 4 * 4   # one pad word before the u64
 
 
 def test_create_fails_cleanly_without_a_device():
