@@ -23,9 +23,10 @@
 // descending and the stride-2 descending windows become ascending ones); derive_kernel
 // writes them, Sb and Eb in one streaming pass over M.
 //
-// Mapping.  A warp scans 32 words of the event source at a time (coalesced), and handles the
-// events one after the other: lane <-> window column (32 shifts), so one event is a 128-byte
-// coalesced, unaligned window load per array + one funnel shift per lane.  The per-shift
+// Mapping.  A warp scans 32 words of the event source at a time (coalesced), stages the
+// window spans of that group in shared memory (see "Span staging" below) and handles the
+// events one after the other: lane <-> window column (32 shifts), so one event is two
+// conflict-free LDS + one funnel shift per lane and array.  The per-shift
 // counts are kept BIT-SLICED in registers: a carry-save binary counter (acc/pend word per
 // level, ~1 CSA = 2 LOP3 per event and counter, independent of the window's density); a
 // carry out of the top level and the final residue go to a per-block shared-memory
@@ -146,18 +147,6 @@ struct Slices {
     }
 };
 
-// Window column `col` (32 bits) of array A starting at bit `st`: every lane loads one word,
-// the upper neighbour comes by shuffle (lane 31 loads its own).
-__device__ __forceinline__ uint32_t window_word(const uint32_t* __restrict__ A, long long st, uint32_t col,
-                                                int lane)
-{
-    const long long w = (st >> 5) + col;
-    const uint32_t lo = __ldg(A + w);
-    uint32_t hi = __shfl_down_sync(0xFFFFFFFFu, lo, 1);
-    if (lane == 31) hi = __ldg(A + w + 1);
-    return __funnelshift_r(lo, hi, (uint32_t)(st & 31));
-}
-
 __device__ __forceinline__ uint32_t range_mask(long long bit0, long long lo, long long hi)
 {
     if (bit0 + 32 <= lo || bit0 >= hi) return 0u;
@@ -165,6 +154,38 @@ __device__ __forceinline__ uint32_t range_mask(long long bit0, long long lo, lon
     if (bit0 < lo) mask &= 0xFFFFFFFFu << (lo - bit0);
     if (bit0 + 32 > hi) mask &= 0xFFFFFFFFu >> (bit0 + 32 - hi);
     return mask;
+}
+
+// Span staging.  All events of one 32-word scan group (1024 bit positions from array bit G)
+// need windows that lie in a <= 68-word span of each array, whose start depends on G only:
+//   ascending arrays  (R, Sb, Eb):  window start = B + e,          B = G + c0
+//   reversed arrays   (Mr, Er, Or): window start = B + (emax - e), B = C - G - emax
+// with e the event's offset inside the group.  The warp loads each span ONCE per group
+// (coalesced, all loads in flight together: one memory latency per group instead of one per
+// event) into its private shared-memory slice; an event then costs two conflict-free LDS and
+// one funnel shift per array.
+constexpr int EV_SPAN = 68;            // words per staged span (>= 33 + 32 + 1, padded)
+constexpr int EV_WARPS = 8;            // warps per CTA
+constexpr int EV_SPANS = 3;            // spans per warp (REV: Mr, Er, Or)
+
+__device__ __forceinline__ void stage_span(uint32_t* dst, const uint32_t* __restrict__ A, long long base_word,
+                                           long long n_words, int lane)
+{
+#pragma unroll
+    for (int i = 0; i < 3; ++i) {
+        const int k = lane + 32 * i;
+        if (k < EV_SPAN) {
+            const long long w = base_word + k;
+            dst[k] = (w >= 0 && w < n_words) ? __ldg(A + w) : 0u;
+        }
+    }
+}
+
+// window column `lane` (+ col0 already folded into the span base) at span bit offset o
+__device__ __forceinline__ uint32_t span_word(const uint32_t* sp, uint32_t o, int lane)
+{
+    const uint32_t w = (o >> 5) + lane;
+    return __funnelshift_r(sp[w], sp[w + 1], o & 31);
 }
 
 template <int KIND>
@@ -175,14 +196,18 @@ template <> struct EvTraits<EV_EDGE> { static constexpr int NC = 2; };   // + an
 
 // KIND: which events; NCC / MSCC: which counters the batch asked for.
 template <int KIND, bool NCC, bool MSCC>
-__global__ void __launch_bounds__(256) event_window_kernel(const EventParams P)
+__global__ void __launch_bounds__(32 * EV_WARPS) event_window_kernel(const EventParams P)
 {
     constexpr int NC = EvTraits<KIND>::NC;
     __shared__ uint32_t hist[NC * 32 * EV_HIST_STRIDE];
+    __shared__ uint32_t spans[EV_WARPS][EV_SPANS][EV_SPAN];
 
     const int lane = threadIdx.x & 31;
     const int warp = threadIdx.x >> 5;
     const int n_warps = blockDim.x >> 5;
+    uint32_t* sp0 = spans[warp][0];
+    uint32_t* sp1 = spans[warp][1];
+    uint32_t* sp2 = spans[warp][2];
 
     const uint32_t t_lo = (uint32_t)(((uint64_t)P.total_tiles * blockIdx.x) / gridDim.x);
     const uint32_t t_hi = (uint32_t)(((uint64_t)P.total_tiles * (blockIdx.x + 1)) / gridDim.x);
@@ -193,12 +218,9 @@ __global__ void __launch_bounds__(256) event_window_kernel(const EventParams P)
 
     Slices<NC> sl;
     sl.reset();
-    // this lane's window column; idle lanes (n_cols < 32) load the word after the last column,
-    // which is what the last active lane needs as its upper neighbour (always inside the halo)
-    const bool col_on = lane < (int)P.n_cols;
-    const uint32_t col = P.col0 + (col_on ? (uint32_t)lane : P.n_cols);
-    const uint32_t col_mask = col_on ? 0xFFFFFFFFu : 0u;
-    const long long D = P.max_shift;
+    const uint32_t col_mask = lane < (int)P.n_cols ? 0xFFFFFFFFu : 0u;   // idle lanes when n_cols < 32
+    const int D = (int)P.max_shift;
+    const int rl = (int)P.read_len;
 
     uint32_t cur_job = 0;
     while (cur_job + 1 < P.n_jobs && P.jobs[cur_job + 1].tile_begin <= t_lo) cur_job++;
@@ -237,17 +259,24 @@ __global__ void __launch_bounds__(256) event_window_kernel(const EventParams P)
         if (KIND != EV_EDGE && (J.flags & EVF_AUTOCORR)) continue;      // no reads in such a job
         if (KIND == EV_REV && !(J.flags & EVF_MSCC)) continue;
         if (KIND == EV_EDGE && !(J.flags & (EVF_MSCC | EVF_AUTOCORR))) continue;
-        const long long N = (long long)J.array_words * 32;
+        const long long W = J.array_words;
+        const long long N = W * 32;
+        const bool job_ncc = NCC && (J.flags & EVF_NCC);
+        const bool job_mscc = MSCC && (J.flags & EVF_MSCC);
         const uint32_t w_begin = (t - J.tile_begin) * P.tile_words + warp * words_per_warp;
 
         for (uint32_t g = w_begin; g < w_begin + words_per_warp; g += 32) {
             if (g >= J.array_words) break;
             const uint32_t i = g + lane;
-            uint32_t ev = 0, ev2 = 0;     // ev: reads / run starts; ev2: run ends
+            const long long G = (long long)g * 32;
+            uint32_t ev = 0, ev2 = 0, mword = 0;     // ev: reads / run starts; ev2: run ends
             if (i < J.array_words) {
-                if (KIND == EV_FWD) ev = __ldg(J.F + i);
-                else if (KIND == EV_REV) ev = __ldg(J.R + i);
-                else {
+                if (KIND == EV_FWD) {
+                    ev = __ldg(J.F + i);
+                    if (job_mscc) mword = __ldg(J.M + i);
+                } else if (KIND == EV_REV) {
+                    ev = __ldg(J.R + i);
+                } else {
                     const uint32_t m = __ldg(J.M + i) & range_mask((long long)i * 32, J.a_lo, J.a_hi);
                     uint32_t prev = 0;
                     if (i > 0) prev = (__ldg(J.M + i - 1) & range_mask((long long)(i - 1) * 32, J.a_lo, J.a_hi)) >> 31;
@@ -257,48 +286,84 @@ __global__ void __launch_bounds__(256) event_window_kernel(const EventParams P)
                 }
             }
             uint32_t nz = __ballot_sync(0xFFFFFFFFu, (ev | ev2) != 0);
+            if (!nz) continue;
+
+            // ---- stage this group's spans (warp-private shared memory)
+            uint32_t r0 = 0, r1 = 0;            // bit offsets of the span origins
+            long long gl = 0, gh = 0;           // REV: k-range of the shard, relative to the group
+            bool full = true;
+            __syncwarp();
+            if constexpr (KIND == EV_FWD) {
+                stage_span(sp0, J.R, (long long)g + P.col0, W, lane);
+                if (job_mscc) {
+                    const long long B = N - G - rl - 1023;
+                    r0 = (uint32_t)(B & 31);
+                    stage_span(sp1, J.Mr, (B >> 5) + P.col0, W, lane);
+                }
+            } else if constexpr (KIND == EV_REV) {
+                gl = G - J.a_lo;                // kmax = min(D, gl + e)
+                gh = G - J.a_hi + 1;            // kmin = max(0, gh + e)
+                if (gl + 1023 < 0 || gh > D) continue;          // no event of the group counts
+                full = (gh + 1023 <= 0) && (gl >= D);
+                const long long B = N - G - 1024;
+                r0 = (uint32_t)(B & 31);
+                stage_span(sp0, J.Mr, (B >> 5) + P.col0, W, lane);
+                const int hmax = (1022 + rl) >> 1;
+                const long long B4 = (N >> 1) - 1 - (G >> 1) - hmax;
+                r1 = (uint32_t)(B4 & 31);
+                stage_span(sp1, J.Er, (B4 >> 5) + P.col0, W >> 1, lane);
+                stage_span(sp2, J.Or, (B4 >> 5) + P.col0, W >> 1, lane);
+            } else {
+                const long long B = G + J.edge_off;
+                r0 = (uint32_t)(B & 31);
+                stage_span(sp0, J.Sb, (B >> 5) + P.col0, W, lane);
+                stage_span(sp1, J.Eb, (B >> 5) + P.col0, W, lane);
+            }
+            __syncwarp();
+
             while (nz) {
                 const int src = __ffs(nz) - 1;
                 nz &= nz - 1;
                 uint32_t e1 = __shfl_sync(0xFFFFFFFFu, ev, src);
                 uint32_t e2 = (KIND == EV_EDGE) ? __shfl_sync(0xFFFFFFFFu, ev2, src) : 0u;
-                const long long base = (long long)(g + src) * 32;
+                const uint32_t msrc = (KIND == EV_FWD && MSCC) ? __shfl_sync(0xFFFFFFFFu, mword, src) : 0u;
                 while (e1 | e2) {
                     const bool is_end = (e1 == 0);
-                    uint32_t& e = is_end ? e2 : e1;
-                    const int bit = __ffs(e) - 1;
-                    e &= e - 1;
-                    const long long a = base + bit;          // array bit of the event
+                    const uint32_t ecur = is_end ? e2 : e1;
+                    const int bit = __ffs(ecur) - 1;
+                    if (is_end) e2 = ecur & (ecur - 1);
+                    else e1 = ecur & (ecur - 1);
+                    const uint32_t eo = 32u * src + bit;          // event offset inside the group
                     if constexpr (KIND == EV_FWD) {
                         uint32_t x[3] = {0u, 0u, 0u};
-                        const uint32_t w1 = window_word(J.R, a, col, lane) & col_mask;
-                        if (NCC && (J.flags & EVF_NCC)) x[0] = w1;
-                        if (MSCC && (J.flags & EVF_MSCC)) {
-                            const uint32_t mp = (__ldg(J.M + (a >> 5)) >> (a & 31)) & 1u;   // M[p]
-                            if (mp) {     // warp-uniform
-                                const uint32_t w2 = window_word(J.Mr, N - a - (long long)P.read_len, col, lane) & col_mask;
-                                x[1] = w2;
-                                x[2] = w1 & w2;
-                            }
+                        const uint32_t w1 = span_word(sp0, eo, lane) & col_mask;
+                        if (job_ncc) x[0] = w1;
+                        if (job_mscc && ((msrc >> bit) & 1u)) {          // M[p], warp-uniform
+                            const uint32_t w2 = span_word(sp1, r0 + 1023u - eo, lane) & col_mask;
+                            x[1] = w2;
+                            x[2] = w1 & w2;
                         }
                         sl.add(x, hist, lane);
                     } else if constexpr (KIND == EV_REV) {
-                        // shifts k with j = q - k inside the counted range
-                        long long kmin = a - J.a_hi + 1, kmax = a - J.a_lo;
-                        if (kmin < 0) kmin = 0;
-                        if (kmax > D) kmax = D;
-                        if (kmin > kmax) continue;           // warp-uniform
-                        const long long tpos = a + (long long)P.read_len - 1;
-                        const uint32_t* dec = (tpos & 1) ? J.Or : J.Er;
-                        uint32_t x[1] = {0u};
-                        const uint32_t w3 = window_word(J.Mr, N - 1 - a, col, lane);
-                        const uint32_t w4 = window_word(dec, (N >> 1) - 1 - (tpos >> 1), col, lane);
-                        x[0] = w3 & w4 & col_mask & range_mask((long long)col * 32, kmin, kmax + 1);
+                        uint32_t kmask = col_mask;
+                        if (!full) {      // shifts k with j = q - k inside the counted range
+                            long long kmin = gh + eo, kmax = gl + eo;
+                            if (kmin < 0) kmin = 0;
+                            if (kmax > D) kmax = D;
+                            if (kmin > kmax) continue;           // warp-uniform
+                            kmask &= range_mask((long long)(P.col0 + lane) * 32, kmin, kmax + 1);
+                        }
+                        const uint32_t tl = eo + (uint32_t)rl - 1u;              // (q + rl - 1) - G
+                        const uint32_t* dec = (tl & 1u) ? sp2 : sp1;
+                        const uint32_t hmax = (uint32_t)((1022 + rl) >> 1);
+                        uint32_t x[1];
+                        const uint32_t w3 = span_word(sp0, r0 + 1023u - eo, lane);
+                        const uint32_t w4 = span_word(dec, r1 + hmax - (tl >> 1), lane);
+                        x[0] = w3 & w4 & kmask;
                         sl.add(x, hist, lane);
                     } else {
-                        const long long st = a + (long long)J.edge_off;
-                        const uint32_t ws = window_word(J.Sb, st, col, lane) & col_mask;
-                        const uint32_t we = window_word(J.Eb, st, col, lane) & col_mask;
+                        const uint32_t ws = span_word(sp0, r0 + eo, lane) & col_mask;
+                        const uint32_t we = span_word(sp1, r0 + eo, lane) & col_mask;
                         uint32_t x[2];
                         x[0] = is_end ? we : ws;     // start.start + end.end
                         x[1] = is_end ? ws : we;     // start.end + end.start
