@@ -375,6 +375,7 @@ static int plan_events(pmb_ctx* c, pmb_batch* b)
         e.counters = b->d_counters + i * PMB_NCOUNTERS * b->stride;
         e.aux = b->d_aux + i * 2 * (size_t)b->stride;
         e.adirect = adirect0 + 2 * i;
+        e.totals = b->d_counters + n * PMB_NCOUNTERS * b->stride + 2 * i;
         const int64_t off = (int64_t)b->halo_words * 32 - j.origin_word * 32;   // chrom bit -> array bit
         e.a_lo = j.lo + off;
         e.a_hi = j.hi + off;
@@ -567,11 +568,15 @@ static int execute_events(pmb_ctx* c, pmb_batch* b)
     const size_t n = b->jobs.size();
 
     CU_TRY(c, cudaEventRecord(c->ev[0], st));
-    CU_TRY(c, cudaMemsetAsync(b->d_bits, 0, std::max<size_t>(b->bits_words, 4) * 4, st));
+    // only the scattered / filled arrays need zeroing (slots F, R, M come first in a job);
+    // Mr, Er, Or, Sb, Eb are written in full by derive_kernel
+    for (const JobPlan& j : b->jobs) {
+        const size_t zero_arrays = j.autocorr ? 1 : ((j.mode & MODE_MSCC) ? 3 : 2);
+        CU_TRY(c, cudaMemsetAsync(b->d_bits + j.bits, 0, zero_arrays * j.array_words * 4, st));
+    }
     CU_TRY(c, cudaMemsetAsync(b->d_counters, 0, b->counter_words * 8, st));
     CU_TRY(c, cudaMemsetAsync(b->d_aux, 0, b->aux_words * 8, st));
     CU_TRY(c, cudaMemsetAsync(b->d_err, 0, 16, st));
-    unsigned long long* d_totals = b->d_counters + n * PMB_NCOUNTERS * b->stride;
     unsigned long long* adirect0 = b->d_aux + n * 2 * (size_t)b->stride;
 
     auto blocks_for = [&](uint64_t items, int per_block) {
@@ -601,11 +606,7 @@ static int execute_events(pmb_ctx* c, pmb_batch* b)
                     arr(E_R), g, b->d_in + j.in_rev, j.a.n_rev, NEG, POS, j.nbits, b->d_err);
                 launches++;
             }
-            prep_kernel<<<blocks_for(j.body_words, 1024), 256, 0, st>>>(
-                arr(E_F) + H, nullptr, nullptr, arr(E_R) + H, j.body_words, g.origin_bit, j.lo, j.hi,
-                d_totals + 2 * i);
-            launches++;
-        }
+        }   // strand totals: counted by the forward-read event kernel while it scans F and R
         if (M) {
             if (j.a.n_intervals) {
                 CU_TRY(c, cudaMemsetAsync(b->d_long, 0, 4, st));
@@ -619,7 +620,7 @@ static int execute_events(pmb_ctx* c, pmb_batch* b)
             }
             const long long lag0 = j.autocorr ? 0 : (long long)b->read_len - 1;
             const long long lag1 = j.autocorr ? 1 : (long long)b->read_len - 2;
-            derive_kernel<<<blocks_for(j.array_words / 2, 256), 256, 0, st>>>(
+            derive_kernel<<<blocks_for(j.array_words / 4, 256), 256, 0, st>>>(
                 M, j.autocorr ? nullptr : arr(E_MR), j.autocorr ? nullptr : arr(E_ER),
                 j.autocorr ? nullptr : arr(E_ER) + j.array_words / 2,
                 j.autocorr ? arr(1) : arr(E_SB), j.autocorr ? arr(2) : arr(E_EB),

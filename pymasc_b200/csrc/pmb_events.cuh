@@ -55,6 +55,7 @@ struct EventJob {
     unsigned long long* counters;   // [5][stride]
     unsigned long long* aux;        // [2][stride]: edge products, + then - (window-bit indexed)
     unsigned long long* adirect;    // [2]: the two directly counted lags
+    unsigned long long* totals;     // [2]: popc(F), popc(R) over the counted range
     long long a_lo, a_hi;           // counted range in array bits
     uint32_t array_words;
     uint32_t tile_begin, n_tiles;
@@ -218,6 +219,7 @@ __global__ void __launch_bounds__(32 * EV_WARPS) event_window_kernel(const Event
 
     Slices<NC> sl;
     sl.reset();
+    uint32_t tot_f = 0, tot_r = 0;       // EV_FWD, first column chunk: strand totals of the job
     const uint32_t col_mask = lane < (int)P.n_cols ? 0xFFFFFFFFu : 0u;   // idle lanes when n_cols < 32
     const int D = (int)P.max_shift;
     const int rl = (int)P.read_len;
@@ -229,6 +231,17 @@ __global__ void __launch_bounds__(32 * EV_WARPS) event_window_kernel(const Event
         sl.flush(hist, lane);
         __syncthreads();
         const EventJob& J = P.jobs[job];
+        if (KIND == EV_FWD && P.col0 == 0) {      // bit_array_num_bits_set (bit_array.c:962-978)
+            for (int o = 16; o; o >>= 1) {
+                tot_f += __shfl_xor_sync(0xFFFFFFFFu, tot_f, o);
+                tot_r += __shfl_xor_sync(0xFFFFFFFFu, tot_r, o);
+            }
+            if (lane == 0) {
+                if (tot_f) atomicAdd(J.totals, (unsigned long long)tot_f);
+                if (tot_r) atomicAdd(J.totals + 1, (unsigned long long)tot_r);
+            }
+            tot_f = tot_r = 0;
+        }
         for (uint32_t i = threadIdx.x; i < NC * 32 * EV_HIST_STRIDE; i += blockDim.x) {
             const uint32_t v = hist[i];
             if (!v) continue;
@@ -274,6 +287,10 @@ __global__ void __launch_bounds__(32 * EV_WARPS) event_window_kernel(const Event
                 if (KIND == EV_FWD) {
                     ev = __ldg(J.F + i);
                     if (job_mscc) mword = __ldg(J.M + i);
+                    if (P.col0 == 0) {
+                        tot_f += __popc(ev);        // F is clipped to the counted range at build
+                        tot_r += __popc(__ldg(J.R + i) & range_mask((long long)i * 32, J.a_lo, J.a_hi));
+                    }
                 } else if (KIND == EV_REV) {
                     ev = __ldg(J.R + i);
                 } else {
@@ -393,18 +410,12 @@ __device__ __forceinline__ uint32_t compress_even(uint64_t x)
     return (uint32_t)x;
 }
 
-__device__ __forceinline__ uint32_t word_at_lag(const uint32_t* __restrict__ M, long long i, long long lag,
-                                                long long W)
+__device__ __forceinline__ uint32_t load_or_zero(const uint32_t* __restrict__ M, long long w, long long W)
 {
-    // bits 32i + lag .. +31 of M (zero outside the array)
-    const long long q = lag >> 5;               // floor
-    const uint32_t r = (uint32_t)(lag & 31);
-    const long long w = i + q;
-    const uint32_t lo = (w >= 0 && w < W) ? M[w] : 0u;
-    const uint32_t hi = (w + 1 >= 0 && w + 1 < W) ? M[w + 1] : 0u;
-    return __funnelshift_r(lo, hi, r);
+    return (w >= 0 && w < W) ? __ldg(M + w) : 0u;
 }
 
+// One thread per 4 words (16-byte loads / stores; array_words is a multiple of 4).
 __global__ void derive_kernel(const uint32_t* __restrict__ M, uint32_t* __restrict__ Mr,
                               uint32_t* __restrict__ Er, uint32_t* __restrict__ Or,
                               uint32_t* __restrict__ Sb, uint32_t* __restrict__ Eb,
@@ -412,34 +423,57 @@ __global__ void derive_kernel(const uint32_t* __restrict__ M, uint32_t* __restri
                               long long lag0, long long lag1, int n_lags,
                               unsigned long long* __restrict__ adirect)
 {
+    const uint32_t quads = array_words >> 2;
     const uint32_t pairs = array_words >> 1;
     const long long W = array_words;
+    const long long q0 = lag0 >> 5, q1 = lag1 >> 5;
+    const uint32_t s0 = (uint32_t)(lag0 & 31), s1 = (uint32_t)(lag1 & 31);
     unsigned int c0 = 0, c1 = 0;
-    for (uint32_t v = blockIdx.x * blockDim.x + threadIdx.x; v < pairs; v += gridDim.x * blockDim.x) {
-        const uint32_t i = 2 * v;
-        const uint32_t m0 = M[i], m1 = M[i + 1];
-        const uint32_t prev = i ? (M[i - 1] >> 31) : 0u;
-        const uint32_t up0 = (m0 << 1) | prev, up1 = (m1 << 1) | (m0 >> 31);
-        Sb[i] = m0 & ~up0;
-        Sb[i + 1] = m1 & ~up1;
-        Eb[i] = ~m0 & up0;
-        Eb[i + 1] = ~m1 & up1;
+    for (uint32_t v = blockIdx.x * blockDim.x + threadIdx.x; v < quads; v += gridDim.x * blockDim.x) {
+        const uint32_t i = 4 * v;
+        const uint4 m4 = *reinterpret_cast<const uint4*>(M + i);
+        const uint32_t m[4] = {m4.x, m4.y, m4.z, m4.w};
+        uint32_t carry = i ? (__ldg(M + i - 1) >> 31) : 0u;
+        uint32_t sb[4], eb[4];
+#pragma unroll
+        for (int t = 0; t < 4; ++t) {
+            const uint32_t up = (m[t] << 1) | carry;      // M[a-1]
+            sb[t] = m[t] & ~up;
+            eb[t] = ~m[t] & up;
+            carry = m[t] >> 31;
+        }
+        *reinterpret_cast<uint4*>(Sb + i) = make_uint4(sb[0], sb[1], sb[2], sb[3]);
+        *reinterpret_cast<uint4*>(Eb + i) = make_uint4(eb[0], eb[1], eb[2], eb[3]);
         if (Mr) {
-            Mr[array_words - 1 - i] = __brev(m0);
-            Mr[array_words - 2 - i] = __brev(m1);
-            const uint64_t x = ((uint64_t)m1 << 32) | m0;
-            Er[pairs - 1 - v] = __brev(compress_even(x));
-            Or[pairs - 1 - v] = __brev(compress_even(x >> 1));
+            *reinterpret_cast<uint4*>(Mr + (array_words - 4 - i)) =
+                make_uint4(__brev(m[3]), __brev(m[2]), __brev(m[1]), __brev(m[0]));
+            const uint64_t x0 = ((uint64_t)m[1] << 32) | m[0], x1 = ((uint64_t)m[3] << 32) | m[2];
+            const uint32_t at = pairs - 2 - (i >> 1);
+            *reinterpret_cast<uint2*>(Er + at) = make_uint2(__brev(compress_even(x1)), __brev(compress_even(x0)));
+            *reinterpret_cast<uint2*>(Or + at) =
+                make_uint2(__brev(compress_even(x1 >> 1)), __brev(compress_even(x0 >> 1)));
         }
-        const uint32_t mc0 = m0 & range_mask((long long)i * 32, a_lo, a_hi);
-        const uint32_t mc1 = m1 & range_mask((long long)(i + 1) * 32, a_lo, a_hi);
-        if (mc0) {
-            c0 += __popc(mc0 & word_at_lag(M, i, lag0, W));
-            if (n_lags > 1) c1 += __popc(mc0 & word_at_lag(M, i, lag1, W));
+        // directly counted lags: sum_j Mc[j] M[j + lag]
+        uint32_t mc[4];
+        uint32_t any = 0;
+#pragma unroll
+        for (int t = 0; t < 4; ++t) {
+            mc[t] = m[t] & range_mask((long long)(i + t) * 32, a_lo, a_hi);
+            any |= mc[t];
         }
-        if (mc1) {
-            c0 += __popc(mc1 & word_at_lag(M, i + 1, lag0, W));
-            if (n_lags > 1) c1 += __popc(mc1 & word_at_lag(M, i + 1, lag1, W));
+        if (any) {
+            uint32_t n0[5], n1[5];
+#pragma unroll
+            for (int t = 0; t < 5; ++t) n0[t] = load_or_zero(M, (long long)i + q0 + t, W);
+            if (n_lags > 1) {
+#pragma unroll
+                for (int t = 0; t < 5; ++t) n1[t] = (q1 == q0) ? n0[t] : load_or_zero(M, (long long)i + q1 + t, W);
+            }
+#pragma unroll
+            for (int t = 0; t < 4; ++t) {
+                c0 += __popc(mc[t] & __funnelshift_r(n0[t], n0[t + 1], s0));
+                if (n_lags > 1) c1 += __popc(mc[t] & __funnelshift_r(n1[t], n1[t + 1], s1));
+            }
         }
     }
     for (int o = 16; o; o >>= 1) {
