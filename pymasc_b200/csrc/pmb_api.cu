@@ -84,6 +84,7 @@ struct pmb_batch {
     uint32_t n_units = 0, stride = 0, halo_words = 0, tile_words = 0;
     uint32_t* d_in = nullptr;  size_t in_words = 0;
     uint32_t* d_bits = nullptr; size_t bits_words = 0;
+    uint32_t* d_bits_raw = nullptr;   // allocation; d_bits = raw + EV_PAD_WORDS (TMA regions may overhang)
     unsigned long long* d_counters = nullptr; size_t counter_words = 0;  // + totals at the end
     WindowJob* d_jobs = nullptr; size_t d_jobs_count = 0;
     int* d_err = nullptr;
@@ -257,7 +258,7 @@ extern "C" void pmb_batch_free(pmb_ctx* c, pmb_batch* b)
     if (c) {
         cudaSetDevice(c->device);
         if (b->d_in) cudaFreeAsync(b->d_in, c->stream);
-        if (b->d_bits) cudaFreeAsync(b->d_bits, c->stream);
+        if (b->d_bits_raw) cudaFreeAsync(b->d_bits_raw, c->stream);
         if (b->d_counters) cudaFreeAsync(b->d_counters, c->stream);
         if (b->d_jobs) cudaFreeAsync(b->d_jobs, c->stream);
         if (b->d_err) cudaFreeAsync(b->d_err, c->stream);
@@ -345,8 +346,7 @@ static int plan_windows(pmb_ctx* c, pmb_batch* b)
 static int plan_events(pmb_ctx* c, pmb_batch* b)
 {
     const size_t n = b->jobs.size();
-    const uint32_t TW = c->event_tile_words > 0 ? (uint32_t)c->event_tile_words : 2048;
-    if (TW % 256) { c->err = "event_tile_words must be a multiple of 256"; return PMB_ERR_ARG; }
+    const uint32_t TW = EV_TILE;
     b->ev_tile_words = TW;
     b->aux_words = n * (2 * (size_t)b->stride + 2);
     CU_TRY(c, cudaMallocAsync((void**)&b->d_aux, b->aux_words * 8, c->stream));
@@ -488,7 +488,12 @@ extern "C" int pmb_batch_prepare(pmb_ctx* c, const pmb_chrom_args* a, uint32_t n
     b->counter_words = (size_t)n * PMB_NCOUNTERS * b->stride + (size_t)n * 2;
 
     CU_TRY(c, cudaMallocAsync((void**)&b->d_in, std::max<size_t>(in_words, 4) * 4, c->stream));
-    CU_TRY(c, cudaMallocAsync((void**)&b->d_bits, std::max<size_t>(bits_words, 4) * 4, c->stream));
+    CU_TRY(c, cudaMallocAsync((void**)&b->d_bits_raw,
+                              (std::max<size_t>(bits_words, 4) + 2 * (size_t)EV_PAD_WORDS) * 4, c->stream));
+    b->d_bits = b->d_bits_raw + EV_PAD_WORDS;
+    // the pads are only ever read by TMA region overhang (never used); zero them once
+    CU_TRY(c, cudaMemsetAsync(b->d_bits_raw, 0, (size_t)EV_PAD_WORDS * 4, c->stream));
+    CU_TRY(c, cudaMemsetAsync(b->d_bits + std::max<size_t>(bits_words, 4), 0, (size_t)EV_PAD_WORDS * 4, c->stream));
     CU_TRY(c, cudaMallocAsync((void**)&b->d_counters, b->counter_words * 8, c->stream));
     CU_TRY(c, cudaMallocAsync((void**)&b->d_err, 16, c->stream));
     uint64_t max_iv = 0;
@@ -644,24 +649,26 @@ static int execute_events(pmb_ctx* c, pmb_batch* b)
     const uint32_t bps = c->event_blocks_per_sm > 0 ? (uint32_t)c->event_blocks_per_sm : 8;
     const uint32_t grid = std::max(1u, std::min(b->ev_total_tiles, (uint32_t)c->num_sms * bps));
     uint32_t window_launches = 0;
-    auto chunks = [&](auto&& launch) {
-        for (uint32_t col0 = 0; col0 < n_cols_total; col0 += 32) {
-            P.col0 = col0;
-            P.n_cols = std::min(32u, n_cols_total - col0);
-            launch();
-            window_launches++;
-        }
-    };
-    if (b->any_ncc || b->any_mscc) chunks([&] {
-        if (b->any_ncc && b->any_mscc) event_window_kernel<EV_FWD, true, true><<<grid, 256, 0, st>>>(P);
-        else if (b->any_ncc) event_window_kernel<EV_FWD, true, false><<<grid, 256, 0, st>>>(P);
-        else event_window_kernel<EV_FWD, false, true><<<grid, 256, 0, st>>>(P);
-    });
+#define PMB_EV_LAUNCH(KIND, NCC, MSCC)                                                              \
+    do {                                                                                            \
+        auto k = event_window_kernel<KIND, NCC, MSCC>;                                              \
+        const size_t sm = event_smem_bytes<KIND>();                                                 \
+        CU_TRY(c, cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));   \
+        for (uint32_t col0 = 0; col0 < n_cols_total; col0 += 32) {                                  \
+            P.col0 = col0;                                                                          \
+            P.n_cols = std::min(32u, n_cols_total - col0);                                          \
+            k<<<grid, 32 * EV_WARPS, sm, st>>>(P);                                                  \
+            window_launches++;                                                                      \
+        }                                                                                           \
+    } while (0)
+    if (b->any_ncc && b->any_mscc) PMB_EV_LAUNCH(EV_FWD, true, true);
+    else if (b->any_ncc) PMB_EV_LAUNCH(EV_FWD, true, false);
+    else if (b->any_mscc) PMB_EV_LAUNCH(EV_FWD, false, true);
     CU_TRY(c, cudaEventRecord(c->evk[0], st));
-    if (b->any_mscc) chunks([&] { event_window_kernel<EV_REV, false, true><<<grid, 256, 0, st>>>(P); });
+    if (b->any_mscc) PMB_EV_LAUNCH(EV_REV, false, true);
     CU_TRY(c, cudaEventRecord(c->evk[1], st));
-    if (b->any_mscc || b->any_autocorr)
-        chunks([&] { event_window_kernel<EV_EDGE, false, true><<<grid, 256, 0, st>>>(P); });
+    if (b->any_mscc || b->any_autocorr) PMB_EV_LAUNCH(EV_EDGE, false, true);
+#undef PMB_EV_LAUNCH
     if (b->any_mscc || b->any_autocorr) {
         finalize_dmp_kernel<<<(unsigned)((n + 63) / 64), 64, 0, st>>>(b->d_evjobs, (uint32_t)n, b->stride,
                                                                      b->max_shift);

@@ -23,9 +23,9 @@
 // descending and the stride-2 descending windows become ascending ones); derive_kernel
 // writes them, Sb and Eb in one streaming pass over M.
 //
-// Mapping.  A warp scans 32 words of the event source at a time (coalesced), stages the
-// window spans of that group in shared memory (see "Span staging" below) and handles the
-// events one after the other: lane <-> window column (32 shifts), so one event is two
+// Mapping.  A CTA stages a tile of the event source and the window regions of that tile in
+// shared memory by TMA (see "Tile staging" below); a warp takes 32 source words at a time and
+// handles their events one after the other: lane <-> window column (32 shifts), so one event is two
 // conflict-free LDS + one funnel shift per lane and array.  The per-shift
 // counts are kept BIT-SLICED in registers: a carry-save binary counter (acc/pend word per
 // level, ~1 CSA = 2 LOP3 per event and counter, independent of the window's density); a
@@ -157,64 +157,77 @@ __device__ __forceinline__ uint32_t range_mask(long long bit0, long long lo, lon
     return mask;
 }
 
-// Span staging.  All events of one 32-word scan group (1024 bit positions from array bit G)
-// need windows that lie in a <= 68-word span of each array, whose start depends on G only:
+// Tile staging.  All events of one 32-word scan group (1024 bit positions from array bit G)
+// need windows that lie in a <= 66-word span of each array, whose start depends on G only:
 //   ascending arrays  (R, Sb, Eb):  window start = B + e,          B = G + c0
 //   reversed arrays   (Mr, Er, Or): window start = B + (emax - e), B = C - G - emax
-// with e the event's offset inside the group.  The warp loads each span ONCE per group
-// (coalesced, all loads in flight together: one memory latency per group instead of one per
-// event) into its private shared-memory slice; an event then costs two conflict-free LDS and
-// one funnel shift per array.
-constexpr int EV_SPAN = 68;            // words per staged span (>= 33 + 32 + 1, padded)
-constexpr int EV_WARPS = 8;            // warps per CTA
-constexpr int EV_SPANS = 3;            // spans per warp (REV: Mr, Er, Or)
+// with e the event's offset inside the group.  So a TILE of EV_TILE source words needs one
+// contiguous region of every array, and a CTA brings those regions in with 1-D TMA bulk copies
+// (cp.async.bulk.shared::cluster.global, completing on an mbarrier), double buffered: the
+// regions of the next tile are in flight while the warps walk the events of this one.  An
+// event then costs two conflict-free LDS and one funnel shift per lane and array, and global
+// latency is off the critical path.  Regions may overhang the job's array by a few words on
+// either side (the allocation is padded; such words are never used by a valid event).
+constexpr int EV_TILE = 1024;                 // source words per tile = 32 scan groups
+constexpr int EV_WARPS = 8;                   // warps per CTA
+constexpr int EV_REGION = EV_TILE + 40;       // words of a full-rate window region
+constexpr int EV_REGION_HALF = EV_TILE / 2 + 44;   // decimated arrays (Er, Or)
+constexpr int EV_PAD_WORDS = 2048;            // padding of the bit-array allocation, both ends
 
-__device__ __forceinline__ void stage_span(uint32_t* dst, const uint32_t* __restrict__ A, long long base_word,
-                                           long long n_words, int lane)
+template <int KIND>
+struct EvTraits;
+template <> struct EvTraits<EV_FWD> {     // counters ncc, mfwd, mscc; regions F, M | R, Mr
+    static constexpr int NC = 3;
+    static constexpr int STAGE_WORDS = 2 * EV_TILE + 2 * EV_REGION;
+};
+template <> struct EvTraits<EV_REV> {     // counter mrev; regions R | Mr, Er, Or
+    static constexpr int NC = 1;
+    static constexpr int STAGE_WORDS = EV_TILE + EV_REGION + 2 * EV_REGION_HALF;
+};
+template <> struct EvTraits<EV_EDGE> {    // + and - edge products; regions M (4 words early) | Sb, Eb
+    static constexpr int NC = 2;
+    static constexpr int STAGE_WORDS = (EV_TILE + 4) + 2 * EV_REGION;
+};
+
+template <int KIND>
+__host__ __device__ constexpr size_t event_smem_bytes()
 {
-#pragma unroll
-    for (int i = 0; i < 3; ++i) {
-        const int k = lane + 32 * i;
-        if (k < EV_SPAN) {
-            const long long w = base_word + k;
-            dst[k] = (w >= 0 && w < n_words) ? __ldg(A + w) : 0u;
-        }
-    }
+    return 16 + (size_t)EvTraits<KIND>::NC * 32 * EV_HIST_STRIDE * 4 + 2 * (size_t)EvTraits<KIND>::STAGE_WORDS * 4;
 }
 
-// window column `lane` (+ col0 already folded into the span base) at span bit offset o
+__device__ __forceinline__ long long floor4(long long w) { return w & ~3ll; }
+
+// window column `lane` at bit offset o of a staged span
 __device__ __forceinline__ uint32_t span_word(const uint32_t* sp, uint32_t o, int lane)
 {
     const uint32_t w = (o >> 5) + lane;
     return __funnelshift_r(sp[w], sp[w + 1], o & 31);
 }
 
-template <int KIND>
-struct EvTraits;
-template <> struct EvTraits<EV_FWD> { static constexpr int NC = 3; };    // ncc, mfwd, mscc
-template <> struct EvTraits<EV_REV> { static constexpr int NC = 1; };    // mrev
-template <> struct EvTraits<EV_EDGE> { static constexpr int NC = 2; };   // + and - edge products
-
 // KIND: which events; NCC / MSCC: which counters the batch asked for.
 template <int KIND, bool NCC, bool MSCC>
 __global__ void __launch_bounds__(32 * EV_WARPS) event_window_kernel(const EventParams P)
 {
     constexpr int NC = EvTraits<KIND>::NC;
-    __shared__ uint32_t hist[NC * 32 * EV_HIST_STRIDE];
-    __shared__ uint32_t spans[EV_WARPS][EV_SPANS][EV_SPAN];
+    constexpr int STAGE = EvTraits<KIND>::STAGE_WORDS;
+    extern __shared__ __align__(16) unsigned char ev_smem[];
+    uint64_t* full = reinterpret_cast<uint64_t*>(ev_smem);                  // [2]
+    uint32_t* hist = reinterpret_cast<uint32_t*>(ev_smem + 16);             // [NC][32][33]
+    uint32_t* stage0 = hist + NC * 32 * EV_HIST_STRIDE;                     // 16-byte aligned
 
     const int lane = threadIdx.x & 31;
     const int warp = threadIdx.x >> 5;
-    const int n_warps = blockDim.x >> 5;
-    uint32_t* sp0 = spans[warp][0];
-    uint32_t* sp1 = spans[warp][1];
-    uint32_t* sp2 = spans[warp][2];
 
     const uint32_t t_lo = (uint32_t)(((uint64_t)P.total_tiles * blockIdx.x) / gridDim.x);
     const uint32_t t_hi = (uint32_t)(((uint64_t)P.total_tiles * (blockIdx.x + 1)) / gridDim.x);
     if (t_lo >= t_hi) return;
 
     for (uint32_t i = threadIdx.x; i < NC * 32 * EV_HIST_STRIDE; i += blockDim.x) hist[i] = 0;
+    if (threadIdx.x == 0) {
+        mbar_init(&full[0], 1);
+        mbar_init(&full[1], 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
     __syncthreads();
 
     Slices<NC> sl;
@@ -223,9 +236,67 @@ __global__ void __launch_bounds__(32 * EV_WARPS) event_window_kernel(const Event
     const uint32_t col_mask = lane < (int)P.n_cols ? 0xFFFFFFFFu : 0u;   // idle lanes when n_cols < 32
     const int D = (int)P.max_shift;
     const int rl = (int)P.read_len;
+    const int hmax = (1022 + rl) >> 1;
 
-    uint32_t cur_job = 0;
-    while (cur_job + 1 < P.n_jobs && P.jobs[cur_job + 1].tile_begin <= t_lo) cur_job++;
+    auto job_active = [&](const EventJob& J) -> bool {
+        if (KIND != EV_EDGE && (J.flags & EVF_AUTOCORR)) return false;     // no reads in such a job
+        if (KIND == EV_REV && !(J.flags & EVF_MSCC)) return false;
+        if (KIND == EV_EDGE && !(J.flags & (EVF_MSCC | EVF_AUTOCORR))) return false;
+        return true;
+    };
+    // Region origins (array word index, multiple of 4) of tile word offset g0 of job J.
+    // a: first full-rate window region, b: decimated regions (REV only).
+    auto region_a = [&](const EventJob& J, uint32_t g0) -> long long {
+        const long long N = (long long)J.array_words * 32;
+        const long long G_last = ((long long)g0 + EV_TILE - 32) * 32;
+        if (KIND == EV_FWD) return floor4(((N - G_last - rl - 1023) >> 5) + P.col0);        // Mr
+        if (KIND == EV_REV) return floor4(((N - G_last - 1024) >> 5) + P.col0);             // Mr
+        return floor4((((long long)g0 * 32 + J.edge_off) >> 5) + P.col0);                  // Sb, Eb
+    };
+    auto region_b = [&](const EventJob& J, uint32_t g0) -> long long {
+        const long long N = (long long)J.array_words * 32;
+        const long long G_last = ((long long)g0 + EV_TILE - 32) * 32;
+        return floor4((((N >> 1) - 1 - (G_last >> 1) - hmax) >> 5) + P.col0);               // Er, Or
+    };
+
+    // producer (thread 0): request the regions of one tile into one stage
+    auto request = [&](uint32_t t, uint32_t job, int s) {
+        const EventJob& J = P.jobs[job];
+        const uint32_t g0 = (t - J.tile_begin) * EV_TILE;
+        uint32_t* st = stage0 + (size_t)s * STAGE;
+        fence_proxy_async();
+        if (KIND == EV_FWD) {
+            const bool mscc = MSCC && (J.flags & EVF_MSCC);
+            mbar_expect_tx(&full[s], (EV_TILE + EV_REGION + (mscc ? EV_TILE + EV_REGION : 0)) * 4);
+            tma_load_1d(st, J.F + g0, EV_TILE * 4, &full[s]);
+            tma_load_1d(st + 2 * EV_TILE, J.R + g0 + P.col0, EV_REGION * 4, &full[s]);
+            if (mscc) {
+                tma_load_1d(st + EV_TILE, J.M + g0, EV_TILE * 4, &full[s]);
+                tma_load_1d(st + 2 * EV_TILE + EV_REGION, J.Mr + region_a(J, g0), EV_REGION * 4, &full[s]);
+            }
+        } else if (KIND == EV_REV) {
+            mbar_expect_tx(&full[s], (EV_TILE + EV_REGION + 2 * EV_REGION_HALF) * 4);
+            tma_load_1d(st, J.R + g0, EV_TILE * 4, &full[s]);
+            tma_load_1d(st + EV_TILE, J.Mr + region_a(J, g0), EV_REGION * 4, &full[s]);
+            const long long rb = region_b(J, g0);
+            tma_load_1d(st + EV_TILE + EV_REGION, J.Er + rb, EV_REGION_HALF * 4, &full[s]);
+            tma_load_1d(st + EV_TILE + EV_REGION + EV_REGION_HALF, J.Or + rb, EV_REGION_HALF * 4, &full[s]);
+        } else {
+            mbar_expect_tx(&full[s], ((EV_TILE + 4) + 2 * EV_REGION) * 4);
+            tma_load_1d(st, J.M + (long long)g0 - 4, (EV_TILE + 4) * 4, &full[s]);
+            const long long ra = region_a(J, g0);
+            tma_load_1d(st + EV_TILE + 4, J.Sb + ra, EV_REGION * 4, &full[s]);
+            tma_load_1d(st + EV_TILE + 4 + EV_REGION, J.Eb + ra, EV_REGION * 4, &full[s]);
+        }
+    };
+    // next tile >= t of an active job (t_hi if none); `cursor` walks the job table
+    auto next_active = [&](uint32_t t, uint32_t& cursor) -> uint32_t {
+        for (; t < t_hi; ++t) {
+            while (cursor + 1 < P.n_jobs && P.jobs[cursor + 1].tile_begin <= t) cursor++;
+            if (job_active(P.jobs[cursor])) return t;
+        }
+        return t_hi;
+    };
 
     auto flush_block = [&](uint32_t job) {
         sl.flush(hist, lane);
@@ -260,83 +331,97 @@ __global__ void __launch_bounds__(32 * EV_WARPS) event_window_kernel(const Event
         __syncthreads();
     };
 
-    const uint32_t words_per_warp = P.tile_words / n_warps;
-    for (uint32_t t = t_lo; t < t_hi; ++t) {
-        uint32_t job = cur_job;
-        while (job + 1 < P.n_jobs && P.jobs[job + 1].tile_begin <= t) job++;
+    // prologue: the first two active tiles are requested up front
+    uint32_t prod_cursor = 0, cons_cursor = 0;
+    uint32_t t = next_active(t_lo, cons_cursor);
+    if (t >= t_hi) return;
+    uint32_t t_req = t_hi;                    // producer's next tile to request (thread 0)
+    if (threadIdx.x == 0) {
+        prod_cursor = cons_cursor;
+        request(t, prod_cursor, 0);
+        t_req = next_active(t + 1, prod_cursor);
+        if (t_req < t_hi) {
+            request(t_req, prod_cursor, 1);
+            t_req = next_active(t_req + 1, prod_cursor);
+        }
+    }
+    uint32_t cur_job = cons_cursor;
+    uint32_t it = 0;                          // active tiles consumed so far
+
+    for (; t < t_hi; t = next_active(t + 1, cons_cursor), ++it) {
+        const uint32_t job = cons_cursor;
         if (job != cur_job) {
             flush_block(cur_job);
             cur_job = job;
         }
         const EventJob& J = P.jobs[job];
-        if (KIND != EV_EDGE && (J.flags & EVF_AUTOCORR)) continue;      // no reads in such a job
-        if (KIND == EV_REV && !(J.flags & EVF_MSCC)) continue;
-        if (KIND == EV_EDGE && !(J.flags & (EVF_MSCC | EVF_AUTOCORR))) continue;
-        const long long W = J.array_words;
-        const long long N = W * 32;
+        const long long N = (long long)J.array_words * 32;
         const bool job_ncc = NCC && (J.flags & EVF_NCC);
         const bool job_mscc = MSCC && (J.flags & EVF_MSCC);
-        const uint32_t w_begin = (t - J.tile_begin) * P.tile_words + warp * words_per_warp;
+        const uint32_t g0 = (t - J.tile_begin) * EV_TILE;
+        const int s = it & 1;
+        const uint32_t* st = stage0 + (size_t)s * STAGE;
+        const long long ra = region_a(J, g0);
+        const long long rb = (KIND == EV_REV) ? region_b(J, g0) : 0;
+        mbar_wait(&full[s], (it >> 1) & 1);
 
-        for (uint32_t g = w_begin; g < w_begin + words_per_warp; g += 32) {
+        for (uint32_t gi = warp; gi < EV_TILE / 32; gi += EV_WARPS) {
+            const uint32_t g = g0 + 32 * gi;
             if (g >= J.array_words) break;
             const uint32_t i = g + lane;
+            const bool in = i < J.array_words;
             const long long G = (long long)g * 32;
             uint32_t ev = 0, ev2 = 0, mword = 0;     // ev: reads / run starts; ev2: run ends
-            if (i < J.array_words) {
-                if (KIND == EV_FWD) {
-                    ev = __ldg(J.F + i);
-                    if (job_mscc) mword = __ldg(J.M + i);
+            if (KIND == EV_FWD) {
+                if (in) {
+                    ev = st[32 * gi + lane];
+                    if (job_mscc) mword = st[EV_TILE + 32 * gi + lane];
                     if (P.col0 == 0) {
                         tot_f += __popc(ev);        // F is clipped to the counted range at build
-                        tot_r += __popc(__ldg(J.R + i) & range_mask((long long)i * 32, J.a_lo, J.a_hi));
+                        tot_r += __popc(st[2 * EV_TILE + 32 * gi + lane] & range_mask((long long)i * 32, J.a_lo, J.a_hi));
                     }
-                } else if (KIND == EV_REV) {
-                    ev = __ldg(J.R + i);
-                } else {
-                    const uint32_t m = __ldg(J.M + i) & range_mask((long long)i * 32, J.a_lo, J.a_hi);
-                    uint32_t prev = 0;
-                    if (i > 0) prev = (__ldg(J.M + i - 1) & range_mask((long long)(i - 1) * 32, J.a_lo, J.a_hi)) >> 31;
-                    const uint32_t up = (m << 1) | prev;     // Mc[a-1]
-                    ev = m & ~up;
-                    ev2 = ~m & up;
                 }
+            } else if (KIND == EV_REV) {
+                if (in) ev = st[32 * gi + lane];
+            } else if (in) {
+                const uint32_t m = st[4 + 32 * gi + lane] & range_mask((long long)i * 32, J.a_lo, J.a_hi);
+                uint32_t prev = 0;
+                if (i > 0) prev = (st[3 + 32 * gi + lane] & range_mask((long long)(i - 1) * 32, J.a_lo, J.a_hi)) >> 31;
+                const uint32_t up = (m << 1) | prev;     // Mc[a-1]
+                ev = m & ~up;
+                ev2 = ~m & up;
             }
             uint32_t nz = __ballot_sync(0xFFFFFFFFu, (ev | ev2) != 0);
             if (!nz) continue;
 
-            // ---- stage this group's spans (warp-private shared memory)
-            uint32_t r0 = 0, r1 = 0;            // bit offsets of the span origins
+            // ---- this group's spans inside the staged regions
+            const uint32_t *sp0, *sp1, *sp2 = nullptr;
+            uint32_t r0, r1 = 0;                // bit offsets of the span origins
             long long gl = 0, gh = 0;           // REV: k-range of the shard, relative to the group
-            bool full = true;
-            __syncwarp();
+            bool full_rng = true;
             if constexpr (KIND == EV_FWD) {
-                stage_span(sp0, J.R, (long long)g + P.col0, W, lane);
-                if (job_mscc) {
-                    const long long B = N - G - rl - 1023;
-                    r0 = (uint32_t)(B & 31);
-                    stage_span(sp1, J.Mr, (B >> 5) + P.col0, W, lane);
-                }
+                sp0 = st + 2 * EV_TILE + 32 * gi;                                   // R: start = G + e
+                const long long B = N - G - rl - 1023;
+                r0 = (uint32_t)(B & 31);
+                sp1 = st + 2 * EV_TILE + EV_REGION + (uint32_t)((B >> 5) + P.col0 - ra);   // Mr
             } else if constexpr (KIND == EV_REV) {
                 gl = G - J.a_lo;                // kmax = min(D, gl + e)
                 gh = G - J.a_hi + 1;            // kmin = max(0, gh + e)
                 if (gl + 1023 < 0 || gh > D) continue;          // no event of the group counts
-                full = (gh + 1023 <= 0) && (gl >= D);
+                full_rng = (gh + 1023 <= 0) && (gl >= D);
                 const long long B = N - G - 1024;
                 r0 = (uint32_t)(B & 31);
-                stage_span(sp0, J.Mr, (B >> 5) + P.col0, W, lane);
-                const int hmax = (1022 + rl) >> 1;
+                sp0 = st + EV_TILE + (uint32_t)((B >> 5) + P.col0 - ra);            // Mr
                 const long long B4 = (N >> 1) - 1 - (G >> 1) - hmax;
                 r1 = (uint32_t)(B4 & 31);
-                stage_span(sp1, J.Er, (B4 >> 5) + P.col0, W >> 1, lane);
-                stage_span(sp2, J.Or, (B4 >> 5) + P.col0, W >> 1, lane);
+                sp1 = st + EV_TILE + EV_REGION + (uint32_t)((B4 >> 5) + P.col0 - rb);   // Er
+                sp2 = sp1 + EV_REGION_HALF;                                         // Or
             } else {
                 const long long B = G + J.edge_off;
                 r0 = (uint32_t)(B & 31);
-                stage_span(sp0, J.Sb, (B >> 5) + P.col0, W, lane);
-                stage_span(sp1, J.Eb, (B >> 5) + P.col0, W, lane);
+                sp0 = st + EV_TILE + 4 + (uint32_t)((B >> 5) + P.col0 - ra);        // Sb
+                sp1 = sp0 + EV_REGION;                                              // Eb
             }
-            __syncwarp();
 
             while (nz) {
                 const int src = __ffs(nz) - 1;
@@ -363,7 +448,7 @@ __global__ void __launch_bounds__(32 * EV_WARPS) event_window_kernel(const Event
                         sl.add(x, hist, lane);
                     } else if constexpr (KIND == EV_REV) {
                         uint32_t kmask = col_mask;
-                        if (!full) {      // shifts k with j = q - k inside the counted range
+                        if (!full_rng) {  // shifts k with j = q - k inside the counted range
                             long long kmin = gh + eo, kmax = gl + eo;
                             if (kmin < 0) kmin = 0;
                             if (kmax > D) kmax = D;
@@ -372,10 +457,9 @@ __global__ void __launch_bounds__(32 * EV_WARPS) event_window_kernel(const Event
                         }
                         const uint32_t tl = eo + (uint32_t)rl - 1u;              // (q + rl - 1) - G
                         const uint32_t* dec = (tl & 1u) ? sp2 : sp1;
-                        const uint32_t hmax = (uint32_t)((1022 + rl) >> 1);
                         uint32_t x[1];
                         const uint32_t w3 = span_word(sp0, r0 + 1023u - eo, lane);
-                        const uint32_t w4 = span_word(dec, r1 + hmax - (tl >> 1), lane);
+                        const uint32_t w4 = span_word(dec, r1 + (uint32_t)hmax - (tl >> 1), lane);
                         x[0] = w3 & w4 & kmask;
                         sl.add(x, hist, lane);
                     } else {
@@ -388,6 +472,11 @@ __global__ void __launch_bounds__(32 * EV_WARPS) event_window_kernel(const Event
                     }
                 }
             }
+        }
+        __syncthreads();   // every warp is done with stage s
+        if (threadIdx.x == 0 && t_req < t_hi) {
+            request(t_req, prod_cursor, s);
+            t_req = next_active(t_req + 1, prod_cursor);
         }
     }
     flush_block(cur_job);
