@@ -11,7 +11,7 @@ import numpy as np
 from .exceptions import DeviceError, PositionOutOfRange
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libpymasc_b200.so")
+LIB_PATH = os.environ.get("PYMASC_B200_LIB") or os.path.join(_HERE, "libpymasc_b200.so")   # override: tuning builds
 
 PMB_OK, PMB_ERR_CUDA, PMB_ERR_RANGE, PMB_ERR_ARG, PMB_ERR_NOMEM = 0, -1, -2, -3, -4
 FLAG_NCC, FLAG_MSCC, FLAG_AUTOCORR = 1, 2, 4

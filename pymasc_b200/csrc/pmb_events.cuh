@@ -76,6 +76,9 @@ struct EventParams {
     uint32_t stride;
 };
 
+#ifndef EV_SWITCH_ADD
+#define EV_SWITCH_ADD 1
+#endif
 constexpr int EV_LEVELS = 6;          // carry-save levels: a top-level carry every 64 events
 constexpr int EV_HIST_STRIDE = 33;    // padded: lane l, bit b -> bank (l + b) % 32
 
@@ -102,36 +105,56 @@ struct Slices {
             atomicAdd(hist + lane * EV_HIST_STRIDE + b, weight);
         }
     }
-    // add one window word per counter
-    __device__ __forceinline__ void add(const uint32_t (&x)[NC], uint32_t* hist, int lane)
+    // Event number m with TZ trailing zero bits: levels 0..TZ-1 each fold (acc, pend, carry)
+    // with one CSA, level TZ parks the carry (or, past the top level, it goes to the histogram).
+    template <int TZ>
+    __device__ __forceinline__ void add_case(const uint32_t (&x)[NC], uint32_t* hist, int lane)
     {
-        ++m;
-        uint32_t mm = m;
         uint32_t c[NC];
 #pragma unroll
         for (int n = 0; n < NC; ++n) c[n] = x[n];
-        bool go = true;
 #pragma unroll
-        for (int i = 0; i < EV_LEVELS; ++i) {
-            if (go) {
-                if (mm & 1u) {
+        for (int i = 0; i < TZ; ++i) {
 #pragma unroll
-                    for (int n = 0; n < NC; ++n) pend[n][i] = c[n];
-                    go = false;
-                } else {
-#pragma unroll
-                    for (int n = 0; n < NC; ++n) {
-                        const uint32_t t = maj3(acc[n][i], pend[n][i], c[n]);
-                        acc[n][i] = xor3(acc[n][i], pend[n][i], c[n]);
-                        c[n] = t;
-                    }
-                    mm >>= 1;
-                }
+            for (int n = 0; n < NC; ++n) {
+                const uint32_t t = maj3(acc[n][i], pend[n][i], c[n]);
+                acc[n][i] = xor3(acc[n][i], pend[n][i], c[n]);
+                c[n] = t;
             }
         }
-        if (go) {
+        if (TZ < EV_LEVELS) {
+#pragma unroll
+            for (int n = 0; n < NC; ++n) pend[n][TZ < EV_LEVELS ? TZ : 0] = c[n];
+        } else {
 #pragma unroll
             for (int n = 0; n < NC; ++n) sink(hist + n * 32 * EV_HIST_STRIDE, lane, c[n], 1u << EV_LEVELS);
+        }
+    }
+    // add one window word per counter; m is warp-uniform, so the switch is a uniform branch
+    // (a predicated cascade over all levels costs ~6x the instructions)
+    __device__ __forceinline__ void add(const uint32_t (&x)[NC], uint32_t* hist, int lane)
+    {
+        ++m;
+        static_assert(EV_LEVELS == 6, "switch below lists the cases of 6 levels");
+        const int tz = __ffs(m | (1u << EV_LEVELS)) - 1;
+#if EV_SWITCH_ADD == 2
+        if (tz == 0) add_case<0>(x, hist, lane);
+        else if (tz == 1) add_case<1>(x, hist, lane);
+        else if (tz == 2) add_case<2>(x, hist, lane);
+        else if (tz == 3) add_case<3>(x, hist, lane);
+        else if (tz == 4) add_case<4>(x, hist, lane);
+        else if (tz == 5) add_case<5>(x, hist, lane);
+        else add_case<6>(x, hist, lane);
+        return;
+#endif
+        switch (tz) {
+            case 0: add_case<0>(x, hist, lane); break;
+            case 1: add_case<1>(x, hist, lane); break;
+            case 2: add_case<2>(x, hist, lane); break;
+            case 3: add_case<3>(x, hist, lane); break;
+            case 4: add_case<4>(x, hist, lane); break;
+            case 5: add_case<5>(x, hist, lane); break;
+            default: add_case<6>(x, hist, lane); break;
         }
     }
     __device__ __forceinline__ void flush(uint32_t* hist, int lane)
@@ -168,7 +191,7 @@ __device__ __forceinline__ uint32_t range_mask(long long bit0, long long lo, lon
 // event then costs two conflict-free LDS and one funnel shift per lane and array, and global
 // latency is off the critical path.  Regions may overhang the job's array by a few words on
 // either side (the allocation is padded; such words are never used by a valid event).
-constexpr int EV_TILE = 1024;                 // source words per tile = 32 scan groups
+constexpr int EV_TILE = 128;                  // source words per (warp-private) tile = 4 scan groups
 constexpr int EV_WARPS = 8;                   // warps per CTA
 constexpr int EV_REGION = EV_TILE + 40;       // words of a full-rate window region
 constexpr int EV_REGION_HALF = EV_TILE / 2 + 44;   // decimated arrays (Er, Or)
@@ -192,7 +215,8 @@ template <> struct EvTraits<EV_EDGE> {    // + and - edge products; regions M (4
 template <int KIND>
 __host__ __device__ constexpr size_t event_smem_bytes()
 {
-    return 16 + (size_t)EvTraits<KIND>::NC * 32 * EV_HIST_STRIDE * 4 + 2 * (size_t)EvTraits<KIND>::STAGE_WORDS * 4;
+    return 16 * EV_WARPS + (size_t)EvTraits<KIND>::NC * 32 * EV_HIST_STRIDE * 4 +
+           2 * (size_t)EV_WARPS * EvTraits<KIND>::STAGE_WORDS * 4;
 }
 
 __device__ __forceinline__ long long floor4(long long w) { return w & ~3ll; }
@@ -211,9 +235,9 @@ __global__ void __launch_bounds__(32 * EV_WARPS) event_window_kernel(const Event
     constexpr int NC = EvTraits<KIND>::NC;
     constexpr int STAGE = EvTraits<KIND>::STAGE_WORDS;
     extern __shared__ __align__(16) unsigned char ev_smem[];
-    uint64_t* full = reinterpret_cast<uint64_t*>(ev_smem);                  // [2]
-    uint32_t* hist = reinterpret_cast<uint32_t*>(ev_smem + 16);             // [NC][32][33]
-    uint32_t* stage0 = hist + NC * 32 * EV_HIST_STRIDE;                     // 16-byte aligned
+    uint64_t* full_all = reinterpret_cast<uint64_t*>(ev_smem);              // [EV_WARPS][2]
+    uint32_t* hist = reinterpret_cast<uint32_t*>(ev_smem + 16 * EV_WARPS);  // [NC][32][33]
+    uint32_t* stage_all = hist + NC * 32 * EV_HIST_STRIDE;                  // [EV_WARPS][2][STAGE]
 
     const int lane = threadIdx.x & 31;
     const int warp = threadIdx.x >> 5;
@@ -223,7 +247,11 @@ __global__ void __launch_bounds__(32 * EV_WARPS) event_window_kernel(const Event
     if (t_lo >= t_hi) return;
 
     for (uint32_t i = threadIdx.x; i < NC * 32 * EV_HIST_STRIDE; i += blockDim.x) hist[i] = 0;
-    if (threadIdx.x == 0) {
+    // every warp runs its own two-stage TMA pipeline (no CTA barrier per tile: events per tile
+    // vary, and a shared barrier left warps idle 3-5 issue slots per instruction)
+    uint64_t* full = full_all + 2 * warp;
+    uint32_t* stage0 = stage_all + (size_t)2 * warp * STAGE;
+    if (lane == 0) {
         mbar_init(&full[0], 1);
         mbar_init(&full[1], 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
@@ -289,15 +317,6 @@ __global__ void __launch_bounds__(32 * EV_WARPS) event_window_kernel(const Event
             tma_load_1d(st + EV_TILE + 4 + EV_REGION, J.Eb + ra, EV_REGION * 4, &full[s]);
         }
     };
-    // next tile >= t of an active job (t_hi if none); `cursor` walks the job table
-    auto next_active = [&](uint32_t t, uint32_t& cursor) -> uint32_t {
-        for (; t < t_hi; ++t) {
-            while (cursor + 1 < P.n_jobs && P.jobs[cursor + 1].tile_begin <= t) cursor++;
-            if (job_active(P.jobs[cursor])) return t;
-        }
-        return t_hi;
-    };
-
     auto flush_block = [&](uint32_t job) {
         sl.flush(hist, lane);
         __syncthreads();
@@ -331,41 +350,32 @@ __global__ void __launch_bounds__(32 * EV_WARPS) event_window_kernel(const Event
         __syncthreads();
     };
 
-    // prologue: the first two active tiles are requested up front
-    uint32_t prod_cursor = 0, cons_cursor = 0;
-    uint32_t t = next_active(t_lo, cons_cursor);
-    if (t >= t_hi) return;
-    uint32_t t_req = t_hi;                    // producer's next tile to request (thread 0)
-    if (threadIdx.x == 0) {
-        prod_cursor = cons_cursor;
-        request(t, prod_cursor, 0);
-        t_req = next_active(t + 1, prod_cursor);
-        if (t_req < t_hi) {
-            request(t_req, prod_cursor, 1);
-            t_req = next_active(t_req + 1, prod_cursor);
-        }
-    }
-    uint32_t cur_job = cons_cursor;
-    uint32_t it = 0;                          // active tiles consumed so far
-
-    for (; t < t_hi; t = next_active(t + 1, cons_cursor), ++it) {
-        const uint32_t job = cons_cursor;
-        if (job != cur_job) {
-            flush_block(cur_job);
-            cur_job = job;
-        }
+    // The CTA's tile range is cut into job segments; inside a segment warp w owns the tiles
+    // seg_lo + w, + EV_WARPS, ... (neighbouring warps read neighbouring memory) and the warps
+    // only meet at the segment end, where the counters of the job are flushed.
+    uint32_t itw = 0;                         // tiles this warp has consumed (stage = itw & 1)
+    uint32_t job = 0;
+    while (job + 1 < P.n_jobs && P.jobs[job + 1].tile_begin <= t_lo) job++;
+    for (uint32_t seg_lo = t_lo; seg_lo < t_hi; ++job) {
         const EventJob& J = P.jobs[job];
+        const uint32_t seg_hi = min(t_hi, J.tile_begin + J.n_tiles);
+        if (!job_active(J)) { seg_lo = seg_hi; continue; }
         const long long N = (long long)J.array_words * 32;
         const bool job_ncc = NCC && (J.flags & EVF_NCC);
         const bool job_mscc = MSCC && (J.flags & EVF_MSCC);
+        if (lane == 0) {
+            if (seg_lo + warp < seg_hi) request(seg_lo + warp, job, itw & 1);
+            if (seg_lo + warp + EV_WARPS < seg_hi) request(seg_lo + warp + EV_WARPS, job, (itw + 1) & 1);
+        }
+      for (uint32_t t = seg_lo + warp; t < seg_hi; t += EV_WARPS, ++itw) {
         const uint32_t g0 = (t - J.tile_begin) * EV_TILE;
-        const int s = it & 1;
+        const int s = itw & 1;
         const uint32_t* st = stage0 + (size_t)s * STAGE;
         const long long ra = region_a(J, g0);
         const long long rb = (KIND == EV_REV) ? region_b(J, g0) : 0;
-        mbar_wait(&full[s], (it >> 1) & 1);
+        mbar_wait(&full[s], (itw >> 1) & 1);
 
-        for (uint32_t gi = warp; gi < EV_TILE / 32; gi += EV_WARPS) {
+        for (uint32_t gi = 0; gi < EV_TILE / 32; ++gi) {
             const uint32_t g = g0 + 32 * gi;
             if (g >= J.array_words) break;
             const uint32_t i = g + lane;
@@ -473,13 +483,12 @@ __global__ void __launch_bounds__(32 * EV_WARPS) event_window_kernel(const Event
                 }
             }
         }
-        __syncthreads();   // every warp is done with stage s
-        if (threadIdx.x == 0 && t_req < t_hi) {
-            request(t_req, prod_cursor, s);
-            t_req = next_active(t_req + 1, prod_cursor);
-        }
+        __syncwarp();      // every lane is done with stage s
+        if (lane == 0 && t + 2 * EV_WARPS < seg_hi) request(t + 2 * EV_WARPS, job, s);
+      }
+        flush_block(job);
+        seg_lo = seg_hi;
     }
-    flush_block(cur_job);
 }
 
 // ---------------------------------------------------------------- derive
