@@ -670,8 +670,7 @@ static int execute_events(pmb_ctx* c, pmb_batch* b)
     if (b->any_mscc || b->any_autocorr) PMB_EV_LAUNCH(EV_EDGE, false, true);
 #undef PMB_EV_LAUNCH
     if (b->any_mscc || b->any_autocorr) {
-        finalize_dmp_kernel<<<(unsigned)((n + 63) / 64), 64, 0, st>>>(b->d_evjobs, (uint32_t)n, b->stride,
-                                                                     b->max_shift);
+        finalize_dmp_kernel<<<(unsigned)n, 256, 0, st>>>(b->d_evjobs, (uint32_t)n, b->stride, b->max_shift);
         window_launches++;
     }
     CU_TRY(c, cudaGetLastError());

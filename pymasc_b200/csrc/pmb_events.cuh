@@ -588,30 +588,49 @@ __global__ void derive_kernel(const uint32_t* __restrict__ M, uint32_t* __restri
 // dmp from the two direct lags and the edge products C[b] = aux[0][b] - aux[1][b]:
 //   MSCC      dmp[0] = A[rl-1], dmp[1] = A[rl-2], dmp[k+1] = 2 dmp[k] - dmp[k-1] - C[D-k]
 //   AUTOCORR  out[0] = A[0],    out[1] = A[1],    out[s+1] = 2 out[s] - out[s-1] - C[s]
-// One thread per job (the chain is (max_shift+1) long and serial; it is tiny).
-__global__ void finalize_dmp_kernel(const EventJob* __restrict__ jobs, uint32_t n_jobs, uint32_t stride,
-                                    uint32_t max_shift)
+// The recurrence is a double prefix sum (first differences d[k+1] = d[k] - C[.], then
+// dmp[k] = dmp[k-1] + d[k]): one CTA per job runs two in-place block scans over the output vector.
+__device__ __forceinline__ void block_scan_inplace(long long* a, uint32_t n, long long* part)
 {
-    const uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
-    if (j >= n_jobs) return;
-    const EventJob& J = jobs[j];
-    if (!(J.flags & (EVF_MSCC | EVF_AUTOCORR))) return;
+    const uint32_t chunk = (n + blockDim.x - 1) / blockDim.x;
+    const uint32_t lo = min(n, threadIdx.x * chunk), hi = min(n, lo + chunk);
+    long long sum = 0;
+    for (uint32_t i = lo; i < hi; ++i) sum += a[i];
+    part[threadIdx.x] = sum;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        long long run = 0;
+        for (uint32_t t = 0; t < blockDim.x; ++t) { const long long v = part[t]; part[t] = run; run += v; }
+    }
+    __syncthreads();
+    long long run = part[threadIdx.x];
+    for (uint32_t i = lo; i < hi; ++i) { run += a[i]; a[i] = run; }
+    __syncthreads();
+}
+
+__global__ void __launch_bounds__(256) finalize_dmp_kernel(const EventJob* __restrict__ jobs, uint32_t n_jobs,
+                                                           uint32_t stride, uint32_t max_shift)
+{
+    __shared__ long long part[256];
+    const EventJob& J = jobs[blockIdx.x];
+    if (!(J.flags & (EVF_MSCC | EVF_AUTOCORR))) return;       // uniform per CTA
     const bool autocorr = (J.flags & EVF_AUTOCORR) != 0;
     long long* out = (long long*)(J.counters + (size_t)C_DMP * stride);
     const long long* plus = (const long long*)J.aux;
     const long long* minus = plus + stride;
-    long long prev = (long long)J.adirect[0];
-    out[0] = prev;
-    if (max_shift == 0) return;
-    long long cur = (long long)J.adirect[1];
-    out[1] = cur;
-    for (uint32_t k = 1; k < max_shift; ++k) {
-        const uint32_t b = autocorr ? k : max_shift - k;
-        const long long nxt = 2 * cur - prev - (plus[b] - minus[b]);
-        out[k + 1] = nxt;
-        prev = cur;
-        cur = nxt;
+    const long long a0 = (long long)J.adirect[0], a1 = (long long)J.adirect[1];
+    if (max_shift == 0) { if (threadIdx.x == 0) out[0] = a0; return; }
+    // out[0] = A0, out[1] = d[1] = A1 - A0, out[k+1] = -C[b(k)] for k = 1 .. max_shift-1
+    for (uint32_t k = threadIdx.x; k <= max_shift; k += blockDim.x) {
+        long long v;
+        if (k == 0) v = a0;
+        else if (k == 1) v = a1 - a0;
+        else { const uint32_t b = autocorr ? k - 1 : max_shift - (k - 1); v = -(plus[b] - minus[b]); }
+        out[k] = v;
     }
+    __syncthreads();
+    block_scan_inplace(out + 1, max_shift, part);        // first differences d[1..max_shift]
+    block_scan_inplace(out, max_shift + 1, part);        // dmp[0..max_shift]
 }
 
 }  // namespace pmb
