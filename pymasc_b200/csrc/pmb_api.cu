@@ -238,11 +238,11 @@ enum { A_F = 0, A_R = 1, A_M = 2, A_MP = 3, A_FM = 4 };
 static bool whole_range(const JobPlan& j) { return j.lo == 0 && j.hi == (int64_t)j.nbits; }
 
 // event-window path: array slots, in units of array_words (Er and Or are half arrays)
-enum { E_F = 0, E_R = 1, E_M = 2, E_MR = 3, E_SB = 4, E_EB = 5, E_ER = 6 };
+enum { E_F = 0, E_R = 1, E_M = 2, E_ER = 3 };
 static size_t event_words_of(const JobPlan& j)
 {
-    if (j.autocorr) return 3 * j.array_words;                       // M, Sb, Eb (slots 0..2)
-    return ((j.mode & MODE_MSCC) ? 7 : 2) * j.array_words;          // F, R [, M, Mr, Sb, Eb, Er|Or]
+    if (j.autocorr) return j.array_words;                           // M (slot 0)
+    return ((j.mode & MODE_MSCC) ? 4 : 2) * j.array_words;          // F, R [, M, Er|Or]
 }
 
 static int arrays_of(const JobPlan& j)
@@ -360,14 +360,14 @@ static int plan_events(pmb_ctx* c, pmb_batch* b)
         auto arr = [&](int slot) { return base + (size_t)slot * j.array_words; };
         EventJob e{};
         if (j.autocorr) {
-            e.M = arr(0); e.Sb = arr(1); e.Eb = arr(2);
+            e.M = arr(0);
             e.flags = EVF_AUTOCORR;
             e.edge_off = 0;
         } else {
             e.F = arr(E_F); e.R = arr(E_R);
             e.flags = (j.mode & MODE_NCC ? EVF_NCC : 0) | (j.mode & MODE_MSCC ? EVF_MSCC : 0);
             if (j.mode & MODE_MSCC) {
-                e.M = arr(E_M); e.Mr = arr(E_MR); e.Sb = arr(E_SB); e.Eb = arr(E_EB);
+                e.M = arr(E_M);
                 e.Er = arr(E_ER); e.Or = arr(E_ER) + j.array_words / 2;
             }
             e.edge_off = (int32_t)b->read_len - 1 - (int32_t)b->max_shift;
@@ -574,7 +574,7 @@ static int execute_events(pmb_ctx* c, pmb_batch* b)
 
     CU_TRY(c, cudaEventRecord(c->ev[0], st));
     // only the scattered / filled arrays need zeroing (slots F, R, M come first in a job);
-    // Mr, Er, Or, Sb, Eb are written in full by derive_kernel
+    // Er and Or are written in full by derive_kernel
     for (const JobPlan& j : b->jobs) {
         const size_t zero_arrays = j.autocorr ? 1 : ((j.mode & MODE_MSCC) ? 3 : 2);
         CU_TRY(c, cudaMemsetAsync(b->d_bits + j.bits, 0, zero_arrays * j.array_words * 4, st));
@@ -626,9 +626,7 @@ static int execute_events(pmb_ctx* c, pmb_batch* b)
             const long long lag0 = j.autocorr ? 0 : (long long)b->read_len - 1;
             const long long lag1 = j.autocorr ? 1 : (long long)b->read_len - 2;
             derive_kernel<<<blocks_for(j.array_words / 4, 256), 256, 0, st>>>(
-                M, j.autocorr ? nullptr : arr(E_MR), j.autocorr ? nullptr : arr(E_ER),
-                j.autocorr ? nullptr : arr(E_ER) + j.array_words / 2,
-                j.autocorr ? arr(1) : arr(E_SB), j.autocorr ? arr(2) : arr(E_EB),
+                M, j.autocorr ? nullptr : arr(E_ER), j.autocorr ? nullptr : arr(E_ER) + j.array_words / 2,
                 (uint32_t)j.array_words, j.lo + off, j.hi + off, lag0, lag1, b->max_shift ? 2 : 1,
                 adirect0 + 2 * i);
             launches++;

@@ -9,19 +9,20 @@
 // bit array (bit b of the window <-> shift k = b):
 //
 //   forward read at p:   ncc  += R[p .. p+D]                                   (:314)
-//     and, if M[p]:      mfwd += M[p+rl-1-k], k = 0..D   = Mr[N-p-rl .. +D]    (:303)
+//     and, if M[p]:      mfwd += M[p+rl-1-k], k = 0..D   (descending window)   (:303)
 //                        mscc += R[p+k] & M[p+rl-1-k]                          (:305)
 //   reverse read at q:   mrev += M[q-k] & M[q+rl-1-2k]   (j = q-k in range)    (:304)
-//                             =  Mr[N-1-q .. +D] & {Er|Or}[N/2-1-((q+rl-1)>>1) .. +D]
+//                             =  M[q-k] & {Er|Or}[N/2-1-((q+rl-1)>>1) .. +D]
 //   mappable-run edges:  popc(D_k) = A[rl-1-k],  A[s] = sum_j Mc[j] M[j+s]     (:291-298)
 //                        2A[s] - A[s-1] - A[s+1] = sum_j dMc[j] dM[j+s]  (dX = starts - ends),
-//                        so every run edge of the (range-clipped) M adds the windows of the
-//                        start/end edge arrays Sb/Eb; two directly counted lags anchor the
-//                        recurrence (finalize_dmp_kernel).  Exact integer arithmetic.
+//                        so every run edge of the (range-clipped) M adds the window of run
+//                        starts / ends of M (formed on the fly from two funnel shifts of M);
+//                        two directly counted lags anchor the recurrence (finalize_dmp_kernel).
+//                        Exact integer arithmetic.
 //
-// Mr is M bit-reversed, Er/Or are the even/odd bits of M bit-reversed (so that the
-// descending and the stride-2 descending windows become ascending ones); derive_kernel
-// writes them, Sb and Eb in one streaming pass over M.
+// Descending windows are read from M itself (per-lane descending words + brev).  Er/Or are the
+// even/odd bits of M bit-reversed (the stride-2 descending window becomes an ascending one);
+// derive_kernel writes them in one streaming pass over M.
 //
 // Mapping.  A CTA stages a tile of the event source and the window regions of that tile in
 // shared memory by TMA (see "Tile staging" below); a warp takes 32 source words at a time and
@@ -47,11 +48,8 @@ struct EventJob {
     const uint32_t* F;    // array word 0 of each array (halo included)
     const uint32_t* R;
     const uint32_t* M;
-    const uint32_t* Mr;
-    const uint32_t* Er;
+    const uint32_t* Er;   // even / odd bits of M, bit-reversed (half arrays)
     const uint32_t* Or;
-    const uint32_t* Sb;
-    const uint32_t* Eb;
     unsigned long long* counters;   // [5][stride]
     unsigned long long* aux;        // [2][stride]: edge products, + then - (window-bit indexed)
     unsigned long long* adirect;    // [2]: the two directly counted lags
@@ -199,17 +197,17 @@ constexpr int EV_PAD_WORDS = 2048;            // padding of the bit-array alloca
 
 template <int KIND>
 struct EvTraits;
-template <> struct EvTraits<EV_FWD> {     // counters ncc, mfwd, mscc; regions F, M | R, Mr
+template <> struct EvTraits<EV_FWD> {     // counters ncc, mfwd, mscc; tiles F, M | regions R, M
     static constexpr int NC = 3;
     static constexpr int STAGE_WORDS = 2 * EV_TILE + 2 * EV_REGION;
 };
-template <> struct EvTraits<EV_REV> {     // counter mrev; regions R | Mr, Er, Or
+template <> struct EvTraits<EV_REV> {     // counter mrev; tile R | regions M, Er, Or
     static constexpr int NC = 1;
     static constexpr int STAGE_WORDS = EV_TILE + EV_REGION + 2 * EV_REGION_HALF;
 };
-template <> struct EvTraits<EV_EDGE> {    // + and - edge products; regions M (4 words early) | Sb, Eb
+template <> struct EvTraits<EV_EDGE> {    // + and - edge products; tile M (4 words early) | region M
     static constexpr int NC = 2;
-    static constexpr int STAGE_WORDS = (EV_TILE + 4) + 2 * EV_REGION;
+    static constexpr int STAGE_WORDS = (EV_TILE + 4) + EV_REGION;
 };
 
 template <int KIND>
@@ -226,6 +224,14 @@ __device__ __forceinline__ uint32_t span_word(const uint32_t* sp, uint32_t o, in
 {
     const uint32_t w = (o >> 5) + lane;
     return __funnelshift_r(sp[w], sp[w + 1], o & 31);
+}
+
+// Descending window: bit k of the result is A[top - k] for lane 0's top = o + 31, lane l 32 l lower.
+// (window column `lane` of the bit-reversed array, read from the array itself: no reversed copy)
+__device__ __forceinline__ uint32_t span_word_rev(const uint32_t* sp, uint32_t o, int lane)
+{
+    const uint32_t w = (o >> 5) - lane;
+    return __brev(__funnelshift_r(sp[w], sp[w + 1], o & 31));
 }
 
 // KIND: which events; NCC / MSCC: which counters the batch asked for.
@@ -275,11 +281,11 @@ __global__ void __launch_bounds__(32 * EV_WARPS) event_window_kernel(const Event
     // Region origins (array word index, multiple of 4) of tile word offset g0 of job J.
     // a: first full-rate window region, b: decimated regions (REV only).
     auto region_a = [&](const EventJob& J, uint32_t g0) -> long long {
-        const long long N = (long long)J.array_words * 32;
-        const long long G_last = ((long long)g0 + EV_TILE - 32) * 32;
-        if (KIND == EV_FWD) return floor4(((N - G_last - rl - 1023) >> 5) + P.col0);        // Mr
-        if (KIND == EV_REV) return floor4(((N - G_last - 1024) >> 5) + P.col0);             // Mr
-        return floor4((((long long)g0 * 32 + J.edge_off) >> 5) + P.col0);                  // Sb, Eb
+        // the M region of the tile: lowest word any lane touches for any event of the tile
+        const long long G0 = (long long)g0 * 32;
+        if (KIND == EV_FWD) return floor4(((G0 + rl - 32) >> 5) - P.col0 - 31);   // M[p+rl-1-k], descending
+        if (KIND == EV_REV) return floor4(((G0 - 31) >> 5) - P.col0 - 31);        // M[q-k], descending
+        return floor4(((G0 + J.edge_off - 1) >> 5) + P.col0);                     // dM[j+s], ascending
     };
     auto region_b = [&](const EventJob& J, uint32_t g0) -> long long {
         const long long N = (long long)J.array_words * 32;
@@ -300,21 +306,19 @@ __global__ void __launch_bounds__(32 * EV_WARPS) event_window_kernel(const Event
             tma_load_1d(st + 2 * EV_TILE, J.R + g0 + P.col0, EV_REGION * 4, &full[s]);
             if (mscc) {
                 tma_load_1d(st + EV_TILE, J.M + g0, EV_TILE * 4, &full[s]);
-                tma_load_1d(st + 2 * EV_TILE + EV_REGION, J.Mr + region_a(J, g0), EV_REGION * 4, &full[s]);
+                tma_load_1d(st + 2 * EV_TILE + EV_REGION, J.M + region_a(J, g0), EV_REGION * 4, &full[s]);
             }
         } else if (KIND == EV_REV) {
             mbar_expect_tx(&full[s], (EV_TILE + EV_REGION + 2 * EV_REGION_HALF) * 4);
             tma_load_1d(st, J.R + g0, EV_TILE * 4, &full[s]);
-            tma_load_1d(st + EV_TILE, J.Mr + region_a(J, g0), EV_REGION * 4, &full[s]);
+            tma_load_1d(st + EV_TILE, J.M + region_a(J, g0), EV_REGION * 4, &full[s]);
             const long long rb = region_b(J, g0);
             tma_load_1d(st + EV_TILE + EV_REGION, J.Er + rb, EV_REGION_HALF * 4, &full[s]);
             tma_load_1d(st + EV_TILE + EV_REGION + EV_REGION_HALF, J.Or + rb, EV_REGION_HALF * 4, &full[s]);
         } else {
-            mbar_expect_tx(&full[s], ((EV_TILE + 4) + 2 * EV_REGION) * 4);
+            mbar_expect_tx(&full[s], ((EV_TILE + 4) + EV_REGION) * 4);
             tma_load_1d(st, J.M + (long long)g0 - 4, (EV_TILE + 4) * 4, &full[s]);
-            const long long ra = region_a(J, g0);
-            tma_load_1d(st + EV_TILE + 4, J.Sb + ra, EV_REGION * 4, &full[s]);
-            tma_load_1d(st + EV_TILE + 4 + EV_REGION, J.Eb + ra, EV_REGION * 4, &full[s]);
+            tma_load_1d(st + EV_TILE + 4, J.M + region_a(J, g0), EV_REGION * 4, &full[s]);
         }
     };
     auto flush_block = [&](uint32_t job) {
@@ -411,26 +415,24 @@ __global__ void __launch_bounds__(32 * EV_WARPS) event_window_kernel(const Event
             bool full_rng = true;
             if constexpr (KIND == EV_FWD) {
                 sp0 = st + 2 * EV_TILE + 32 * gi;                                   // R: start = G + e
-                const long long B = N - G - rl - 1023;
-                r0 = (uint32_t)(B & 31);
-                sp1 = st + 2 * EV_TILE + EV_REGION + (uint32_t)((B >> 5) + P.col0 - ra);   // Mr
+                sp1 = st + 2 * EV_TILE + EV_REGION;                                 // M region
+                // lane 0's lowest bit of M[p+rl-1-k], k = 32 col0 .. +31, for the group's e = 0
+                r0 = (uint32_t)(G + rl - 32 - 32ll * P.col0 - 32 * ra);
             } else if constexpr (KIND == EV_REV) {
                 gl = G - J.a_lo;                // kmax = min(D, gl + e)
                 gh = G - J.a_hi + 1;            // kmin = max(0, gh + e)
                 if (gl + 1023 < 0 || gh > D) continue;          // no event of the group counts
                 full_rng = (gh + 1023 <= 0) && (gl >= D);
-                const long long B = N - G - 1024;
-                r0 = (uint32_t)(B & 31);
-                sp0 = st + EV_TILE + (uint32_t)((B >> 5) + P.col0 - ra);            // Mr
+                sp0 = st + EV_TILE;                                                 // M region
+                r0 = (uint32_t)(G - 31 - 32ll * P.col0 - 32 * ra);                  // M[q-k], as above
                 const long long B4 = (N >> 1) - 1 - (G >> 1) - hmax;
                 r1 = (uint32_t)(B4 & 31);
                 sp1 = st + EV_TILE + EV_REGION + (uint32_t)((B4 >> 5) + P.col0 - rb);   // Er
                 sp2 = sp1 + EV_REGION_HALF;                                         // Or
             } else {
-                const long long B = G + J.edge_off;
-                r0 = (uint32_t)(B & 31);
-                sp0 = st + EV_TILE + 4 + (uint32_t)((B >> 5) + P.col0 - ra);        // Sb
-                sp1 = sp0 + EV_REGION;                                              // Eb
+                sp0 = st + EV_TILE + 4;                                             // M region
+                sp1 = sp0;
+                r0 = (uint32_t)(G + J.edge_off + 32ll * P.col0 - 32 * ra);          // window start, e = 0
             }
 
             while (nz) {
@@ -451,7 +453,7 @@ __global__ void __launch_bounds__(32 * EV_WARPS) event_window_kernel(const Event
                         const uint32_t w1 = span_word(sp0, eo, lane) & col_mask;
                         if (job_ncc) x[0] = w1;
                         if (job_mscc && ((msrc >> bit) & 1u)) {          // M[p], warp-uniform
-                            const uint32_t w2 = span_word(sp1, r0 + 1023u - eo, lane) & col_mask;
+                            const uint32_t w2 = span_word_rev(sp1, r0 + eo, lane) & col_mask;
                             x[1] = w2;
                             x[2] = w1 & w2;
                         }
@@ -468,13 +470,16 @@ __global__ void __launch_bounds__(32 * EV_WARPS) event_window_kernel(const Event
                         const uint32_t tl = eo + (uint32_t)rl - 1u;              // (q + rl - 1) - G
                         const uint32_t* dec = (tl & 1u) ? sp2 : sp1;
                         uint32_t x[1];
-                        const uint32_t w3 = span_word(sp0, r0 + 1023u - eo, lane);
+                        const uint32_t w3 = span_word_rev(sp0, r0 + eo, lane);
                         const uint32_t w4 = span_word(dec, r1 + (uint32_t)hmax - (tl >> 1), lane);
                         x[0] = w3 & w4 & kmask;
                         sl.add(x, hist, lane);
                     } else {
-                        const uint32_t ws = span_word(sp0, r0 + eo, lane) & col_mask;
-                        const uint32_t we = span_word(sp1, r0 + eo, lane) & col_mask;
+                        // run starts / ends of M inside the window: dM = M[a] - M[a-1]
+                        const uint32_t m1 = span_word(sp0, r0 + eo, lane);
+                        const uint32_t m0 = span_word(sp0, r0 + eo - 1u, lane);
+                        const uint32_t ws = m1 & ~m0 & col_mask;
+                        const uint32_t we = ~m1 & m0 & col_mask;
                         uint32_t x[2];
                         x[0] = is_end ? we : ws;     // start.start + end.end
                         x[1] = is_end ? ws : we;     // start.end + end.start
@@ -493,9 +498,8 @@ __global__ void __launch_bounds__(32 * EV_WARPS) event_window_kernel(const Event
 
 // ---------------------------------------------------------------- derive
 // One streaming pass over the (unclipped) M window of a job:
-//   Mr[w]  = brev(M[W-1-w])                    reversed
-//   Er/Or  = even / odd bits of M, reversed    (W/2 words each)
-//   Sb/Eb  = run starts M[a] & ~M[a-1] / run ends ~M[a] & M[a-1]
+//   Er/Or  = even / odd bits of M, bit-reversed (W/2 words each): the stride-2 descending window
+//            M[q+rl-1-2k] of a reverse read becomes an ascending window of one of them
 //   adirect[0..1] += sum_j Mc[j] M[j + lag0/lag1]   (Mc = M clipped to [a_lo, a_hi))
 __device__ __forceinline__ uint32_t compress_even(uint64_t x)
 {
@@ -514,9 +518,8 @@ __device__ __forceinline__ uint32_t load_or_zero(const uint32_t* __restrict__ M,
 }
 
 // One thread per 4 words (16-byte loads / stores; array_words is a multiple of 4).
-__global__ void derive_kernel(const uint32_t* __restrict__ M, uint32_t* __restrict__ Mr,
+__global__ void derive_kernel(const uint32_t* __restrict__ M,
                               uint32_t* __restrict__ Er, uint32_t* __restrict__ Or,
-                              uint32_t* __restrict__ Sb, uint32_t* __restrict__ Eb,
                               uint32_t array_words, long long a_lo, long long a_hi,
                               long long lag0, long long lag1, int n_lags,
                               unsigned long long* __restrict__ adirect)
@@ -531,20 +534,7 @@ __global__ void derive_kernel(const uint32_t* __restrict__ M, uint32_t* __restri
         const uint32_t i = 4 * v;
         const uint4 m4 = *reinterpret_cast<const uint4*>(M + i);
         const uint32_t m[4] = {m4.x, m4.y, m4.z, m4.w};
-        uint32_t carry = i ? (__ldg(M + i - 1) >> 31) : 0u;
-        uint32_t sb[4], eb[4];
-#pragma unroll
-        for (int t = 0; t < 4; ++t) {
-            const uint32_t up = (m[t] << 1) | carry;      // M[a-1]
-            sb[t] = m[t] & ~up;
-            eb[t] = ~m[t] & up;
-            carry = m[t] >> 31;
-        }
-        *reinterpret_cast<uint4*>(Sb + i) = make_uint4(sb[0], sb[1], sb[2], sb[3]);
-        *reinterpret_cast<uint4*>(Eb + i) = make_uint4(eb[0], eb[1], eb[2], eb[3]);
-        if (Mr) {
-            *reinterpret_cast<uint4*>(Mr + (array_words - 4 - i)) =
-                make_uint4(__brev(m[3]), __brev(m[2]), __brev(m[1]), __brev(m[0]));
+        if (Er) {
             const uint64_t x0 = ((uint64_t)m[1] << 32) | m[0], x1 = ((uint64_t)m[3] << 32) | m[2];
             const uint32_t at = pairs - 2 - (i >> 1);
             *reinterpret_cast<uint2*>(Er + at) = make_uint2(__brev(compress_even(x1)), __brev(compress_even(x0)));
