@@ -367,6 +367,8 @@ def gpu_arm(args):
         pairs = t["window_word_shift_pairs"]
         win_launches = t["window_launches"]
         used_path = t["path"]
+        if world > 1:
+            dist.all_reduce(ctr)        # the last execute above left this rank's partial counts
         resident = batch.fetch()
         batch.free()
 

@@ -66,6 +66,7 @@ struct JobPlan {
     // offsets (in uint32 words) into the batch's device buffers
     size_t in_fwd = 0, in_rev = 0, in_mb = 0, in_me = 0;
     size_t bits = 0;           // start of this job's arrays; each array_words long
+    size_t bits_d = 0;         // event path: start of the derived Er|Or array (after all F/R/M)
     size_t array_words = 0;    // 2H + Wpad
 };
 
@@ -95,6 +96,12 @@ struct pmb_batch {
     EventJob* d_evjobs = nullptr;
     uint32_t ev_total_tiles = 0, ev_tile_words = 0;
     bool any_ncc = false, any_mscc = false, any_autocorr = false;
+    size_t zero_words = 0;              // event path: [0, zero_words) of d_bits = all jobs' F, R, M
+    void* d_tasks = nullptr;            // batched build: task tables + prefix sums (one allocation)
+    ScatterTask* d_scatter = nullptr; uint64_t* d_scatter_prefix = nullptr; uint32_t n_scatter = 0; uint64_t scatter_items = 0;
+    FillTask* d_fill = nullptr; uint64_t* d_fill_prefix = nullptr; uint32_t n_fill = 0; uint64_t fill_items = 0;
+    DeriveTask* d_derive = nullptr; uint64_t* d_derive_prefix = nullptr; uint32_t n_derive = 0; uint64_t derive_ctas = 0;
+    unsigned long long* d_long64 = nullptr;   // long-interval queue of fill_multi_kernel
 };
 
 // ------------------------------------------------------------------ context
@@ -239,12 +246,6 @@ static bool whole_range(const JobPlan& j) { return j.lo == 0 && j.hi == (int64_t
 
 // event-window path: array slots, in units of array_words (Er and Or are half arrays)
 enum { E_F = 0, E_R = 1, E_M = 2, E_ER = 3 };
-static size_t event_words_of(const JobPlan& j)
-{
-    if (j.autocorr) return j.array_words;                           // M (slot 0)
-    return ((j.mode & MODE_MSCC) ? 4 : 2) * j.array_words;          // F, R [, M, Er|Or]
-}
-
 static int arrays_of(const JobPlan& j)
 {
     // autocorrelation: M (whole window, the "R" role) [+ M clipped to the shard, the "F" role]
@@ -265,6 +266,8 @@ extern "C" void pmb_batch_free(pmb_ctx* c, pmb_batch* b)
         if (b->d_long) cudaFreeAsync(b->d_long, c->stream);
         if (b->d_aux) cudaFreeAsync(b->d_aux, c->stream);
         if (b->d_evjobs) cudaFreeAsync(b->d_evjobs, c->stream);
+        if (b->d_tasks) cudaFreeAsync(b->d_tasks, c->stream);
+        if (b->d_long64) cudaFreeAsync(b->d_long64, c->stream);
         cudaStreamSynchronize(c->stream);
     }
     delete b;
@@ -368,7 +371,7 @@ static int plan_events(pmb_ctx* c, pmb_batch* b)
             e.flags = (j.mode & MODE_NCC ? EVF_NCC : 0) | (j.mode & MODE_MSCC ? EVF_MSCC : 0);
             if (j.mode & MODE_MSCC) {
                 e.M = arr(E_M);
-                e.Er = arr(E_ER); e.Or = arr(E_ER) + j.array_words / 2;
+                e.Er = b->d_bits + j.bits_d; e.Or = e.Er + j.array_words / 2;
             }
             e.edge_off = (int32_t)b->read_len - 1 - (int32_t)b->max_shift;
         }
@@ -386,6 +389,70 @@ static int plan_events(pmb_ctx* c, pmb_batch* b)
         table[i] = e;
     }
     b->ev_total_tiles = tiles;
+
+    // batched build: one scatter / fill / derive launch for the whole batch
+    {
+        const int64_t NEG = -(1ll << 40), POS = (1ll << 40);
+        std::vector<ScatterTask> sc; std::vector<uint64_t> scp{0};
+        std::vector<FillTask> fl; std::vector<uint64_t> flp{0};
+        std::vector<DeriveTask> dv; std::vector<uint64_t> dvp{0};
+        unsigned long long* adir0 = b->d_aux + n * 2 * (size_t)b->stride;
+        for (size_t i = 0; i < n; i++) {
+            JobPlan& j = b->jobs[i];
+            Geometry g;
+            g.origin_bit = j.origin_word * 32;
+            g.halo_bits = (int64_t)b->halo_words * 32;
+            g.total_bits = (int64_t)j.array_words * 32;
+            uint32_t* base = b->d_bits + j.bits;
+            auto arr = [&](int slot) { return base + (size_t)slot * j.array_words; };
+            const bool mscc = !j.autocorr && (j.mode & MODE_MSCC);
+            if (!j.autocorr) {
+                if (j.a.n_fwd) { sc.push_back({arr(E_F), g, b->d_in + j.in_fwd, j.lo, j.hi, j.nbits}); scp.push_back(scp.back() + j.a.n_fwd); }
+                if (j.a.n_rev) { sc.push_back({arr(E_R), g, b->d_in + j.in_rev, NEG, POS, j.nbits}); scp.push_back(scp.back() + j.a.n_rev); }
+            }
+            uint32_t* M = j.autocorr ? arr(0) : (mscc ? arr(E_M) : nullptr);
+            if (!M) continue;
+            if (j.a.n_intervals) {
+                fl.push_back({M, g, b->d_in + j.in_mb, b->d_in + j.in_me, 0, NEG, POS, j.nbits});
+                flp.push_back(flp.back() + j.a.n_intervals);
+            }
+            DeriveTask d{};
+            d.M = M;
+            d.Er = mscc ? b->d_bits + j.bits_d : nullptr;
+            d.Or = mscc ? d.Er + j.array_words / 2 : nullptr;
+            d.adirect = adir0 + 2 * i;
+            const int64_t off = g.halo_bits - g.origin_bit;
+            d.a_lo = j.lo + off; d.a_hi = j.hi + off;
+            d.lag0 = j.autocorr ? 0 : (long long)b->read_len - 1;
+            d.lag1 = j.autocorr ? 1 : (long long)b->read_len - 2;
+            d.array_words = (uint32_t)j.array_words;
+            dv.push_back(d);
+            dvp.push_back(dvp.back() + (j.array_words / 4 + DERIVE_QUADS_PER_CTA - 1) / DERIVE_QUADS_PER_CTA);
+        }
+        b->n_scatter = (uint32_t)sc.size(); b->scatter_items = scp.back();
+        b->n_fill = (uint32_t)fl.size(); b->fill_items = flp.back();
+        b->n_derive = (uint32_t)dv.size(); b->derive_ctas = dvp.back();
+        auto bytes8 = [](size_t x) { return (x + 15) & ~(size_t)15; };
+        const size_t o_sc = 0, o_scp = o_sc + bytes8(sc.size() * sizeof(ScatterTask));
+        const size_t o_fl = o_scp + bytes8(scp.size() * 8), o_flp = o_fl + bytes8(fl.size() * sizeof(FillTask));
+        const size_t o_dv = o_flp + bytes8(flp.size() * 8), o_dvp = o_dv + bytes8(dv.size() * sizeof(DeriveTask));
+        const size_t total = o_dvp + bytes8(dvp.size() * 8);
+        std::vector<unsigned char> blob(total, 0);
+        if (!sc.empty()) memcpy(blob.data() + o_sc, sc.data(), sc.size() * sizeof(ScatterTask));
+        memcpy(blob.data() + o_scp, scp.data(), scp.size() * 8);
+        if (!fl.empty()) memcpy(blob.data() + o_fl, fl.data(), fl.size() * sizeof(FillTask));
+        memcpy(blob.data() + o_flp, flp.data(), flp.size() * 8);
+        if (!dv.empty()) memcpy(blob.data() + o_dv, dv.data(), dv.size() * sizeof(DeriveTask));
+        memcpy(blob.data() + o_dvp, dvp.data(), dvp.size() * 8);
+        CU_TRY(c, cudaMallocAsync(&b->d_tasks, total, c->stream));
+        CU_TRY(c, cudaMemcpyAsync(b->d_tasks, blob.data(), total, cudaMemcpyHostToDevice, c->stream));
+        unsigned char* d = (unsigned char*)b->d_tasks;
+        b->d_scatter = (ScatterTask*)(d + o_sc); b->d_scatter_prefix = (uint64_t*)(d + o_scp);
+        b->d_fill = (FillTask*)(d + o_fl); b->d_fill_prefix = (uint64_t*)(d + o_flp);
+        b->d_derive = (DeriveTask*)(d + o_dv); b->d_derive_prefix = (uint64_t*)(d + o_dvp);
+        CU_TRY(c, cudaMallocAsync((void**)&b->d_long64, (b->fill_items + 1) * 8, c->stream));
+        CU_TRY(c, cudaStreamSynchronize(c->stream));   // `blob` is a local
+    }
     CU_TRY(c, cudaMemcpyAsync(b->d_evjobs, table.data(), n * sizeof(EventJob), cudaMemcpyHostToDevice,
                               c->stream));
     CU_TRY(c, cudaStreamSynchronize(c->stream));   // `table` is a local
@@ -478,12 +545,22 @@ extern "C" int pmb_batch_prepare(pmb_ctx* c, const pmb_chrom_args* a, uint32_t n
         j.body_words = (uint64_t)j.n_tiles * T;
         j.array_words = 2 * (size_t)b->halo_words + j.body_words;
         j.bits = bits_words;
-        bits_words += b->path == 2 ? event_words_of(j) : (size_t)arrays_of(j) * j.array_words;
+        if (b->path == 2) {     // F, R, M of all jobs first (one memset), the derived arrays after them
+            const size_t z = j.autocorr ? 1 : ((j.mode & MODE_MSCC) ? 3 : 2);
+            bits_words += z * j.array_words;
+        } else {
+            bits_words += (size_t)arrays_of(j) * j.array_words;
+        }
         auto take = [&](uint64_t cnt) { size_t o = in_words; in_words += (cnt + 3) & ~3ull; return o; };
         if (!j.autocorr) { j.in_fwd = take(j.a.n_fwd); j.in_rev = take(j.a.n_rev); }
         if ((j.mode & MODE_MSCC) || j.autocorr) { j.in_mb = take(j.a.n_intervals); j.in_me = take(j.a.n_intervals); }
     }
     b->in_words = in_words;
+    if (b->path == 2) {
+        b->zero_words = bits_words;
+        for (auto& j : b->jobs)
+            if (!j.autocorr && (j.mode & MODE_MSCC)) { j.bits_d = bits_words; bits_words += j.array_words; }
+    }
     b->bits_words = bits_words;
     b->counter_words = (size_t)n * PMB_NCOUNTERS * b->stride + (size_t)n * 2;
 
@@ -573,64 +650,33 @@ static int execute_events(pmb_ctx* c, pmb_batch* b)
     const size_t n = b->jobs.size();
 
     CU_TRY(c, cudaEventRecord(c->ev[0], st));
-    // only the scattered / filled arrays need zeroing (slots F, R, M come first in a job);
-    // Er and Or are written in full by derive_kernel
-    for (const JobPlan& j : b->jobs) {
-        const size_t zero_arrays = j.autocorr ? 1 : ((j.mode & MODE_MSCC) ? 3 : 2);
-        CU_TRY(c, cudaMemsetAsync(b->d_bits + j.bits, 0, zero_arrays * j.array_words * 4, st));
-    }
+    // only the scattered / filled arrays need zeroing (F, R, M of all jobs come first);
+    // Er and Or are written in full by derive_multi_kernel
+    CU_TRY(c, cudaMemsetAsync(b->d_bits, 0, std::max<size_t>(b->zero_words, 4) * 4, st));
     CU_TRY(c, cudaMemsetAsync(b->d_counters, 0, b->counter_words * 8, st));
     CU_TRY(c, cudaMemsetAsync(b->d_aux, 0, b->aux_words * 8, st));
     CU_TRY(c, cudaMemsetAsync(b->d_err, 0, 16, st));
-    unsigned long long* adirect0 = b->d_aux + n * 2 * (size_t)b->stride;
 
     auto blocks_for = [&](uint64_t items, int per_block) {
         uint64_t g = (items + per_block - 1) / per_block;
         return (unsigned)std::min<uint64_t>(std::max<uint64_t>(g, 1), (uint64_t)c->num_sms * 16);
     };
-    for (size_t i = 0; i < n; i++) {
-        JobPlan& j = b->jobs[i];
-        Geometry g;
-        g.origin_bit = j.origin_word * 32;
-        g.halo_bits = (int64_t)H * 32;
-        g.total_bits = (int64_t)j.array_words * 32;
-        uint32_t* base = b->d_bits + j.bits;
-        auto arr = [&](int slot) { return base + (size_t)slot * j.array_words; };
-        const int64_t off = g.halo_bits - g.origin_bit;
-        const bool mscc = !j.autocorr && (j.mode & MODE_MSCC);
-        uint32_t* M = j.autocorr ? arr(0) : (mscc ? arr(E_M) : nullptr);
-
-        if (!j.autocorr) {
-            if (j.a.n_fwd) {
-                scatter_bits_kernel<<<blocks_for(j.a.n_fwd, 256), 256, 0, st>>>(
-                    arr(E_F), g, b->d_in + j.in_fwd, j.a.n_fwd, j.lo, j.hi, j.nbits, b->d_err);
-                launches++;
-            }
-            if (j.a.n_rev) {
-                scatter_bits_kernel<<<blocks_for(j.a.n_rev, 256), 256, 0, st>>>(
-                    arr(E_R), g, b->d_in + j.in_rev, j.a.n_rev, NEG, POS, j.nbits, b->d_err);
-                launches++;
-            }
-        }   // strand totals: counted by the forward-read event kernel while it scans F and R
-        if (M) {
-            if (j.a.n_intervals) {
-                CU_TRY(c, cudaMemsetAsync(b->d_long, 0, 4, st));
-                fill_intervals_kernel<<<blocks_for(j.a.n_intervals, 8), 256, 0, st>>>(
-                    M, g, b->d_in + j.in_mb, b->d_in + j.in_me, j.a.n_intervals, 0, NEG, POS, j.nbits,
-                    b->d_err, b->d_long + 1, b->d_long);
-                fill_long_kernel<<<c->num_sms * 4, 256, 0, st>>>(M, g, b->d_in + j.in_mb,
-                                                                 b->d_in + j.in_me, 0, NEG, POS,
-                                                                 b->d_long + 1, b->d_long);
-                launches += 2;
-            }
-            const long long lag0 = j.autocorr ? 0 : (long long)b->read_len - 1;
-            const long long lag1 = j.autocorr ? 1 : (long long)b->read_len - 2;
-            derive_kernel<<<blocks_for(j.array_words / 4, 256), 256, 0, st>>>(
-                M, j.autocorr ? nullptr : arr(E_ER), j.autocorr ? nullptr : arr(E_ER) + j.array_words / 2,
-                (uint32_t)j.array_words, j.lo + off, j.hi + off, lag0, lag1, b->max_shift ? 2 : 1,
-                adirect0 + 2 * i);
-            launches++;
-        }
+    if (b->scatter_items) {     // strand totals are counted by the forward-read event kernel
+        scatter_multi_kernel<<<blocks_for(b->scatter_items, 256), 256, 0, st>>>(
+            b->d_scatter, b->d_scatter_prefix, b->n_scatter, b->d_err);
+        launches++;
+    }
+    if (b->fill_items) {
+        CU_TRY(c, cudaMemsetAsync(b->d_long, 0, 4, st));
+        fill_multi_kernel<<<blocks_for(b->fill_items, 8), 256, 0, st>>>(
+            b->d_fill, b->d_fill_prefix, b->n_fill, b->d_err, b->d_long64, b->d_long);
+        fill_long_multi_kernel<<<c->num_sms * 4, 256, 0, st>>>(b->d_fill, b->d_long64, b->d_long);
+        launches += 2;
+    }
+    if (b->derive_ctas) {
+        derive_multi_kernel<<<(unsigned)b->derive_ctas, 256, 0, st>>>(b->d_derive, b->d_derive_prefix,
+                                                                     b->n_derive, b->max_shift ? 2 : 1);
+        launches++;
     }
     CU_TRY(c, cudaGetLastError());
     CU_TRY(c, cudaEventRecord(c->ev[1], st));

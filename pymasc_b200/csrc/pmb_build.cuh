@@ -166,3 +166,111 @@ __global__ void prep_kernel(const uint32_t* __restrict__ F, const uint32_t* __re
 }
 
 }  // namespace pmb
+
+// ---------------------------------------------------------------- batched build (all jobs, one launch)
+// With 24+ chromosomes per batch the per-job launches above are launch-bound (a job's scatter
+// is a few microseconds of work).  The *_multi kernels take a task table and a prefix-sum of
+// the task sizes; a thread (warp) finds its task by binary search and then does exactly what
+// the per-job kernel does.
+namespace pmb {
+
+struct ScatterTask {
+    uint32_t* arr;
+    Geometry g;
+    const uint32_t* pos;
+    int64_t clip_lo, clip_hi;
+    uint64_t nbits;
+};
+
+struct FillTask {
+    uint32_t* arr;
+    Geometry g;
+    const uint32_t* begins;
+    const uint32_t* ends;
+    int64_t shift_down, clip_lo, clip_hi;
+    uint64_t nbits;
+};
+
+// index of the task whose [prefix[t], prefix[t+1]) holds item i (prefix has n_tasks + 1 entries)
+__device__ __forceinline__ uint32_t find_task(const uint64_t* __restrict__ prefix, uint32_t n_tasks, uint64_t i)
+{
+    uint32_t lo = 0, hi = n_tasks;           // invariant: prefix[lo] <= i < prefix[hi]
+    while (hi - lo > 1) {
+        const uint32_t mid = (lo + hi) >> 1;
+        if (prefix[mid] <= i) lo = mid; else hi = mid;
+    }
+    return lo;
+}
+
+__global__ void scatter_multi_kernel(const ScatterTask* __restrict__ tasks, const uint64_t* __restrict__ prefix,
+                                     uint32_t n_tasks, int* __restrict__ err_flag)
+{
+    const uint64_t total = prefix[n_tasks];
+    uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+    for (; i < total; i += stride) {
+        const uint32_t t = find_task(prefix, n_tasks, i);
+        const ScatterTask& T = tasks[t];
+        const int64_t p = T.pos[i - prefix[t]];
+        if ((uint64_t)p >= T.nbits) { atomicExch(err_flag, 1); continue; }
+        if (p < T.clip_lo || p >= T.clip_hi) continue;
+        const int64_t a = to_array_bit(T.g, p);
+        if (a < 0) continue;
+        atomicOr(T.arr + (a >> 5), 1u << (a & 31));
+    }
+}
+
+// long_list entries: (task << 32) | interval index
+__global__ void fill_multi_kernel(const FillTask* __restrict__ tasks, const uint64_t* __restrict__ prefix,
+                                  uint32_t n_tasks, int* __restrict__ err_flag,
+                                  unsigned long long* __restrict__ long_list, uint32_t* __restrict__ long_count)
+{
+    const int lane = threadIdx.x & 31;
+    const uint64_t total = prefix[n_tasks];
+    uint64_t warp = ((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const uint64_t nwarps = ((uint64_t)gridDim.x * blockDim.x) >> 5;
+    for (uint64_t i = warp; i < total; i += nwarps) {
+        const uint32_t t = find_task(prefix, n_tasks, i);
+        const FillTask& T = tasks[t];
+        const uint64_t k = i - prefix[t];
+        const uint32_t b = T.begins[k], e = T.ends[k];
+        if (e <= b) continue;                       // zero-length region
+        if ((uint64_t)e >= T.nbits) { if (lane == 0) atomicExch(err_flag, 1); continue; }
+        int64_t a0, a1;
+        if (!interval_span(T.g, b, e, T.shift_down, T.clip_lo, T.clip_hi, a0, a1)) continue;
+        const int64_t fw = a0 >> 5, lw = a1 >> 5;
+        const uint32_t fmask = 0xFFFFFFFFu << (a0 & 31);
+        const uint32_t lmask = 0xFFFFFFFFu >> (31 - (a1 & 31));
+        if (fw == lw) {
+            if (lane == 0) atomicOr(T.arr + fw, fmask & lmask);
+            continue;
+        }
+        if (lane == 0) atomicOr(T.arr + fw, fmask);
+        if (lane == 1) atomicOr(T.arr + lw, lmask);
+        if (lw - fw - 1 > LONG_WORDS) {
+            if (lane == 0) long_list[atomicAdd(long_count, 1u)] = ((unsigned long long)t << 32) | (uint32_t)k;
+            continue;
+        }
+        for (int64_t w = fw + 1 + lane; w < lw; w += 32) T.arr[w] = 0xFFFFFFFFu;
+    }
+}
+
+__global__ void fill_long_multi_kernel(const FillTask* __restrict__ tasks,
+                                       const unsigned long long* __restrict__ long_list,
+                                       const uint32_t* __restrict__ long_count)
+{
+    const uint32_t n = *long_count;
+    const uint64_t tid = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const uint64_t nth = (uint64_t)gridDim.x * blockDim.x;
+    for (uint32_t q = 0; q < n; q++) {
+        const unsigned long long ent = long_list[q];
+        const FillTask& T = tasks[(uint32_t)(ent >> 32)];
+        const uint32_t k = (uint32_t)ent;
+        int64_t a0, a1;
+        if (!interval_span(T.g, T.begins[k], T.ends[k], T.shift_down, T.clip_lo, T.clip_hi, a0, a1)) continue;
+        const int64_t fw = a0 >> 5, lw = a1 >> 5;
+        for (int64_t w = fw + 1 + (int64_t)tid; w < lw; w += (int64_t)nth) T.arr[w] = 0xFFFFFFFFu;
+    }
+}
+
+}  // namespace pmb

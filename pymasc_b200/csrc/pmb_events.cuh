@@ -517,20 +517,45 @@ __device__ __forceinline__ uint32_t load_or_zero(const uint32_t* __restrict__ M,
     return (w >= 0 && w < W) ? __ldg(M + w) : 0u;
 }
 
-// One thread per 4 words (16-byte loads / stores; array_words is a multiple of 4).
-__global__ void derive_kernel(const uint32_t* __restrict__ M,
-                              uint32_t* __restrict__ Er, uint32_t* __restrict__ Or,
-                              uint32_t array_words, long long a_lo, long long a_hi,
-                              long long lag0, long long lag1, int n_lags,
-                              unsigned long long* __restrict__ adirect)
+// One thread per 4 words (16-byte loads / stores; array_words is a multiple of 4); all jobs of
+// the batch in ONE launch: a CTA owns DERIVE_QUADS_PER_CTA quads of one task (block -> task by
+// binary search over the prefix sum of the tasks' CTA counts).
+struct DeriveTask {
+    const uint32_t* M;
+    uint32_t* Er;
+    uint32_t* Or;
+    unsigned long long* adirect;
+    long long a_lo, a_hi;
+    long long lag0, lag1;
+    uint32_t array_words;
+    uint32_t reserved;
+};
+constexpr uint32_t DERIVE_QUADS_PER_CTA = 2048;
+
+__global__ void __launch_bounds__(256) derive_multi_kernel(const DeriveTask* __restrict__ tasks,
+                                                           const uint64_t* __restrict__ cta_prefix,
+                                                           uint32_t n_tasks, int n_lags)
 {
+    uint32_t lo_t = 0, hi_t = n_tasks;          // cta_prefix[lo_t] <= blockIdx.x < cta_prefix[hi_t]
+    while (hi_t - lo_t > 1) {
+        const uint32_t mid = (lo_t + hi_t) >> 1;
+        if (cta_prefix[mid] <= blockIdx.x) lo_t = mid; else hi_t = mid;
+    }
+    const DeriveTask& T = tasks[lo_t];
+    const uint32_t* __restrict__ M = T.M;
+    uint32_t* __restrict__ Er = T.Er;
+    uint32_t* __restrict__ Or = T.Or;
+    const uint32_t array_words = T.array_words;
+    const long long a_lo = T.a_lo, a_hi = T.a_hi;
     const uint32_t quads = array_words >> 2;
     const uint32_t pairs = array_words >> 1;
     const long long W = array_words;
-    const long long q0 = lag0 >> 5, q1 = lag1 >> 5;
-    const uint32_t s0 = (uint32_t)(lag0 & 31), s1 = (uint32_t)(lag1 & 31);
+    const long long q0 = T.lag0 >> 5, q1 = T.lag1 >> 5;
+    const uint32_t s0 = (uint32_t)(T.lag0 & 31), s1 = (uint32_t)(T.lag1 & 31);
+    const uint32_t v_lo = (uint32_t)(blockIdx.x - cta_prefix[lo_t]) * DERIVE_QUADS_PER_CTA;
+    const uint32_t v_hi = min(quads, v_lo + DERIVE_QUADS_PER_CTA);
     unsigned int c0 = 0, c1 = 0;
-    for (uint32_t v = blockIdx.x * blockDim.x + threadIdx.x; v < quads; v += gridDim.x * blockDim.x) {
+    for (uint32_t v = v_lo + threadIdx.x; v < v_hi; v += blockDim.x) {
         const uint32_t i = 4 * v;
         const uint4 m4 = *reinterpret_cast<const uint4*>(M + i);
         const uint32_t m[4] = {m4.x, m4.y, m4.z, m4.w};
@@ -569,8 +594,8 @@ __global__ void derive_kernel(const uint32_t* __restrict__ M,
         c1 += __shfl_xor_sync(0xFFFFFFFFu, c1, o);
     }
     if ((threadIdx.x & 31) == 0) {
-        if (c0) atomicAdd(adirect, (unsigned long long)c0);
-        if (c1) atomicAdd(adirect + 1, (unsigned long long)c1);
+        if (c0) atomicAdd(T.adirect, (unsigned long long)c0);
+        if (c1) atomicAdd(T.adirect + 1, (unsigned long long)c1);
     }
 }
 
