@@ -72,18 +72,28 @@ class ClockSampler(object):
         except Exception as e:      # noqa: BLE001
             self.nv, self.err = None, repr(e)
 
-    def _poll(self):
+    def _sample(self, power=False):
         nv = self.nv
+        try:
+            sm = nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM)
+            rs = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+            pw = nv.nvmlDeviceGetPowerUsage(self.h) / 1000.0 if power else 0.0
+            self.samples.append((sm, rs, pw))
+            return True
+        except Exception as e:  # noqa: BLE001
+            self.err = repr(e)
+            return False
+
+    def _poll(self):
+        # NVML queries take a driver lock that delays work submission on the device (measured:
+        # a 2 ms poll added 0.45 ms to a 2.4 ms step), so poll sparsely: one sample when the
+        # region starts, one every PERIOD seconds, one (with power) when it ends.
         while not self.stop_flag:
-            try:
-                sm = nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM)
-                rs = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
-                pw = nv.nvmlDeviceGetPowerUsage(self.h) / 1000.0
-                self.samples.append((sm, rs, pw))
-            except Exception as e:  # noqa: BLE001
-                self.err = repr(e)
+            if not self._sample():
                 return
-            time.sleep(0.002)
+            time.sleep(self.PERIOD)
+
+    PERIOD = 0.02
 
     def start(self):
         if self.nv is not None:
@@ -93,6 +103,8 @@ class ClockSampler(object):
 
     def stop(self):
         self.stop_flag = True
+        if self.nv is not None:
+            self._sample(power=True)     # the device is still busy: the timed work has not drained yet
         if self.thread is not None:
             self.thread.join(timeout=2)
         if not self.samples:
@@ -103,7 +115,9 @@ class ClockSampler(object):
             mask |= x[1]
         return {"sm_mhz": float(np.median(sm)), "sm_min_mhz": float(min(sm)), "sm_max_mhz": float(self.max_sm),
                 "power_w_max": max(x[2] for x in self.samples), "samples": len(sm),
-                "reasons": [name for bit, name in self.REASONS if mask & bit], "source": "nvml, 2 ms poll"}
+                "reasons": [name for bit, name in self.REASONS if mask & bit],
+                "source": "nvml, polled (start / every 20 ms / end) over the same K steps repeated back to back "
+                          "right after the timed ones: queries inside the timed region perturb it"}
 
 
 def pinned_u32(a):
@@ -345,14 +359,19 @@ def gpu_arm(args):
         for _ in range(args.warmup):
             step()
         barrier()
-        sampler = ClockSampler(local).start() if rank == 0 else None
         ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         ev0.record(stream)
         for _ in range(args.steps):
             step()
         ev1.record(stream)
+        # Clocks: NVML queries take a driver lock that stalls submission / NCCL progress (measured:
+        # two queries inside the region added 0.45 ms to every 2.4 ms step at N=2), so they are
+        # taken over the SAME steps run again back to back, the device never going idle between.
+        sampler = ClockSampler(local).start() if (rank == 0 and not args.no_clocks) else None
+        for _ in range(args.steps):
+            step()
+        clocks = sampler.stop() if sampler else None      # steps are enqueued, the device is still in them
         barrier()
-        clocks = sampler.stop() if sampler else None
         dev_ms = max_over_ranks(ev0.elapsed_time(ev1))
         ms_per_step = dev_ms / args.steps
         launches_per_step = dev.timing()["launches"]
@@ -367,7 +386,17 @@ def gpu_arm(args):
         pairs = t["window_word_shift_pairs"]
         win_launches = t["window_launches"]
         used_path = t["path"]
+        # N > 1: the same K steps without the all-reduce (slowest rank) -> what the collective costs
+        exec_only_ms = None
         if world > 1:
+            barrier()
+            ev0.record(stream)
+            for _ in range(args.steps):
+                batch.execute()
+            ev1.record(stream)
+            barrier()
+            mine_ms = ev0.elapsed_time(ev1) / args.steps
+            exec_only_ms = {"max": max_over_ranks(mine_ms), "min": -max_over_ranks(-mine_ms)}
             dist.all_reduce(ctr)        # the last execute above left this rank's partial counts
         resident = batch.fetch()
         batch.free()
@@ -383,6 +412,8 @@ def gpu_arm(args):
                 ob.execute()
                 t2 = dev.timing()
                 o_win.append(t2["window_ms"]); o_build.append(t2["build_ms"])
+            if world > 1:
+                dist.all_reduce(counters_tensor(ob))
             o_out = ob.fetch()
             ob.free()
             dev.set_option("path", {"auto": 0, "dense": 1, "events": 2}[args.path])
@@ -502,6 +533,7 @@ def gpu_arm(args):
             "clocks": clocks,
             "roofline": roof,
             "paths": paths,
+            "execute_only_ms_per_step_over_ranks": exec_only_ms,
             "resident_equals_e2e": bool(same),
             "synthetic_generation_s": round(gen_s, 1),
         }
@@ -535,6 +567,7 @@ def main():
                     help="device algorithm: dense shift-window kernel or event-window kernels")
     ap.add_argument("--opt", action="append", default=[], help="pmb_set_option name=value (tuning)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-clocks", action="store_true", help="do not poll NVML during the timed region (diagnostic)")
     ap.add_argument("--cpu-sample-bp", type=int, default=20_000_000)
     ap.add_argument("--ref-cores", type=int, default=0)
     args = ap.parse_args()
