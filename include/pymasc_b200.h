@@ -114,13 +114,19 @@ void pmb_destroy(pmb_ctx *ctx);
 const char *pmb_last_error(pmb_ctx *ctx);   /* ctx may be NULL: last create error */
 
 /* Whole path for one chromosome / a list of chromosomes from HOST arrays:
- * H2D, bit-array build, shift-window kernel, D2H.  Synchronous. */
+ * H2D, bit-array build, correlation kernels, D2H.  Synchronous for the caller; inside,
+ * the input copy runs on a copy stream in "h2d_groups" groups of chromosomes and the
+ * kernels of one group overlap the copy of the next. */
 int pmb_run_chrom(pmb_ctx *ctx, const pmb_chrom_args *a, pmb_chrom_out *o);
 int pmb_run_batch(pmb_ctx *ctx, const pmb_chrom_args *a, pmb_chrom_out *o, uint32_t n);
 
 /* The same path in three steps, so that inputs can stay resident in HBM and the
  * counters can be reduced across GPUs before they leave the device:
- *   prepare : copy positions/intervals to the device (H2D), plan tiles
+ *   prepare : copy positions/intervals to the device (H2D), plan tiles.  With option
+ *             "async_h2d" = 1 it returns while the copy is still in flight (grouped as in
+ *             pmb_run_batch); the host arrays must then stay valid and unchanged until
+ *             the FIRST execute of the batch has completed (pmb_batch_fetch or
+ *             pmb_synchronize after it).  Default 0: the arrays are free on return.
  *   execute : build bit arrays + shift-window kernel; counters stay on the device;
  *             may be called repeatedly (each call recomputes from the resident inputs)
  *   fetch   : D2H of the counters into caller-allocated outputs
@@ -152,7 +158,8 @@ void pmb_host_free(void *p);
  * kernels -- two algorithms for the same counts (identical results); auto takes the
  * event path unless the inputs hold more than 4 events (reads + run edges) per 32-bit
  * word.  Tuning: "variant" (carry-save depth of the shift-window counters), "tile_words",
- * "grid_blocks", "block_warps", "event_tile_words", "event_blocks_per_sm". */
+ * "grid_blocks", "block_warps", "event_tile_words", "event_blocks_per_sm".
+ * Input copy: "async_h2d" (0/1, see pmb_batch_prepare), "h2d_groups" (1..64, default 3). */
 int  pmb_set_option(pmb_ctx *ctx, const char *name, int64_t value);
 
 /* Integer-pipe calibration on the device: runs a dependent-free loop of `what`

@@ -205,22 +205,31 @@ class Device(object):
 
     @staticmethod
     def _outputs(jobs):
+        """Output structs over ONE int64 block (a view per counter): per-array allocations and
+        .ctypes lookups cost more host time than the D2H copy itself."""
         n = len(jobs)
         outs = (ChromOut * n)()
+        names = []
+        total = 0
+        for j in jobs:
+            if j.flags & FLAG_AUTOCORR:
+                ks = ("dmp",)
+            else:
+                ks = (("ncc",) if j.flags & FLAG_NCC else ()) + \
+                     (("dmp", "mfwd", "mrev", "mscc") if j.flags & FLAG_MSCC else ())
+            names.append(ks)
+            total += len(ks) * (j.max_shift + 1)
+        block = np.empty(max(total, 1), np.int64)
+        base = block.ctypes.data
         arrays = []
-        for o, j in zip(outs, jobs):
+        off = 0
+        for o, j, ks in zip(outs, jobs, names):
             S = j.max_shift + 1
             d = {}
-            if j.flags & FLAG_AUTOCORR:
-                d["dmp"] = np.zeros(S, np.int64)
-            else:
-                if j.flags & FLAG_NCC:
-                    d["ncc"] = np.zeros(S, np.int64)
-                if j.flags & FLAG_MSCC:
-                    for k in ("dmp", "mfwd", "mrev", "mscc"):
-                        d[k] = np.zeros(S, np.int64)
-            for k, v in d.items():
-                setattr(o, k, v.ctypes.data)
+            for k in ks:
+                d[k] = block[off:off + S]
+                setattr(o, k, base + 8 * off)
+                off += S
             arrays.append(d)
         return outs, arrays
 

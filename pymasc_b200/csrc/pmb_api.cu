@@ -37,6 +37,12 @@ struct pmb_ctx {
     int path = 0;            // 0 auto, 1 dense shift-window, 2 event-window
     int event_tile_words = 0;
     int event_blocks_per_sm = 0;
+    int async_h2d = 0;       // prepare returns before the input copy has finished (see header)
+    int h2d_groups = 3;      // event path: job groups whose build + kernels overlap the H2D of the next
+    cudaStream_t copy_stream = nullptr;
+    cudaStream_t side_stream = nullptr;   // grouped execute: odd groups run here, so that one group's
+                                          // kernel tails overlap the next group's build
+    cudaEvent_t ev_alloc = nullptr, ev_side = nullptr;
     // pinned staging for counters
     void* h_stage = nullptr;
     size_t h_stage_bytes = 0;
@@ -102,6 +108,17 @@ struct pmb_batch {
     FillTask* d_fill = nullptr; uint64_t* d_fill_prefix = nullptr; uint32_t n_fill = 0; uint64_t fill_items = 0;
     DeriveTask* d_derive = nullptr; uint64_t* d_derive_prefix = nullptr; uint32_t n_derive = 0; uint64_t derive_ctas = 0;
     unsigned long long* d_long64 = nullptr;   // long-interval queue of fill_multi_kernel
+    // pipelined H2D: consecutive jobs in groups; a group's inputs arrive on the copy stream and
+    // `done` is recorded behind them.  Task / tile ranges are those of the group's jobs.
+    struct Group {
+        uint32_t job_lo = 0, job_hi = 0;
+        uint32_t sc_lo = 0, sc_hi = 0, fl_lo = 0, fl_hi = 0, dv_lo = 0, dv_hi = 0;
+        uint64_t sc_items = 0, fl_items = 0, dv_ctas = 0;
+        uint32_t tile_lo = 0, tile_hi = 0;
+        cudaEvent_t done = nullptr;
+    };
+    std::vector<Group> groups;
+    bool h2d_pending = false;           // the first execute has to wait for the groups' events
 };
 
 // ------------------------------------------------------------------ context
@@ -141,6 +158,14 @@ extern "C" int pmb_create(pmb_ctx** out, int device_ordinal)
     if ((e = cudaStreamCreateWithFlags(&c->own_stream, cudaStreamNonBlocking)) != cudaSuccess)
         return fail("cudaStreamCreate", e);
     c->stream = c->own_stream;
+    if ((e = cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking)) != cudaSuccess)
+        return fail("cudaStreamCreate", e);
+    if ((e = cudaStreamCreateWithFlags(&c->side_stream, cudaStreamNonBlocking)) != cudaSuccess)
+        return fail("cudaStreamCreate", e);
+    if ((e = cudaEventCreateWithFlags(&c->ev_alloc, cudaEventDisableTiming)) != cudaSuccess)
+        return fail("cudaEventCreate", e);
+    if ((e = cudaEventCreateWithFlags(&c->ev_side, cudaEventDisableTiming)) != cudaSuccess)
+        return fail("cudaEventCreate", e);
     for (auto& ev : c->ev)
         if ((e = cudaEventCreate(&ev)) != cudaSuccess) return fail("cudaEventCreate", e);
     for (auto& ev : c->evk)
@@ -165,6 +190,10 @@ extern "C" void pmb_destroy(pmb_ctx* c)
     for (auto& ev : c->evk)
         if (ev) cudaEventDestroy(ev);
     if (c->h_stage) cudaFreeHost(c->h_stage);
+    if (c->ev_alloc) cudaEventDestroy(c->ev_alloc);
+    if (c->ev_side) cudaEventDestroy(c->ev_side);
+    if (c->side_stream) { cudaStreamSynchronize(c->side_stream); cudaStreamDestroy(c->side_stream); }
+    if (c->copy_stream) { cudaStreamSynchronize(c->copy_stream); cudaStreamDestroy(c->copy_stream); }
     if (c->own_stream) cudaStreamDestroy(c->own_stream);
     delete c;
 }
@@ -214,6 +243,8 @@ extern "C" int pmb_set_option(pmb_ctx* c, const char* name, int64_t value)
     else if (!strcmp(name, "path")) c->path = (int)value;
     else if (!strcmp(name, "event_tile_words")) c->event_tile_words = (int)value;
     else if (!strcmp(name, "event_blocks_per_sm")) c->event_blocks_per_sm = (int)value;
+    else if (!strcmp(name, "async_h2d")) c->async_h2d = value != 0;
+    else if (!strcmp(name, "h2d_groups")) c->h2d_groups = (int)std::max<int64_t>(1, std::min<int64_t>(value, 64));
     else { c->err = std::string("unknown option ") + name; return PMB_ERR_ARG; }
     return PMB_OK;
 }
@@ -258,6 +289,9 @@ extern "C" void pmb_batch_free(pmb_ctx* c, pmb_batch* b)
     if (!b) return;
     if (c) {
         cudaSetDevice(c->device);
+        if (b->h2d_pending && c->copy_stream) cudaStreamSynchronize(c->copy_stream);   // never executed
+        for (auto& g : b->groups)
+            if (g.done) cudaEventDestroy(g.done);
         if (b->d_in) cudaFreeAsync(b->d_in, c->stream);
         if (b->d_bits_raw) cudaFreeAsync(b->d_bits_raw, c->stream);
         if (b->d_counters) cudaFreeAsync(b->d_counters, c->stream);
@@ -397,8 +431,10 @@ static int plan_events(pmb_ctx* c, pmb_batch* b)
         std::vector<FillTask> fl; std::vector<uint64_t> flp{0};
         std::vector<DeriveTask> dv; std::vector<uint64_t> dvp{0};
         unsigned long long* adir0 = b->d_aux + n * 2 * (size_t)b->stride;
+        std::vector<uint32_t> sc_at(n + 1), fl_at(n + 1), dv_at(n + 1);
         for (size_t i = 0; i < n; i++) {
             JobPlan& j = b->jobs[i];
+            sc_at[i] = (uint32_t)sc.size(); fl_at[i] = (uint32_t)fl.size(); dv_at[i] = (uint32_t)dv.size();
             Geometry g;
             g.origin_bit = j.origin_word * 32;
             g.halo_bits = (int64_t)b->halo_words * 32;
@@ -429,6 +465,14 @@ static int plan_events(pmb_ctx* c, pmb_batch* b)
             dv.push_back(d);
             dvp.push_back(dvp.back() + (j.array_words / 4 + DERIVE_QUADS_PER_CTA - 1) / DERIVE_QUADS_PER_CTA);
         }
+        sc_at[n] = (uint32_t)sc.size(); fl_at[n] = (uint32_t)fl.size(); dv_at[n] = (uint32_t)dv.size();
+        for (auto& gr : b->groups) {
+            gr.sc_lo = sc_at[gr.job_lo]; gr.sc_hi = sc_at[gr.job_hi]; gr.sc_items = scp[gr.sc_hi] - scp[gr.sc_lo];
+            gr.fl_lo = fl_at[gr.job_lo]; gr.fl_hi = fl_at[gr.job_hi]; gr.fl_items = flp[gr.fl_hi] - flp[gr.fl_lo];
+            gr.dv_lo = dv_at[gr.job_lo]; gr.dv_hi = dv_at[gr.job_hi]; gr.dv_ctas = dvp[gr.dv_hi] - dvp[gr.dv_lo];
+            gr.tile_lo = table[gr.job_lo].tile_begin;
+            gr.tile_hi = table[gr.job_hi - 1].tile_begin + table[gr.job_hi - 1].n_tiles;
+        }
         b->n_scatter = (uint32_t)sc.size(); b->scatter_items = scp.back();
         b->n_fill = (uint32_t)fl.size(); b->fill_items = flp.back();
         b->n_derive = (uint32_t)dv.size(); b->derive_ctas = dvp.back();
@@ -450,7 +494,7 @@ static int plan_events(pmb_ctx* c, pmb_batch* b)
         b->d_scatter = (ScatterTask*)(d + o_sc); b->d_scatter_prefix = (uint64_t*)(d + o_scp);
         b->d_fill = (FillTask*)(d + o_fl); b->d_fill_prefix = (uint64_t*)(d + o_flp);
         b->d_derive = (DeriveTask*)(d + o_dv); b->d_derive_prefix = (uint64_t*)(d + o_dvp);
-        CU_TRY(c, cudaMallocAsync((void**)&b->d_long64, (b->fill_items + 1) * 8, c->stream));
+        CU_TRY(c, cudaMallocAsync((void**)&b->d_long64, 2 * (b->fill_items + 1) * 8, c->stream));   // main | side
         CU_TRY(c, cudaStreamSynchronize(c->stream));   // `blob` is a local
     }
     CU_TRY(c, cudaMemcpyAsync(b->d_evjobs, table.data(), n * sizeof(EventJob), cudaMemcpyHostToDevice,
@@ -459,7 +503,7 @@ static int plan_events(pmb_ctx* c, pmb_batch* b)
     return PMB_OK;
 }
 
-extern "C" int pmb_batch_prepare(pmb_ctx* c, const pmb_chrom_args* a, uint32_t n, pmb_batch** out)
+static int prepare_impl(pmb_ctx* c, const pmb_chrom_args* a, uint32_t n, pmb_batch** out, bool async)
 {
     if (!c || !a || !out || n == 0) return PMB_ERR_ARG;
     *out = nullptr;
@@ -565,6 +609,71 @@ extern "C" int pmb_batch_prepare(pmb_ctx* c, const pmb_chrom_args* a, uint32_t n
     b->counter_words = (size_t)n * PMB_NCOUNTERS * b->stride + (size_t)n * 2;
 
     CU_TRY(c, cudaMallocAsync((void**)&b->d_in, std::max<size_t>(in_words, 4) * 4, c->stream));
+    // H2D of the packed inputs.  Synchronous mode: on the compute stream, complete when prepare
+    // returns.  Asynchronous mode: on the copy stream in groups of consecutive jobs of about equal
+    // bytes, an event behind each group; the first execute consumes group g while g+1 is in flight.
+    cudaStream_t up_stream = c->stream;
+    {
+        const uint32_t want = async ? (b->path == 2 ? (uint32_t)c->h2d_groups : 1u) : 1u;
+        std::vector<size_t> job_words(n);
+        for (uint32_t i = 0; i < n; i++) {
+            const JobPlan& j = b->jobs[i];
+            job_words[i] = (j.autocorr ? 0 : j.a.n_fwd + j.a.n_rev) +
+                           (((j.mode & MODE_MSCC) || j.autocorr) ? 2 * j.a.n_intervals : 0);
+        }
+        size_t total = 0, acc = 0;
+        for (size_t w : job_words) total += w;
+        // Group sizes grow geometrically: the first group is small so the kernels start early,
+        // and each later group may be larger because computing on a group takes ~2.4x as long
+        // as copying it (so the copy of group g+1 hides behind the kernels of group g).
+        const double growth = 2.4;
+        std::vector<double> cum(want, 1.0);
+        {
+            double sum = 0, w = 1;
+            for (uint32_t g = 0; g < want; g++, w *= growth) sum += w;
+            double run = 0; w = 1;
+            for (uint32_t g = 0; g < want; g++, w *= growth) { run += w; cum[g] = run / sum; }
+        }
+        pmb_batch::Group g;
+        for (uint32_t i = 0; i < n; i++) {
+            acc += job_words[i];
+            const uint32_t made = (uint32_t)b->groups.size();
+            // close the group once its share of the bytes is in (the last group takes the rest)
+            if (i + 1 == n || (made + 1 < want && (double)acc >= cum[made] * (double)total)) {
+                g.job_hi = i + 1;
+                b->groups.push_back(g);
+                g = pmb_batch::Group();
+                g.job_lo = i + 1;
+            }
+        }
+        if (async) {
+            for (auto& gr : b->groups)
+                CU_TRY(c, cudaEventCreateWithFlags(&gr.done, cudaEventDisableTiming));
+            CU_TRY(c, cudaEventRecord(c->ev_alloc, c->stream));        // d_in exists from here on
+            CU_TRY(c, cudaStreamWaitEvent(c->copy_stream, c->ev_alloc, 0));
+            up_stream = c->copy_stream;
+            b->h2d_pending = true;
+        }
+    }
+    for (auto& gr : b->groups) {
+      for (uint32_t ji = gr.job_lo; ji < gr.job_hi; ji++) {
+        JobPlan& j = b->jobs[ji];
+        auto up = [&](size_t off, const uint32_t* src, uint64_t cnt) -> cudaError_t {
+            if (!cnt) return cudaSuccess;
+            return cudaMemcpyAsync(b->d_in + off, src, cnt * 4, cudaMemcpyHostToDevice, up_stream);
+        };
+        if (!j.autocorr) {
+            CU_TRY(c, up(j.in_fwd, j.a.fwd_pos, j.a.n_fwd));
+            CU_TRY(c, up(j.in_rev, j.a.rev_pos, j.a.n_rev));
+        }
+        if ((j.mode & MODE_MSCC) || j.autocorr) {
+            CU_TRY(c, up(j.in_mb, j.a.map_begin, j.a.n_intervals));
+            CU_TRY(c, up(j.in_me, j.a.map_end, j.a.n_intervals));
+        }
+        j.a.fwd_pos = j.a.rev_pos = j.a.map_begin = j.a.map_end = nullptr;   // not read again by the host
+      }
+      if (async) CU_TRY(c, cudaEventRecord(gr.done, up_stream));
+    }
     CU_TRY(c, cudaMallocAsync((void**)&b->d_bits_raw,
                               (std::max<size_t>(bits_words, 4) + 2 * (size_t)EV_PAD_WORDS) * 4, c->stream));
     b->d_bits = b->d_bits_raw + EV_PAD_WORDS;
@@ -581,30 +690,21 @@ extern "C" int pmb_batch_prepare(pmb_ctx* c, const pmb_chrom_args* a, uint32_t n
     b->d_jobs_count = (size_t)n * ((b->n_units + 63) / 64 + 1) * 3;
     CU_TRY(c, cudaMallocAsync((void**)&b->d_jobs, b->d_jobs_count * sizeof(WindowJob), c->stream));
 
-    // H2D of the packed inputs
-    for (auto& j : b->jobs) {
-        auto up = [&](size_t off, const uint32_t* src, uint64_t cnt) -> cudaError_t {
-            if (!cnt) return cudaSuccess;
-            return cudaMemcpyAsync(b->d_in + off, src, cnt * 4, cudaMemcpyHostToDevice, c->stream);
-        };
-        if (!j.autocorr) {
-            CU_TRY(c, up(j.in_fwd, j.a.fwd_pos, j.a.n_fwd));
-            CU_TRY(c, up(j.in_rev, j.a.rev_pos, j.a.n_rev));
-        }
-        if ((j.mode & MODE_MSCC) || j.autocorr) {
-            CU_TRY(c, up(j.in_mb, j.a.map_begin, j.a.n_intervals));
-            CU_TRY(c, up(j.in_me, j.a.map_end, j.a.n_intervals));
-        }
-        j.a.fwd_pos = j.a.rev_pos = j.a.map_begin = j.a.map_end = nullptr;   // borrowed no longer
-    }
     {
         int rc = b->path == 2 ? plan_events(c, b) : plan_windows(c, b);
         if (rc != PMB_OK) return rc;
     }
-    CU_TRY(c, cudaStreamSynchronize(c->stream));   // host arrays may be released by the caller
+    // synchronous mode: host arrays may be released by the caller; asynchronous mode: they are
+    // still being read by the copy engine until the first execute of this batch has completed
+    CU_TRY(c, cudaStreamSynchronize(c->stream));
     guard.armed = false;
     *out = b;
     return PMB_OK;
+}
+
+extern "C" int pmb_batch_prepare(pmb_ctx* c, const pmb_chrom_args* a, uint32_t n, pmb_batch** out)
+{
+    return prepare_impl(c, a, n, out, c && c->async_h2d);
 }
 
 // ------------------------------------------------------------------ batch: execute
@@ -644,8 +744,6 @@ static cudaError_t launch_window(pmb_ctx* c, int variant, const WindowParams& P,
 static int execute_events(pmb_ctx* c, pmb_batch* b)
 {
     cudaStream_t st = c->stream;
-    const uint32_t H = b->halo_words;
-    const int64_t NEG = -(1ll << 40), POS = (1ll << 40);
     uint32_t launches = 0;
     const size_t n = b->jobs.size();
 
@@ -661,37 +759,33 @@ static int execute_events(pmb_ctx* c, pmb_batch* b)
         uint64_t g = (items + per_block - 1) / per_block;
         return (unsigned)std::min<uint64_t>(std::max<uint64_t>(g, 1), (uint64_t)c->num_sms * 16);
     };
-    if (b->scatter_items) {     // strand totals are counted by the forward-read event kernel
-        scatter_multi_kernel<<<blocks_for(b->scatter_items, 256), 256, 0, st>>>(
-            b->d_scatter, b->d_scatter_prefix, b->n_scatter, b->d_err);
-        launches++;
+    // One pass = build + event kernels over a run of jobs: the whole batch, or (first execute
+    // after an asynchronous prepare) one H2D group at a time, each behind its copy event, so the
+    // kernels of group g run while the inputs of group g+1 are still crossing PCIe.
+    pmb_batch::Group whole;
+    whole.job_lo = 0; whole.job_hi = (uint32_t)n;
+    whole.sc_lo = 0; whole.sc_hi = b->n_scatter; whole.sc_items = b->scatter_items;
+    whole.fl_lo = 0; whole.fl_hi = b->n_fill; whole.fl_items = b->fill_items;
+    whole.dv_lo = 0; whole.dv_hi = b->n_derive; whole.dv_ctas = b->derive_ctas;
+    whole.tile_lo = 0; whole.tile_hi = b->ev_total_tiles;
+    const bool grouped = b->h2d_pending && b->groups.size() > 1;
+    const size_t n_pass = grouped ? b->groups.size() : 1;
+    if (b->h2d_pending && !grouped)
+        for (auto& gr : b->groups) CU_TRY(c, cudaStreamWaitEvent(st, gr.done, 0));
+    if (grouped) {      // the side stream starts behind the memsets above
+        CU_TRY(c, cudaEventRecord(c->ev_side, st));
+        CU_TRY(c, cudaStreamWaitEvent(c->side_stream, c->ev_side, 0));
     }
-    if (b->fill_items) {
-        CU_TRY(c, cudaMemsetAsync(b->d_long, 0, 4, st));
-        fill_multi_kernel<<<blocks_for(b->fill_items, 8), 256, 0, st>>>(
-            b->d_fill, b->d_fill_prefix, b->n_fill, b->d_err, b->d_long64, b->d_long);
-        fill_long_multi_kernel<<<c->num_sms * 4, 256, 0, st>>>(b->d_fill, b->d_long64, b->d_long);
-        launches += 2;
-    }
-    if (b->derive_ctas) {
-        derive_multi_kernel<<<(unsigned)b->derive_ctas, 256, 0, st>>>(b->d_derive, b->d_derive_prefix,
-                                                                     b->n_derive, b->max_shift ? 2 : 1);
-        launches++;
-    }
-    CU_TRY(c, cudaGetLastError());
-    CU_TRY(c, cudaEventRecord(c->ev[1], st));
 
     EventParams P{};
     P.jobs = b->d_evjobs;
     P.n_jobs = (uint32_t)n;
-    P.total_tiles = b->ev_total_tiles;
     P.tile_words = b->ev_tile_words;
     P.max_shift = b->max_shift;
     P.read_len = b->read_len;
     P.stride = b->stride;
     const uint32_t n_cols_total = (b->n_shifts + 31) / 32;
     const uint32_t bps = c->event_blocks_per_sm > 0 ? (uint32_t)c->event_blocks_per_sm : 8;
-    const uint32_t grid = std::max(1u, std::min(b->ev_total_tiles, (uint32_t)c->num_sms * bps));
     uint32_t window_launches = 0;
 #define PMB_EV_LAUNCH(KIND, NCC, MSCC)                                                              \
     do {                                                                                            \
@@ -701,18 +795,61 @@ static int execute_events(pmb_ctx* c, pmb_batch* b)
         for (uint32_t col0 = 0; col0 < n_cols_total; col0 += 32) {                                  \
             P.col0 = col0;                                                                          \
             P.n_cols = std::min(32u, n_cols_total - col0);                                          \
-            k<<<grid, 32 * EV_WARPS, sm, st>>>(P);                                                  \
+            k<<<grid, 32 * EV_WARPS, sm, ps>>>(P);                                                  \
             window_launches++;                                                                      \
         }                                                                                           \
     } while (0)
-    if (b->any_ncc && b->any_mscc) PMB_EV_LAUNCH(EV_FWD, true, true);
-    else if (b->any_ncc) PMB_EV_LAUNCH(EV_FWD, true, false);
-    else if (b->any_mscc) PMB_EV_LAUNCH(EV_FWD, false, true);
-    CU_TRY(c, cudaEventRecord(c->evk[0], st));
-    if (b->any_mscc) PMB_EV_LAUNCH(EV_REV, false, true);
-    CU_TRY(c, cudaEventRecord(c->evk[1], st));
-    if (b->any_mscc || b->any_autocorr) PMB_EV_LAUNCH(EV_EDGE, false, true);
+    for (size_t pass = 0; pass < n_pass; pass++) {
+        const pmb_batch::Group& G = grouped ? b->groups[pass] : whole;
+        // odd groups run on the side stream: a group's kernel tails then overlap the next
+        // group's build instead of leaving the SMs idle between 7 short launches
+        const bool side = grouped && (pass & 1);
+        cudaStream_t ps = side ? c->side_stream : st;
+        uint32_t* long_count = b->d_long + (side ? 1 : 0);
+        unsigned long long* long_list = b->d_long64 + (side ? b->fill_items + 1 : 0);
+        if (grouped) CU_TRY(c, cudaStreamWaitEvent(ps, G.done, 0));
+        if (G.sc_items) {     // strand totals are counted by the forward-read event kernel
+            scatter_multi_kernel<<<blocks_for(G.sc_items, 256), 256, 0, ps>>>(
+                b->d_scatter + G.sc_lo, b->d_scatter_prefix + G.sc_lo, G.sc_hi - G.sc_lo, b->d_err);
+            launches++;
+        }
+        if (G.fl_items) {
+            CU_TRY(c, cudaMemsetAsync(long_count, 0, 4, ps));
+            fill_multi_kernel<<<blocks_for(G.fl_items, 8), 256, 0, ps>>>(
+                b->d_fill + G.fl_lo, b->d_fill_prefix + G.fl_lo, G.fl_hi - G.fl_lo, b->d_err, long_list,
+                long_count);
+            fill_long_multi_kernel<<<c->num_sms * 4, 256, 0, ps>>>(b->d_fill + G.fl_lo, long_list, long_count);
+            launches += 2;
+        }
+        if (G.dv_ctas) {
+            derive_multi_kernel<<<(unsigned)G.dv_ctas, 256, 0, ps>>>(
+                b->d_derive + G.dv_lo, b->d_derive_prefix + G.dv_lo, G.dv_hi - G.dv_lo, b->max_shift ? 2 : 1);
+            launches++;
+        }
+        CU_TRY(c, cudaGetLastError());
+        if (!grouped) CU_TRY(c, cudaEventRecord(c->ev[1], st));
+
+        P.tile_lo = G.tile_lo;
+        P.tile_hi = G.tile_hi;
+        if (G.tile_hi == G.tile_lo) continue;
+        const uint32_t grid = std::max(1u, std::min(G.tile_hi - G.tile_lo, (uint32_t)c->num_sms * bps));
+        if (b->any_ncc && b->any_mscc) PMB_EV_LAUNCH(EV_FWD, true, true);
+        else if (b->any_ncc) PMB_EV_LAUNCH(EV_FWD, true, false);
+        else if (b->any_mscc) PMB_EV_LAUNCH(EV_FWD, false, true);
+        if (!grouped) CU_TRY(c, cudaEventRecord(c->evk[0], st));
+        if (b->any_mscc) PMB_EV_LAUNCH(EV_REV, false, true);
+        if (!grouped) CU_TRY(c, cudaEventRecord(c->evk[1], st));
+        if (b->any_mscc || b->any_autocorr) PMB_EV_LAUNCH(EV_EDGE, false, true);
+    }
 #undef PMB_EV_LAUNCH
+    if (grouped) {      // join the side stream; the per-kernel split is not meaningful here
+        CU_TRY(c, cudaEventRecord(c->ev_side, c->side_stream));
+        CU_TRY(c, cudaStreamWaitEvent(st, c->ev_side, 0));
+        CU_TRY(c, cudaEventRecord(c->ev[1], st));
+        CU_TRY(c, cudaEventRecord(c->evk[0], st));
+        CU_TRY(c, cudaEventRecord(c->evk[1], st));
+    }
+    b->h2d_pending = false;
     if (b->any_mscc || b->any_autocorr) {
         finalize_dmp_kernel<<<(unsigned)n, 256, 0, st>>>(b->d_evjobs, (uint32_t)n, b->stride, b->max_shift);
         window_launches++;
@@ -738,6 +875,10 @@ extern "C" int pmb_batch_execute(pmb_ctx* c, pmb_batch* b)
     uint32_t launches = 0;
 
     CU_TRY(c, cudaEventRecord(c->ev[0], st));
+    if (b->h2d_pending) {       // asynchronous prepare: the inputs arrive on the copy stream
+        for (auto& gr : b->groups) CU_TRY(c, cudaStreamWaitEvent(st, gr.done, 0));
+        b->h2d_pending = false;
+    }
     CU_TRY(c, cudaMemsetAsync(b->d_bits, 0, std::max<size_t>(b->bits_words, 4) * 4, st));
     CU_TRY(c, cudaMemsetAsync(b->d_counters, 0, b->counter_words * 8, st));
     CU_TRY(c, cudaMemsetAsync(b->d_err, 0, 16, st));
@@ -888,7 +1029,8 @@ extern "C" int pmb_batch_fetch(pmb_ctx* c, pmb_batch* b, pmb_chrom_out* o)
 extern "C" int pmb_run_batch(pmb_ctx* c, const pmb_chrom_args* a, pmb_chrom_out* o, uint32_t n)
 {
     pmb_batch* b = nullptr;
-    int rc = pmb_batch_prepare(c, a, n, &b);
+    // the caller's arrays stay valid for the whole call, so the input copy may overlap the kernels
+    int rc = prepare_impl(c, a, n, &b, true);
     if (rc != PMB_OK) return rc;
     rc = pmb_batch_execute(c, b);
     if (rc == PMB_OK) rc = pmb_batch_fetch(c, b, o);

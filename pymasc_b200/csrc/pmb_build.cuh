@@ -205,8 +205,10 @@ __device__ __forceinline__ uint32_t find_task(const uint64_t* __restrict__ prefi
 __global__ void scatter_multi_kernel(const ScatterTask* __restrict__ tasks, const uint64_t* __restrict__ prefix,
                                      uint32_t n_tasks, int* __restrict__ err_flag)
 {
+    // `tasks` / `prefix` may point into the middle of the batch's tables (one group of jobs):
+    // items are numbered from prefix[0]
     const uint64_t total = prefix[n_tasks];
-    uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    uint64_t i = prefix[0] + (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
     const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
     for (; i < total; i += stride) {
         const uint32_t t = find_task(prefix, n_tasks, i);
@@ -229,7 +231,7 @@ __global__ void fill_multi_kernel(const FillTask* __restrict__ tasks, const uint
     const uint64_t total = prefix[n_tasks];
     uint64_t warp = ((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const uint64_t nwarps = ((uint64_t)gridDim.x * blockDim.x) >> 5;
-    for (uint64_t i = warp; i < total; i += nwarps) {
+    for (uint64_t i = prefix[0] + warp; i < total; i += nwarps) {
         const uint32_t t = find_task(prefix, n_tasks, i);
         const FillTask& T = tasks[t];
         const uint64_t k = i - prefix[t];

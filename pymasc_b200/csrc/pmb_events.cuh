@@ -65,7 +65,8 @@ struct EventJob {
 struct EventParams {
     const EventJob* jobs;
     uint32_t n_jobs;
-    uint32_t total_tiles;
+    uint32_t tile_lo;       // this launch covers the tiles [tile_lo, tile_hi) of the batch
+    uint32_t tile_hi;       //   (everything, or one H2D group of jobs)
     uint32_t tile_words;    // multiple of 32 * warps per block
     uint32_t col0;          // first window column of this launch
     uint32_t n_cols;        // <= 32
@@ -248,8 +249,9 @@ __global__ void __launch_bounds__(32 * EV_WARPS) event_window_kernel(const Event
     const int lane = threadIdx.x & 31;
     const int warp = threadIdx.x >> 5;
 
-    const uint32_t t_lo = (uint32_t)(((uint64_t)P.total_tiles * blockIdx.x) / gridDim.x);
-    const uint32_t t_hi = (uint32_t)(((uint64_t)P.total_tiles * (blockIdx.x + 1)) / gridDim.x);
+    const uint32_t n_launch_tiles = P.tile_hi - P.tile_lo;
+    const uint32_t t_lo = P.tile_lo + (uint32_t)(((uint64_t)n_launch_tiles * blockIdx.x) / gridDim.x);
+    const uint32_t t_hi = P.tile_lo + (uint32_t)(((uint64_t)n_launch_tiles * (blockIdx.x + 1)) / gridDim.x);
     if (t_lo >= t_hi) return;
 
     for (uint32_t i = threadIdx.x; i < NC * 32 * EV_HIST_STRIDE; i += blockDim.x) hist[i] = 0;
@@ -536,10 +538,12 @@ __global__ void __launch_bounds__(256) derive_multi_kernel(const DeriveTask* __r
                                                            const uint64_t* __restrict__ cta_prefix,
                                                            uint32_t n_tasks, int n_lags)
 {
-    uint32_t lo_t = 0, hi_t = n_tasks;          // cta_prefix[lo_t] <= blockIdx.x < cta_prefix[hi_t]
+    // `tasks` / `cta_prefix` may point into the middle of the batch's tables (one group of jobs)
+    const uint64_t cta = cta_prefix[0] + blockIdx.x;
+    uint32_t lo_t = 0, hi_t = n_tasks;          // cta_prefix[lo_t] <= cta < cta_prefix[hi_t]
     while (hi_t - lo_t > 1) {
         const uint32_t mid = (lo_t + hi_t) >> 1;
-        if (cta_prefix[mid] <= blockIdx.x) lo_t = mid; else hi_t = mid;
+        if (cta_prefix[mid] <= cta) lo_t = mid; else hi_t = mid;
     }
     const DeriveTask& T = tasks[lo_t];
     const uint32_t* __restrict__ M = T.M;
@@ -552,7 +556,7 @@ __global__ void __launch_bounds__(256) derive_multi_kernel(const DeriveTask* __r
     const long long W = array_words;
     const long long q0 = T.lag0 >> 5, q1 = T.lag1 >> 5;
     const uint32_t s0 = (uint32_t)(T.lag0 & 31), s1 = (uint32_t)(T.lag1 & 31);
-    const uint32_t v_lo = (uint32_t)(blockIdx.x - cta_prefix[lo_t]) * DERIVE_QUADS_PER_CTA;
+    const uint32_t v_lo = (uint32_t)(cta - cta_prefix[lo_t]) * DERIVE_QUADS_PER_CTA;
     const uint32_t v_hi = min(quads, v_lo + DERIVE_QUADS_PER_CTA);
     unsigned int c0 = 0, c1 = 0;
     for (uint32_t v = v_lo + threadIdx.x; v < v_hi; v += blockDim.x) {

@@ -180,6 +180,54 @@ def test_prepare_execute_fetch_is_repeatable(dev):
     batch.free()
 
 
+@pytest.mark.parametrize("groups", [1, 2, 3, 7])
+def test_pipelined_input_copy_gives_the_same_counts(pdev, groups):
+    """pmb_run_batch / async prepare: the H2D runs on a copy stream in groups of chromosomes and
+    each group's build + kernels wait only for their own inputs.  Same counts as copy-then-compute,
+    for every group count (more groups than jobs, jobs without reads or intervals included)."""
+    dev = pdev
+    rl, D = 36, 300
+    jobs = []
+    for i, L in enumerate([70000, 3000, 150000, 40000, 90000, 64]):
+        fwd, rev, b, e = random_case(60 + i, L, rl, max(4, L // 12))
+        if i == 1:
+            fwd = fwd[:0]
+        if i == 3:
+            b, e = b[:0], e[:0]
+        jobs.append(_shim.Job(L, rl, D, _shim.FLAG_NCC | _shim.FLAG_MSCC, fwd, rev, b, e))
+    _, _, b, e = random_case(70, 50000, rl, 10)
+    jobs.insert(2, _shim.Job(50000, rl, D, _shim.FLAG_AUTOCORR, None, None, b, e))
+    dev.set_option("async_h2d", 0)
+    sync = dev.prepare(jobs)
+    sync.execute()
+    want = sync.fetch()
+    sync.free()
+    k0 = jobs[0]
+    ref = cc_oracle.chrom_counts(k0.chrom_len, rl, D, k0.fwd_pos, k0.rev_pos, k0.map_begins, k0.map_ends)
+    for k in ref:
+        assert np.array_equal(np.asarray(want[0][k]), np.asarray(ref[k])), k
+    dev.set_option("h2d_groups", groups)
+    try:
+        dev.set_option("async_h2d", 1)
+        batch = dev.prepare(jobs)
+        for _ in range(2):                       # first execute is grouped, the second is not
+            batch.execute()
+            got = batch.fetch()
+            for a, w in zip(got, want):
+                assert sorted(a) == sorted(w)
+                for k in w:
+                    assert np.array_equal(np.asarray(a[k]), np.asarray(w[k])), k
+        batch.free()
+        dev.prepare(jobs).free()                 # never executed: free waits for the copy
+        dev.set_option("async_h2d", 0)
+        for a, w in zip(dev.run_batch(jobs), want):   # run_batch pipelines by itself
+            for k in w:
+                assert np.array_equal(np.asarray(a[k]), np.asarray(w[k])), k
+    finally:
+        dev.set_option("async_h2d", 0)
+        dev.set_option("h2d_groups", 3)
+
+
 # ----------------------------------------------------------------- the reference's own pins
 def test_fixture_golden_tables_through_the_calculator():
     """configs[0]: tests/data ChIP-seq fixture, -d 300 -q 10 -r 36, against tests/golden."""
