@@ -27,7 +27,9 @@ def stale():
     if not os.path.exists(OUT):
         return True
     t = os.path.getmtime(OUT)
-    return any(os.path.getmtime(os.path.join(CSRC, f)) > t for f in SOURCES + HEADERS)
+    # every header next to the sources counts (a stale library behind a changed .cuh is a silent lie)
+    deps = set(SOURCES + HEADERS) | {f for f in os.listdir(CSRC) if f.endswith((".cuh", ".cu", ".h"))}
+    return any(os.path.getmtime(os.path.join(CSRC, f)) > t for f in deps)
 
 
 def build(force=False, verbose=False):

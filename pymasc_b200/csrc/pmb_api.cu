@@ -4,6 +4,7 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <stdio.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include <algorithm>
@@ -72,7 +73,8 @@ struct JobPlan {
     // offsets (in uint32 words) into the batch's device buffers
     size_t in_fwd = 0, in_rev = 0, in_mb = 0, in_me = 0;
     size_t bits = 0;           // start of this job's arrays; each array_words long
-    size_t bits_d = 0;         // event path: start of the derived Er|Or array (after all F/R/M)
+    size_t bits_m = 0;         // event path: start of M (after all F/R)
+    size_t bits_d = 0;         // event path: start of the derived Er|Or array (after all M)
     size_t array_words = 0;    // 2H + Wpad
 };
 
@@ -102,7 +104,10 @@ struct pmb_batch {
     EventJob* d_evjobs = nullptr;
     uint32_t ev_total_tiles = 0, ev_tile_words = 0;
     bool any_ncc = false, any_mscc = false, any_autocorr = false;
-    size_t zero_words = 0;              // event path: [0, zero_words) of d_bits = all jobs' F, R, M
+    size_t zero_words = 0;              // event path: [0, zero_words) of d_bits is zeroed per execute
+    size_t m_begin = 0, m_end = 0;      // event path: the M arrays of all jobs, [m_begin, m_end) of d_bits
+    bool gather_m = false;              // M is gathered (mask_build_multi_kernel), not scattered
+    uint32_t gather_k = 1;              // look-ahead quads of the gather
     void* d_tasks = nullptr;            // batched build: task tables + prefix sums (one allocation)
     ScatterTask* d_scatter = nullptr; uint64_t* d_scatter_prefix = nullptr; uint32_t n_scatter = 0; uint64_t scatter_items = 0;
     FillTask* d_fill = nullptr; uint64_t* d_fill_prefix = nullptr; uint32_t n_fill = 0; uint64_t fill_items = 0;
@@ -119,6 +124,19 @@ struct pmb_batch {
     };
     std::vector<Group> groups;
     bool h2d_pending = false;           // the first execute has to wait for the groups' events
+    // word range of the M arrays of jobs [lo, hi) (they are laid out in job order)
+    size_t jobs_m_lo(uint32_t lo, uint32_t hi) const
+    {
+        for (uint32_t i = lo; i < hi; i++)
+            if (jobs[i].autocorr || (jobs[i].mode & MODE_MSCC)) return jobs[i].bits_m;
+        return 0;
+    }
+    size_t jobs_m_hi(uint32_t lo, uint32_t hi) const
+    {
+        for (uint32_t i = hi; i > lo; i--)
+            if (jobs[i - 1].autocorr || (jobs[i - 1].mode & MODE_MSCC)) return jobs[i - 1].bits_m + jobs[i - 1].array_words;
+        return 0;
+    }
 };
 
 // ------------------------------------------------------------------ context
@@ -397,14 +415,14 @@ static int plan_events(pmb_ctx* c, pmb_batch* b)
         auto arr = [&](int slot) { return base + (size_t)slot * j.array_words; };
         EventJob e{};
         if (j.autocorr) {
-            e.M = arr(0);
+            e.M = b->d_bits + j.bits_m;
             e.flags = EVF_AUTOCORR;
             e.edge_off = 0;
         } else {
             e.F = arr(E_F); e.R = arr(E_R);
             e.flags = (j.mode & MODE_NCC ? EVF_NCC : 0) | (j.mode & MODE_MSCC ? EVF_MSCC : 0);
             if (j.mode & MODE_MSCC) {
-                e.M = arr(E_M);
+                e.M = b->d_bits + j.bits_m;
                 e.Er = b->d_bits + j.bits_d; e.Or = e.Er + j.array_words / 2;
             }
             e.edge_off = (int32_t)b->read_len - 1 - (int32_t)b->max_shift;
@@ -446,7 +464,7 @@ static int plan_events(pmb_ctx* c, pmb_batch* b)
                 if (j.a.n_fwd) { sc.push_back({arr(E_F), g, b->d_in + j.in_fwd, j.lo, j.hi, j.nbits}); scp.push_back(scp.back() + j.a.n_fwd); }
                 if (j.a.n_rev) { sc.push_back({arr(E_R), g, b->d_in + j.in_rev, NEG, POS, j.nbits}); scp.push_back(scp.back() + j.a.n_rev); }
             }
-            uint32_t* M = j.autocorr ? arr(0) : (mscc ? arr(E_M) : nullptr);
+            uint32_t* M = (j.autocorr || mscc) ? b->d_bits + j.bits_m : nullptr;
             if (!M) continue;
             if (j.a.n_intervals) {
                 fl.push_back({M, g, b->d_in + j.in_mb, b->d_in + j.in_me, 0, NEG, POS, j.nbits});
@@ -462,6 +480,10 @@ static int plan_events(pmb_ctx* c, pmb_batch* b)
             d.lag0 = j.autocorr ? 0 : (long long)b->read_len - 1;
             d.lag1 = j.autocorr ? 1 : (long long)b->read_len - 2;
             d.array_words = (uint32_t)j.array_words;
+            d.n_intervals = (uint32_t)j.a.n_intervals;
+            d.begins = b->d_in + j.in_mb;
+            d.ends = b->d_in + j.in_me;
+            d.p_off = g.origin_bit - g.halo_bits;
             dv.push_back(d);
             dvp.push_back(dvp.back() + (j.array_words / 4 + DERIVE_QUADS_PER_CTA - 1) / DERIVE_QUADS_PER_CTA);
         }
@@ -589,9 +611,8 @@ static int prepare_impl(pmb_ctx* c, const pmb_chrom_args* a, uint32_t n, pmb_bat
         j.body_words = (uint64_t)j.n_tiles * T;
         j.array_words = 2 * (size_t)b->halo_words + j.body_words;
         j.bits = bits_words;
-        if (b->path == 2) {     // F, R, M of all jobs first (one memset), the derived arrays after them
-            const size_t z = j.autocorr ? 1 : ((j.mode & MODE_MSCC) ? 3 : 2);
-            bits_words += z * j.array_words;
+        if (b->path == 2) {     // F, R of all jobs first (one memset), then all M, then the derived arrays
+            if (!j.autocorr) bits_words += 2 * j.array_words;
         } else {
             bits_words += (size_t)arrays_of(j) * j.array_words;
         }
@@ -601,9 +622,21 @@ static int prepare_impl(pmb_ctx* c, const pmb_chrom_args* a, uint32_t n, pmb_bat
     }
     b->in_words = in_words;
     if (b->path == 2) {
-        b->zero_words = bits_words;
+        b->m_begin = bits_words;
+        for (auto& j : b->jobs)
+            if (j.autocorr || (j.mode & MODE_MSCC)) { j.bits_m = bits_words; bits_words += j.array_words; }
+        b->m_end = bits_words;
         for (auto& j : b->jobs)
             if (!j.autocorr && (j.mode & MODE_MSCC)) { j.bits_d = bits_words; bits_words += j.array_words; }
+        // M is gathered from the sorted intervals unless the direct lags reach further than the
+        // gather's look-ahead (reads longer than ~900 bp); then it is scattered into zeroed memory
+        const uint32_t qmax = b->read_len > 0 ? (b->read_len - 1) >> 5 : 0;
+        b->gather_k = (qmax + 4) >> 2;
+        b->gather_m = b->gather_k <= 8 && b->read_len >= 2;   // rl 1: the second lag is negative
+        for (auto& j : b->jobs)
+            if (j.a.n_intervals >= (1ull << 31)) b->gather_m = false;
+        if (getenv("PMB_NO_GATHER")) b->gather_m = false;     // debug aid: always scatter M
+        b->zero_words = b->gather_m ? b->m_begin : b->m_end;
     }
     b->bits_words = bits_words;
     b->counter_words = (size_t)n * PMB_NCOUNTERS * b->stride + (size_t)n * 2;
@@ -681,7 +714,7 @@ static int prepare_impl(pmb_ctx* c, const pmb_chrom_args* a, uint32_t n, pmb_bat
     CU_TRY(c, cudaMemsetAsync(b->d_bits_raw, 0, (size_t)EV_PAD_WORDS * 4, c->stream));
     CU_TRY(c, cudaMemsetAsync(b->d_bits + std::max<size_t>(bits_words, 4), 0, (size_t)EV_PAD_WORDS * 4, c->stream));
     CU_TRY(c, cudaMallocAsync((void**)&b->d_counters, b->counter_words * 8, c->stream));
-    CU_TRY(c, cudaMallocAsync((void**)&b->d_err, 16, c->stream));
+    CU_TRY(c, cudaMallocAsync((void**)&b->d_err, 4 * (4 + 64), c->stream));
     uint64_t max_iv = 0;
     for (auto& j : b->jobs) max_iv = std::max<uint64_t>(max_iv, j.a.n_intervals);
     b->long_cap = (size_t)max_iv + 4;
@@ -746,14 +779,25 @@ static int execute_events(pmb_ctx* c, pmb_batch* b)
     cudaStream_t st = c->stream;
     uint32_t launches = 0;
     const size_t n = b->jobs.size();
+    // PMB_STAGE_TIMING=1: per-stage device times of the build on stderr (debug aid, adds a sync)
+    static const bool stage_timing = getenv("PMB_STAGE_TIMING") != nullptr;
+    cudaEvent_t sev[8] = {};
+    int n_sev = 0;
+    auto mark = [&]() {
+        if (!stage_timing || n_sev >= 8) return;
+        cudaEventCreate(&sev[n_sev]);
+        cudaEventRecord(sev[n_sev++], st);
+    };
 
     CU_TRY(c, cudaEventRecord(c->ev[0], st));
+    mark();
     // only the scattered / filled arrays need zeroing (F, R, M of all jobs come first);
     // Er and Or are written in full by derive_multi_kernel
     CU_TRY(c, cudaMemsetAsync(b->d_bits, 0, std::max<size_t>(b->zero_words, 4) * 4, st));
     CU_TRY(c, cudaMemsetAsync(b->d_counters, 0, b->counter_words * 8, st));
     CU_TRY(c, cudaMemsetAsync(b->d_aux, 0, b->aux_words * 8, st));
-    CU_TRY(c, cudaMemsetAsync(b->d_err, 0, 16, st));
+    CU_TRY(c, cudaMemsetAsync(b->d_err, 0, 4 * (4 + 64), st));
+    mark();
 
     auto blocks_for = [&](uint64_t items, int per_block) {
         uint64_t g = (items + per_block - 1) / per_block;
@@ -813,21 +857,48 @@ static int execute_events(pmb_ctx* c, pmb_batch* b)
                 b->d_scatter + G.sc_lo, b->d_scatter_prefix + G.sc_lo, G.sc_hi - G.sc_lo, b->d_err);
             launches++;
         }
+        if (!grouped) mark();
+        // M (+ Er, Or, direct lags).  Gather build: verify that the intervals are sorted and
+        // disjoint, then ONE pass writes everything; the scatter-style kernels stay in the stream
+        // behind it, gated on the "unsorted" flag (they return at once in the normal case).
+        int* gate = b->gather_m ? b->d_err + 4 + (grouped ? (int)pass : 0) : nullptr;   // per group: groups run concurrently
+        if (b->gather_m) {
+            if (G.fl_items) {
+                check_intervals_multi_kernel<<<blocks_for(G.fl_items, 256), 256, 0, ps>>>(
+                    b->d_fill + G.fl_lo, b->d_fill_prefix + G.fl_lo, G.fl_hi - G.fl_lo, b->d_err, gate);
+                launches++;
+            }
+            if (G.dv_ctas) {
+                mask_build_multi_kernel<<<(unsigned)G.dv_ctas, 256, 0, ps>>>(
+                    b->d_derive + G.dv_lo, b->d_derive_prefix + G.dv_lo, G.dv_hi - G.dv_lo,
+                    b->max_shift ? 2 : 1, b->gather_k, gate);
+                launches++;
+            }
+            if (G.dv_ctas && G.fl_items) {      // fallback: zero this group's M arrays first
+                const size_t m_lo = b->jobs_m_lo(G.job_lo, G.job_hi), m_hi = b->jobs_m_hi(G.job_lo, G.job_hi);
+                if (m_hi > m_lo) {
+                    zero_gated_kernel<<<c->num_sms * 8, 512, 0, ps>>>((uint4*)(b->d_bits + m_lo), (m_hi - m_lo) / 4, gate);
+                    launches++;
+                }
+            }
+        }
         if (G.fl_items) {
             CU_TRY(c, cudaMemsetAsync(long_count, 0, 4, ps));
             fill_multi_kernel<<<blocks_for(G.fl_items, 8), 256, 0, ps>>>(
                 b->d_fill + G.fl_lo, b->d_fill_prefix + G.fl_lo, G.fl_hi - G.fl_lo, b->d_err, long_list,
-                long_count);
-            fill_long_multi_kernel<<<c->num_sms * 4, 256, 0, ps>>>(b->d_fill + G.fl_lo, long_list, long_count);
+                long_count, gate);
+            fill_long_multi_kernel<<<c->num_sms * 4, 256, 0, ps>>>(b->d_fill + G.fl_lo, long_list, long_count, gate);
             launches += 2;
         }
-        if (G.dv_ctas) {
+        if (!grouped) mark();
+        if (G.dv_ctas && (!b->gather_m || G.fl_items)) {
             derive_multi_kernel<<<(unsigned)G.dv_ctas, 256, 0, ps>>>(
-                b->d_derive + G.dv_lo, b->d_derive_prefix + G.dv_lo, G.dv_hi - G.dv_lo, b->max_shift ? 2 : 1);
+                b->d_derive + G.dv_lo, b->d_derive_prefix + G.dv_lo, G.dv_hi - G.dv_lo, b->max_shift ? 2 : 1, gate);
             launches++;
         }
         CU_TRY(c, cudaGetLastError());
         if (!grouped) CU_TRY(c, cudaEventRecord(c->ev[1], st));
+        if (!grouped) mark();
 
         P.tile_lo = G.tile_lo;
         P.tile_hi = G.tile_hi;
@@ -850,6 +921,28 @@ static int execute_events(pmb_ctx* c, pmb_batch* b)
         CU_TRY(c, cudaEventRecord(c->evk[1], st));
     }
     b->h2d_pending = false;
+    if (n_sev > 1) {
+        cudaEventSynchronize(sev[n_sev - 1]);
+        static const char* names[] = {"memset", "scatter", "mask/fill", "derive", "?", "?", "?"};
+        fprintf(stderr, "[pmb stages]");
+        for (int i = 1; i < n_sev; i++) {
+            float ms = 0; cudaEventElapsedTime(&ms, sev[i - 1], sev[i]);
+            fprintf(stderr, " %s %.1f us", names[i - 1], ms * 1e3f);
+        }
+        fprintf(stderr, "\n");
+    }
+    for (int i = 0; i < n_sev; i++) cudaEventDestroy(sev[i]);
+    if (const char* dump = getenv("PMB_DUMP_ARRAYS")) {      // debug aid: job 0's F, R, M, Er|Or to a file
+        const JobPlan& j = b->jobs[0];
+        cudaStreamSynchronize(st);
+        std::vector<uint32_t> h(4 * j.array_words, 0u);
+        if (!j.autocorr) cudaMemcpy(h.data(), b->d_bits + j.bits, 2 * j.array_words * 4, cudaMemcpyDeviceToHost);
+        if (j.autocorr || (j.mode & MODE_MSCC))
+            cudaMemcpy(h.data() + 2 * j.array_words, b->d_bits + j.bits_m, j.array_words * 4, cudaMemcpyDeviceToHost);
+        if (!j.autocorr && (j.mode & MODE_MSCC))
+            cudaMemcpy(h.data() + 3 * j.array_words, b->d_bits + j.bits_d, j.array_words * 4, cudaMemcpyDeviceToHost);
+        if (FILE* f = fopen(dump, "wb")) { fwrite(h.data(), 4, h.size(), f); fclose(f); }
+    }
     if (b->any_mscc || b->any_autocorr) {
         finalize_dmp_kernel<<<(unsigned)n, 256, 0, st>>>(b->d_evjobs, (uint32_t)n, b->stride, b->max_shift);
         window_launches++;
@@ -881,7 +974,7 @@ extern "C" int pmb_batch_execute(pmb_ctx* c, pmb_batch* b)
     }
     CU_TRY(c, cudaMemsetAsync(b->d_bits, 0, std::max<size_t>(b->bits_words, 4) * 4, st));
     CU_TRY(c, cudaMemsetAsync(b->d_counters, 0, b->counter_words * 8, st));
-    CU_TRY(c, cudaMemsetAsync(b->d_err, 0, 16, st));
+    CU_TRY(c, cudaMemsetAsync(b->d_err, 0, 4 * (4 + 64), st));
     const size_t n = b->jobs.size();
     unsigned long long* d_totals = b->d_counters + n * PMB_NCOUNTERS * b->stride;
 

@@ -225,8 +225,10 @@ __global__ void scatter_multi_kernel(const ScatterTask* __restrict__ tasks, cons
 // long_list entries: (task << 32) | interval index
 __global__ void fill_multi_kernel(const FillTask* __restrict__ tasks, const uint64_t* __restrict__ prefix,
                                   uint32_t n_tasks, int* __restrict__ err_flag,
-                                  unsigned long long* __restrict__ long_list, uint32_t* __restrict__ long_count)
+                                  unsigned long long* __restrict__ long_list, uint32_t* __restrict__ long_count,
+                                  const int* __restrict__ gate)
 {
+    if (gate && !*gate) return;      // fallback of the gather build: runs only when the flag is set
     const int lane = threadIdx.x & 31;
     const uint64_t total = prefix[n_tasks];
     uint64_t warp = ((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
@@ -259,8 +261,10 @@ __global__ void fill_multi_kernel(const FillTask* __restrict__ tasks, const uint
 
 __global__ void fill_long_multi_kernel(const FillTask* __restrict__ tasks,
                                        const unsigned long long* __restrict__ long_list,
-                                       const uint32_t* __restrict__ long_count)
+                                       const uint32_t* __restrict__ long_count,
+                                       const int* __restrict__ gate)
 {
+    if (gate && !*gate) return;
     const uint32_t n = *long_count;
     const uint64_t tid = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
     const uint64_t nth = (uint64_t)gridDim.x * blockDim.x;
@@ -273,6 +277,15 @@ __global__ void fill_long_multi_kernel(const FillTask* __restrict__ tasks,
         const int64_t fw = a0 >> 5, lw = a1 >> 5;
         for (int64_t w = fw + 1 + (int64_t)tid; w < lw; w += (int64_t)nth) T.arr[w] = 0xFFFFFFFFu;
     }
+}
+
+// zero a word range (16-byte stores), only when *gate is set
+__global__ void zero_gated_kernel(uint4* __restrict__ p, size_t n16, const int* __restrict__ gate)
+{
+    if (gate && !*gate) return;
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const size_t stride = (size_t)gridDim.x * blockDim.x;
+    for (; i < n16; i += stride) p[i] = make_uint4(0u, 0u, 0u, 0u);
 }
 
 }  // namespace pmb

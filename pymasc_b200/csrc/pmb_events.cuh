@@ -514,6 +514,28 @@ __device__ __forceinline__ uint32_t compress_even(uint64_t x)
     return (uint32_t)x;
 }
 
+// Even bits of x in the low half, odd bits in the high half (outer perfect unshuffle,
+// Hacker's Delight 7-2; the byte-level step is one PRMT): 13 instructions for both halves.
+__device__ __forceinline__ uint32_t unshuffle16(uint32_t x)
+{
+    uint32_t t;
+    t = (x ^ (x >> 1)) & 0x22222222u; x ^= t ^ (t << 1);
+    t = (x ^ (x >> 2)) & 0x0C0C0C0Cu; x ^= t ^ (t << 2);
+    t = (x ^ (x >> 4)) & 0x00F000F0u; x ^= t ^ (t << 4);
+    return __byte_perm(x, 0u, 0x3120);
+}
+
+// Er / Or words of one quad of M (see derive_multi_kernel): even / odd bits, bit-reversed
+__device__ __forceinline__ void store_decimated(uint32_t* __restrict__ Er, uint32_t* __restrict__ Or, uint32_t at,
+                                                uint32_t m0, uint32_t m1, uint32_t m2, uint32_t m3)
+{
+    const uint32_t u0 = unshuffle16(m0), u1 = unshuffle16(m1), u2 = unshuffle16(m2), u3 = unshuffle16(m3);
+    *reinterpret_cast<uint2*>(Er + at) =
+        make_uint2(__brev(__byte_perm(u2, u3, 0x5410)), __brev(__byte_perm(u0, u1, 0x5410)));
+    *reinterpret_cast<uint2*>(Or + at) =
+        make_uint2(__brev(__byte_perm(u2, u3, 0x7632)), __brev(__byte_perm(u0, u1, 0x7632)));
+}
+
 __device__ __forceinline__ uint32_t load_or_zero(const uint32_t* __restrict__ M, long long w, long long W)
 {
     return (w >= 0 && w < W) ? __ldg(M + w) : 0u;
@@ -530,14 +552,19 @@ struct DeriveTask {
     long long a_lo, a_hi;
     long long lag0, lag1;
     uint32_t array_words;
-    uint32_t reserved;
+    uint32_t n_intervals;           // mask_build_multi_kernel only, like the three below
+    const uint32_t* begins;
+    const uint32_t* ends;
+    long long p_off;                // chromosome bit of array bit 0 (negative inside the left halo)
 };
 constexpr uint32_t DERIVE_QUADS_PER_CTA = 2048;
 
 __global__ void __launch_bounds__(256) derive_multi_kernel(const DeriveTask* __restrict__ tasks,
                                                            const uint64_t* __restrict__ cta_prefix,
-                                                           uint32_t n_tasks, int n_lags)
+                                                           uint32_t n_tasks, int n_lags,
+                                                           const int* __restrict__ gate)
 {
+    if (gate && !*gate) return;      // fallback of mask_build_multi_kernel
     // `tasks` / `cta_prefix` may point into the middle of the batch's tables (one group of jobs)
     const uint64_t cta = cta_prefix[0] + blockIdx.x;
     uint32_t lo_t = 0, hi_t = n_tasks;          // cta_prefix[lo_t] <= cta < cta_prefix[hi_t]
@@ -563,13 +590,7 @@ __global__ void __launch_bounds__(256) derive_multi_kernel(const DeriveTask* __r
         const uint32_t i = 4 * v;
         const uint4 m4 = *reinterpret_cast<const uint4*>(M + i);
         const uint32_t m[4] = {m4.x, m4.y, m4.z, m4.w};
-        if (Er) {
-            const uint64_t x0 = ((uint64_t)m[1] << 32) | m[0], x1 = ((uint64_t)m[3] << 32) | m[2];
-            const uint32_t at = pairs - 2 - (i >> 1);
-            *reinterpret_cast<uint2*>(Er + at) = make_uint2(__brev(compress_even(x1)), __brev(compress_even(x0)));
-            *reinterpret_cast<uint2*>(Or + at) =
-                make_uint2(__brev(compress_even(x1 >> 1)), __brev(compress_even(x0 >> 1)));
-        }
+        if (Er) store_decimated(Er, Or, pairs - 2 - (i >> 1), m[0], m[1], m[2], m[3]);
         // directly counted lags: sum_j Mc[j] M[j + lag]
         uint32_t mc[4];
         uint32_t any = 0;
@@ -598,6 +619,182 @@ __global__ void __launch_bounds__(256) derive_multi_kernel(const DeriveTask* __r
         c1 += __shfl_xor_sync(0xFFFFFFFFu, c1, o);
     }
     if ((threadIdx.x & 31) == 0) {
+        if (c0) atomicAdd(T.adirect, (unsigned long long)c0);
+        if (c1) atomicAdd(T.adirect + 1, (unsigned long long)c1);
+    }
+}
+
+// ---------------------------------------------------------------- mask build (gather)
+// M, Er, Or and the two direct lags in ONE pass, without memset, atomics or a second read of M.
+// BigWig intervals are sorted and disjoint (check_intervals_multi_kernel verifies it on the
+// device; otherwise the fill + derive kernels above run instead, gated on the same flag), so
+// M can be GATHERED: a warp owns 32 consecutive quads (4096 bits), finds the first interval
+// that reaches them (one binary search per warp, then a running cursor), loads the candidate
+// intervals 32 at a time (coalesced) and every lane ORs the candidates into its own quad.
+// The quads of one iteration are staged in shared memory so that a lane can read the words
+// `lag` bits above its own (the direct lags); the last K quads of an iteration only serve as
+// that look-ahead and are computed again by the next iteration, K = (max lag / 32 + 4) / 4.
+__device__ __forceinline__ uint32_t ones_from(int lo)      // bits [lo, 32), lo in [0, inf)
+{
+    return __funnelshift_lc(0u, 0xFFFFFFFFu, (uint32_t)lo);
+}
+__device__ __forceinline__ uint32_t ones_below(int hi)     // bits [0, hi), hi in (-inf, 32]
+{
+    return __funnelshift_rc(0xFFFFFFFFu, 0u, (uint32_t)(32 - hi));
+}
+
+__global__ void __launch_bounds__(256) check_intervals_multi_kernel(const FillTask* __restrict__ tasks,
+                                                                    const uint64_t* __restrict__ prefix,
+                                                                    uint32_t n_tasks, int* __restrict__ err_flag,
+                                                                    int* __restrict__ unsorted)
+{
+    // err_flag: an interval lies beyond the array (error, as in fill_multi_kernel)
+    // unsorted: begins / ends are not sorted and disjoint -> the gather is not valid
+    const uint64_t total = prefix[n_tasks];
+    uint64_t i = prefix[0] + (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+    for (; i < total; i += stride) {
+        const uint32_t t = find_task(prefix, n_tasks, i);
+        const FillTask& T = tasks[t];
+        const uint64_t k = i - prefix[t];
+        const uint32_t b = T.begins[k], e = T.ends[k];
+        if (e > b && (uint64_t)e >= T.nbits) atomicExch(err_flag, 1);
+        if (b > e) atomicExch(unsorted, 1);
+        if (i + 1 < prefix[t + 1] && e > T.begins[k + 1]) atomicExch(unsorted, 1);
+    }
+}
+
+__global__ void __launch_bounds__(256) mask_build_multi_kernel(const DeriveTask* __restrict__ tasks,
+                                                               const uint64_t* __restrict__ cta_prefix,
+                                                               uint32_t n_tasks, int n_lags, uint32_t K,
+                                                               const int* __restrict__ unsorted)
+{
+    if (*unsorted) return;                      // the scatter-style fallback builds M instead
+    __shared__ uint4 wbuf[8][32];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const uint64_t cta = cta_prefix[0] + blockIdx.x;
+    uint32_t lo_t = 0, hi_t = n_tasks;
+    while (hi_t - lo_t > 1) {
+        const uint32_t mid = (lo_t + hi_t) >> 1;
+        if (cta_prefix[mid] <= cta) lo_t = mid; else hi_t = mid;
+    }
+    const DeriveTask& T = tasks[lo_t];
+    uint32_t* __restrict__ M = const_cast<uint32_t*>(T.M);
+    uint32_t* __restrict__ Er = T.Er;
+    uint32_t* __restrict__ Or = T.Or;
+    const uint32_t* __restrict__ begins = T.begins;
+    const uint32_t* __restrict__ ends = T.ends;
+    const uint32_t nI = T.n_intervals;
+    const long long p_off = T.p_off;
+    const long long a_lo = T.a_lo, a_hi = T.a_hi;
+    const uint32_t quads = T.array_words >> 2;
+    const uint32_t pairs = T.array_words >> 1;
+    const uint32_t q0 = (uint32_t)(T.lag0 >> 5), q1 = (uint32_t)(T.lag1 >> 5);
+    const uint32_t s0 = (uint32_t)(T.lag0 & 31), s1 = (uint32_t)(T.lag1 & 31);
+    const uint32_t v_lo = (uint32_t)(cta - cta_prefix[lo_t]) * DERIVE_QUADS_PER_CTA;
+    const uint32_t v_hi = min(quads, v_lo + DERIVE_QUADS_PER_CTA);
+    const uint32_t per_warp = DERIVE_QUADS_PER_CTA / 8;
+    const uint32_t w_lo = v_lo + warp * per_warp;
+    const uint32_t w_hi = min(v_hi, w_lo + per_warp);
+    const uint32_t step = 32 - K;
+    const long long POS = 1ll << 40;
+    unsigned int c0 = 0, c1 = 0;
+
+    // first interval whose end reaches the warp's first bit: a 32-ary search (one coalesced
+    // probe per round, 3-4 rounds) instead of 17 dependent loads of a binary search
+    uint32_t idx = 0;                           // first interval the NEXT group may need
+    if (w_lo < w_hi) {
+        const long long P0 = (long long)w_lo * 128 + p_off;
+        uint32_t lo = 0, hi = nI;               // the answer lies in [lo, hi]
+        while (hi - lo >= 33) {
+            const uint32_t width = hi - lo;
+            const uint32_t pi = lo + (uint32_t)(((uint64_t)width * (lane + 1)) / 33);
+            const uint32_t cnt = __popc(__ballot_sync(0xFFFFFFFFu, (long long)ends[pi] < P0));   // a prefix
+            const uint32_t nlo = cnt ? lo + (uint32_t)(((uint64_t)width * cnt) / 33) + 1 : lo;
+            const uint32_t nhi = cnt < 32 ? lo + (uint32_t)(((uint64_t)width * (cnt + 1)) / 33) : hi;
+            lo = nlo; hi = nhi;
+        }
+        const uint32_t pi = lo + lane;
+        idx = lo + __popc(__ballot_sync(0xFFFFFFFFu, pi < hi && (long long)ends[pi] < P0));
+    }
+    bool have = false;                          // (cb, ce) hold the candidates c_loaded .. c_loaded+31
+    uint32_t c_loaded = 0;
+    long long cb = POS, ce = POS;
+    for (uint32_t base = w_lo; base < w_hi; base += step) {
+        const uint32_t v = base + lane;
+        const long long G_lo = (long long)base * 128 + p_off;      // chromosome bit of the group's bit 0
+        const long long G_next = G_lo + 128ll * step;              // ... of the next group's (they overlap by K quads)
+        uint32_t m0 = 0, m1 = 0, m2 = 0, m3 = 0;
+        // ~13 intervals reach a warp's 32768 bits: the batch in registers usually serves every group
+        uint32_t c = (have && idx >= c_loaded && idx < c_loaded + 32) ? c_loaded : idx;
+        bool front = true;                      // every candidate before c ends before G_next
+        for (;; c += 32) {
+            if (!have || c != c_loaded) {
+                const uint32_t ci = c + lane;
+                cb = POS; ce = POS;                                 // sentinels past the last interval
+                if (ci < nI) { cb = begins[ci]; ce = ends[ci]; }
+                have = true;
+                c_loaded = c;
+            }
+            // this lane's candidate as bit offsets into the group: bits [rb, re] (chromosome b+1 .. e)
+            const unsigned below = __ballot_sync(0xFFFFFFFFu, ce < G_lo);             // a prefix of the lanes
+            const unsigned beyond = __ballot_sync(0xFFFFFFFFu, cb + 1 >= G_lo + 4096);  // a suffix
+            if (front) {
+                const unsigned done = __ballot_sync(0xFFFFFFFFu, ce < G_next);         // a prefix, too
+                idx = c + __popc(done);
+                front = (done == 0xFFFFFFFFu);
+            }
+            const int rb = (int)max(cb + 1 - G_lo, 0ll), re = (int)min(ce - G_lo, 4095ll);
+            unsigned live = ~below & ~beyond;
+            while (live) {
+                const int src = __ffs(live) - 1;
+                live &= live - 1;
+                const int s = __shfl_sync(0xFFFFFFFFu, rb, src) - 128 * lane;   // relative to the quad
+                const int t = __shfl_sync(0xFFFFFFFFu, re, src) - 128 * lane;
+                if (s <= t && t >= 0 && s <= 127) {
+                    m0 |= ones_from(max(s, 0)) & ones_below(min(t + 1, 32));
+                    m1 |= ones_from(max(s - 32, 0)) & ones_below(min(t + 1 - 32, 32));
+                    m2 |= ones_from(max(s - 64, 0)) & ones_below(min(t + 1 - 64, 32));
+                    m3 |= ones_from(max(s - 96, 0)) & ones_below(min(t + 1 - 96, 32));
+                }
+            }
+            if (beyond) break;                  // sentinels (past the last interval) count as beyond
+        }
+        if (v >= quads) m0 = m1 = m2 = m3 = 0;  // nothing exists past the array
+        __syncwarp();                           // the previous iteration's readers are done
+        wbuf[warp][lane] = make_uint4(m0, m1, m2, m3);
+        __syncwarp();
+        if (lane < (int)step && v < w_hi) {
+            const uint32_t i = 4 * v;
+            *reinterpret_cast<uint4*>(M + i) = make_uint4(m0, m1, m2, m3);
+            if (Er) store_decimated(Er, Or, pairs - 2 - (i >> 1), m0, m1, m2, m3);
+            uint32_t mc[4] = {m0, m1, m2, m3};
+            if ((long long)i * 32 < a_lo || (long long)(i + 4) * 32 > a_hi) {
+#pragma unroll
+                for (int t = 0; t < 4; ++t) mc[t] &= range_mask((long long)(i + t) * 32, a_lo, a_hi);
+            }
+            if (mc[0] | mc[1] | mc[2] | mc[3]) {
+                const uint32_t* wl = reinterpret_cast<const uint32_t*>(wbuf[warp]) + 4 * lane;
+                uint32_t n0[5], n1[5];
+#pragma unroll
+                for (int t = 0; t < 5; ++t) n0[t] = wl[q0 + t];
+                if (n_lags > 1) {
+#pragma unroll
+                    for (int t = 0; t < 5; ++t) n1[t] = (q1 == q0) ? n0[t] : wl[q1 + t];
+                }
+#pragma unroll
+                for (int t = 0; t < 4; ++t) {
+                    c0 += __popc(mc[t] & __funnelshift_r(n0[t], n0[t + 1], s0));
+                    if (n_lags > 1) c1 += __popc(mc[t] & __funnelshift_r(n1[t], n1[t + 1], s1));
+                }
+            }
+        }
+    }
+    for (int o = 16; o; o >>= 1) {
+        c0 += __shfl_xor_sync(0xFFFFFFFFu, c0, o);
+        c1 += __shfl_xor_sync(0xFFFFFFFFu, c1, o);
+    }
+    if (lane == 0) {
         if (c0) atomicAdd(T.adirect, (unsigned long long)c0);
         if (c1) atomicAdd(T.adirect + 1, (unsigned long long)c1);
     }

@@ -180,6 +180,54 @@ def test_prepare_execute_fetch_is_repeatable(dev):
     batch.free()
 
 
+def test_mappability_gather_and_its_fallback(dev):
+    """Event path: M is gathered from sorted, disjoint intervals in one pass; anything else
+    (overlaps, unsorted, end < begin) takes the scatter-style kernels behind the device-side
+    check.  Both must give bit_array_set_region's result (bit_array.c:423-479)."""
+    L, rl, D = 120000, 36, 300
+    fwd, rev, b, e = random_case(80, L, rl, 8000)
+    u32 = lambda x: np.asarray(x, np.uint32)
+    # touching intervals, zero-length ones, a run of tiny ones (> 32 per 4096 bits), one huge
+    tb = np.arange(20000, 24000, 10, dtype=np.uint32)
+    sb = np.concatenate([u32([5, 100, 100, 300, 300]), tb, u32([30000, 119990])])
+    se = np.concatenate([u32([100, 100, 300, 300, 1000]), tb + 4, u32([110000, L + rl + D + 99])])
+    check_job(dev, L, rl, D, fwd, rev, sb, se)
+    check_job(dev, L, rl, D, fwd, rev, sb[:1], se[:1])
+    # overlapping, unsorted, and one with end < begin: the fallback
+    ob = u32([5000, 100, 4000, 90000, 70000, 800])
+    oe = u32([9000, 6000, 4500, 95000, 93000, 700])
+    check_job(dev, L, rl, D, fwd, rev, ob, oe)
+    check_job(dev, L, rl, D, fwd, rev, b[::-1].copy(), e[::-1].copy())
+    # sharded ranges use the same build
+    check_job(dev, L, rl, D, fwd, rev, sb, se, lo=30016, hi=90000)
+    check_job(dev, L, rl, D, fwd, rev, ob, oe, lo=30016, hi=90000)
+    # in one batch: a sorted job next to an unsorted one (the flag is per group, not per job)
+    jobs = [_shim.Job(L, rl, D, 3, fwd, rev, sb, se), _shim.Job(L, rl, D, 3, fwd, rev, ob, oe),
+            _shim.Job(L, rl, D, _shim.FLAG_AUTOCORR, None, None, ob, oe),
+            _shim.Job(L, rl, D, _shim.FLAG_AUTOCORR, None, None, sb, se)]
+    wants = [cc_oracle.chrom_counts(L, rl, D, fwd, rev, sb, se), cc_oracle.chrom_counts(L, rl, D, fwd, rev, ob, oe),
+             {"dmp": cc_oracle.mappable_autocorr(L, rl, D, ob, oe)}, {"dmp": cc_oracle.mappable_autocorr(L, rl, D, sb, se)}]
+    try:
+        dev.set_option("path", 2)
+        for groups in (1, 4):
+            dev.set_option("h2d_groups", groups)
+            for got, want in zip(dev.run_batch(jobs), wants):
+                for k in want:
+                    assert np.array_equal(np.asarray(got[k]), np.asarray(want[k])), (k, groups)
+    finally:
+        dev.set_option("path", 0)
+        dev.set_option("h2d_groups", 3)
+
+
+@pytest.mark.parametrize("rl", [1, 32, 33, 129, 300, 1000, 1200])
+def test_read_lengths_and_the_direct_lags(dev, rl):
+    """The two directly counted lags (rl-1, rl-2) reach 1 .. 8 look-ahead quads of the gather;
+    past that (rl 1200) the build falls back to fill + derive."""
+    L, D = 90000, 200
+    fwd, rev, b, e = random_case(90 + rl, L, rl, 3000)
+    check_job(dev, L, rl, D, fwd, rev, b, e)
+
+
 @pytest.mark.parametrize("groups", [1, 2, 3, 7])
 def test_pipelined_input_copy_gives_the_same_counts(pdev, groups):
     """pmb_run_batch / async prepare: the H2D runs on a copy stream in groups of chromosomes and
