@@ -791,12 +791,18 @@ static int execute_events(pmb_ctx* c, pmb_batch* b)
 
     CU_TRY(c, cudaEventRecord(c->ev[0], st));
     mark();
-    // only the scattered / filled arrays need zeroing (F, R, M of all jobs come first);
-    // Er and Or are written in full by derive_multi_kernel
-    CU_TRY(c, cudaMemsetAsync(b->d_bits, 0, std::max<size_t>(b->zero_words, 4) * 4, st));
-    CU_TRY(c, cudaMemsetAsync(b->d_counters, 0, b->counter_words * 8, st));
-    CU_TRY(c, cudaMemsetAsync(b->d_aux, 0, b->aux_words * 8, st));
-    CU_TRY(c, cudaMemsetAsync(b->d_err, 0, 4 * (4 + 64), st));
+    // only the scattered arrays need zeroing (F, R of all jobs come first; M too when it is not
+    // gathered); M, Er and Or are written in full by mask_build_multi_kernel.  One launch also
+    // clears the counters, the edge sums and the flags.
+    {
+        ZeroSegs z{};
+        z.p[0] = (uint4*)b->d_bits;      z.n16[0] = b->zero_words / 4;
+        z.p[1] = (uint4*)b->d_counters;  z.n16[1] = b->counter_words * 8 / 16;
+        z.p[2] = (uint4*)b->d_aux;       z.n16[2] = b->aux_words * 8 / 16;
+        z.p[3] = (uint4*)b->d_err;       z.n16[3] = 4 * (4 + 64) / 16;
+        zero_segments_kernel<<<c->num_sms * 8, 512, 0, st>>>(z);
+        launches++;
+    }
     mark();
 
     auto blocks_for = [&](uint64_t items, int per_block) {

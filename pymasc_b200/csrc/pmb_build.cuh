@@ -279,6 +279,21 @@ __global__ void fill_long_multi_kernel(const FillTask* __restrict__ tasks,
     }
 }
 
+// Zero up to four buffers in one launch (16-byte stores): four cudaMemsetAsync calls cost
+// ~120 us of mostly launch gaps per execute, one grid-stride pass over the same bytes ~35 us.
+struct ZeroSegs {
+    uint4* p[4];
+    size_t n16[4];      // 16-byte units
+};
+__global__ void zero_segments_kernel(ZeroSegs z)
+{
+    const size_t tid = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const size_t stride = (size_t)gridDim.x * blockDim.x;
+#pragma unroll
+    for (int s = 0; s < 4; ++s)
+        for (size_t i = tid; i < z.n16[s]; i += stride) z.p[s][i] = make_uint4(0u, 0u, 0u, 0u);
+}
+
 // zero a word range (16-byte stores), only when *gate is set
 __global__ void zero_gated_kernel(uint4* __restrict__ p, size_t n16, const int* __restrict__ gate)
 {

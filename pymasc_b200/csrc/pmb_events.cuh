@@ -156,6 +156,26 @@ struct Slices {
             default: add_case<6>(x, hist, lane); break;
         }
     }
+    // The same, with the window words produced by `compute(x)`.  The trailing zeros of m are
+    // tested bit by bit (half of all events stop at the first test and just park x in pend[0];
+    // the jump-table dispatch of a switch costs ~18 instructions for every event).
+    template <class F>
+    __device__ __forceinline__ void add_with(uint32_t* hist, int lane, F&& compute)
+    {
+        static_assert(EV_LEVELS == 6, "the chain below lists the cases of 6 levels");
+        ++m;
+        uint32_t x[NC];
+        compute(x);
+        if (m & 1u) {
+#pragma unroll
+            for (int n = 0; n < NC; ++n) pend[n][0] = x[n];
+        } else if (m & 2u) add_case<1>(x, hist, lane);
+        else if (m & 4u) add_case<2>(x, hist, lane);
+        else if (m & 8u) add_case<3>(x, hist, lane);
+        else if (m & 16u) add_case<4>(x, hist, lane);
+        else if (m & 32u) add_case<5>(x, hist, lane);
+        else add_case<6>(x, hist, lane);
+    }
     __device__ __forceinline__ void flush(uint32_t* hist, int lane)
     {
 #pragma unroll
@@ -247,7 +267,9 @@ __global__ void __launch_bounds__(32 * EV_WARPS) event_window_kernel(const Event
     uint32_t* stage_all = hist + NC * 32 * EV_HIST_STRIDE;                  // [EV_WARPS][2][STAGE]
 
     const int lane = threadIdx.x & 31;
-    const int warp = threadIdx.x >> 5;
+    // read through a shuffle so the compiler KNOWS it is warp-uniform: the tile loops, the event
+    // count and the carry-save dispatch then compile to uniform branches (BRA.U, no BSSY/BSYNC)
+    const int warp = __shfl_sync(0xFFFFFFFFu, (int)(threadIdx.x >> 5), 0);
 
     const uint32_t n_launch_tiles = P.tile_hi - P.tile_lo;
     const uint32_t t_lo = P.tile_lo + (uint32_t)(((uint64_t)n_launch_tiles * blockIdx.x) / gridDim.x);
@@ -451,15 +473,17 @@ __global__ void __launch_bounds__(32 * EV_WARPS) event_window_kernel(const Event
                     else e1 = ecur & (ecur - 1);
                     const uint32_t eo = 32u * src + bit;          // event offset inside the group
                     if constexpr (KIND == EV_FWD) {
-                        uint32_t x[3] = {0u, 0u, 0u};
-                        const uint32_t w1 = span_word(sp0, eo, lane) & col_mask;
-                        if (job_ncc) x[0] = w1;
-                        if (job_mscc && ((msrc >> bit) & 1u)) {          // M[p], warp-uniform
-                            const uint32_t w2 = span_word_rev(sp1, r0 + eo, lane) & col_mask;
-                            x[1] = w2;
-                            x[2] = w1 & w2;
-                        }
-                        sl.add(x, hist, lane);
+                        sl.add_with(hist, lane, [&](uint32_t (&x)[3]) {
+                            const uint32_t w1 = span_word(sp0, eo, lane) & col_mask;
+                            x[0] = job_ncc ? w1 : 0u;
+                            x[1] = 0u;
+                            x[2] = 0u;
+                            if (job_mscc && ((msrc >> bit) & 1u)) {          // M[p], warp-uniform
+                                const uint32_t w2 = span_word_rev(sp1, r0 + eo, lane) & col_mask;
+                                x[1] = w2;
+                                x[2] = w1 & w2;
+                            }
+                        });
                     } else if constexpr (KIND == EV_REV) {
                         uint32_t kmask = col_mask;
                         if (!full_rng) {  // shifts k with j = q - k inside the counted range
@@ -471,21 +495,21 @@ __global__ void __launch_bounds__(32 * EV_WARPS) event_window_kernel(const Event
                         }
                         const uint32_t tl = eo + (uint32_t)rl - 1u;              // (q + rl - 1) - G
                         const uint32_t* dec = (tl & 1u) ? sp2 : sp1;
-                        uint32_t x[1];
-                        const uint32_t w3 = span_word_rev(sp0, r0 + eo, lane);
-                        const uint32_t w4 = span_word(dec, r1 + (uint32_t)hmax - (tl >> 1), lane);
-                        x[0] = w3 & w4 & kmask;
-                        sl.add(x, hist, lane);
+                        sl.add_with(hist, lane, [&](uint32_t (&x)[1]) {
+                            const uint32_t w3 = span_word_rev(sp0, r0 + eo, lane);
+                            const uint32_t w4 = span_word(dec, r1 + (uint32_t)hmax - (tl >> 1), lane);
+                            x[0] = w3 & w4 & kmask;
+                        });
                     } else {
                         // run starts / ends of M inside the window: dM = M[a] - M[a-1]
-                        const uint32_t m1 = span_word(sp0, r0 + eo, lane);
-                        const uint32_t m0 = span_word(sp0, r0 + eo - 1u, lane);
-                        const uint32_t ws = m1 & ~m0 & col_mask;
-                        const uint32_t we = ~m1 & m0 & col_mask;
-                        uint32_t x[2];
-                        x[0] = is_end ? we : ws;     // start.start + end.end
-                        x[1] = is_end ? ws : we;     // start.end + end.start
-                        sl.add(x, hist, lane);
+                        sl.add_with(hist, lane, [&](uint32_t (&x)[2]) {
+                            const uint32_t m1 = span_word(sp0, r0 + eo, lane);
+                            const uint32_t m0 = span_word(sp0, r0 + eo - 1u, lane);
+                            const uint32_t ws = m1 & ~m0 & col_mask;
+                            const uint32_t we = ~m1 & m0 & col_mask;
+                            x[0] = is_end ? we : ws;     // start.start + end.end
+                            x[1] = is_end ? ws : we;     // start.end + end.start
+                        });
                     }
                 }
             }
