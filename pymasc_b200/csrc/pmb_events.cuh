@@ -164,12 +164,19 @@ struct Slices {
     {
         static_assert(EV_LEVELS == 6, "the chain below lists the cases of 6 levels");
         ++m;
-        uint32_t x[NC];
-        compute(x);
-        if (m & 1u) {
+        if (m & 1u) {           // the words are produced straight into the level-0 slots
+            uint32_t x[NC];
+            compute(x);
 #pragma unroll
             for (int n = 0; n < NC; ++n) pend[n][0] = x[n];
-        } else if (m & 2u) add_case<1>(x, hist, lane);
+            return;
+        }
+        // (compute is instantiated a second time here on purpose: with one shared copy the
+        // compiler computes x into pend[.][0]'s registers and pays 9 moves per event to save,
+        // clear and restore them around the carry-save cases)
+        uint32_t x[NC];
+        compute(x);
+        if (m & 2u) add_case<1>(x, hist, lane);
         else if (m & 4u) add_case<2>(x, hist, lane);
         else if (m & 8u) add_case<3>(x, hist, lane);
         else if (m & 16u) add_case<4>(x, hist, lane);
@@ -388,7 +395,12 @@ __global__ void __launch_bounds__(32 * EV_WARPS) event_window_kernel(const Event
         const EventJob& J = P.jobs[job];
         const uint32_t seg_hi = min(t_hi, J.tile_begin + J.n_tiles);
         if (!job_active(J)) { seg_lo = seg_hi; continue; }
-        const long long N = (long long)J.array_words * 32;
+        // the job's fields in registers: the mbarrier / TMA asm clobbers memory, so every J.x in
+        // the loops below would be a fresh global load
+        const uint32_t J_words = J.array_words, J_tile_begin = J.tile_begin;
+        const long long J_lo = J.a_lo, J_hi = J.a_hi;
+        const int J_edge_off = J.edge_off;
+        const long long N = (long long)J_words * 32;
         const bool job_ncc = NCC && (J.flags & EVF_NCC);
         const bool job_mscc = MSCC && (J.flags & EVF_MSCC);
         if (lane == 0) {
@@ -396,7 +408,12 @@ __global__ void __launch_bounds__(32 * EV_WARPS) event_window_kernel(const Event
             if (seg_lo + warp + EV_WARPS < seg_hi) request(seg_lo + warp + EV_WARPS, job, (itw + 1) & 1);
         }
       for (uint32_t t = seg_lo + warp; t < seg_hi; t += EV_WARPS, ++itw) {
-        const uint32_t g0 = (t - J.tile_begin) * EV_TILE;
+        const uint32_t g0 = (t - J_tile_begin) * EV_TILE;
+        // most tiles lie wholly inside the counted range: no clip masks then (64-bit compares)
+        const bool tile_inside = ((long long)g0 * 32 - 32 >= J_lo) && (((long long)g0 + EV_TILE) * 32 <= J_hi);
+        auto clip = [&](uint32_t word_index) -> uint32_t {
+            return tile_inside ? 0xFFFFFFFFu : range_mask((long long)word_index * 32, J_lo, J_hi);
+        };
         const int s = itw & 1;
         const uint32_t* st = stage0 + (size_t)s * STAGE;
         const long long ra = region_a(J, g0);
@@ -405,9 +422,9 @@ __global__ void __launch_bounds__(32 * EV_WARPS) event_window_kernel(const Event
 
         for (uint32_t gi = 0; gi < EV_TILE / 32; ++gi) {
             const uint32_t g = g0 + 32 * gi;
-            if (g >= J.array_words) break;
+            if (g >= J_words) break;
             const uint32_t i = g + lane;
-            const bool in = i < J.array_words;
+            const bool in = i < J_words;
             const long long G = (long long)g * 32;
             uint32_t ev = 0, ev2 = 0, mword = 0;     // ev: reads / run starts; ev2: run ends
             if (KIND == EV_FWD) {
@@ -416,15 +433,15 @@ __global__ void __launch_bounds__(32 * EV_WARPS) event_window_kernel(const Event
                     if (job_mscc) mword = st[EV_TILE + 32 * gi + lane];
                     if (P.col0 == 0) {
                         tot_f += __popc(ev);        // F is clipped to the counted range at build
-                        tot_r += __popc(st[2 * EV_TILE + 32 * gi + lane] & range_mask((long long)i * 32, J.a_lo, J.a_hi));
+                        tot_r += __popc(st[2 * EV_TILE + 32 * gi + lane] & clip(i));
                     }
                 }
             } else if (KIND == EV_REV) {
                 if (in) ev = st[32 * gi + lane];
             } else if (in) {
-                const uint32_t m = st[4 + 32 * gi + lane] & range_mask((long long)i * 32, J.a_lo, J.a_hi);
+                const uint32_t m = st[4 + 32 * gi + lane] & clip(i);
                 uint32_t prev = 0;
-                if (i > 0) prev = (st[3 + 32 * gi + lane] & range_mask((long long)(i - 1) * 32, J.a_lo, J.a_hi)) >> 31;
+                if (i > 0) prev = (st[3 + 32 * gi + lane] & clip(i - 1)) >> 31;
                 const uint32_t up = (m << 1) | prev;     // Mc[a-1]
                 ev = m & ~up;
                 ev2 = ~m & up;
@@ -443,8 +460,8 @@ __global__ void __launch_bounds__(32 * EV_WARPS) event_window_kernel(const Event
                 // lane 0's lowest bit of M[p+rl-1-k], k = 32 col0 .. +31, for the group's e = 0
                 r0 = (uint32_t)(G + rl - 32 - 32ll * P.col0 - 32 * ra);
             } else if constexpr (KIND == EV_REV) {
-                gl = G - J.a_lo;                // kmax = min(D, gl + e)
-                gh = G - J.a_hi + 1;            // kmin = max(0, gh + e)
+                gl = G - J_lo;                  // kmax = min(D, gl + e)
+                gh = G - J_hi + 1;              // kmin = max(0, gh + e)
                 if (gl + 1023 < 0 || gh > D) continue;          // no event of the group counts
                 full_rng = (gh + 1023 <= 0) && (gl >= D);
                 sp0 = st + EV_TILE;                                                 // M region
@@ -456,7 +473,7 @@ __global__ void __launch_bounds__(32 * EV_WARPS) event_window_kernel(const Event
             } else {
                 sp0 = st + EV_TILE + 4;                                             // M region
                 sp1 = sp0;
-                r0 = (uint32_t)(G + J.edge_off + 32ll * P.col0 - 32 * ra);          // window start, e = 0
+                r0 = (uint32_t)(G + J_edge_off + 32ll * P.col0 - 32 * ra);          // window start, e = 0
             }
 
             while (nz) {
