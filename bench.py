@@ -573,7 +573,7 @@ def main():
     ap.add_argument("--single-path", action="store_true", help="skip the cross-check pass of the other algorithm")
     ap.add_argument("--path", default="auto", choices=["auto", "dense", "events"],
                     help="device algorithm: dense shift-window kernel or event-window kernels")
-    ap.add_argument("--h2d-groups", type=int, default=3,
+    ap.add_argument("--h2d-groups", type=int, default=4,
                     help="e2e arm: chromosome groups whose H2D overlaps the kernels (0 = no overlap)")
     ap.add_argument("--opt", action="append", default=[], help="pmb_set_option name=value (tuning)")
     ap.add_argument("--no-cpu-baseline", action="store_true")

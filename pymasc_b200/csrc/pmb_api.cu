@@ -39,7 +39,8 @@ struct pmb_ctx {
     int event_tile_words = 0;
     int event_blocks_per_sm = 0;
     int async_h2d = 0;       // prepare returns before the input copy has finished (see header)
-    int h2d_groups = 3;      // event path: job groups whose build + kernels overlap the H2D of the next
+    int h2d_growth_x10 = 13; // size ratio of consecutive H2D groups, in tenths
+    int h2d_groups = 4;      // event path: job groups whose build + kernels overlap the H2D of the next
     cudaStream_t copy_stream = nullptr;
     cudaStream_t side_stream = nullptr;   // grouped execute: odd groups run here, so that one group's
                                           // kernel tails overlap the next group's build
@@ -122,6 +123,10 @@ struct pmb_batch {
         uint32_t tile_lo = 0, tile_hi = 0;
         cudaEvent_t done = nullptr;
     };
+    // host copies of the uploaded tables: they live as long as the batch, so prepare does not
+    // have to wait for their (stream-ordered) upload
+    std::vector<unsigned char> h_blob;
+    std::vector<EventJob> h_table;
     std::vector<Group> groups;
     bool h2d_pending = false;           // the first execute has to wait for the groups' events
     // word range of the M arrays of jobs [lo, hi) (they are laid out in job order)
@@ -262,6 +267,7 @@ extern "C" int pmb_set_option(pmb_ctx* c, const char* name, int64_t value)
     else if (!strcmp(name, "event_tile_words")) c->event_tile_words = (int)value;
     else if (!strcmp(name, "event_blocks_per_sm")) c->event_blocks_per_sm = (int)value;
     else if (!strcmp(name, "async_h2d")) c->async_h2d = value != 0;
+    else if (!strcmp(name, "h2d_growth_x10")) c->h2d_growth_x10 = (int)std::max<int64_t>(10, std::min<int64_t>(value, 100));
     else if (!strcmp(name, "h2d_groups")) c->h2d_groups = (int)std::max<int64_t>(1, std::min<int64_t>(value, 64));
     else { c->err = std::string("unknown option ") + name; return PMB_ERR_ARG; }
     return PMB_OK;
@@ -403,10 +409,11 @@ static int plan_events(pmb_ctx* c, pmb_batch* b)
     const size_t n = b->jobs.size();
     const uint32_t TW = EV_TILE;
     b->ev_tile_words = TW;
-    b->aux_words = n * (2 * (size_t)b->stride + 2);
+    b->aux_words = n * (2 * (size_t)b->stride + 4);      // edge sums, direct lags (scatter | gather build)
     CU_TRY(c, cudaMallocAsync((void**)&b->d_aux, b->aux_words * 8, c->stream));
     CU_TRY(c, cudaMallocAsync((void**)&b->d_evjobs, n * sizeof(EventJob), c->stream));
-    std::vector<EventJob> table(n);
+    std::vector<EventJob>& table = b->h_table;
+    table.assign(n, EventJob{});
     uint32_t tiles = 0;
     unsigned long long* adirect0 = b->d_aux + n * 2 * (size_t)b->stride;
     for (size_t i = 0; i < n; i++) {
@@ -430,6 +437,7 @@ static int plan_events(pmb_ctx* c, pmb_batch* b)
         e.counters = b->d_counters + i * PMB_NCOUNTERS * b->stride;
         e.aux = b->d_aux + i * 2 * (size_t)b->stride;
         e.adirect = adirect0 + 2 * i;
+        e.agather = adirect0 + 2 * n + 2 * i;
         e.totals = b->d_counters + n * PMB_NCOUNTERS * b->stride + 2 * i;
         const int64_t off = (int64_t)b->halo_words * 32 - j.origin_word * 32;   // chrom bit -> array bit
         e.a_lo = j.lo + off;
@@ -467,7 +475,13 @@ static int plan_events(pmb_ctx* c, pmb_batch* b)
             uint32_t* M = (j.autocorr || mscc) ? b->d_bits + j.bits_m : nullptr;
             if (!M) continue;
             if (j.a.n_intervals) {
-                fl.push_back({M, g, b->d_in + j.in_mb, b->d_in + j.in_me, 0, NEG, POS, j.nbits});
+                FillTask f{M, g, b->d_in + j.in_mb, b->d_in + j.in_me, 0, NEG, POS, j.nbits};
+                f.c_lo = j.lo; f.c_hi = j.hi;
+                f.p_lo = g.origin_bit - g.halo_bits; f.p_hi = f.p_lo + g.total_bits;
+                f.lag0 = j.autocorr ? 0 : (long long)b->read_len - 1;
+                f.lag1 = j.autocorr ? 1 : (long long)b->read_len - 2;
+                f.agather = adir0 + 2 * n + 2 * i;
+                fl.push_back(f);
                 flp.push_back(flp.back() + j.a.n_intervals);
             }
             DeriveTask d{};
@@ -492,6 +506,7 @@ static int plan_events(pmb_ctx* c, pmb_batch* b)
             gr.sc_lo = sc_at[gr.job_lo]; gr.sc_hi = sc_at[gr.job_hi]; gr.sc_items = scp[gr.sc_hi] - scp[gr.sc_lo];
             gr.fl_lo = fl_at[gr.job_lo]; gr.fl_hi = fl_at[gr.job_hi]; gr.fl_items = flp[gr.fl_hi] - flp[gr.fl_lo];
             gr.dv_lo = dv_at[gr.job_lo]; gr.dv_hi = dv_at[gr.job_hi]; gr.dv_ctas = dvp[gr.dv_hi] - dvp[gr.dv_lo];
+            for (uint32_t q = gr.job_lo; q < gr.job_hi; q++) table[q].gate_index = (uint32_t)(&gr - b->groups.data());
             gr.tile_lo = table[gr.job_lo].tile_begin;
             gr.tile_hi = table[gr.job_hi - 1].tile_begin + table[gr.job_hi - 1].n_tiles;
         }
@@ -503,7 +518,8 @@ static int plan_events(pmb_ctx* c, pmb_batch* b)
         const size_t o_fl = o_scp + bytes8(scp.size() * 8), o_flp = o_fl + bytes8(fl.size() * sizeof(FillTask));
         const size_t o_dv = o_flp + bytes8(flp.size() * 8), o_dvp = o_dv + bytes8(dv.size() * sizeof(DeriveTask));
         const size_t total = o_dvp + bytes8(dvp.size() * 8);
-        std::vector<unsigned char> blob(total, 0);
+        std::vector<unsigned char>& blob = b->h_blob;
+        blob.assign(total, 0);
         if (!sc.empty()) memcpy(blob.data() + o_sc, sc.data(), sc.size() * sizeof(ScatterTask));
         memcpy(blob.data() + o_scp, scp.data(), scp.size() * 8);
         if (!fl.empty()) memcpy(blob.data() + o_fl, fl.data(), fl.size() * sizeof(FillTask));
@@ -517,11 +533,9 @@ static int plan_events(pmb_ctx* c, pmb_batch* b)
         b->d_fill = (FillTask*)(d + o_fl); b->d_fill_prefix = (uint64_t*)(d + o_flp);
         b->d_derive = (DeriveTask*)(d + o_dv); b->d_derive_prefix = (uint64_t*)(d + o_dvp);
         CU_TRY(c, cudaMallocAsync((void**)&b->d_long64, 2 * (b->fill_items + 1) * 8, c->stream));   // main | side
-        CU_TRY(c, cudaStreamSynchronize(c->stream));   // `blob` is a local
     }
     CU_TRY(c, cudaMemcpyAsync(b->d_evjobs, table.data(), n * sizeof(EventJob), cudaMemcpyHostToDevice,
                               c->stream));
-    CU_TRY(c, cudaStreamSynchronize(c->stream));   // `table` is a local
     return PMB_OK;
 }
 
@@ -628,11 +642,9 @@ static int prepare_impl(pmb_ctx* c, const pmb_chrom_args* a, uint32_t n, pmb_bat
         b->m_end = bits_words;
         for (auto& j : b->jobs)
             if (!j.autocorr && (j.mode & MODE_MSCC)) { j.bits_d = bits_words; bits_words += j.array_words; }
-        // M is gathered from the sorted intervals unless the direct lags reach further than the
-        // gather's look-ahead (reads longer than ~900 bp); then it is scattered into zeroed memory
-        const uint32_t qmax = b->read_len > 0 ? (b->read_len - 1) >> 5 : 0;
-        b->gather_k = (qmax + 4) >> 2;
-        b->gather_m = b->gather_k <= 8 && b->read_len >= 2;   // rl 1: the second lag is negative
+        // M is gathered from the sorted intervals (the scatter kernels stay as the fallback)
+        b->gather_k = 0;
+        b->gather_m = b->read_len >= 2;   // rl 1: the second lag is negative
         for (auto& j : b->jobs)
             if (j.a.n_intervals >= (1ull << 31)) b->gather_m = false;
         if (getenv("PMB_NO_GATHER")) b->gather_m = false;     // debug aid: always scatter M
@@ -657,9 +669,9 @@ static int prepare_impl(pmb_ctx* c, const pmb_chrom_args* a, uint32_t n, pmb_bat
         size_t total = 0, acc = 0;
         for (size_t w : job_words) total += w;
         // Group sizes grow geometrically: the first group is small so the kernels start early,
-        // and each later group may be larger because computing on a group takes ~2.4x as long
+        // and each later group may be larger because computing on a group takes ~2x as long
         // as copying it (so the copy of group g+1 hides behind the kernels of group g).
-        const double growth = 2.4;
+        const double growth = c->h2d_growth_x10 / 10.0;
         std::vector<double> cum(want, 1.0);
         {
             double sum = 0, w = 1;
@@ -729,7 +741,7 @@ static int prepare_impl(pmb_ctx* c, const pmb_chrom_args* a, uint32_t n, pmb_bat
     }
     // synchronous mode: host arrays may be released by the caller; asynchronous mode: they are
     // still being read by the copy engine until the first execute of this batch has completed
-    CU_TRY(c, cudaStreamSynchronize(c->stream));
+    if (!async || b->path != 2) CU_TRY(c, cudaStreamSynchronize(c->stream));
     guard.armed = false;
     *out = b;
     return PMB_OK;
@@ -871,13 +883,13 @@ static int execute_events(pmb_ctx* c, pmb_batch* b)
         if (b->gather_m) {
             if (G.fl_items) {
                 check_intervals_multi_kernel<<<blocks_for(G.fl_items, 256), 256, 0, ps>>>(
-                    b->d_fill + G.fl_lo, b->d_fill_prefix + G.fl_lo, G.fl_hi - G.fl_lo, b->d_err, gate);
+                    b->d_fill + G.fl_lo, b->d_fill_prefix + G.fl_lo, G.fl_hi - G.fl_lo, b->max_shift ? 2 : 1,
+                    b->d_err, gate);
                 launches++;
             }
             if (G.dv_ctas) {
                 mask_build_multi_kernel<<<(unsigned)G.dv_ctas, 256, 0, ps>>>(
-                    b->d_derive + G.dv_lo, b->d_derive_prefix + G.dv_lo, G.dv_hi - G.dv_lo,
-                    b->max_shift ? 2 : 1, b->gather_k, gate);
+                    b->d_derive + G.dv_lo, b->d_derive_prefix + G.dv_lo, G.dv_hi - G.dv_lo, gate);
                 launches++;
             }
             if (G.dv_ctas && G.fl_items) {      // fallback: zero this group's M arrays first
@@ -950,7 +962,8 @@ static int execute_events(pmb_ctx* c, pmb_batch* b)
         if (FILE* f = fopen(dump, "wb")) { fwrite(h.data(), 4, h.size(), f); fclose(f); }
     }
     if (b->any_mscc || b->any_autocorr) {
-        finalize_dmp_kernel<<<(unsigned)n, 256, 0, st>>>(b->d_evjobs, (uint32_t)n, b->stride, b->max_shift);
+        finalize_dmp_kernel<<<(unsigned)n, 256, 0, st>>>(b->d_evjobs, (uint32_t)n, b->stride, b->max_shift,
+                                                         b->gather_m ? b->d_err + 4 : nullptr, grouped ? 1 : 0);
         window_launches++;
     }
     CU_TRY(c, cudaGetLastError());

@@ -189,6 +189,11 @@ struct FillTask {
     const uint32_t* ends;
     int64_t shift_down, clip_lo, clip_hi;
     uint64_t nbits;
+    // check_intervals_multi_kernel only: the direct lags from the intervals themselves
+    int64_t c_lo, c_hi;             // counted range [c_lo, c_hi), chromosome bits
+    int64_t p_lo, p_hi;             // bits the array holds, [p_lo, p_hi)
+    int64_t lag0, lag1;
+    unsigned long long* agather;    // [2]
 };
 
 // index of the task whose [prefix[t], prefix[t+1]) holds item i (prefix has n_tasks + 1 entries)

@@ -59,7 +59,9 @@ struct EventJob {
     uint32_t tile_begin, n_tiles;
     int32_t edge_off;               // window start relative to an edge: rl-1-D, or 0 (autocorr)
     uint32_t flags;
-    uint32_t reserved;
+    uint32_t gate_index;            // H2D group of the job: which "unsorted" flag covers it
+    // gather build: the direct lags counted from the intervals (valid unless the flag is set)
+    const unsigned long long* agather;
 };
 
 struct EventParams {
@@ -666,15 +668,13 @@ __global__ void __launch_bounds__(256) derive_multi_kernel(const DeriveTask* __r
 }
 
 // ---------------------------------------------------------------- mask build (gather)
-// M, Er, Or and the two direct lags in ONE pass, without memset, atomics or a second read of M.
+// M, Er and Or in ONE pass, without memset, atomics or a second read of M.
 // BigWig intervals are sorted and disjoint (check_intervals_multi_kernel verifies it on the
 // device; otherwise the fill + derive kernels above run instead, gated on the same flag), so
 // M can be GATHERED: a warp owns 32 consecutive quads (4096 bits), finds the first interval
 // that reaches them (one binary search per warp, then a running cursor), loads the candidate
 // intervals 32 at a time (coalesced) and every lane ORs the candidates into its own quad.
-// The quads of one iteration are staged in shared memory so that a lane can read the words
-// `lag` bits above its own (the direct lags); the last K quads of an iteration only serve as
-// that look-ahead and are computed again by the next iteration, K = (max lag / 32 + 4) / 4.
+// The two directly counted lags come from the intervals themselves (check_intervals_multi_kernel).
 __device__ __forceinline__ uint32_t ones_from(int lo)      // bits [lo, 32), lo in [0, inf)
 {
     return __funnelshift_lc(0u, 0xFFFFFFFFu, (uint32_t)lo);
@@ -686,32 +686,74 @@ __device__ __forceinline__ uint32_t ones_below(int hi)     // bits [0, hi), hi i
 
 __global__ void __launch_bounds__(256) check_intervals_multi_kernel(const FillTask* __restrict__ tasks,
                                                                     const uint64_t* __restrict__ prefix,
-                                                                    uint32_t n_tasks, int* __restrict__ err_flag,
+                                                                    uint32_t n_tasks, int n_lags,
+                                                                    int* __restrict__ err_flag,
                                                                     int* __restrict__ unsorted)
 {
     // err_flag: an interval lies beyond the array (error, as in fill_multi_kernel)
     // unsorted: begins / ends are not sorted and disjoint -> the gather is not valid
+    // Also the two directly counted lags, sum_j Mc[j] M[j + lag], straight from the intervals:
+    // with disjoint sorted runs it is the overlap of run k (clipped to the counted range) with
+    // run k, k+1, ... moved down by `lag` -- a handful of integer operations per interval instead
+    // of a popcount pass over the whole array.  (Meaningless for unsorted input, and unused then.)
     const uint64_t total = prefix[n_tasks];
-    uint64_t i = prefix[0] + (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int lane = threadIdx.x & 31;
     const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
-    for (; i < total; i += stride) {
-        const uint32_t t = find_task(prefix, n_tasks, i);
+    // warp-uniform trip count: the lag sums are reduced over the warp before they go to memory
+    for (uint64_t wb = prefix[0] + (uint64_t)blockIdx.x * blockDim.x + (threadIdx.x & ~31u); wb < total; wb += stride) {
+        const uint64_t i = wb + lane;
+        const bool on = i < total;
+        const uint32_t t = find_task(prefix, n_tasks, on ? i : total - 1);
         const FillTask& T = tasks[t];
-        const uint64_t k = i - prefix[t];
-        const uint32_t b = T.begins[k], e = T.ends[k];
-        if (e > b && (uint64_t)e >= T.nbits) atomicExch(err_flag, 1);
-        if (b > e) atomicExch(unsorted, 1);
-        if (i + 1 < prefix[t + 1] && e > T.begins[k + 1]) atomicExch(unsorted, 1);
+        unsigned long long s0 = 0, s1 = 0;
+        if (on) {
+            const uint64_t k = i - prefix[t], n = prefix[t + 1] - prefix[t];
+            const uint32_t b = T.begins[k], e = T.ends[k];
+            if (e > b && (uint64_t)e >= T.nbits) atomicExch(err_flag, 1);
+            if (b > e) atomicExch(unsorted, 1);
+            if (k + 1 < n && e > T.begins[k + 1]) atomicExch(unsorted, 1);
+            // run k = chromosome bits b+1 .. e; its counted part A
+            const long long A_lo = max(max((long long)b + 1, (long long)T.c_lo), (long long)T.p_lo);
+            const long long A_hi = min(min((long long)e, (long long)T.c_hi - 1), (long long)T.p_hi - 1);
+            const long long L0 = T.lag0, L1 = T.lag1, Lmax = max(L0, L1);
+            long long prev = b;
+            int guard = 0;
+            for (uint64_t kk = k; kk < n && A_hi >= A_lo; ++kk) {
+                const long long bb = T.begins[kk], ee = T.ends[kk];
+                const long long B_lo = max(bb + 1, (long long)T.p_lo), B_hi = min(ee, (long long)T.p_hi - 1);
+                if (bb < prev || B_lo - Lmax > A_hi) break;
+                prev = bb;
+                if (++guard > 4096) { atomicExch(unsorted, 1); break; }   // absurd input: let the fallback count
+                if (B_hi < B_lo) continue;
+                const long long o0 = min(A_hi, B_hi - L0) - max(A_lo, B_lo - L0) + 1;
+                if (o0 > 0) s0 += (unsigned long long)o0;
+                const long long o1 = min(A_hi, B_hi - L1) - max(A_lo, B_lo - L1) + 1;
+                if (n_lags > 1 && o1 > 0) s1 += (unsigned long long)o1;
+            }
+        }
+        const uint32_t t0 = __shfl_sync(0xFFFFFFFFu, t, 0);
+        if (__all_sync(0xFFFFFFFFu, t == t0)) {         // one task in the warp: one atomic pair
+            for (int o = 16; o; o >>= 1) {
+                s0 += __shfl_xor_sync(0xFFFFFFFFu, s0, o);
+                s1 += __shfl_xor_sync(0xFFFFFFFFu, s1, o);
+            }
+            if (lane == 0) {
+                if (s0) atomicAdd(T.agather, s0);
+                if (s1) atomicAdd(T.agather + 1, s1);
+            }
+        } else {
+            if (s0) atomicAdd(T.agather, s0);
+            if (s1) atomicAdd(T.agather + 1, s1);
+        }
     }
 }
 
 __global__ void __launch_bounds__(256) mask_build_multi_kernel(const DeriveTask* __restrict__ tasks,
                                                                const uint64_t* __restrict__ cta_prefix,
-                                                               uint32_t n_tasks, int n_lags, uint32_t K,
+                                                               uint32_t n_tasks,
                                                                const int* __restrict__ unsorted)
 {
     if (*unsorted) return;                      // the scatter-style fallback builds M instead
-    __shared__ uint4 wbuf[8][32];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const uint64_t cta = cta_prefix[0] + blockIdx.x;
     uint32_t lo_t = 0, hi_t = n_tasks;
@@ -727,19 +769,15 @@ __global__ void __launch_bounds__(256) mask_build_multi_kernel(const DeriveTask*
     const uint32_t* __restrict__ ends = T.ends;
     const uint32_t nI = T.n_intervals;
     const long long p_off = T.p_off;
-    const long long a_lo = T.a_lo, a_hi = T.a_hi;
     const uint32_t quads = T.array_words >> 2;
     const uint32_t pairs = T.array_words >> 1;
-    const uint32_t q0 = (uint32_t)(T.lag0 >> 5), q1 = (uint32_t)(T.lag1 >> 5);
-    const uint32_t s0 = (uint32_t)(T.lag0 & 31), s1 = (uint32_t)(T.lag1 & 31);
     const uint32_t v_lo = (uint32_t)(cta - cta_prefix[lo_t]) * DERIVE_QUADS_PER_CTA;
     const uint32_t v_hi = min(quads, v_lo + DERIVE_QUADS_PER_CTA);
     const uint32_t per_warp = DERIVE_QUADS_PER_CTA / 8;
     const uint32_t w_lo = v_lo + warp * per_warp;
     const uint32_t w_hi = min(v_hi, w_lo + per_warp);
-    const uint32_t step = 32 - K;
+    const uint32_t step = 32;
     const long long POS = 1ll << 40;
-    unsigned int c0 = 0, c1 = 0;
 
     // first interval whose end reaches the warp's first bit: a 32-ary search (one coalesced
     // probe per round, 3-4 rounds) instead of 17 dependent loads of a binary search
@@ -764,7 +802,7 @@ __global__ void __launch_bounds__(256) mask_build_multi_kernel(const DeriveTask*
     for (uint32_t base = w_lo; base < w_hi; base += step) {
         const uint32_t v = base + lane;
         const long long G_lo = (long long)base * 128 + p_off;      // chromosome bit of the group's bit 0
-        const long long G_next = G_lo + 128ll * step;              // ... of the next group's (they overlap by K quads)
+        const long long G_next = G_lo + 128ll * step;              // ... of the next group's
         uint32_t m0 = 0, m1 = 0, m2 = 0, m3 = 0;
         // ~13 intervals reach a warp's 32768 bits: the batch in registers usually serves every group
         uint32_t c = (have && idx >= c_loaded && idx < c_loaded + 32) ? c_loaded : idx;
@@ -801,43 +839,11 @@ __global__ void __launch_bounds__(256) mask_build_multi_kernel(const DeriveTask*
             }
             if (beyond) break;                  // sentinels (past the last interval) count as beyond
         }
-        if (v >= quads) m0 = m1 = m2 = m3 = 0;  // nothing exists past the array
-        __syncwarp();                           // the previous iteration's readers are done
-        wbuf[warp][lane] = make_uint4(m0, m1, m2, m3);
-        __syncwarp();
-        if (lane < (int)step && v < w_hi) {
+        if (v < w_hi) {                         // (w_hi <= quads: nothing exists past the array)
             const uint32_t i = 4 * v;
             *reinterpret_cast<uint4*>(M + i) = make_uint4(m0, m1, m2, m3);
             if (Er) store_decimated(Er, Or, pairs - 2 - (i >> 1), m0, m1, m2, m3);
-            uint32_t mc[4] = {m0, m1, m2, m3};
-            if ((long long)i * 32 < a_lo || (long long)(i + 4) * 32 > a_hi) {
-#pragma unroll
-                for (int t = 0; t < 4; ++t) mc[t] &= range_mask((long long)(i + t) * 32, a_lo, a_hi);
-            }
-            if (mc[0] | mc[1] | mc[2] | mc[3]) {
-                const uint32_t* wl = reinterpret_cast<const uint32_t*>(wbuf[warp]) + 4 * lane;
-                uint32_t n0[5], n1[5];
-#pragma unroll
-                for (int t = 0; t < 5; ++t) n0[t] = wl[q0 + t];
-                if (n_lags > 1) {
-#pragma unroll
-                    for (int t = 0; t < 5; ++t) n1[t] = (q1 == q0) ? n0[t] : wl[q1 + t];
-                }
-#pragma unroll
-                for (int t = 0; t < 4; ++t) {
-                    c0 += __popc(mc[t] & __funnelshift_r(n0[t], n0[t + 1], s0));
-                    if (n_lags > 1) c1 += __popc(mc[t] & __funnelshift_r(n1[t], n1[t + 1], s1));
-                }
-            }
         }
-    }
-    for (int o = 16; o; o >>= 1) {
-        c0 += __shfl_xor_sync(0xFFFFFFFFu, c0, o);
-        c1 += __shfl_xor_sync(0xFFFFFFFFu, c1, o);
-    }
-    if (lane == 0) {
-        if (c0) atomicAdd(T.adirect, (unsigned long long)c0);
-        if (c1) atomicAdd(T.adirect + 1, (unsigned long long)c1);
     }
 }
 
@@ -866,7 +872,8 @@ __device__ __forceinline__ void block_scan_inplace(long long* a, uint32_t n, lon
 }
 
 __global__ void __launch_bounds__(256) finalize_dmp_kernel(const EventJob* __restrict__ jobs, uint32_t n_jobs,
-                                                           uint32_t stride, uint32_t max_shift)
+                                                           uint32_t stride, uint32_t max_shift,
+                                                           const int* __restrict__ gates, int per_group)
 {
     __shared__ long long part[256];
     const EventJob& J = jobs[blockIdx.x];
@@ -875,7 +882,10 @@ __global__ void __launch_bounds__(256) finalize_dmp_kernel(const EventJob* __res
     long long* out = (long long*)(J.counters + (size_t)C_DMP * stride);
     const long long* plus = (const long long*)J.aux;
     const long long* minus = plus + stride;
-    const long long a0 = (long long)J.adirect[0], a1 = (long long)J.adirect[1];
+    // gates: the gather build's "unsorted" flags (one per H2D group, or flag 0 for a whole-batch pass)
+    const bool gathered = gates && !gates[per_group ? J.gate_index : 0];
+    const long long a0 = (long long)(gathered ? J.agather[0] : J.adirect[0]);
+    const long long a1 = (long long)(gathered ? J.agather[1] : J.adirect[1]);
     if (max_shift == 0) { if (threadIdx.x == 0) out[0] = a0; return; }
     // out[0] = A0, out[1] = d[1] = A1 - A0, out[k+1] = -C[b(k)] for k = 1 .. max_shift-1
     for (uint32_t k = threadIdx.x; k <= max_shift; k += blockDim.x) {

@@ -216,7 +216,7 @@ def test_mappability_gather_and_its_fallback(dev):
                     assert np.array_equal(np.asarray(got[k]), np.asarray(want[k])), (k, groups)
     finally:
         dev.set_option("path", 0)
-        dev.set_option("h2d_groups", 3)
+        dev.set_option("h2d_groups", 4)
 
 
 @pytest.mark.parametrize("rl", [1, 32, 33, 129, 300, 1000, 1200])
@@ -273,7 +273,7 @@ def test_pipelined_input_copy_gives_the_same_counts(pdev, groups):
                 assert np.array_equal(np.asarray(a[k]), np.asarray(w[k])), k
     finally:
         dev.set_option("async_h2d", 0)
-        dev.set_option("h2d_groups", 3)
+        dev.set_option("h2d_groups", 4)
 
 
 # ----------------------------------------------------------------- the reference's own pins

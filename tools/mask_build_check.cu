@@ -1,4 +1,4 @@
-// Unit harness: mask_build_multi_kernel (gather) against fill_multi + derive_multi (scatter)
+// Unit harness: check_intervals + mask_build (gather build) against fill_multi + derive_multi (scatter)
 // on random sorted intervals, on poisoned buffers.  Prints the first differing words.
 // nvcc -gencode arch=compute_100a,code=sm_100a -O3 -std=c++17 -I pymasc_b200/csrc -o tools/mask_build_check.bin tools/mask_build_check.cu
 #include <cstdio>
@@ -58,6 +58,8 @@ int main(int argc, char** argv)
         CK(cudaMalloc(&d_flags, 64)); CK(cudaMemset(d_flags, 0, 64));
         Geometry g{0, (int64_t)halo * 32, (int64_t)W * 32};
         FillTask ft{d_M[0], g, d_b, d_e, 0, -(1ll << 40), (1ll << 40), nbits};
+        ft.c_lo = 0; ft.c_hi = (int64_t)nbits; ft.p_lo = -(int64_t)halo * 32; ft.p_hi = ft.p_lo + (int64_t)W * 32;
+        ft.lag0 = rl - 1; ft.lag1 = (int64_t)rl - 2; ft.agather = d_adir + 2;
         uint64_t fp[2] = {0, nI};
         DeriveTask dt[2];
         for (int v = 0; v < 2; v++) {
@@ -80,9 +82,9 @@ int main(int argc, char** argv)
         fill_long_multi_kernel<<<64, 256>>>(d_ft, d_long64, d_long, nullptr);
         derive_multi_kernel<<<(unsigned)ctas, 256>>>(d_dt, d_dp, 1, 2, nullptr);
         // gather
-        check_intervals_multi_kernel<<<64, 256>>>(d_ft, d_fp, 1, d_flags, d_flags + 1);
-        const uint32_t K = (((rl - 1) >> 5) + 4) >> 2;
-        mask_build_multi_kernel<<<(unsigned)ctas, 256>>>(d_dt + 1, d_dp, 1, 2, K, d_flags + 1);
+        check_intervals_multi_kernel<<<64, 256>>>(d_ft, d_fp, 1, 2, d_flags, d_flags + 1);
+        const uint32_t K = 0;
+        mask_build_multi_kernel<<<(unsigned)ctas, 256>>>(d_dt + 1, d_dp, 1, d_flags + 1);
         CK(cudaDeviceSynchronize());
         std::vector<uint32_t> M0(W), M1(W), D0(W), D1(W);
         unsigned long long adir[4]; int flags[2];
