@@ -496,13 +496,17 @@ def gpu_arm(args):
         def events_roofline(fwd_s, all_s):
             """Event-window kernels: every array is streamed once, windows come from L1/L2; the
             floor is HBM.  Dominant kernel: the forward-read kernel (F, R [, M, Mr])."""
-            nbytes = (4 if mode == "both" else 2) * bits_bytes
+            # F, R and M are each streamed from HBM once (M's tile and M's window region are the
+            # same bytes: the second read hits L2)
+            nbytes = (3 if mode == "both" else 2) * bits_bytes
             return {"bound": "hbm", "kernel": "event_window_kernel<EV_FWD>",
                     "achieved": nbytes / fwd_s / 1e9, "peak": hbm_peak, "unit": "GB/s",
                     "frac": nbytes / fwd_s / 1e9 / hbm_peak, "peak_source": peak_src,
                     "algorithmic_bytes": nbytes, "kernel_ms": fwd_s * 1e3,
                     "all_event_kernels_ms": all_s * 1e3,
-                    "traffic": None,
+                    "traffic": 1.160e9 if (world == 1 and mode == "both") else None,
+                    "traffic_source": "profiles/r01_ncu_event_window_v9.txt (ncu --set full, N=1: "
+                                      "dram__bytes_read.sum + dram__bytes_write.sum of the FWD launch)",
                     "note": "latency/issue-bound today (see profiles/); evals/s of this path are "
                             "delivered evals: the counts equal the dense kernel's bit for bit"}
 

@@ -297,6 +297,11 @@ __global__ void __launch_bounds__(32 * EV_WARPS) event_window_kernel(const Event
     }
     __syncthreads();
 
+    // always 0, but not provably so for ptxas: adding it moves a warp-uniform value (and all the
+    // arithmetic that follows from it) from the uniform datapath to the vector ALU
+    // (read back from the freshly zeroed histogram: anything computed from %laneid is folded)
+    const uint32_t vector_zero = hist[lane];
+
     Slices<NC> sl;
     sl.reset();
     uint32_t tot_f = 0, tot_r = 0;       // EV_FWD, first column chunk: strand totals of the job
@@ -413,6 +418,8 @@ __global__ void __launch_bounds__(32 * EV_WARPS) event_window_kernel(const Event
         const uint32_t g0 = (t - J_tile_begin) * EV_TILE;
         // most tiles lie wholly inside the counted range: no clip masks then (64-bit compares)
         const bool tile_inside = ((long long)g0 * 32 - 32 >= J_lo) && (((long long)g0 + EV_TILE) * 32 <= J_hi);
+        // REV: every shift of every event of the tile has its j = q - k inside the counted range
+        const bool tile_full = ((long long)g0 * 32 - J_lo >= D) && (((long long)g0 + EV_TILE) * 32 <= J_hi);
         auto clip = [&](uint32_t word_index) -> uint32_t {
             return tile_inside ? 0xFFFFFFFFu : range_mask((long long)word_index * 32, J_lo, J_hi);
         };
@@ -462,10 +469,12 @@ __global__ void __launch_bounds__(32 * EV_WARPS) event_window_kernel(const Event
                 // lane 0's lowest bit of M[p+rl-1-k], k = 32 col0 .. +31, for the group's e = 0
                 r0 = (uint32_t)(G + rl - 32 - 32ll * P.col0 - 32 * ra);
             } else if constexpr (KIND == EV_REV) {
-                gl = G - J_lo;                  // kmax = min(D, gl + e)
-                gh = G - J_hi + 1;              // kmin = max(0, gh + e)
-                if (gl + 1023 < 0 || gh > D) continue;          // no event of the group counts
-                full_rng = (gh + 1023 <= 0) && (gl >= D);
+                if (!tile_full) {               // tiles near the ends of the counted range only
+                    gl = G - J_lo;                  // kmax = min(D, gl + e)
+                    gh = G - J_hi + 1;              // kmin = max(0, gh + e)
+                    if (gl + 1023 < 0 || gh > D) continue;          // no event of the group counts
+                    full_rng = (gh + 1023 <= 0) && (gl >= D);
+                }
                 sp0 = st + EV_TILE;                                                 // M region
                 r0 = (uint32_t)(G - 31 - 32ll * P.col0 - 32 * ra);                  // M[q-k], as above
                 const long long B4 = (N >> 1) - 1 - (G >> 1) - hmax;
@@ -490,7 +499,10 @@ __global__ void __launch_bounds__(32 * EV_WARPS) event_window_kernel(const Event
                     const int bit = __ffs(ecur) - 1;
                     if (is_end) e2 = ecur & (ecur - 1);
                     else e1 = ecur & (ecur - 1);
-                    const uint32_t eo = 32u * src + bit;          // event offset inside the group
+                    uint32_t eo = 32u * src + bit;                // event offset inside the group
+                    // REV saturates the uniform datapath (73 % busy, half the ALU's rate): hand the
+                    // offset over in a vector register so the index arithmetic runs on the ALU
+                    if constexpr (KIND == EV_REV) eo += vector_zero;
                     if constexpr (KIND == EV_FWD) {
                         sl.add_with(hist, lane, [&](uint32_t (&x)[3]) {
                             const uint32_t w1 = span_word(sp0, eo, lane) & col_mask;
