@@ -108,6 +108,9 @@ struct pmb_batch {
     size_t zero_words = 0;              // event path: [0, zero_words) of d_bits is zeroed per execute
     size_t m_begin = 0, m_end = 0;      // event path: the M arrays of all jobs, [m_begin, m_end) of d_bits
     bool gather_m = false;              // M is gathered (mask_build_multi_kernel), not scattered
+    bool pack_reads = false;            // F, R are packed from the sorted reads (pack_reads_multi_kernel)
+    PackTask* d_pack = nullptr; uint64_t* d_pack_prefix = nullptr; uint32_t n_pack = 0; uint64_t pack_chunks = 0;
+    ZeroRun* d_runs = nullptr; size_t runs_cap = 0;     // main | side queue
     uint32_t gather_k = 1;              // look-ahead quads of the gather
     void* d_tasks = nullptr;            // batched build: task tables + prefix sums (one allocation)
     ScatterTask* d_scatter = nullptr; uint64_t* d_scatter_prefix = nullptr; uint32_t n_scatter = 0; uint64_t scatter_items = 0;
@@ -118,8 +121,9 @@ struct pmb_batch {
     // `done` is recorded behind them.  Task / tile ranges are those of the group's jobs.
     struct Group {
         uint32_t job_lo = 0, job_hi = 0;
-        uint32_t sc_lo = 0, sc_hi = 0, fl_lo = 0, fl_hi = 0, dv_lo = 0, dv_hi = 0;
-        uint64_t sc_items = 0, fl_items = 0, dv_ctas = 0;
+        uint32_t sc_lo = 0, sc_hi = 0, fl_lo = 0, fl_hi = 0, dv_lo = 0, dv_hi = 0, pk_lo = 0, pk_hi = 0;
+        uint64_t sc_items = 0, fl_items = 0, dv_ctas = 0, pk_chunks = 0;
+        size_t fr_lo = 0, fr_hi = 0;    // the group's F, R arrays: [fr_lo, fr_hi) of d_bits
         uint32_t tile_lo = 0, tile_hi = 0;
         cudaEvent_t done = nullptr;
     };
@@ -326,6 +330,7 @@ extern "C" void pmb_batch_free(pmb_ctx* c, pmb_batch* b)
         if (b->d_evjobs) cudaFreeAsync(b->d_evjobs, c->stream);
         if (b->d_tasks) cudaFreeAsync(b->d_tasks, c->stream);
         if (b->d_long64) cudaFreeAsync(b->d_long64, c->stream);
+        if (b->d_runs) cudaFreeAsync(b->d_runs, c->stream);
         cudaStreamSynchronize(c->stream);
     }
     delete b;
@@ -456,11 +461,14 @@ static int plan_events(pmb_ctx* c, pmb_batch* b)
         std::vector<ScatterTask> sc; std::vector<uint64_t> scp{0};
         std::vector<FillTask> fl; std::vector<uint64_t> flp{0};
         std::vector<DeriveTask> dv; std::vector<uint64_t> dvp{0};
+        std::vector<PackTask> pk; std::vector<uint64_t> pkp{0};
+        std::vector<uint32_t> pk_at(n + 1);
         unsigned long long* adir0 = b->d_aux + n * 2 * (size_t)b->stride;
         std::vector<uint32_t> sc_at(n + 1), fl_at(n + 1), dv_at(n + 1);
         for (size_t i = 0; i < n; i++) {
             JobPlan& j = b->jobs[i];
             sc_at[i] = (uint32_t)sc.size(); fl_at[i] = (uint32_t)fl.size(); dv_at[i] = (uint32_t)dv.size();
+            pk_at[i] = (uint32_t)pk.size();
             Geometry g;
             g.origin_bit = j.origin_word * 32;
             g.halo_bits = (int64_t)b->halo_words * 32;
@@ -471,6 +479,11 @@ static int plan_events(pmb_ctx* c, pmb_batch* b)
             if (!j.autocorr) {
                 if (j.a.n_fwd) { sc.push_back({arr(E_F), g, b->d_in + j.in_fwd, j.lo, j.hi, j.nbits}); scp.push_back(scp.back() + j.a.n_fwd); }
                 if (j.a.n_rev) { sc.push_back({arr(E_R), g, b->d_in + j.in_rev, NEG, POS, j.nbits}); scp.push_back(scp.back() + j.a.n_rev); }
+                // packed build: every F and R array is a task (an array without reads is all zeros)
+                pk.push_back({arr(E_F), g, b->d_in + j.in_fwd, j.a.n_fwd, j.lo, j.hi, j.nbits, (uint32_t)j.array_words, 0u});
+                pkp.push_back(pkp.back() + std::max<uint64_t>(1, (j.a.n_fwd + PACK_CHUNK - 1) / PACK_CHUNK));
+                pk.push_back({arr(E_R), g, b->d_in + j.in_rev, j.a.n_rev, NEG, POS, j.nbits, (uint32_t)j.array_words, 0u});
+                pkp.push_back(pkp.back() + std::max<uint64_t>(1, (j.a.n_rev + PACK_CHUNK - 1) / PACK_CHUNK));
             }
             uint32_t* M = (j.autocorr || mscc) ? b->d_bits + j.bits_m : nullptr;
             if (!M) continue;
@@ -502,10 +515,18 @@ static int plan_events(pmb_ctx* c, pmb_batch* b)
             dvp.push_back(dvp.back() + (j.array_words / 4 + DERIVE_QUADS_PER_CTA - 1) / DERIVE_QUADS_PER_CTA);
         }
         sc_at[n] = (uint32_t)sc.size(); fl_at[n] = (uint32_t)fl.size(); dv_at[n] = (uint32_t)dv.size();
+        pk_at[n] = (uint32_t)pk.size();
         for (auto& gr : b->groups) {
             gr.sc_lo = sc_at[gr.job_lo]; gr.sc_hi = sc_at[gr.job_hi]; gr.sc_items = scp[gr.sc_hi] - scp[gr.sc_lo];
             gr.fl_lo = fl_at[gr.job_lo]; gr.fl_hi = fl_at[gr.job_hi]; gr.fl_items = flp[gr.fl_hi] - flp[gr.fl_lo];
             gr.dv_lo = dv_at[gr.job_lo]; gr.dv_hi = dv_at[gr.job_hi]; gr.dv_ctas = dvp[gr.dv_hi] - dvp[gr.dv_lo];
+            gr.pk_lo = pk_at[gr.job_lo]; gr.pk_hi = pk_at[gr.job_hi]; gr.pk_chunks = pkp[gr.pk_hi] - pkp[gr.pk_lo];
+            gr.fr_lo = gr.fr_hi = 0;
+            for (uint32_t q = gr.job_lo; q < gr.job_hi; q++)
+                if (!b->jobs[q].autocorr) {
+                    if (gr.fr_hi == 0) gr.fr_lo = b->jobs[q].bits;
+                    gr.fr_hi = b->jobs[q].bits + 2 * b->jobs[q].array_words;
+                }
             for (uint32_t q = gr.job_lo; q < gr.job_hi; q++) table[q].gate_index = (uint32_t)(&gr - b->groups.data());
             gr.tile_lo = table[gr.job_lo].tile_begin;
             gr.tile_hi = table[gr.job_hi - 1].tile_begin + table[gr.job_hi - 1].n_tiles;
@@ -513,11 +534,13 @@ static int plan_events(pmb_ctx* c, pmb_batch* b)
         b->n_scatter = (uint32_t)sc.size(); b->scatter_items = scp.back();
         b->n_fill = (uint32_t)fl.size(); b->fill_items = flp.back();
         b->n_derive = (uint32_t)dv.size(); b->derive_ctas = dvp.back();
+        b->n_pack = (uint32_t)pk.size(); b->pack_chunks = pkp.back();
         auto bytes8 = [](size_t x) { return (x + 15) & ~(size_t)15; };
         const size_t o_sc = 0, o_scp = o_sc + bytes8(sc.size() * sizeof(ScatterTask));
         const size_t o_fl = o_scp + bytes8(scp.size() * 8), o_flp = o_fl + bytes8(fl.size() * sizeof(FillTask));
         const size_t o_dv = o_flp + bytes8(flp.size() * 8), o_dvp = o_dv + bytes8(dv.size() * sizeof(DeriveTask));
-        const size_t total = o_dvp + bytes8(dvp.size() * 8);
+        const size_t o_pk = o_dvp + bytes8(dvp.size() * 8), o_pkp = o_pk + bytes8(pk.size() * sizeof(PackTask));
+        const size_t total = o_pkp + bytes8(pkp.size() * 8);
         std::vector<unsigned char>& blob = b->h_blob;
         blob.assign(total, 0);
         if (!sc.empty()) memcpy(blob.data() + o_sc, sc.data(), sc.size() * sizeof(ScatterTask));
@@ -526,12 +549,17 @@ static int plan_events(pmb_ctx* c, pmb_batch* b)
         memcpy(blob.data() + o_flp, flp.data(), flp.size() * 8);
         if (!dv.empty()) memcpy(blob.data() + o_dv, dv.data(), dv.size() * sizeof(DeriveTask));
         memcpy(blob.data() + o_dvp, dvp.data(), dvp.size() * 8);
+        if (!pk.empty()) memcpy(blob.data() + o_pk, pk.data(), pk.size() * sizeof(PackTask));
+        memcpy(blob.data() + o_pkp, pkp.data(), pkp.size() * 8);
         CU_TRY(c, cudaMallocAsync(&b->d_tasks, total, c->stream));
         CU_TRY(c, cudaMemcpyAsync(b->d_tasks, blob.data(), total, cudaMemcpyHostToDevice, c->stream));
         unsigned char* d = (unsigned char*)b->d_tasks;
         b->d_scatter = (ScatterTask*)(d + o_sc); b->d_scatter_prefix = (uint64_t*)(d + o_scp);
         b->d_fill = (FillTask*)(d + o_fl); b->d_fill_prefix = (uint64_t*)(d + o_flp);
         b->d_derive = (DeriveTask*)(d + o_dv); b->d_derive_prefix = (uint64_t*)(d + o_dvp);
+        b->d_pack = (PackTask*)(d + o_pk); b->d_pack_prefix = (uint64_t*)(d + o_pkp);
+        b->runs_cap = b->m_begin / PACK_LONG_GAP + pk.size() + 16;
+        CU_TRY(c, cudaMallocAsync((void**)&b->d_runs, 2 * b->runs_cap * sizeof(ZeroRun), c->stream));
         CU_TRY(c, cudaMallocAsync((void**)&b->d_long64, 2 * (b->fill_items + 1) * 8, c->stream));   // main | side
     }
     CU_TRY(c, cudaMemcpyAsync(b->d_evjobs, table.data(), n * sizeof(EventJob), cudaMemcpyHostToDevice,
@@ -648,6 +676,7 @@ static int prepare_impl(pmb_ctx* c, const pmb_chrom_args* a, uint32_t n, pmb_bat
         for (auto& j : b->jobs)
             if (j.a.n_intervals >= (1ull << 31)) b->gather_m = false;
         if (getenv("PMB_NO_GATHER")) b->gather_m = false;     // debug aid: always scatter M
+        b->pack_reads = getenv("PMB_NO_PACK") == nullptr;      // debug aid: always scatter F, R
         b->zero_words = b->gather_m ? b->m_begin : b->m_end;
     }
     b->bits_words = bits_words;
@@ -726,7 +755,7 @@ static int prepare_impl(pmb_ctx* c, const pmb_chrom_args* a, uint32_t n, pmb_bat
     CU_TRY(c, cudaMemsetAsync(b->d_bits_raw, 0, (size_t)EV_PAD_WORDS * 4, c->stream));
     CU_TRY(c, cudaMemsetAsync(b->d_bits + std::max<size_t>(bits_words, 4), 0, (size_t)EV_PAD_WORDS * 4, c->stream));
     CU_TRY(c, cudaMallocAsync((void**)&b->d_counters, b->counter_words * 8, c->stream));
-    CU_TRY(c, cudaMallocAsync((void**)&b->d_err, 4 * (4 + 64), c->stream));
+    CU_TRY(c, cudaMallocAsync((void**)&b->d_err, 4 * (4 + 128), c->stream));
     uint64_t max_iv = 0;
     for (auto& j : b->jobs) max_iv = std::max<uint64_t>(max_iv, j.a.n_intervals);
     b->long_cap = (size_t)max_iv + 4;
@@ -808,10 +837,12 @@ static int execute_events(pmb_ctx* c, pmb_batch* b)
     // clears the counters, the edge sums and the flags.
     {
         ZeroSegs z{};
-        z.p[0] = (uint4*)b->d_bits;      z.n16[0] = b->zero_words / 4;
+        // F, R unless they are packed; M unless it is gathered (layout: all F, R | all M | Er, Or)
+        const size_t z_lo = b->pack_reads ? b->m_begin : 0, z_hi = b->zero_words;
+        z.p[0] = (uint4*)(b->d_bits + z_lo);  z.n16[0] = z_hi > z_lo ? (z_hi - z_lo) / 4 : 0;
         z.p[1] = (uint4*)b->d_counters;  z.n16[1] = b->counter_words * 8 / 16;
         z.p[2] = (uint4*)b->d_aux;       z.n16[2] = b->aux_words * 8 / 16;
-        z.p[3] = (uint4*)b->d_err;       z.n16[3] = 4 * (4 + 64) / 16;
+        z.p[3] = (uint4*)b->d_err;       z.n16[3] = 4 * (4 + 128) / 16;
         zero_segments_kernel<<<c->num_sms * 8, 512, 0, st>>>(z);
         launches++;
     }
@@ -830,6 +861,8 @@ static int execute_events(pmb_ctx* c, pmb_batch* b)
     whole.fl_lo = 0; whole.fl_hi = b->n_fill; whole.fl_items = b->fill_items;
     whole.dv_lo = 0; whole.dv_hi = b->n_derive; whole.dv_ctas = b->derive_ctas;
     whole.tile_lo = 0; whole.tile_hi = b->ev_total_tiles;
+    whole.pk_lo = 0; whole.pk_hi = b->n_pack; whole.pk_chunks = b->pack_chunks;
+    whole.fr_lo = 0; whole.fr_hi = b->m_begin;
     const bool grouped = b->h2d_pending && b->groups.size() > 1;
     const size_t n_pass = grouped ? b->groups.size() : 1;
     if (b->h2d_pending && !grouped)
@@ -870,9 +903,27 @@ static int execute_events(pmb_ctx* c, pmb_batch* b)
         uint32_t* long_count = b->d_long + (side ? 1 : 0);
         unsigned long long* long_list = b->d_long64 + (side ? b->fill_items + 1 : 0);
         if (grouped) CU_TRY(c, cudaStreamWaitEvent(ps, G.done, 0));
-        if (G.sc_items) {     // strand totals are counted by the forward-read event kernel
+        // F, R (strand totals are counted by the forward-read event kernel).  Packed build: one
+        // pass writes every word once; the zero + atomicOr scatter stays behind it, gated on the
+        // "reads unsorted" flag of the group.
+        int* rgate = b->pack_reads ? b->d_err + 4 + 64 + (grouped ? (int)pass : 0) : nullptr;
+        if (b->pack_reads && G.pk_chunks) {
+            uint32_t* run_count = b->d_long + (side ? 3 : 2);
+            ZeroRun* runs = b->d_runs + (side ? b->runs_cap : 0);
+            CU_TRY(c, cudaMemsetAsync(run_count, 0, 4, ps));
+            pack_reads_multi_kernel<<<(unsigned)((G.pk_chunks + PACK_WARPS - 1) / PACK_WARPS), 32 * PACK_WARPS, 0, ps>>>(
+                b->d_pack + G.pk_lo, b->d_pack_prefix + G.pk_lo, G.pk_hi - G.pk_lo, b->d_err, rgate, runs, run_count,
+                (uint32_t)b->runs_cap);
+            zero_runs_kernel<<<c->num_sms * 4, 256, 0, ps>>>(b->d_pack + G.pk_lo, runs, run_count, (uint32_t)b->runs_cap);
+            launches += 2;
+            if (G.sc_items && G.fr_hi > G.fr_lo) {
+                zero_gated_kernel<<<c->num_sms * 8, 512, 0, ps>>>((uint4*)(b->d_bits + G.fr_lo), (G.fr_hi - G.fr_lo) / 4, rgate);
+                launches++;
+            }
+        }
+        if (G.sc_items) {
             scatter_multi_kernel<<<blocks_for(G.sc_items, 256), 256, 0, ps>>>(
-                b->d_scatter + G.sc_lo, b->d_scatter_prefix + G.sc_lo, G.sc_hi - G.sc_lo, b->d_err);
+                b->d_scatter + G.sc_lo, b->d_scatter_prefix + G.sc_lo, G.sc_hi - G.sc_lo, b->d_err, rgate);
             launches++;
         }
         if (!grouped) mark();
@@ -993,7 +1044,7 @@ extern "C" int pmb_batch_execute(pmb_ctx* c, pmb_batch* b)
     }
     CU_TRY(c, cudaMemsetAsync(b->d_bits, 0, std::max<size_t>(b->bits_words, 4) * 4, st));
     CU_TRY(c, cudaMemsetAsync(b->d_counters, 0, b->counter_words * 8, st));
-    CU_TRY(c, cudaMemsetAsync(b->d_err, 0, 4 * (4 + 64), st));
+    CU_TRY(c, cudaMemsetAsync(b->d_err, 0, 4 * (4 + 128), st));
     const size_t n = b->jobs.size();
     unsigned long long* d_totals = b->d_counters + n * PMB_NCOUNTERS * b->stride;
 

@@ -208,8 +208,9 @@ __device__ __forceinline__ uint32_t find_task(const uint64_t* __restrict__ prefi
 }
 
 __global__ void scatter_multi_kernel(const ScatterTask* __restrict__ tasks, const uint64_t* __restrict__ prefix,
-                                     uint32_t n_tasks, int* __restrict__ err_flag)
+                                     uint32_t n_tasks, int* __restrict__ err_flag, const int* __restrict__ gate)
 {
+    if (gate && !*gate) return;      // fallback of pack_reads_multi_kernel
     // `tasks` / `prefix` may point into the middle of the batch's tables (one group of jobs):
     // items are numbered from prefix[0]
     const uint64_t total = prefix[n_tasks];
@@ -306,6 +307,176 @@ __global__ void zero_gated_kernel(uint4* __restrict__ p, size_t n16, const int* 
     size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     const size_t stride = (size_t)gridDim.x * blockDim.x;
     for (; i < n16; i += stride) p[i] = make_uint4(0u, 0u, 0u, 0u);
+}
+
+}  // namespace pmb
+
+// ---------------------------------------------------------------- read arrays without memset or global atomics
+// F and R from SORTED read positions (the host feeds them sorted, mscc.pyx:351-418 raises on
+// anything else; the kernel verifies it and the atomicOr scatter above stays behind it as the
+// gated fallback).  A warp takes a chunk of PACK_CHUNK consecutive reads and OWNS the words from
+// the word of its first read up to the word of the next chunk's first read: it builds them
+// PACK_PIECE words at a time in its own shared memory (zero, OR the reads in, copy out
+// coalesced), so every word of the array is written exactly once -- zeros included -- and
+// nothing has to be cleared beforehand.  Reads of the previous chunk that fall into the warp's
+// first word belong to it too (it walks back over them); its own last reads that fall into
+// the next chunk's first word do not.
+namespace pmb {
+
+constexpr uint32_t PACK_CHUNK = 256;      // reads per warp
+constexpr uint32_t PACK_PIECE = 1024;     // words of shared memory per warp
+constexpr uint32_t PACK_WARPS = 8;
+
+struct PackTask {
+    uint32_t* arr;
+    Geometry g;
+    const uint32_t* pos;
+    uint64_t n;
+    int64_t clip_lo, clip_hi;
+    uint64_t nbits;
+    uint32_t array_words;
+    uint32_t reserved;
+};
+
+// array bit of a position clamped into [0, total_bits]: monotone in p, word = bit >> 5
+__device__ __forceinline__ int64_t clamped_array_bit(const Geometry& g, int64_t p)
+{
+    int64_t a = p - g.origin_bit + g.halo_bits;
+    return a < 0 ? 0 : (a > g.total_bits ? g.total_bits : a);
+}
+
+// A run of >= PACK_LONG_GAP read-less words is not written by its owner warp (one warp zeroing
+// a centromere, or a chromosome without reads, would be the tail of the whole launch): it is
+// queued, and zero_runs_kernel clears all queued runs with the whole grid.
+constexpr uint32_t PACK_LONG_GAP = 16 * PACK_PIECE;
+struct ZeroRun {
+    uint32_t task, start, count, pad;
+};
+
+__global__ void __launch_bounds__(32 * PACK_WARPS) pack_reads_multi_kernel(const PackTask* __restrict__ tasks,
+                                                                           const uint64_t* __restrict__ chunk_prefix,
+                                                                           uint32_t n_tasks, int* __restrict__ err_flag,
+                                                                           int* __restrict__ unsorted,
+                                                                           ZeroRun* __restrict__ runs,
+                                                                           uint32_t* __restrict__ run_count,
+                                                                           uint32_t run_cap)
+{
+    __shared__ __align__(16) uint32_t piece_all[PACK_WARPS][PACK_PIECE];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    uint32_t* piece = piece_all[warp];
+    const uint64_t chunk_id = chunk_prefix[0] + (uint64_t)blockIdx.x * PACK_WARPS + warp;
+    if (chunk_id >= chunk_prefix[n_tasks]) return;            // (no block-level barrier below)
+    const uint32_t t = find_task(chunk_prefix, n_tasks, chunk_id);
+    const PackTask& T = tasks[t];
+    const Geometry g = T.g;
+    const uint32_t* __restrict__ pos = T.pos;
+    const uint64_t n = T.n;
+    const uint64_t c = chunk_id - chunk_prefix[t];
+    const uint64_t r_lo = c * PACK_CHUNK, r_hi = min(n, r_lo + PACK_CHUNK);
+    const uint32_t W = T.array_words;
+    constexpr int PER_LANE = PACK_CHUNK / 32;
+    const uint32_t NONE = 0xFFFFFFFFu;
+    // word index and bit mask of a read (mask 0: the read sets nothing -- clipped or outside the window)
+    auto place = [&](uint32_t p, uint32_t& w, uint32_t& bit) {
+        const int64_t a = (int64_t)p - g.origin_bit + g.halo_bits;
+        w = (uint32_t)(clamped_array_bit(g, p) >> 5);
+        const bool sets = (uint64_t)p < T.nbits && (int64_t)p >= T.clip_lo && (int64_t)p < T.clip_hi && a >= 0 &&
+                          a < g.total_bits;
+        bit = sets ? 1u << (a & 31) : 0u;
+    };
+    // all loads up front (independent: one memory latency for the whole chunk)
+    uint32_t rw[PER_LANE], rb[PER_LANE];
+    bool bad_order = false, bad_range = false;
+#pragma unroll
+    for (int k = 0; k < PER_LANE; ++k) {
+        const uint64_t idx = r_lo + 32u * k + lane;
+        rw[k] = NONE; rb[k] = 0u;
+        if (idx < r_hi) {
+            const uint32_t p = pos[idx];
+            bad_range |= (uint64_t)p >= T.nbits;
+            bad_order |= idx + 1 < n && pos[idx + 1] < p;
+            place(p, rw[k], rb[k]);
+        }
+    }
+    uint32_t next_w = W, next_bit;                              // first read of the next chunk
+    if (r_hi < n) { place(pos[r_hi], next_w, next_bit); next_w = min(next_w, W); }
+    uint32_t back_w = 0, back_bit = 0;                          // the 32 reads before this chunk
+    const bool has_back = c > 0 && r_lo >= (uint64_t)lane + 1;
+    if (has_back) place(pos[r_lo - 1 - lane], back_w, back_bit);
+    if (bad_range) atomicExch(err_flag, 1);
+    if (bad_order) atomicExch(unsorted, 1);
+
+    const uint32_t W_lo = c == 0 ? 0u : __shfl_sync(0xFFFFFFFFu, rw[0], 0);
+    const uint32_t W_hi = next_w;
+    if (W_hi < W_lo || (c > 0 && W_lo == NONE)) { if (lane == 0) atomicExch(unsorted, 1); return; }
+    // reads of earlier chunks that fall into this warp's first word belong to it: walk back
+    uint32_t first_extra = 0;
+    if (c > 0) {
+        uint64_t cur = r_lo;
+        for (uint32_t walked = 0;; walked += 32) {
+            if (walked) {       // more than 32 earlier reads in that word: keep loading (rare)
+                back_w = 0; back_bit = 0;
+                if (cur >= (uint64_t)lane + 1) place(pos[cur - 1 - lane], back_w, back_bit);
+            }
+            const bool ok = cur >= (uint64_t)lane + 1 && back_w >= W_lo;
+            const unsigned m = __ballot_sync(0xFFFFFFFFu, ok);
+            const uint32_t cnt = m == 0xFFFFFFFFu ? 32u : (uint32_t)__ffs(~m) - 1u;
+            first_extra |= __reduce_or_sync(0xFFFFFFFFu, (uint32_t)lane < cnt && back_w == W_lo ? back_bit : 0u);
+            cur -= cnt;
+            if (cnt < 32) break;
+            if (walked > (1u << 16)) { if (lane == 0) atomicExch(unsorted, 1); return; }   // absurd pile-up: fallback
+        }
+    }
+    for (uint32_t wp = W_lo; wp < W_hi;) {
+        // a long read-less run ahead?  queue it for zero_runs_kernel
+        uint32_t mine = W_hi;
+#pragma unroll
+        for (int k = PER_LANE - 1; k >= 0; --k)
+            if (rw[k] >= wp && rw[k] < mine) mine = rw[k];
+        const uint32_t ahead = __reduce_min_sync(0xFFFFFFFFu, mine);       // next word with a read (or W_hi)
+        if (ahead > wp && ahead - wp >= PACK_LONG_GAP) {
+            if (lane == 0) {
+                const uint32_t q = atomicAdd(run_count, 1u);
+                if (q < run_cap) runs[q] = ZeroRun{t, wp, ahead - wp, 0u};
+                else atomicExch(unsorted, 1);       // cannot happen with sorted reads: let the fallback build it
+            }
+            wp = ahead;
+            continue;
+        }
+        // the piece starts at the 16-byte boundary below wp, so shared and global quads line up
+        const uint32_t off = wp & 3u;
+        const uint32_t pw = min(PACK_PIECE - off, W_hi - wp);
+        const uint32_t span = off + pw, nq = (span + 3) >> 2;
+        uint4* piece4 = reinterpret_cast<uint4*>(piece);
+        for (uint32_t q = lane; q < nq; q += 32) piece4[q] = make_uint4(0u, 0u, 0u, 0u);
+        __syncwarp();
+        if (wp == W_lo && lane == 0 && first_extra) atomicOr(piece + off, first_extra);
+#pragma unroll
+        for (int k = 0; k < PER_LANE; ++k)
+            if (rb[k] && rw[k] >= wp && rw[k] < wp + pw) atomicOr(piece + off + (rw[k] - wp), rb[k]);
+        __syncwarp();
+        uint32_t* base = T.arr + (wp - off);
+        for (uint32_t q = lane; q < nq; q += 32) {
+            const uint32_t lo = max(off, 4 * q), hi = min(span, 4 * q + 4);     // words of this quad the warp owns
+            if (hi - lo == 4) *reinterpret_cast<uint4*>(base + 4 * q) = piece4[q];
+            else for (uint32_t i = lo; i < hi; ++i) base[i] = piece[i];
+        }
+        __syncwarp();
+        wp += pw;
+    }
+}
+
+__global__ void zero_runs_kernel(const PackTask* __restrict__ tasks, const ZeroRun* __restrict__ runs,
+                                 const uint32_t* __restrict__ run_count, uint32_t run_cap)
+{
+    const uint32_t n = min(*run_count, run_cap);
+    const size_t tid = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const size_t nth = (size_t)gridDim.x * blockDim.x;
+    for (uint32_t q = 0; q < n; q++) {
+        const ZeroRun r = runs[q];
+        uint32_t* dst = tasks[r.task].arr + r.start;
+        for (size_t w = tid; w < r.count; w += nth) dst[w] = 0u;
+    }
 }
 
 }  // namespace pmb

@@ -219,6 +219,46 @@ def test_mappability_gather_and_its_fallback(dev):
         dev.set_option("h2d_groups", 4)
 
 
+def test_packed_read_arrays_and_their_fallback(dev):
+    """Event path: F and R are packed from the sorted reads by word-owning warps (no memset, no
+    global atomics): long read-less runs (queued and zeroed by the whole grid), pile-ups that
+    cross chunk boundaries, reads outside a shard's window -- and unsorted reads, which take the
+    atomicOr scatter behind the device-side check.  bit_array_set_bit semantics (bit_array.c:668)."""
+    rng = np.random.default_rng(123)
+    L, rl, D = 3000000, 36, 300
+    u32 = lambda x: np.asarray(x, np.uint32)
+    # two clusters 2.5 Mb apart, a pile-up of 700 reads on 3 positions, a run of reads in one word
+    left = np.sort(rng.integers(1, 200000, size=30000))
+    right = np.sort(rng.integers(2800000, L, size=20000))
+    pile = np.repeat(u32([150000, 150001, 150040]), [400, 250, 50])
+    fwd = np.sort(np.concatenate([left, pile, right])).astype(np.uint32)
+    rev = np.sort(np.concatenate([rng.integers(rl, 260000, size=25000), np.arange(2900000, 2900400),
+                                  np.full(513, 2950000)])).astype(np.uint32)
+    _, _, b, e = random_case(7, L, rl, 10)
+    check_job(dev, L, rl, D, fwd, rev, b, e)
+    check_job(dev, L, rl, D, fwd, rev, b, e, lo=100000 + 64, hi=2900000 - 32)     # reads outside the window
+    check_job(dev, L, rl, D, fwd[:1], rev[-1:], b, e)
+    check_job(dev, L, rl, D, fwd, rev)
+    # unsorted reads: the fallback (the C ABI takes them; the calculator would have raised)
+    perm = rng.permutation(fwd.size)
+    check_job(dev, L, rl, D, fwd[perm], rev[::-1].copy(), b, e)
+    # a batch that mixes sorted and unsorted jobs, with and without H2D groups
+    jobs = [_shim.Job(L, rl, D, 3, fwd, rev, b, e), _shim.Job(L, rl, D, 3, fwd[perm], rev, b, e),
+            _shim.Job(200000, rl, D, 1, left.astype(np.uint32), u32([]))]
+    wants = [cc_oracle.chrom_counts(L, rl, D, fwd, rev, b, e)] * 2 + \
+            [cc_oracle.chrom_counts(200000, rl, D, left.astype(np.uint32), u32([]))]
+    try:
+        dev.set_option("path", 2)
+        for groups in (1, 3):
+            dev.set_option("h2d_groups", groups)
+            for got, want in zip(dev.run_batch(jobs), wants):
+                for k in want:
+                    assert np.array_equal(np.asarray(got[k]), np.asarray(want[k])), (k, groups)
+    finally:
+        dev.set_option("path", 0)
+        dev.set_option("h2d_groups", 4)
+
+
 @pytest.mark.parametrize("rl", [1, 32, 33, 129, 300, 1000, 1200])
 def test_read_lengths_and_the_direct_lags(dev, rl):
     """The two directly counted lags (rl-1, rl-2) reach 1 .. 8 look-ahead quads of the gather;
