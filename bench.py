@@ -135,6 +135,30 @@ def pinned_u32(a):
 _PINNED = []
 
 
+def pinned_pack(jobs):
+    """All position / interval arrays of the jobs in ONE page-locked buffer, back to back with
+    16-byte padding (fwd, rev, begins, ends per job): the C ABI then moves a whole group of
+    chromosomes with one copy.  Returns the payload bytes (padding not counted)."""
+    import torch
+    names = ("fwd_pos", "rev_pos", "map_begins", "map_ends")
+    total = sum((getattr(j, n).size + 3) & ~3 for j in jobs for n in names if getattr(j, n) is not None)
+    t = torch.empty(max(total, 4), dtype=torch.int32).pin_memory()
+    buf = t.numpy().view(np.uint32)
+    _PINNED.append(t)
+    off = payload = 0
+    for j in jobs:
+        for n in names:
+            a = getattr(j, n)
+            if a is None:
+                continue
+            v = buf[off:off + a.size]
+            v[:] = a
+            setattr(j, n, v)
+            off += (a.size + 3) & ~3
+            payload += a.size * 4
+    return payload
+
+
 def build_workload(mode, chrom_indices=None):
     from pymasc_b200 import synth
     names = [n for n, _ in synth.HG38]
@@ -312,13 +336,7 @@ def gpu_arm(args):
     workload, gen_s = build_workload(mode, chrom_indices=need)
     jobs = sharding.jobs_for_rank(workload, pieces, READ_LEN, MAX_SHIFT)
     # page-locked copies of the packed inputs: what the host side hands to the C ABI
-    h2d = 0
-    for j in jobs:
-        for name in ("fwd_pos", "rev_pos", "map_begins", "map_ends"):
-            a = getattr(j, name)
-            if a is not None and a.size:
-                setattr(j, name, pinned_u32(a))
-                h2d += a.size * 4
+    h2d = pinned_pack(jobs)
     evals_total = synth.evals(lengths, READ_LEN, MAX_SHIFT)
     P = 5 if mode == "both" else 1
 

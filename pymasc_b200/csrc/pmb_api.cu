@@ -729,24 +729,43 @@ static int prepare_impl(pmb_ctx* c, const pmb_chrom_args* a, uint32_t n, pmb_bat
             b->h2d_pending = true;
         }
     }
+    // One cudaMemcpyAsync per run of arrays that lie back to back in host memory with the same
+    // 16-byte padding as on the device (a host that packs its position arrays into one pinned
+    // buffer gets one copy per group instead of four per chromosome; ~1.5 us of launch each).
     for (auto& gr : b->groups) {
-      for (uint32_t ji = gr.job_lo; ji < gr.job_hi; ji++) {
-        JobPlan& j = b->jobs[ji];
+        const uint32_t* run_src = nullptr; size_t run_dst = 0, run_words = 0;
+        auto flush = [&]() -> cudaError_t {
+            cudaError_t e = cudaSuccess;
+            if (run_words)
+                e = cudaMemcpyAsync(b->d_in + run_dst, run_src, run_words * 4, cudaMemcpyHostToDevice, up_stream);
+            run_words = 0;
+            return e;
+        };
         auto up = [&](size_t off, const uint32_t* src, uint64_t cnt) -> cudaError_t {
             if (!cnt) return cudaSuccess;
-            return cudaMemcpyAsync(b->d_in + off, src, cnt * 4, cudaMemcpyHostToDevice, up_stream);
+            const size_t padded = (run_words + 3) & ~(size_t)3;
+            if (run_words && src == run_src + padded && off == run_dst + padded) {
+                run_words = padded + cnt;       // the pad words in between are the host's own padding
+                return cudaSuccess;
+            }
+            cudaError_t e = flush();
+            run_src = src; run_dst = off; run_words = cnt;
+            return e;
         };
-        if (!j.autocorr) {
-            CU_TRY(c, up(j.in_fwd, j.a.fwd_pos, j.a.n_fwd));
-            CU_TRY(c, up(j.in_rev, j.a.rev_pos, j.a.n_rev));
+        for (uint32_t ji = gr.job_lo; ji < gr.job_hi; ji++) {
+            JobPlan& j = b->jobs[ji];
+            if (!j.autocorr) {
+                CU_TRY(c, up(j.in_fwd, j.a.fwd_pos, j.a.n_fwd));
+                CU_TRY(c, up(j.in_rev, j.a.rev_pos, j.a.n_rev));
+            }
+            if ((j.mode & MODE_MSCC) || j.autocorr) {
+                CU_TRY(c, up(j.in_mb, j.a.map_begin, j.a.n_intervals));
+                CU_TRY(c, up(j.in_me, j.a.map_end, j.a.n_intervals));
+            }
+            j.a.fwd_pos = j.a.rev_pos = j.a.map_begin = j.a.map_end = nullptr;   // not read again by the host
         }
-        if ((j.mode & MODE_MSCC) || j.autocorr) {
-            CU_TRY(c, up(j.in_mb, j.a.map_begin, j.a.n_intervals));
-            CU_TRY(c, up(j.in_me, j.a.map_end, j.a.n_intervals));
-        }
-        j.a.fwd_pos = j.a.rev_pos = j.a.map_begin = j.a.map_end = nullptr;   // not read again by the host
-      }
-      if (async) CU_TRY(c, cudaEventRecord(gr.done, up_stream));
+        CU_TRY(c, flush());
+        if (async) CU_TRY(c, cudaEventRecord(gr.done, up_stream));
     }
     CU_TRY(c, cudaMallocAsync((void**)&b->d_bits_raw,
                               (std::max<size_t>(bits_words, 4) + 2 * (size_t)EV_PAD_WORDS) * 4, c->stream));

@@ -316,6 +316,37 @@ def test_pipelined_input_copy_gives_the_same_counts(pdev, groups):
         dev.set_option("h2d_groups", 4)
 
 
+def test_inputs_packed_in_one_host_buffer(pdev):
+    """Position arrays that lie back to back in host memory with 16-byte padding travel as one
+    copy per group; arrays that merely touch (no padding) or lie anywhere else do not merge."""
+    dev = pdev
+    rl, D = 36, 200
+    cases = [random_case(200 + i, L, rl, max(5, L // 15)) for i, L in enumerate([30000, 30001, 50003, 777])]
+    lens = [30000, 30001, 50003, 777]
+    want = [cc_oracle.chrom_counts(L, rl, D, *cs) for L, cs in zip(lens, cases)]
+    for pad in (True, False):
+        total = sum(((a.size + 3) & ~3) if pad else a.size for cs in cases for a in cs)
+        buf = np.zeros(total + 8, np.uint32)
+        off, jobs = 0, []
+        for L, cs in zip(lens, cases):
+            views = []
+            for a in cs:
+                v = buf[off:off + a.size]
+                v[:] = a
+                views.append(v)
+                off += ((a.size + 3) & ~3) if pad else a.size
+            jobs.append(_shim.Job(L, rl, D, 3, *views))
+        for groups in (1, 3):
+            dev.set_option("h2d_groups", groups)
+            try:
+                got = dev.run_batch(jobs)
+            finally:
+                dev.set_option("h2d_groups", 4)
+            for g, w in zip(got, want):
+                for k in w:
+                    assert np.array_equal(np.asarray(g[k]), np.asarray(w[k])), (k, pad, groups)
+
+
 # ----------------------------------------------------------------- the reference's own pins
 def test_fixture_golden_tables_through_the_calculator():
     """configs[0]: tests/data ChIP-seq fixture, -d 300 -q 10 -r 36, against tests/golden."""

@@ -20,13 +20,7 @@ def main():
     pieces = sharding.plan(lengths, bench.READ_LEN, bench.MAX_SHIFT, 1)[0]
     workload, _ = bench.build_workload("both")
     jobs = sharding.jobs_for_rank(workload, pieces, bench.READ_LEN, bench.MAX_SHIFT)
-    nbytes = 0
-    for j in jobs:
-        for name in ("fwd_pos", "rev_pos", "map_begins", "map_ends"):
-            a = getattr(j, name)
-            if a is not None and a.size:
-                setattr(j, name, bench.pinned_u32(a))
-                nbytes += a.size * 4
+    nbytes = bench.pinned_pack(jobs)
     dev = _shim.Device(0)
     out = {"h2d_bytes": nbytes}
 
