@@ -328,12 +328,10 @@ def gpu_arm(args):
     mode = args.mode
 
     lengths = [L for _, L in synth.HG38]
-    pieces = sharding.plan(lengths, READ_LEN, MAX_SHIFT, world)[rank]
-    mine = sorted({ci for ci, _, _ in pieces})
-    need = set(mine)
-    if rank == 0 and world == 1 and not args.no_cpu_baseline:
-        need.add(20)
-    workload, gen_s = build_workload(mode, chrom_indices=need)
+    # every rank generates the whole (seeded) genome: the position plan weighs reads and run
+    # edges as well as length, so all ranks need the same view of the data to agree on the cuts
+    workload, gen_s = build_workload(mode)
+    pieces = sharding.plan_weighted(workload, READ_LEN, MAX_SHIFT, world)[rank]
     jobs = sharding.jobs_for_rank(workload, pieces, READ_LEN, MAX_SHIFT)
     # page-locked copies of the packed inputs: what the host side hands to the C ABI
     h2d = pinned_pack(jobs)

@@ -159,7 +159,8 @@ void pmb_host_free(void *p);
  * event path unless the inputs hold more than 4 events (reads + run edges) per 32-bit
  * word.  Tuning: "variant" (carry-save depth of the shift-window counters), "tile_words",
  * "grid_blocks", "block_warps", "event_tile_words", "event_blocks_per_sm".
- * Input copy: "async_h2d" (0/1, see pmb_batch_prepare), "h2d_groups" (1..64, default 4),
+ * Input copy: "async_h2d" (0/1, see pmb_batch_prepare), "h2d_groups" (1..64, default 4: at most that many),
+ * "h2d_min_group_bytes" (default 16 MiB: no group smaller than that on average; 0 = always h2d_groups),
  * "h2d_growth_x10" (size ratio of consecutive groups in tenths, default 13). */
 int  pmb_set_option(pmb_ctx *ctx, const char *name, int64_t value);
 

@@ -39,6 +39,7 @@ struct pmb_ctx {
     int event_tile_words = 0;
     int event_blocks_per_sm = 0;
     int async_h2d = 0;       // prepare returns before the input copy has finished (see header)
+    int64_t h2d_min_group_bytes = 16 << 20;   // no H2D group smaller than this on average
     int h2d_growth_x10 = 13; // size ratio of consecutive H2D groups, in tenths
     int h2d_groups = 4;      // event path: job groups whose build + kernels overlap the H2D of the next
     cudaStream_t copy_stream = nullptr;
@@ -272,6 +273,7 @@ extern "C" int pmb_set_option(pmb_ctx* c, const char* name, int64_t value)
     else if (!strcmp(name, "event_blocks_per_sm")) c->event_blocks_per_sm = (int)value;
     else if (!strcmp(name, "async_h2d")) c->async_h2d = value != 0;
     else if (!strcmp(name, "h2d_growth_x10")) c->h2d_growth_x10 = (int)std::max<int64_t>(10, std::min<int64_t>(value, 100));
+    else if (!strcmp(name, "h2d_min_group_bytes")) c->h2d_min_group_bytes = std::max<int64_t>(0, value);
     else if (!strcmp(name, "h2d_groups")) c->h2d_groups = (int)std::max<int64_t>(1, std::min<int64_t>(value, 64));
     else { c->err = std::string("unknown option ") + name; return PMB_ERR_ARG; }
     return PMB_OK;
@@ -688,7 +690,6 @@ static int prepare_impl(pmb_ctx* c, const pmb_chrom_args* a, uint32_t n, pmb_bat
     // bytes, an event behind each group; the first execute consumes group g while g+1 is in flight.
     cudaStream_t up_stream = c->stream;
     {
-        const uint32_t want = async ? (b->path == 2 ? (uint32_t)c->h2d_groups : 1u) : 1u;
         std::vector<size_t> job_words(n);
         for (uint32_t i = 0; i < n; i++) {
             const JobPlan& j = b->jobs[i];
@@ -697,6 +698,14 @@ static int prepare_impl(pmb_ctx* c, const pmb_chrom_args* a, uint32_t n, pmb_bat
         }
         size_t total = 0, acc = 0;
         for (size_t w : job_words) total += w;
+        // a group is only worth its extra launches when its copy takes a few hundred microseconds:
+        // at most "h2d_groups" groups, and none smaller than ~16 MB on average
+        uint32_t want = 1;
+        if (async && b->path == 2)
+            want = c->h2d_min_group_bytes > 0
+                       ? (uint32_t)std::min<size_t>((size_t)c->h2d_groups,
+                                                    std::max<size_t>(1, total * 4 / (size_t)c->h2d_min_group_bytes))
+                       : (uint32_t)c->h2d_groups;
         // Group sizes grow geometrically: the first group is small so the kernels start early,
         // and each later group may be larger because computing on a group takes ~2x as long
         // as copying it (so the copy of group g+1 hides behind the kernels of group g).

@@ -3,7 +3,7 @@
 ``ShardedEngine`` is an engine for ``CCBitArrayCalculator`` (``engine=`` keyword).  Every rank
 of the process group feeds the same reads (or at least closes the same chromosomes) and calls
 ``run(jobs)`` with the same job list; each rank counts its position shard of every chromosome
-(``sharding.plan``), the (max_shift+1)-long int64 count vectors are summed across ranks with a
+(``sharding.plan_weighted``), the (max_shift+1)-long int64 count vectors are summed across ranks with a
 single ``all_reduce`` -- NCCL over NVLink/NVSwitch when the local engine is a device, on the
 device counter block itself (no host round trip) -- and every rank returns the full result.
 
@@ -48,7 +48,7 @@ def shard_jobs(jobs, rank, world):
         return []
     rl, D = jobs[0].read_len, jobs[0].max_shift
     chroms = job_chroms(jobs)
-    pieces = sharding.plan([c["length"] for c in chroms], rl, D, world)[rank]
+    pieces = sharding.plan_weighted(chroms, rl, D, world)[rank]     # every rank holds the same jobs
     mine = sharding.jobs_for_rank(chroms, pieces, rl, D, flags_of=lambda c: c["flags"])
     for j in mine:   # read-less autocorrelation jobs carry no reads
         if j.flags & _shim.FLAG_AUTOCORR:

@@ -40,6 +40,10 @@ def plan(lengths, read_len, max_shift, world):
         c = (total * r // world) // ALIGN_BITS * ALIGN_BITS
         cuts.append(max(c, cuts[-1]))
     cuts.append(total)
+    return _pieces_from_cuts(cuts, nbits, world)
+
+
+def _pieces_from_cuts(cuts, nbits, world):
     out = [[] for _ in range(world)]
     base = 0
     for ci, nb in enumerate(nbits):
@@ -50,6 +54,53 @@ def plan(lengths, read_len, max_shift, world):
                 out[r].append((ci, lo, hi))
         base += nb
     return out
+
+
+# Relative cost of one read / one run edge of the mappability track against one bit position, for
+# the event-window kernels (ncu instruction counts, profiles/r01_ncu_event_window_v9.txt: ~0.4
+# warp instructions per bit position over the build and the three scans, ~60 per event).
+READ_COST = 150.0
+EDGE_COST = 150.0
+
+
+def plan_weighted(chroms, read_len, max_shift, world, read_cost=READ_COST, edge_cost=EDGE_COST):
+    """Like ``plan``, but the cuts equalise bits + read_cost * reads + edge_cost * run edges per
+    rank (a rank's time follows its events as much as its length).  `chroms`: dicts with
+    ``length``, ``fwd``, ``rev`` and optionally ``begins`` (sorted arrays, as for
+    ``jobs_for_rank``); every rank must call it with the same data."""
+    nbits = [array_bits(c["length"], read_len, max_shift) for c in chroms]
+
+    def arrays(c):
+        out = [(a, read_cost) for a in (c.get("fwd"), c.get("rev")) if a is not None and len(a)]
+        b = c.get("begins")
+        if b is not None and len(b):
+            out.append((b, 2.0 * edge_cost))
+        return out
+
+    def cost_upto(c, x):        # cost of bits [0, x) of chromosome c
+        return float(x) + sum(w * float(np.searchsorted(a, x, side="left")) for a, w in arrays(c))
+
+    whole = [cost_upto(c, nb) for c, nb in zip(chroms, nbits)]
+    total = sum(whole)
+    bases = np.concatenate([[0], np.cumsum(nbits)]).astype(np.int64)
+    cuts = [0]
+    for r in range(1, world):
+        target = total * r / world
+        acc, ci = 0.0, 0
+        while ci < len(chroms) - 1 and acc + whole[ci] < target:
+            acc += whole[ci]
+            ci += 1
+        lo, hi = 0, nbits[ci]                      # first x with cost_upto >= target - acc
+        while lo < hi:
+            mid = (lo + hi) // 2
+            if acc + cost_upto(chroms[ci], mid) < target:
+                lo = mid + 1
+            else:
+                hi = mid
+        cut = (int(bases[ci]) + lo) // ALIGN_BITS * ALIGN_BITS
+        cuts.append(max(cut, cuts[-1]))
+    cuts.append(int(bases[-1]))
+    return _pieces_from_cuts(cuts, nbits, world)
 
 
 def plan_by_chromosome(lengths, read_len, max_shift, world):

@@ -18,6 +18,7 @@ PATHS = (1, 2)      # 1 dense shift-window, 2 event-window (0 = auto picks one o
 @pytest.fixture(scope="module")
 def dev():
     d = _shim.Device(0)
+    d.set_option("h2d_min_group_bytes", 0)      # tests are small: let "h2d_groups" form groups anyway
     yield d
     d.close()
 

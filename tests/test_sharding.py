@@ -43,6 +43,40 @@ def test_plan_covers_every_bit_once(world):
     assert max(sizes) - min(sizes) <= 2 * sharding.ALIGN_BITS
 
 
+@pytest.mark.parametrize("world", [1, 2, 3, 8])
+def test_weighted_plan_covers_every_bit_once_and_balances_events(world):
+    """Cuts that equalise bits + 150 * events: all reads of a skewed genome sit in 10 % of it."""
+    rng = np.random.default_rng(5)
+    rl, D = 36, 300
+    chroms = []
+    for L in (400000, 90000, 250000):
+        hot = np.sort(rng.integers(1, L // 10, size=L // 20)).astype(np.uint32)
+        chroms.append({"length": L, "fwd": hot, "rev": hot + 40, "begins": None, "ends": None})
+    plan = sharding.plan_weighted(chroms, rl, D, world)
+    assert len(plan) == world
+    cost = []
+    for pieces in plan:
+        c = 0.0
+        for ci, lo, hi in pieces:
+            a = chroms[ci]["fwd"]
+            n = int(np.searchsorted(a, hi) - np.searchsorted(a, lo))
+            a = chroms[ci]["rev"]
+            n += int(np.searchsorted(a, hi) - np.searchsorted(a, lo))
+            c += (hi - lo) + sharding.READ_COST * n
+        cost.append(c)
+    for ci, ch in enumerate(chroms):
+        nb = sharding.array_bits(ch["length"], rl, D)
+        segs = sorted((lo, hi) for pieces in plan for c, lo, hi in pieces if c == ci)
+        assert segs[0][0] == 0 and segs[-1][1] == nb
+        for (a, b), (c, d) in zip(segs, segs[1:]):
+            assert b == c
+    # balanced to within the reads of one 128-bit granule (dense pile-ups: ~20 reads per granule here)
+    assert max(cost) - min(cost) <= 0.02 * sum(cost) / world + 2 * sharding.ALIGN_BITS * (1 + sharding.READ_COST)
+    equal = sharding.plan([c["length"] for c in chroms], rl, D, world)
+    if world > 1:
+        assert plan != equal
+
+
 def test_plan_by_chromosome_is_lpt():
     lengths = [100, 90, 50, 40, 30, 10]
     plan = sharding.plan_by_chromosome(lengths, 10, 20, 2)
