@@ -554,7 +554,8 @@ def gpu_arm(args):
             "e2e": {"value": evals_total / (e2e_ms * 1e-3), "unit": UNIT, "ms_per_step": e2e_ms,
                     "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
                     "api": "pmb_batch_prepare/execute/fetch via ctypes (pymasc_b200._shim)",
-                    "h2d": ("pipelined: %d chromosome groups on a copy stream" % args.h2d_groups)
+                    "h2d": ("pipelined: up to %d chromosome groups (none under 16 MiB) on a copy stream"
+                            % args.h2d_groups)
                            if args.h2d_groups > 0 else "copy, then compute"},
             "gpu_launches": int(launches_per_step * args.steps),
             "launches_per_step": int(launches_per_step),
