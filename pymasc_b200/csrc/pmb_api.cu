@@ -110,6 +110,7 @@ struct pmb_batch {
     size_t m_begin = 0, m_end = 0;      // event path: the M arrays of all jobs, [m_begin, m_end) of d_bits
     bool gather_m = false;              // M is gathered (mask_build_multi_kernel), not scattered
     bool pack_reads = false;            // F, R are packed from the sorted reads (pack_reads_multi_kernel)
+    uint64_t* d_edge_prefix = nullptr; uint64_t edge_ctas = 0;      // edge_list_kernel, over the derive tasks
     PackTask* d_pack = nullptr; uint64_t* d_pack_prefix = nullptr; uint32_t n_pack = 0; uint64_t pack_chunks = 0;
     ZeroRun* d_runs = nullptr; size_t runs_cap = 0;     // main | side queue
     uint32_t gather_k = 1;              // look-ahead quads of the gather
@@ -123,7 +124,7 @@ struct pmb_batch {
     struct Group {
         uint32_t job_lo = 0, job_hi = 0;
         uint32_t sc_lo = 0, sc_hi = 0, fl_lo = 0, fl_hi = 0, dv_lo = 0, dv_hi = 0, pk_lo = 0, pk_hi = 0;
-        uint64_t sc_items = 0, fl_items = 0, dv_ctas = 0, pk_chunks = 0;
+        uint64_t sc_items = 0, fl_items = 0, dv_ctas = 0, pk_chunks = 0, ed_ctas = 0;
         size_t fr_lo = 0, fr_hi = 0;    // the group's F, R arrays: [fr_lo, fr_hi) of d_bits
         uint32_t tile_lo = 0, tile_hi = 0;
         cudaEvent_t done = nullptr;
@@ -464,6 +465,7 @@ static int plan_events(pmb_ctx* c, pmb_batch* b)
         std::vector<FillTask> fl; std::vector<uint64_t> flp{0};
         std::vector<DeriveTask> dv; std::vector<uint64_t> dvp{0};
         std::vector<PackTask> pk; std::vector<uint64_t> pkp{0};
+        std::vector<uint64_t> edp{0};
         std::vector<uint32_t> pk_at(n + 1);
         unsigned long long* adir0 = b->d_aux + n * 2 * (size_t)b->stride;
         std::vector<uint32_t> sc_at(n + 1), fl_at(n + 1), dv_at(n + 1);
@@ -513,7 +515,10 @@ static int plan_events(pmb_ctx* c, pmb_batch* b)
             d.begins = b->d_in + j.in_mb;
             d.ends = b->d_in + j.in_me;
             d.p_off = g.origin_bit - g.halo_bits;
+            d.aux = b->d_aux + i * 2 * (size_t)b->stride;
+            d.edge_off = j.autocorr ? 0 : (int)b->read_len - 1 - (int)b->max_shift;
             dv.push_back(d);
+            edp.push_back(edp.back() + (j.a.n_intervals + EDGE_INTERVALS_PER_CTA - 1) / EDGE_INTERVALS_PER_CTA);
             dvp.push_back(dvp.back() + (j.array_words / 4 + DERIVE_QUADS_PER_CTA - 1) / DERIVE_QUADS_PER_CTA);
         }
         sc_at[n] = (uint32_t)sc.size(); fl_at[n] = (uint32_t)fl.size(); dv_at[n] = (uint32_t)dv.size();
@@ -523,6 +528,7 @@ static int plan_events(pmb_ctx* c, pmb_batch* b)
             gr.fl_lo = fl_at[gr.job_lo]; gr.fl_hi = fl_at[gr.job_hi]; gr.fl_items = flp[gr.fl_hi] - flp[gr.fl_lo];
             gr.dv_lo = dv_at[gr.job_lo]; gr.dv_hi = dv_at[gr.job_hi]; gr.dv_ctas = dvp[gr.dv_hi] - dvp[gr.dv_lo];
             gr.pk_lo = pk_at[gr.job_lo]; gr.pk_hi = pk_at[gr.job_hi]; gr.pk_chunks = pkp[gr.pk_hi] - pkp[gr.pk_lo];
+            gr.ed_ctas = edp[gr.dv_hi] - edp[gr.dv_lo];
             gr.fr_lo = gr.fr_hi = 0;
             for (uint32_t q = gr.job_lo; q < gr.job_hi; q++)
                 if (!b->jobs[q].autocorr) {
@@ -537,12 +543,14 @@ static int plan_events(pmb_ctx* c, pmb_batch* b)
         b->n_fill = (uint32_t)fl.size(); b->fill_items = flp.back();
         b->n_derive = (uint32_t)dv.size(); b->derive_ctas = dvp.back();
         b->n_pack = (uint32_t)pk.size(); b->pack_chunks = pkp.back();
+        b->edge_ctas = edp.back();
         auto bytes8 = [](size_t x) { return (x + 15) & ~(size_t)15; };
         const size_t o_sc = 0, o_scp = o_sc + bytes8(sc.size() * sizeof(ScatterTask));
         const size_t o_fl = o_scp + bytes8(scp.size() * 8), o_flp = o_fl + bytes8(fl.size() * sizeof(FillTask));
         const size_t o_dv = o_flp + bytes8(flp.size() * 8), o_dvp = o_dv + bytes8(dv.size() * sizeof(DeriveTask));
         const size_t o_pk = o_dvp + bytes8(dvp.size() * 8), o_pkp = o_pk + bytes8(pk.size() * sizeof(PackTask));
-        const size_t total = o_pkp + bytes8(pkp.size() * 8);
+        const size_t o_edp = o_pkp + bytes8(pkp.size() * 8);
+        const size_t total = o_edp + bytes8(edp.size() * 8);
         std::vector<unsigned char>& blob = b->h_blob;
         blob.assign(total, 0);
         if (!sc.empty()) memcpy(blob.data() + o_sc, sc.data(), sc.size() * sizeof(ScatterTask));
@@ -553,6 +561,7 @@ static int plan_events(pmb_ctx* c, pmb_batch* b)
         memcpy(blob.data() + o_dvp, dvp.data(), dvp.size() * 8);
         if (!pk.empty()) memcpy(blob.data() + o_pk, pk.data(), pk.size() * sizeof(PackTask));
         memcpy(blob.data() + o_pkp, pkp.data(), pkp.size() * 8);
+        memcpy(blob.data() + o_edp, edp.data(), edp.size() * 8);
         CU_TRY(c, cudaMallocAsync(&b->d_tasks, total, c->stream));
         CU_TRY(c, cudaMemcpyAsync(b->d_tasks, blob.data(), total, cudaMemcpyHostToDevice, c->stream));
         unsigned char* d = (unsigned char*)b->d_tasks;
@@ -560,6 +569,7 @@ static int plan_events(pmb_ctx* c, pmb_batch* b)
         b->d_fill = (FillTask*)(d + o_fl); b->d_fill_prefix = (uint64_t*)(d + o_flp);
         b->d_derive = (DeriveTask*)(d + o_dv); b->d_derive_prefix = (uint64_t*)(d + o_dvp);
         b->d_pack = (PackTask*)(d + o_pk); b->d_pack_prefix = (uint64_t*)(d + o_pkp);
+        b->d_edge_prefix = (uint64_t*)(d + o_edp);
         b->runs_cap = b->m_begin / PACK_LONG_GAP + pk.size() + 16;
         CU_TRY(c, cudaMallocAsync((void**)&b->d_runs, 2 * b->runs_cap * sizeof(ZeroRun), c->stream));
         CU_TRY(c, cudaMallocAsync((void**)&b->d_long64, 2 * (b->fill_items + 1) * 8, c->stream));   // main | side
@@ -890,6 +900,7 @@ static int execute_events(pmb_ctx* c, pmb_batch* b)
     whole.dv_lo = 0; whole.dv_hi = b->n_derive; whole.dv_ctas = b->derive_ctas;
     whole.tile_lo = 0; whole.tile_hi = b->ev_total_tiles;
     whole.pk_lo = 0; whole.pk_hi = b->n_pack; whole.pk_chunks = b->pack_chunks;
+    whole.ed_ctas = b->edge_ctas;
     whole.fr_lo = 0; whole.fr_hi = b->m_begin;
     const bool grouped = b->h2d_pending && b->groups.size() > 1;
     const size_t n_pass = grouped ? b->groups.size() : 1;
@@ -1007,7 +1018,22 @@ static int execute_events(pmb_ctx* c, pmb_batch* b)
         if (!grouped) CU_TRY(c, cudaEventRecord(c->evk[0], st));
         if (b->any_mscc) PMB_EV_LAUNCH(EV_REV, false, true);
         if (!grouped) CU_TRY(c, cudaEventRecord(c->evk[1], st));
-        if (b->any_mscc || b->any_autocorr) PMB_EV_LAUNCH(EV_EDGE, false, true);
+        if (b->any_mscc || b->any_autocorr) {
+            // run edges: from the interval list when M was gathered from it; the scan over M stays
+            // behind it, gated on the same "unsorted" flag
+            const bool listed = b->gather_m && !getenv("PMB_NO_EDGE_LIST");
+            if (listed && G.ed_ctas) {
+                for (uint32_t col0 = 0; col0 < n_cols_total; col0 += 32) {
+                    EdgeListParams E{col0, std::min(32u, n_cols_total - col0), b->max_shift, b->stride};
+                    edge_list_kernel<<<(unsigned)G.ed_ctas, 256, 0, ps>>>(
+                        b->d_derive + G.dv_lo, b->d_edge_prefix + G.dv_lo, G.dv_hi - G.dv_lo, E, gate);
+                    window_launches++;
+                }
+            }
+            P.gate = listed ? gate : nullptr;
+            if (!listed || G.fl_items) PMB_EV_LAUNCH(EV_EDGE, false, true);
+            P.gate = nullptr;
+        }
     }
 #undef PMB_EV_LAUNCH
     if (grouped) {      // join the side stream; the per-kernel split is not meaningful here

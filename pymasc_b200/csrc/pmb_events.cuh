@@ -75,6 +75,7 @@ struct EventParams {
     uint32_t max_shift;
     uint32_t read_len;
     uint32_t stride;
+    const int* gate;        // EV_EDGE: run only if *gate is set (fallback of edge_list_kernel); may be null
 };
 
 #ifndef EV_SWITCH_ADD
@@ -280,6 +281,7 @@ __global__ void __launch_bounds__(32 * EV_WARPS) event_window_kernel(const Event
     // count and the carry-save dispatch then compile to uniform branches (BRA.U, no BSSY/BSYNC)
     const int warp = __shfl_sync(0xFFFFFFFFu, (int)(threadIdx.x >> 5), 0);
 
+    if (KIND == EV_EDGE && P.gate && !*P.gate) return;
     const uint32_t n_launch_tiles = P.tile_hi - P.tile_lo;
     const uint32_t t_lo = P.tile_lo + (uint32_t)(((uint64_t)n_launch_tiles * blockIdx.x) / gridDim.x);
     const uint32_t t_hi = P.tile_lo + (uint32_t)(((uint64_t)n_launch_tiles * (blockIdx.x + 1)) / gridDim.x);
@@ -611,6 +613,9 @@ struct DeriveTask {
     const uint32_t* begins;
     const uint32_t* ends;
     long long p_off;                // chromosome bit of array bit 0 (negative inside the left halo)
+    unsigned long long* aux;        // edge_list_kernel: [2][stride] edge sums of the job
+    int edge_off;                   //   window start relative to an edge (as EventJob::edge_off)
+    int reserved;
 };
 constexpr uint32_t DERIVE_QUADS_PER_CTA = 2048;
 
@@ -856,6 +861,123 @@ __global__ void __launch_bounds__(256) mask_build_multi_kernel(const DeriveTask*
             *reinterpret_cast<uint4*>(M + i) = make_uint4(m0, m1, m2, m3);
             if (Er) store_decimated(Er, Or, pairs - 2 - (i >> 1), m0, m1, m2, m3);
         }
+    }
+}
+
+// ---------------------------------------------------------------- run edges from the interval list
+// With sorted, disjoint intervals (the gather build's precondition) the run edges of Mc are
+// KNOWN: interval (b, e] clipped to the counted range starts a run at s and ends one at t.  So
+// the edge sums need no scan over M at all: a CTA takes 256 consecutive intervals of one job, a
+// warp 32 of them, and every edge adds its window of dM straight from global memory (two
+// coalesced words per lane, the next interval's words in flight while this one is counted).
+// Touching and empty intervals produce a start and an end at the same bit, whose windows cancel
+// exactly in C = plus - minus.  The scan-based run-edge kernel stays behind this one as the gated
+// fallback for unsorted input.
+constexpr uint32_t EDGE_INTERVALS_PER_CTA = 256;
+
+struct EdgeListParams {
+    uint32_t col0, n_cols, max_shift, stride;
+};
+
+__global__ void __launch_bounds__(256) edge_list_kernel(const DeriveTask* __restrict__ tasks,
+                                                        const uint64_t* __restrict__ cta_prefix,
+                                                        uint32_t n_tasks, EdgeListParams P,
+                                                        const int* __restrict__ unsorted)
+{
+    if (*unsorted) return;
+    __shared__ uint32_t hist[2 * 32 * EV_HIST_STRIDE];
+    const int lane = threadIdx.x & 31;
+    const int warp = __shfl_sync(0xFFFFFFFFu, (int)(threadIdx.x >> 5), 0);
+    const uint64_t cta = cta_prefix[0] + blockIdx.x;
+    uint32_t lo_t = 0, hi_t = n_tasks;
+    while (hi_t - lo_t > 1) {
+        const uint32_t mid = (lo_t + hi_t) >> 1;
+        if (cta_prefix[mid] <= cta) lo_t = mid; else hi_t = mid;
+    }
+    const DeriveTask& T = tasks[lo_t];
+    const uint32_t* __restrict__ M = T.M;
+    const long long W = T.array_words;
+    const uint32_t nI = T.n_intervals;
+    for (uint32_t i = threadIdx.x; i < 2 * 32 * EV_HIST_STRIDE; i += blockDim.x) hist[i] = 0;
+    __syncthreads();
+
+    // this lane's interval as array bits: a run of Mc starts at s and ends at t (first bit after it)
+    const uint32_t iv = (uint32_t)(cta - cta_prefix[lo_t]) * EDGE_INTERVALS_PER_CTA + 32u * warp + lane;
+    long long s = 0, t = 0;
+    if (iv < nI) {
+        const long long b = T.begins[iv], e = T.ends[iv];
+        s = max(b + 1 - T.p_off, T.a_lo);
+        t = min(e + 1 - T.p_off, T.a_hi);
+    }
+    const bool valid = s < t;
+    const unsigned vmask = __ballot_sync(0xFFFFFFFFu, valid);
+    const uint32_t col_mask = lane < (int)P.n_cols ? 0xFFFFFFFFu : 0u;
+    const long long shift0 = (long long)T.edge_off + 32ll * P.col0;     // window start relative to the edge
+
+    // the two window words of lane `lane` for an edge at array bit a (zero outside the array)
+    auto fetch = [&](long long a, uint32_t& w0, uint32_t& w1, uint32_t& wm) {
+        const long long o = a + shift0;
+        const long long wi = (o >> 5) + lane;
+        w0 = (wi >= 0 && wi < W) ? __ldg(M + wi) : 0u;
+        w1 = (wi + 1 >= 0 && wi + 1 < W) ? __ldg(M + wi + 1) : 0u;
+        wm = 0u;
+        if ((o & 31) == 0) wm = (wi - 1 >= 0 && wi - 1 < W) ? __ldg(M + wi - 1) : 0u;   // bit o-1 (uniform branch)
+    };
+    Slices<2> sl;
+    sl.reset();
+    auto count = [&](long long a, bool is_end, uint32_t w0, uint32_t w1, uint32_t wm) {
+        const uint32_t sh = (uint32_t)((a + shift0) & 31);
+        sl.add_with(hist, lane, [&](uint32_t (&x)[2]) {
+            const uint32_t m1 = __funnelshift_r(w0, w1, sh);
+            const uint32_t m0 = sh ? __funnelshift_r(w0, w1, sh - 1u) : __funnelshift_r(wm, w0, 31u);
+            const uint32_t ws = m1 & ~m0 & col_mask;
+            const uint32_t we = ~m1 & m0 & col_mask;
+            x[0] = is_end ? we : ws;     // start.start + end.end
+            x[1] = is_end ? ws : we;     // start.end + end.start
+        });
+    };
+    // software pipeline over the warp's valid intervals: the words of interval k+1 are requested
+    // before interval k is counted
+    unsigned todo = vmask;
+    uint32_t a0 = 0, a1 = 0, am = 0, b0 = 0, b1 = 0, bm = 0;        // start / end edge of the current interval
+    long long cs = 0, ct = 0;
+    if (todo) {
+        const int k = __ffs(todo) - 1;
+        todo &= todo - 1;
+        cs = __shfl_sync(0xFFFFFFFFu, s, k);
+        ct = __shfl_sync(0xFFFFFFFFu, t, k);
+        fetch(cs, a0, a1, am);
+        fetch(ct, b0, b1, bm);
+        for (;;) {
+            uint32_t n0 = 0, n1 = 0, nm = 0, q0 = 0, q1 = 0, qm = 0;
+            long long ns = 0, nt = 0;
+            const bool more = todo != 0;
+            if (more) {
+                const int k2 = __ffs(todo) - 1;
+                todo &= todo - 1;
+                ns = __shfl_sync(0xFFFFFFFFu, s, k2);
+                nt = __shfl_sync(0xFFFFFFFFu, t, k2);
+                fetch(ns, n0, n1, nm);
+                fetch(nt, q0, q1, qm);
+            }
+            count(cs, false, a0, a1, am);
+            count(ct, true, b0, b1, bm);
+            if (!more) break;
+            cs = ns; ct = nt;
+            a0 = n0; a1 = n1; am = nm; b0 = q0; b1 = q1; bm = qm;
+        }
+    }
+    sl.flush(hist, lane);
+    __syncthreads();
+    for (uint32_t i = threadIdx.x; i < 2 * 32 * EV_HIST_STRIDE; i += blockDim.x) {
+        const uint32_t v = hist[i];
+        if (!v) continue;
+        const uint32_t n = i / (32 * EV_HIST_STRIDE);
+        const uint32_t r = i % (32 * EV_HIST_STRIDE);
+        const uint32_t c = r / EV_HIST_STRIDE, b = r % EV_HIST_STRIDE;
+        if (b >= 32 || c >= P.n_cols) continue;
+        const uint32_t k = 32 * (P.col0 + c) + b;
+        atomicAdd(T.aux + (size_t)n * P.stride + k, (unsigned long long)v);
     }
 }
 
