@@ -109,6 +109,7 @@ struct pmb_batch {
     size_t zero_words = 0;              // event path: [0, zero_words) of d_bits is zeroed per execute
     size_t m_begin = 0, m_end = 0;      // event path: the M arrays of all jobs, [m_begin, m_end) of d_bits
     bool gather_m = false;              // M is gathered (mask_build_multi_kernel), not scattered
+    bool edge_list_ok = false;          // every array is shorter than 2^32 bits (edge_list_kernel's 32-bit offsets)
     bool pack_reads = false;            // F, R are packed from the sorted reads (pack_reads_multi_kernel)
     uint64_t* d_edge_prefix = nullptr; uint64_t edge_ctas = 0;      // edge_list_kernel, over the derive tasks
     PackTask* d_pack = nullptr; uint64_t* d_pack_prefix = nullptr; uint32_t n_pack = 0; uint64_t pack_chunks = 0;
@@ -688,6 +689,9 @@ static int prepare_impl(pmb_ctx* c, const pmb_chrom_args* a, uint32_t n, pmb_bat
         for (auto& j : b->jobs)
             if (j.a.n_intervals >= (1ull << 31)) b->gather_m = false;
         if (getenv("PMB_NO_GATHER")) b->gather_m = false;     // debug aid: always scatter M
+        b->edge_list_ok = true;
+        for (auto& j : b->jobs)
+            if ((uint64_t)j.array_words * 32 + 32ull * b->stride >= (1ull << 32)) b->edge_list_ok = false;
         b->pack_reads = getenv("PMB_NO_PACK") == nullptr;      // debug aid: always scatter F, R
         b->zero_words = b->gather_m ? b->m_begin : b->m_end;
     }
@@ -1021,7 +1025,7 @@ static int execute_events(pmb_ctx* c, pmb_batch* b)
         if (b->any_mscc || b->any_autocorr) {
             // run edges: from the interval list when M was gathered from it; the scan over M stays
             // behind it, gated on the same "unsorted" flag
-            const bool listed = b->gather_m && !getenv("PMB_NO_EDGE_LIST");
+            const bool listed = b->gather_m && b->edge_list_ok && !getenv("PMB_NO_EDGE_LIST");
             if (listed && G.ed_ctas) {
                 for (uint32_t col0 = 0; col0 < n_cols_total; col0 += 32) {
                     EdgeListParams E{col0, std::min(32u, n_cols_total - col0), b->max_shift, b->stride};

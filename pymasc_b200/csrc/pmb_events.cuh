@@ -901,32 +901,37 @@ __global__ void __launch_bounds__(256) edge_list_kernel(const DeriveTask* __rest
     for (uint32_t i = threadIdx.x; i < 2 * 32 * EV_HIST_STRIDE; i += blockDim.x) hist[i] = 0;
     __syncthreads();
 
-    // this lane's interval as array bits: a run of Mc starts at s and ends at t (first bit after it)
+    // this lane's interval as array bits: a run of Mc starts at s and ends at t (first bit after
+    // it).  What travels through the warp is the window start o = edge + edge_off + 32 col0 of
+    // each edge as ONE 32-bit value (the host only takes this path for arrays under 2^32 bits; the
+    // halo keeps every counted window, and the bit below it, inside the array).
     const uint32_t iv = (uint32_t)(cta - cta_prefix[lo_t]) * EDGE_INTERVALS_PER_CTA + 32u * warp + lane;
-    long long s = 0, t = 0;
+    const long long shift0 = (long long)T.edge_off + 32ll * P.col0;     // window start relative to the edge
+    uint32_t os = 0, ot = 0;
+    bool valid = false;
     if (iv < nI) {
         const long long b = T.begins[iv], e = T.ends[iv];
-        s = max(b + 1 - T.p_off, T.a_lo);
-        t = min(e + 1 - T.p_off, T.a_hi);
+        const long long s = max(b + 1 - T.p_off, T.a_lo), t = min(e + 1 - T.p_off, T.a_hi);
+        valid = s < t;
+        os = (uint32_t)(s + shift0);
+        ot = (uint32_t)(t + shift0);
     }
-    const bool valid = s < t;
     const unsigned vmask = __ballot_sync(0xFFFFFFFFu, valid);
     const uint32_t col_mask = lane < (int)P.n_cols ? 0xFFFFFFFFu : 0u;
-    const long long shift0 = (long long)T.edge_off + 32ll * P.col0;     // window start relative to the edge
+    const uint32_t w_last = T.array_words - 1;      // columns past max_shift may point past the array: clamp (masked)
 
-    // the two window words of lane `lane` for an edge at array bit a (zero outside the array)
-    auto fetch = [&](long long a, uint32_t& w0, uint32_t& w1, uint32_t& wm) {
-        const long long o = a + shift0;
-        const long long wi = (o >> 5) + lane;
-        w0 = (wi >= 0 && wi < W) ? __ldg(M + wi) : 0u;
-        w1 = (wi + 1 >= 0 && wi + 1 < W) ? __ldg(M + wi + 1) : 0u;
+    // the window words of lane `lane` for a window starting at array bit o
+    auto fetch = [&](uint32_t o, uint32_t& w0, uint32_t& w1, uint32_t& wm) {
+        const uint32_t wi = (o >> 5) + lane;
+        w0 = __ldg(M + min(wi, w_last));
+        w1 = __ldg(M + min(wi + 1, w_last));
         wm = 0u;
-        if ((o & 31) == 0) wm = (wi - 1 >= 0 && wi - 1 < W) ? __ldg(M + wi - 1) : 0u;   // bit o-1 (uniform branch)
+        if ((o & 31u) == 0u) wm = __ldg(M + min(wi - 1, w_last));      // bit o-1 (uniform branch)
     };
     Slices<2> sl;
     sl.reset();
-    auto count = [&](long long a, bool is_end, uint32_t w0, uint32_t w1, uint32_t wm) {
-        const uint32_t sh = (uint32_t)((a + shift0) & 31);
+    auto count = [&](uint32_t o, bool is_end, uint32_t w0, uint32_t w1, uint32_t wm) {
+        const uint32_t sh = o & 31u;
         sl.add_with(hist, lane, [&](uint32_t (&x)[2]) {
             const uint32_t m1 = __funnelshift_r(w0, w1, sh);
             const uint32_t m0 = sh ? __funnelshift_r(w0, w1, sh - 1u) : __funnelshift_r(wm, w0, 31u);
@@ -940,23 +945,22 @@ __global__ void __launch_bounds__(256) edge_list_kernel(const DeriveTask* __rest
     // before interval k is counted
     unsigned todo = vmask;
     uint32_t a0 = 0, a1 = 0, am = 0, b0 = 0, b1 = 0, bm = 0;        // start / end edge of the current interval
-    long long cs = 0, ct = 0;
+    uint32_t cs = 0, ct = 0;
     if (todo) {
         const int k = __ffs(todo) - 1;
         todo &= todo - 1;
-        cs = __shfl_sync(0xFFFFFFFFu, s, k);
-        ct = __shfl_sync(0xFFFFFFFFu, t, k);
+        cs = __shfl_sync(0xFFFFFFFFu, os, k);
+        ct = __shfl_sync(0xFFFFFFFFu, ot, k);
         fetch(cs, a0, a1, am);
         fetch(ct, b0, b1, bm);
         for (;;) {
-            uint32_t n0 = 0, n1 = 0, nm = 0, q0 = 0, q1 = 0, qm = 0;
-            long long ns = 0, nt = 0;
+            uint32_t n0 = 0, n1 = 0, nm = 0, q0 = 0, q1 = 0, qm = 0, ns = 0, nt = 0;
             const bool more = todo != 0;
             if (more) {
                 const int k2 = __ffs(todo) - 1;
                 todo &= todo - 1;
-                ns = __shfl_sync(0xFFFFFFFFu, s, k2);
-                nt = __shfl_sync(0xFFFFFFFFu, t, k2);
+                ns = __shfl_sync(0xFFFFFFFFu, os, k2);
+                nt = __shfl_sync(0xFFFFFFFFu, ot, k2);
                 fetch(ns, n0, n1, nm);
                 fetch(nt, q0, q1, qm);
             }
