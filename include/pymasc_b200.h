@@ -53,6 +53,12 @@ typedef enum {
 #define PMB_FLAG_MSCC     2u  /* compute dmp/mfwd/mrev/mscc[k]; needs intervals        */
 #define PMB_FLAG_AUTOCORR 4u  /* read-less chromosome: dmp[k] = sum_j M[j] M[j+k]      */
                               /* (mscc.pyx:207-215); other outputs untouched           */
+#define PMB_FLAG_SAME_TRACK 8u /* this MSCC job reads the mappability track of the PREVIOUS */
+                              /* job of the batch (same chrom_len and range, another read  */
+                              /* set: a multi-file run over one BigWig).  map_begin/map_end */
+                              /* are ignored; M and dmp[k] (popc(D_k), independent of the  */
+                              /* reads) are built once per run of such jobs and every job  */
+                              /* of the run reports the same dmp.                          */
 
 #define PMB_EXTRA_ALLOCATE_SIZE 100 /* mscc.pyx:118 */
 

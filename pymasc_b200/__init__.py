@@ -10,5 +10,6 @@ from .result import (  # noqa: F401
     MSCCGenomeWideResult, MSCCResult, NCCGenomeWideResult, NCCResult,
 )
 from .calculator import CCBitArrayCalculator, DeviceEngine  # noqa: F401
+from .multifile import MultiFileCalculation  # noqa: F401
 
 __version__ = "0.1.0"

@@ -14,7 +14,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("PYMASC_B200_LIB") or os.path.join(_HERE, "libpymasc_b200.so")   # override: tuning builds
 
 PMB_OK, PMB_ERR_CUDA, PMB_ERR_RANGE, PMB_ERR_ARG, PMB_ERR_NOMEM = 0, -1, -2, -3, -4
-FLAG_NCC, FLAG_MSCC, FLAG_AUTOCORR = 1, 2, 4
+FLAG_NCC, FLAG_MSCC, FLAG_AUTOCORR, FLAG_SAME_TRACK = 1, 2, 4, 8
 NCOUNTERS = 5
 COUNTER_ORDER = ("ncc", "dmp", "mfwd", "mrev", "mscc")
 
@@ -128,10 +128,12 @@ def _as_u32(a):
 
 
 class Job(object):
-    """One chromosome (or position shard) handed to the device."""
+    """One chromosome (or position shard) handed to the device.  ``track_key`` (host only)
+    names the mappability track the intervals come from: jobs of one chromosome with equal
+    keys may be merged into a FLAG_SAME_TRACK run (pymasc_b200.multifile)."""
 
     __slots__ = ("chrom_len", "read_len", "max_shift", "flags", "fwd_pos", "rev_pos",
-                 "map_begins", "map_ends", "lo", "hi")
+                 "map_begins", "map_ends", "lo", "hi", "track_key")
 
     def __init__(self, chrom_len, read_len, max_shift, flags, fwd_pos=None, rev_pos=None,
                  map_begins=None, map_ends=None, lo=0, hi=0):
@@ -140,6 +142,7 @@ class Job(object):
         self.fwd_pos, self.rev_pos = _as_u32(fwd_pos), _as_u32(rev_pos)
         self.map_begins, self.map_ends = _as_u32(map_begins), _as_u32(map_ends)
         self.lo, self.hi = int(lo), int(hi)
+        self.track_key = None
 
 
 class Device(object):

@@ -284,10 +284,17 @@ class CCBitArrayCalculator(object):
             r.calc_cc()
             self.ref2mscc_result[chrom] = r
 
-    def _compute_pending(self, fill=()):
-        """One device batch: every queued chromosome plus the mappable-length
-        autocorrelation of the read-less chromosomes in `fill` (mscc.pyx:181-215)."""
+    def _track_key(self, chrom):
+        return (id(self._bwfeeder), chrom)
+
+    def _collect_jobs(self, fill=()):
+        """Device jobs of every queued chromosome plus the mappable-length autocorrelation of
+        the read-less chromosomes in `fill` (mscc.pyx:181-215).  Returns (jobs, fills); the
+        outputs of `jobs`, in order, go to _apply_results."""
         jobs = [self._job_of(p) for p in self._pending]
+        for j, p in zip(jobs, self._pending):
+            if p.intervals is not None:
+                j.track_key = self._track_key(p.chrom)
         fills = []
         for chrom in fill:
             self._chr = chrom                                   # side effect of _fill_result
@@ -303,17 +310,26 @@ class CCBitArrayCalculator(object):
             except KeyError:
                 continue
             self._logging_info("Calc {} mappable length...".format(chrom))
-            jobs.append(_shim.Job(self.ref2genomelen[chrom], self._read_len, self._max_shift,
-                                  _shim.FLAG_AUTOCORR, None, None, iv[0], iv[1]))
+            job = _shim.Job(self.ref2genomelen[chrom], self._read_len, self._max_shift,
+                            _shim.FLAG_AUTOCORR, None, None, iv[0], iv[1])
+            job.track_key = self._track_key(chrom)
+            jobs.append(job)
             fills.append(res)
-        if not jobs:
-            return
-        outs = self._engine.run(jobs)
+        return jobs, fills
+
+    def _apply_results(self, outs, fills):
         for p, out in zip(self._pending, outs):
             self._store(p, out)
         for res, out in zip(fills, outs[len(self._pending):]):
             res.mappable_len = tuple(int(x) for x in out["dmp"])
         self._pending = []
+
+    def _compute_pending(self, fill=()):
+        """One device batch for everything _collect_jobs returns."""
+        jobs, fills = self._collect_jobs(fill)
+        if not jobs:
+            return
+        self._apply_results(self._engine.run(jobs), fills)
 
     # ------------------------------------------------------------------ public protocol
     def flush(self, chrom=None):

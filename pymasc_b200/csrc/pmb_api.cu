@@ -72,6 +72,7 @@ struct JobPlan {
     uint32_t n_tiles = 0;
     int mode = 0;              // MODE_NCC / MODE_MSCC / MODE_BOTH; autocorr -> MODE_NCC on M
     bool autocorr = false;
+    int owner = -1;            // PMB_FLAG_SAME_TRACK: the earlier job of the batch whose M this one reads
     // offsets (in uint32 words) into the batch's device buffers
     size_t in_fwd = 0, in_rev = 0, in_mb = 0, in_me = 0;
     size_t bits = 0;           // start of this job's arrays; each array_words long
@@ -444,9 +445,13 @@ static int plan_events(pmb_ctx* c, pmb_batch* b)
             e.edge_off = (int32_t)b->read_len - 1 - (int32_t)b->max_shift;
         }
         e.counters = b->d_counters + i * PMB_NCOUNTERS * b->stride;
-        e.aux = b->d_aux + i * 2 * (size_t)b->stride;
-        e.adirect = adirect0 + 2 * i;
-        e.agather = adirect0 + 2 * n + 2 * i;
+        // a job that shares its track reads the owner's edge sums and direct lags: finalize_dmp
+        // then writes the same dmp into its own counters, and nothing is built or scanned twice
+        const size_t io = j.owner >= 0 ? (size_t)j.owner : i;
+        if (j.owner >= 0) e.flags |= EVF_SHARED;
+        e.aux = b->d_aux + io * 2 * (size_t)b->stride;
+        e.adirect = adirect0 + 2 * io;
+        e.agather = adirect0 + 2 * n + 2 * io;
         e.totals = b->d_counters + n * PMB_NCOUNTERS * b->stride + 2 * i;
         const int64_t off = (int64_t)b->halo_words * 32 - j.origin_word * 32;   // chrom bit -> array bit
         e.a_lo = j.lo + off;
@@ -491,7 +496,7 @@ static int plan_events(pmb_ctx* c, pmb_batch* b)
                 pkp.push_back(pkp.back() + std::max<uint64_t>(1, (j.a.n_rev + PACK_CHUNK - 1) / PACK_CHUNK));
             }
             uint32_t* M = (j.autocorr || mscc) ? b->d_bits + j.bits_m : nullptr;
-            if (!M) continue;
+            if (!M || j.owner >= 0) continue;       // a shared track is built by its owner
             if (j.a.n_intervals) {
                 FillTask f{M, g, b->d_in + j.in_mb, b->d_in + j.in_me, 0, NEG, POS, j.nbits};
                 f.c_lo = j.lo; f.c_hi = j.hi;
@@ -618,7 +623,8 @@ static int prepare_impl(pmb_ctx* c, const pmb_chrom_args* a, uint32_t n, pmb_bat
         j.mode = (a[i].flags & PMB_FLAG_NCC ? MODE_NCC : 0) | (a[i].flags & PMB_FLAG_MSCC ? MODE_MSCC : 0);
         if (j.autocorr) j.mode = MODE_NCC;
         if (j.mode == 0) { c->err = "flags select nothing to compute"; return PMB_ERR_ARG; }
-        if ((j.mode & MODE_MSCC) && a[i].n_intervals && (!a[i].map_begin || !a[i].map_end)) {
+        if ((j.mode & MODE_MSCC) && !(a[i].flags & PMB_FLAG_SAME_TRACK) && a[i].n_intervals &&
+            (!a[i].map_begin || !a[i].map_end)) {
             c->err = "interval arrays missing"; return PMB_ERR_ARG;
         }
         if ((a[i].n_fwd && !a[i].fwd_pos) || (a[i].n_rev && !a[i].rev_pos)) {
@@ -628,6 +634,19 @@ static int prepare_impl(pmb_ctx* c, const pmb_chrom_args* a, uint32_t n, pmb_bat
         j.hi = a[i].range_hi ? (int64_t)a[i].range_hi : (int64_t)j.nbits;
         if (j.hi > (int64_t)j.nbits) j.hi = (int64_t)j.nbits;
         if (j.lo > j.hi) j.lo = j.hi;
+        if (a[i].flags & PMB_FLAG_SAME_TRACK) {
+            // same chromosome, range and intervals as the previous job (another read set over the
+            // same mappability track): M, Er/Or and dmp are built once, by the first job of the run
+            const JobPlan* p = i ? &b->jobs[i - 1] : nullptr;
+            if (!p || j.autocorr || !(j.mode & MODE_MSCC) || p->autocorr || !(p->mode & MODE_MSCC) ||
+                p->nbits != j.nbits || p->lo != j.lo || p->hi != j.hi) {
+                c->err = "PMB_FLAG_SAME_TRACK needs a preceding MSCC job with the same chrom_len and range";
+                return PMB_ERR_ARG;
+            }
+            j.owner = p->owner >= 0 ? p->owner : (int)i - 1;
+            j.a.n_intervals = b->jobs[j.owner].a.n_intervals;
+            j.a.map_begin = j.a.map_end = nullptr;
+        }
         j.origin_word = (j.lo >> 5) & ~(int64_t)3;
         total_words += (uint64_t)(((j.hi + 31) >> 5) - j.origin_word);
     }
@@ -636,7 +655,7 @@ static int prepare_impl(pmb_ctx* c, const pmb_chrom_args* a, uint32_t n, pmb_bat
     // inputs are so dense that there are more than 4 events per 32-bit word.
     uint64_t total_events = 0;
     for (uint32_t i = 0; i < n; i++) {
-        total_events += a[i].n_fwd + a[i].n_rev + 2 * a[i].n_intervals;
+        total_events += a[i].n_fwd + a[i].n_rev + (b->jobs[i].owner < 0 ? 2 * a[i].n_intervals : 0);
         b->any_ncc |= (a[i].flags & PMB_FLAG_NCC) && !(a[i].flags & PMB_FLAG_AUTOCORR);
         b->any_mscc |= (a[i].flags & PMB_FLAG_MSCC) && !(a[i].flags & PMB_FLAG_AUTOCORR);
         b->any_autocorr |= (a[i].flags & PMB_FLAG_AUTOCORR) != 0;
@@ -673,16 +692,19 @@ static int prepare_impl(pmb_ctx* c, const pmb_chrom_args* a, uint32_t n, pmb_bat
         }
         auto take = [&](uint64_t cnt) { size_t o = in_words; in_words += (cnt + 3) & ~3ull; return o; };
         if (!j.autocorr) { j.in_fwd = take(j.a.n_fwd); j.in_rev = take(j.a.n_rev); }
-        if ((j.mode & MODE_MSCC) || j.autocorr) { j.in_mb = take(j.a.n_intervals); j.in_me = take(j.a.n_intervals); }
+        if (j.owner >= 0) { j.in_mb = b->jobs[j.owner].in_mb; j.in_me = b->jobs[j.owner].in_me; }
+        else if ((j.mode & MODE_MSCC) || j.autocorr) { j.in_mb = take(j.a.n_intervals); j.in_me = take(j.a.n_intervals); }
     }
     b->in_words = in_words;
     if (b->path == 2) {
         b->m_begin = bits_words;
         for (auto& j : b->jobs)
-            if (j.autocorr || (j.mode & MODE_MSCC)) { j.bits_m = bits_words; bits_words += j.array_words; }
+            if (j.owner >= 0) j.bits_m = b->jobs[j.owner].bits_m;
+            else if (j.autocorr || (j.mode & MODE_MSCC)) { j.bits_m = bits_words; bits_words += j.array_words; }
         b->m_end = bits_words;
         for (auto& j : b->jobs)
-            if (!j.autocorr && (j.mode & MODE_MSCC)) { j.bits_d = bits_words; bits_words += j.array_words; }
+            if (j.owner >= 0) j.bits_d = b->jobs[j.owner].bits_d;
+            else if (!j.autocorr && (j.mode & MODE_MSCC)) { j.bits_d = bits_words; bits_words += j.array_words; }
         // M is gathered from the sorted intervals (the scatter kernels stay as the fallback)
         b->gather_k = 0;
         b->gather_m = b->read_len >= 2;   // rl 1: the second lag is negative
@@ -708,7 +730,7 @@ static int prepare_impl(pmb_ctx* c, const pmb_chrom_args* a, uint32_t n, pmb_bat
         for (uint32_t i = 0; i < n; i++) {
             const JobPlan& j = b->jobs[i];
             job_words[i] = (j.autocorr ? 0 : j.a.n_fwd + j.a.n_rev) +
-                           (((j.mode & MODE_MSCC) || j.autocorr) ? 2 * j.a.n_intervals : 0);
+                           ((((j.mode & MODE_MSCC) || j.autocorr) && j.owner < 0) ? 2 * j.a.n_intervals : 0);
         }
         size_t total = 0, acc = 0;
         for (size_t w : job_words) total += w;
@@ -736,7 +758,9 @@ static int prepare_impl(pmb_ctx* c, const pmb_chrom_args* a, uint32_t n, pmb_bat
             acc += job_words[i];
             const uint32_t made = (uint32_t)b->groups.size();
             // close the group once its share of the bytes is in (the last group takes the rest)
-            if (i + 1 == n || (made + 1 < want && (double)acc >= cum[made] * (double)total)) {
+            // (never in front of a job that shares the track of this group's jobs)
+            if (i + 1 == n || (made + 1 < want && (double)acc >= cum[made] * (double)total &&
+                               b->jobs[i + 1].owner < 0)) {
                 g.job_hi = i + 1;
                 b->groups.push_back(g);
                 g = pmb_batch::Group();
@@ -781,7 +805,7 @@ static int prepare_impl(pmb_ctx* c, const pmb_chrom_args* a, uint32_t n, pmb_bat
                 CU_TRY(c, up(j.in_fwd, j.a.fwd_pos, j.a.n_fwd));
                 CU_TRY(c, up(j.in_rev, j.a.rev_pos, j.a.n_rev));
             }
-            if ((j.mode & MODE_MSCC) || j.autocorr) {
+            if (((j.mode & MODE_MSCC) || j.autocorr) && j.owner < 0) {
                 CU_TRY(c, up(j.in_mb, j.a.map_begin, j.a.n_intervals));
                 CU_TRY(c, up(j.in_me, j.a.map_end, j.a.n_intervals));
             }

@@ -42,7 +42,8 @@
 namespace pmb {
 
 enum { EV_FWD = 0, EV_REV = 1, EV_EDGE = 2 };
-enum { EVF_NCC = 1u, EVF_MSCC = 2u, EVF_AUTOCORR = 4u };
+enum { EVF_NCC = 1u, EVF_MSCC = 2u, EVF_AUTOCORR = 4u,
+       EVF_SHARED = 8u };   // M, Er/Or, aux and the direct lags belong to an earlier job (same track)
 
 struct EventJob {
     const uint32_t* F;    // array word 0 of each array (halo included)
@@ -316,6 +317,7 @@ __global__ void __launch_bounds__(32 * EV_WARPS) event_window_kernel(const Event
         if (KIND != EV_EDGE && (J.flags & EVF_AUTOCORR)) return false;     // no reads in such a job
         if (KIND == EV_REV && !(J.flags & EVF_MSCC)) return false;
         if (KIND == EV_EDGE && !(J.flags & (EVF_MSCC | EVF_AUTOCORR))) return false;
+        if (KIND == EV_EDGE && (J.flags & EVF_SHARED)) return false;       // the owner's scan covers it
         return true;
     };
     // Region origins (array word index, multiple of 4) of tile word offset g0 of job J.

@@ -348,6 +348,115 @@ def test_inputs_packed_in_one_host_buffer(pdev):
                     assert np.array_equal(np.asarray(g[k]), np.asarray(w[k])), (k, pad, groups)
 
 
+# ----------------------------------------------------------------- several read sets, one track
+@pytest.mark.parametrize("groups", [1, 3])
+def test_read_sets_sharing_one_track(pdev, groups):
+    """BASELINE config 5 (multi-file run over one BigWig): FLAG_SAME_TRACK jobs read the M,
+    Er/Or, edge sums and direct lags of the run's first job.  Every job must count exactly what
+    it counts alone with its own copy of the intervals -- MSCC only, NCC+MSCC, with H2D groups,
+    next to unrelated jobs, for sorted tracks (gather build + edge list) and for unsorted ones
+    (scatter build + M scan fallback)."""
+    dev = pdev
+    rl, D = 36, 300
+    S = _shim.FLAG_SAME_TRACK
+    tracks, jobs, wants = [], [], []
+    for c, (L, sorted_track) in enumerate([(90000, True), (150000, False), (40000, True)]):
+        _, _, b, e = random_case(200 + c, L, rl, 10)
+        if not sorted_track:
+            b, e = b[::-1].copy(), e[::-1].copy()
+        for f in range(3):
+            fwd, rev, _, _ = random_case(210 + 10 * c + f, L, rl, max(8, L // (10 + 5 * f)), with_track=False)
+            flags = _shim.FLAG_MSCC | (_shim.FLAG_NCC if (c + f) % 2 else 0)
+            if f == 2 and c == 0:
+                fwd = fwd[:0]                                    # a file without forward reads here
+            jobs.append(_shim.Job(L, rl, D, flags | (S if f else 0), fwd, rev,
+                                  None if f else b, None if f else e))
+            wants.append(cc_oracle.chrom_counts(L, rl, D, fwd, rev, b, e, skip_ncc=not flags & _shim.FLAG_NCC))
+        if c == 0:      # an unrelated NCC-only job and an autocorrelation between the runs
+            fwd, rev, b2, e2 = random_case(300, 30000, rl, 900)
+            jobs.append(_shim.Job(30000, rl, D, _shim.FLAG_NCC, fwd, rev))
+            wants.append(cc_oracle.chrom_counts(30000, rl, D, fwd, rev))
+            jobs.append(_shim.Job(30000, rl, D, _shim.FLAG_AUTOCORR, None, None, b2, e2))
+            wants.append({"dmp": cc_oracle.mappable_autocorr(30000, rl, D, b2, e2)})
+    dev.set_option("h2d_groups", groups)
+    try:
+        for got, want in zip(dev.run_batch(jobs), wants):
+            assert sorted(got) == sorted(want)
+            for k in want:
+                assert np.array_equal(np.asarray(got[k]), np.asarray(want[k])), k
+        # resident inputs, executed twice (the second execute is one ungrouped pass)
+        dev.set_option("async_h2d", 1)
+        batch = dev.prepare(jobs)
+        for _ in range(2):
+            batch.execute()
+            for got, want in zip(batch.fetch(), wants):
+                for k in want:
+                    assert np.array_equal(np.asarray(got[k]), np.asarray(want[k])), k
+        batch.free()
+    finally:
+        dev.set_option("async_h2d", 0)
+        dev.set_option("h2d_groups", 4)
+
+
+def test_shared_track_position_shards_and_short_reads(dev):
+    """FLAG_SAME_TRACK with position shards (the runs share range_lo/range_hi) and with
+    read_len 1 (no gathered M: the scan-based edge kernel runs, and must skip the followers)."""
+    S = _shim.FLAG_SAME_TRACK
+    for rl, D, lo, hi in ((36, 200, 20000 + 32, 61000), (1, 70, 0, 0)):
+        L = 80000
+        _, _, b, e = random_case(400 + rl, L, max(rl, 2), 10)
+        jobs, wants = [], []
+        for f in range(3):
+            fwd, rev, _, _ = random_case(410 + f, L, max(rl, 2), 4000, with_track=False)
+            jobs.append(_shim.Job(L, rl, D, 3 | (S if f else 0), fwd, rev, None if f else b, None if f else e, lo, hi))
+            wants.append(cc_oracle.chrom_counts(L, rl, D, fwd, rev, b, e, lo=lo, hi=hi or None))
+        try:
+            for path in PATHS:
+                dev.set_option("path", path)
+                for got, want in zip(dev.run_batch(jobs), wants):
+                    for k in want:
+                        assert np.array_equal(np.asarray(got[k]), np.asarray(want[k])), (k, rl, path)
+        finally:
+            dev.set_option("path", 0)
+
+
+def test_shared_track_flag_needs_a_matching_owner(dev):
+    S = _shim.FLAG_SAME_TRACK
+    fwd, rev, b, e = random_case(1, 5000, 20, 100)
+    bad = [
+        [_shim.Job(5000, 20, 50, 3 | S, fwd, rev)],                                            # first job
+        [_shim.Job(5000, 20, 50, 1, fwd, rev), _shim.Job(5000, 20, 50, 3 | S, fwd, rev)],      # owner has no track
+        [_shim.Job(5000, 20, 50, 3, fwd, rev, b, e), _shim.Job(6000, 20, 50, 3 | S, fwd, rev)],   # other chromosome
+        [_shim.Job(5000, 20, 50, 3, fwd, rev, b, e), _shim.Job(5000, 20, 50, 3 | S, fwd, rev, None, None, 64, 2000)],
+        [_shim.Job(5000, 20, 50, 3, fwd, rev, b, e), _shim.Job(5000, 20, 50, 1 | S, fwd, rev)],   # follower without MSCC
+    ]
+    for jobs in bad:
+        with pytest.raises(ValueError):
+            dev.run_batch(jobs)
+
+
+def test_multifile_calculation_on_the_device():
+    """MultiFileCalculation (one batch, shared tracks) against calculators finished alone."""
+    from pymasc_b200 import MultiFileCalculation
+    spec = helpers.TOY_SPECS[0]
+    toys = [helpers.make_toy(dict(spec, seed=spec["seed"] + 100 * f)) for f in range(3)]
+    feeder = helpers.ListFeeder(toys[0]["tracks"])
+    del toys[2]["reads"]["c1"]
+    alone, together = [], []
+    for t in toys:
+        for dst in (alone, together):
+            c = CCBitArrayCalculator(spec["D"], spec["rl"], t["references"], t["lengths"], feeder, spec["skip_ncc"])
+            for chrom, r in t["reads"].items():
+                c.feed_batch(chrom, r["pos"], r["readlen"], r["is_reverse"])
+            dst.append(c)
+    for c in alone:
+        c.finishup_calculation()
+    MultiFileCalculation(together).finishup_calculation()
+    for a, b in zip(alone, together):
+        helpers.assert_snapshots_equal(helpers.snapshot_whole(b.get_whole_result()),
+                                       helpers.snapshot_whole(a.get_whole_result()), rtol=RTOL)
+
+
 # ----------------------------------------------------------------- the reference's own pins
 def test_fixture_golden_tables_through_the_calculator():
     """configs[0]: tests/data ChIP-seq fixture, -d 300 -q 10 -r 36, against tests/golden."""

@@ -1,0 +1,95 @@
+"""Multi-file runs over one mappability track (BASELINE config 5): the merged batch must answer
+every calculator exactly as if it had been finished alone.  Host logic here (OracleEngine stands
+in for the device); the device side of FLAG_SAME_TRACK is tested in tests/test_gpu_parity.py."""
+import numpy as np
+import pytest
+
+import helpers
+from oracle_engine import OracleEngine
+from pymasc_b200 import CCBitArrayCalculator, MultiFileCalculation, _shim
+from pymasc_b200.multifile import merge_shared_tracks
+
+
+def toy_files(spec, n_files):
+    """n_files read sets over the tracks of one toy."""
+    toys = []
+    for f in range(n_files):
+        s = dict(spec, seed=spec["seed"] + 100 * f)
+        toys.append(helpers.make_toy(s))
+    for t in toys[1:]:
+        t["tracks"] = toys[0]["tracks"]
+    return toys
+
+
+def feed(calc, toy):
+    for chrom, r in toy["reads"].items():
+        calc.feed_batch(chrom, r["pos"], r["readlen"], r["is_reverse"])
+
+
+@pytest.mark.parametrize("spec", [helpers.TOY_SPECS[0], helpers.TOY_SPECS[1], helpers.TOY_SPECS[7]],
+                         ids=lambda s: s["name"])
+def test_merged_run_equals_separate_runs(spec):
+    toys = toy_files(spec, 3)
+    # file 2 has no reads on the first chromosome: its job there is an autocorrelation fill
+    del toys[2]["reads"]["c1"]
+    feeder = helpers.ListFeeder(toys[0]["tracks"])
+    engine = OracleEngine()
+    alone, together = [], []
+    for t in toys:
+        for dst, eng in ((alone, OracleEngine()), (together, engine)):
+            c = CCBitArrayCalculator(spec["D"], spec["rl"], t["references"], t["lengths"], feeder,
+                                     spec["skip_ncc"], None, None, engine=eng)
+            feed(c, t)
+            dst.append(c)
+    for c in alone:
+        c.finishup_calculation()
+    MultiFileCalculation(together).finishup_calculation()
+    assert len(engine.batches) == 1                      # one device batch for all files
+    for a, b in zip(alone, together):
+        helpers.assert_snapshots_equal(helpers.snapshot_whole(b.get_whole_result()),
+                                       helpers.snapshot_whole(a.get_whole_result()))
+
+
+def test_merge_forms_runs_and_collapses_fills():
+    F, M, A, S = _shim.FLAG_NCC, _shim.FLAG_MSCC, _shim.FLAG_AUTOCORR, _shim.FLAG_SAME_TRACK
+    b, e = np.array([1, 50], np.uint32), np.array([20, 90], np.uint32)
+
+    def job(flags, L, key):
+        j = _shim.Job(L, 10, 30, flags, [3], [40], b if key else None, e if key else None)
+        j.track_key = key
+        return j
+
+    lists = [
+        [job(F | M, 1000, ("t", "c1")), job(F | M, 2000, ("t", "c2")), job(A, 500, ("t", "c3"))],
+        [job(F | M, 1000, ("t", "c1")), job(F, 2000, None), job(A, 500, ("t", "c3"))],
+        [job(F | M, 1000, ("u", "c1")), job(F | M, 2000, ("t", "c2"))],      # another track on c1
+    ]
+    merged, route = merge_shared_tracks(lists)
+    flags = [(j.chrom_len, j.flags) for j in merged]
+    assert flags == [(1000, F | M), (1000, F | M | S), (2000, F | M), (2000, F | M | S),
+                     (500, A), (2000, F), (1000, F | M)]
+    assert route == [[0, 2, 4], [1, 5, 4], [6, 3]]
+    assert merged[1].map_begins.size == 0 and merged[0].map_begins.size == 2
+    assert merged[1].fwd_pos is lists[1][0].fwd_pos          # reads are not copied
+
+
+def test_calculators_with_different_geometry_get_their_own_batches():
+    spec = helpers.TOY_SPECS[0]
+    toys = toy_files(spec, 2)
+    feeder = helpers.ListFeeder(toys[0]["tracks"])
+    engine = OracleEngine()
+    calcs = []
+    for t, rl in zip(toys, (20, 24)):
+        c = CCBitArrayCalculator(spec["D"], rl, t["references"], t["lengths"], feeder, False,
+                                 engine=engine)
+        feed(c, t)
+        calcs.append(c)
+    MultiFileCalculation(calcs).finishup_calculation()
+    assert len(engine.batches) == 2
+    for c, t, rl in zip(calcs, toys, (20, 24)):
+        ref = CCBitArrayCalculator(spec["D"], rl, t["references"], t["lengths"], feeder, False,
+                                   engine=OracleEngine())
+        feed(ref, t)
+        ref.finishup_calculation()
+        helpers.assert_snapshots_equal(helpers.snapshot_whole(c.get_whole_result()),
+                                       helpers.snapshot_whole(ref.get_whole_result()))
