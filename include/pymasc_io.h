@@ -1,0 +1,91 @@
+/*
+ * pymasc_io.h -- C ABI of libpymasc_io.so: host-side BAM (BGZF) and BigWig decoding into the
+ * packed arrays that libpymasc_b200.so consumes (include/pymasc_b200.h).  Plain C / zlib /
+ * pthreads; no CUDA in this library.  north_star keeps BAM/BigWig decoding on the host; the
+ * reference does it through pysam and pyBigWig, neither of which exists in this image.
+ *
+ * Reference interfaces replaced (paths relative to the PyMaSC checkout):
+ *   pmio_bam_load ............ the `for read in AlignmentFile(path)` loops of
+ *                              PyMaSC/handler/calc.py:140-153 and handler/worker.py:126-132 with
+ *                              the filter of handler/read.py:62-90 (read2, MAPQ, unmapped,
+ *                              duplicate) and the coordinate rules of handler/read.py:132-149
+ *                              (pos = reference_start + 1, readlen = infer_query_length()).
+ *   pmio_bam_readlen_hist .... the length counter of estimate_readlen, core/readlen.pyx:130-160
+ *                              (not unmapped, not duplicate, MAPQ >= criteria; read2 included).
+ *   pmio_bw_open / _intervals  BigWigReader.__init__ / .fetch, reader/bigwig.pyx:114-177
+ *                              (pyBigWig.open, .chroms(), .intervals(chrom, 0, size), value filter).
+ *
+ * Every function returns 0 or a negative pmio_status; text in pmio_last_error() (thread-local).
+ * Arrays returned by the getters are owned by the handle and live until it is freed (BigWig:
+ * until the next pmio_bw_intervals call on the same handle).
+ */
+#ifndef PYMASC_IO_H
+#define PYMASC_IO_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef enum {
+    PMIO_OK = 0,
+    PMIO_ERR_IO = -1,       /* open / read failed                                   */
+    PMIO_ERR_FORMAT = -2,   /* not a BAM / BigWig file, or a corrupt one            */
+    PMIO_ERR_ARG = -3,
+    PMIO_ERR_NOMEM = -4,
+    PMIO_ERR_KEY = -5       /* chromosome not in the file (KeyError on the Python side) */
+} pmio_status;
+
+const char *pmio_last_error(void);
+
+/* ------------------------------------------------------------------ BAM */
+typedef struct pmio_bam pmio_bam;
+
+typedef struct {
+    uint64_t n_records;     /* alignment records in the file                               */
+    uint64_t n_with_ref;    /* records with a reference (readlen.pyx: `nreads`)           */
+    uint64_t n_unmapped;    /* of those, flag 0x4                                          */
+    uint64_t n_paired;      /* of those, flag 0x1                                          */
+    uint64_t n_read2;       /* of those, paired and flag 0x80                              */
+    uint64_t n_accepted;    /* records handed to the calculator (handler/read.py rules)   */
+    uint32_t sorted;        /* 1 if the accepted reads are coordinate sorted: no reference */
+                            /* revisited, positions non-decreasing (mscc.pyx:351-366)     */
+    uint32_t reserved;
+} pmio_bam_stats;
+
+/* Decode the whole file: BGZF blocks are inflated on `threads` threads (0 = all cores), records
+ * are filtered (skip read2, MAPQ < mapq_criteria, unmapped, duplicate, no reference, no CIGAR)
+ * and packed per reference in file order. */
+int  pmio_bam_load(const char *path, int mapq_criteria, int threads, pmio_bam **out);
+void pmio_bam_free(pmio_bam *b);
+int  pmio_bam_stats_get(const pmio_bam *b, pmio_bam_stats *s);
+uint32_t    pmio_bam_n_refs(const pmio_bam *b);
+const char *pmio_bam_ref_name(const pmio_bam *b, uint32_t i);
+uint64_t    pmio_bam_ref_len(const pmio_bam *b, uint32_t i);
+/* Accepted reads of reference i: 1-based leftmost base, query length (CIGAR M/I/S/=/X), strand
+ * (1 = reverse). */
+int  pmio_bam_reads(const pmio_bam *b, uint32_t i, const uint32_t **pos, const uint32_t **qlen,
+                    const uint8_t **is_reverse, uint64_t *n);
+/* Query-length histogram for the read-length estimator, ascending by length. */
+int  pmio_bam_readlen_hist(const pmio_bam *b, const uint32_t **lengths, const uint64_t **counts,
+                           uint32_t *n);
+
+/* ------------------------------------------------------------------ BigWig */
+typedef struct pmio_bw pmio_bw;
+
+int  pmio_bw_open(const char *path, pmio_bw **out);
+void pmio_bw_close(pmio_bw *w);
+uint32_t    pmio_bw_n_chroms(const pmio_bw *w);
+const char *pmio_bw_chrom_name(const pmio_bw *w, uint32_t i);
+uint64_t    pmio_bw_chrom_len(const pmio_bw *w, uint32_t i);
+/* All intervals of `chrom` with value >= threshold (every interval when threshold <= 0, as
+ * reader/bigwig.pyx:171-175 does), in file order: 0-based half-open begins/ends and the
+ * float32 values.  PMIO_ERR_KEY when the file has no such chromosome. */
+int  pmio_bw_intervals(pmio_bw *w, const char *chrom, float threshold, const uint32_t **begins,
+                       const uint32_t **ends, const float **values, uint64_t *n);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* PYMASC_IO_H */

@@ -1,0 +1,267 @@
+"""BAM and BigWig readers over libpymasc_io.so (include/pymasc_io.h): binary files in, packed
+numpy arrays out -- the host-side producers of what the CUDA path consumes.
+
+The reference reads BAM through pysam and BigWig through pyBigWig; neither exists in this image
+(SURVEY.md 8f rank 3), so the on-disk formats are decoded natively (pymasc_b200/csrc/pmb_io.cpp:
+multi-threaded BGZF inflate, one filtering pass over the records; bbi B+ tree / R-tree walk).
+Interfaces follow the reference:
+
+* ``BigWigReader``      PyMaSC/reader/bigwig.pyx:100-200 -- ``chromsizes``, ``fetch(valfilter,
+                        chrom)`` (KeyError for an unknown chromosome), ``disable_progress_bar``,
+                        ``close``; plus ``fetch_arrays`` -- the packed form the calculator prefers.
+* ``BamFile``           the parts of pysam.AlignmentFile that PyMaSC uses (``references``,
+                        ``lengths``) plus the packed per-chromosome reads, already filtered by
+                        the rules of PyMaSC/handler/read.py:62-90 and :132-149.
+* ``estimate_readlen``  PyMaSC/core/readlen.pyx:89-177 (MEAN / MEDIAN / MODE / MIN / MAX over
+                        the query lengths of mapped, non-duplicate reads with MAPQ >= criteria).
+* ``feed_bam``          the read loop of PyMaSC/handler/calc.py:140-161 as one ``feed_batch``
+                        per chromosome.
+"""
+import ctypes
+import os
+
+import numpy as np
+
+from .exceptions import ReadUnsortedError
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.environ.get("PYMASC_IO_LIB") or os.path.join(_HERE, "libpymasc_io.so")
+
+EXPORTS = (
+    "pmio_last_error", "pmio_bam_load", "pmio_bam_free", "pmio_bam_stats_get", "pmio_bam_n_refs",
+    "pmio_bam_ref_name", "pmio_bam_ref_len", "pmio_bam_reads", "pmio_bam_readlen_hist",
+    "pmio_bw_open", "pmio_bw_close", "pmio_bw_n_chroms", "pmio_bw_chrom_name", "pmio_bw_chrom_len",
+    "pmio_bw_intervals",
+)
+PMIO_ERR_IO, PMIO_ERR_FORMAT, PMIO_ERR_ARG, PMIO_ERR_NOMEM, PMIO_ERR_KEY = -1, -2, -3, -4, -5
+
+
+class BamStats(ctypes.Structure):
+    _fields_ = [("n_records", ctypes.c_uint64), ("n_with_ref", ctypes.c_uint64),
+                ("n_unmapped", ctypes.c_uint64), ("n_paired", ctypes.c_uint64),
+                ("n_read2", ctypes.c_uint64), ("n_accepted", ctypes.c_uint64),
+                ("sorted", ctypes.c_uint32), ("reserved", ctypes.c_uint32)]
+
+
+_lib = None
+
+
+def load_library():
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise OSError("libpymasc_io.so is missing (%s). Build it with `python -m pymasc_b200.build`."
+                      % LIB_PATH)
+    L = ctypes.CDLL(LIB_PATH)
+    vp, vpp = ctypes.c_void_p, ctypes.POINTER(ctypes.c_void_p)
+    u32pp = ctypes.POINTER(ctypes.POINTER(ctypes.c_uint32))
+    L.pmio_last_error.restype = ctypes.c_char_p
+    L.pmio_bam_load.argtypes = [ctypes.c_char_p, ctypes.c_int, ctypes.c_int, vpp]
+    L.pmio_bam_free.argtypes = [vp]
+    L.pmio_bam_free.restype = None
+    L.pmio_bam_stats_get.argtypes = [vp, ctypes.POINTER(BamStats)]
+    L.pmio_bam_n_refs.argtypes = [vp]
+    L.pmio_bam_n_refs.restype = ctypes.c_uint32
+    L.pmio_bam_ref_name.argtypes = [vp, ctypes.c_uint32]
+    L.pmio_bam_ref_name.restype = ctypes.c_char_p
+    L.pmio_bam_ref_len.argtypes = [vp, ctypes.c_uint32]
+    L.pmio_bam_ref_len.restype = ctypes.c_uint64
+    L.pmio_bam_reads.argtypes = [vp, ctypes.c_uint32, u32pp, u32pp,
+                                 ctypes.POINTER(ctypes.POINTER(ctypes.c_uint8)),
+                                 ctypes.POINTER(ctypes.c_uint64)]
+    L.pmio_bam_readlen_hist.argtypes = [vp, u32pp, ctypes.POINTER(ctypes.POINTER(ctypes.c_uint64)),
+                                        ctypes.POINTER(ctypes.c_uint32)]
+    L.pmio_bw_open.argtypes = [ctypes.c_char_p, vpp]
+    L.pmio_bw_close.argtypes = [vp]
+    L.pmio_bw_close.restype = None
+    L.pmio_bw_n_chroms.argtypes = [vp]
+    L.pmio_bw_n_chroms.restype = ctypes.c_uint32
+    L.pmio_bw_chrom_name.argtypes = [vp, ctypes.c_uint32]
+    L.pmio_bw_chrom_name.restype = ctypes.c_char_p
+    L.pmio_bw_chrom_len.argtypes = [vp, ctypes.c_uint32]
+    L.pmio_bw_chrom_len.restype = ctypes.c_uint64
+    L.pmio_bw_intervals.argtypes = [vp, ctypes.c_char_p, ctypes.c_float, u32pp, u32pp,
+                                    ctypes.POINTER(ctypes.POINTER(ctypes.c_float)),
+                                    ctypes.POINTER(ctypes.c_uint64)]
+    _lib = L
+    return L
+
+
+def _raise(L, rc, path=None):
+    msg = L.pmio_last_error().decode(errors="replace")
+    if rc == PMIO_ERR_KEY:
+        raise KeyError(msg)
+    if rc == PMIO_ERR_IO:
+        raise IOError(msg)
+    if rc == PMIO_ERR_NOMEM:
+        raise MemoryError(msg)
+    raise ValueError(msg)
+
+
+def _copy(ptr, n, dtype):
+    if n == 0:
+        return np.zeros(0, dtype)
+    return np.ctypeslib.as_array(ptr, shape=(n,)).astype(dtype, copy=True)
+
+
+# ---------------------------------------------------------------------------------------- BAM
+class BamFile(object):
+    """A decoded BAM file: header plus the accepted reads as packed arrays per reference.
+
+    ``reads[chrom]`` is a dict of ``pos`` (1-based leftmost base), ``readlen`` (query length) and
+    ``is_reverse`` in file order -- the arguments of ``CCBitArrayCalculator.feed_batch``.
+    Filter: skip read2, MAPQ < mapq_criteria, unmapped, duplicate, records without a reference or
+    a CIGAR (PyMaSC/handler/read.py:62-90, :132-143)."""
+
+    def __init__(self, path, mapq_criteria=1, threads=0):
+        path = str(path)
+        if not os.path.exists(path):
+            raise IOError("input file '{0}' dose not exist.".format(path))
+        L = load_library()
+        h = ctypes.c_void_p()
+        rc = L.pmio_bam_load(path.encode(), int(mapq_criteria), int(threads), ctypes.byref(h))
+        if rc != 0:
+            _raise(L, rc)
+        try:
+            n = L.pmio_bam_n_refs(h)
+            self.references = tuple(L.pmio_bam_ref_name(h, i).decode() for i in range(n))
+            self.lengths = tuple(int(L.pmio_bam_ref_len(h, i)) for i in range(n))
+            st = BamStats()
+            L.pmio_bam_stats_get(h, ctypes.byref(st))
+            self.stats = {k: int(getattr(st, k)) for k, _ in BamStats._fields_ if k != "reserved"}
+            self.sorted = bool(st.sorted)
+            self.reads = {}
+            p, q = ctypes.POINTER(ctypes.c_uint32)(), ctypes.POINTER(ctypes.c_uint32)()
+            r, cnt = ctypes.POINTER(ctypes.c_uint8)(), ctypes.c_uint64()
+            for i, name in enumerate(self.references):
+                L.pmio_bam_reads(h, i, ctypes.byref(p), ctypes.byref(q), ctypes.byref(r), ctypes.byref(cnt))
+                if cnt.value:
+                    self.reads[name] = {"pos": _copy(p, cnt.value, np.int64),
+                                        "readlen": _copy(q, cnt.value, np.int64),
+                                        "is_reverse": _copy(r, cnt.value, bool)}
+            hl, hc, hn = ctypes.POINTER(ctypes.c_uint32)(), ctypes.POINTER(ctypes.c_uint64)(), ctypes.c_uint32()
+            L.pmio_bam_readlen_hist(h, ctypes.byref(hl), ctypes.byref(hc), ctypes.byref(hn))
+            self.readlen_counter = dict(zip(_copy(hl, hn.value, np.int64).tolist(),
+                                            _copy(hc, hn.value, np.int64).tolist()))
+        finally:
+            L.pmio_bam_free(h)
+        self.path = path
+        self.mapq_criteria = int(mapq_criteria)
+
+
+def _mean(c):
+    return int(round(sum(length * freq for length, freq in c.items()) / float(sum(c.values()))))
+
+
+def _median(c):
+    # core/readlen.pyx:41-69
+    num = sum(c.values())
+    target = num / 2
+    acc = 0
+    lengths = sorted(c)
+    if num % 2:
+        for l in lengths:
+            acc += c[l]
+            if target <= acc:
+                return l
+    else:
+        for i, l in enumerate(lengths):
+            acc += c[l]
+            if target < acc:
+                return l
+            elif target == acc:
+                return int(round((l + float(lengths[i + 1])) / 2))
+
+
+def _mode(c):
+    return [k for k, v in sorted(c.items(), key=lambda x: x[1])][-1]
+
+
+ESTFUNCTIONS = dict(MEAN=_mean, MEDIAN=_median, MODE=_mode, MIN=min, MAX=max)
+
+
+def estimate_readlen(path, esttype="MEDIAN", mapq_criteria=1, threads=0):
+    """core/readlen.pyx:89-177.  `path` may be a BamFile already decoded with the same MAPQ."""
+    bam = path if isinstance(path, BamFile) else BamFile(path, mapq_criteria, threads)
+    if bam.mapq_criteria != int(mapq_criteria):
+        raise ValueError("BamFile was decoded with another MAPQ criterion")
+    if not bam.readlen_counter:
+        raise ValueError("There is no read to estimate the read length from.")
+    return ESTFUNCTIONS[esttype](bam.readlen_counter)
+
+
+def feed_bam(calc, bam):
+    """Feed every accepted read of `bam` to a calculator, one ``feed_batch`` per chromosome in
+    file order (handler/calc.py:140-153), raising ReadUnsortedError as the per-read loop would."""
+    if not bam.sorted:
+        raise ReadUnsortedError
+    order = [c for c in bam.references if c in bam.reads]
+    # chromosomes appear in the file in the order of their first accepted read; for a sorted
+    # file that is the header order restricted to chromosomes with reads
+    for chrom in order:
+        r = bam.reads[chrom]
+        calc.feed_batch(chrom, r["pos"], r["readlen"], r["is_reverse"])
+
+
+# ------------------------------------------------------------------------------------- BigWig
+class BigWigReader(object):
+    """reader/bigwig.pyx:100-200 over the native decoder."""
+
+    def __init__(self, path):
+        path_str = str(path)
+        if not os.path.exists(path_str) and path_str != '-':
+            raise IOError("input file '{0}' dose not exist.".format(path_str))
+        if path_str == '-':
+            raise ValueError("BigWig input from stdin is not supported")
+        self.path = path_str
+        self.closed = False
+        self._L = load_library()
+        h = ctypes.c_void_p()
+        rc = self._L.pmio_bw_open(path_str.encode(), ctypes.byref(h))
+        if rc != 0:
+            self.closed = True
+            if rc == PMIO_ERR_FORMAT:
+                raise IOError("Failed to open BigWig file: {} ({})".format(
+                    path_str, self._L.pmio_last_error().decode()))
+            _raise(self._L, rc)
+        self._h = h
+        n = self._L.pmio_bw_n_chroms(h)
+        self.chromsizes = {self._L.pmio_bw_chrom_name(h, i).decode(): int(self._L.pmio_bw_chrom_len(h, i))
+                           for i in range(n)}
+
+    def fetch_arrays(self, valfilter, chrom, with_values=False):
+        """(begins, ends[, values]) of the intervals with value >= valfilter: 0-based half-open
+        uint32 arrays in file order.  KeyError for a chromosome the file does not have."""
+        if self.closed:
+            raise ValueError("I/O operation on closed BigWig file")
+        if chrom not in self.chromsizes:
+            raise KeyError(chrom)
+        b, e = ctypes.POINTER(ctypes.c_uint32)(), ctypes.POINTER(ctypes.c_uint32)()
+        v, n = ctypes.POINTER(ctypes.c_float)(), ctypes.c_uint64()
+        rc = self._L.pmio_bw_intervals(self._h, chrom.encode(), float(valfilter), ctypes.byref(b),
+                                       ctypes.byref(e), ctypes.byref(v), ctypes.byref(n))
+        if rc != 0:
+            _raise(self._L, rc)
+        out = (_copy(b, n.value, np.uint32), _copy(e, n.value, np.uint32))
+        return out + (_copy(v, n.value, np.float32),) if with_values else out
+
+    def fetch(self, valfilter, chrom):
+        """List of (begin, end, value) tuples, as BigWigFileIterator yields them."""
+        b, e, v = self.fetch_arrays(valfilter, chrom, with_values=True)
+        return list(zip(b.tolist(), e.tolist(), v.astype(np.float64).tolist()))
+
+    def disable_progress_bar(self):
+        pass
+
+    def close(self):
+        if not self.closed:
+            self._L.pmio_bw_close(self._h)
+            self._h = None
+            self.closed = True
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:       # noqa: BLE001 -- interpreter shutdown
+            pass
