@@ -16,9 +16,15 @@ Writes, beside this script:
                             (oracle/_ref) on the fixture (-d 300 -r 36, NCC+MSCC) and on the
                             toy cases of tests/helpers.py (host semantics: duplicates,
                             read-less chromosomes, missing tracks, skip_ncc, list lengths).
+  ENCFF000RMB-test.bam, hg19_36mer-test.bigwig
+                            the reference's binary test DATA files (tests/data), byte for byte:
+                            the BAM / BigWig twins of the .sam / .bedGraph the arrays above were
+                            parsed from -- inputs of tests/test_io_native.py (pymasc_b200.io_native
+                            must decode them to exactly fixture_encff000rmb.npz).
 """
 import json
 import os
+import shutil
 import sys
 
 import numpy as np
@@ -44,7 +50,14 @@ def table(path, cols):
     return {c: [r[i] for r in rows[1:]] for c, i in zip(cols, idx)}
 
 
+def copy_binary_fixtures():
+    for name in ("ENCFF000RMB-test.bam", "hg19_36mer-test.bigwig"):
+        shutil.copyfile(os.path.join(DATA, name), os.path.join(HERE, name))
+        os.chmod(os.path.join(HERE, name), 0o644)
+
+
 def main():
+    copy_binary_fixtures()
     refs, lens, reads = read_sam(os.path.join(DATA, "ENCFF000RMB-test.sam"), mapq_criteria=10)
     assert list(reads) == ["chr1"]
     tracks = read_bedgraph(os.path.join(DATA, "hg19_36mer-test.bedGraph"))

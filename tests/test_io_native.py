@@ -1,0 +1,237 @@
+"""libpymasc_io.so (include/pymasc_io.h) and pymasc_b200.io_native: native BAM / BigWig decoding.
+
+Pins: the reference's own binary fixtures (tests/golden/ENCFF000RMB-test.bam and
+hg19_36mer-test.bigwig, copied byte for byte from the reference's tests/data by
+tests/golden/make_golden.py) must decode to exactly the arrays parsed from their text twins
+(.sam / .bedGraph -> fixture_encff000rmb.npz); synthetic files written by tests/io_writers.py
+cover what the fixtures lack.  No GPU needed.
+"""
+import ctypes
+import os
+import struct
+
+import numpy as np
+import pytest
+
+import helpers
+import io_writers as W
+from oracle_engine import OracleEngine
+from pymasc_b200 import CCBitArrayCalculator, ReadUnsortedError, io_native
+
+BAM = os.path.join(helpers.GOLDEN, "ENCFF000RMB-test.bam")
+BIGWIG = os.path.join(helpers.GOLDEN, "hg19_36mer-test.bigwig")
+
+
+def test_library_exports_every_declared_symbol():
+    L = io_native.load_library()
+    header = open(os.path.join(helpers.ROOT, "include", "pymasc_io.h")).read()
+    import re
+    declared = set(re.findall(r"\b(pmio_[a-z0-9_]+)\s*\(", header))
+    assert declared == set(io_native.EXPORTS)
+    for name in declared:
+        assert hasattr(L, name), name
+    assert ctypes.sizeof(io_native.BamStats) == 56
+
+
+# ---------------------------------------------------------------------------------------- BAM
+@pytest.mark.parametrize("threads", [1, 4])
+def test_reference_bam_fixture_decodes_to_the_sam_arrays(threads):
+    fx = helpers.load_fixture()
+    bam = io_native.BamFile(BAM, mapq_criteria=10, threads=threads)
+    assert list(bam.references) == fx["references"] and list(bam.lengths) == fx["lengths"]
+    assert list(bam.reads) == ["chr1"] and bam.sorted
+    r = bam.reads["chr1"]
+    assert np.array_equal(r["pos"], fx["pos"])
+    assert np.array_equal(r["readlen"], fx["readlen"])
+    assert np.array_equal(r["is_reverse"], fx["is_reverse"])
+    assert bam.stats["n_records"] == 2501 and bam.stats["n_accepted"] == 1292
+    # read-length estimate (core/readlen.pyx): the fixture is a 36-mer library
+    assert io_native.estimate_readlen(bam, "MEDIAN", 10) == 36
+    assert io_native.estimate_readlen(bam, "MODE", 10) == 36
+    assert io_native.estimate_readlen(bam, "MIN", 10) == min(bam.readlen_counter)
+    assert io_native.estimate_readlen(bam, "MAX", 10) == max(bam.readlen_counter)
+    c = bam.readlen_counter
+    assert io_native.estimate_readlen(bam, "MEAN", 10) == int(round(sum(k * v for k, v in c.items()) / sum(c.values())))
+
+
+def test_bam_to_golden_tables_through_the_calculator():
+    """BAM + BigWig files in, the reference's golden NCC/MSCC curves out (configs[0] from the
+    binary files; the device is replaced by the oracle engine in the CPU suite)."""
+    gold = helpers.load_golden_tables()
+    bam = io_native.BamFile(BAM, mapq_criteria=10)
+    bw = io_native.BigWigReader(BIGWIG)
+    calc = CCBitArrayCalculator(300, 36, bam.references, bam.lengths, bw, engine=OracleEngine())
+    io_native.feed_bam(calc, bam)
+    calc.finishup_calculation()
+    whole = calc.get_whole_result()
+    bw.close()
+    for got, want in ((whole.chroms["chr1"].cc, gold["cc"]["chr1"]),
+                      (whole.mappable_chroms["chr1"].cc, gold["mscc"]["chr1"])):
+        want = np.array(want)
+        assert np.max(np.abs(np.asarray(got) - want) / np.abs(want)) <= 1e-9
+
+
+def synthetic_records():
+    """(records, expected accepted reads per chromosome, expected read-length counter)."""
+    rng = np.random.default_rng(5)
+    recs, want, hist = [], {"c1": [], "c2": [], "c3": []}, {}
+    pos = 10
+    for ref, chrom, n in ((0, "c1", 3000), (2, "c3", 1500)):
+        pos = 10
+        for i in range(n):
+            pos += int(rng.integers(0, 40))
+            kind = i % 11
+            flag, mapq = (16 if rng.random() < 0.5 else 0), int(rng.integers(0, 60))
+            cigar = [(int(rng.integers(20, 60)), "M")]
+            if kind == 1:
+                cigar = [(5, "S"), (30, "M"), (2, "I"), (3, "D"), (10, "="), (100, "N"), (4, "X"), (6, "H")]
+            if kind == 2:
+                flag |= 0x4                       # unmapped
+            if kind == 3:
+                flag |= 0x400                     # duplicate
+            if kind == 4:
+                flag |= 0x1 | 0x80                # paired, read2
+            if kind == 5:
+                flag |= 0x1 | 0x40                # paired, read1
+            if kind == 6:
+                cigar = []                        # no CIGAR: infer_query_length() is None
+            name = b"read%07d" % i + b"x" * int(rng.integers(0, 30))
+            recs.append(W.bam_record(ref, pos - 1, mapq, flag, cigar, name,
+                                     l_seq=40 if not cigar else None))
+            ql = sum(n_ for n_, op in cigar if op in "MIS=X")
+            good = not flag & 0x4 and not flag & 0x400 and mapq >= 20
+            if good:
+                hist[ql] = hist.get(ql, 0) + 1
+            if good and not flag & 0x80 and ql:
+                want[chrom].append((pos, ql, bool(flag & 16)))
+    recs.append(W.bam_record(-1, -1, 0, 4, [], b"unplaced", l_seq=30))      # no reference
+    return recs, want, hist
+
+
+@pytest.mark.parametrize("block_payload,threads", [(65280, 1), (997, 3), (64, 2)])
+def test_synthetic_bam_flags_cigars_and_block_boundaries(tmp_path, block_payload, threads):
+    recs, want, hist = synthetic_records()
+    path = str(tmp_path / "syn.bam")
+    W.write_bam(path, [("c1", 200000), ("c2", 5000), ("c3", 90000)], recs, block_payload)
+    bam = io_native.BamFile(path, mapq_criteria=20, threads=threads)
+    assert bam.references == ("c1", "c2", "c3") and bam.lengths == (200000, 5000, 90000)
+    assert sorted(bam.reads) == ["c1", "c3"] and bam.sorted
+    for chrom in ("c1", "c3"):
+        r = bam.reads[chrom]
+        got = list(zip(r["pos"].tolist(), r["readlen"].tolist(), r["is_reverse"].tolist()))
+        assert got == want[chrom]
+    assert bam.readlen_counter == hist
+    st = bam.stats
+    assert st["n_records"] == 4501 and st["n_with_ref"] == 4500
+    assert st["n_unmapped"] == sum(1 for i in range(3000) if i % 11 == 2) + sum(1 for i in range(1500) if i % 11 == 2)
+    assert st["n_paired"] == st["n_read2"] + sum(1 for n in (3000, 1500) for i in range(n) if i % 11 == 5)
+    assert st["n_accepted"] == len(want["c1"]) + len(want["c3"])
+
+
+def test_unsorted_bam_is_reported_and_refused(tmp_path):
+    recs = [W.bam_record(0, 100, 30, 0, [(36, "M")]), W.bam_record(0, 50, 30, 0, [(36, "M")])]
+    path = str(tmp_path / "unsorted.bam")
+    W.write_bam(path, [("c1", 1000)], recs)
+    bam = io_native.BamFile(path, 1)
+    assert not bam.sorted
+    calc = CCBitArrayCalculator(50, 36, bam.references, bam.lengths, engine=OracleEngine())
+    with pytest.raises(ReadUnsortedError):
+        io_native.feed_bam(calc, bam)
+    # a chromosome revisited after another one
+    recs = [W.bam_record(0, 10, 30, 0, [(36, "M")]), W.bam_record(1, 10, 30, 0, [(36, "M")]),
+            W.bam_record(0, 20, 30, 0, [(36, "M")])]
+    W.write_bam(path, [("c1", 1000), ("c2", 1000)], recs)
+    assert not io_native.BamFile(path, 1).sorted
+
+
+def test_bam_errors(tmp_path):
+    with pytest.raises(IOError):
+        io_native.BamFile(str(tmp_path / "missing.bam"))
+    p = str(tmp_path / "text.bam")
+    open(p, "wb").write(b"@HD\tVN:1.6\n" * 10)
+    with pytest.raises(ValueError):
+        io_native.BamFile(p)
+    # truncated in the middle of a block / of a record; corrupted payload (CRC)
+    good = str(tmp_path / "good.bam")
+    W.write_bam(good, [("c1", 100000)], [W.bam_record(0, i, 30, 0, [(36, "M")]) for i in range(2000)], 4000)
+    raw = open(good, "rb").read()
+    for cut in (len(raw) // 2, len(raw) - 40):
+        open(p, "wb").write(raw[:cut])
+        with pytest.raises(ValueError):
+            io_native.BamFile(p)
+    blob = bytearray(raw)
+    blob[len(raw) // 2] ^= 0xFF
+    open(p, "wb").write(bytes(blob))
+    with pytest.raises(ValueError):
+        io_native.BamFile(p)
+    # a file that ends inside a record although every block is intact
+    stream_cut = str(tmp_path / "cut.bam")
+    recs = [W.bam_record(0, 5, 30, 0, [(36, "M")])]
+    W.write_bam(stream_cut, [("c1", 1000)], recs + [recs[0][:20]])
+    with pytest.raises(ValueError):
+        io_native.BamFile(stream_cut)
+
+
+# ------------------------------------------------------------------------------------- BigWig
+def test_reference_bigwig_fixture_decodes_to_the_bedgraph_arrays():
+    fx = helpers.load_fixture()
+    bw = io_native.BigWigReader(BIGWIG)
+    assert bw.chromsizes == {"chr1": 249250621}
+    b, e = bw.fetch_arrays(1.0, "chr1")
+    assert np.array_equal(b, fx["map_begins"]) and np.array_equal(e, fx["map_ends"])
+    rows = bw.fetch(1.0, "chr1")
+    assert rows[0] == (int(b[0]), int(e[0]), 1.0) and len(rows) == 985
+    every = bw.fetch_arrays(0.0, "chr1", with_values=True)
+    assert every[0].size > b.size and every[2].min() < 1.0          # unfiltered: all intervals
+    keep = every[2] >= 1.0
+    assert np.array_equal(every[0][keep], b)
+    with pytest.raises(KeyError):
+        bw.fetch(1.0, "chr2")
+    bw.disable_progress_bar()
+    bw.close()
+    bw.close()
+    with pytest.raises(ValueError):
+        bw.fetch_arrays(1.0, "chr1")
+
+
+@pytest.mark.parametrize("compress,two_level", [(True, False), (False, False), (True, True)])
+def test_synthetic_bigwig_sections(tmp_path, compress, two_level):
+    chroms = [("chrB", 50000), ("chrA", 30000), ("chrEmpty", 1000)]
+    sections = [
+        {"chrom_id": 0, "type": "bedgraph", "items": [(0, 10, 1.0), (10, 25, 0.5), (40, 100, 1.0)]},
+        {"chrom_id": 0, "type": "varstep", "span": 5, "items": [(200, 1.0), (300, 0.25), (400, 2.0)]},
+        {"chrom_id": 0, "type": "fixedstep", "start": 1000, "step": 10, "span": 4, "items": [1.0, 0.0, 1.0, 1.0]},
+        {"chrom_id": 1, "type": "bedgraph", "items": [(5, 6, 1.0), (29990, 30000, 1.0)]},
+        {"chrom_id": 1, "type": "bedgraph", "items": [(30000 - 1, 30000 + 50, 1.0)]},   # overhangs the end
+    ]
+    path = str(tmp_path / "syn.bw")
+    W.write_bigwig(path, chroms, sections, compress=compress, two_level=two_level)
+    bw = io_native.BigWigReader(path)
+    assert bw.chromsizes == {"chrB": 50000, "chrA": 30000, "chrEmpty": 1000}
+    b, e, v = bw.fetch_arrays(1.0, "chrB", with_values=True)
+    assert list(zip(b.tolist(), e.tolist())) == [(0, 10), (40, 100), (200, 205), (400, 405),
+                                                 (1000, 1004), (1020, 1024), (1030, 1034)]
+    assert v.tolist() == [1.0, 1.0, 1.0, 2.0, 1.0, 1.0, 1.0]
+    b, e = bw.fetch_arrays(0.0, "chrB")
+    assert b.size == 10
+    b, e = bw.fetch_arrays(1.0, "chrA")
+    assert list(zip(b.tolist(), e.tolist())) == [(5, 6), (29990, 30000), (29999, 30050)]   # as stored
+    b, e = bw.fetch_arrays(1.0, "chrEmpty")
+    assert b.size == 0 and e.size == 0
+    with pytest.raises(KeyError):
+        bw.fetch_arrays(1.0, "chrZ")
+    bw.close()
+
+
+def test_bigwig_errors(tmp_path):
+    with pytest.raises(IOError):
+        io_native.BigWigReader(str(tmp_path / "missing.bw"))
+    p = str(tmp_path / "junk.bw")
+    open(p, "wb").write(b"\0" * 200)
+    with pytest.raises(IOError):
+        io_native.BigWigReader(p)
+    open(p, "wb").write(struct.pack("<I", 0x888FFC26) + b"\xff" * 100)     # offsets outside the file
+    with pytest.raises(IOError):
+        io_native.BigWigReader(p)
+    with pytest.raises(ValueError):
+        io_native.BigWigReader("-")
