@@ -235,3 +235,35 @@ def test_bigwig_errors(tmp_path):
         io_native.BigWigReader(p)
     with pytest.raises(ValueError):
         io_native.BigWigReader("-")
+
+
+# ----------------------------------------------------------------------------------- pipeline
+def test_run_files_from_bam_and_bigwig_matches_golden_tables(tmp_path):
+    """pymasc_b200.pipeline.run_files: files in, the reference's golden curves out; a second
+    file over the same track shares it (one device batch) and a header / BigWig length
+    mismatch resolves to the longer length (reader/bam.py:217-255)."""
+    from pymasc_b200 import pipeline
+    gold = helpers.load_golden_tables()
+    engine = OracleEngine()
+    # second file: the same reads shifted by 7 bp on a header that understates chr1
+    fx = helpers.load_fixture()
+    recs = [W.bam_record(0, int(p) - 1 + 7, 30, 16 if r else 0, [(int(l), "M")])
+            for p, l, r in zip(fx["pos"], fx["readlen"], fx["is_reverse"])]
+    other = str(tmp_path / "other.bam")
+    W.write_bam(other, [("chr1", 249250000), ("chrM", 16571)], recs)
+    results, info = pipeline.run_files([BAM, other], BIGWIG, max_shift=300, mapq_criteria=10,
+                                       engine=engine)
+    assert len(engine.batches) == 1
+    assert [f["read_len"] for f in info["files"]] == [36, 36]
+    whole = results[0]
+    for got, want in ((whole.chroms["chr1"].cc, gold["cc"]["chr1"]),
+                      (whole.mappable_chroms["chr1"].cc, gold["mscc"]["chr1"])):
+        want = np.array(want)
+        assert np.max(np.abs(np.asarray(got) - want) / np.abs(want)) <= 1e-9
+    assert results[1].chroms["chr1"].genomelen == 249250621          # the BigWig's, longer
+    assert results[1].genomelen == 249250621 + 16571
+    alone, _ = pipeline.run_files(other, BIGWIG, max_shift=300, mapq_criteria=10, engine=OracleEngine())
+    helpers.assert_snapshots_equal(helpers.snapshot_whole(results[1]), helpers.snapshot_whole(alone[0]))
+    with pytest.raises(ValueError):
+        pipeline.run_files(BAM, None, max_shift=20, mapq_criteria=10, engine=OracleEngine())
+    assert pipeline.reconcile_chromosome_sizes(["a", "b", "c"], [10, 20, 30], {"a": 12, "b": 15}) == [12, 20, 30]
