@@ -64,9 +64,17 @@ uint32_t    pmio_bam_n_refs(const pmio_bam *b);
 const char *pmio_bam_ref_name(const pmio_bam *b, uint32_t i);
 uint64_t    pmio_bam_ref_len(const pmio_bam *b, uint32_t i);
 /* Accepted reads of reference i: 1-based leftmost base, query length (CIGAR M/I/S/=/X), strand
- * (1 = reverse). */
-int  pmio_bam_reads(const pmio_bam *b, uint32_t i, const uint32_t **pos, const uint32_t **qlen,
+ * (1 = reverse).  The arrays are assembled on the first request that asks for them (pass NULL
+ * pointers to get the count only). */
+int  pmio_bam_reads(pmio_bam *b, uint32_t i, const uint32_t **pos, const uint32_t **qlen,
                     const uint8_t **is_reverse, uint64_t *n);
+/* The same reads reduced by the calculator's feed rules (mscc.pyx:370-418), for coordinate-
+ * sorted files only (PMIO_ERR_ARG otherwise): sorted unique forward 5' positions (consecutive
+ * repeats dropped) and sorted unique reverse 5' ends pos + qlen - 1, each with the summed query
+ * length of the reads that set a bit first; first/last leftmost position fed. */
+int  pmio_bam_packed(const pmio_bam *b, uint32_t i, const uint32_t **fwd, uint64_t *n_fwd,
+                     uint64_t *fwd_len_sum, const uint32_t **rev, uint64_t *n_rev,
+                     uint64_t *rev_len_sum, uint32_t *first_pos, uint32_t *last_pos);
 /* Query-length histogram for the read-length estimator, ascending by length. */
 int  pmio_bam_readlen_hist(const pmio_bam *b, const uint32_t **lengths, const uint64_t **counts,
                            uint32_t *n);

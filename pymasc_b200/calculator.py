@@ -95,6 +95,7 @@ class CCBitArrayCalculator(object):
         self._nbits = 0
         self._last_pos = self._last_forward_pos = 0
         self._forward_read_len_sum = 0
+        self._packed = None                     # feed_packed: (fwd, fwd_len_sum, rev, rev_len_sum)
 
     # readonly attributes of the reference (mscc.pyx:75-79)
     max_shift = property(lambda self: self._max_shift)
@@ -120,6 +121,7 @@ class CCBitArrayCalculator(object):
         self._last_pos = 0
         self._last_forward_pos = 0
         self._forward_read_len_sum = 0
+        self._packed = None
 
     def _check_pos(self, chrom, pos):
         # mscc.pyx:351-366
@@ -133,6 +135,8 @@ class CCBitArrayCalculator(object):
             self._chr = chrom
             self._init_buff()
             self._logging_info("Loading {} reads to bit array...".format(chrom))
+        elif self._packed is not None:
+            raise ValueError("chromosome %s was fed packed (feed_packed); it takes no further reads" % chrom)
         if pos < self._last_pos:
             raise ReadUnsortedError
         self._last_pos = pos
@@ -189,6 +193,27 @@ class CCBitArrayCalculator(object):
             self._rev_end.frombytes(rend.astype(np.uint32).tobytes())
             self._rev_len.frombytes(readlen[is_reverse].astype(np.uint32).tobytes())
 
+    def feed_packed(self, chrom, fwd, fwd_len_sum, rev, rev_len_sum, first_pos, last_pos):
+        """A WHOLE chromosome's reads already reduced by the feed rules (what a native decoder
+        produces, pymasc_b200.io_native.BamFile.packed): ``fwd`` sorted unique forward 5'
+        positions with ``fwd_len_sum`` the query lengths of the reads kept by the duplicate rule
+        (mscc.pyx:388-393), ``rev`` sorted unique reverse 5' ends with ``rev_len_sum`` over the
+        first read of each end (:416-418); ``first_pos`` / ``last_pos`` are the leftmost
+        positions of the first and last read fed.  Equivalent to feeding those reads one by one;
+        the chromosome cannot take further reads afterwards."""
+        if chrom == self._chr:
+            raise ValueError("feed_packed needs a chromosome that has not been fed yet")
+        self._check_pos(chrom, int(first_pos))
+        fwd = np.ascontiguousarray(fwd, dtype=np.uint32)
+        rev = np.ascontiguousarray(rev, dtype=np.uint32)
+        if fwd.size and int(fwd[-1]) >= self._nbits:
+            raise PositionOutOfRange("forward read on %s beyond the bit array" % chrom)
+        if rev.size and int(rev[-1]) >= self._nbits:
+            raise PositionOutOfRange("reverse read end on %s beyond the bit array" % chrom)
+        self._last_pos = int(last_pos)
+        self._last_forward_pos = int(fwd[-1]) if fwd.size else 0
+        self._packed = (fwd, int(fwd_len_sum), rev, int(rev_len_sum))
+
     # ------------------------------------------------------------------ mappability (host)
     def _load_intervals(self, chrom):
         """(begins, ends) uint32 arrays of the intervals with value >= 1.0, or None without a
@@ -220,6 +245,11 @@ class CCBitArrayCalculator(object):
         chrom = self._chr
         p = _Pending()
         p.chrom = chrom
+        if self._packed is not None:
+            p.fwd, p.fwd_len_sum, p.rev, p.rev_len_sum = self._packed
+            self._packed = None
+            self._queue(p)
+            return
         p.fwd = np.frombuffer(self._fwd, dtype=np.uint32).copy() if len(self._fwd) else np.zeros(0, np.uint32)
         rev_end = np.frombuffer(self._rev_end, dtype=np.uint32) if len(self._rev_end) else np.zeros(0, np.uint32)
         rev_len = np.frombuffer(self._rev_len, dtype=np.uint32) if len(self._rev_len) else np.zeros(0, np.uint32)
@@ -228,6 +258,10 @@ class CCBitArrayCalculator(object):
         p.rev = uniq.astype(np.uint32)
         p.fwd_len_sum = int(self._forward_read_len_sum)
         p.rev_len_sum = int(rev_len[first].sum()) if first.size else 0
+        self._queue(p)
+
+    def _queue(self, p):
+        chrom = p.chrom
         self.forward_read_len_sum += p.fwd_len_sum
         self.reverse_read_len_sum += p.rev_len_sum
         if not self._skip_ncc:

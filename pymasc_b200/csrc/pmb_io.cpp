@@ -2,10 +2,12 @@
 // host into packed arrays.  zlib + std::thread; no CUDA here.
 //
 // BAM: the file is memory-mapped, BGZF block headers are walked sequentially (18 bytes per
-// <= 64 KiB block), batches of blocks are inflated in parallel straight into their final
-// offsets of one buffer (ISIZE in each block's footer gives the offsets up front), and the
-// records of the batch are filtered and packed by one pass over that buffer; a record cut by
-// the batch boundary is carried into the next batch.
+// <= 64 KiB block), cache-sized batches of blocks are inflated in parallel straight into their
+// final offsets of one buffer (ISIZE in each block's footer gives the offsets up front), record
+// boundaries are found by one hop over the block_size fields, and the batch is filtered in
+// parallel shares whose outputs stay as the handle's storage (no merge copy); a record cut by
+// the batch boundary is carried into the next batch.  The reads of every reference are then
+// reduced by the calculator's feed rules, references in parallel.
 // BigWig: bbi header, chromosome B+ tree and the R-tree index are read from the mapping; a
 // chromosome's data blocks are found through the R-tree, inflated and decoded (bedGraph,
 // varStep and fixedStep sections).
@@ -21,7 +23,9 @@
 
 #include <algorithm>
 #include <atomic>
+#include <chrono>
 #include <map>
+#include <memory>
 #include <string>
 #include <thread>
 #include <vector>
@@ -93,32 +97,49 @@ struct Block { size_t data_off; uint32_t csize, isize, crc; size_t out_off; };
 }  // namespace
 
 // ====================================================================== BAM
+// One thread's share of a batch: a run of complete records, filtered into arrays that stay
+// alive as the storage of the handle (no merge pass: a reference's reads are the concatenation
+// of its segments, in file order).  Accepted reads form runs of one reference (a sorted file has
+// one or two per share).
+struct pmio_chunk {
+    struct Run { int32_t ref; size_t begin; uint32_t first_pos, last_pos; };
+    std::vector<uint32_t> pos, qlen;
+    std::vector<uint8_t> rev;
+    std::vector<Run> runs;
+};
+
 struct pmio_bam {
     std::vector<std::string> names;
     std::vector<uint64_t> lens;
+    std::vector<std::unique_ptr<pmio_chunk>> store;
+    struct Seg { const pmio_chunk* c; size_t begin, end; };
+    std::vector<std::vector<Seg>> segs;         // per reference, file order
+    std::vector<uint64_t> counts;               // accepted reads per reference
+    std::vector<uint32_t> first_pos, last_pos;
+    // per-read arrays, concatenated on first request (pmio_bam_reads)
     std::vector<std::vector<uint32_t>> pos, qlen;
     std::vector<std::vector<uint8_t>> rev;
+    std::vector<uint8_t> materialised;
     std::vector<uint32_t> hist_len;
     std::vector<uint64_t> hist_cnt;
     pmio_bam_stats st{};
+    // per reference, the reads reduced by the calculator's feed rules (mscc.pyx:370-418)
+    struct Packed {
+        std::vector<uint32_t> fwd, rev;
+        uint64_t fwd_len_sum = 0, rev_len_sum = 0;
+    };
+    std::vector<Packed> packed;
 };
 
 namespace {
 
-struct BamParser {
+// Header (magic, text, reference list): sequential, resumable across batches.
+struct BamHeaderParser {
     pmio_bam* b;
-    int mapq;
-    // header state
-    int stage = 0;              // 0 magic + text, 1 references, 2 records
+    int stage = 0;              // 0 magic + text, 1 references, 2 done (records follow)
     uint32_t refs_left = 0;
-    std::map<uint32_t, uint64_t> hist;
-    std::vector<uint64_t> hist_small = std::vector<uint64_t>(1024, 0);
-    int32_t cur_ref = -1;
-    uint32_t last_pos = 0;
-    std::vector<uint8_t> seen;
-    bool sorted = true;
 
-    // consumes as many complete items as [p, p+n) holds; returns bytes consumed, or -1
+    // consumes what [p, p+n) holds of the header; returns bytes consumed, or -1
     long long feed(const uint8_t* p, size_t n)
     {
         size_t o = 0;
@@ -136,8 +157,10 @@ struct BamParser {
         while (stage == 1) {
             if (refs_left == 0) {
                 const size_t nr = b->names.size();
+                b->segs.resize(nr); b->counts.assign(nr, 0);
+                b->first_pos.assign(nr, 0); b->last_pos.assign(nr, 0);
                 b->pos.resize(nr); b->qlen.resize(nr); b->rev.resize(nr);
-                seen.assign(nr, 0);
+                b->materialised.assign(nr, 0);
                 stage = 2;
                 break;
             }
@@ -150,56 +173,157 @@ struct BamParser {
             o += 8 + (size_t)l_name;
             refs_left--;
         }
-        pmio_bam_stats& st = b->st;
-        const uint32_t n_refs = (uint32_t)b->names.size();
-        while (n - o >= 4) {
-            const int32_t bs = rdi32(p + o);
-            if (bs < 32) { g_err = "corrupt BAM record (block_size < 32)"; return -1; }
-            if (n - o < 4 + (size_t)bs) break;
-            const uint8_t* r = p + o + 4;
-            o += 4 + (size_t)bs;
-            st.n_records++;
-            const int32_t ref = rdi32(r);
-            if (ref < 0) continue;                                   // reference_name is None
-            if ((uint32_t)ref >= n_refs) { g_err = "BAM record names an unknown reference"; return -1; }
-            const int32_t pos0 = rdi32(r + 4);
-            const uint32_t l_name = r[8], mq = r[9];
-            const uint32_t n_cig = rd16(r + 12), flag = rd16(r + 14);
-            st.n_with_ref++;
-            if (flag & 0x1) { st.n_paired++; if (flag & 0x80) st.n_read2++; }
-            if (flag & 0x4) st.n_unmapped++;
-            if (32 + l_name + 4ull * n_cig > (uint32_t)bs) { g_err = "corrupt BAM record (CIGAR overruns)"; return -1; }
-            // infer_query_length(): M, I, S, =, X; None (skip) without a CIGAR
-            uint32_t ql = 0;
-            const uint8_t* cg = r + 32 + l_name;
-            for (uint32_t i = 0; i < n_cig; i++) {
-                const uint32_t c = rd32(cg + 4 * i), op = c & 15;
-                if (op == 0 || op == 1 || op == 4 || op == 7 || op == 8) ql += c >> 4;
-            }
-            const bool good = !(flag & 0x4) && !(flag & 0x400) && (int)mq >= mapq;
-            // estimate_readlen's counter (readlen.pyx:150-156): read2 is NOT excluded there
-            if (good) {
-                if (ql < hist_small.size()) hist_small[ql]++;
-                else hist[ql]++;
-            }
-            if ((flag & 0x80) || !good || ql == 0) continue;        // handler/read.py:62-90, :132-143
-            if (ref != cur_ref) {
-                if (seen[ref]) sorted = false;
-                seen[ref] = 1;
-                cur_ref = ref;
-                last_pos = 0;
-            }
-            const uint32_t p1 = (uint32_t)(pos0 + 1);
-            if (p1 < last_pos) sorted = false;
-            last_pos = p1;
-            b->pos[ref].push_back(p1);
-            b->qlen[ref].push_back(ql);
-            b->rev[ref].push_back((flag & 0x10) ? 1 : 0);
-            st.n_accepted++;
-        }
         return (long long)o;
     }
 };
+
+// Counters of one share (scratch, reused from batch to batch).
+struct ShareStats {
+    pmio_bam_stats st{};
+    std::vector<uint64_t> hist_small = std::vector<uint64_t>(1024, 0);
+    std::map<uint32_t, uint64_t> hist;
+    bool sorted = true;         // within every run
+    const char* err = nullptr;
+    void reset()
+    {
+        st = pmio_bam_stats{};
+        std::fill(hist_small.begin(), hist_small.end(), 0);
+        hist.clear();
+        sorted = true;
+        err = nullptr;
+    }
+};
+
+// [p, p+n) holds complete records only (the boundary scan has validated every block_size).
+void parse_share(const uint8_t* p, size_t n, uint32_t n_refs, int mapq, pmio_chunk& out, ShareStats& ss)
+{
+    pmio_bam_stats& st = ss.st;
+    const size_t guess = n / 64 + 16;       // virtual reservation; untouched pages cost nothing
+    out.pos.reserve(guess); out.qlen.reserve(guess); out.rev.reserve(guess);
+    size_t o = 0;
+    while (o < n) {
+        const int32_t bs = rdi32(p + o);
+        const uint8_t* r = p + o + 4;
+        o += 4 + (size_t)bs;
+        st.n_records++;
+        const int32_t ref = rdi32(r);
+        if (ref < 0) continue;                                   // reference_name is None
+        if ((uint32_t)ref >= n_refs) { ss.err = "BAM record names an unknown reference"; return; }
+        const int32_t pos0 = rdi32(r + 4);
+        const uint32_t l_name = r[8], mq = r[9];
+        const uint32_t n_cig = rd16(r + 12), flag = rd16(r + 14);
+        st.n_with_ref++;
+        if (flag & 0x1) { st.n_paired++; if (flag & 0x80) st.n_read2++; }
+        if (flag & 0x4) st.n_unmapped++;
+        if (32 + l_name + 4ull * n_cig > (uint32_t)bs) { ss.err = "corrupt BAM record (CIGAR overruns)"; return; }
+        // infer_query_length(): M, I, S, =, X; None (skip) without a CIGAR
+        uint32_t ql = 0;
+        const uint8_t* cg = r + 32 + l_name;
+        for (uint32_t i = 0; i < n_cig; i++) {
+            const uint32_t c = rd32(cg + 4 * i), op = c & 15;
+            if (op == 0 || op == 1 || op == 4 || op == 7 || op == 8) ql += c >> 4;
+        }
+        const bool good = !(flag & 0x4) && !(flag & 0x400) && (int)mq >= mapq;
+        // estimate_readlen's counter (readlen.pyx:150-156): read2 is NOT excluded there
+        if (good) {
+            if (ql < ss.hist_small.size()) ss.hist_small[ql]++;
+            else ss.hist[ql]++;
+        }
+        if ((flag & 0x80) || !good || ql == 0) continue;        // handler/read.py:62-90, :132-143
+        const uint32_t p1 = (uint32_t)(pos0 + 1);
+        if (out.runs.empty() || out.runs.back().ref != ref) out.runs.push_back({ref, out.pos.size(), p1, p1});
+        else if (p1 < out.runs.back().last_pos) ss.sorted = false;
+        out.runs.back().last_pos = p1;
+        out.pos.push_back(p1);
+        out.qlen.push_back(ql);
+        out.rev.push_back((flag & 0x10) ? 1 : 0);
+        st.n_accepted++;
+    }
+}
+
+// Shares of a batch, in file order: their runs become segments of the per-reference lists;
+// coordinate order across shares and references is checked here (mscc.pyx:351-366: no reference
+// revisited, positions non-decreasing).
+struct BamMerger {
+    pmio_bam* b;
+    std::map<uint32_t, uint64_t> hist;
+    std::vector<uint64_t> hist_small = std::vector<uint64_t>(1024, 0);
+    int32_t cur_ref = -1;
+    uint32_t last_pos = 0;
+    std::vector<uint8_t> seen;
+    bool sorted = true;
+
+    void take(const pmio_chunk& c, const ShareStats& ss)
+    {
+        pmio_bam_stats& st = b->st;
+        st.n_records += ss.st.n_records; st.n_with_ref += ss.st.n_with_ref; st.n_unmapped += ss.st.n_unmapped;
+        st.n_paired += ss.st.n_paired; st.n_read2 += ss.st.n_read2; st.n_accepted += ss.st.n_accepted;
+        for (size_t l = 0; l < hist_small.size(); l++) hist_small[l] += ss.hist_small[l];
+        for (auto& kv : ss.hist) hist[kv.first] += kv.second;
+        if (!ss.sorted) sorted = false;
+        if (seen.size() < b->names.size()) seen.resize(b->names.size(), 0);
+        for (size_t k = 0; k < c.runs.size(); k++) {
+            const pmio_chunk::Run& r = c.runs[k];
+            const size_t end = k + 1 < c.runs.size() ? c.runs[k + 1].begin : c.pos.size();
+            if (r.ref != cur_ref) {
+                if (seen[r.ref]) sorted = false;
+                seen[r.ref] = 1;
+                cur_ref = r.ref;
+                last_pos = 0;
+            }
+            if (r.first_pos < last_pos) sorted = false;
+            last_pos = r.last_pos;
+            if (b->counts[r.ref] == 0) b->first_pos[r.ref] = r.first_pos;
+            b->last_pos[r.ref] = r.last_pos;
+            b->counts[r.ref] += end - r.begin;
+            b->segs[r.ref].push_back({&c, r.begin, end});
+        }
+    }
+};
+
+// What feed_forward_read / feed_reverse_read leave behind for one chromosome of sorted reads:
+// forward 5' positions with consecutive repeats dropped (mscc.pyx:388-393: a read at
+// _last_forward_pos is a duplicate) and the query lengths of the kept reads summed; reverse 5'
+// ends pos + qlen - 1, each bit counted once with the query length of the FIRST read that set
+// it (mscc.pyx:416-418).  Both lists come out sorted and unique.
+void pack_reference(const std::vector<pmio_bam::Seg>& segs, uint64_t n, pmio_bam::Packed& out)
+{
+    out.fwd.reserve(n / 2 + n / 8 + 16);
+    std::vector<uint32_t> ends, lens;
+    ends.reserve(n / 2 + n / 8 + 16);
+    lens.reserve(n / 2 + n / 8 + 16);
+    uint32_t last_f = 0;
+    bool ends_sorted = true;
+    for (const pmio_bam::Seg& s : segs) {
+        const uint32_t* pos = s.c->pos.data();
+        const uint32_t* qlen = s.c->qlen.data();
+        const uint8_t* rev = s.c->rev.data();
+        for (size_t i = s.begin; i < s.end; i++) {
+            if (!rev[i]) {
+                if (pos[i] == last_f) continue;
+                last_f = pos[i];
+                out.fwd.push_back(pos[i]);
+                out.fwd_len_sum += qlen[i];
+            } else {
+                const uint32_t e = pos[i] + qlen[i] - 1;
+                if (!ends.empty() && e < ends.back()) ends_sorted = false;
+                ends.push_back(e);
+                lens.push_back(qlen[i]);
+            }
+        }
+    }
+    if (ends_sorted) {
+        out.rev.reserve(ends.size());
+        for (size_t i = 0; i < ends.size(); i++)
+            if (i == 0 || ends[i] != ends[i - 1]) { out.rev.push_back(ends[i]); out.rev_len_sum += lens[i]; }
+        return;
+    }
+    std::vector<uint32_t> idx(ends.size());
+    for (size_t i = 0; i < idx.size(); i++) idx[i] = (uint32_t)i;
+    std::stable_sort(idx.begin(), idx.end(), [&](uint32_t a, uint32_t b) { return ends[a] < ends[b]; });
+    for (size_t k = 0; k < idx.size(); k++)
+        if (k == 0 || ends[idx[k]] != ends[idx[k - 1]]) { out.rev.push_back(ends[idx[k]]); out.rev_len_sum += lens[idx[k]]; }
+}
 
 }  // namespace
 
@@ -215,8 +339,19 @@ extern "C" int pmio_bam_load(const char* path, int mapq_criteria, int threads, p
 
     pmio_bam* b = new (std::nothrow) pmio_bam();
     if (!b) return fail(PMIO_ERR_NOMEM, "out of memory");
-    BamParser parser{b, mapq_criteria};
-    const size_t BATCH_BLOCKS = 2048;                 // <= 128 MiB inflated per batch
+    BamHeaderParser header{b};
+    BamMerger merger{b};
+    std::vector<ShareStats> share_stats((size_t)threads);
+    std::vector<size_t> cuts;
+    // PMIO_TIMING=1: seconds per stage on stderr (debug aid)
+    static const bool timing = getenv("PMIO_TIMING") != nullptr;
+    auto now = []() { return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count(); };
+    double t_inflate = 0, t_scan = 0, t_parse = 0, t_pack = 0, t_mark = now();
+    // Batch size: large enough that the two thread-pool start-ups per batch are noise (measured:
+    // 256-block batches on 8 threads cost 1.7x the inflate time of 4096-block ones), small
+    // enough to bound the buffer (<= 256 MiB inflated).
+    size_t BATCH_BLOCKS = std::min<size_t>(4096, 512 * (size_t)threads);
+    if (const char* e = getenv("PMIO_BATCH_BLOCKS")) BATCH_BLOCKS = std::max<size_t>(1, (size_t)atoll(e));
     std::vector<uint8_t> buf;
     std::vector<Block> blocks;
     size_t carry = 0, off = 0;
@@ -270,19 +405,89 @@ extern "C" int pmio_bam_load(const char* path, int mapq_criteria, int threads, p
         work();
         for (auto& t : pool) t.join();
         if (!ok.load()) { g_err = "BGZF block does not inflate (corrupt data or CRC mismatch)"; bad = true; break; }
-        // ---- parse; keep the cut record for the next batch
-        const long long used = parser.feed(buf.data(), out_off);
-        if (used < 0) { bad = true; break; }
-        carry = out_off - (size_t)used;
+        { const double t = now(); t_inflate += t - t_mark; t_mark = t; }
+        // ---- header first (sequential), then the records: find the record boundaries by
+        //      hopping over block_size fields, cut the batch into one share per thread at record
+        //      boundaries, filter the shares in parallel, take them in file order.  The record
+        //      cut by the end of the batch is carried into the next one.
+        size_t used = 0;
+        if (header.stage != 2) {
+            const long long h = header.feed(buf.data(), out_off);
+            if (h < 0) { bad = true; break; }
+            used = (size_t)h;
+        }
+        if (header.stage == 2) {
+            const uint8_t* p = buf.data();
+            const size_t share = std::max<size_t>((out_off - used) / (size_t)threads + 1, 1 << 16);
+            cuts.clear();
+            cuts.push_back(used);
+            size_t o = used;
+            while (out_off - o >= 4) {
+                const int32_t bs = rdi32(p + o);
+                if (bs < 32) { g_err = "corrupt BAM record (block_size < 32)"; bad = true; break; }
+                if (out_off - o < 4 + (size_t)bs) break;
+                o += 4 + (size_t)bs;
+                if (o - cuts.back() >= share) cuts.push_back(o);
+            }
+            if (bad) break;
+            if (cuts.back() != o) cuts.push_back(o);
+            { const double t = now(); t_scan += t - t_mark; t_mark = t; }
+            const size_t n_shares = cuts.size() - 1;
+            const uint32_t n_refs = (uint32_t)b->names.size();
+            if (share_stats.size() < n_shares) share_stats.resize(n_shares);
+            const size_t store0 = b->store.size();
+            for (size_t i = 0; i < n_shares; i++) b->store.emplace_back(new pmio_chunk());
+            std::atomic<size_t> next_share{0};
+            auto parse_work = [&]() {
+                for (size_t i; (i = next_share.fetch_add(1)) < n_shares;) {
+                    share_stats[i].reset();
+                    parse_share(p + cuts[i], cuts[i + 1] - cuts[i], n_refs, mapq_criteria, *b->store[store0 + i],
+                                share_stats[i]);
+                }
+            };
+            std::vector<std::thread> ppool;
+            for (size_t t = 1; t < std::min<size_t>((size_t)threads, n_shares); t++) ppool.emplace_back(parse_work);
+            parse_work();
+            for (auto& t : ppool) t.join();
+            for (size_t i = 0; i < n_shares && !bad; i++) {
+                if (share_stats[i].err) { g_err = share_stats[i].err; bad = true; break; }
+                merger.take(*b->store[store0 + i], share_stats[i]);
+            }
+            if (bad) break;
+            used = o;
+        }
+        carry = out_off - used;
         if (carry && used) memmove(buf.data(), buf.data() + used, carry);
+        { const double t = now(); t_parse += t - t_mark; t_mark = t; }
     }
-    if (!bad && parser.stage != 2) { g_err = "truncated BAM header"; bad = true; }
+    if (!bad && header.stage != 2) { g_err = "truncated BAM header"; bad = true; }
     if (!bad && carry) { g_err = "truncated BAM file (incomplete record at the end)"; bad = true; }
     if (bad) { delete b; return PMIO_ERR_FORMAT; }
-    b->st.sorted = parser.sorted ? 1 : 0;
-    for (size_t l = 0; l < parser.hist_small.size(); l++)
-        if (parser.hist_small[l]) parser.hist[(uint32_t)l] += parser.hist_small[l];
-    for (auto& kv : parser.hist) { b->hist_len.push_back(kv.first); b->hist_cnt.push_back(kv.second); }
+    b->st.sorted = merger.sorted ? 1 : 0;
+    for (size_t l = 0; l < merger.hist_small.size(); l++)
+        if (merger.hist_small[l]) merger.hist[(uint32_t)l] += merger.hist_small[l];
+    for (auto& kv : merger.hist) { b->hist_len.push_back(kv.first); b->hist_cnt.push_back(kv.second); }
+    // packed form per reference, references spread over the threads (longest first)
+    if (b->st.sorted) {
+        b->packed.resize(b->names.size());
+        std::vector<size_t> order;
+        for (size_t i = 0; i < b->names.size(); i++)
+            if (b->counts[i]) order.push_back(i);
+        std::sort(order.begin(), order.end(), [&](size_t x, size_t y) { return b->counts[x] > b->counts[y]; });
+        std::atomic<size_t> next{0};
+        auto work = [&]() {
+            for (size_t k; (k = next.fetch_add(1)) < order.size();)
+                pack_reference(b->segs[order[k]], b->counts[order[k]], b->packed[order[k]]);
+        };
+        std::vector<std::thread> pool;
+        for (size_t t = 1; t < std::min<size_t>((size_t)threads, order.size()); t++) pool.emplace_back(work);
+        work();
+        for (auto& t : pool) t.join();
+    }
+    t_pack = now() - t_mark;
+    if (timing)
+        fprintf(stderr, "[pmio bam] %d threads, %zu-block batches: inflate %.3f s, boundary scan %.3f s, filter %.3f s, "
+                        "pack %.3f s\n", threads, BATCH_BLOCKS, t_inflate, t_scan, t_parse, t_pack);
     *out = b;
     return PMIO_OK;
 }
@@ -308,14 +513,41 @@ extern "C" uint64_t pmio_bam_ref_len(const pmio_bam* b, uint32_t i)
     return b && i < b->lens.size() ? b->lens[i] : 0;
 }
 
-extern "C" int pmio_bam_reads(const pmio_bam* b, uint32_t i, const uint32_t** pos, const uint32_t** qlen,
+extern "C" int pmio_bam_reads(pmio_bam* b, uint32_t i, const uint32_t** pos, const uint32_t** qlen,
                               const uint8_t** is_reverse, uint64_t* n)
 {
     if (!b || i >= b->names.size()) return fail(PMIO_ERR_ARG, "reference index out of range");
+    if ((pos || qlen || is_reverse) && !b->materialised[i]) {      // concatenate the segments once
+        b->pos[i].reserve(b->counts[i]); b->qlen[i].reserve(b->counts[i]); b->rev[i].reserve(b->counts[i]);
+        for (const pmio_bam::Seg& s : b->segs[i]) {
+            b->pos[i].insert(b->pos[i].end(), s.c->pos.begin() + s.begin, s.c->pos.begin() + s.end);
+            b->qlen[i].insert(b->qlen[i].end(), s.c->qlen.begin() + s.begin, s.c->qlen.begin() + s.end);
+            b->rev[i].insert(b->rev[i].end(), s.c->rev.begin() + s.begin, s.c->rev.begin() + s.end);
+        }
+        b->materialised[i] = 1;
+    }
     if (pos) *pos = b->pos[i].data();
     if (qlen) *qlen = b->qlen[i].data();
     if (is_reverse) *is_reverse = b->rev[i].data();
-    if (n) *n = b->pos[i].size();
+    if (n) *n = b->counts[i];
+    return PMIO_OK;
+}
+
+extern "C" int pmio_bam_packed(const pmio_bam* b, uint32_t i, const uint32_t** fwd, uint64_t* n_fwd,
+                               uint64_t* fwd_len_sum, const uint32_t** rev, uint64_t* n_rev,
+                               uint64_t* rev_len_sum, uint32_t* first_pos, uint32_t* last_pos)
+{
+    if (!b || i >= b->names.size()) return fail(PMIO_ERR_ARG, "reference index out of range");
+    if (!b->st.sorted) return fail(PMIO_ERR_ARG, "reads are not coordinate sorted");
+    const pmio_bam::Packed& k = b->packed[i];
+    if (fwd) *fwd = k.fwd.data();
+    if (n_fwd) *n_fwd = k.fwd.size();
+    if (fwd_len_sum) *fwd_len_sum = k.fwd_len_sum;
+    if (rev) *rev = k.rev.data();
+    if (n_rev) *n_rev = k.rev.size();
+    if (rev_len_sum) *rev_len_sum = k.rev_len_sum;
+    if (first_pos) *first_pos = b->first_pos[i];
+    if (last_pos) *last_pos = b->last_pos[i];
     return PMIO_OK;
 }
 

@@ -29,7 +29,7 @@ LIB_PATH = os.environ.get("PYMASC_IO_LIB") or os.path.join(_HERE, "libpymasc_io.
 
 EXPORTS = (
     "pmio_last_error", "pmio_bam_load", "pmio_bam_free", "pmio_bam_stats_get", "pmio_bam_n_refs",
-    "pmio_bam_ref_name", "pmio_bam_ref_len", "pmio_bam_reads", "pmio_bam_readlen_hist",
+    "pmio_bam_ref_name", "pmio_bam_ref_len", "pmio_bam_reads", "pmio_bam_packed", "pmio_bam_readlen_hist",
     "pmio_bw_open", "pmio_bw_close", "pmio_bw_n_chroms", "pmio_bw_chrom_name", "pmio_bw_chrom_len",
     "pmio_bw_intervals",
 )
@@ -70,6 +70,9 @@ def load_library():
     L.pmio_bam_reads.argtypes = [vp, ctypes.c_uint32, u32pp, u32pp,
                                  ctypes.POINTER(ctypes.POINTER(ctypes.c_uint8)),
                                  ctypes.POINTER(ctypes.c_uint64)]
+    u64p = ctypes.POINTER(ctypes.c_uint64)
+    L.pmio_bam_packed.argtypes = [vp, ctypes.c_uint32, u32pp, u64p, u64p, u32pp, u64p, u64p,
+                                  ctypes.POINTER(ctypes.c_uint32), ctypes.POINTER(ctypes.c_uint32)]
     L.pmio_bam_readlen_hist.argtypes = [vp, u32pp, ctypes.POINTER(ctypes.POINTER(ctypes.c_uint64)),
                                         ctypes.POINTER(ctypes.c_uint32)]
     L.pmio_bw_open.argtypes = [ctypes.c_char_p, vpp]
@@ -106,48 +109,117 @@ def _copy(ptr, n, dtype):
 
 
 # ---------------------------------------------------------------------------------------- BAM
+class _LazyReads(object):
+    """chrom -> {pos, readlen, is_reverse}; a chromosome's arrays are copied out of the native
+    handle on first access (most callers only ever need the packed form)."""
+
+    def __init__(self, bam):
+        self._bam, self._got = bam, {}
+
+    def __getitem__(self, chrom):
+        if chrom not in self._got:
+            self._got[chrom] = self._bam._reads_of(chrom)
+        return self._got[chrom]
+
+    def __contains__(self, chrom):
+        return chrom in self._bam._counts
+
+    def __iter__(self):
+        return iter(self._bam._counts)
+
+    def __len__(self):
+        return len(self._bam._counts)
+
+    def keys(self):
+        return self._bam._counts.keys()
+
+    def items(self):
+        return ((c, self[c]) for c in self._bam._counts)
+
+
 class BamFile(object):
-    """A decoded BAM file: header plus the accepted reads as packed arrays per reference.
+    """A decoded BAM file: header plus the accepted reads per reference.
 
     ``reads[chrom]`` is a dict of ``pos`` (1-based leftmost base), ``readlen`` (query length) and
-    ``is_reverse`` in file order -- the arguments of ``CCBitArrayCalculator.feed_batch``.
+    ``is_reverse`` in file order -- the arguments of ``CCBitArrayCalculator.feed_batch``;
+    ``packed(chrom)`` is the same chromosome already reduced by the calculator's feed rules --
+    the arguments of ``feed_packed``.
     Filter: skip read2, MAPQ < mapq_criteria, unmapped, duplicate, records without a reference or
     a CIGAR (PyMaSC/handler/read.py:62-90, :132-143)."""
 
     def __init__(self, path, mapq_criteria=1, threads=0):
         path = str(path)
+        self._h = None
         if not os.path.exists(path):
             raise IOError("input file '{0}' dose not exist.".format(path))
-        L = load_library()
+        L = self._L = load_library()
         h = ctypes.c_void_p()
         rc = L.pmio_bam_load(path.encode(), int(mapq_criteria), int(threads), ctypes.byref(h))
         if rc != 0:
             _raise(L, rc)
-        try:
-            n = L.pmio_bam_n_refs(h)
-            self.references = tuple(L.pmio_bam_ref_name(h, i).decode() for i in range(n))
-            self.lengths = tuple(int(L.pmio_bam_ref_len(h, i)) for i in range(n))
-            st = BamStats()
-            L.pmio_bam_stats_get(h, ctypes.byref(st))
-            self.stats = {k: int(getattr(st, k)) for k, _ in BamStats._fields_ if k != "reserved"}
-            self.sorted = bool(st.sorted)
-            self.reads = {}
-            p, q = ctypes.POINTER(ctypes.c_uint32)(), ctypes.POINTER(ctypes.c_uint32)()
-            r, cnt = ctypes.POINTER(ctypes.c_uint8)(), ctypes.c_uint64()
-            for i, name in enumerate(self.references):
-                L.pmio_bam_reads(h, i, ctypes.byref(p), ctypes.byref(q), ctypes.byref(r), ctypes.byref(cnt))
-                if cnt.value:
-                    self.reads[name] = {"pos": _copy(p, cnt.value, np.int64),
-                                        "readlen": _copy(q, cnt.value, np.int64),
-                                        "is_reverse": _copy(r, cnt.value, bool)}
-            hl, hc, hn = ctypes.POINTER(ctypes.c_uint32)(), ctypes.POINTER(ctypes.c_uint64)(), ctypes.c_uint32()
-            L.pmio_bam_readlen_hist(h, ctypes.byref(hl), ctypes.byref(hc), ctypes.byref(hn))
-            self.readlen_counter = dict(zip(_copy(hl, hn.value, np.int64).tolist(),
-                                            _copy(hc, hn.value, np.int64).tolist()))
-        finally:
-            L.pmio_bam_free(h)
+        self._h = h
+        n = L.pmio_bam_n_refs(h)
+        self.references = tuple(L.pmio_bam_ref_name(h, i).decode() for i in range(n))
+        self.lengths = tuple(int(L.pmio_bam_ref_len(h, i)) for i in range(n))
+        self._index = {name: i for i, name in enumerate(self.references)}
+        st = BamStats()
+        L.pmio_bam_stats_get(h, ctypes.byref(st))
+        self.stats = {k: int(getattr(st, k)) for k, _ in BamStats._fields_ if k != "reserved"}
+        self.sorted = bool(st.sorted)
+        self._counts = {}                       # chromosomes with accepted reads, header order
+        cnt = ctypes.c_uint64()
+        for i, name in enumerate(self.references):
+            L.pmio_bam_reads(h, i, None, None, None, ctypes.byref(cnt))
+            if cnt.value:
+                self._counts[name] = int(cnt.value)
+        self.reads = _LazyReads(self)
+        hl, hc, hn = ctypes.POINTER(ctypes.c_uint32)(), ctypes.POINTER(ctypes.c_uint64)(), ctypes.c_uint32()
+        L.pmio_bam_readlen_hist(h, ctypes.byref(hl), ctypes.byref(hc), ctypes.byref(hn))
+        self.readlen_counter = dict(zip(_copy(hl, hn.value, np.int64).tolist(),
+                                        _copy(hc, hn.value, np.int64).tolist()))
         self.path = path
         self.mapq_criteria = int(mapq_criteria)
+
+    def _reads_of(self, chrom):
+        if chrom not in self._counts:
+            raise KeyError(chrom)
+        p, q = ctypes.POINTER(ctypes.c_uint32)(), ctypes.POINTER(ctypes.c_uint32)()
+        r, cnt = ctypes.POINTER(ctypes.c_uint8)(), ctypes.c_uint64()
+        self._L.pmio_bam_reads(self._h, self._index[chrom], ctypes.byref(p), ctypes.byref(q),
+                               ctypes.byref(r), ctypes.byref(cnt))
+        return {"pos": _copy(p, cnt.value, np.int64), "readlen": _copy(q, cnt.value, np.int64),
+                "is_reverse": _copy(r, cnt.value, bool)}
+
+    def packed(self, chrom):
+        """The chromosome's reads after the feed rules of mscc.pyx:370-418: dict of ``fwd``
+        (sorted unique forward 5' positions, uint32), ``fwd_len_sum``, ``rev`` (sorted unique
+        reverse 5' ends), ``rev_len_sum``, ``first_pos``, ``last_pos``.  Sorted files only."""
+        if not self.sorted:
+            raise ReadUnsortedError
+        if chrom not in self._counts:
+            raise KeyError(chrom)
+        f, r = ctypes.POINTER(ctypes.c_uint32)(), ctypes.POINTER(ctypes.c_uint32)()
+        nf, nr, fs, rs = ctypes.c_uint64(), ctypes.c_uint64(), ctypes.c_uint64(), ctypes.c_uint64()
+        p0, p1 = ctypes.c_uint32(), ctypes.c_uint32()
+        rc = self._L.pmio_bam_packed(self._h, self._index[chrom], ctypes.byref(f), ctypes.byref(nf),
+                                     ctypes.byref(fs), ctypes.byref(r), ctypes.byref(nr), ctypes.byref(rs),
+                                     ctypes.byref(p0), ctypes.byref(p1))
+        if rc != 0:
+            _raise(self._L, rc)
+        return {"fwd": _copy(f, nf.value, np.uint32), "fwd_len_sum": int(fs.value),
+                "rev": _copy(r, nr.value, np.uint32), "rev_len_sum": int(rs.value),
+                "first_pos": int(p0.value), "last_pos": int(p1.value)}
+
+    def close(self):
+        if getattr(self, "_h", None):
+            self._L.pmio_bam_free(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:       # noqa: BLE001 -- interpreter shutdown
+            pass
 
 
 def _mean(c):
@@ -192,16 +264,14 @@ def estimate_readlen(path, esttype="MEDIAN", mapq_criteria=1, threads=0):
 
 
 def feed_bam(calc, bam):
-    """Feed every accepted read of `bam` to a calculator, one ``feed_batch`` per chromosome in
+    """Feed every accepted read of `bam` to a calculator, one ``feed_packed`` per chromosome in
     file order (handler/calc.py:140-153), raising ReadUnsortedError as the per-read loop would."""
     if not bam.sorted:
         raise ReadUnsortedError
-    order = [c for c in bam.references if c in bam.reads]
-    # chromosomes appear in the file in the order of their first accepted read; for a sorted
-    # file that is the header order restricted to chromosomes with reads
-    for chrom in order:
-        r = bam.reads[chrom]
-        calc.feed_batch(chrom, r["pos"], r["readlen"], r["is_reverse"])
+    # chromosomes appear in a sorted file in header order; the per-read rules (duplicates,
+    # read-length sums) were applied natively while decoding
+    for chrom in bam.reads:
+        calc.feed_packed(chrom, **bam.packed(chrom))
 
 
 # ------------------------------------------------------------------------------------- BigWig

@@ -267,3 +267,52 @@ def test_run_files_from_bam_and_bigwig_matches_golden_tables(tmp_path):
     with pytest.raises(ValueError):
         pipeline.run_files(BAM, None, max_shift=20, mapq_criteria=10, engine=OracleEngine())
     assert pipeline.reconcile_chromosome_sizes(["a", "b", "c"], [10, 20, 30], {"a": 12, "b": 15}) == [12, 20, 30]
+
+
+@pytest.mark.parametrize("spec", helpers.TOY_SPECS, ids=lambda s: s["name"])
+def test_packed_feed_from_bam_equals_reference_vectors(tmp_path, spec):
+    """The toy cases (exact duplicates, strand collisions, variable query lengths, read-less
+    chromosomes) written as BAM, decoded natively, reduced by pack_reference and fed with
+    feed_packed: the whole result must equal the unmodified reference's, read-length sums
+    included (they depend on the duplicate rules of mscc.pyx:388-393 and :416-418)."""
+    toy = helpers.make_toy(spec)
+    recs = []
+    for ci, chrom in enumerate(toy["references"]):
+        r = toy["reads"].get(chrom)
+        if r is None:
+            continue
+        for p, l, rev in zip(r["pos"].tolist(), r["readlen"].tolist(), r["is_reverse"].tolist()):
+            recs.append(W.bam_record(ci, p - 1, 30, 16 if rev else 0, [(l, "M")]))
+    path = str(tmp_path / "toy.bam")
+    W.write_bam(path, list(zip(toy["references"], toy["lengths"])), recs, 3000)
+    bam = io_native.BamFile(path, 1)
+    feeder = helpers.ListFeeder(toy["tracks"]) if toy["tracks"] is not None else None
+    calc = CCBitArrayCalculator(spec["D"], spec["rl"], toy["references"], toy["lengths"], feeder,
+                                spec["skip_ncc"], engine=OracleEngine())
+    io_native.feed_bam(calc, bam)
+    calc.finishup_calculation()
+    helpers.assert_snapshots_equal(helpers.snapshot_whole(calc.get_whole_result()),
+                                   helpers.load_ref_vectors()["toy_" + spec["name"]])
+    # per-read arrays and the packed form agree with a numpy restatement of the rules
+    for chrom in bam.reads:
+        r, k = bam.reads[chrom], bam.packed(chrom)
+        f = r["pos"][~r["is_reverse"]]
+        keep = np.ones(f.size, bool)
+        keep[1:] = f[1:] != f[:-1]
+        assert np.array_equal(k["fwd"], f[keep]) and k["fwd_len_sum"] == int(r["readlen"][~r["is_reverse"]][keep].sum())
+        ends = (r["pos"] + r["readlen"] - 1)[r["is_reverse"]]
+        u, first = np.unique(ends, return_index=True)
+        assert np.array_equal(k["rev"], u) and k["rev_len_sum"] == int(r["readlen"][r["is_reverse"]][first].sum())
+        assert (k["first_pos"], k["last_pos"]) == (int(r["pos"][0]), int(r["pos"][-1]))
+
+
+def test_feed_packed_closes_the_chromosome_to_further_reads():
+    calc = CCBitArrayCalculator(50, 20, ["c1", "c2"], [1000, 1000], engine=OracleEngine())
+    calc.feed_packed("c1", [5, 9], 40, [60], 20, 5, 41)
+    with pytest.raises(ValueError):
+        calc.feed_forward_read("c1", 100, 20)
+    with pytest.raises(ValueError):
+        calc.feed_packed("c1", [200], 20, [], 0, 200, 200)
+    calc.feed_forward_read("c2", 7, 20)                  # the next chromosome feeds normally
+    with pytest.raises(ReadUnsortedError):
+        calc.feed_packed("c1", [300], 20, [], 0, 300, 300)     # c1 is already solved
