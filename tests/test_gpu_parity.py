@@ -563,3 +563,31 @@ def test_rank_jobs_from_the_sharding_plan_add_up(pdev, world):
         assert sorted(a) == sorted(m)
         for k in a:
             assert np.array_equal(np.asarray(a[k]), np.asarray(m[k])), k
+
+
+# ----------------------------------------------------------------- from the binary files
+def test_files_to_golden_tables_on_the_device(tmp_path):
+    """configs[0] end to end: the reference's BAM + BigWig fixtures through the native readers
+    and the CUDA path (pymasc_b200.pipeline.run_files) against the reference's golden curves,
+    and the mappable-length statistics (pymasc_b200.mappability) against the reference's JSON."""
+    import json
+    import os
+    import shutil
+    from pymasc_b200 import pipeline
+    from pymasc_b200.mappability import MappabilityHandler
+    gold = helpers.load_golden_tables()
+    bam = os.path.join(helpers.GOLDEN, "ENCFF000RMB-test.bam")
+    bw = str(tmp_path / "hg19_36mer-test.bigwig")
+    shutil.copyfile(os.path.join(helpers.GOLDEN, "hg19_36mer-test.bigwig"), bw)
+    results, info = pipeline.run_files([bam, bam], bw, max_shift=300, mapq_criteria=10)
+    assert info["files"][0]["read_len"] == 36
+    for whole in results:
+        assert (whole.forward_sum, whole.reverse_sum, whole.genomelen) == (622, 670, 3137454505)
+        for got, want in ((whole.chroms["chr1"].cc, gold["cc"]["chr1"]),
+                          (whole.mappable_chroms["chr1"].cc, gold["mscc"]["chr1"])):
+            want = np.array(want)
+            assert np.max(np.abs(np.asarray(got) - want) / np.abs(want)) <= RTOL
+    h = MappabilityHandler(bw, max_shift=300, readlen=36)
+    h.calc_mappability()
+    h.save_mappability_stats()
+    assert json.load(open(h.map_path)) == gold["mappability_json"]

@@ -316,3 +316,41 @@ def test_feed_packed_closes_the_chromosome_to_further_reads():
     calc.feed_forward_read("c2", 7, 20)                  # the next chromosome feeds normally
     with pytest.raises(ReadUnsortedError):
         calc.feed_packed("c1", [300], 20, [], 0, 300, 300)     # c1 is already solved
+
+
+# ------------------------------------------------------------------- mappable-length statistics
+def test_mappability_handler_reproduces_the_reference_json(tmp_path):
+    """pymasc_b200.mappability.MappabilityHandler on the reference's BigWig fixture must write
+    the reference's own tests/data/hg19_36mer-test_mappability.json (committed inside
+    tests/golden/golden_encff000rmb.json): same keys, same 266 values per list."""
+    import json
+    import shutil
+    from pymasc_b200.mappability import MappabilityHandler, BWIOError
+    want = helpers.load_golden_tables()["mappability_json"]
+    bw = str(tmp_path / "hg19_36mer-test.bigwig")
+    shutil.copyfile(BIGWIG, bw)
+    assert MappabilityHandler.calc_mappable_len_required_shift_size(36, 300) == 265
+    assert MappabilityHandler.calc_mappable_len_required_shift_size(36, 50) == 36
+    h = MappabilityHandler(bw, max_shift=300, readlen=36, engine=OracleEngine())
+    assert h.max_shift == 265 and h.need_save_stats and not h.is_called
+    assert str(h.map_path).endswith("hg19_36mer-test_mappability.json")
+    h.calc_mappability()
+    assert h.is_called and list(h.chrom2mappable_len) == ["chr1"]
+    h.save_mappability_stats()
+    got = json.load(open(h.map_path))
+    assert got == want
+    assert h.get_mappable_len("chr1", 0, 3) == tuple(want["references"]["chr1"][:3])
+    assert h.get_mappable_len(shift_from=10, shift_to=12) == want["__whole__"][10:12]
+    assert h.get_mappable_len("chrNope") is None
+    # a second handler finds the cache and calculates nothing; a longer shift needs an update
+    engine = OracleEngine()
+    h2 = MappabilityHandler(bw, max_shift=200, readlen=36, engine=engine)
+    assert h2.is_called and not h2.need_save_stats and h2.max_shift == 165
+    assert h2.mappable_len == want["__whole__"][:166]
+    h2.calc_mappability()
+    assert engine.batches == []
+    h3 = MappabilityHandler(bw, max_shift=400, readlen=36, engine=engine)
+    assert h3.need_save_stats and not h3.is_called
+    assert h3.get_mappable_len("chr1", force=True)[:266] == tuple(want["references"]["chr1"])
+    with pytest.raises(BWIOError):
+        MappabilityHandler(str(tmp_path / "missing.bw"), 300, 36)
