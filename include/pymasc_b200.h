@@ -115,6 +115,7 @@ typedef struct {
     float ev_edge_ms;   /* event path: run-edge kernel(s) + finalize          */
 } pmb_timing;
 
+int  pmb_device_count(void);                 /* usable CUDA devices (0 on any error)   */
 int  pmb_create(pmb_ctx **out, int device_ordinal);
 void pmb_destroy(pmb_ctx *ctx);
 const char *pmb_last_error(pmb_ctx *ctx);   /* ctx may be NULL: last create error */

@@ -59,7 +59,7 @@ EXPORTS = (
     "pmb_create", "pmb_destroy", "pmb_last_error", "pmb_run_chrom", "pmb_run_batch",
     "pmb_batch_prepare", "pmb_batch_execute", "pmb_batch_fetch", "pmb_batch_counters",
     "pmb_batch_free", "pmb_get_timing", "pmb_stream", "pmb_synchronize", "pmb_host_alloc",
-    "pmb_host_free", "pmb_set_option", "pmb_pipe_probe", "pmb_set_stream",
+    "pmb_host_free", "pmb_set_option", "pmb_pipe_probe", "pmb_set_stream", "pmb_device_count",
 )
 
 _lib = None
@@ -78,6 +78,8 @@ def load_library():
     vp, vpp = ctypes.c_void_p, ctypes.POINTER(ctypes.c_void_p)
     L.pmb_create.argtypes = [vpp, ctypes.c_int]
     L.pmb_create.restype = ctypes.c_int
+    L.pmb_device_count.argtypes = []
+    L.pmb_device_count.restype = ctypes.c_int
     L.pmb_destroy.argtypes = [vp]
     L.pmb_destroy.restype = None
     L.pmb_last_error.argtypes = [vp]
@@ -125,6 +127,11 @@ def _as_u32(a):
     if a.dtype != np.uint32 or not a.flags.c_contiguous:
         a = np.ascontiguousarray(a, dtype=np.uint32)
     return a
+
+
+def device_count():
+    """CUDA devices the library can see (0 without a driver or GPU)."""
+    return int(load_library().pmb_device_count())
 
 
 class Job(object):

@@ -211,6 +211,12 @@ extern "C" int pmb_create(pmb_ctx** out, int device_ordinal)
     return PMB_OK;
 }
 
+extern "C" int pmb_device_count(void)
+{
+    int n = 0;
+    return cudaGetDeviceCount(&n) == cudaSuccess ? n : 0;
+}
+
 extern "C" void pmb_destroy(pmb_ctx* c)
 {
     if (!c) return;

@@ -591,3 +591,28 @@ def test_files_to_golden_tables_on_the_device(tmp_path):
     h.calc_mappability()
     h.save_mappability_stats()
     assert json.load(open(h.map_path)) == gold["mappability_json"]
+
+
+def test_multi_device_engine_with_two_contexts():
+    """MultiDeviceEngine drives one pmb_ctx per device from its own host thread; with a single
+    GPU in the box two contexts on device 0 exercise the same concurrency."""
+    from pymasc_b200.multigpu import MultiDeviceEngine
+    rl, D, S = 36, 300, _shim.FLAG_SAME_TRACK
+    jobs, wants = [], []
+    for c, L in enumerate([120000, 60000, 200000, 33000]):
+        _, _, b, e = random_case(700 + c, L, rl, 10)
+        for f in range(2):
+            fwd, rev, _, _ = random_case(710 + 10 * c + f, L, rl, L // 15, with_track=False)
+            jobs.append(_shim.Job(L, rl, D, 3 | (S if f else 0), fwd, rev, None if f else b, None if f else e))
+            wants.append(cc_oracle.chrom_counts(L, rl, D, fwd, rev, b, e))
+    eng = MultiDeviceEngine([0, 0])
+    try:
+        for _ in range(2):
+            got = eng.run(jobs)
+            assert all(len(idx) for idx in eng.last_placement)
+            for g, w in zip(got, wants):
+                for k in w:
+                    assert np.array_equal(np.asarray(g[k]), np.asarray(w[k])), k
+    finally:
+        eng.close()
+    assert _shim.device_count() >= 1

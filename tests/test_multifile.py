@@ -93,3 +93,78 @@ def test_calculators_with_different_geometry_get_their_own_batches():
         ref.finishup_calculation()
         helpers.assert_snapshots_equal(helpers.snapshot_whole(c.get_whole_result()),
                                        helpers.snapshot_whole(ref.get_whole_result()))
+
+
+# ------------------------------------------------------------------ several devices, one process
+def _batch_for_devices():
+    from pymasc_b200.multifile import merge_shared_tracks
+    spec = helpers.TOY_SPECS[0]
+    toys = toy_files(spec, 3)
+    feeder = helpers.ListFeeder(toys[0]["tracks"])
+    calcs = []
+    for t in toys:
+        c = CCBitArrayCalculator(spec["D"], spec["rl"], t["references"], t["lengths"], feeder, False,
+                                 engine=OracleEngine())
+        feed(c, t)
+        c._close_chromosome()
+        calcs.append(c)
+    lists = [c._collect_jobs(fill=list(c.references))[0] for c in calcs]
+    return merge_shared_tracks(lists)[0]
+
+
+def test_placement_keeps_shared_track_runs_on_one_device():
+    from pymasc_b200.multigpu import place_jobs, job_cost
+    jobs = _batch_for_devices()
+    S = _shim.FLAG_SAME_TRACK
+    for n_dev in (1, 2, 3, 8):
+        placement = place_jobs(jobs, n_dev)
+        assert sorted(i for idx in placement for i in idx) == list(range(len(jobs)))
+        where = {i: d for d, idx in enumerate(placement) for i in idx}
+        for i, j in enumerate(jobs):
+            if j.flags & S:
+                assert where[i] == where[i - 1]             # a follower sits right behind its owner
+                assert placement[where[i]].index(i) == placement[where[i]].index(i - 1) + 1
+    two = place_jobs(jobs, 2)
+    loads = [sum(job_cost(jobs[i]) for i in idx) for idx in two]
+    assert min(loads) > 0.5 * max(loads)                    # LPT: no device is left nearly idle
+
+
+def test_multi_device_engine_equals_one_device():
+    from pymasc_b200.multigpu import MultiDeviceEngine
+    jobs = _batch_for_devices()
+    want = OracleEngine().run(jobs)
+    devices = [OracleEngine(), OracleEngine(), OracleEngine()]
+    eng = MultiDeviceEngine(devices)
+    got = eng.run(jobs)
+    assert sum(len(d.batches) for d in devices) == 3 and all(d.batches for d in devices)
+    for g, w in zip(got, want):
+        assert sorted(g) == sorted(w)
+        for k in w:
+            assert np.array_equal(np.asarray(g[k]), np.asarray(w[k])), k
+    assert eng.run([]) == []
+
+    class Broken(object):
+        def run(self, jobs):
+            raise RuntimeError("device lost")
+    with pytest.raises(RuntimeError):
+        MultiDeviceEngine([OracleEngine(), Broken()]).run(jobs)
+
+
+def test_multifile_calculation_over_several_devices():
+    from pymasc_b200.multigpu import MultiDeviceEngine
+    spec = helpers.TOY_SPECS[0]
+    toys = toy_files(spec, 3)
+    feeder = helpers.ListFeeder(toys[0]["tracks"])
+    alone, together = [], []
+    for t in toys:
+        for dst in (alone, together):
+            c = CCBitArrayCalculator(spec["D"], spec["rl"], t["references"], t["lengths"], feeder,
+                                     spec["skip_ncc"], engine=OracleEngine())
+            feed(c, t)
+            dst.append(c)
+    for c in alone:
+        c.finishup_calculation()
+    MultiFileCalculation(together, engine=MultiDeviceEngine([OracleEngine(), OracleEngine()])).finishup_calculation()
+    for a, b in zip(alone, together):
+        helpers.assert_snapshots_equal(helpers.snapshot_whole(b.get_whole_result()),
+                                       helpers.snapshot_whole(a.get_whole_result()))

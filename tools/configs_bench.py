@@ -148,9 +148,69 @@ def config5(args, dev, stream):
     return out
 
 
+def by_chromosome(args):
+    """configs[2] (one genome) or configs[4] (--files read sets over one track) on --devices GPUs
+    of the box, one process: whole chromosomes per GPU (the reference's -p N unit), no
+    collective.  Timed end to end from pinned host arrays, wall clock around
+    MultiDeviceEngine.run, with each device's own CUDA-event time beside it."""
+    import torch
+    import bench
+    from pymasc_b200 import _shim, synth
+    from pymasc_b200.multigpu import MultiDeviceEngine
+    D = args.max_shift or 1000
+    S = _shim.FLAG_SAME_TRACK
+    lengths = [L for _, L in synth.HG38]
+    total = float(sum(lengths))
+    flags = _shim.FLAG_MSCC | (0 if args.files > 1 else _shim.FLAG_NCC)
+    t0 = time.time()
+    jobs = []
+    for i, L in enumerate(lengths):
+        n = max(8, int(round(20_000_000 * L / total)))
+        b, e = synth.mappability(i, L)
+        for f in range(args.files):
+            fwd, rev = synth.chip_reads(i, L, n, READ_LEN, seed=20260101 + 100 * f)
+            jobs.append(_shim.Job(L, READ_LEN, D, flags | (S if f else 0), fwd, rev,
+                                  None if f else b, None if f else e))
+    gen_s = time.time() - t0
+    h2d = bench.pinned_pack(jobs)
+    evals = synth.evals(lengths, READ_LEN, D) * args.files
+    out = {"config": "%d read set(s), %s, max_shift %d, whole chromosomes per GPU, one process" %
+                     (args.files, "MSCC only, shared track" if args.files > 1 else "NCC+MSCC", D),
+           "metric": "bit-position x shift evals/s", "unit": "evals/s", "evals_per_step": evals,
+           "h2d_bytes_per_step": int(h2d), "steps": args.steps, "warmup": args.warmup,
+           "synthetic_generation_s": round(gen_s, 1), "by_devices": {}}
+    ref = None
+    n_dev = 1
+    while n_dev <= args.devices:
+        eng = MultiDeviceEngine(list(range(n_dev)))
+        for _ in range(args.warmup):
+            res = eng.run(jobs)
+        torch.cuda.synchronize()
+        walls, dev_ms = [], []
+        for _ in range(args.steps):
+            t0 = time.perf_counter()
+            res = eng.run(jobs)
+            walls.append((time.perf_counter() - t0) * 1e3)
+            dev_ms.append(max(x for x in eng.last_device_ms if x is not None))
+        eng.close()
+        if ref is None:
+            ref = res
+        same = all(np.array_equal(np.asarray(a[k]), np.asarray(b2[k])) for a, b2 in zip(ref, res) for k in a)
+        out["by_devices"][str(n_dev)] = {
+            "e2e_ms_per_step": float(np.mean(walls)), "e2e_ms_min": float(np.min(walls)),
+            "value_e2e": evals / (float(np.mean(walls)) * 1e-3),
+            "slowest_device_execute_ms": float(np.mean(dev_ms)),
+            "jobs_per_device": [len(idx) for idx in eng.last_placement],
+            "equals_1_device": bool(same)}
+        n_dev *= 2
+    return out
+
+
 def main():
     ap = argparse.ArgumentParser()
-    ap.add_argument("--config", type=int, required=True, choices=[4, 5])
+    ap.add_argument("--config", type=int, required=True, choices=[3, 4, 5])
+    ap.add_argument("--devices", type=int, default=0,
+                    help="config 3 / 5: run on 1, 2, 4 ... up to this many GPUs through MultiDeviceEngine")
     ap.add_argument("--reads", type=int, default=200_000_000)
     ap.add_argument("--files", type=int, default=16)
     ap.add_argument("--max-shift", type=int, default=0)
@@ -160,6 +220,11 @@ def main():
     args = ap.parse_args()
     import torch
     from pymasc_b200 import _shim
+    if args.config == 3 or args.devices:
+        if args.config == 3:
+            args.files = 1
+        print(json.dumps(by_chromosome(args)), flush=True)
+        return
     torch.cuda.set_device(0)
     dev = _shim.Device(0)
     stream = torch.cuda.Stream(device=0)
