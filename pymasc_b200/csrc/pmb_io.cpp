@@ -183,9 +183,11 @@ struct ShareStats {
     std::vector<uint64_t> hist_small = std::vector<uint64_t>(1024, 0);
     std::map<uint32_t, uint64_t> hist;
     bool sorted = true;         // within every run
+    bool incomplete = false;    // stopped at a record that runs past the end of the batch
     const char* err = nullptr;
     void reset()
     {
+        incomplete = false;
         st = pmio_bam_stats{};
         std::fill(hist_small.begin(), hist_small.end(), 0);
         hist.clear();
@@ -194,28 +196,37 @@ struct ShareStats {
     }
 };
 
-// [p, p+n) holds complete records only (the boundary scan has validated every block_size).
-void parse_share(const uint8_t* p, size_t n, uint32_t n_refs, int mapq, pmio_chunk& out, ShareStats& ss)
+// Filters the records that START in [start, limit) of the batch buffer p[0, end); returns where
+// it stopped: the start of the first record at or beyond `limit`, or of a record that does not
+// end inside the batch (ss.incomplete).  `start` may be a guess (a BGZF block boundary): every
+// read is bounds-checked, and what a wrong guess produces (ss.err, or a stop that the caller's
+// validation rejects) is thrown away.
+size_t parse_share(const uint8_t* p, size_t start, size_t limit, size_t end, uint32_t n_refs, int mapq,
+                   pmio_chunk& out, ShareStats& ss)
 {
     pmio_bam_stats& st = ss.st;
-    const size_t guess = n / 64 + 16;       // virtual reservation; untouched pages cost nothing
+    const size_t guess = (limit - start) / 64 + 16;       // virtual reservation; untouched pages cost nothing
     out.pos.reserve(guess); out.qlen.reserve(guess); out.rev.reserve(guess);
-    size_t o = 0;
-    while (o < n) {
+    size_t o = start;
+    while (o < limit) {
+        if (end - o < 4) { ss.incomplete = true; return o; }
         const int32_t bs = rdi32(p + o);
+        if (bs < 32) { ss.err = "corrupt BAM record (block_size < 32)"; return o; }
+        if (end - o < 4 + (size_t)bs) { ss.incomplete = true; return o; }
         const uint8_t* r = p + o + 4;
+        const size_t rec = o;
         o += 4 + (size_t)bs;
         st.n_records++;
         const int32_t ref = rdi32(r);
         if (ref < 0) continue;                                   // reference_name is None
-        if ((uint32_t)ref >= n_refs) { ss.err = "BAM record names an unknown reference"; return; }
+        if ((uint32_t)ref >= n_refs) { ss.err = "BAM record names an unknown reference"; return rec; }
         const int32_t pos0 = rdi32(r + 4);
         const uint32_t l_name = r[8], mq = r[9];
         const uint32_t n_cig = rd16(r + 12), flag = rd16(r + 14);
         st.n_with_ref++;
         if (flag & 0x1) { st.n_paired++; if (flag & 0x80) st.n_read2++; }
         if (flag & 0x4) st.n_unmapped++;
-        if (32 + l_name + 4ull * n_cig > (uint32_t)bs) { ss.err = "corrupt BAM record (CIGAR overruns)"; return; }
+        if (32 + l_name + 4ull * n_cig > (uint32_t)bs) { ss.err = "corrupt BAM record (CIGAR overruns)"; return rec; }
         // infer_query_length(): M, I, S, =, X; None (skip) without a CIGAR
         uint32_t ql = 0;
         const uint8_t* cg = r + 32 + l_name;
@@ -239,6 +250,7 @@ void parse_share(const uint8_t* p, size_t n, uint32_t n_refs, int mapq, pmio_chu
         out.rev.push_back((flag & 0x10) ? 1 : 0);
         st.n_accepted++;
     }
+    return o;
 }
 
 // Shares of a batch, in file order: their runs become segments of the per-reference lists;
@@ -342,7 +354,7 @@ extern "C" int pmio_bam_load(const char* path, int mapq_criteria, int threads, p
     BamHeaderParser header{b};
     BamMerger merger{b};
     std::vector<ShareStats> share_stats((size_t)threads);
-    std::vector<size_t> cuts;
+    std::vector<size_t> cuts, stops;
     // PMIO_TIMING=1: seconds per stage on stderr (debug aid)
     static const bool timing = getenv("PMIO_TIMING") != nullptr;
     auto now = []() { return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count(); };
@@ -406,10 +418,14 @@ extern "C" int pmio_bam_load(const char* path, int mapq_criteria, int threads, p
         for (auto& t : pool) t.join();
         if (!ok.load()) { g_err = "BGZF block does not inflate (corrupt data or CRC mismatch)"; bad = true; break; }
         { const double t = now(); t_inflate += t - t_mark; t_mark = t; }
-        // ---- header first (sequential), then the records: find the record boundaries by
-        //      hopping over block_size fields, cut the batch into one share per thread at record
-        //      boundaries, filter the shares in parallel, take them in file order.  The record
-        //      cut by the end of the batch is carried into the next one.
+        // ---- header first (sequential), then the records.  Shares start at BGZF block boundaries
+        //      -- htslib never lets a record straddle two blocks unless it is longer than one, so a
+        //      block boundary is almost always a record boundary -- and are filtered in parallel ON
+        //      THAT GUESS; afterwards the guesses are checked inductively in file order (share 0
+        //      starts at a known boundary; share i+1's start is right iff it is where share i
+        //      stopped) and a share whose start was wrong is filtered again from the true boundary.
+        //      No sequential pass over the records remains in the common case.  The record cut by
+        //      the end of the batch is carried into the next one.
         size_t used = 0;
         if (header.stage != 2) {
             const long long h = header.feed(buf.data(), out_off);
@@ -421,44 +437,52 @@ extern "C" int pmio_bam_load(const char* path, int mapq_criteria, int threads, p
             const size_t share = std::max<size_t>((out_off - used) / (size_t)threads + 1, 1 << 16);
             cuts.clear();
             cuts.push_back(used);
-            size_t o = used;
-            while (out_off - o >= 4) {
-                const int32_t bs = rdi32(p + o);
-                if (bs < 32) { g_err = "corrupt BAM record (block_size < 32)"; bad = true; break; }
-                if (out_off - o < 4 + (size_t)bs) break;
-                o += 4 + (size_t)bs;
-                if (o - cuts.back() >= share) cuts.push_back(o);
-            }
-            if (bad) break;
-            if (cuts.back() != o) cuts.push_back(o);
-            { const double t = now(); t_scan += t - t_mark; t_mark = t; }
+            for (const Block& k : blocks)
+                if (k.out_off > cuts.back() && k.out_off - cuts.back() >= share) cuts.push_back(k.out_off);
+            cuts.push_back(out_off);
             const size_t n_shares = cuts.size() - 1;
             const uint32_t n_refs = (uint32_t)b->names.size();
             if (share_stats.size() < n_shares) share_stats.resize(n_shares);
+            stops.assign(n_shares, 0);
             const size_t store0 = b->store.size();
             for (size_t i = 0; i < n_shares; i++) b->store.emplace_back(new pmio_chunk());
             std::atomic<size_t> next_share{0};
             auto parse_work = [&]() {
                 for (size_t i; (i = next_share.fetch_add(1)) < n_shares;) {
                     share_stats[i].reset();
-                    parse_share(p + cuts[i], cuts[i + 1] - cuts[i], n_refs, mapq_criteria, *b->store[store0 + i],
-                                share_stats[i]);
+                    stops[i] = parse_share(p, cuts[i], cuts[i + 1], out_off, n_refs, mapq_criteria,
+                                           *b->store[store0 + i], share_stats[i]);
                 }
             };
             std::vector<std::thread> ppool;
             for (size_t t = 1; t < std::min<size_t>((size_t)threads, n_shares); t++) ppool.emplace_back(parse_work);
             parse_work();
             for (auto& t : ppool) t.join();
-            for (size_t i = 0; i < n_shares && !bad; i++) {
+            { const double t = now(); t_parse += t - t_mark; t_mark = t; }
+            size_t at = used;                       // a true record boundary
+            for (size_t i = 0; i < n_shares; i++) {
+                pmio_chunk& c = *b->store[store0 + i];
+                if (at >= cuts[i + 1] && cuts[i + 1] != cuts[i]) { c = pmio_chunk(); continue; }   // inside a long record
+                if (at != cuts[i]) {                // wrong guess: again, from the true boundary
+                    c = pmio_chunk();
+                    share_stats[i].reset();
+                    stops[i] = parse_share(p, at, cuts[i + 1], out_off, n_refs, mapq_criteria, c, share_stats[i]);
+                    b->st.reparsed_shares++;
+                }
                 if (share_stats[i].err) { g_err = share_stats[i].err; bad = true; break; }
-                merger.take(*b->store[store0 + i], share_stats[i]);
+                merger.take(c, share_stats[i]);
+                at = stops[i];
+                if (share_stats[i].incomplete) {
+                    for (size_t k = i + 1; k < n_shares; k++) *b->store[store0 + k] = pmio_chunk();
+                    break;
+                }
             }
             if (bad) break;
-            used = o;
+            used = at;
+            { const double t = now(); t_scan += t - t_mark; t_mark = t; }
         }
         carry = out_off - used;
         if (carry && used) memmove(buf.data(), buf.data() + used, carry);
-        { const double t = now(); t_parse += t - t_mark; t_mark = t; }
     }
     if (!bad && header.stage != 2) { g_err = "truncated BAM header"; bad = true; }
     if (!bad && carry) { g_err = "truncated BAM file (incomplete record at the end)"; bad = true; }
@@ -486,8 +510,9 @@ extern "C" int pmio_bam_load(const char* path, int mapq_criteria, int threads, p
     }
     t_pack = now() - t_mark;
     if (timing)
-        fprintf(stderr, "[pmio bam] %d threads, %zu-block batches: inflate %.3f s, boundary scan %.3f s, filter %.3f s, "
-                        "pack %.3f s\n", threads, BATCH_BLOCKS, t_inflate, t_scan, t_parse, t_pack);
+        fprintf(stderr, "[pmio bam] %d threads, %zu-block batches: inflate %.3f s, filter %.3f s, validate + carry %.3f s "
+                        "(%u shares filtered again), pack %.3f s\n", threads, BATCH_BLOCKS, t_inflate, t_parse, t_scan,
+                b->st.reparsed_shares, t_pack);
     *out = b;
     return PMIO_OK;
 }

@@ -35,11 +35,18 @@ def counters_tensor(batch):
 
 
 def job_chroms(jobs):
-    """The sharding module's chromosome dicts from whole-chromosome jobs."""
-    return [{"length": j.chrom_len, "fwd": j.fwd_pos, "rev": j.rev_pos,
-             "begins": j.map_begins if j.flags & (_shim.FLAG_MSCC | _shim.FLAG_AUTOCORR) else None,
-             "ends": j.map_ends if j.flags & (_shim.FLAG_MSCC | _shim.FLAG_AUTOCORR) else None,
-             "flags": j.flags} for j in jobs]
+    """The sharding module's chromosome dicts from whole-chromosome jobs.  Position shards cut
+    every job at its own place, so a FLAG_SAME_TRACK follower (whose range must equal its
+    owner's, include/pymasc_b200.h) becomes an ordinary job over the owner's intervals."""
+    out, track = [], (None, None)
+    for j in jobs:
+        has_map = bool(j.flags & (_shim.FLAG_MSCC | _shim.FLAG_AUTOCORR))
+        if has_map and not j.flags & _shim.FLAG_SAME_TRACK:
+            track = (j.map_begins, j.map_ends)
+        out.append({"length": j.chrom_len, "fwd": j.fwd_pos, "rev": j.rev_pos,
+                    "begins": track[0] if has_map else None, "ends": track[1] if has_map else None,
+                    "flags": j.flags & ~_shim.FLAG_SAME_TRACK})
+    return out
 
 
 def shard_jobs(jobs, rank, world):

@@ -40,7 +40,7 @@ class BamStats(ctypes.Structure):
     _fields_ = [("n_records", ctypes.c_uint64), ("n_with_ref", ctypes.c_uint64),
                 ("n_unmapped", ctypes.c_uint64), ("n_paired", ctypes.c_uint64),
                 ("n_read2", ctypes.c_uint64), ("n_accepted", ctypes.c_uint64),
-                ("sorted", ctypes.c_uint32), ("reserved", ctypes.c_uint32)]
+                ("sorted", ctypes.c_uint32), ("reparsed_shares", ctypes.c_uint32)]
 
 
 _lib = None
@@ -164,7 +164,7 @@ class BamFile(object):
         self._index = {name: i for i, name in enumerate(self.references)}
         st = BamStats()
         L.pmio_bam_stats_get(h, ctypes.byref(st))
-        self.stats = {k: int(getattr(st, k)) for k, _ in BamStats._fields_ if k != "reserved"}
+        self.stats = {k: int(getattr(st, k)) for k, _ in BamStats._fields_}
         self.sorted = bool(st.sorted)
         self._counts = {}                       # chromosomes with accepted reads, header order
         cnt = ctypes.c_uint64()

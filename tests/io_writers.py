@@ -33,17 +33,36 @@ def bam_record(ref_id, pos0, mapq, flag, cigar, name=b"r", l_seq=None):
     return struct.pack("<i", len(body)) + body
 
 
-def write_bam(path, refs, records, block_payload=65280, text=b"@HD\tVN:1.6\tSO:coordinate\n"):
+def write_bam(path, refs, records, block_payload=65280, text=b"@HD\tVN:1.6\tSO:coordinate\n",
+              align_records=False):
     """refs: [(name, length)]; records: bytes objects from bam_record.  The uncompressed stream
-    is cut into blocks of `block_payload` bytes regardless of record boundaries."""
-    stream = b"BAM\1" + struct.pack("<i", len(text)) + text + struct.pack("<i", len(refs))
+    is cut into blocks of `block_payload` bytes regardless of record boundaries; with
+    `align_records` the way htslib does it: the header in blocks of its own, and a record that
+    would not fit starts a new block (no record straddles two blocks unless it is longer than
+    one)."""
+    head = b"BAM\1" + struct.pack("<i", len(text)) + text + struct.pack("<i", len(refs))
     for name, length in refs:
         nm = name.encode() + b"\0"
-        stream += struct.pack("<i", len(nm)) + nm + struct.pack("<i", length)
-    stream += b"".join(records)
+        head += struct.pack("<i", len(nm)) + nm + struct.pack("<i", length)
     with open(path, "wb") as fh:
-        for o in range(0, len(stream), block_payload):
-            fh.write(bgzf_block(stream[o:o + block_payload]))
+        if not align_records:
+            stream = head + b"".join(records)
+            for o in range(0, len(stream), block_payload):
+                fh.write(bgzf_block(stream[o:o + block_payload]))
+        else:
+            for o in range(0, len(head), block_payload):
+                fh.write(bgzf_block(head[o:o + block_payload]))
+            cur = b""
+            for r in records:
+                if cur and len(cur) + len(r) > block_payload:
+                    fh.write(bgzf_block(cur))
+                    cur = b""
+                cur += r
+                while len(cur) > block_payload:           # a record longer than a block
+                    fh.write(bgzf_block(cur[:block_payload]))
+                    cur = cur[block_payload:]
+            if cur:
+                fh.write(bgzf_block(cur))
         fh.write(BGZF_EOF)
 
 

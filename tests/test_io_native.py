@@ -108,12 +108,21 @@ def synthetic_records():
     return recs, want, hist
 
 
-@pytest.mark.parametrize("block_payload,threads", [(65280, 1), (997, 3), (64, 2)])
-def test_synthetic_bam_flags_cigars_and_block_boundaries(tmp_path, block_payload, threads):
+@pytest.mark.parametrize("block_payload,threads,aligned", [
+    (65280, 1, False), (997, 3, False), (64, 2, False), (8192, 4, False),
+    (8192, 4, True), (997, 3, True), (150, 2, True)])       # 150: some records are longer than a block
+def test_synthetic_bam_flags_cigars_and_block_boundaries(tmp_path, block_payload, threads, aligned):
+    """Shares of a batch start at BGZF block boundaries on the guess that those are record
+    boundaries (true for htslib-written files: `aligned`); every wrong guess must be caught by
+    the validation pass and filtered again -- same result either way."""
     recs, want, hist = synthetic_records()
     path = str(tmp_path / "syn.bam")
-    W.write_bam(path, [("c1", 200000), ("c2", 5000), ("c3", 90000)], recs, block_payload)
+    W.write_bam(path, [("c1", 200000), ("c2", 5000), ("c3", 90000)], recs, block_payload, align_records=aligned)
     bam = io_native.BamFile(path, mapq_criteria=20, threads=threads)
+    if aligned and block_payload >= 997:
+        assert bam.stats["reparsed_shares"] == 0
+    if not aligned and block_payload == 8192:
+        assert bam.stats["reparsed_shares"] > 0
     assert bam.references == ("c1", "c2", "c3") and bam.lengths == (200000, 5000, 90000)
     assert sorted(bam.reads) == ["c1", "c3"] and bam.sorted
     for chrom in ("c1", "c3"):

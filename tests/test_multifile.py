@@ -168,3 +168,23 @@ def test_multifile_calculation_over_several_devices():
     for a, b in zip(alone, together):
         helpers.assert_snapshots_equal(helpers.snapshot_whole(b.get_whole_result()),
                                        helpers.snapshot_whole(a.get_whole_result()))
+
+
+def test_position_shards_of_a_shared_track_batch_add_up():
+    """ShardedEngine's decomposition cuts every job at its own place, so followers are turned
+    back into ordinary jobs over the owner's intervals; the rank partials still sum to the whole."""
+    from pymasc_b200 import sharding
+    from pymasc_b200.distributed import shard_jobs
+    jobs = _batch_for_devices()
+    assert any(j.flags & _shim.FLAG_SAME_TRACK for j in jobs)
+    whole = OracleEngine().run(jobs)
+    for world in (2, 3):
+        parts = []
+        for r in range(world):
+            mine = shard_jobs(jobs, r, world)
+            assert not any(j.flags & _shim.FLAG_SAME_TRACK for j in mine)
+            parts.append(OracleEngine().run(mine))
+        for a, m in zip(whole, sharding.sum_outputs(parts)):
+            assert sorted(a) == sorted(m)
+            for k in a:
+                assert np.array_equal(np.asarray(a[k]), np.asarray(m[k])), k

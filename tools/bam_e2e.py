@@ -47,9 +47,13 @@ def write_bam(path, workload, threads):
         nm = w["name"].encode() + b"\0"
         head += struct.pack("<i", len(nm)) + nm + struct.pack("<i", w["length"])
     n_total = 0
-    BLK = 65280
+    # like htslib: the header is flushed in blocks of its own and no record straddles two blocks
+    # (bgzf_flush_try before a record that would not fit)
+    BLK = 65280 // REC.itemsize * REC.itemsize
     with open(path, "wb") as fh, ThreadPoolExecutor(threads) as pool:
-        pending = head
+        for o in range(0, len(head), 65280):
+            fh.write(_bgzf(head[o:o + 65280]))
+        pending = b""
         for ci, w in enumerate(workload):
             left = np.concatenate([w["fwd"].astype(np.int64), w["rev"].astype(np.int64) - READ_LEN + 1])
             rev = np.concatenate([np.zeros(w["fwd"].size, bool), np.ones(w["rev"].size, bool)])
