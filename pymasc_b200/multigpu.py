@@ -11,8 +11,15 @@ put back in job order.  No collective, no device-to-device traffic.
 
 A run of ``FLAG_SAME_TRACK`` jobs (several read sets over one mappability track,
 pymasc_b200.multifile) is the unit that is placed -- it stays on one device so that the track is
-built once.  For position sharding of single chromosomes across GPUs (deep libraries) use
-``pymasc_b200.distributed.ShardedEngine`` instead.
+built once.
+
+``split="position"`` is the other decomposition of SURVEY.md 8(e), for deep libraries whose
+largest chromosome is too much for one GPU's share (BASELINE configs[3]): every device counts
+one position range of the concatenated genome with halos rebuilt from the clipped inputs
+(pymasc_b200.sharding), and the per-device count vectors -- (max_shift+1) int64 per counter and
+chromosome, ~1 MB per device -- are summed on the host after the D2H.  (One process per GPU
+with an NCCL all-reduce of the device counter blocks is ``pymasc_b200.distributed.ShardedEngine``;
+in one process the host sum is cheaper than setting up a communicator.)
 """
 import os
 import threading
@@ -56,7 +63,10 @@ class MultiDeviceEngine(object):
     devices: device ordinals (default: every visible CUDA device, or the comma-separated
     ``PYMASC_B200_DEVICES``), or objects with ``run(jobs)`` (tests)."""
 
-    def __init__(self, devices=None):
+    def __init__(self, devices=None, split="chromosome"):
+        if split not in ("chromosome", "position"):
+            raise ValueError("split must be 'chromosome' or 'position'")
+        self.split = split
         if devices is None:
             env = os.environ.get("PYMASC_B200_DEVICES")
             devices = [int(x) for x in env.split(",")] if env else list(range(_shim.device_count()))
@@ -76,10 +86,18 @@ class MultiDeviceEngine(object):
     def run(self, jobs):
         if not jobs:
             return []
-        placement = self.last_placement = place_jobs(jobs, len(self._specs))
+        n_dev = len(self._specs)
+        by_position = self.split == "position" and n_dev > 1
+        if by_position:
+            from .distributed import shard_jobs
+            shards = [shard_jobs(jobs, k, n_dev) for k in range(n_dev)]
+            placement = self.last_placement = [list(range(len(jobs)))] * n_dev
+            parts = [None] * n_dev
+        else:
+            placement = self.last_placement = place_jobs(jobs, n_dev)
         results = [None] * len(jobs)
         errors = []
-        self.last_device_ms = [None] * len(self._specs)
+        self.last_device_ms = [None] * n_dev
 
         def work(k):
             idx = placement[k]
@@ -87,8 +105,11 @@ class MultiDeviceEngine(object):
                 return
             try:
                 eng = self._engine(k)
-                for i, out in zip(idx, eng.run([jobs[i] for i in idx])):
-                    results[i] = out
+                if by_position:
+                    parts[k] = eng.run(shards[k])
+                else:
+                    for i, out in zip(idx, eng.run([jobs[i] for i in idx])):
+                        results[i] = out
                 if isinstance(eng, _DeviceRunner):
                     self.last_device_ms[k] = eng.device.timing()["total_ms"]
             except BaseException as e:      # noqa: BLE001 -- re-raised on the calling thread
@@ -102,6 +123,9 @@ class MultiDeviceEngine(object):
             t.join()
         if errors:
             raise errors[0]
+        if by_position:
+            from .sharding import sum_outputs
+            return sum_outputs(parts)
         return results
 
     def close(self):

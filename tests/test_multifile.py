@@ -188,3 +188,19 @@ def test_position_shards_of_a_shared_track_batch_add_up():
             assert sorted(a) == sorted(m)
             for k in a:
                 assert np.array_equal(np.asarray(a[k]), np.asarray(m[k])), k
+
+
+def test_multi_device_engine_position_split_equals_one_device():
+    from pymasc_b200.multigpu import MultiDeviceEngine
+    jobs = _batch_for_devices()
+    want = OracleEngine().run(jobs)
+    for n_dev in (2, 3):
+        devices = [OracleEngine() for _ in range(n_dev)]
+        got = MultiDeviceEngine(devices, split="position").run(jobs)
+        assert all(d.batches == [len(jobs)] for d in devices)        # every device sees every job
+        for g, w in zip(got, want):
+            assert sorted(g) == sorted(w)
+            for k in w:
+                assert np.array_equal(np.asarray(g[k]), np.asarray(w[k])), k
+    with pytest.raises(ValueError):
+        MultiDeviceEngine([OracleEngine()], split="files")

@@ -206,6 +206,63 @@ def by_chromosome(args):
     return out
 
 
+def by_position(args):
+    """configs[3] (deep library, max_shift 5000) on --devices GPUs, one process: every GPU counts
+    one position range of the concatenated genome with halos rebuilt from its clipped inputs
+    (MultiDeviceEngine(split="position")), count vectors summed on the host.  End to end from
+    pinned host arrays, wall clock around run()."""
+    import torch
+    import bench
+    from concurrent.futures import ThreadPoolExecutor
+    from pymasc_b200 import _shim, synth
+    from pymasc_b200.multigpu import MultiDeviceEngine
+    D = args.max_shift or 5000
+    lengths = [L for _, L in synth.HG38]
+    total = float(sum(lengths))
+    t0 = time.time()
+
+    def make(i):
+        L = lengths[i]
+        fwd, rev = synth.chip_reads(i, L, max(8, int(round(args.reads * L / total))), READ_LEN)
+        b, e = synth.mappability(i, L)
+        return _shim.Job(L, READ_LEN, D, 3, fwd, rev, b, e)
+    with ThreadPoolExecutor(8) as pool:
+        jobs = list(pool.map(make, range(len(lengths))))
+    gen_s = time.time() - t0
+    h2d = bench.pinned_pack(jobs)
+    evals = synth.evals(lengths, READ_LEN, D)
+    out = {"config": "BASELINE configs[3]: deep library (%d reads requested, %d distinct 5' positions), NCC+MSCC, "
+                     "max_shift %d, position ranges with halos, one process" %
+                     (args.reads, sum(j.fwd_pos.size + j.rev_pos.size for j in jobs), D),
+           "metric": "bit-position x shift evals/s", "unit": "evals/s", "evals_per_step": evals,
+           "h2d_bytes_whole_genome": int(h2d), "steps": args.steps, "warmup": args.warmup,
+           "synthetic_generation_s": round(gen_s, 1), "by_devices": {}}
+    ref = None
+    n_dev = 1
+    while n_dev <= args.devices:
+        eng = MultiDeviceEngine(list(range(n_dev)), split="position")
+        for _ in range(args.warmup):
+            res = eng.run(jobs)
+        torch.cuda.synchronize()
+        walls, dev_ms = [], []
+        for _ in range(args.steps):
+            t0 = time.perf_counter()
+            res = eng.run(jobs)
+            walls.append((time.perf_counter() - t0) * 1e3)
+            dev_ms.append([x for x in eng.last_device_ms])
+        eng.close()
+        if ref is None:
+            ref = res
+        same = all(np.array_equal(np.asarray(a[k]), np.asarray(b2[k])) for a, b2 in zip(ref, res) for k in a)
+        out["by_devices"][str(n_dev)] = {
+            "e2e_ms_per_step": float(np.mean(walls)), "e2e_ms_min": float(np.min(walls)),
+            "value_e2e": evals / (float(np.mean(walls)) * 1e-3),
+            "device_execute_ms": [float(np.mean([d[k] for d in dev_ms])) for k in range(n_dev)],
+            "equals_1_device": bool(same)}
+        n_dev *= 2
+    return out
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--config", type=int, required=True, choices=[3, 4, 5])
@@ -220,6 +277,9 @@ def main():
     args = ap.parse_args()
     import torch
     from pymasc_b200 import _shim
+    if args.config == 4 and args.devices:
+        print(json.dumps(by_position(args)), flush=True)
+        return
     if args.config == 3 or args.devices:
         if args.config == 3:
             args.files = 1
