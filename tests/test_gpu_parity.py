@@ -616,3 +616,21 @@ def test_multi_device_engine_with_two_contexts():
     finally:
         eng.close()
     assert _shim.device_count() >= 1
+
+
+def test_multi_device_engine_position_split_with_two_contexts():
+    from pymasc_b200.multigpu import MultiDeviceEngine
+    rl, D = 36, 1300                       # two column chunks
+    jobs, wants = [], []
+    for c, L in enumerate([150000, 70000, 260000]):
+        fwd, rev, b, e = random_case(800 + c, L, rl, L // 10)
+        jobs.append(_shim.Job(L, rl, D, 3, fwd, rev, b, e))
+        wants.append(cc_oracle.chrom_counts(L, rl, D, fwd, rev, b, e))
+    eng = MultiDeviceEngine([0, 0, 0], split="position")
+    try:
+        got = eng.run(jobs)
+    finally:
+        eng.close()
+    for g, w in zip(got, wants):
+        for k in w:
+            assert np.array_equal(np.asarray(g[k]), np.asarray(w[k])), k
