@@ -95,7 +95,7 @@ def run_files(bam_paths, bigwig_path=None, max_shift=1000, mapq_criteria=1, read
             info["seconds"]["decode"] += t1 - t0
             info["seconds"]["feed"] += t2 - t1
             calcs.append(calc)
-            del bam
+            bam.close()                          # the packed arrays were copied out; free the decoder's memory now
         t0 = time.perf_counter()
         MultiFileCalculation(calcs, engine=engine).finishup_calculation()
         results = [c.get_whole_result() for c in calcs]
