@@ -66,6 +66,19 @@ def timed(dev, stream, jobs, steps, warmup, e2e_groups=4):
         for _ in range(min(warmup, 2)):
             e2e_step()
         torch.cuda.synchronize()
+        if os.environ.get("PMB_BREAKDOWN"):     # host wall time per phase of one e2e step (stderr)
+            acc = np.zeros(5)
+            for _ in range(steps):
+                tt = [time.perf_counter()]
+                b = dev.prepare(jobs); tt.append(time.perf_counter())
+                b.execute(); tt.append(time.perf_counter())
+                dev.synchronize(); tt.append(time.perf_counter())
+                b.fetch(); tt.append(time.perf_counter())
+                b.free(); tt.append(time.perf_counter())
+                acc += np.diff(tt)
+            print("[e2e breakdown] prepare %.2f execute_call %.2f wait %.2f fetch %.2f free %.2f ms; "
+                  "device execute %.2f ms" % (tuple(acc / steps * 1e3) + (dev.timing()["total_ms"],)),
+                  file=sys.stderr)
         t0 = time.perf_counter()
         for _ in range(steps):
             e2e_out = e2e_step()
