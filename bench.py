@@ -232,6 +232,20 @@ def cpu_baseline_leg(workload, mode, sample_bp, check_device=None):
                      (task[1], task[0], len(task[2]), len(task[3]),
                       "no" if task[4] is None else len(task[4]), MAX_SHIFT + 1,
                       "NCC+MSCC" if mode == "both" else "NCC")}
+    # the same sample through the reference rebuilt with -mpopcnt (its setup.py does
+    # not pass it, so the stock build popcounts in software, external/bitcnt.h:26-44), in a
+    # spawned interpreter because one process can import only one build of the package
+    if ref_runner.available(popcnt=True):
+        import multiprocessing as mp
+        os.environ["PYMASC_REF_POPCNT"] = "1"
+        try:
+            with mp.get_context("spawn").Pool(1) as pool:
+                ev2, dt2, head2 = pool.apply(_ref_task, (task + (mode,),))
+        finally:
+            os.environ.pop("PYMASC_REF_POPCNT", None)
+        out["reference_plus_popcnt"] = {"value": ev2 / dt2, "unit": UNIT, "cores": 1, "seconds": round(dt2, 2),
+                                        "flags": "-O3 -ffast-math -mpopcnt (oracle/_ref_popcnt)",
+                                        "same_counts": head2 == head}
     if check_device is not None:   # the same sample through the CUDA path must agree
         from pymasc_b200 import _shim
         flags = _shim.FLAG_NCC | (_shim.FLAG_MSCC if mode == "both" else 0)

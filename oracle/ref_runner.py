@@ -17,15 +17,21 @@ import numpy as np
 HERE = os.path.dirname(os.path.abspath(__file__))
 
 
-def ref_dir(popcnt=False):
-    return os.path.join(HERE, "_ref_popcnt" if popcnt else "_ref")
+def _popcnt(popcnt):
+    """None: the process-wide choice, PYMASC_REF_POPCNT=1 (one interpreter can import only one
+    build of the package, so bench.py picks the variant per spawned worker through the env)."""
+    return os.environ.get("PYMASC_REF_POPCNT") == "1" if popcnt is None else bool(popcnt)
 
 
-def available(popcnt=False):
+def ref_dir(popcnt=None):
+    return os.path.join(HERE, "_ref_popcnt" if _popcnt(popcnt) else "_ref")
+
+
+def available(popcnt=None):
     return bool(glob.glob(os.path.join(ref_dir(popcnt), "PyMaSC", "core", "bitarray", "mscc*.so")))
 
 
-def import_reference(popcnt=False):
+def import_reference(popcnt=None):
     """Put oracle/_ref (and the pyBigWig stand-in) on sys.path; return the calculator class."""
     if not available(popcnt):
         raise ImportError("compiled reference missing: run python oracle/build_ref.py")
