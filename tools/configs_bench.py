@@ -1,8 +1,13 @@
 #!/usr/bin/env python
-"""BASELINE.json configs[3] and configs[4] on one B200 (bench.py covers configs[1]/[2]).
+"""BASELINE.json configs[2], [3] and [4] (bench.py covers configs[1]/[2] over position shards).
 
-    python tools/configs_bench.py --config 4 [--reads 200000000] [--steps 5]
-    python tools/configs_bench.py --config 5 [--files 16] [--steps 5]
+    python tools/configs_bench.py --config 4 [--reads 200000000] [--steps 5]       # 1 GPU
+    python tools/configs_bench.py --config 5 [--files 16] [--steps 5]              # 1 GPU, shared vs per-file track
+    python tools/configs_bench.py --config 3 --devices 4     # one genome, whole chromosomes per GPU, 1/2/4 GPUs
+    python tools/configs_bench.py --config 5 --devices 4     # 16 read sets, shared-track runs per GPU
+    python tools/configs_bench.py --config 4 --devices 4     # deep library, position ranges per GPU
+    (--devices runs one process over 1, 2, 4 ... GPUs through pymasc_b200.multigpu.MultiDeviceEngine;
+     PMB_BREAKDOWN=1 prints the host-phase breakdown of the 1-GPU end-to-end step)
 
 config 4  deep library: 200 M reads, NCC+MSCC, max_shift 5000 (evals = 1.544e13).
 config 5  16 read sets (seeds 20260101 + 100 b + chrom_index) sharing the config-3 mappability
