@@ -255,7 +255,7 @@ ESTFUNCTIONS = dict(MEAN=_mean, MEDIAN=_median, MODE=_mode, MIN=min, MAX=max)
 
 def estimate_readlen(path, esttype="MEDIAN", mapq_criteria=1, threads=0):
     """core/readlen.pyx:89-177.  `path` may be a BamFile already decoded with the same MAPQ."""
-    bam = path if isinstance(path, BamFile) else BamFile(path, mapq_criteria, threads)
+    bam = path if hasattr(path, "readlen_counter") else BamFile(path, mapq_criteria, threads)
     if bam.mapq_criteria != int(mapq_criteria):
         raise ValueError("BamFile was decoded with another MAPQ criterion")
     if not bam.readlen_counter:

@@ -22,15 +22,18 @@ def query_length(cigar):
     return sum(int(n) for n, op in _CIGAR.findall(cigar) if op in _QUERY_OPS)
 
 
-def read_sam(path, mapq_criteria=1):
+def read_sam(path, mapq_criteria=1, with_readlen_counter=False):
     """Parse a SAM file.
 
     Returns (references, lengths, reads) where reads maps chrom -> dict of numpy arrays
     ``pos`` (1-based leftmost base, int64), ``readlen`` (int64), ``is_reverse`` (bool),
-    in file order (coordinate sorted input stays sorted).
+    in file order (coordinate sorted input stays sorted).  With ``with_readlen_counter`` a
+    fourth value: the query-length counter of estimate_readlen (core/readlen.pyx:150-156:
+    mapped, not duplicate, MAPQ >= criteria, with a reference; read2 included).
     """
     refs, lens = [], []
     acc = {}
+    counter = {}
     with open(path) as fh:
         for line in fh:
             if line.startswith("@"):
@@ -41,14 +44,22 @@ def read_sam(path, mapq_criteria=1):
                 continue
             f = line.split("\t")
             flag = int(f[1])
-            if flag & 0x80 or flag & 0x4 or flag & 0x400 or int(f[4]) < mapq_criteria:
+            if f[2] == "*":
+                continue
+            good = not (flag & 0x4 or flag & 0x400 or int(f[4]) < mapq_criteria)
+            qlen = query_length(f[5]) if good else 0
+            if good:
+                counter[qlen] = counter.get(qlen, 0) + 1
+            if flag & 0x80 or not good or qlen == 0:
                 continue
             rec = acc.setdefault(f[2], ([], [], []))
             rec[0].append(int(f[3]))
-            rec[1].append(query_length(f[5]))
+            rec[1].append(qlen)
             rec[2].append(bool(flag & 0x10))
     reads = {c: {"pos": np.asarray(p, np.int64), "readlen": np.asarray(l, np.int64),
                  "is_reverse": np.asarray(r, bool)} for c, (p, l, r) in acc.items()}
+    if with_readlen_counter:
+        return refs, lens, reads, counter
     return refs, lens, reads
 
 

@@ -13,7 +13,7 @@ It stops where the hot path stops: what comes back are the reference's result ob
 import logging
 import time
 
-from . import io_native
+from . import io_native, io_text
 from .calculator import CCBitArrayCalculator
 from .multifile import MultiFileCalculation
 
@@ -33,6 +33,38 @@ def reconcile_chromosome_sizes(references, lengths, external_sizes):
         else:
             out.append(bam_size)
     return out
+
+
+class SamFile(object):
+    """A text SAM file behind the interface ``run_files`` needs from ``io_native.BamFile``
+    (pysam reads both formats for the reference; the text twin is parsed in Python,
+    pymasc_b200/io_text.py, and is meant for small files and tests)."""
+
+    def __init__(self, path, mapq_criteria=1):
+        refs, lens, self.reads, self.readlen_counter = io_text.read_sam(path, mapq_criteria, with_readlen_counter=True)
+        self.references, self.lengths = tuple(refs), tuple(lens)
+        self.mapq_criteria = int(mapq_criteria)
+        self.stats = {"n_accepted": sum(len(r["pos"]) for r in self.reads.values())}
+        self.path = str(path)
+
+    def close(self):
+        pass
+
+
+def open_alignment(path, mapq_criteria=1, threads=0):
+    """BamFile for BGZF input, SamFile for text (decided by the gzip magic, as htslib does)."""
+    with open(path, "rb") as fh:
+        magic = fh.read(2)
+    if magic == b"\x1f\x8b":
+        return io_native.BamFile(path, mapq_criteria, threads)
+    return SamFile(path, mapq_criteria)
+
+
+def feed_alignment(calc, aln):
+    if isinstance(aln, io_native.BamFile):
+        return io_native.feed_bam(calc, aln)
+    for chrom, r in aln.reads.items():          # file order; feed_batch raises ReadUnsortedError itself
+        calc.feed_batch(chrom, r["pos"], r["readlen"], r["is_reverse"])
 
 
 class CachedTrack(object):
@@ -76,7 +108,7 @@ def run_files(bam_paths, bigwig_path=None, max_shift=1000, mapq_criteria=1, read
     try:
         for path in bam_paths:
             t0 = time.perf_counter()
-            bam = io_native.BamFile(path, mapq_criteria, threads)
+            bam = open_alignment(path, mapq_criteria, threads)
             t1 = time.perf_counter()
             rl = read_len
             if rl is None:                       # handler/calc.py:85-98
@@ -89,7 +121,7 @@ def run_files(bam_paths, bigwig_path=None, max_shift=1000, mapq_criteria=1, read
                 lengths = reconcile_chromosome_sizes(bam.references, lengths, feeder.chromsizes)
             calc = CCBitArrayCalculator(max_shift, rl, list(bam.references), lengths, feeder,
                                         skip_ncc, engine=engine)
-            io_native.feed_bam(calc, bam)
+            feed_alignment(calc, bam)
             t2 = time.perf_counter()
             info["files"].append({"path": str(path), "read_len": int(rl), "stats": bam.stats})
             info["seconds"]["decode"] += t1 - t0

@@ -363,3 +363,28 @@ def test_mappability_handler_reproduces_the_reference_json(tmp_path):
     assert h3.get_mappable_len("chr1", force=True)[:266] == tuple(want["references"]["chr1"])
     with pytest.raises(BWIOError):
         MappabilityHandler(str(tmp_path / "missing.bw"), 300, 36)
+
+
+def test_run_files_takes_text_sam_too(tmp_path):
+    """pysam reads SAM and BAM alike for the reference; run_files sniffs the gzip magic and
+    parses text SAM through io_text.  The same reads as SAM and as BAM give the same result."""
+    from pymasc_b200 import pipeline
+    fx = helpers.load_fixture()
+    n = 400
+    refs = [("chr1", 249250621), ("chrM", 16571)]
+    sam = ["@HD\tVN:1.6\tSO:coordinate"] + ["@SQ\tSN:%s\tLN:%d" % r for r in refs]
+    recs = []
+    for i, (p, l, r) in enumerate(zip(fx["pos"][:n], fx["readlen"][:n], fx["is_reverse"][:n])):
+        flag = (16 if r else 0) | (0x400 if i % 50 == 7 else 0)
+        mapq = 5 if i % 40 == 3 else 30
+        sam.append("r%d\t%d\tchr1\t%d\t%d\t%dM\t*\t0\t0\t%s\t%s" % (i, flag, p, mapq, l, "A" * l, "I" * l))
+        recs.append(W.bam_record(0, int(p) - 1, mapq, flag, [(int(l), "M")]))
+    sam.append("u\t4\t*\t0\t0\t*\t*\t0\t0\tACGT\tIIII")
+    sam_path, bam_path = str(tmp_path / "x.sam"), str(tmp_path / "x.bam")
+    open(sam_path, "w").write("\n".join(sam) + "\n")
+    W.write_bam(bam_path, refs, recs)
+    a, ia = pipeline.run_files(sam_path, BIGWIG, max_shift=200, mapq_criteria=10, engine=OracleEngine())
+    b, ib = pipeline.run_files(bam_path, BIGWIG, max_shift=200, mapq_criteria=10, engine=OracleEngine())
+    assert ia["files"][0]["read_len"] == ib["files"][0]["read_len"] == 36
+    assert ia["files"][0]["stats"]["n_accepted"] == ib["files"][0]["stats"]["n_accepted"] < n
+    helpers.assert_snapshots_equal(helpers.snapshot_whole(a[0]), helpers.snapshot_whole(b[0]))
