@@ -778,26 +778,26 @@ static int prepare_impl(pmb_ctx* c, const pmb_chrom_args* a, uint32_t n, pmb_bat
         // table uploads are small H2D copies on the compute stream, and behind 90 MB .. 1.2 GB of
         // inputs on the same copy engine they held the first kernel back by the whole input copy
         // (measured: 16 read sets, execute started 22 ms late; one genome, ~1 ms).
-    CU_TRY(c, cudaMallocAsync((void**)&b->d_bits_raw,
-                              (std::max<size_t>(bits_words, 4) + 2 * (size_t)EV_PAD_WORDS) * 4, c->stream));
-    b->d_bits = b->d_bits_raw + EV_PAD_WORDS;
-    // the pads are only ever read by TMA region overhang (never used); zero them once
-    CU_TRY(c, cudaMemsetAsync(b->d_bits_raw, 0, (size_t)EV_PAD_WORDS * 4, c->stream));
-    CU_TRY(c, cudaMemsetAsync(b->d_bits + std::max<size_t>(bits_words, 4), 0, (size_t)EV_PAD_WORDS * 4, c->stream));
-    CU_TRY(c, cudaMallocAsync((void**)&b->d_counters, b->counter_words * 8, c->stream));
-    CU_TRY(c, cudaMallocAsync((void**)&b->d_err, 4 * (4 + 128), c->stream));
-    uint64_t max_iv = 0;
-    for (auto& j : b->jobs) max_iv = std::max<uint64_t>(max_iv, j.a.n_intervals);
-    b->long_cap = (size_t)max_iv + 4;
-    CU_TRY(c, cudaMallocAsync((void**)&b->d_long, b->long_cap * 4, c->stream));
-    // window job tables: one per unit chunk (filled in execute)
-    b->d_jobs_count = (size_t)n * ((b->n_units + 63) / 64 + 1) * 3;
-    CU_TRY(c, cudaMallocAsync((void**)&b->d_jobs, b->d_jobs_count * sizeof(WindowJob), c->stream));
+        CU_TRY(c, cudaMallocAsync((void**)&b->d_bits_raw,
+                                  (std::max<size_t>(bits_words, 4) + 2 * (size_t)EV_PAD_WORDS) * 4, c->stream));
+        b->d_bits = b->d_bits_raw + EV_PAD_WORDS;
+        // the pads are only ever read by TMA region overhang (never used); zero them once
+        CU_TRY(c, cudaMemsetAsync(b->d_bits_raw, 0, (size_t)EV_PAD_WORDS * 4, c->stream));
+        CU_TRY(c, cudaMemsetAsync(b->d_bits + std::max<size_t>(bits_words, 4), 0, (size_t)EV_PAD_WORDS * 4, c->stream));
+        CU_TRY(c, cudaMallocAsync((void**)&b->d_counters, b->counter_words * 8, c->stream));
+        CU_TRY(c, cudaMallocAsync((void**)&b->d_err, 4 * (4 + 128), c->stream));
+        uint64_t max_iv = 0;
+        for (auto& j : b->jobs) max_iv = std::max<uint64_t>(max_iv, j.a.n_intervals);
+        b->long_cap = (size_t)max_iv + 4;
+        CU_TRY(c, cudaMallocAsync((void**)&b->d_long, b->long_cap * 4, c->stream));
+        // window job tables: one per unit chunk (filled in execute)
+        b->d_jobs_count = (size_t)n * ((b->n_units + 63) / 64 + 1) * 3;
+        CU_TRY(c, cudaMallocAsync((void**)&b->d_jobs, b->d_jobs_count * sizeof(WindowJob), c->stream));
 
-    {
-        int rc = b->path == 2 ? plan_events(c, b) : plan_windows(c, b);
-        if (rc != PMB_OK) return rc;
-    }
+        {
+            int rc = b->path == 2 ? plan_events(c, b) : plan_windows(c, b);
+            if (rc != PMB_OK) return rc;
+        }
         if (async) {
             for (auto& gr : b->groups)
                 CU_TRY(c, cudaEventCreateWithFlags(&gr.done, cudaEventDisableTiming));
