@@ -222,35 +222,39 @@ class BamFile(object):
             pass
 
 
-def _mean(c):
-    return int(round(sum(length * freq for length, freq in c.items()) / float(sum(c.values()))))
+def _counter_arrays(counter):
+    lengths = np.array(sorted(counter), dtype=np.int64)
+    return lengths, np.array([counter[int(l)] for l in lengths], dtype=np.int64)
 
 
-def _median(c):
-    # core/readlen.pyx:41-69
-    num = sum(c.values())
-    target = num / 2
-    acc = 0
-    lengths = sorted(c)
-    if num % 2:
-        for l in lengths:
-            acc += c[l]
-            if target <= acc:
-                return l
-    else:
-        for i, l in enumerate(lengths):
-            acc += c[l]
-            if target < acc:
-                return l
-            elif target == acc:
-                return int(round((l + float(lengths[i + 1])) / 2))
+def _estimate(counter, esttype):
+    """The five estimators of core/readlen.pyx:22-86 over a {query length: reads} counter.
+    MEAN rounds the weighted mean (Python ``round``); MEDIAN is the lower-half boundary of the
+    cumulative counts, the rounded midpoint of two lengths when an even total splits exactly
+    between them; MODE is the most frequent length (the reference breaks a tie by the order in
+    which lengths first occur in the file, this one by taking the longer)."""
+    lengths, counts = _counter_arrays(counter)
+    if esttype == "MIN":
+        return int(lengths[0])
+    if esttype == "MAX":
+        return int(lengths[-1])
+    if esttype == "MODE":
+        return int(lengths[len(counts) - 1 - int(np.argmax(counts[::-1]))])
+    total = int(counts.sum())
+    if esttype == "MEAN":
+        return int(round(int((lengths * counts).sum()) / float(total)))
+    if esttype != "MEDIAN":
+        raise KeyError(esttype)
+    cum = np.cumsum(counts)
+    half = total / 2
+    at = int(np.searchsorted(cum, half, side="left"))          # first length whose cumulative count >= half
+    if total % 2 == 0 and cum[at] == half:
+        return int(round((int(lengths[at]) + float(lengths[at + 1])) / 2))
+    return int(lengths[at])
 
 
-def _mode(c):
-    return [k for k, v in sorted(c.items(), key=lambda x: x[1])][-1]
-
-
-ESTFUNCTIONS = dict(MEAN=_mean, MEDIAN=_median, MODE=_mode, MIN=min, MAX=max)
+ESTFUNCTIONS = {name: (lambda counter, _n=name: _estimate(counter, _n))
+                for name in ("MEAN", "MEDIAN", "MODE", "MIN", "MAX")}
 
 
 def estimate_readlen(path, esttype="MEDIAN", mapq_criteria=1, threads=0):

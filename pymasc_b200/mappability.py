@@ -34,10 +34,6 @@ class JSONIOError(IOError):
     pass
 
 
-class NeedUpdate(Exception):
-    pass
-
-
 class MappabilityHandler(object):
     MAPPABILITY_THRESHOLD = 1.
 
@@ -67,101 +63,80 @@ class MappabilityHandler(object):
         self.need_save_stats = True
         self._engine = engine
 
-        if map_path:
-            self.map_path = map_path
-        else:       # /path/to/file.bw -> /path/to/file_mappability.json
-            p = Path(path)
-            self.map_path = p.parent / (p.with_suffix("").name + "_mappability.json")
-
-        if not Path(self.map_path).exists():
-            self._check_saving_directory_is_writable()
-            logger.info("Calcurate mappable length with max shift size {}.".format(max_shift))
-        elif not Path(self.map_path).is_file():
-            logger.critical("Specified path is not file: '{}'".format(self.map_path))
-            raise JSONIOError
-        elif not os.access(self.map_path, os.R_OK):
-            logger.error("Failed to read '{}'".format(self.map_path))
-        else:
-            self._try_load_mappability_stats()
-            if self.need_save_stats:
-                self._check_stats_is_overwritable()
-                logger.info("Calcurate mappable length with max shift size {}.".format(max_shift))
-            else:
-                logger.info("Use mappability stats read from '{}'".format(self.map_path))
+        # /path/to/track.bw -> /path/to/track_mappability.json unless told otherwise
+        self.map_path = map_path or Path(path).with_name(Path(path).with_suffix("").name + "_mappability.json")
+        self._adopt_cache_or_prepare_to_write()
 
     # ------------------------------------------------------------------ the JSON cache
-    def _check_saving_directory_is_writable(self):
-        dirname = str(Path(self.map_path).parent) or '.'
-        try:
-            os.makedirs(dirname, exist_ok=True)
-        except OSError:
+    # Behaviour of handler/mappability.py:197-309: a readable, well-formed cache that covers at
+    # least this max_shift and every chromosome of the BigWig is used (truncated to this
+    # max_shift) and nothing is calculated or written; a cache for a shorter max_shift, a
+    # malformed or an unreadable one is recalculated and overwritten; a cache path that is not a
+    # file, or a target that cannot be written, is JSONIOError.
+    def _adopt_cache_or_prepare_to_write(self):
+        target = Path(self.map_path)
+        if target.exists() and not target.is_file():
+            logger.critical("Specified path is not file: '{}'".format(self.map_path))
             raise JSONIOError
-        if not os.access(dirname, os.W_OK):
-            logger.critical("Directory '{}' is not writable.".format(dirname))
-            raise JSONIOError
-
-    def _try_load_mappability_stats(self):
-        try:
-            stats = self._read_mappability_stats()
-        except IOError as e:
-            logger.error("Failed to read '{}'".format(self.map_path))
-            logger.error("[Errno {}] {}".format(e.errno, str(e)))
-        except (TypeError, OverflowError, ValueError, KeyError, IndexError):
-            logger.error("Failed to load json file: '{}'".format(self.map_path))
-        except NeedUpdate:
-            pass
+        cached = self._usable_cache() if target.exists() else None
+        if cached is not None:
+            top = self.max_shift + 1
+            self.mappable_len = cached["__whole__"][:top]
+            self.chrom2mappable_len = {c: v[:top] for c, v in cached["references"].items()}
+            self.chrom2is_called = dict.fromkeys(self.chromsizes, True)
+            self.is_called, self.need_save_stats = True, False
+            logger.info("Use mappability stats read from '{}'".format(self.map_path))
+            return
+        if target.exists():
+            if not os.access(self.map_path, os.W_OK):
+                logger.critical("Failed to overwrite '{}'".format(self.map_path))
+                raise JSONIOError
+            logger.warning("Existing file '{}' will be overwritten.".format(self.map_path))
         else:
-            self._load_mappability_stats(stats)
+            folder = str(target.parent) or "."
+            try:
+                os.makedirs(folder, exist_ok=True)
+            except OSError:
+                raise JSONIOError
+            if not os.access(folder, os.W_OK):
+                logger.critical("Directory '{}' is not writable.".format(folder))
+                raise JSONIOError
+        logger.info("Calcurate mappable length with max shift size {}.".format(self.max_shift))
 
-    def _read_mappability_stats(self):
-        with open(self.map_path) as f:
-            stats = json.load(f)
-        for k in ("max_shift", "__whole__", "references"):
-            if k not in stats:
-                logger.error("Mandatory key '{}' not found.".format(k))
-                raise KeyError(k)
-        if stats["max_shift"] < self.max_shift:
+    def _usable_cache(self):
+        """The parsed cache file if it can stand in for a calculation, else None."""
+        try:
+            with open(self.map_path) as fh:
+                stats = json.load(fh)
+            cached_shift = stats["max_shift"]
+            lists = [stats["__whole__"]] + [stats["references"][c] for c in self.chromsizes]
+        except OSError as e:
+            logger.error("Failed to read '{}': [Errno {}] {}".format(self.map_path, e.errno, e))
+            return None
+        except (TypeError, ValueError, KeyError, IndexError, OverflowError) as e:
+            logger.error("Failed to load json file '{}': {!r}".format(self.map_path, e))
+            return None
+        if cached_shift < self.max_shift:
             logger.info("Specified shift length longer than former analysis. The stats will be updated.")
-            raise NeedUpdate
-        if stats["max_shift"] != len(stats["__whole__"]) - 1:
-            logger.error("Max shift length for whole genome unmatched.")
-            raise IndexError
-        for ref in self.chromsizes:
-            if ref not in stats["references"]:
-                logger.error("Reference '{}' not found.".format(ref))
-                raise KeyError(ref)
-            if stats["max_shift"] != len(stats["references"][ref]) - 1:
-                logger.error("Max shift length for '{}' unmatched.".format(ref))
-                raise IndexError
+            return None
+        if any(len(v) != cached_shift + 1 for v in lists):
+            logger.error("Max shift length unmatched in '{}'.".format(self.map_path))
+            return None
         return stats
 
-    def _load_mappability_stats(self, stats):
-        self.mappable_len = stats["__whole__"][:self.max_shift + 1]
-        self.chrom2mappable_len = {ref: b[:self.max_shift + 1] for ref, b in stats["references"].items()}
-        self.chrom2is_called = {ref: True for ref in self.chromsizes}
-        self.is_called = True
-        self.need_save_stats = False
-
-    def _check_stats_is_overwritable(self):
-        if not os.access(self.map_path, os.W_OK):
-            logger.critical("Failed to overwrite '{}'".format(self.map_path))
-            raise JSONIOError
-        logger.warning("Existing file '{}' will be overwritten.".format(self.map_path))
-
     def save_mappability_stats(self):
-        # handler/mappability.py:283-309: same keys, indent and key order
+        """Write the cache (keys max_shift / __whole__ / references, 4-space indent, sorted keys:
+        the layout of handler/mappability.py:296-301) unless it was read from disk."""
         if not self.need_save_stats:
             return logger.info("Mappability stats updating is not required.")
         logger.info("Save mappable length to '{}'".format(self.map_path))
+        doc = {"max_shift": int(self.max_shift), "__whole__": [int(x) for x in self.mappable_len],
+               "references": {c: [int(x) for x in v] for c, v in self.chrom2mappable_len.items()}}
         try:
-            with open(self.map_path, 'w') as f:
-                json.dump({
-                    "max_shift": int(self.max_shift),
-                    "__whole__": [int(x) for x in self.mappable_len],
-                    "references": {c: [int(x) for x in v] for c, v in self.chrom2mappable_len.items()},
-                }, f, indent=4, sort_keys=True)
-        except IOError as e:
-            logger.error("Faild to output: {}\n[Errno {}] {}".format(e.filename, e.errno, str(e)))
+            with open(self.map_path, "w") as fh:
+                json.dump(doc, fh, indent=4, sort_keys=True)
+        except OSError as e:
+            logger.error("Faild to output: {}\n[Errno {}] {}".format(e.filename, e.errno, e))
         self.need_save_stats = False
 
     # ------------------------------------------------------------------ the calculation

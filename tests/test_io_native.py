@@ -388,3 +388,32 @@ def test_run_files_takes_text_sam_too(tmp_path):
     assert ia["files"][0]["read_len"] == ib["files"][0]["read_len"] == 36
     assert ia["files"][0]["stats"]["n_accepted"] == ib["files"][0]["stats"]["n_accepted"] < n
     helpers.assert_snapshots_equal(helpers.snapshot_whole(a[0]), helpers.snapshot_whole(b[0]))
+
+
+def test_read_length_estimators_follow_the_reference_rules():
+    """core/readlen.pyx:22-86 restated naively (loops over the sorted counter) against the
+    vectorised estimators, on random counters including exact even splits."""
+    import random
+
+    def median(c):                      # readlen.pyx:41-69
+        num, acc = sum(c.values()), 0
+        keys = sorted(c)
+        for i, l in enumerate(keys):
+            acc += c[l]
+            if num % 2:
+                if num / 2 <= acc:
+                    return l
+            elif num / 2 < acc:
+                return l
+            elif num / 2 == acc:
+                return int(round((l + float(keys[i + 1])) / 2))
+
+    rnd = random.Random(7)
+    for _ in range(3000):
+        c = {rnd.randint(20, 60): rnd.randint(1, 6) for _ in range(rnd.randint(1, 6))}
+        assert io_native.ESTFUNCTIONS["MEDIAN"](c) == median(c), c
+        assert io_native.ESTFUNCTIONS["MEAN"](c) == int(round(sum(l * f for l, f in c.items()) / float(sum(c.values()))))
+        assert (io_native.ESTFUNCTIONS["MIN"](c), io_native.ESTFUNCTIONS["MAX"](c)) == (min(c), max(c))
+        assert c[io_native.ESTFUNCTIONS["MODE"](c)] == max(c.values())
+    assert io_native.ESTFUNCTIONS["MEDIAN"]({35: 2, 36: 2}) == 36        # 35.5 rounds half to even
+    assert io_native.ESTFUNCTIONS["MEDIAN"]({36: 2, 37: 2}) == 36        # 36.5 rounds half to even
