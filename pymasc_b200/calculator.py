@@ -18,6 +18,7 @@ There is no CPU fallback: without the CUDA library and an sm_100 device the firs
 ``DeviceError``.
 """
 import logging
+import os
 from array import array
 
 import numpy as np
@@ -319,7 +320,13 @@ class CCBitArrayCalculator(object):
             self.ref2mscc_result[chrom] = r
 
     def _track_key(self, chrom):
-        return (id(self._bwfeeder), chrom)
+        """Names the mappability track of a job for pymasc_b200.multifile: readers of the same
+        BigWig file (the reference opens one per input file, reader/bigwig.pyx:129-137) share a
+        key through their ``path``; anything else is keyed by object identity."""
+        path = getattr(self._bwfeeder, "path", None)
+        if isinstance(path, (str, os.PathLike)):
+            return ("file", os.path.abspath(os.fspath(path)), float(self.MAPPABILITY_THRESHOLD), chrom)
+        return ("object", id(self._bwfeeder), chrom)
 
     def _collect_jobs(self, fill=()):
         """Device jobs of every queued chromosome plus the mappable-length autocorrelation of

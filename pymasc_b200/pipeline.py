@@ -73,6 +73,7 @@ class CachedTrack(object):
 
     def __init__(self, reader):
         self._reader = reader
+        self.path = reader.path
         self.chromsizes = reader.chromsizes
         self._cache = {}
 

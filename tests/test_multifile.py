@@ -204,3 +204,26 @@ def test_multi_device_engine_position_split_equals_one_device():
                 assert np.array_equal(np.asarray(g[k]), np.asarray(w[k])), k
     with pytest.raises(ValueError):
         MultiDeviceEngine([OracleEngine()], split="files")
+
+
+def test_readers_of_the_same_bigwig_file_share_a_track():
+    """The reference opens one BigWigReader per input file; two reader objects of one file must
+    still form a shared-track run (keyed by path), readers of different files must not."""
+    import os
+    from pymasc_b200 import io_native
+    bw = os.path.join(helpers.GOLDEN, "hg19_36mer-test.bigwig")
+    fx = helpers.load_fixture()
+    engine = OracleEngine()
+    seen = []
+    engine_run = engine.run
+    engine.run = lambda jobs: (seen.append([j.flags for j in jobs]), engine_run(jobs))[1]
+    calcs = []
+    for f in range(2):
+        c = CCBitArrayCalculator(100, 36, ["chr1"], [fx["lengths"][0]], io_native.BigWigReader(bw), engine=engine)
+        c.feed_batch("chr1", fx["pos"] + 3 * f, fx["readlen"], fx["is_reverse"])
+        calcs.append(c)
+    MultiFileCalculation(calcs).finishup_calculation()
+    assert seen == [[3, 3 | _shim.FLAG_SAME_TRACK]]
+    assert calcs[0]._track_key("chr1") == calcs[1]._track_key("chr1")
+    other = CCBitArrayCalculator(100, 36, ["chr1"], [1000], helpers.ListFeeder({}), engine=engine)
+    assert other._track_key("chr1") != calcs[0]._track_key("chr1")
