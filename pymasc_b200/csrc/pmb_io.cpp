@@ -151,7 +151,7 @@ struct BamHeaderParser {
             if (n < 12 + (size_t)l_text) return 0;
             refs_left = rd32(p + 8 + l_text);
             o = 12 + (size_t)l_text;
-            b->names.reserve(refs_left);
+            b->names.reserve(std::min<uint32_t>(refs_left, 1u << 20));
             stage = 1;
         }
         while (stage == 1) {
@@ -339,18 +339,40 @@ void pack_reference(const std::vector<pmio_bam::Seg>& segs, uint64_t n, pmio_bam
 
 }  // namespace
 
+static int bam_load_impl(const char* path, int mapq_criteria, int threads, pmio_bam** out);
+
+// Nothing may propagate out of the C ABI: allocation failures and anything unexpected become codes.
+template <class F>
+static int guarded(F&& body)
+{
+    try {
+        return body();
+    } catch (const std::bad_alloc&) {
+        return fail(PMIO_ERR_NOMEM, "out of memory");
+    } catch (const std::exception& e) {
+        return fail(PMIO_ERR_FORMAT, std::string("unexpected error: ") + e.what());
+    } catch (...) {
+        return fail(PMIO_ERR_FORMAT, "unexpected error");
+    }
+}
+
 extern "C" int pmio_bam_load(const char* path, int mapq_criteria, int threads, pmio_bam** out)
 {
     if (!path || !out) return fail(PMIO_ERR_ARG, "null argument");
     *out = nullptr;
+    return guarded([&]() { return bam_load_impl(path, mapq_criteria, threads, out); });
+}
+
+static int bam_load_impl(const char* path, int mapq_criteria, int threads, pmio_bam** out)
+{
     Mapping m;
     int rc = m.open(path);
     if (rc != PMIO_OK) return rc;
     if (threads <= 0) threads = (int)std::max(1u, std::thread::hardware_concurrency());
     threads = std::min(threads, 64);
 
-    pmio_bam* b = new (std::nothrow) pmio_bam();
-    if (!b) return fail(PMIO_ERR_NOMEM, "out of memory");
+    std::unique_ptr<pmio_bam> owner(new pmio_bam());      // freed on every early return and on exceptions
+    pmio_bam* b = owner.get();
     BamHeaderParser header{b};
     BamMerger merger{b};
     std::vector<ShareStats> share_stats((size_t)threads);
@@ -393,6 +415,7 @@ extern "C" int pmio_bam_load(const char* path, int mapq_criteria, int threads, p
             k.csize = bsize - 12 - xlen - 8;
             k.crc = rd32(m.p + off + bsize - 8);
             k.isize = rd32(m.p + off + bsize - 4);
+            if (k.isize > 65536) { g_err = "corrupt BGZF block (ISIZE > 64 KiB)"; bad = true; break; }
             k.out_off = out_off;
             out_off += k.isize;
             if (k.isize) blocks.push_back(k);
@@ -447,17 +470,23 @@ extern "C" int pmio_bam_load(const char* path, int mapq_criteria, int threads, p
             const size_t store0 = b->store.size();
             for (size_t i = 0; i < n_shares; i++) b->store.emplace_back(new pmio_chunk());
             std::atomic<size_t> next_share{0};
+            std::atomic<bool> oom{false};
             auto parse_work = [&]() {
                 for (size_t i; (i = next_share.fetch_add(1)) < n_shares;) {
                     share_stats[i].reset();
-                    stops[i] = parse_share(p, cuts[i], cuts[i + 1], out_off, n_refs, mapq_criteria,
-                                           *b->store[store0 + i], share_stats[i]);
+                    try {       // an exception must not leave a worker thread
+                        stops[i] = parse_share(p, cuts[i], cuts[i + 1], out_off, n_refs, mapq_criteria,
+                                               *b->store[store0 + i], share_stats[i]);
+                    } catch (...) {
+                        oom.store(true);
+                    }
                 }
             };
             std::vector<std::thread> ppool;
             for (size_t t = 1; t < std::min<size_t>((size_t)threads, n_shares); t++) ppool.emplace_back(parse_work);
             parse_work();
             for (auto& t : ppool) t.join();
+            if (oom.load()) throw std::bad_alloc();
             { const double t = now(); t_parse += t - t_mark; t_mark = t; }
             size_t at = used;                       // a true record boundary
             for (size_t i = 0; i < n_shares; i++) {
@@ -486,7 +515,7 @@ extern "C" int pmio_bam_load(const char* path, int mapq_criteria, int threads, p
     }
     if (!bad && header.stage != 2) { g_err = "truncated BAM header"; bad = true; }
     if (!bad && carry) { g_err = "truncated BAM file (incomplete record at the end)"; bad = true; }
-    if (bad) { delete b; return PMIO_ERR_FORMAT; }
+    if (bad) return PMIO_ERR_FORMAT;
     b->st.sorted = merger.sorted ? 1 : 0;
     for (size_t l = 0; l < merger.hist_small.size(); l++)
         if (merger.hist_small[l]) merger.hist[(uint32_t)l] += merger.hist_small[l];
@@ -499,21 +528,28 @@ extern "C" int pmio_bam_load(const char* path, int mapq_criteria, int threads, p
             if (b->counts[i]) order.push_back(i);
         std::sort(order.begin(), order.end(), [&](size_t x, size_t y) { return b->counts[x] > b->counts[y]; });
         std::atomic<size_t> next{0};
+        std::atomic<bool> oom{false};
         auto work = [&]() {
-            for (size_t k; (k = next.fetch_add(1)) < order.size();)
-                pack_reference(b->segs[order[k]], b->counts[order[k]], b->packed[order[k]]);
+            for (size_t k; (k = next.fetch_add(1)) < order.size();) {
+                try {
+                    pack_reference(b->segs[order[k]], b->counts[order[k]], b->packed[order[k]]);
+                } catch (...) {
+                    oom.store(true);
+                }
+            }
         };
         std::vector<std::thread> pool;
         for (size_t t = 1; t < std::min<size_t>((size_t)threads, order.size()); t++) pool.emplace_back(work);
         work();
         for (auto& t : pool) t.join();
+        if (oom.load()) throw std::bad_alloc();
     }
     t_pack = now() - t_mark;
     if (timing)
         fprintf(stderr, "[pmio bam] %d threads, %zu-block batches: inflate %.3f s, filter %.3f s, validate + carry %.3f s "
                         "(%u shares filtered again), pack %.3f s\n", threads, BATCH_BLOCKS, t_inflate, t_parse, t_scan,
                 b->st.reparsed_shares, t_pack);
-    *out = b;
+    *out = owner.release();
     return PMIO_OK;
 }
 
@@ -543,6 +579,7 @@ extern "C" int pmio_bam_reads(pmio_bam* b, uint32_t i, const uint32_t** pos, con
 {
     if (!b || i >= b->names.size()) return fail(PMIO_ERR_ARG, "reference index out of range");
     if ((pos || qlen || is_reverse) && !b->materialised[i]) {      // concatenate the segments once
+      const int rc = guarded([&]() {
         b->pos[i].reserve(b->counts[i]); b->qlen[i].reserve(b->counts[i]); b->rev[i].reserve(b->counts[i]);
         for (const pmio_bam::Seg& s : b->segs[i]) {
             b->pos[i].insert(b->pos[i].end(), s.c->pos.begin() + s.begin, s.c->pos.begin() + s.end);
@@ -550,6 +587,9 @@ extern "C" int pmio_bam_reads(pmio_bam* b, uint32_t i, const uint32_t** pos, con
             b->rev[i].insert(b->rev[i].end(), s.c->rev.begin() + s.begin, s.c->rev.begin() + s.end);
         }
         b->materialised[i] = 1;
+        return (int)PMIO_OK;
+      });
+      if (rc != PMIO_OK) return rc;
     }
     if (pos) *pos = b->pos[i].data();
     if (qlen) *qlen = b->qlen[i].data();
@@ -647,17 +687,22 @@ bool walk_rtree(const pmio_bw* w, uint64_t node, uint32_t id, std::vector<Leaf>&
 
 }  // namespace
 
+static int bw_open_impl(const char* path, pmio_bw** out);
 extern "C" int pmio_bw_open(const char* path, pmio_bw** out)
 {
     if (!path || !out) return fail(PMIO_ERR_ARG, "null argument");
     *out = nullptr;
-    pmio_bw* w = new (std::nothrow) pmio_bw();
-    if (!w) return fail(PMIO_ERR_NOMEM, "out of memory");
+    return guarded([&]() { return bw_open_impl(path, out); });
+}
+
+static int bw_open_impl(const char* path, pmio_bw** out)
+{
+    std::unique_ptr<pmio_bw> owner(new pmio_bw());
+    pmio_bw* w = owner.get();
     int rc = w->m.open(path);
-    if (rc != PMIO_OK) { delete w; return rc; }
+    if (rc != PMIO_OK) return rc;
     const uint8_t* p = w->m.p;
     if (w->m.n < 64 || rd32(p) != 0x888FFC26u) {
-        delete w;
         return fail(PMIO_ERR_FORMAT, std::string(path) + " is not a little-endian BigWig file (bad magic)");
     }
     const uint64_t chrom_tree = rd64(p + 8);
@@ -665,15 +710,13 @@ extern "C" int pmio_bw_open(const char* path, pmio_bw** out)
     w->uncompress_buf = rd32(p + 52);
     if (!in_file(w, chrom_tree, 32) || rd32(p + chrom_tree) != 0x78CA8C91u ||
         !in_file(w, w->index_off, 48) || rd32(p + w->index_off) != 0x2468ACE0u) {
-        delete w;
         return fail(PMIO_ERR_FORMAT, "corrupt BigWig file (chromosome tree or index)");
     }
     const uint32_t key_size = rd32(p + chrom_tree + 8), val_size = rd32(p + chrom_tree + 12);
     if (val_size != 8 || key_size == 0 || key_size > 4096 || !walk_chrom_tree(w, chrom_tree + 32, key_size, 0)) {
-        delete w;
         return fail(PMIO_ERR_FORMAT, "corrupt BigWig chromosome tree");
     }
-    *out = w;
+    *out = owner.release();
     return PMIO_OK;
 }
 
@@ -688,10 +731,18 @@ extern "C" uint64_t pmio_bw_chrom_len(const pmio_bw* w, uint32_t i)
     return w && i < w->lens.size() ? w->lens[i] : 0;
 }
 
+static int bw_intervals_impl(pmio_bw* w, const char* chrom, float threshold, const uint32_t** begins,
+                             const uint32_t** ends, const float** values, uint64_t* n);
 extern "C" int pmio_bw_intervals(pmio_bw* w, const char* chrom, float threshold, const uint32_t** begins,
                                  const uint32_t** ends, const float** values, uint64_t* n)
 {
     if (!w || !chrom) return fail(PMIO_ERR_ARG, "null argument");
+    return guarded([&]() { return bw_intervals_impl(w, chrom, threshold, begins, ends, values, n); });
+}
+
+static int bw_intervals_impl(pmio_bw* w, const char* chrom, float threshold, const uint32_t** begins,
+                             const uint32_t** ends, const float** values, uint64_t* n)
+{
     size_t ci = 0;
     for (; ci < w->names.size(); ci++)
         if (w->names[ci] == chrom) break;

@@ -417,3 +417,19 @@ def test_read_length_estimators_follow_the_reference_rules():
         assert c[io_native.ESTFUNCTIONS["MODE"](c)] == max(c.values())
     assert io_native.ESTFUNCTIONS["MEDIAN"]({35: 2, 36: 2}) == 36        # 35.5 rounds half to even
     assert io_native.ESTFUNCTIONS["MEDIAN"]({36: 2, 37: 2}) == 36        # 36.5 rounds half to even
+
+
+def test_hostile_bgzf_sizes_are_format_errors(tmp_path):
+    """A block that claims more than 64 KiB of inflated data (BGZF allows at most 65536) must not
+    size a buffer from that claim; a header that announces 2^31 references must not reserve them."""
+    raw = bytearray(W.bgzf_block(b"BAM\x01" + struct.pack("<ii", 0, 1) + struct.pack("<i", 3) + b"c1\0" + struct.pack("<i", 100)))
+    p = str(tmp_path / "isize.bam")
+    blob = bytearray(raw)
+    blob[-4:] = struct.pack("<I", 0xFFFFFFF0)
+    open(p, "wb").write(bytes(blob) + W.BGZF_EOF)
+    with pytest.raises(ValueError):
+        io_native.BamFile(p)
+    p2 = str(tmp_path / "nref.bam")
+    open(p2, "wb").write(W.bgzf_block(b"BAM\x01" + struct.pack("<ii", 0, 0x7FFFFFFF)) + W.BGZF_EOF)
+    with pytest.raises(ValueError):
+        io_native.BamFile(p2)               # truncated header, not an allocation of 2^31 names
