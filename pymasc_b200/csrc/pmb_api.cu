@@ -63,6 +63,22 @@ struct pmb_ctx {
         }                                                                                   \
     } while (0)
 
+// Nothing may propagate out of the C ABI: host allocation failures (std::vector, new) become
+// PMB_ERR_NOMEM, anything else unexpected PMB_ERR_ARG with the text in pmb_last_error.
+template <class F>
+static int guarded(pmb_ctx* c, F&& body)
+{
+    try {
+        return body();
+    } catch (const std::bad_alloc&) {
+        if (c) c->err = "host memory allocation failed";
+        return PMB_ERR_NOMEM;
+    } catch (const std::exception& e) {
+        if (c) c->err = std::string("unexpected error: ") + e.what();
+        return PMB_ERR_ARG;
+    }
+}
+
 struct JobPlan {
     pmb_chrom_args a;          // host pointers are only valid during prepare
     uint64_t nbits = 0;
@@ -855,7 +871,7 @@ static int prepare_impl(pmb_ctx* c, const pmb_chrom_args* a, uint32_t n, pmb_bat
 
 extern "C" int pmb_batch_prepare(pmb_ctx* c, const pmb_chrom_args* a, uint32_t n, pmb_batch** out)
 {
-    return prepare_impl(c, a, n, out, c && c->async_h2d);
+    return guarded(c, [&]() -> int { return prepare_impl(c, a, n, out, c && c->async_h2d); });
 }
 
 // ------------------------------------------------------------------ batch: execute
@@ -1120,11 +1136,19 @@ static int execute_events(pmb_ctx* c, pmb_batch* b)
     return PMB_OK;
 }
 
+static int execute_dense(pmb_ctx* c, pmb_batch* b);
+
 extern "C" int pmb_batch_execute(pmb_ctx* c, pmb_batch* b)
 {
     if (!c || !b) return PMB_ERR_ARG;
-    CU_TRY(c, cudaSetDevice(c->device));
-    if (b->path == 2) return execute_events(c, b);
+    return guarded(c, [&]() -> int {
+        CU_TRY(c, cudaSetDevice(c->device));
+        return b->path == 2 ? execute_events(c, b) : execute_dense(c, b);
+    });
+}
+
+static int execute_dense(pmb_ctx* c, pmb_batch* b)
+{
     cudaStream_t st = c->stream;
     const uint32_t H = b->halo_words;
     const int64_t NEG = -(1ll << 40), POS = (1ll << 40);
@@ -1286,7 +1310,7 @@ extern "C" int pmb_run_batch(pmb_ctx* c, const pmb_chrom_args* a, pmb_chrom_out*
 {
     pmb_batch* b = nullptr;
     // the caller's arrays stay valid for the whole call, so the input copy may overlap the kernels
-    int rc = prepare_impl(c, a, n, &b, true);
+    int rc = guarded(c, [&]() -> int { return prepare_impl(c, a, n, &b, true); });
     if (rc != PMB_OK) return rc;
     rc = pmb_batch_execute(c, b);
     if (rc == PMB_OK) rc = pmb_batch_fetch(c, b, o);
