@@ -180,11 +180,15 @@ def sum_outputs(per_rank_outputs):
     element-wise sum of the per-rank output dicts of the same job list."""
     first = per_rank_outputs[0]
     merged = []
-    for j in range(len(first)):
+    for j, job_out in enumerate(first):
         d = {}
-        for k in first[j]:
-            vals = [outs[j][k] for outs in per_rank_outputs]
-            d[k] = sum(int(v) for v in vals) if np.isscalar(vals[0]) or isinstance(vals[0], int) \
-                else np.sum(np.stack(vals), axis=0)
+        for k, v0 in job_out.items():
+            if np.isscalar(v0) or isinstance(v0, int):
+                d[k] = sum(int(outs[j][k]) for outs in per_rank_outputs)
+            else:
+                acc = np.array(v0, dtype=np.int64, copy=True)
+                for outs in per_rank_outputs[1:]:
+                    acc += outs[j][k]
+                d[k] = acc
         merged.append(d)
     return merged
