@@ -534,8 +534,8 @@ def gpu_arm(args):
                     "frac": nbytes / fwd_s / 1e9 / hbm_peak, "peak_source": peak_src,
                     "algorithmic_bytes": nbytes, "kernel_ms": fwd_s * 1e3,
                     "all_event_kernels_ms": all_s * 1e3,
-                    "traffic": 1.160e9 if (world == 1 and mode == "both") else None,
-                    "traffic_source": "profiles/r01_ncu_event_window_v9.txt (ncu --set full, N=1: "
+                    "traffic": 1.168e9 if (world == 1 and mode == "both") else None,
+                    "traffic_source": "profiles/r01_ncu_event_window_v20.txt (ncu --set full, N=1: "
                                       "dram__bytes_read.sum + dram__bytes_write.sum of the FWD launch)",
                     "note": "latency/issue-bound today (see profiles/); evals/s of this path are "
                             "delivered evals: the counts equal the dense kernel's bit for bit"}
