@@ -33,6 +33,12 @@ from .result import (
 logger = logging.getLogger(__name__)
 
 
+def _ints(v):
+    """Python ints of a count vector (ndarray.tolist converts at C speed; the reference's
+    result fields are plain lists of ints)."""
+    return v.tolist() if hasattr(v, "tolist") else [int(x) for x in v]
+
+
 class DeviceEngine(object):
     """Runs batches of chromosome jobs on one B200 through the C ABI."""
 
@@ -288,15 +294,15 @@ class CCBitArrayCalculator(object):
                          p.fwd, p.rev, b, e)
 
     def _mappable_len_list(self, dmp):
-        # mscc.pyx:271, :292-298 -- popc(D_k) re-indexed by |read_len-1-k|
-        rl = self._read_len
+        # mscc.pyx:271, :292-298 -- popc(D_k) re-indexed by |read_len-1-k|: shifts k < read_len
+        # fill ml[read_len-1-k], shifts k >= 2*read_len-1 are appended, the ones between repeat
+        # values already stored and are dropped
+        rl, S = self._read_len, self._max_shift + 1
+        d = dmp.tolist() if hasattr(dmp, "tolist") else [int(x) for x in dmp]
+        n = min(rl, S)
         ml = [None] * rl
-        for k in range(self._max_shift + 1):
-            if k < rl:
-                ml[rl - k - 1] = int(dmp[k])
-            elif k >= rl * 2 - 1:
-                ml.append(int(dmp[k]))
-        return ml
+        ml[rl - n:rl] = d[:n][::-1]
+        return ml + d[2 * rl - 1:S]
 
     def _store(self, p, out):
         chrom, L = p.chrom, self.ref2genomelen[p.chrom]
@@ -306,15 +312,15 @@ class CCBitArrayCalculator(object):
             r = NCCResult(max_shift=self._max_shift, read_len=self._read_len, genomelen=L,
                           forward_sum=out["fwd_total"], reverse_sum=out["rev_total"],
                           forward_read_len_sum=p.fwd_len_sum, reverse_read_len_sum=p.rev_len_sum,
-                          ccbins=[int(x) for x in out["ncc"]])
+                          ccbins=_ints(out["ncc"]))
             r.calc_cc()
             self.ref2ncc_result[chrom] = r
         if p.intervals is not None:
             r = MSCCResult(max_shift=self._max_shift, read_len=self._read_len, genomelen=L,
-                           forward_sum=[int(x) for x in out["mfwd"]],
-                           reverse_sum=[int(x) for x in out["mrev"]],
+                           forward_sum=_ints(out["mfwd"]),
+                           reverse_sum=_ints(out["mrev"]),
                            forward_read_len_sum=p.fwd_len_sum, reverse_read_len_sum=p.rev_len_sum,
-                           ccbins=[int(x) for x in out["mscc"]],
+                           ccbins=_ints(out["mscc"]),
                            mappable_len=self._mappable_len_list(out["dmp"]))
             r.calc_cc()
             self.ref2mscc_result[chrom] = r
@@ -362,7 +368,7 @@ class CCBitArrayCalculator(object):
         for p, out in zip(self._pending, outs):
             self._store(p, out)
         for res, out in zip(fills, outs[len(self._pending):]):
-            res.mappable_len = tuple(int(x) for x in out["dmp"])
+            res.mappable_len = tuple(_ints(out["dmp"]))
         self._pending = []
 
     def _compute_pending(self, fill=()):
