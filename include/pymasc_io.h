@@ -39,6 +39,12 @@ typedef enum {
 
 const char *pmio_last_error(void);
 
+/* One raw-DEFLATE stream (RFC 1951, no zlib/gzip wrapper) into exactly out_len bytes, by the
+ * library's own decoder (use_zlib = 0; pymasc_b200/csrc/pmb_inflate.h -- what BGZF blocks go
+ * through first) or by zlib (use_zlib = 1; the fallback for anything the former refuses).
+ * PMIO_ERR_FORMAT when the stream does not decode to that size. */
+int pmio_inflate_raw(const uint8_t *in, uint64_t in_len, uint8_t *out, uint64_t out_len, int use_zlib);
+
 /* ------------------------------------------------------------------ BAM */
 typedef struct pmio_bam pmio_bam;
 

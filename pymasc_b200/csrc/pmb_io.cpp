@@ -31,6 +31,7 @@
 #include <vector>
 
 #include "../../include/pymasc_io.h"
+#include "pmb_inflate.h"
 
 static thread_local std::string g_err;
 
@@ -75,10 +76,8 @@ inline int32_t rdi32(const uint8_t* p) { int32_t v; memcpy(&v, p, 4); return v; 
 inline uint64_t rd64(const uint8_t* p) { uint64_t v; memcpy(&v, p, 8); return v; }
 inline float rdf32(const uint8_t* p) { float v; memcpy(&v, p, 4); return v; }
 
-// raw-deflate payload -> dst (exactly `isize` bytes); crc checked
-bool inflate_block(const uint8_t* src, size_t csize, uint8_t* dst, size_t isize, uint32_t crc)
+bool zlib_inflate_raw(const uint8_t* src, size_t csize, uint8_t* dst, size_t isize)
 {
-    if (isize == 0) return true;
     z_stream zs;
     memset(&zs, 0, sizeof zs);
     if (inflateInit2(&zs, -15) != Z_OK) return false;
@@ -89,12 +88,33 @@ bool inflate_block(const uint8_t* src, size_t csize, uint8_t* dst, size_t isize,
     int rc = inflate(&zs, Z_FINISH);
     const bool ok = rc == Z_STREAM_END && zs.total_out == isize;
     inflateEnd(&zs);
-    return ok && (uint32_t)crc32(crc32(0L, Z_NULL, 0), dst, (uInt)isize) == crc;
+    return ok;
+}
+
+// raw-deflate payload -> dst (exactly `isize` bytes); crc checked.  The fast decoder
+// (pmb_inflate.h) goes first; whatever it refuses or gets wrong (size or CRC) is done by zlib.
+bool inflate_block(const uint8_t* src, size_t csize, uint8_t* dst, size_t isize, uint32_t crc)
+{
+    if (isize == 0) return true;
+    static const bool zlib_only = getenv("PMIO_ZLIB_ONLY") != nullptr;      // A/B aid
+    auto crc_ok = [&]() { return (uint32_t)crc32(crc32(0L, Z_NULL, 0), dst, (uInt)isize) == crc; };
+    if (!zlib_only && pmb_inflate::inflate(src, csize, dst, isize) && crc_ok()) return true;
+    return zlib_inflate_raw(src, csize, dst, isize) && crc_ok();
 }
 
 struct Block { size_t data_off; uint32_t csize, isize, crc; size_t out_off; };
 
 }  // namespace
+
+// Raw-DEFLATE decoding of one buffer by either decoder (test hook: the fast decoder is checked
+// against zlib on arbitrary streams, tests/test_io_native.py).
+extern "C" int pmio_inflate_raw(const uint8_t* in, uint64_t in_len, uint8_t* out, uint64_t out_len, int use_zlib)
+{
+    if (!in || (!out && out_len)) return fail(PMIO_ERR_ARG, "null argument");
+    const bool ok = use_zlib ? zlib_inflate_raw(in, (size_t)in_len, out, (size_t)out_len)
+                             : pmb_inflate::inflate(in, (size_t)in_len, out, (size_t)out_len);
+    return ok ? PMIO_OK : fail(PMIO_ERR_FORMAT, "stream does not inflate to the given size");
+}
 
 // ====================================================================== BAM
 // One thread's share of a batch: a run of complete records, filtered into arrays that stay

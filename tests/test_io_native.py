@@ -433,3 +433,94 @@ def test_hostile_bgzf_sizes_are_format_errors(tmp_path):
     open(p2, "wb").write(W.bgzf_block(b"BAM\x01" + struct.pack("<ii", 0, 0x7FFFFFFF)) + W.BGZF_EOF)
     with pytest.raises(ValueError):
         io_native.BamFile(p2)               # truncated header, not an allocation of 2^31 names
+
+
+# ------------------------------------------------------------------ the library's own inflate
+def _raw_deflate(data, level, strategy, wbits=-15):
+    import zlib
+    co = zlib.compressobj(level, zlib.DEFLATED, wbits, 9, strategy)
+    return co.compress(data) + co.flush()
+
+
+def _inflate_payloads():
+    rng = np.random.default_rng(11)
+    yield b""
+    yield b"a"
+    yield b"a" * 65536                                           # one long run: distance 1, length 258
+    yield bytes(range(256)) * 200
+    yield rng.integers(0, 256, 65280, dtype=np.uint8).tobytes()   # incompressible: stored blocks
+    yield b"ACGT" * 9000 + rng.integers(0, 256, 100, dtype=np.uint8).tobytes() + b"T" * 7000
+    for n in (1, 7, 8, 9, 257, 258, 259, 4095, 30000, 65536):
+        yield rng.integers(0, 4, n, dtype=np.uint8).tobytes()
+        skew = np.r_[np.full(16, 0.05), np.full(240, 0.2 / 240)]  # long and short codes: second-level tables
+        yield rng.choice(np.arange(256, dtype=np.uint8), n, p=skew).tobytes()
+        yield (b"SRR1234567.%d\0" % n) * (n // 12 + 1)
+
+
+def test_own_inflate_agrees_with_zlib_on_every_block_type():
+    """pmb_inflate.h decodes what zlib wrote -- stored, fixed-Huffman and dynamic blocks, short
+    windows, levels 0-9 -- byte for byte, and the zlib route of the same entry point agrees."""
+    import zlib
+    n = 0
+    for data in _inflate_payloads():
+        for level in (0, 1, 6, 9):
+            for strategy in (zlib.Z_DEFAULT_STRATEGY, zlib.Z_FIXED, zlib.Z_HUFFMAN_ONLY, zlib.Z_RLE):
+                for wbits in (-15, -9):
+                    stream = _raw_deflate(data, level, strategy, wbits)
+                    assert io_native.inflate_raw(stream, len(data)) == data
+                    n += 1
+        assert io_native.inflate_raw(_raw_deflate(data, 6, zlib.Z_DEFAULT_STRATEGY), len(data), use_zlib=True) == data
+    assert n > 1000
+
+
+def test_own_inflate_refuses_what_it_cannot_vouch_for():
+    """Wrong size, truncation and flipped bits: the decoder either refuses (the BGZF path then asks
+    zlib and the CRC decides) or returns exactly what zlib returns; it never writes past the
+    buffer it was given (the canary after it stays intact inside the library call)."""
+    import zlib
+    rng = np.random.default_rng(12)
+    data = rng.integers(0, 16, 30000, dtype=np.uint8).tobytes()
+    stream = _raw_deflate(data, 6, zlib.Z_DEFAULT_STRATEGY)
+    for wrong in (len(data) - 1, len(data) + 1, 0):
+        with pytest.raises(ValueError):
+            io_native.inflate_raw(stream, wrong)
+    with pytest.raises(ValueError):
+        io_native.inflate_raw(b"\x07", 10)                      # reserved block type 3
+    refused = 0
+    for _ in range(600):
+        b = bytearray(stream)
+        b[int(rng.integers(len(b)))] ^= 1 << int(rng.integers(8))
+        if rng.random() < 0.3:
+            b = b[:int(rng.integers(len(b)))]
+        try:
+            got = io_native.inflate_raw(bytes(b), len(data))
+        except ValueError:
+            refused += 1
+            continue
+        try:
+            assert got == io_native.inflate_raw(bytes(b), len(data), use_zlib=True)
+        except ValueError:
+            pass                                                # zlib refuses it: the CRC check is what decides
+    assert refused > 100
+
+
+def test_bam_decodes_the_same_with_and_without_the_own_inflate(tmp_path):
+    """A/B of the BGZF path: PMIO_ZLIB_ONLY=1 (read once per process, so in a child) gives the
+    same arrays as the default route."""
+    import subprocess
+    import sys
+    recs, _, _ = synthetic_records()
+    p = str(tmp_path / "ab.bam")
+    W.write_bam(p, [("c1", 200000), ("c2", 5000), ("c3", 90000)], recs, block_payload=4000, align_records=True)
+    code = ("import sys, hashlib; sys.path.insert(0, %r); from pymasc_b200 import io_native; "
+            "b = io_native.BamFile(%r, mapq_criteria=1); h = hashlib.sha256(); "
+            "[h.update(b.reads[c][k].tobytes()) for c in sorted(b.reads) for k in ('pos', 'readlen', 'is_reverse')]; "
+            "print(h.hexdigest(), b.stats['n_accepted'])"
+            % (os.path.dirname(os.path.dirname(os.path.abspath(__file__))), p))
+    outs = []
+    for env_extra in ({}, {"PMIO_ZLIB_ONLY": "1"}):
+        env = {k: v for k, v in os.environ.items() if k != "PMIO_ZLIB_ONLY"}
+        env.update(env_extra)
+        outs.append(subprocess.run([sys.executable, "-c", code], env=env, check=True,
+                                   capture_output=True, text=True).stdout.strip())
+    assert outs[0] == outs[1] and int(outs[0].split()[1]) > 1000
