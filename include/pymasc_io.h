@@ -57,8 +57,9 @@ typedef struct {
     uint64_t n_accepted;    /* records handed to the calculator (handler/read.py rules)   */
     uint32_t sorted;        /* 1 if the accepted reads are coordinate sorted: no reference */
                             /* revisited, positions non-decreasing (mscc.pyx:351-366)     */
-    uint32_t reparsed_shares; /* decoder statistic: shares whose guessed start (a BGZF block    */
-                            /* boundary) was not a record boundary and were filtered again    */
+    uint32_t reparsed_shares; /* decoder statistic: shares whose guessed first record (found   */
+                            /* from the bytes at a BGZF block boundary) was wrong and were    */
+                            /* filtered again from the true boundary                          */
 } pmio_bam_stats;
 
 /* Decode the whole file: BGZF blocks are inflated on `threads` threads (0 = all cores), records

@@ -1,13 +1,16 @@
 // pmb_io.cpp -- libpymasc_io.so (include/pymasc_io.h): BAM (BGZF) and BigWig decoding on the
 // host into packed arrays.  zlib + std::thread; no CUDA here.
 //
-// BAM: the file is memory-mapped, BGZF block headers are walked sequentially (18 bytes per
-// <= 64 KiB block), cache-sized batches of blocks are inflated in parallel straight into their
-// final offsets of one buffer (ISIZE in each block's footer gives the offsets up front), record
-// boundaries are found by one hop over the block_size fields, and the batch is filtered in
-// parallel shares whose outputs stay as the handle's storage (no merge copy); a record cut by
-// the batch boundary is carried into the next batch.  The reads of every reference are then
-// reduced by the calculator's feed rules, references in parallel.
+// BAM: the file is memory-mapped and the BGZF block headers are walked sequentially (18 bytes per
+// <= 64 KiB block; ISIZE in each footer gives every block's offset in the inflated stream up
+// front).  A batch of blocks (<= 256 MiB inflated) is cut into shares of about 512 KiB; a worker
+// thread inflates one share (pmb_inflate.h, CRC-checked, zlib behind it) and filters its records
+// straight away, while they are in its cache, into arrays that stay as the handle's storage (no
+// merge copy).  Where a share's first record starts is guessed from the bytes (the block
+// boundary in htslib-written files, a few bytes on in htsjdk-written ones) and the guesses are
+// validated in file order afterwards; the one record that crosses a share's end is filtered
+// then, and a record cut by the end of the batch is carried into the next.  The reads of every
+// reference are finally reduced by the calculator's feed rules, references in parallel.
 // BigWig: bbi header, chromosome B+ tree and the R-tree index are read from the mapping; a
 // chromosome's data blocks are found through the R-tree, inflated and decoded (bedGraph,
 // varStep and fixedStep sections).
@@ -121,7 +124,9 @@ extern "C" int pmio_inflate_raw(const uint8_t* in, uint64_t in_len, uint8_t* out
 // alive as the storage of the handle (no merge pass: a reference's reads are the concatenation
 // of its segments, in file order).  Accepted reads form runs of one reference (a sorted file has
 // one or two per share).
-struct pmio_chunk {
+// (cache-line aligned, like the other per-thread structs below: neighbours are written by
+// different threads once per record)
+struct alignas(128) pmio_chunk {
     struct Run { int32_t ref; size_t begin; uint32_t first_pos, last_pos; };
     std::vector<uint32_t> pos, qlen;
     std::vector<uint8_t> rev;
@@ -144,7 +149,7 @@ struct pmio_bam {
     std::vector<uint64_t> hist_cnt;
     pmio_bam_stats st{};
     // per reference, the reads reduced by the calculator's feed rules (mscc.pyx:370-418)
-    struct Packed {
+    struct alignas(128) Packed {
         std::vector<uint32_t> fwd, rev;
         uint64_t fwd_len_sum = 0, rev_len_sum = 0;
     };
@@ -198,9 +203,9 @@ struct BamHeaderParser {
 };
 
 // Counters of one share (scratch, reused from batch to batch).
-struct ShareStats {
+struct alignas(128) ShareStats {
     pmio_bam_stats st{};
-    std::vector<uint64_t> hist_small = std::vector<uint64_t>(1024, 0);
+    std::vector<uint64_t> hist_small = std::vector<uint64_t>(512, 0);
     std::map<uint32_t, uint64_t> hist;
     bool sorted = true;         // within every run
     bool incomplete = false;    // stopped at a record that runs past the end of the batch
@@ -273,13 +278,54 @@ size_t parse_share(const uint8_t* p, size_t start, size_t limit, size_t end, uin
     return o;
 }
 
+// Does p[o, hi) look like the start of a BAM record?  Field ranges of the fixed part, the sizes
+// adding up inside block_size, the NUL that ends the read name.  `whole` = the record ends
+// inside [o, hi) (then *next is where the following one starts).
+inline bool plausible_record(const uint8_t* p, size_t o, size_t hi, uint32_t n_refs, size_t* next, bool* whole)
+{
+    if (hi - o < 36) return false;
+    const int32_t bs = rdi32(p + o);
+    if (bs < 32 || bs > (1 << 28)) return false;
+    const uint8_t* r = p + o + 4;
+    const int32_t ref = rdi32(r), pos0 = rdi32(r + 4), l_seq = rdi32(r + 16), nref = rdi32(r + 20), npos = rdi32(r + 24);
+    const uint32_t l_name = r[8], n_cig = rd16(r + 12);
+    if (ref < -1 || (ref >= 0 && (uint32_t)ref >= n_refs) || nref < -1 || (nref >= 0 && (uint32_t)nref >= n_refs)) return false;
+    if (pos0 < -1 || npos < -1 || l_seq < 0 || l_name == 0) return false;
+    if (32ull + l_name + 4ull * n_cig + ((uint64_t)l_seq + 1) / 2 + (uint64_t)l_seq > (uint64_t)bs) return false;
+    if (o + 36 + l_name <= hi && r[32 + l_name - 1] != 0) return false;
+    *next = o + 4 + (size_t)bs;
+    *whole = *next <= hi;
+    return true;
+}
+
+// Where the first record that STARTS in [lo, hi) begins, judged from the bytes alone: the first
+// offset from which a chain of plausible records runs (six of them, or up to the end of the
+// range).  lo itself in an htslib-written file (records never straddle its BGZF blocks); a few
+// bytes further where the writer cuts blocks anywhere (htsjdk).  SIZE_MAX: none found.  Only a
+// guess: the caller checks it against where the previous share really stopped.
+size_t find_record_start(const uint8_t* p, size_t lo, size_t hi, uint32_t n_refs)
+{
+    const size_t scan_end = std::min(hi, lo + (1u << 17));
+    for (size_t o = lo; o < scan_end; o++) {
+        size_t at = o, next = 0;
+        bool whole = false, ok = true;
+        for (int k = 0; k < 6 && at < hi; k++) {
+            if (!plausible_record(p, at, hi, n_refs, &next, &whole)) { ok = hi - at < 36 && k > 0; break; }
+            if (!whole) { ok = k > 0; break; }
+            at = next;
+        }
+        if (ok) return o;
+    }
+    return SIZE_MAX;
+}
+
 // Shares of a batch, in file order: their runs become segments of the per-reference lists;
 // coordinate order across shares and references is checked here (mscc.pyx:351-366: no reference
 // revisited, positions non-decreasing).
 struct BamMerger {
     pmio_bam* b;
     std::map<uint32_t, uint64_t> hist;
-    std::vector<uint64_t> hist_small = std::vector<uint64_t>(1024, 0);
+    std::vector<uint64_t> hist_small = std::vector<uint64_t>(512, 0);
     int32_t cur_ref = -1;
     uint32_t last_pos = 0;
     std::vector<uint8_t> seen;
@@ -320,12 +366,43 @@ struct BamMerger {
 // it (mscc.pyx:416-418).  Both lists come out sorted and unique.
 void pack_reference(const std::vector<pmio_bam::Seg>& segs, uint64_t n, pmio_bam::Packed& out)
 {
+    // One streaming pass while the reverse ends come in order (always, when the reads have one
+    // length): both lists are written once, nothing else is allocated.
     out.fwd.reserve(n / 2 + n / 8 + 16);
+    out.rev.reserve(n / 2 + n / 8 + 16);
+    uint32_t last_f = 0, last_e = 0;
+    bool ends_sorted = true;
+    for (const pmio_bam::Seg& s : segs) {
+        const uint32_t* pos = s.c->pos.data();
+        const uint32_t* qlen = s.c->qlen.data();
+        const uint8_t* rev = s.c->rev.data();
+        size_t i = s.begin;
+        for (; i < s.end; i++) {
+            if (!rev[i]) {
+                if (pos[i] == last_f) continue;
+                last_f = pos[i];
+                out.fwd.push_back(pos[i]);
+                out.fwd_len_sum += qlen[i];
+            } else {
+                const uint32_t e = pos[i] + qlen[i] - 1;
+                if (e == last_e) continue;              // that bit is set: the first read's length stays
+                if (e < last_e) { ends_sorted = false; break; }
+                last_e = e;
+                out.rev.push_back(e);
+                out.rev_len_sum += qlen[i];
+            }
+        }
+        if (!ends_sorted) break;
+    }
+    if (ends_sorted) return;
+    // Reads of several lengths: the ends are out of order.  Collect them all, sort stably (the
+    // first read to set a bit is the one whose length counts), drop repeats.
+    out.fwd.clear(); out.rev.clear();
+    out.fwd_len_sum = out.rev_len_sum = 0;
     std::vector<uint32_t> ends, lens;
     ends.reserve(n / 2 + n / 8 + 16);
     lens.reserve(n / 2 + n / 8 + 16);
-    uint32_t last_f = 0;
-    bool ends_sorted = true;
+    last_f = 0;
     for (const pmio_bam::Seg& s : segs) {
         const uint32_t* pos = s.c->pos.data();
         const uint32_t* qlen = s.c->qlen.data();
@@ -337,18 +414,10 @@ void pack_reference(const std::vector<pmio_bam::Seg>& segs, uint64_t n, pmio_bam
                 out.fwd.push_back(pos[i]);
                 out.fwd_len_sum += qlen[i];
             } else {
-                const uint32_t e = pos[i] + qlen[i] - 1;
-                if (!ends.empty() && e < ends.back()) ends_sorted = false;
-                ends.push_back(e);
+                ends.push_back(pos[i] + qlen[i] - 1);
                 lens.push_back(qlen[i]);
             }
         }
-    }
-    if (ends_sorted) {
-        out.rev.reserve(ends.size());
-        for (size_t i = 0; i < ends.size(); i++)
-            if (i == 0 || ends[i] != ends[i - 1]) { out.rev.push_back(ends[i]); out.rev_len_sum += lens[i]; }
-        return;
     }
     std::vector<uint32_t> idx(ends.size());
     for (size_t i = 0; i < idx.size(); i++) idx[i] = (uint32_t)i;
@@ -395,18 +464,37 @@ static int bam_load_impl(const char* path, int mapq_criteria, int threads, pmio_
     pmio_bam* b = owner.get();
     BamHeaderParser header{b};
     BamMerger merger{b};
-    std::vector<ShareStats> share_stats((size_t)threads);
-    std::vector<size_t> cuts, stops;
+    std::vector<ShareStats> share_stats;
+    ShareStats straddler_stats;
     // PMIO_TIMING=1: seconds per stage on stderr (debug aid)
     static const bool timing = getenv("PMIO_TIMING") != nullptr;
     auto now = []() { return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count(); };
-    double t_inflate = 0, t_scan = 0, t_parse = 0, t_pack = 0, t_mark = now();
-    // Batch size: large enough that the two thread-pool start-ups per batch are noise (measured:
-    // 256-block batches on 8 threads cost 1.7x the inflate time of 4096-block ones), small
-    // enough to bound the buffer (<= 256 MiB inflated).
-    size_t BATCH_BLOCKS = std::min<size_t>(4096, 512 * (size_t)threads);
+    double t_decode = 0, t_validate = 0, t_pack = 0, t_mark = now();
+    // A batch bounds the buffer (<= 256 MiB inflated); inside it the unit of work is a SHARE: a
+    // run of whole BGZF blocks of about SHARE_BYTES inflated, small enough that the thread which
+    // inflated it filters it while it is still in its cache -- the inflated bytes are written
+    // once and never read back from DRAM.
+    size_t BATCH_BLOCKS = 4096, SHARE_BYTES = 512u << 10;
     if (const char* e = getenv("PMIO_BATCH_BLOCKS")) BATCH_BLOCKS = std::max<size_t>(1, (size_t)atoll(e));
-    std::vector<uint8_t> buf;
+    if (const char* e = getenv("PMIO_SHARE_BYTES")) SHARE_BYTES = std::max<size_t>(1, (size_t)atoll(e));
+    // not a std::vector: nothing may zero (= touch, sequentially) 256 MiB before the workers write it
+    struct RawBuffer {
+        uint8_t* p = nullptr;
+        size_t cap = 0;
+        ~RawBuffer() { free(p); }
+        void grow(size_t n, size_t keep)
+        {
+            if (n <= cap) return;
+            uint8_t* q = (uint8_t*)malloc(n);
+            if (!q) throw std::bad_alloc();
+            if (keep) memcpy(q, p, keep);
+            free(p);
+            p = q;
+            cap = n;
+        }
+    } buf;
+    struct Share { size_t blk_lo, blk_hi, lo, hi, start, stop; };
+    std::vector<Share> shares;
     std::vector<Block> blocks;
     size_t carry = 0, off = 0;
     bool bad = false;
@@ -442,96 +530,111 @@ static int bam_load_impl(const char* path, int mapq_criteria, int threads, pmio_
             off += bsize;
         }
         if (bad) break;
-        if (buf.size() < out_off) buf.resize(out_off);
-        // ---- inflate the batch in parallel
-        std::atomic<size_t> next{0};
-        std::atomic<bool> ok{true};
+        buf.grow((out_off + (1u << 20)) & ~(size_t)((1u << 20) - 1), carry);
+        const char* const inflate_err = "BGZF block does not inflate (corrupt data or CRC mismatch)";
+        // ---- the header (first batch): the main thread inflates blocks until it is complete
+        size_t used = 0, blk0 = 0;
+        while (header.stage != 2 && blk0 < blocks.size()) {
+            const Block& k = blocks[blk0++];
+            if (!inflate_block(m.p + k.data_off, k.csize, buf.p + k.out_off, k.isize, k.crc)) { g_err = inflate_err; bad = true; break; }
+            const long long h = header.feed(buf.p + used, k.out_off + k.isize - used);
+            if (h < 0) { bad = true; break; }
+            used += (size_t)h;
+        }
+        if (bad) break;
+        if (header.stage != 2) {            // a header longer than the batch: carry what is left of it
+            carry = out_off - used;
+            if (carry && used) memmove(buf.p, buf.p + used, carry);
+            continue;
+        }
+        // ---- shares: [used, ...) cut at block boundaries every SHARE_BYTES or so
+        shares.clear();
+        {
+            Share s{blk0, blk0, used, used, used, used};
+            for (size_t j = blk0; j < blocks.size(); j++) {
+                s.blk_hi = j + 1;
+                s.hi = blocks[j].out_off + blocks[j].isize;
+                if (s.hi - s.lo >= SHARE_BYTES && j + 1 < blocks.size()) {
+                    shares.push_back(s);
+                    s = Share{j + 1, j + 1, s.hi, s.hi, SIZE_MAX, s.hi};
+                }
+            }
+            s.hi = out_off;
+            if (s.hi > s.lo) shares.push_back(s);
+        }
+        const size_t n_shares = shares.size();
+        const uint32_t n_refs = (uint32_t)b->names.size();
+        if (share_stats.size() < n_shares) share_stats.resize(n_shares);
+        const size_t store0 = b->store.size();      // two chunks per share: its records, then the one that straddles its end
+        for (size_t i = 0; i < 2 * n_shares; i++) b->store.emplace_back(new pmio_chunk());
+        // ---- every share: inflate, guess where its first record starts, filter -- one thread, one pass.
+        //      Share 0 starts at a known record boundary.  The others start at a BGZF block boundary,
+        //      which IS a record boundary in an htslib-written file and a few bytes before one
+        //      otherwise (find_record_start); a share stops at the record that crosses its end.
+        std::atomic<size_t> next_share{0};
+        std::atomic<int> failure{0};                // 1 inflate, 2 exception
+        const uint8_t* p = buf.p;
         auto work = [&]() {
-            for (;;) {
-                const size_t i = next.fetch_add(1);
-                if (i >= blocks.size() || !ok.load()) return;
-                const Block& k = blocks[i];
-                if (!inflate_block(m.p + k.data_off, k.csize, buf.data() + k.out_off, k.isize, k.crc)) ok.store(false);
+            for (size_t i; (i = next_share.fetch_add(1)) < n_shares && !failure.load(std::memory_order_relaxed);) {
+                Share& s = shares[i];
+                try {       // an exception must not leave a worker thread
+                    for (size_t j = s.blk_lo; j < s.blk_hi; j++) {
+                        const Block& k = blocks[j];
+                        if (!inflate_block(m.p + k.data_off, k.csize, buf.p + k.out_off, k.isize, k.crc)) { failure.store(1); return; }
+                    }
+                    share_stats[i].reset();
+                    if (i > 0) s.start = find_record_start(p, s.lo, s.hi, n_refs);
+                    s.stop = s.start == SIZE_MAX ? s.lo
+                           : parse_share(p, s.start, s.hi, s.hi, n_refs, mapq_criteria, *b->store[store0 + 2 * i], share_stats[i]);
+                } catch (...) {
+                    failure.store(2);
+                }
             }
         };
-        const int nt = (int)std::min<size_t>((size_t)threads, std::max<size_t>(1, blocks.size() / 4));
-        std::vector<std::thread> pool;
-        for (int t = 1; t < nt; t++) pool.emplace_back(work);
-        work();
-        for (auto& t : pool) t.join();
-        if (!ok.load()) { g_err = "BGZF block does not inflate (corrupt data or CRC mismatch)"; bad = true; break; }
-        { const double t = now(); t_inflate += t - t_mark; t_mark = t; }
-        // ---- header first (sequential), then the records.  Shares start at BGZF block boundaries
-        //      -- htslib never lets a record straddle two blocks unless it is longer than one, so a
-        //      block boundary is almost always a record boundary -- and are filtered in parallel ON
-        //      THAT GUESS; afterwards the guesses are checked inductively in file order (share 0
-        //      starts at a known boundary; share i+1's start is right iff it is where share i
-        //      stopped) and a share whose start was wrong is filtered again from the true boundary.
-        //      No sequential pass over the records remains in the common case.  The record cut by
-        //      the end of the batch is carried into the next one.
-        size_t used = 0;
-        if (header.stage != 2) {
-            const long long h = header.feed(buf.data(), out_off);
-            if (h < 0) { bad = true; break; }
-            used = (size_t)h;
+        {
+            std::vector<std::thread> pool;
+            for (size_t t = 1; t < std::min<size_t>((size_t)threads, n_shares); t++) pool.emplace_back(work);
+            work();
+            for (auto& t : pool) t.join();
         }
-        if (header.stage == 2) {
-            const uint8_t* p = buf.data();
-            const size_t share = std::max<size_t>((out_off - used) / (size_t)threads + 1, 1 << 16);
-            cuts.clear();
-            cuts.push_back(used);
-            for (const Block& k : blocks)
-                if (k.out_off > cuts.back() && k.out_off - cuts.back() >= share) cuts.push_back(k.out_off);
-            cuts.push_back(out_off);
-            const size_t n_shares = cuts.size() - 1;
-            const uint32_t n_refs = (uint32_t)b->names.size();
-            if (share_stats.size() < n_shares) share_stats.resize(n_shares);
-            stops.assign(n_shares, 0);
-            const size_t store0 = b->store.size();
-            for (size_t i = 0; i < n_shares; i++) b->store.emplace_back(new pmio_chunk());
-            std::atomic<size_t> next_share{0};
-            std::atomic<bool> oom{false};
-            auto parse_work = [&]() {
-                for (size_t i; (i = next_share.fetch_add(1)) < n_shares;) {
-                    share_stats[i].reset();
-                    try {       // an exception must not leave a worker thread
-                        stops[i] = parse_share(p, cuts[i], cuts[i + 1], out_off, n_refs, mapq_criteria,
-                                               *b->store[store0 + i], share_stats[i]);
-                    } catch (...) {
-                        oom.store(true);
-                    }
-                }
-            };
-            std::vector<std::thread> ppool;
-            for (size_t t = 1; t < std::min<size_t>((size_t)threads, n_shares); t++) ppool.emplace_back(parse_work);
-            parse_work();
-            for (auto& t : ppool) t.join();
-            if (oom.load()) throw std::bad_alloc();
-            { const double t = now(); t_parse += t - t_mark; t_mark = t; }
-            size_t at = used;                       // a true record boundary
-            for (size_t i = 0; i < n_shares; i++) {
-                pmio_chunk& c = *b->store[store0 + i];
-                if (at >= cuts[i + 1] && cuts[i + 1] != cuts[i]) { c = pmio_chunk(); continue; }   // inside a long record
-                if (at != cuts[i]) {                // wrong guess: again, from the true boundary
-                    c = pmio_chunk();
-                    share_stats[i].reset();
-                    stops[i] = parse_share(p, at, cuts[i + 1], out_off, n_refs, mapq_criteria, c, share_stats[i]);
-                    b->st.reparsed_shares++;
-                }
-                if (share_stats[i].err) { g_err = share_stats[i].err; bad = true; break; }
-                merger.take(c, share_stats[i]);
-                at = stops[i];
-                if (share_stats[i].incomplete) {
-                    for (size_t k = i + 1; k < n_shares; k++) *b->store[store0 + k] = pmio_chunk();
-                    break;
-                }
+        if (failure.load() == 2) throw std::bad_alloc();
+        if (failure.load() == 1) { g_err = inflate_err; bad = true; break; }
+        { const double t = now(); t_decode += t - t_mark; t_mark = t; }
+        // ---- the guesses are checked in file order: share i+1's start is right iff it is where
+        //      share i, and the record that straddled its end, really stopped.  A wrong guess (or
+        //      none) is filtered again from the true boundary; a share that lies inside one long
+        //      record is dropped.  The record cut by the end of the batch is carried over.
+        size_t at = used;
+        for (size_t i = 0; i < n_shares && !bad; i++) {
+            Share& s = shares[i];
+            pmio_chunk& c = *b->store[store0 + 2 * i];
+            if (at >= s.hi) { c = pmio_chunk(); continue; }
+            if (s.start != at) {
+                c = pmio_chunk();
+                share_stats[i].reset();
+                s.stop = parse_share(p, at, s.hi, s.hi, n_refs, mapq_criteria, c, share_stats[i]);
+                b->st.reparsed_shares++;
             }
-            if (bad) break;
-            used = at;
-            { const double t = now(); t_scan += t - t_mark; t_mark = t; }
+            if (share_stats[i].err) { g_err = share_stats[i].err; bad = true; break; }
+            merger.take(c, share_stats[i]);
+            at = s.stop;
+            if (at >= s.hi) continue;
+            // the record starting at `at` crosses the end of the share (or of the batch)
+            pmio_chunk& c2 = *b->store[store0 + 2 * i + 1];
+            straddler_stats.reset();
+            const size_t stop2 = parse_share(p, at, at + 1, out_off, n_refs, mapq_criteria, c2, straddler_stats);
+            if (straddler_stats.err) { g_err = straddler_stats.err; bad = true; break; }
+            if (straddler_stats.incomplete) {       // it runs past the batch: nothing after it can be right
+                for (size_t k = i + 1; k < n_shares; k++) *b->store[store0 + 2 * k] = pmio_chunk();
+                break;
+            }
+            merger.take(c2, straddler_stats);
+            at = stop2;
         }
-        carry = out_off - used;
-        if (carry && used) memmove(buf.data(), buf.data() + used, carry);
+        if (bad) break;
+        { const double t = now(); t_validate += t - t_mark; t_mark = t; }
+        carry = out_off - std::min(at, out_off);
+        if (carry && at) memmove(buf.p, buf.p + at, carry);
     }
     if (!bad && header.stage != 2) { g_err = "truncated BAM header"; bad = true; }
     if (!bad && carry) { g_err = "truncated BAM file (incomplete record at the end)"; bad = true; }
@@ -566,9 +669,9 @@ static int bam_load_impl(const char* path, int mapq_criteria, int threads, pmio_
     }
     t_pack = now() - t_mark;
     if (timing)
-        fprintf(stderr, "[pmio bam] %d threads, %zu-block batches: inflate %.3f s, filter %.3f s, validate + carry %.3f s "
-                        "(%u shares filtered again), pack %.3f s\n", threads, BATCH_BLOCKS, t_inflate, t_parse, t_scan,
-                b->st.reparsed_shares, t_pack);
+        fprintf(stderr, "[pmio bam] %d threads, %zu-block batches, %zu-byte shares: inflate + filter %.3f s, "
+                        "validate + carry %.3f s (%u shares filtered again), pack %.3f s\n", threads, BATCH_BLOCKS,
+                SHARE_BYTES, t_decode, t_validate, b->st.reparsed_shares, t_pack);
     *out = owner.release();
     return PMIO_OK;
 }

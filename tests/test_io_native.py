@@ -108,21 +108,31 @@ def synthetic_records():
     return recs, want, hist
 
 
-@pytest.mark.parametrize("block_payload,threads,aligned", [
-    (65280, 1, False), (997, 3, False), (64, 2, False), (8192, 4, False),
-    (8192, 4, True), (997, 3, True), (150, 2, True)])       # 150: some records are longer than a block
-def test_synthetic_bam_flags_cigars_and_block_boundaries(tmp_path, block_payload, threads, aligned):
-    """Shares of a batch start at BGZF block boundaries on the guess that those are record
-    boundaries (true for htslib-written files: `aligned`); every wrong guess must be caught by
-    the validation pass and filtered again -- same result either way."""
+@pytest.mark.parametrize("block_payload,threads,aligned,share_bytes", [
+    (65280, 1, False, None), (997, 3, False, None), (64, 2, False, None), (8192, 4, False, None),
+    (8192, 4, True, None), (997, 3, True, None), (150, 2, True, None),      # 150: some records are longer than a block
+    (8192, 4, False, 20000), (997, 3, False, 5000), (8192, 4, True, 20000), (997, 3, True, 5000),
+    (64, 2, False, 100), (150, 2, True, 300), (64, 3, False, 1)])           # shares shorter than a record
+def test_synthetic_bam_flags_cigars_and_block_boundaries(tmp_path, monkeypatch, block_payload, threads, aligned,
+                                                         share_bytes):
+    """Every share of a batch but the first starts at a BGZF block boundary and has to guess where
+    its first record begins: at the boundary in an htslib-written file (`aligned`), a few bytes on
+    where the writer cuts blocks anywhere (htsjdk).  The guesses are validated in file order;
+    where one is wrong or impossible (shares inside one long record) the share is filtered again
+    from the true boundary -- the result is the same either way.  PMIO_SHARE_BYTES shrinks the
+    shares so that a 300 KB file has many of them."""
+    if share_bytes is None:
+        monkeypatch.delenv("PMIO_SHARE_BYTES", raising=False)
+    else:
+        monkeypatch.setenv("PMIO_SHARE_BYTES", str(share_bytes))
     recs, want, hist = synthetic_records()
     path = str(tmp_path / "syn.bam")
     W.write_bam(path, [("c1", 200000), ("c2", 5000), ("c3", 90000)], recs, block_payload, align_records=aligned)
     bam = io_native.BamFile(path, mapq_criteria=20, threads=threads)
-    if aligned and block_payload >= 997:
-        assert bam.stats["reparsed_shares"] == 0
-    if not aligned and block_payload == 8192:
-        assert bam.stats["reparsed_shares"] > 0
+    if share_bytes in (20000, 5000):
+        assert bam.stats["reparsed_shares"] == 0        # all guesses right, aligned or not
+    if share_bytes in (100, 1):
+        assert bam.stats["reparsed_shares"] > 0         # the fallback ran, too
     assert bam.references == ("c1", "c2", "c3") and bam.lengths == (200000, 5000, 90000)
     assert sorted(bam.reads) == ["c1", "c3"] and bam.sorted
     for chrom in ("c1", "c3"):
@@ -524,3 +534,30 @@ def test_bam_decodes_the_same_with_and_without_the_own_inflate(tmp_path):
         outs.append(subprocess.run([sys.executable, "-c", code], env=env, check=True,
                                    capture_output=True, text=True).stdout.strip())
     assert outs[0] == outs[1] and int(outs[0].split()[1]) > 1000
+
+
+def test_blocks_cut_anywhere_decode_in_parallel_without_a_second_pass(tmp_path):
+    """An htsjdk-style file (records straddle the BGZF blocks) of several MiB at the default share
+    size: every share finds its first record from the bytes alone, nothing is filtered twice, and
+    the arrays equal those of the htslib-style file with the same records."""
+    rng = np.random.default_rng(21)
+    n = 120000
+    pos = np.cumsum(rng.integers(0, 30, n)) + 1
+    recs = [W.bam_record(0 if i < n // 2 else 1, int(pos[i] if i < n // 2 else pos[i] - pos[n // 2] + 1) - 1,
+                         int(rng.integers(0, 60)), 16 if rng.random() < 0.5 else 0,
+                         [(int(rng.integers(30, 51)), "M")], b"SRR%07d.%d" % (i * 7919 % 10**7, i))
+            for i in range(n)]
+    refs = [("chrA", 4_000_000), ("chrB", 4_000_000)]
+    loaded = []
+    for name, aligned in (("cut.bam", False), ("whole.bam", True)):
+        p = str(tmp_path / name)
+        W.write_bam(p, refs, recs, block_payload=65280, align_records=aligned)
+        assert os.path.getsize(p) > 2_000_000
+        bam = io_native.BamFile(p, mapq_criteria=10, threads=4)
+        assert bam.stats["reparsed_shares"] == 0 and bam.stats["n_records"] == n and bam.sorted
+        loaded.append(bam)
+    for chrom in ("chrA", "chrB"):
+        for key in ("pos", "readlen", "is_reverse"):
+            assert np.array_equal(loaded[0].reads[chrom][key], loaded[1].reads[chrom][key])
+        assert all(np.array_equal(x, y) if isinstance(x, np.ndarray) else x == y
+                   for x, y in zip(loaded[0].packed(chrom), loaded[1].packed(chrom)))
