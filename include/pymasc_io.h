@@ -45,6 +45,10 @@ const char *pmio_last_error(void);
  * PMIO_ERR_FORMAT when the stream does not decode to that size. */
 int pmio_inflate_raw(const uint8_t *in, uint64_t in_len, uint8_t *out, uint64_t out_len, int use_zlib);
 
+/* CRC-32 (gzip) of a buffer, by carry-less multiplication where the CPU has it (use_zlib = 0;
+ * pymasc_b200/csrc/pmb_crc32.h -- what checks every BGZF block) or by zlib's crc32 (use_zlib = 1). */
+uint32_t pmio_crc32(const uint8_t *data, uint64_t len, int use_zlib);
+
 /* ------------------------------------------------------------------ BAM */
 typedef struct pmio_bam pmio_bam;
 

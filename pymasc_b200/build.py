@@ -19,7 +19,7 @@ NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", 
 
 IO_OUT = os.path.join(HERE, "libpymasc_io.so")
 IO_SOURCES = ["pmb_io.cpp"]
-IO_DEPS = IO_SOURCES + ["pmb_inflate.h", os.path.join("..", "..", "include", "pymasc_io.h")]
+IO_DEPS = IO_SOURCES + ["pmb_inflate.h", "pmb_crc32.h", os.path.join("..", "..", "include", "pymasc_io.h")]
 IO_FLAGS = ["-O3", "-std=c++17", "-shared", "-fPIC", "-Wall"]
 
 

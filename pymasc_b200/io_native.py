@@ -28,7 +28,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("PYMASC_IO_LIB") or os.path.join(_HERE, "libpymasc_io.so")
 
 EXPORTS = (
-    "pmio_last_error", "pmio_inflate_raw", "pmio_bam_load", "pmio_bam_free", "pmio_bam_stats_get", "pmio_bam_n_refs",
+    "pmio_last_error", "pmio_inflate_raw", "pmio_crc32", "pmio_bam_load", "pmio_bam_free", "pmio_bam_stats_get", "pmio_bam_n_refs",
     "pmio_bam_ref_name", "pmio_bam_ref_len", "pmio_bam_reads", "pmio_bam_packed", "pmio_bam_readlen_hist",
     "pmio_bw_open", "pmio_bw_close", "pmio_bw_n_chroms", "pmio_bw_chrom_name", "pmio_bw_chrom_len",
     "pmio_bw_intervals",
@@ -58,6 +58,8 @@ def load_library():
     u32pp = ctypes.POINTER(ctypes.POINTER(ctypes.c_uint32))
     L.pmio_last_error.restype = ctypes.c_char_p
     L.pmio_inflate_raw.argtypes = [ctypes.c_char_p, ctypes.c_uint64, ctypes.c_char_p, ctypes.c_uint64, ctypes.c_int]
+    L.pmio_crc32.argtypes = [ctypes.c_char_p, ctypes.c_uint64, ctypes.c_int]
+    L.pmio_crc32.restype = ctypes.c_uint32
     L.pmio_bam_load.argtypes = [ctypes.c_char_p, ctypes.c_int, ctypes.c_int, vpp]
     L.pmio_bam_free.argtypes = [vp]
     L.pmio_bam_free.restype = None
@@ -101,6 +103,12 @@ def inflate_raw(data, out_len, use_zlib=False):
     if rc != 0:
         _raise(L, rc)
     return out.raw[:int(out_len)]
+
+
+def crc32(data, use_zlib=False):
+    """CRC-32 of a bytes-like object through the library (the BGZF block check)."""
+    data = bytes(data)
+    return int(load_library().pmio_crc32(data, len(data), int(bool(use_zlib))))
 
 
 def _raise(L, rc, path=None):

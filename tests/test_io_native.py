@@ -561,3 +561,20 @@ def test_blocks_cut_anywhere_decode_in_parallel_without_a_second_pass(tmp_path):
             assert np.array_equal(loaded[0].reads[chrom][key], loaded[1].reads[chrom][key])
         assert all(np.array_equal(x, y) if isinstance(x, np.ndarray) else x == y
                    for x, y in zip(loaded[0].packed(chrom), loaded[1].packed(chrom)))
+
+
+def test_clmul_crc32_agrees_with_zlib_on_every_length():
+    """pmb_crc32.h (carry-less multiplication, folding by 512 and 128 bits, the last 16..31 bytes
+    through zlib) against zlib.crc32: every length around the 16- and 64-byte strides, BGZF block
+    sizes, constant and random bytes."""
+    import zlib
+    rng = np.random.default_rng(31)
+    lengths = list(range(0, 330)) + [1000, 4095, 4096, 4097, 65279, 65280, 65536, (1 << 20) + 7]
+    for n in lengths:
+        d = rng.integers(0, 256, n, dtype=np.uint8).tobytes()
+        assert io_native.crc32(d) == zlib.crc32(d) == io_native.crc32(d, use_zlib=True), n
+    for n in (64, 65, 127, 128, 4096, 100001):
+        for fill in (b"\0", b"\xff", b"\x80"):
+            assert io_native.crc32(fill * n) == zlib.crc32(fill * n)
+    assert io_native.crc32(b"123456789" * 8) == zlib.crc32(b"123456789" * 8)
+    assert io_native.crc32(b"123456789", use_zlib=True) == 0xCBF43926      # the check value of CRC-32
