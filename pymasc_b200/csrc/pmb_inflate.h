@@ -2,7 +2,11 @@
 // 64-bit bit buffer refilled eight bytes at a time, two-level decode tables indexed by the next
 // bits of the stream (11 bits for literals/lengths, 8 for distances; longer codes go through
 // fixed-size second-level tables), length/distance base and extra-bit count packed in the table
-// entry, word-wide match copies where the output has room.
+// entry, a main loop that runs without bounds checks while input and output have room to spare
+// and takes up to three literals per refill (BAM payloads -- names, packed bases, qualities --
+// are mostly literals; the ends of the block go through a checked loop, one symbol at a time),
+// word-wide match copies.  (Tried and dropped: first-level slots holding two literals -- the
+// longer table build and the variable advance cost more than the shorter dependency chain won.)
 //
 // It is an accelerator, not the authority: the caller knows the exact inflated size (ISIZE) and
 // the CRC-32 of every BGZF block, checks both, and hands any block this decoder refuses (or gets
@@ -20,6 +24,9 @@ constexpr int LL_BITS = 11;      // first-level index width, literal/length code
 constexpr int D_BITS = 8;        // first-level index width, distance codes
 constexpr int MAX_LEN = 15;      // longest Huffman code of DEFLATE
 // entry: value << 16 | extra << 8 | kind << 4 | code bits consumed at this level
+//   LITERAL   value = the byte
+//   BASE      value = base length / distance, extra = number of extra bits
+//   SUBTABLE  value = offset of the second-level table, extra = its index width
 enum Kind : uint32_t { LITERAL = 0, BASE = 1, END_OF_BLOCK = 2, SUBTABLE = 3, INVALID = 4 };
 constexpr uint32_t entry(uint32_t value, uint32_t extra, uint32_t kind, uint32_t bits)
 {
@@ -131,6 +138,14 @@ struct BitReader {
             }
         }
     }
+    inline void refill_fast()       // the caller knows end - in >= 8 and 0 <= bits <= 63
+    {
+        uint64_t w;
+        memcpy(&w, in, 8);
+        buf |= w << bits;
+        in += (63 - bits) >> 3;
+        bits |= 56;
+    }
     inline uint32_t peek(int n) const { return (uint32_t)buf & ((1u << n) - 1u); }
     inline void drop(int n) { buf >>= n; bits -= n; }
     inline uint32_t take(int n) { const uint32_t v = peek(n); drop(n); return v; }
@@ -227,54 +242,90 @@ inline bool inflate(const uint8_t* in, size_t in_len, uint8_t* out, size_t out_l
             if (!read_dynamic_tables(br, dyn)) return false;
             t = &dyn;
         }
-        for (;;) {
-            br.refill();
-            uint32_t e = t->ll[br.peek(LL_BITS)];
-            if (((e >> 4) & 7u) == SUBTABLE) {
-                br.drop(LL_BITS);
-                e = t->ll[(e >> 16) + br.peek((int)((e >> 8) & 0xFFu))];
-            }
-            br.drop((int)(e & 15u));
-            uint32_t kind = (e >> 4) & 7u;
-            if (kind == LITERAL) {
-                if (out == out_end) return false;
-                *out++ = (uint8_t)(e >> 16);
-                // up to two more literals on the same refill (>= 41 bits are still there)
-                e = t->ll[br.peek(LL_BITS)];
-                if (((e >> 4) & 7u) != LITERAL || out == out_end) continue;
-                br.drop((int)(e & 15u));
-                *out++ = (uint8_t)(e >> 16);
-                e = t->ll[br.peek(LL_BITS)];
-                if (((e >> 4) & 7u) != LITERAL || out == out_end) continue;
-                br.drop((int)(e & 15u));
-                *out++ = (uint8_t)(e >> 16);
-                continue;
-            }
-            if (kind == END_OF_BLOCK) break;
-            if (kind != BASE) return false;
+        // length and distance of a match whose length code is `e` (already dropped); false = refuse
+        auto copy_match = [&](uint32_t e, bool roomy) -> bool {
             const uint32_t len = (e >> 16) + br.take((int)((e >> 8) & 0xFFu));
             br.refill();
             uint32_t d = t->d[br.peek(D_BITS)];
-            if (((d >> 4) & 7u) == SUBTABLE) {
+            if ((d & 0x70u) == (SUBTABLE << 4)) {
                 br.drop(D_BITS);
                 d = t->d[(d >> 16) + br.peek((int)((d >> 8) & 0xFFu))];
             }
             br.drop((int)(d & 15u));
-            if (((d >> 4) & 7u) != BASE) return false;
+            if ((d & 0x70u) != (BASE << 4)) return false;
             const uint32_t dist = (d >> 16) + br.take((int)((d >> 8) & 0xFFu));
             if (br.bits < 0 || dist > (size_t)(out - out0) || len > (size_t)(out_end - out)) return false;
             const uint8_t* src = out - dist;
             uint8_t* const stop = out + len;
-            if (dist >= 8 && (size_t)(out_end - out) >= len + 8) {      // word-wide, may overshoot by < 8
-                do {
-                    memcpy(out, src, 8);
-                    out += 8;
-                    src += 8;
-                } while (out < stop);
+            if (roomy || (size_t)(out_end - out) >= len + 16) {     // copies may overshoot by < 16
+                if (dist >= 16) {
+                    do {
+                        memcpy(out, src, 16);
+                        out += 16;
+                        src += 16;
+                    } while (out < stop);
+                } else if (dist >= 8) {
+                    do {
+                        memcpy(out, src, 8);
+                        out += 8;
+                        src += 8;
+                    } while (out < stop);
+                } else if (dist == 1) {
+                    memset(out, *src, len);
+                } else {
+                    do *out++ = *src++; while (out < stop);
+                }
                 out = stop;
             } else {
                 do *out++ = *src++; while (out < stop);
             }
+            return true;
+        };
+        auto is_literal = [](uint32_t e) { return (e & 0x70u) == (LITERAL << 4); };
+        constexpr size_t ROOM = 3 + 1 + 258 + 16 + 8;       // what one round of the fast loop may write, and more
+        for (bool end_of_block = false; !end_of_block;) {
+            // ---- fast: no bounds checks while >= 16 bytes of input and ROOM bytes of output are left
+            while ((size_t)(br.end - br.in) >= 16 && (size_t)(out_end - out) >= ROOM) {
+                br.refill_fast();                       // >= 56 bits: three first-level codes and a length fit
+                uint32_t e = t->ll[br.peek(LL_BITS)];
+                #define PMB_EMIT(e) do { *out++ = (uint8_t)((e) >> 16); br.drop((int)((e) & 15u)); } while (0)
+                if (is_literal(e)) {
+                    PMB_EMIT(e);
+                    e = t->ll[br.peek(LL_BITS)];
+                    if (is_literal(e)) {
+                        PMB_EMIT(e);
+                        e = t->ll[br.peek(LL_BITS)];
+                        if (is_literal(e)) { PMB_EMIT(e); continue; }
+                    }
+                }
+                if ((e & 0x70u) == (SUBTABLE << 4)) {
+                    br.drop(LL_BITS);
+                    e = t->ll[(e >> 16) + br.peek((int)((e >> 8) & 0xFFu))];
+                    if (is_literal(e)) { PMB_EMIT(e); continue; }
+                }
+                #undef PMB_EMIT
+                br.drop((int)(e & 15u));
+                const uint32_t kind = (e >> 4) & 7u;
+                if (kind == END_OF_BLOCK) { end_of_block = true; break; }
+                if (kind != BASE || !copy_match(e, true)) return false;
+            }
+            if (end_of_block) break;
+            // ---- checked: one symbol
+            br.refill();
+            uint32_t e = t->ll[br.peek(LL_BITS)];
+            if ((e & 0x70u) == (SUBTABLE << 4)) {
+                br.drop(LL_BITS);
+                e = t->ll[(e >> 16) + br.peek((int)((e >> 8) & 0xFFu))];
+            }
+            br.drop((int)(e & 15u));
+            const uint32_t kind = (e >> 4) & 7u;
+            if (kind == LITERAL) {
+                if (out == out_end) return false;
+                *out++ = (uint8_t)(e >> 16);
+                continue;
+            }
+            if (kind == END_OF_BLOCK) break;
+            if (kind != BASE || !copy_match(e, false)) return false;
         }
         if (br.bits < 0) return false;
     }
