@@ -104,6 +104,11 @@ uint64_t    pmio_bw_chrom_len(const pmio_bw *w, uint32_t i);
  * float32 values.  PMIO_ERR_KEY when the file has no such chromosome. */
 int  pmio_bw_intervals(pmio_bw *w, const char *chrom, float threshold, const uint32_t **begins,
                        const uint32_t **ends, const float **values, uint64_t *n);
+/* Decodes EVERY chromosome at `threshold` on `threads` threads (0 = all cores) and keeps the
+ * arrays in the handle: pmio_bw_intervals calls with the same threshold then return them without
+ * decoding (pointers valid until pmio_bw_close or the next prefetch).  What a run over all
+ * chromosomes (handler/mappability.py, the calculator's per-chromosome fetch) wants. */
+int  pmio_bw_prefetch(pmio_bw *w, float threshold, int threads);
 
 #ifdef __cplusplus
 }

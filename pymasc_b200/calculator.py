@@ -235,9 +235,14 @@ class CCBitArrayCalculator(object):
             arr = np.asarray(rows, dtype=np.int64).reshape(-1, 2)
             b, e = arr[:, 0], arr[:, 1]
         self._logging_info("Loading {} mappability to bit array...".format(chrom))
+        nbits = self.ref2genomelen[chrom] + self._array_extend_size
+        if (isinstance(b, np.ndarray) and isinstance(e, np.ndarray) and b.dtype == np.uint32 and e.dtype == np.uint32
+                and b.flags.c_contiguous and e.flags.c_contiguous):     # the native readers' arrays: no conversions
+            if e.size and int(e.max()) >= nbits:
+                raise PositionOutOfRange("mappability interval on %s beyond the bit array" % chrom)
+            return b, e
         b = np.ascontiguousarray(b, dtype=np.int64)
         e = np.ascontiguousarray(e, dtype=np.int64)
-        nbits = self.ref2genomelen[chrom] + self._array_extend_size
         if b.size and (b.min() < 0 or e.max() >= nbits):
             # the reference aborts on a BitArray assert here (bit_array.c:825)
             raise PositionOutOfRange("mappability interval on %s beyond the bit array" % chrom)

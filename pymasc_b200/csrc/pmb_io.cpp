@@ -827,6 +827,14 @@ struct pmio_bw {
     uint32_t uncompress_buf = 0;
     std::vector<uint32_t> begins, ends;
     std::vector<float> values;
+    // pmio_bw_prefetch: every chromosome's intervals at one threshold, by index into `names`
+    struct Track {
+        std::vector<uint32_t> begins, ends;
+        std::vector<float> values;
+    };
+    std::vector<Track> cache;
+    bool have_cache = false;
+    float cache_threshold = 0;
 };
 
 namespace {
@@ -931,6 +939,48 @@ extern "C" int pmio_bw_intervals(pmio_bw* w, const char* chrom, float threshold,
     return guarded([&]() { return bw_intervals_impl(w, chrom, threshold, begins, ends, values, n); });
 }
 
+// One data block (a bedGraph, varStep or fixedStep section of chromosome `id`) appended to B/E/V;
+// `buf` is the caller's inflate scratch.  Returns an error message, or nullptr.
+static const char* bw_decode_block(const pmio_bw* w, const Leaf& lf, uint32_t id, uint64_t chrom_len, float threshold,
+                                   std::vector<uint8_t>& buf, std::vector<uint32_t>& B, std::vector<uint32_t>& E,
+                                   std::vector<float>& V)
+{
+    if (!in_file(w, lf.off, lf.size)) return "BigWig data block outside the file";
+    const uint8_t* d = w->m.p + lf.off;
+    size_t dn = (size_t)lf.size;
+    if (w->uncompress_buf) {
+        if (buf.size() < std::max<size_t>(w->uncompress_buf, 64)) buf.resize(std::max<size_t>(w->uncompress_buf, 64));
+        uLongf got = (uLongf)buf.size();
+        int zr = uncompress(buf.data(), &got, d, (uLong)lf.size);
+        while (zr == Z_BUF_ERROR && buf.size() < (1u << 28)) {       // header understated the size
+            buf.resize(buf.size() * 2);
+            got = (uLongf)buf.size();
+            zr = uncompress(buf.data(), &got, d, (uLong)lf.size);
+        }
+        if (zr != Z_OK) return "BigWig data block does not inflate";
+        d = buf.data();
+        dn = (size_t)got;
+    }
+    if (dn < 24) return "short BigWig data block";
+    if (rd32(d) != id) return nullptr;
+    const uint32_t start0 = rd32(d + 4), step = rd32(d + 12), span = rd32(d + 16);
+    const uint32_t type = d[20], count = rd16(d + 22);
+    const size_t item = type == 1 ? 12 : type == 2 ? 8 : 4;
+    if (type < 1 || type > 3 || dn < 24 + count * item) return "corrupt BigWig data block";
+    for (uint32_t i = 0; i < count; i++) {
+        const uint8_t* it = d + 24 + i * item;
+        uint32_t s, e;
+        float v;
+        if (type == 1) { s = rd32(it); e = rd32(it + 4); v = rdf32(it + 8); }
+        else if (type == 2) { s = rd32(it); e = s + span; v = rdf32(it + 4); }
+        else { s = start0 + i * step; e = s + span; v = rdf32(it); }
+        if (s >= chrom_len || e == 0) continue;                  // intervals(chrom, 0, size): overlap only
+        if (threshold > 0 && !(v >= threshold)) continue;        // reader/bigwig.pyx:174-175
+        B.push_back(s); E.push_back(e); V.push_back(v);
+    }
+    return nullptr;
+}
+
 static int bw_intervals_impl(pmio_bw* w, const char* chrom, float threshold, const uint32_t** begins,
                              const uint32_t** ends, const float** values, uint64_t* n)
 {
@@ -938,50 +988,108 @@ static int bw_intervals_impl(pmio_bw* w, const char* chrom, float threshold, con
     for (; ci < w->names.size(); ci++)
         if (w->names[ci] == chrom) break;
     if (ci == w->names.size()) return fail(PMIO_ERR_KEY, chrom);
-    const uint32_t id = w->ids[ci];
-    const uint64_t chrom_len = w->lens[ci];
+    if (w->have_cache && w->cache_threshold == threshold) {      // decoded by pmio_bw_prefetch
+        const pmio_bw::Track& t = w->cache[ci];
+        if (begins) *begins = t.begins.data();
+        if (ends) *ends = t.ends.data();
+        if (values) *values = t.values.data();
+        if (n) *n = t.begins.size();
+        return PMIO_OK;
+    }
     std::vector<Leaf> leaves;
-    if (!walk_rtree(w, w->index_off + 48, id, leaves, 0)) return fail(PMIO_ERR_FORMAT, "corrupt BigWig index");
+    if (!walk_rtree(w, w->index_off + 48, w->ids[ci], leaves, 0)) return fail(PMIO_ERR_FORMAT, "corrupt BigWig index");
     w->begins.clear(); w->ends.clear(); w->values.clear();
     std::vector<uint8_t> buf;
-    for (const Leaf& lf : leaves) {
-        if (!in_file(w, lf.off, lf.size)) return fail(PMIO_ERR_FORMAT, "BigWig data block outside the file");
-        const uint8_t* d = w->m.p + lf.off;
-        size_t dn = (size_t)lf.size;
-        if (w->uncompress_buf) {
-            buf.resize(std::max<size_t>(w->uncompress_buf, 64));
-            uLongf got = (uLongf)buf.size();
-            int zr = uncompress(buf.data(), &got, d, (uLong)lf.size);
-            while (zr == Z_BUF_ERROR && buf.size() < (1u << 28)) {       // header understated the size
-                buf.resize(buf.size() * 2);
-                got = (uLongf)buf.size();
-                zr = uncompress(buf.data(), &got, d, (uLong)lf.size);
-            }
-            if (zr != Z_OK) return fail(PMIO_ERR_FORMAT, "BigWig data block does not inflate");
-            d = buf.data();
-            dn = (size_t)got;
-        }
-        if (dn < 24) return fail(PMIO_ERR_FORMAT, "short BigWig data block");
-        if (rd32(d) != id) continue;
-        const uint32_t start0 = rd32(d + 4), step = rd32(d + 12), span = rd32(d + 16);
-        const uint32_t type = d[20], count = rd16(d + 22);
-        const size_t item = type == 1 ? 12 : type == 2 ? 8 : 4;
-        if (type < 1 || type > 3 || dn < 24 + count * item) return fail(PMIO_ERR_FORMAT, "corrupt BigWig data block");
-        for (uint32_t i = 0; i < count; i++) {
-            const uint8_t* it = d + 24 + i * item;
-            uint32_t s, e;
-            float v;
-            if (type == 1) { s = rd32(it); e = rd32(it + 4); v = rdf32(it + 8); }
-            else if (type == 2) { s = rd32(it); e = s + span; v = rdf32(it + 4); }
-            else { s = start0 + i * step; e = s + span; v = rdf32(it); }
-            if (s >= chrom_len || e == 0) continue;                  // intervals(chrom, 0, size): overlap only
-            if (threshold > 0 && !(v >= threshold)) continue;        // reader/bigwig.pyx:174-175
-            w->begins.push_back(s); w->ends.push_back(e); w->values.push_back(v);
-        }
-    }
+    for (const Leaf& lf : leaves)
+        if (const char* err = bw_decode_block(w, lf, w->ids[ci], w->lens[ci], threshold, buf, w->begins, w->ends, w->values))
+            return fail(PMIO_ERR_FORMAT, err);
     if (begins) *begins = w->begins.data();
     if (ends) *ends = w->ends.data();
     if (values) *values = w->values.data();
     if (n) *n = w->begins.size();
     return PMIO_OK;
+}
+
+// Every chromosome at once: the data blocks of the whole file are decoded by a pool of threads
+// (runs of 32 consecutive blocks of a chromosome per task), then stitched per chromosome.
+static int bw_prefetch_impl(pmio_bw* w, float threshold, int threads)
+{
+    if (threads <= 0) threads = (int)std::max(1u, std::thread::hardware_concurrency());
+    threads = std::min(threads, 64);
+    struct Piece { size_t ci; size_t lo, hi; pmio_bw::Track out; };
+    auto now = []() { return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count(); };
+    const double t0 = now();
+    const size_t nc = w->names.size();
+    std::vector<std::vector<Leaf>> leaves(nc);
+    std::vector<Piece> pieces;
+    for (size_t ci = 0; ci < nc; ci++) {
+        if (!walk_rtree(w, w->index_off + 48, w->ids[ci], leaves[ci], 0)) return fail(PMIO_ERR_FORMAT, "corrupt BigWig index");
+        for (size_t lo = 0; lo < leaves[ci].size(); lo += 32)
+            pieces.push_back(Piece{ci, lo, std::min(lo + 32, leaves[ci].size()), {}});
+    }
+    std::atomic<size_t> next{0};
+    std::atomic<const char*> error{nullptr};
+    std::atomic<bool> oom{false};
+    auto decode = [&]() {
+        std::vector<uint8_t> buf;
+        try {
+            for (size_t k; (k = next.fetch_add(1)) < pieces.size() && !error.load();) {
+                Piece& pc = pieces[k];
+                pmio_bw::Track out;     // on this thread's stack: neighbouring pieces belong to other threads
+                for (size_t j = pc.lo; j < pc.hi; j++)
+                    if (const char* err = bw_decode_block(w, leaves[pc.ci][j], w->ids[pc.ci], w->lens[pc.ci], threshold, buf,
+                                                          out.begins, out.ends, out.values)) {
+                        error.store(err);
+                        return;
+                    }
+                pc.out = std::move(out);
+            }
+        } catch (...) {
+            oom.store(true);
+        }
+    };
+    const double t1 = now();
+    WorkerPool pool((size_t)threads - 1);
+    if (!pieces.empty()) pool.run(decode, pieces.size() - 1);
+    const double t2 = now();
+    if (oom.load()) throw std::bad_alloc();
+    if (error.load()) return fail(PMIO_ERR_FORMAT, error.load());
+    // pieces are in (chromosome, file) order
+    std::vector<size_t> first(nc, pieces.size());       // a chromosome without blocks: no pieces
+    for (size_t k = pieces.size(); k-- > 0;) first[pieces[k].ci] = k;
+    std::vector<pmio_bw::Track> cache(nc);
+    std::atomic<size_t> next_chrom{0};
+    auto stitch = [&]() {
+        try {
+            for (size_t ci; (ci = next_chrom.fetch_add(1)) < nc;) {
+                size_t total = 0;
+                for (size_t k = first[ci]; k < pieces.size() && pieces[k].ci == ci; k++) total += pieces[k].out.begins.size();
+                pmio_bw::Track& t = cache[ci];
+                t.begins.reserve(total); t.ends.reserve(total); t.values.reserve(total);
+                for (size_t k = first[ci]; k < pieces.size() && pieces[k].ci == ci; k++) {
+                    const pmio_bw::Track& o = pieces[k].out;
+                    t.begins.insert(t.begins.end(), o.begins.begin(), o.begins.end());
+                    t.ends.insert(t.ends.end(), o.ends.begin(), o.ends.end());
+                    t.values.insert(t.values.end(), o.values.begin(), o.values.end());
+                }
+            }
+        } catch (...) {
+            oom.store(true);
+        }
+    };
+    if (nc) pool.run(stitch, nc - 1);
+    if (oom.load()) throw std::bad_alloc();
+    if (getenv("PMIO_TIMING"))
+        fprintf(stderr, "[pmio bigwig] %d threads, %zu pieces: index %.4f s, decode %.4f s, stitch %.4f s\n", threads,
+                pieces.size(), t1 - t0, t2 - t1, now() - t2);
+    w->cache.swap(cache);
+    w->cache_threshold = threshold;
+    w->have_cache = true;
+    return PMIO_OK;
+}
+
+extern "C" int pmio_bw_prefetch(pmio_bw* w, float threshold, int threads)
+{
+    if (!w) return fail(PMIO_ERR_ARG, "null argument");
+    return guarded([&]() { return bw_prefetch_impl(w, threshold, threads); });
 }

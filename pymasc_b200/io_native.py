@@ -31,7 +31,7 @@ EXPORTS = (
     "pmio_last_error", "pmio_inflate_raw", "pmio_crc32", "pmio_bam_load", "pmio_bam_free", "pmio_bam_stats_get", "pmio_bam_n_refs",
     "pmio_bam_ref_name", "pmio_bam_ref_len", "pmio_bam_reads", "pmio_bam_packed", "pmio_bam_readlen_hist",
     "pmio_bw_open", "pmio_bw_close", "pmio_bw_n_chroms", "pmio_bw_chrom_name", "pmio_bw_chrom_len",
-    "pmio_bw_intervals",
+    "pmio_bw_intervals", "pmio_bw_prefetch",
 )
 PMIO_ERR_IO, PMIO_ERR_FORMAT, PMIO_ERR_ARG, PMIO_ERR_NOMEM, PMIO_ERR_KEY = -1, -2, -3, -4, -5
 
@@ -90,6 +90,7 @@ def load_library():
     L.pmio_bw_intervals.argtypes = [vp, ctypes.c_char_p, ctypes.c_float, u32pp, u32pp,
                                     ctypes.POINTER(ctypes.POINTER(ctypes.c_float)),
                                     ctypes.POINTER(ctypes.c_uint64)]
+    L.pmio_bw_prefetch.argtypes = [vp, ctypes.c_float, ctypes.c_int]
     _lib = L
     return L
 
@@ -339,6 +340,15 @@ class BigWigReader(object):
             _raise(self._L, rc)
         out = (_copy(b, n.value, np.uint32), _copy(e, n.value, np.uint32))
         return out + (_copy(v, n.value, np.float32),) if with_values else out
+
+    def prefetch(self, valfilter, threads=0):
+        """Decode every chromosome at `valfilter` now, on `threads` threads (0 = all cores);
+        fetch / fetch_arrays with that threshold then only copy."""
+        if self.closed:
+            raise ValueError("I/O operation on closed BigWig file")
+        rc = self._L.pmio_bw_prefetch(self._h, float(valfilter), int(threads))
+        if rc != 0:
+            _raise(self._L, rc)
 
     def fetch(self, valfilter, chrom):
         """List of (begin, end, value) tuples, as BigWigFileIterator yields them."""

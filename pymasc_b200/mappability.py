@@ -11,7 +11,8 @@ chromosome (``_feed_track``, mappability.pyx:176-205) on ``nworker`` processes. 
 chromosome that still has to be calculated becomes one ``PMB_FLAG_AUTOCORR`` job
 (include/pymasc_b200.h) and all of them run as ONE device batch: the track is gathered into bit
 arrays and the same run-edge kernels that produce ``popc(D_k)`` for MSCC count the
-autocorrelation.  ``nworker`` is accepted and ignored.  There is no CPU fallback.
+autocorrelation.  ``nworker`` only sizes the thread pool that decodes the BigWig (1, the
+reference's default, means all cores).  There is no CPU fallback.
 """
 import json
 import logging
@@ -159,6 +160,8 @@ class MappabilityHandler(object):
             rl = max(int(self.readlen), 2)      # only sizes the bit array; the counts do not depend on it
             jobs = []
             try:
+                if len(targets) > 1:
+                    reader.prefetch(self.MAPPABILITY_THRESHOLD, self.nworker if self.nworker > 1 else 0)
                 for c in targets:
                     logger.info("Calc {} mappable length...".format(c))
                     b, e = reader.fetch_arrays(self.MAPPABILITY_THRESHOLD, c)

@@ -254,6 +254,22 @@ def test_bigwig_errors(tmp_path):
         io_native.BigWigReader(p)
     with pytest.raises(ValueError):
         io_native.BigWigReader("-")
+    # a data block that does not inflate: the same ValueError from the per-chromosome decode
+    # and from a worker thread of the prefetch
+    p = str(tmp_path / "rotten.bw")
+    sections = [{"chrom_id": 0, "type": "bedgraph", "items": [(10 * i + 1000 * k, 10 * i + 1000 * k + 5, 1.0) for i in range(50)]}
+                for k in range(40)]
+    W.write_bigwig(p, [("c1", 100000)], sections)
+    blob = bytearray(open(p, "rb").read())
+    data_off = struct.unpack_from("<Q", blob, 16)[0]
+    blob[data_off + 8 + 300:data_off + 8 + 340] = b"\xff" * 40        # inside the zlib streams of the first blocks
+    open(p, "wb").write(bytes(blob))
+    r = io_native.BigWigReader(p)
+    with pytest.raises(ValueError):
+        r.fetch_arrays(1.0, "c1")
+    with pytest.raises(ValueError):
+        r.prefetch(1.0, 3)
+    r.close()
 
 
 # ----------------------------------------------------------------------------------- pipeline
@@ -578,3 +594,39 @@ def test_clmul_crc32_agrees_with_zlib_on_every_length():
             assert io_native.crc32(fill * n) == zlib.crc32(fill * n)
     assert io_native.crc32(b"123456789" * 8) == zlib.crc32(b"123456789" * 8)
     assert io_native.crc32(b"123456789", use_zlib=True) == 0xCBF43926      # the check value of CRC-32
+
+
+@pytest.mark.parametrize("threads", [1, 3, 0])
+def test_bigwig_prefetch_equals_the_per_chromosome_decode(tmp_path, threads):
+    """pmio_bw_prefetch decodes the whole file on a thread pool; fetch_arrays / fetch with the
+    prefetched threshold return the same arrays as the per-chromosome decode, another threshold
+    goes through the decoder again, a chromosome without data comes back empty."""
+    rng = np.random.default_rng(41)
+    chroms = [("c1", 500000), ("c2", 300000), ("empty", 1000), ("c3", 800000)]
+    sections = []
+    for ci, (_, ln) in enumerate(chroms):
+        if ci == 2:
+            continue
+        starts = np.sort(rng.choice(ln - 50, 4000, replace=False))
+        starts = starts[np.r_[True, np.diff(starts) > 40]]
+        for o in range(0, len(starts), 100):            # many blocks: several pieces per chromosome
+            items = [(int(s), int(s) + int(rng.integers(1, 40)), float(rng.choice([0.5, 1.0]))) for s in starts[o:o + 100]]
+            sections.append({"chrom_id": ci, "type": "bedgraph", "items": items})
+    p = str(tmp_path / "many.bigwig")
+    W.write_bigwig(p, chroms, sections, two_level=True)
+    plain, pre = io_native.BigWigReader(p), io_native.BigWigReader(p)
+    pre.prefetch(1.0, threads)
+    for name, _ in chroms:
+        a, b = plain.fetch_arrays(1.0, name, with_values=True), pre.fetch_arrays(1.0, name, with_values=True)
+        assert all(np.array_equal(x, y) for x, y in zip(a, b)) and (len(a[0]) > 0) == (name != "empty")
+        assert plain.fetch(1.0, name) == pre.fetch(1.0, name)
+        a, b = plain.fetch_arrays(0, name, with_values=True), pre.fetch_arrays(0, name, with_values=True)
+        assert all(np.array_equal(x, y) for x, y in zip(a, b)) and (len(a[0]) > len(pre.fetch_arrays(1.0, name)[0]) or name == "empty")
+    pre.prefetch(0, threads)                              # replaces the cache
+    assert all(np.array_equal(x, y) for x, y in zip(plain.fetch_arrays(0, "c3"), pre.fetch_arrays(0, "c3")))
+    with pytest.raises(KeyError):
+        pre.fetch_arrays(0, "nope")
+    pre.close()
+    with pytest.raises(ValueError):
+        pre.prefetch(1.0)
+    plain.close()
