@@ -44,6 +44,11 @@ const char *pmio_last_error(void);
  * through first) or by zlib (use_zlib = 1; the fallback for anything the former refuses).
  * PMIO_ERR_FORMAT when the stream does not decode to that size. */
 int pmio_inflate_raw(const uint8_t *in, uint64_t in_len, uint8_t *out, uint64_t out_len, int use_zlib);
+/* Two independent raw-DEFLATE streams decoded together by the library's own decoder (their
+ * decode loops take turns; what pairs of BGZF blocks go through).  ok[i] = 1 when stream i decoded
+ * to exactly out_len[i] bytes.  Always PMIO_OK unless an argument is null. */
+int pmio_inflate_raw2(const uint8_t *const in[2], const uint64_t in_len[2], uint8_t *const out[2],
+                      const uint64_t out_len[2], int ok[2]);
 
 /* CRC-32 (gzip) of a buffer, by carry-less multiplication where the CPU has it (use_zlib = 0;
  * pymasc_b200/csrc/pmb_crc32.h -- what checks every BGZF block) or by zlib's crc32 (use_zlib = 1). */

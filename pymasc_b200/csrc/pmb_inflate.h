@@ -5,7 +5,7 @@
 // entry, a main loop that runs without bounds checks while input and output have room to spare
 // and takes up to three literals per refill (BAM payloads -- names, packed bases, qualities --
 // are mostly literals; the ends of the block go through a checked loop, one symbol at a time),
-// word-wide match copies.  (Tried and dropped: first-level slots holding two literals -- the
+// word-wide match copies; two streams can be decoded together (inflate2).  (Tried and dropped: first-level slots holding two literals -- the
 // longer table build and the variable advance cost more than the shorter dependency chain won.)
 //
 // It is an accelerator, not the authority: the caller knows the exact inflated size (ISIZE) and
@@ -208,129 +208,274 @@ inline bool read_dynamic_tables(BitReader& br, Tables& t)
            build_table(lens + hlit, hdist, D_BITS, t.d, D_TABLE, d_payload);
 }
 
-// Inflate in[0, in_len) into exactly out[0, out_len).  false: not decoded (use zlib).
-inline bool inflate(const uint8_t* in, size_t in_len, uint8_t* out, size_t out_len)
+// ---- the decoder.  State of one stream; `prepare` walks block headers, stored blocks and the
+// checked one-symbol loop until the stream stands inside a Huffman block with room for the fast
+// loop (or is finished / refused); `fast_round` is one refill's worth of that loop.  Two streams
+// can take turns in it (inflate2): the decode of a symbol is one dependency chain -- table load,
+// shift of the bit buffer by the code length just loaded, mask, next load -- and two independent
+// chains overlap in the out-of-order core.
+#define PMB_INLINE inline __attribute__((always_inline))
+
+// what the fast loop keeps in registers
+struct Hot {
+    uint64_t buf;
+    int bits;
+    const uint8_t* in;
+    uint8_t* out;
+};
+
+constexpr size_t FAST_IN = 16;                      // input bytes one round may read past `in`
+constexpr size_t FAST_OUT = 3 + 1 + 258 + 16 + 8;   // output bytes one round may write, and more
+
+enum Round { MORE = 0, BLOCK_END = 1, REFUSED = 2 };
+
+// One round: up to three literals, or a literal from a second-level table, or a match, or the
+// end of the block.  No bounds checks: the caller guarantees FAST_IN / FAST_OUT.
+static PMB_INLINE Round fast_round(Hot& h, const Tables* t, const uint8_t* out0)
 {
-    BitReader br{in, in + in_len};
-    uint8_t* const out0 = out;
-    uint8_t* const out_end = out + out_len;
+    auto refill = [&]() {
+        uint64_t w;
+        memcpy(&w, h.in, 8);
+        h.buf |= w << h.bits;
+        h.in += (63 - h.bits) >> 3;
+        h.bits |= 56;
+    };
+    auto drop = [&](uint32_t n) { h.buf >>= n; h.bits -= (int)n; };
+    auto take = [&](uint32_t n) { const uint32_t v = (uint32_t)h.buf & ((1u << n) - 1u); drop(n); return v; };
+    auto is_literal = [](uint32_t e) { return (e & 0x70u) == (LITERAL << 4); };
+    constexpr uint32_t LL_MASK = (1u << LL_BITS) - 1u, D_MASK = (1u << D_BITS) - 1u;
+    refill();                                       // >= 56 bits: three first-level codes and a length fit
+    uint32_t e = t->ll[(uint32_t)h.buf & LL_MASK];
+    if (is_literal(e)) {
+        *h.out++ = (uint8_t)(e >> 16); drop(e & 15u);
+        e = t->ll[(uint32_t)h.buf & LL_MASK];
+        if (is_literal(e)) {
+            *h.out++ = (uint8_t)(e >> 16); drop(e & 15u);
+            e = t->ll[(uint32_t)h.buf & LL_MASK];
+            if (is_literal(e)) { *h.out++ = (uint8_t)(e >> 16); drop(e & 15u); return MORE; }
+        }
+    }
+    if ((e & 0x70u) == (SUBTABLE << 4)) {
+        drop(LL_BITS);
+        e = t->ll[(e >> 16) + ((uint32_t)h.buf & ((1u << ((e >> 8) & 0xFFu)) - 1u))];
+        if (is_literal(e)) { *h.out++ = (uint8_t)(e >> 16); drop(e & 15u); return MORE; }
+    }
+    drop(e & 15u);
+    const uint32_t kind = (e >> 4) & 7u;
+    if (kind == END_OF_BLOCK) return BLOCK_END;
+    if (kind != BASE) return REFUSED;
+    const uint32_t len = (e >> 16) + take((e >> 8) & 0xFFu);
+    refill();
+    uint32_t d = t->d[(uint32_t)h.buf & D_MASK];
+    if ((d & 0x70u) == (SUBTABLE << 4)) {
+        drop(D_BITS);
+        d = t->d[(d >> 16) + ((uint32_t)h.buf & ((1u << ((d >> 8) & 0xFFu)) - 1u))];
+    }
+    drop(d & 15u);
+    if ((d & 0x70u) != (BASE << 4)) return REFUSED;
+    const uint32_t dist = (d >> 16) + take((d >> 8) & 0xFFu);
+    if (dist > (size_t)(h.out - out0)) return REFUSED;
+    const uint8_t* src = h.out - dist;
+    uint8_t* const stop = h.out + len;
+    if (dist >= 16) {                               // copies may overshoot by < 16
+        do {
+            memcpy(h.out, src, 16);
+            h.out += 16;
+            src += 16;
+        } while (h.out < stop);
+    } else if (dist >= 8) {
+        do {
+            memcpy(h.out, src, 8);
+            h.out += 8;
+            src += 8;
+        } while (h.out < stop);
+    } else if (dist == 1) {
+        memset(h.out, *src, len);
+    } else {
+        do *h.out++ = *src++; while (h.out < stop);
+    }
+    h.out = stop;
+    return MORE;
+}
+
+struct Decoder {
+    BitReader br{nullptr, nullptr};
+    uint8_t* out0 = nullptr;
+    uint8_t* out = nullptr;
+    uint8_t* out_end = nullptr;
+    const Tables* t = nullptr;
+    bool last = false;          // the block being decoded is the final one
+    bool in_block = false;      // inside a Huffman block (t is its tables)
+    bool done = false;          // the stream ended exactly at out_end
+    bool refused = false;
     Tables dyn;
-    for (bool last = false; !last;) {
+
+    void init(const uint8_t* in, size_t in_len, uint8_t* o, size_t out_len)
+    {
+        br = BitReader{in, in + in_len};
+        out0 = out = o;
+        out_end = o + out_len;
+        last = in_block = done = refused = false;
+    }
+    bool fast_ok() const { return (size_t)(br.end - br.in) >= FAST_IN && (size_t)(out_end - out) >= FAST_OUT; }
+    Hot hot() const { return Hot{br.buf, br.bits, br.in, out}; }
+    void keep(const Hot& h) { br.buf = h.buf; br.bits = h.bits; br.in = h.in; out = h.out; }
+    bool live() const { return !done && !refused; }
+    void end_block() { in_block = false; }
+
+    // block header (RFC 1951 3.2.3); a stored block is copied here
+    void open_block()
+    {
         br.refill();
         last = br.take(1) != 0;
         const uint32_t type = br.take(2);
-        if (br.bits < 0) return false;
+        if (br.bits < 0 || type == 3) { refused = true; return; }
         if (type == 0) {                // stored: back to a byte boundary, LEN, ~LEN, bytes
             br.drop(br.bits & 7);
             br.refill();
-            if (br.bits < 32) return false;
+            if (br.bits < 32) { refused = true; return; }
             const uint32_t len = br.take(16), nlen = br.take(16);
-            if ((len ^ nlen) != 0xFFFFu) return false;
-            // hand the bytes still in the bit buffer back to the input
-            br.in -= br.bits >> 3;
+            if ((len ^ nlen) != 0xFFFFu) { refused = true; return; }
+            br.in -= br.bits >> 3;      // hand the bytes still in the bit buffer back to the input
             br.buf = 0;
             br.bits = 0;
-            if ((size_t)(br.end - br.in) < len || (size_t)(out_end - out) < len) return false;
+            if ((size_t)(br.end - br.in) < len || (size_t)(out_end - out) < len) { refused = true; return; }
             memcpy(out, br.in, len);
             br.in += len;
             out += len;
-            continue;
+            return;
         }
-        if (type == 3) return false;
-        const Tables* t = &fixed_tables();
+        t = &fixed_tables();
         if (type == 2) {
-            if (!read_dynamic_tables(br, dyn)) return false;
+            if (!read_dynamic_tables(br, dyn)) { refused = true; return; }
             t = &dyn;
         }
-        // length and distance of a match whose length code is `e` (already dropped); false = refuse
-        auto copy_match = [&](uint32_t e, bool roomy) -> bool {
-            const uint32_t len = (e >> 16) + br.take((int)((e >> 8) & 0xFFu));
-            br.refill();
-            uint32_t d = t->d[br.peek(D_BITS)];
-            if ((d & 0x70u) == (SUBTABLE << 4)) {
-                br.drop(D_BITS);
-                d = t->d[(d >> 16) + br.peek((int)((d >> 8) & 0xFFu))];
-            }
-            br.drop((int)(d & 15u));
-            if ((d & 0x70u) != (BASE << 4)) return false;
-            const uint32_t dist = (d >> 16) + br.take((int)((d >> 8) & 0xFFu));
-            if (br.bits < 0 || dist > (size_t)(out - out0) || len > (size_t)(out_end - out)) return false;
-            const uint8_t* src = out - dist;
-            uint8_t* const stop = out + len;
-            if (roomy || (size_t)(out_end - out) >= len + 16) {     // copies may overshoot by < 16
-                if (dist >= 16) {
-                    do {
-                        memcpy(out, src, 16);
-                        out += 16;
-                        src += 16;
-                    } while (out < stop);
-                } else if (dist >= 8) {
-                    do {
-                        memcpy(out, src, 8);
-                        out += 8;
-                        src += 8;
-                    } while (out < stop);
-                } else if (dist == 1) {
-                    memset(out, *src, len);
-                } else {
-                    do *out++ = *src++; while (out < stop);
+        in_block = true;
+    }
+
+    // one symbol with every bound checked (the ends of the input and of the output)
+    void checked_symbol()
+    {
+        br.refill();
+        uint32_t e = t->ll[br.peek(LL_BITS)];
+        if ((e & 0x70u) == (SUBTABLE << 4)) {
+            br.drop(LL_BITS);
+            e = t->ll[(e >> 16) + br.peek((int)((e >> 8) & 0xFFu))];
+        }
+        br.drop((int)(e & 15u));
+        const uint32_t kind = (e >> 4) & 7u;
+        if (kind == LITERAL) {
+            if (out == out_end) { refused = true; return; }
+            *out++ = (uint8_t)(e >> 16);
+            return;
+        }
+        if (kind == END_OF_BLOCK) {
+            if (br.bits < 0) refused = true;
+            end_block();
+            return;
+        }
+        if (kind != BASE) { refused = true; return; }
+        const uint32_t len = (e >> 16) + br.take((int)((e >> 8) & 0xFFu));
+        br.refill();
+        uint32_t d = t->d[br.peek(D_BITS)];
+        if ((d & 0x70u) == (SUBTABLE << 4)) {
+            br.drop(D_BITS);
+            d = t->d[(d >> 16) + br.peek((int)((d >> 8) & 0xFFu))];
+        }
+        br.drop((int)(d & 15u));
+        if ((d & 0x70u) != (BASE << 4)) { refused = true; return; }
+        const uint32_t dist = (d >> 16) + br.take((int)((d >> 8) & 0xFFu));
+        if (br.bits < 0 || dist > (size_t)(out - out0) || len > (size_t)(out_end - out)) { refused = true; return; }
+        const uint8_t* src = out - dist;
+        for (uint8_t* const stop = out + len; out < stop;) *out++ = *src++;
+    }
+
+    // until the stream stands in a Huffman block with room for the fast loop, or is over
+    void prepare()
+    {
+        while (live()) {
+            if (!in_block) {
+                if (last) {
+                    if (out == out_end && br.bits >= 0) done = true;
+                    else refused = true;
+                    return;
                 }
-                out = stop;
-            } else {
-                do *out++ = *src++; while (out < stop);
-            }
-            return true;
-        };
-        auto is_literal = [](uint32_t e) { return (e & 0x70u) == (LITERAL << 4); };
-        constexpr size_t ROOM = 3 + 1 + 258 + 16 + 8;       // what one round of the fast loop may write, and more
-        for (bool end_of_block = false; !end_of_block;) {
-            // ---- fast: no bounds checks while >= 16 bytes of input and ROOM bytes of output are left
-            while ((size_t)(br.end - br.in) >= 16 && (size_t)(out_end - out) >= ROOM) {
-                br.refill_fast();                       // >= 56 bits: three first-level codes and a length fit
-                uint32_t e = t->ll[br.peek(LL_BITS)];
-                #define PMB_EMIT(e) do { *out++ = (uint8_t)((e) >> 16); br.drop((int)((e) & 15u)); } while (0)
-                if (is_literal(e)) {
-                    PMB_EMIT(e);
-                    e = t->ll[br.peek(LL_BITS)];
-                    if (is_literal(e)) {
-                        PMB_EMIT(e);
-                        e = t->ll[br.peek(LL_BITS)];
-                        if (is_literal(e)) { PMB_EMIT(e); continue; }
-                    }
-                }
-                if ((e & 0x70u) == (SUBTABLE << 4)) {
-                    br.drop(LL_BITS);
-                    e = t->ll[(e >> 16) + br.peek((int)((e >> 8) & 0xFFu))];
-                    if (is_literal(e)) { PMB_EMIT(e); continue; }
-                }
-                #undef PMB_EMIT
-                br.drop((int)(e & 15u));
-                const uint32_t kind = (e >> 4) & 7u;
-                if (kind == END_OF_BLOCK) { end_of_block = true; break; }
-                if (kind != BASE || !copy_match(e, true)) return false;
-            }
-            if (end_of_block) break;
-            // ---- checked: one symbol
-            br.refill();
-            uint32_t e = t->ll[br.peek(LL_BITS)];
-            if ((e & 0x70u) == (SUBTABLE << 4)) {
-                br.drop(LL_BITS);
-                e = t->ll[(e >> 16) + br.peek((int)((e >> 8) & 0xFFu))];
-            }
-            br.drop((int)(e & 15u));
-            const uint32_t kind = (e >> 4) & 7u;
-            if (kind == LITERAL) {
-                if (out == out_end) return false;
-                *out++ = (uint8_t)(e >> 16);
+                open_block();
                 continue;
             }
-            if (kind == END_OF_BLOCK) break;
-            if (kind != BASE || !copy_match(e, false)) return false;
+            if (fast_ok()) return;
+            checked_symbol();
         }
-        if (br.bits < 0) return false;
     }
-    return out == out_end;
+
+    // the rest of the stream, alone
+    bool finish()
+    {
+        for (;;) {
+            prepare();
+            if (!live()) return done;
+            Hot h = hot();
+            Round r = MORE;
+            // (locals: the byte stores of the loop could alias anything reachable from `this`)
+            const uint8_t* const in_lim = br.end - FAST_IN;
+            uint8_t* const out_lim = out_end - FAST_OUT;
+            const Tables* const tables = t;
+            const uint8_t* const base = out0;
+            while (r == MORE && h.in <= in_lim && h.out <= out_lim) r = fast_round(h, tables, base);
+            keep(h);
+            if (r == REFUSED) return false;
+            if (r == BLOCK_END) end_block();
+        }
+    }
+};
+
+// Inflate in[0, in_len) into exactly out[0, out_len).  false: not decoded (use zlib).
+inline bool inflate(const uint8_t* in, size_t in_len, uint8_t* out, size_t out_len)
+{
+    Decoder d;
+    d.init(in, in_len, out, out_len);
+    return d.finish();
 }
+
+// Two independent streams at once (two BGZF blocks): their fast loops take turns, round by
+// round, so that the two dependency chains overlap.  ok[i]: stream i decoded.
+inline void inflate2(const uint8_t* const in[2], const size_t in_len[2], uint8_t* const out[2], const size_t out_len[2],
+                     bool ok[2])
+{
+    Decoder a, b;
+    a.init(in[0], in_len[0], out[0], out_len[0]);
+    b.init(in[1], in_len[1], out[1], out_len[1]);
+    for (;;) {
+        a.prepare();
+        b.prepare();
+        if (!a.live() || !b.live()) break;
+        Hot ha = a.hot(), hb = b.hot();
+        Round ra = MORE, rb = MORE;
+        const uint8_t* const a_in_lim = a.br.end - FAST_IN;
+        const uint8_t* const b_in_lim = b.br.end - FAST_IN;
+        uint8_t* const a_out_lim = a.out_end - FAST_OUT;
+        uint8_t* const b_out_lim = b.out_end - FAST_OUT;
+        const Tables* const ta = a.t;
+        const Tables* const tb = b.t;
+        const uint8_t* const a_base = a.out0;
+        const uint8_t* const b_base = b.out0;
+        while (ha.in <= a_in_lim && ha.out <= a_out_lim && hb.in <= b_in_lim && hb.out <= b_out_lim) {
+            ra = fast_round(ha, ta, a_base);
+            rb = fast_round(hb, tb, b_base);
+            if (ra | rb) break;
+        }
+        a.keep(ha);
+        b.keep(hb);
+        if (ra == REFUSED) a.refused = true;
+        if (rb == REFUSED) b.refused = true;
+        if (ra == BLOCK_END) a.end_block();
+        if (rb == BLOCK_END) b.end_block();
+    }
+    ok[0] = a.refused ? false : a.finish();
+    ok[1] = b.refused ? false : b.finish();
+}
+
+#undef PMB_INLINE
 
 }  // namespace pmb_inflate
 #endif

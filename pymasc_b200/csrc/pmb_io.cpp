@@ -109,6 +109,21 @@ bool inflate_block(const uint8_t* src, size_t csize, uint8_t* dst, size_t isize,
     return zlib_inflate_raw(src, csize, dst, isize) && crc_ok();
 }
 
+// Two blocks at once: their decode loops take turns (pmb_inflate::inflate2), each is CRC-checked,
+// and one the fast decoder refuses or gets wrong goes through zlib like a single block.
+bool inflate_block_pair(const uint8_t* const src[2], const size_t csize[2], uint8_t* const dst[2], const size_t isize[2],
+                        const uint32_t crc[2])
+{
+    static const bool zlib_only = getenv("PMIO_ZLIB_ONLY") != nullptr;
+    bool ok[2] = {false, false};
+    if (!zlib_only && isize[0] && isize[1]) pmb_inflate::inflate2(src, csize, dst, isize, ok);
+    for (int i = 0; i < 2; i++) {
+        if (ok[i] && pmb_crc32::compute(dst[i], isize[i], true) == crc[i]) continue;
+        if (!inflate_block(src[i], csize[i], dst[i], isize[i], crc[i])) return false;
+    }
+    return true;
+}
+
 struct Block { size_t data_off; uint32_t csize, isize, crc; size_t out_off; };
 
 // Threads that live as long as one pmio_bam_load: a BAM file is decoded in many small batches
@@ -176,6 +191,18 @@ extern "C" int pmio_inflate_raw(const uint8_t* in, uint64_t in_len, uint8_t* out
     const bool ok = use_zlib ? zlib_inflate_raw(in, (size_t)in_len, out, (size_t)out_len)
                              : pmb_inflate::inflate(in, (size_t)in_len, out, (size_t)out_len);
     return ok ? PMIO_OK : fail(PMIO_ERR_FORMAT, "stream does not inflate to the given size");
+}
+
+extern "C" int pmio_inflate_raw2(const uint8_t* const in[2], const uint64_t in_len[2], uint8_t* const out[2],
+                                 const uint64_t out_len[2], int ok[2])
+{
+    if (!in || !in_len || !out || !out_len || !ok || !in[0] || !in[1] || !out[0] || !out[1]) return fail(PMIO_ERR_ARG, "null argument");
+    const size_t il[2] = {(size_t)in_len[0], (size_t)in_len[1]}, ol[2] = {(size_t)out_len[0], (size_t)out_len[1]};
+    bool good[2];
+    pmb_inflate::inflate2(in, il, out, ol, good);
+    ok[0] = good[0];
+    ok[1] = good[1];
+    return PMIO_OK;
 }
 
 extern "C" uint32_t pmio_crc32(const uint8_t* data, uint64_t len, int use_zlib)
@@ -647,7 +674,16 @@ static int bam_load_impl(const char* path, int mapq_criteria, int threads, pmio_
                 Share& s = shares[i];
                 try {       // an exception must not leave a worker thread
                     const double t0 = timing ? now() : 0;
-                    for (size_t j = s.blk_lo; j < s.blk_hi; j++) {
+                    size_t j = s.blk_lo;
+                    for (; j + 1 < s.blk_hi; j += 2) {          // in pairs: two decode chains overlap
+                        const Block &k0 = blocks[j], &k1 = blocks[j + 1];
+                        const uint8_t* const src[2] = {m.p + k0.data_off, m.p + k1.data_off};
+                        const size_t csize[2] = {k0.csize, k1.csize}, isize[2] = {k0.isize, k1.isize};
+                        uint8_t* const dst[2] = {buf.p + k0.out_off, buf.p + k1.out_off};
+                        const uint32_t crc[2] = {k0.crc, k1.crc};
+                        if (!inflate_block_pair(src, csize, dst, isize, crc)) { failure.store(1); return; }
+                    }
+                    for (; j < s.blk_hi; j++) {
                         const Block& k = blocks[j];
                         if (!inflate_block(m.p + k.data_off, k.csize, buf.p + k.out_off, k.isize, k.crc)) { failure.store(1); return; }
                     }

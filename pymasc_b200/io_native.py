@@ -28,7 +28,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("PYMASC_IO_LIB") or os.path.join(_HERE, "libpymasc_io.so")
 
 EXPORTS = (
-    "pmio_last_error", "pmio_inflate_raw", "pmio_crc32", "pmio_bam_load", "pmio_bam_free", "pmio_bam_stats_get", "pmio_bam_n_refs",
+    "pmio_last_error", "pmio_inflate_raw", "pmio_inflate_raw2", "pmio_crc32", "pmio_bam_load", "pmio_bam_free", "pmio_bam_stats_get", "pmio_bam_n_refs",
     "pmio_bam_ref_name", "pmio_bam_ref_len", "pmio_bam_reads", "pmio_bam_packed", "pmio_bam_readlen_hist",
     "pmio_bw_open", "pmio_bw_close", "pmio_bw_n_chroms", "pmio_bw_chrom_name", "pmio_bw_chrom_len",
     "pmio_bw_intervals", "pmio_bw_prefetch",
@@ -58,6 +58,7 @@ def load_library():
     u32pp = ctypes.POINTER(ctypes.POINTER(ctypes.c_uint32))
     L.pmio_last_error.restype = ctypes.c_char_p
     L.pmio_inflate_raw.argtypes = [ctypes.c_char_p, ctypes.c_uint64, ctypes.c_char_p, ctypes.c_uint64, ctypes.c_int]
+    L.pmio_inflate_raw2.argtypes = [ctypes.c_void_p] * 5
     L.pmio_crc32.argtypes = [ctypes.c_char_p, ctypes.c_uint64, ctypes.c_int]
     L.pmio_crc32.restype = ctypes.c_uint32
     L.pmio_bam_load.argtypes = [ctypes.c_char_p, ctypes.c_int, ctypes.c_int, vpp]
@@ -104,6 +105,24 @@ def inflate_raw(data, out_len, use_zlib=False):
     if rc != 0:
         _raise(L, rc)
     return out.raw[:int(out_len)]
+
+
+def inflate_raw2(data_a, out_len_a, data_b, out_len_b):
+    """Two raw-DEFLATE streams through the library's two-stream decoder: a pair of bytes objects,
+    None where a stream was refused."""
+    L = load_library()
+    datas = (bytes(data_a), bytes(data_b))
+    lens = (int(out_len_a), int(out_len_b))
+    outs = [ctypes.create_string_buffer(max(n, 1)) for n in lens]
+    ins = (ctypes.c_char_p * 2)(*datas)
+    in_len = (ctypes.c_uint64 * 2)(len(datas[0]), len(datas[1]))
+    out_ptr = (ctypes.c_void_p * 2)(ctypes.addressof(outs[0]), ctypes.addressof(outs[1]))
+    out_len = (ctypes.c_uint64 * 2)(*lens)
+    ok = (ctypes.c_int * 2)(0, 0)
+    rc = L.pmio_inflate_raw2(ins, in_len, out_ptr, out_len, ok)
+    if rc != 0:
+        _raise(L, rc)
+    return tuple(outs[i].raw[:lens[i]] if ok[i] else None for i in range(2))
 
 
 def crc32(data, use_zlib=False):

@@ -630,3 +630,42 @@ def test_bigwig_prefetch_equals_the_per_chromosome_decode(tmp_path, threads):
     with pytest.raises(ValueError):
         pre.prefetch(1.0)
     plain.close()
+
+
+def test_two_stream_inflate_decodes_each_stream_on_its_own_terms():
+    """pmb_inflate::inflate2 interleaves the decode loops of two streams (pairs of BGZF blocks):
+    every combination of block types and sizes comes out as zlib wrote it, and a corrupt or
+    truncated partner does not disturb the other stream."""
+    import zlib
+    payloads = list(_inflate_payloads())
+    rng = np.random.default_rng(51)
+    streams = []
+    for k, data in enumerate(payloads):
+        level = (0, 1, 6, 9)[k % 4]
+        strategy = (zlib.Z_DEFAULT_STRATEGY, zlib.Z_FIXED, zlib.Z_HUFFMAN_ONLY, zlib.Z_RLE)[(k // 4) % 4]
+        streams.append((_raw_deflate(data, level, strategy), data))
+    n = 0
+    for i in range(len(streams)):
+        for j in rng.choice(len(streams), 6, replace=False):
+            (ca, a), (cb, b) = streams[i], streams[int(j)]
+            assert io_native.inflate_raw2(ca, len(a), cb, len(b)) == (a, b)
+            n += 1
+    assert n > 150
+    (ca, a), (cb, b) = [(c, d) for c, d in streams if len(d) > 20000 and 2000 < len(c) < len(d) // 2][:2]
+    assert io_native.inflate_raw2(ca, len(a), cb[:len(cb) // 2], len(b)) == (a, None)
+    assert io_native.inflate_raw2(ca[:100], len(a), cb, len(b)) == (None, b)
+    assert io_native.inflate_raw2(ca, len(a) + 1, cb, len(b) - 1) == (None, None)
+    refused = 0
+    for _ in range(300):
+        bad = bytearray(ca)
+        bad[int(rng.integers(len(bad)))] ^= 1 << int(rng.integers(8))
+        got_a, got_b = io_native.inflate_raw2(bytes(bad), len(a), cb, len(b))
+        assert got_b == b
+        if got_a is None:
+            refused += 1
+        else:
+            try:
+                assert got_a == io_native.inflate_raw(bytes(bad), len(a), use_zlib=True)
+            except ValueError:
+                pass
+    assert refused > 30
