@@ -41,13 +41,6 @@ struct Tables {
     uint32_t d[D_TABLE];
 };
 
-inline uint32_t reverse_bits(uint32_t code, int len)
-{
-    uint32_t r = 0;
-    for (int i = 0; i < len; i++) r |= ((code >> i) & 1u) << (len - 1 - i);
-    return r;
-}
-
 // symbol -> entry payload (value, extra, kind) of the two alphabets
 inline uint32_t ll_payload(int sym)
 {
@@ -73,47 +66,79 @@ inline uint32_t d_payload(int sym)
 // longer codes share a second-level table per `first`-bit prefix, all of 2^(longest-first)
 // slots.  Returns false for an over-subscribed code; an incomplete one leaves INVALID slots
 // (legal for a single distance code, harmless otherwise: hitting one fails the block).
+//
+// The symbols are taken in code order (by length, then by symbol: a counting sort), so that
+//  * the bit-reversed code word is kept incrementally -- +1 on a mirrored number is "clear the
+//    set bits from the top, set the first clear one" -- and stays the same number when the length
+//    grows (the zeros appended to the code go to the top of its mirror image);
+//  * the first level is built by doubling: a code of l bits is stored ONCE in the table of 2^l
+//    slots that exists when its length is reached, and every step to the next length copies the
+//    table onto its upper half (a slot's index gains a high bit that the code does not look at).
+//    No per-symbol fill loops, whose trip counts the branch predictor cannot learn;
+//  * codes longer than `first` bits arrive grouped by their first-level prefix, so a second-level
+//    table is opened whenever the prefix changes.
 template <class Payload>
 inline bool build_table(const uint8_t* lens, int n_syms, int first, uint32_t* table, int capacity, Payload payload)
 {
     int count[MAX_LEN + 1] = {0};
     for (int s = 0; s < n_syms; s++) count[lens[s]]++;
     count[0] = 0;
-    int longest = 0;
-    for (int l = 1; l <= MAX_LEN; l++)
-        if (count[l]) longest = l;
-    uint32_t next_code[MAX_LEN + 2] = {0};
-    uint32_t code = 0;
+    int longest = 0, start[MAX_LEN + 2];
     long long space = 1;
+    start[1] = 0;
     for (int l = 1; l <= MAX_LEN; l++) {
-        code = (code + (uint32_t)count[l - 1]) << 1;
-        next_code[l] = code;
+        if (count[l]) longest = l;
+        start[l + 1] = start[l] + count[l];
         space = space * 2 - count[l];
         if (space < 0) return false;
     }
+    uint16_t sorted[288];
+    {
+        int at[MAX_LEN + 1];
+        for (int l = 1; l <= MAX_LEN; l++) at[l] = start[l];
+        for (int s = 0; s < n_syms; s++)
+            if (lens[s]) sorted[at[lens[s]]++] = (uint16_t)s;
+    }
+    const bool complete = space == 0;           // then every slot gets written below
     const int size1 = 1 << first;
-    for (int i = 0; i < size1; i++) table[i] = entry(0, 0, INVALID, 1);
+    if (!complete)
+        for (int i = 0; i < size1; i++) table[i] = entry(0, 0, INVALID, 1);
+    uint32_t rev = 0;                           // mirror image of the next code word
+    auto next_code = [&rev](int len) {
+        const uint32_t all = (1u << len) - 1u;
+        if (rev == all) { rev = 0; return; }    // that was the last code of a complete code
+        const uint32_t bit = 1u << (31 - __builtin_clz(rev ^ all));
+        rev = (rev & (bit - 1u)) | bit;
+    };
+    int k = 0, size = 1;
+    for (int len = 1; len <= first; len++) {
+        memcpy(table + size, table, (size_t)size * sizeof(uint32_t));
+        size *= 2;
+        for (int c = 0; c < count[len]; c++, k++) {
+            table[rev] = payload((int)sorted[k]) | (uint32_t)len;
+            next_code(len);
+        }
+    }
     const int sub_bits = longest > first ? longest - first : 0;
     int used = size1;
-    for (int s = 0; s < n_syms; s++) {
-        const int l = lens[s];
-        if (!l) continue;
-        const uint32_t rev = reverse_bits(next_code[l]++, l);
-        if (l <= first) {
-            const uint32_t e = payload(s) | (uint32_t)l;
-            for (uint32_t i = rev; i < (uint32_t)size1; i += 1u << l) table[i] = e;
-            continue;
+    uint32_t prefix_now = ~0u;
+    uint32_t* sub = nullptr;
+    for (int len = first + 1; len <= longest; len++) {
+        for (int c = 0; c < count[len]; c++, k++) {
+            const uint32_t prefix = rev & (uint32_t)(size1 - 1);
+            if (prefix != prefix_now) {
+                if (used + (1 << sub_bits) > capacity) return false;
+                table[prefix] = entry((uint32_t)used, (uint32_t)sub_bits, SUBTABLE, (uint32_t)first);
+                sub = table + used;
+                if (!complete)
+                    for (int i = 0; i < (1 << sub_bits); i++) sub[i] = entry(0, 0, INVALID, 1);
+                used += 1 << sub_bits;
+                prefix_now = prefix;
+            }
+            const uint32_t e = payload((int)sorted[k]) | (uint32_t)(len - first);
+            for (uint32_t i = rev >> first; i < (1u << sub_bits); i += 1u << (len - first)) sub[i] = e;
+            next_code(len);
         }
-        const uint32_t prefix = rev & (uint32_t)(size1 - 1);
-        if (((table[prefix] >> 4) & 7u) != SUBTABLE) {
-            if (used + (1 << sub_bits) > capacity) return false;
-            table[prefix] = entry((uint32_t)used, (uint32_t)sub_bits, SUBTABLE, (uint32_t)first);
-            for (int i = 0; i < (1 << sub_bits); i++) table[used + i] = entry(0, 0, INVALID, 1);
-            used += 1 << sub_bits;
-        }
-        uint32_t* sub = table + (table[prefix] >> 16);
-        const uint32_t e = payload(s) | (uint32_t)(l - first);
-        for (uint32_t i = rev >> first; i < (1u << sub_bits); i += 1u << (l - first)) sub[i] = e;
     }
     return true;
 }
@@ -185,7 +210,7 @@ inline bool read_dynamic_tables(BitReader& br, Tables& t)
     uint8_t lens[286 + 30 + 138];
     int n = 0;
     while (n < hlit + hdist) {
-        br.refill();
+        if (br.bits < 14) br.refill();          // a code of <= 7 bits and <= 7 extra bits
         const uint32_t e = pre[br.peek(7)];
         if (((e >> 4) & 7u) != LITERAL) return false;
         br.drop((int)(e & 15u));
