@@ -30,3 +30,10 @@ def test_decode_bench_times_both_inflate_routes(tmp_path):
     assert line["accepted"] == line["records"] > 100000
     assert line["own_inflate_and_crc_s"] > 0 and line["zlib_s"] > 0
     assert err.count("[pmio bam]") == 2                 # the PMIO_TIMING stage line of each child
+
+
+def test_inflate_bench_compares_the_decoders(tmp_path):
+    line, _ = _run(["tools/inflate_bench.py", "--blocks", "4", "--reps", "1"], tmp_path)
+    for kind in ("literal_heavy", "match_heavy"):
+        assert all(line[kind][k] > 0 for k in ("own", "own_two_streams", "zlib", "crc32_clmul", "crc32_zlib"))
+    assert line["literal_heavy"]["compression_ratio"] < 4 < line["match_heavy"]["compression_ratio"]
