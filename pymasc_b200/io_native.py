@@ -307,15 +307,17 @@ def estimate_readlen(path, esttype="MEDIAN", mapq_criteria=1, threads=0):
     return ESTFUNCTIONS[esttype](bam.readlen_counter)
 
 
-def feed_bam(calc, bam):
+def feed_bam(calc, bam, only=None):
     """Feed every accepted read of `bam` to a calculator, one ``feed_packed`` per chromosome in
-    file order (handler/calc.py:140-153), raising ReadUnsortedError as the per-read loop would."""
+    file order (handler/calc.py:140-153), raising ReadUnsortedError as the per-read loop would.
+    `only`: a set of chromosome names; reads elsewhere are skipped (handler/calc.py:143-144)."""
     if not bam.sorted:
         raise ReadUnsortedError
     # chromosomes appear in a sorted file in header order; the per-read rules (duplicates,
     # read-length sums) were applied natively while decoding
     for chrom in bam.reads:
-        calc.feed_packed(chrom, **bam.packed(chrom))
+        if only is None or chrom in only:
+            calc.feed_packed(chrom, **bam.packed(chrom))
 
 
 # ------------------------------------------------------------------------------------- BigWig

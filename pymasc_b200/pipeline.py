@@ -10,8 +10,10 @@ are built once per chromosome for all files.
 It stops where the hot path stops: what comes back are the reference's result objects
 (``get_whole_result()``), ready for the reference's own stats.py / output code.
 """
+import fnmatch
 import logging
 import time
+from itertools import groupby
 
 from . import io_native, io_text
 from .calculator import CCBitArrayCalculator
@@ -62,11 +64,49 @@ def open_alignment(path, mapq_criteria=1, threads=0):
     return SamFile(path, mapq_criteria)
 
 
-def feed_alignment(calc, aln):
+class NoTargetChromosomes(ValueError):
+    """The chromosome filter leaves nothing (reader/bam.py:201-203, BAMNoTargetChroms)."""
+
+
+def filter_chroms(chroms, filters):
+    """The set of chromosome names that -i / --include-chrom and -e / --exclude-chrom select
+    (utils/calc.py:49-91).  `filters` is the reference's ``chromfilter`` list, in command-line
+    order: (True, [patterns]) for an include option, (False, [patterns]) for an exclude option,
+    shell-style patterns.  Runs of the same kind act as one option.  An exclude keeps what it
+    does not match and hands what it DID match to the option after it, so that a later include
+    can take names back; an include narrows the names still under consideration to its matches;
+    what the last option leaves is selected if that option is an include."""
+    if filters is None:
+        return set(chroms)
+    considered, selected, including = set(chroms), set(), False
+    for including, group in groupby(filters, key=lambda f: f[0]):
+        patterns = {p for _, pats in group for p in pats}
+        matched = {c for p in patterns for c in fnmatch.filter(considered, p)}
+        if not including:
+            selected |= considered - matched
+        considered = matched
+    if including:
+        selected |= considered
+    return selected
+
+
+def apply_chromfilter(references, lengths, chromfilter):
+    """(references, lengths) of the selected chromosomes, header order (reader/bam.py:180-215)."""
+    keep = filter_chroms(references, chromfilter)
+    if not keep:
+        raise NoTargetChromosomes("There is no targeted chromosomes.")
+    pairs = [(r, n) for r, n in zip(references, lengths) if r in keep]
+    return [r for r, _ in pairs], [n for _, n in pairs]
+
+
+def feed_alignment(calc, aln, only=None):
+    """Every accepted read to the calculator, file order; reads on chromosomes outside `only`
+    (the filtered reference list) are skipped as handler/calc.py:143-144 skips them."""
     if isinstance(aln, io_native.BamFile):
-        return io_native.feed_bam(calc, aln)
+        return io_native.feed_bam(calc, aln, only)
     for chrom, r in aln.reads.items():          # file order; feed_batch raises ReadUnsortedError itself
-        calc.feed_batch(chrom, r["pos"], r["readlen"], r["is_reverse"])
+        if only is None or chrom in only:
+            calc.feed_batch(chrom, r["pos"], r["readlen"], r["is_reverse"])
 
 
 class CachedTrack(object):
@@ -100,13 +140,15 @@ class CachedTrack(object):
 
 
 def run_files(bam_paths, bigwig_path=None, max_shift=1000, mapq_criteria=1, read_len=None,
-              esttype="MEDIAN", skip_ncc=False, threads=0, engine=None):
+              esttype="MEDIAN", skip_ncc=False, threads=0, engine=None, chromfilter=None):
     """Cross-correlation results of one or more BAM files.
 
     Returns (results, info): ``results[i]`` is the genome-wide result of ``bam_paths[i]``
     (NCCGenomeWideResult / MSCCGenomeWideResult / BothGenomeWideResult, as
     ``CCBitArrayCalculator.get_whole_result`` of the reference returns them); ``info`` holds
-    per-file read lengths, read statistics and wall-clock seconds per stage."""
+    per-file read lengths, read statistics and wall-clock seconds per stage.  ``chromfilter`` is
+    the reference's include / exclude list (see filter_chroms); the read-length estimate looks at
+    every chromosome, as core/readlen.pyx does."""
     if isinstance(bam_paths, (str, bytes)) or hasattr(bam_paths, "__fspath__"):
         bam_paths = [bam_paths]
     info = {"files": [], "seconds": {"decode": 0.0, "feed": 0.0, "correlate": 0.0}}
@@ -127,12 +169,11 @@ def run_files(bam_paths, bigwig_path=None, max_shift=1000, mapq_criteria=1, read
             if rl > max_shift:
                 raise ValueError("Read length ({}) seems to be longer than shift size ({})."
                                  .format(rl, max_shift))
-            lengths = list(bam.lengths)
+            references, lengths = apply_chromfilter(list(bam.references), list(bam.lengths), chromfilter)
             if feeder is not None:
-                lengths = reconcile_chromosome_sizes(bam.references, lengths, feeder.chromsizes)
-            calc = CCBitArrayCalculator(max_shift, rl, list(bam.references), lengths, feeder,
-                                        skip_ncc, engine=engine)
-            feed_alignment(calc, bam)
+                lengths = reconcile_chromosome_sizes(references, lengths, feeder.chromsizes)
+            calc = CCBitArrayCalculator(max_shift, rl, references, lengths, feeder, skip_ncc, engine=engine)
+            feed_alignment(calc, bam, None if chromfilter is None else set(references))
             t2 = time.perf_counter()
             info["files"].append({"path": str(path), "read_len": int(rl), "stats": bam.stats})
             info["seconds"]["decode"] += t1 - t0

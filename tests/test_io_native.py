@@ -304,6 +304,52 @@ def test_run_files_from_bam_and_bigwig_matches_golden_tables(tmp_path):
     assert pipeline.reconcile_chromosome_sizes(["a", "b", "c"], [10, 20, 30], {"a": 12, "b": 15}) == [12, 20, 30]
 
 
+def test_chromosome_filter_selects_what_the_reference_selects():
+    """pipeline.filter_chroms against the reference's utils/calc.py:49-91 on 68 include /
+    exclude option lists (tests/golden/chromfilter_cases.json, tests/golden/make_chromfilter_cases.py)."""
+    import json
+    from pymasc_b200 import pipeline
+    with open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "chromfilter_cases.json")) as fh:
+        gold = json.load(fh)
+    assert len(gold["cases"]) >= 60
+    for filters, want in gold["cases"]:
+        filters = None if filters is None else [(bool(flag), pats) for flag, pats in filters]
+        assert sorted(pipeline.filter_chroms(gold["chroms"], filters)) == want, filters
+    assert pipeline.apply_chromfilter(["b", "a", "c"], [2, 1, 3], [(False, ["a"])]) == (["b", "c"], [2, 3])
+    with pytest.raises(pipeline.NoTargetChromosomes):
+        pipeline.apply_chromfilter(["b", "a"], [2, 1], [(True, ["zzz*"])])
+
+
+def test_run_files_with_a_chromosome_filter(tmp_path):
+    """-i / -e as run_files(chromfilter=...): only the selected chromosomes get results, equal to
+    their results in the unfiltered run; reads elsewhere are skipped (handler/calc.py:143-144);
+    the read length is still estimated over the whole file."""
+    from pymasc_b200 import pipeline
+    rng = np.random.default_rng(61)
+    refs = [("c1", 60000), ("c2", 40000), ("c3_random", 30000)]
+    recs = []
+    for ref, (_, ln) in enumerate(refs):
+        for p in np.sort(rng.integers(1, ln - 100, 400)):
+            recs.append(W.bam_record(ref, int(p), 30, 16 if rng.random() < 0.5 else 0, [(36 if ref else 40, "M")]))
+    bam = str(tmp_path / "three.bam")
+    W.write_bam(bam, refs, recs)
+    sections = [{"chrom_id": ci, "type": "bedgraph", "items": [(s, s + 300, 1.0) for s in range(100, ln - 400, 1000)]}
+                for ci, (_, ln) in enumerate(refs)]
+    bw = str(tmp_path / "three.bigwig")
+    W.write_bigwig(bw, refs, sections)
+    everything, info_all = pipeline.run_files(bam, bw, max_shift=120, mapq_criteria=10, engine=OracleEngine())
+    picked, info = pipeline.run_files(bam, bw, max_shift=120, mapq_criteria=10, engine=OracleEngine(),
+                                      chromfilter=[(False, ["*_random"]), (False, ["c1"])])
+    assert info["files"][0]["read_len"] == info_all["files"][0]["read_len"]
+    assert sorted(picked[0].chroms) == ["c2"] and sorted(picked[0].mappable_chroms) == ["c2"]
+    assert picked[0].genomelen == 40000
+    for table in ("chroms", "mappable_chroms"):
+        a, b = getattr(picked[0], table)["c2"], getattr(everything[0], table)["c2"]
+        assert list(a.ccbins) == list(b.ccbins) and a.forward_sum == b.forward_sum and a.reverse_sum == b.reverse_sum
+    with pytest.raises(pipeline.NoTargetChromosomes):
+        pipeline.run_files(bam, bw, max_shift=120, mapq_criteria=10, engine=OracleEngine(), chromfilter=[(True, ["chrZ"])])
+
+
 @pytest.mark.parametrize("spec", helpers.TOY_SPECS, ids=lambda s: s["name"])
 def test_packed_feed_from_bam_equals_reference_vectors(tmp_path, spec):
     """The toy cases (exact duplicates, strand collisions, variable query lengths, read-less
