@@ -1,7 +1,8 @@
 /*
  * pymasc_io.h -- C ABI of libpymasc_io.so: host-side BAM (BGZF) and BigWig decoding into the
- * packed arrays that libpymasc_b200.so consumes (include/pymasc_b200.h).  Plain C / zlib /
- * pthreads; no CUDA in this library.  north_star keeps BAM/BigWig decoding on the host; the
+ * packed arrays that libpymasc_b200.so consumes (include/pymasc_b200.h).  C++ behind a plain C
+ * ABI: its own inflate and CRC-32 for BGZF blocks with zlib as the fallback, std::thread; no
+ * CUDA in this library.  north_star keeps BAM/BigWig decoding on the host; the
  * reference does it through pysam and pyBigWig, neither of which exists in this image.
  *
  * Reference interfaces replaced (paths relative to the PyMaSC checkout):
@@ -14,10 +15,14 @@
  *                              (not unmapped, not duplicate, MAPQ >= criteria; read2 included).
  *   pmio_bw_open / _intervals  BigWigReader.__init__ / .fetch, reader/bigwig.pyx:114-177
  *                              (pyBigWig.open, .chroms(), .intervals(chrom, 0, size), value filter).
+ *   pmio_bw_prefetch ......... the same decode for every chromosome at once, on a thread pool
+ *                              (the reference fetches per chromosome and per input file).
+ *   pmio_inflate_raw[2], pmio_crc32 ... test hooks of the block decoder (no reference counterpart:
+ *                              pysam's htslib does this inside).
  *
  * Every function returns 0 or a negative pmio_status; text in pmio_last_error() (thread-local).
  * Arrays returned by the getters are owned by the handle and live until it is freed (BigWig:
- * until the next pmio_bw_intervals call on the same handle).
+ * until the next pmio_bw_intervals / pmio_bw_prefetch call on the same handle).
  */
 #ifndef PYMASC_IO_H
 #define PYMASC_IO_H

@@ -1,5 +1,6 @@
 // pmb_io.cpp -- libpymasc_io.so (include/pymasc_io.h): BAM (BGZF) and BigWig decoding on the
-// host into packed arrays.  zlib + std::thread; no CUDA here.
+// host into packed arrays.  Own inflate / CRC-32 (pmb_inflate.h, pmb_crc32.h) with zlib behind
+// them, std::thread; no CUDA here.
 //
 // BAM: the file is memory-mapped and the BGZF block headers are walked sequentially (18 bytes per
 // <= 64 KiB block; ISIZE in each footer gives every block's offset in the inflated stream up
@@ -126,8 +127,9 @@ bool inflate_block_pair(const uint8_t* const src[2], const size_t csize[2], uint
 
 struct Block { size_t data_off; uint32_t csize, isize, crc; size_t out_off; };
 
-// Threads that live as long as one pmio_bam_load: a BAM file is decoded in many small batches
-// (the buffer stays in cache), and starting threads per batch would cost more than the batch.
+// Threads that live as long as one pmio_bam_load / pmio_bw_prefetch: a BAM file is decoded in many
+// small batches (the buffer stays in cache), and starting threads per batch would cost more than
+// the batch.
 // run(f, helpers): f() on the caller and on up to `helpers` pool threads; returns when all are back.
 class WorkerPool {
     std::vector<std::thread> threads;
