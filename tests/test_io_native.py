@@ -715,3 +715,62 @@ def test_two_stream_inflate_decodes_each_stream_on_its_own_terms():
             except ValueError:
                 pass
     assert refused > 30
+
+
+def _load_outcome(path, threads, share_bytes, monkeypatch):
+    if share_bytes is None:
+        monkeypatch.delenv("PMIO_SHARE_BYTES", raising=False)
+    else:
+        monkeypatch.setenv("PMIO_SHARE_BYTES", str(share_bytes))
+    try:
+        bam = io_native.BamFile(path, mapq_criteria=20, threads=threads)
+    except (ValueError, IOError) as e:
+        return ("error", type(e).__name__)
+    out = [bam.stats["n_records"], bam.stats["n_accepted"], bam.sorted, sorted(bam.readlen_counter.items())]
+    for chrom in sorted(bam.reads):
+        r = bam.reads[chrom]
+        out.append((chrom, r["pos"].tobytes(), r["readlen"].tobytes(), r["is_reverse"].tobytes()))
+    bam.close()
+    return out
+
+
+def test_damaged_bam_files_give_the_same_outcome_however_the_work_is_split(tmp_path, monkeypatch):
+    """Bit flips in the compressed file, truncation, and bytes changed in the INFLATED stream
+    (re-wrapped in valid BGZF blocks, so only the record parser can notice): the loader either
+    refuses the file or returns arrays -- and which of the two, and which arrays, must not depend
+    on threads and share size, because every share's guessed start is validated against the
+    sequential order of the records."""
+    import random
+    import zlib
+    rnd = random.Random(71)
+    recs, _, _ = synthetic_records()
+    refs = [("c1", 200000), ("c2", 5000), ("c3", 90000)]
+    base, mutated = str(tmp_path / "base.bam"), str(tmp_path / "m.bam")
+    refused = 0
+    for it in range(36):
+        W.write_bam(base, refs, recs, rnd.choice([150, 997, 4000, 65280]), align_records=it % 2 == 0)
+        blob = bytearray(open(base, "rb").read())
+        mode = it % 3
+        if mode == 0:
+            for _ in range(rnd.randint(1, 3)):
+                blob[rnd.randrange(len(blob))] ^= 1 << rnd.randrange(8)
+            data = bytes(blob)
+        elif mode == 1:
+            data = bytes(blob[:rnd.randrange(1, len(blob))])
+        else:
+            o, payloads = 0, []
+            while o < len(blob):
+                bsize = struct.unpack_from("<H", blob, o + 16)[0] + 1
+                payloads.append(bytearray(zlib.decompress(bytes(blob[o + 18:o + bsize - 8]), -15)))
+                o += bsize
+            for _ in range(rnd.randint(1, 4)):
+                k = rnd.randrange(len(payloads))
+                if payloads[k]:
+                    payloads[k][rnd.randrange(len(payloads[k]))] = rnd.randrange(256)
+            data = b"".join(W.bgzf_block(bytes(p)) for p in payloads if p) + W.BGZF_EOF
+        open(mutated, "wb").write(data)
+        sequential = _load_outcome(mutated, 1, 1 << 30, monkeypatch)
+        for threads, share in ((3, 3000), (4, 100), (2, None)):
+            assert _load_outcome(mutated, threads, share, monkeypatch) == sequential, (it, mode, threads, share)
+        refused += sequential[0] == "error"
+    assert 5 < refused < 36
