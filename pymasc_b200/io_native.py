@@ -199,7 +199,7 @@ class BamFile(object):
             _raise(L, rc)
         self._h = h
         n = L.pmio_bam_n_refs(h)
-        self.references = tuple(L.pmio_bam_ref_name(h, i).decode() for i in range(n))
+        self.references = tuple(L.pmio_bam_ref_name(h, i).decode("utf-8", "surrogateescape") for i in range(n))
         self.lengths = tuple(int(L.pmio_bam_ref_len(h, i)) for i in range(n))
         self._index = {name: i for i, name in enumerate(self.references)}
         st = BamStats()
@@ -343,7 +343,7 @@ class BigWigReader(object):
             _raise(self._L, rc)
         self._h = h
         n = self._L.pmio_bw_n_chroms(h)
-        self.chromsizes = {self._L.pmio_bw_chrom_name(h, i).decode(): int(self._L.pmio_bw_chrom_len(h, i))
+        self.chromsizes = {self._L.pmio_bw_chrom_name(h, i).decode("utf-8", "surrogateescape"): int(self._L.pmio_bw_chrom_len(h, i))
                            for i in range(n)}
 
     def fetch_arrays(self, valfilter, chrom, with_values=False):
@@ -355,7 +355,7 @@ class BigWigReader(object):
             raise KeyError(chrom)
         b, e = ctypes.POINTER(ctypes.c_uint32)(), ctypes.POINTER(ctypes.c_uint32)()
         v, n = ctypes.POINTER(ctypes.c_float)(), ctypes.c_uint64()
-        rc = self._L.pmio_bw_intervals(self._h, chrom.encode(), float(valfilter), ctypes.byref(b),
+        rc = self._L.pmio_bw_intervals(self._h, chrom.encode("utf-8", "surrogateescape"), float(valfilter), ctypes.byref(b),
                                        ctypes.byref(e), ctypes.byref(v), ctypes.byref(n))
         if rc != 0:
             _raise(self._L, rc)
