@@ -331,8 +331,9 @@ struct Decoder {
     const Tables* t = nullptr;
     bool last = false;          // the block being decoded is the final one
     bool in_block = false;      // inside a Huffman block (t is its tables)
-    bool done = false;          // the stream ended exactly at out_end
+    bool done = false;          // the stream ended (exactly at out_end, unless `exact` is off)
     bool refused = false;
+    bool exact = true;          // off: out_end is a capacity, the stream may end before it
     Tables dyn;
 
     void init(const uint8_t* in, size_t in_len, uint8_t* o, size_t out_len)
@@ -341,6 +342,7 @@ struct Decoder {
         out0 = out = o;
         out_end = o + out_len;
         last = in_block = done = refused = false;
+        exact = true;
     }
     bool fast_ok() const { return (size_t)(br.end - br.in) >= FAST_IN && (size_t)(out_end - out) >= FAST_OUT; }
     Hot hot() const { return Hot{br.buf, br.bits, br.in, out}; }
@@ -421,7 +423,7 @@ struct Decoder {
         while (live()) {
             if (!in_block) {
                 if (last) {
-                    if (out == out_end && br.bits >= 0) done = true;
+                    if ((out == out_end || !exact) && br.bits >= 0) done = true;
                     else refused = true;
                     return;
                 }
@@ -460,6 +462,18 @@ inline bool inflate(const uint8_t* in, size_t in_len, uint8_t* out, size_t out_l
     Decoder d;
     d.init(in, in_len, out, out_len);
     return d.finish();
+}
+
+// Inflate in[0, in_len) into out[0, capacity): a stream whose inflated size is not known up
+// front (BigWig data blocks).  *produced = its size.  false: not decoded, or it did not fit.
+inline bool inflate_upto(const uint8_t* in, size_t in_len, uint8_t* out, size_t capacity, size_t* produced)
+{
+    Decoder d;
+    d.init(in, in_len, out, capacity);
+    d.exact = false;
+    if (!d.finish()) return false;
+    *produced = (size_t)(d.out - d.out0);
+    return true;
 }
 
 // Two independent streams at once (two BGZF blocks): their fast loops take turns, round by

@@ -988,8 +988,16 @@ static const char* bw_decode_block(const pmio_bw* w, const Leaf& lf, uint32_t id
     size_t dn = (size_t)lf.size;
     if (w->uncompress_buf) {
         if (buf.size() < std::max<size_t>(w->uncompress_buf, 64)) buf.resize(std::max<size_t>(w->uncompress_buf, 64));
-        uLongf got = (uLongf)buf.size();
-        int zr = uncompress(buf.data(), &got, d, (uLong)lf.size);
+        // a zlib stream (RFC 1950): 2 header bytes, raw DEFLATE, Adler-32.  The library's own
+        // inflate first, vouched for by the checksum; zlib's uncompress for whatever it refuses.
+        static const bool zlib_only = getenv("PMIO_ZLIB_ONLY") != nullptr;
+        size_t own = 0;
+        const bool fast = !zlib_only && dn > 6 && (d[0] & 0x0F) == 8 && ((d[0] << 8 | d[1]) % 31) == 0 && !(d[1] & 0x20) &&
+                          pmb_inflate::inflate_upto(d + 2, dn - 6, buf.data(), buf.size(), &own) &&
+                          (uint32_t)adler32(adler32(0L, Z_NULL, 0), buf.data(), (uInt)own) ==
+                              ((uint32_t)d[dn - 4] << 24 | (uint32_t)d[dn - 3] << 16 | (uint32_t)d[dn - 2] << 8 | d[dn - 1]);
+        uLongf got = fast ? (uLongf)own : (uLongf)buf.size();
+        int zr = fast ? Z_OK : uncompress(buf.data(), &got, d, (uLong)lf.size);
         while (zr == Z_BUF_ERROR && buf.size() < (1u << 28)) {       // header understated the size
             buf.resize(buf.size() * 2);
             got = (uLongf)buf.size();

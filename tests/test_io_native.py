@@ -774,3 +774,36 @@ def test_damaged_bam_files_give_the_same_outcome_however_the_work_is_split(tmp_p
             assert _load_outcome(mutated, threads, share, monkeypatch) == sequential, (it, mode, threads, share)
         refused += sequential[0] == "error"
     assert 5 < refused < 36
+
+
+def test_bigwig_decodes_the_same_with_and_without_the_own_inflate(tmp_path):
+    """BigWig data blocks are zlib streams of unknown inflated size: the library's decoder
+    (inflate_upto + Adler-32) and zlib's uncompress (PMIO_ZLIB_ONLY=1, read once per process, so
+    in a child) must give the same arrays, on the reference's track and on a file with every
+    section type."""
+    import subprocess
+    import sys
+    chroms = [("c1", 50000), ("c2", 30000)]
+    sections = [{"chrom_id": 0, "type": "bedgraph", "items": [(100 * i, 100 * i + 37, 1.0 if i % 3 else 0.25) for i in range(400)]},
+                {"chrom_id": 1, "type": "varstep", "items": [(50 * i, 1.0) for i in range(300)], "span": 20},
+                {"chrom_id": 1, "type": "fixedstep", "items": [1.0, 0.5] * 100, "start": 20000, "step": 30, "span": 10}]
+    mixed = str(tmp_path / "mixed.bigwig")
+    W.write_bigwig(mixed, chroms, sections)
+    code = ("import sys, hashlib; sys.path.insert(0, %r); from pymasc_b200 import io_native; h = hashlib.sha256(); n = 0\n"
+            "for path in %r:\n"
+            "    for pre in (False, True):\n"
+            "        r = io_native.BigWigReader(path)\n"
+            "        if pre: r.prefetch(1.0, 2)\n"
+            "        for c in sorted(r.chromsizes):\n"
+            "            for a in r.fetch_arrays(1.0, c, with_values=True) + r.fetch_arrays(0, c, with_values=True):\n"
+            "                h.update(a.tobytes()); n += a.size\n"
+            "        r.close()\n"
+            "print(h.hexdigest(), n)"
+            % (os.path.dirname(os.path.dirname(os.path.abspath(__file__))), [BIGWIG, mixed]))
+    outs = []
+    for env_extra in ({}, {"PMIO_ZLIB_ONLY": "1"}):
+        env = {k: v for k, v in os.environ.items() if k != "PMIO_ZLIB_ONLY"}
+        env.update(env_extra)
+        outs.append(subprocess.run([sys.executable, "-c", code], env=env, check=True,
+                                   capture_output=True, text=True).stdout.strip())
+    assert outs[0] == outs[1] and int(outs[0].split()[1]) > 10000
