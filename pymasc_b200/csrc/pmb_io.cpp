@@ -661,8 +661,8 @@ static int bam_load_impl(const char* path, int mapq_criteria, int threads, pmio_
         const size_t n_shares = shares.size();
         const uint32_t n_refs = (uint32_t)b->names.size();
         if (share_stats.size() < n_shares) share_stats.resize(n_shares);
-        const size_t store0 = b->store.size();      // two chunks per share: its records, then the one that straddles its end
-        for (size_t i = 0; i < 2 * n_shares; i++) b->store.emplace_back(new pmio_chunk());
+        const size_t store0 = b->store.size();      // one chunk per share (the rare record that straddles a share's end gets its own, later)
+        for (size_t i = 0; i < n_shares; i++) b->store.emplace_back(new pmio_chunk());
         // ---- every share: inflate, guess where its first record starts, filter -- one thread, one pass.
         //      Share 0 starts at a known record boundary.  The others start at a BGZF block boundary,
         //      which IS a record boundary in an htslib-written file and a few bytes before one
@@ -693,7 +693,7 @@ static int bam_load_impl(const char* path, int mapq_criteria, int threads, pmio_
                     share_stats[i].reset();
                     if (i > 0) s.start = find_record_start(p, s.lo, s.hi, n_refs);
                     s.stop = s.start == SIZE_MAX ? s.lo
-                           : parse_share(p, s.start, s.hi, s.hi, n_refs, mapq_criteria, *b->store[store0 + 2 * i], share_stats[i]);
+                           : parse_share(p, s.start, s.hi, s.hi, n_refs, mapq_criteria, *b->store[store0 + i], share_stats[i]);
                     if (timing) {
                         ns_inflate += (uint64_t)((t1 - t0) * 1e9);
                         ns_filter += (uint64_t)((now() - t1) * 1e9);
@@ -716,7 +716,7 @@ static int bam_load_impl(const char* path, int mapq_criteria, int threads, pmio_
         size_t at = used;
         for (size_t i = 0; i < n_shares && !bad; i++) {
             Share& s = shares[i];
-            pmio_chunk& c = *b->store[store0 + 2 * i];
+            pmio_chunk& c = *b->store[store0 + i];
             if (at >= s.hi) { c = pmio_chunk(); continue; }
             if (s.start != at) {
                 c = pmio_chunk();
@@ -729,15 +729,20 @@ static int bam_load_impl(const char* path, int mapq_criteria, int threads, pmio_
             at = s.stop;
             if (at >= s.hi) continue;
             // the record starting at `at` crosses the end of the share (or of the batch)
-            pmio_chunk& c2 = *b->store[store0 + 2 * i + 1];
+            pmio_chunk one;
             straddler_stats.reset();
-            const size_t stop2 = parse_share(p, at, at + 1, out_off, n_refs, mapq_criteria, c2, straddler_stats);
+            const size_t stop2 = parse_share(p, at, at + 1, out_off, n_refs, mapq_criteria, one, straddler_stats);
             if (straddler_stats.err) { g_err = straddler_stats.err; bad = true; break; }
             if (straddler_stats.incomplete) {       // it runs past the batch: nothing after it can be right
-                for (size_t k = i + 1; k < n_shares; k++) *b->store[store0 + 2 * k] = pmio_chunk();
+                for (size_t k = i + 1; k < n_shares; k++) *b->store[store0 + k] = pmio_chunk();
                 break;
             }
-            merger.take(c2, straddler_stats);
+            if (one.pos.empty()) {
+                merger.take(one, straddler_stats);          // counters only; no segment points into `one`
+            } else {
+                b->store.emplace_back(new pmio_chunk(std::move(one)));
+                merger.take(*b->store.back(), straddler_stats);
+            }
             at = stop2;
         }
         if (bad) break;
