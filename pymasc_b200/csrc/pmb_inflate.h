@@ -233,6 +233,8 @@ inline bool read_dynamic_tables(BitReader& br, Tables& t)
            build_table(lens + hlit, hdist, D_BITS, t.d, D_TABLE, d_payload);
 }
 
+// (inflate / inflate2 / inflate_upto are always inlined: the caller decides the instruction set,
+// pmb_io.cpp clones its wrappers for BMI2, whose flag-free variable shifts are worth ~9 % here.)
 // ---- the decoder.  State of one stream; `prepare` walks block headers, stored blocks and the
 // checked one-symbol loop until the stream stands inside a Huffman block with room for the fast
 // loop (or is finished / refused); `fast_round` is one refill's worth of that loop.  Two streams
@@ -436,7 +438,7 @@ struct Decoder {
     }
 
     // the rest of the stream, alone
-    bool finish()
+    PMB_INLINE bool finish()
     {
         for (;;) {
             prepare();
@@ -457,7 +459,7 @@ struct Decoder {
 };
 
 // Inflate in[0, in_len) into exactly out[0, out_len).  false: not decoded (use zlib).
-inline bool inflate(const uint8_t* in, size_t in_len, uint8_t* out, size_t out_len)
+PMB_INLINE bool inflate(const uint8_t* in, size_t in_len, uint8_t* out, size_t out_len)
 {
     Decoder d;
     d.init(in, in_len, out, out_len);
@@ -466,7 +468,7 @@ inline bool inflate(const uint8_t* in, size_t in_len, uint8_t* out, size_t out_l
 
 // Inflate in[0, in_len) into out[0, capacity): a stream whose inflated size is not known up
 // front (BigWig data blocks).  *produced = its size.  false: not decoded, or it did not fit.
-inline bool inflate_upto(const uint8_t* in, size_t in_len, uint8_t* out, size_t capacity, size_t* produced)
+PMB_INLINE bool inflate_upto(const uint8_t* in, size_t in_len, uint8_t* out, size_t capacity, size_t* produced)
 {
     Decoder d;
     d.init(in, in_len, out, capacity);
@@ -478,7 +480,7 @@ inline bool inflate_upto(const uint8_t* in, size_t in_len, uint8_t* out, size_t 
 
 // Two independent streams at once (two BGZF blocks): their fast loops take turns, round by
 // round, so that the two dependency chains overlap.  ok[i]: stream i decoded.
-inline void inflate2(const uint8_t* const in[2], const size_t in_len[2], uint8_t* const out[2], const size_t out_len[2],
+PMB_INLINE void inflate2(const uint8_t* const in[2], const size_t in_len[2], uint8_t* const out[2], const size_t out_len[2],
                      bool ok[2])
 {
     Decoder a, b;

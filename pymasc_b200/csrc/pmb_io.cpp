@@ -84,6 +84,27 @@ inline int32_t rdi32(const uint8_t* p) { int32_t v; memcpy(&v, p, 4); return v; 
 inline uint64_t rd64(const uint8_t* p) { uint64_t v; memcpy(&v, p, 8); return v; }
 inline float rdf32(const uint8_t* p) { float v; memcpy(&v, p, 4); return v; }
 
+// The decoder's entry points, compiled twice: for any x86-64 and for BMI2 (SHRX / SHLX / BZHI in
+// the bit-buffer arithmetic: +9 % per thread); the loader picks one (ifunc).
+#if defined(__x86_64__) && defined(__GNUC__) && !defined(__clang__) && !defined(__SANITIZE_THREAD__) && !defined(__SANITIZE_ADDRESS__)
+#define PMB_CLONES __attribute__((target_clones("default", "bmi2")))
+#else
+#define PMB_CLONES
+#endif
+PMB_CLONES bool own_inflate(const uint8_t* in, size_t in_len, uint8_t* out, size_t out_len)
+{
+    return pmb_inflate::inflate(in, in_len, out, out_len);
+}
+PMB_CLONES bool own_inflate_upto(const uint8_t* in, size_t in_len, uint8_t* out, size_t capacity, size_t* produced)
+{
+    return pmb_inflate::inflate_upto(in, in_len, out, capacity, produced);
+}
+PMB_CLONES void own_inflate2(const uint8_t* const in[2], const size_t in_len[2], uint8_t* const out[2],
+                             const size_t out_len[2], bool ok[2])
+{
+    pmb_inflate::inflate2(in, in_len, out, out_len, ok);
+}
+
 bool zlib_inflate_raw(const uint8_t* src, size_t csize, uint8_t* dst, size_t isize)
 {
     z_stream zs;
@@ -106,7 +127,7 @@ bool inflate_block(const uint8_t* src, size_t csize, uint8_t* dst, size_t isize,
     if (isize == 0) return true;
     static const bool zlib_only = getenv("PMIO_ZLIB_ONLY") != nullptr;      // A/B aid
     auto crc_ok = [&]() { return pmb_crc32::compute(dst, isize, !zlib_only) == crc; };
-    if (!zlib_only && pmb_inflate::inflate(src, csize, dst, isize) && crc_ok()) return true;
+    if (!zlib_only && own_inflate(src, csize, dst, isize) && crc_ok()) return true;
     return zlib_inflate_raw(src, csize, dst, isize) && crc_ok();
 }
 
@@ -117,7 +138,7 @@ bool inflate_block_pair(const uint8_t* const src[2], const size_t csize[2], uint
 {
     static const bool zlib_only = getenv("PMIO_ZLIB_ONLY") != nullptr;
     bool ok[2] = {false, false};
-    if (!zlib_only && isize[0] && isize[1]) pmb_inflate::inflate2(src, csize, dst, isize, ok);
+    if (!zlib_only && isize[0] && isize[1]) own_inflate2(src, csize, dst, isize, ok);
     for (int i = 0; i < 2; i++) {
         if (ok[i] && pmb_crc32::compute(dst[i], isize[i], true) == crc[i]) continue;
         if (!inflate_block(src[i], csize[i], dst[i], isize[i], crc[i])) return false;
@@ -191,7 +212,7 @@ extern "C" int pmio_inflate_raw(const uint8_t* in, uint64_t in_len, uint8_t* out
 {
     if (!in || (!out && out_len)) return fail(PMIO_ERR_ARG, "null argument");
     const bool ok = use_zlib ? zlib_inflate_raw(in, (size_t)in_len, out, (size_t)out_len)
-                             : pmb_inflate::inflate(in, (size_t)in_len, out, (size_t)out_len);
+                             : own_inflate(in, (size_t)in_len, out, (size_t)out_len);
     return ok ? PMIO_OK : fail(PMIO_ERR_FORMAT, "stream does not inflate to the given size");
 }
 
@@ -201,7 +222,7 @@ extern "C" int pmio_inflate_raw2(const uint8_t* const in[2], const uint64_t in_l
     if (!in || !in_len || !out || !out_len || !ok || !in[0] || !in[1] || !out[0] || !out[1]) return fail(PMIO_ERR_ARG, "null argument");
     const size_t il[2] = {(size_t)in_len[0], (size_t)in_len[1]}, ol[2] = {(size_t)out_len[0], (size_t)out_len[1]};
     bool good[2];
-    pmb_inflate::inflate2(in, il, out, ol, good);
+    own_inflate2(in, il, out, ol, good);
     ok[0] = good[0];
     ok[1] = good[1];
     return PMIO_OK;
@@ -998,7 +1019,7 @@ static const char* bw_decode_block(const pmio_bw* w, const Leaf& lf, uint32_t id
         static const bool zlib_only = getenv("PMIO_ZLIB_ONLY") != nullptr;
         size_t own = 0;
         const bool fast = !zlib_only && dn > 6 && (d[0] & 0x0F) == 8 && ((d[0] << 8 | d[1]) % 31) == 0 && !(d[1] & 0x20) &&
-                          pmb_inflate::inflate_upto(d + 2, dn - 6, buf.data(), buf.size(), &own) &&
+                          own_inflate_upto(d + 2, dn - 6, buf.data(), buf.size(), &own) &&
                           (uint32_t)adler32(adler32(0L, Z_NULL, 0), buf.data(), (uInt)own) ==
                               ((uint32_t)d[dn - 4] << 24 | (uint32_t)d[dn - 3] << 16 | (uint32_t)d[dn - 2] << 8 | d[dn - 1]);
         uLongf got = fast ? (uLongf)own : (uLongf)buf.size();
