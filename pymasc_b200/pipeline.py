@@ -139,6 +139,24 @@ class CachedTrack(object):
         self._reader.close()
 
 
+def precalc_mappability(bigwig_path, max_shift=1000, max_readlen=1000, stats_path=None, threads=0, engine=None):
+    """The body of ``pymasc-precalc`` (calcmappablelen.py:54-58): mappable-length statistics of a
+    BigWig track for shifts up to what (max_shift, max_readlen) require, written to the JSON
+    cache that ``pymasc`` reads (next to the BigWig unless `stats_path` says otherwise).  Every
+    chromosome in one device batch.  Returns the handler (``mappable_len``,
+    ``chrom2mappable_len``, ``map_path``)."""
+    from .mappability import MappabilityHandler
+    if stats_path is not None and str(stats_path) == str(bigwig_path):      # calcmappablelen.py:51-52
+        stats_path = None
+    handler = MappabilityHandler(bigwig_path, max_shift, max_readlen, stats_path, threads or 1, engine=engine)
+    try:
+        handler.calc_mappability()
+        handler.save_mappability_stats()
+    finally:
+        handler.close()
+    return handler
+
+
 def run_files(bam_paths, bigwig_path=None, max_shift=1000, mapq_criteria=1, read_len=None,
               esttype="MEDIAN", skip_ncc=False, threads=0, engine=None, chromfilter=None):
     """Cross-correlation results of one or more BAM files.

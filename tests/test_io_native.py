@@ -435,6 +435,11 @@ def test_mappability_handler_reproduces_the_reference_json(tmp_path):
     assert h3.get_mappable_len("chr1", force=True)[:266] == tuple(want["references"]["chr1"])
     with pytest.raises(BWIOError):
         MappabilityHandler(str(tmp_path / "missing.bw"), 300, 36)
+    # the body of pymasc-precalc (calcmappablelen.py:54-58) in one call, to a path of its own
+    from pymasc_b200 import pipeline
+    out = str(tmp_path / "stats" / "precalc.json")
+    done = pipeline.precalc_mappability(bw, max_shift=300, max_readlen=36, stats_path=out, engine=OracleEngine())
+    assert json.load(open(out)) == want and str(done.map_path) == out and not done.need_save_stats
 
 
 def test_run_files_takes_text_sam_too(tmp_path):
