@@ -78,7 +78,13 @@ typedef struct {
 
 /* Decode the whole file: BGZF blocks are inflated on `threads` threads (0 = all cores), records
  * are filtered (skip read2, MAPQ < mapq_criteria, unmapped, duplicate, no reference, no CIGAR)
- * and packed per reference in file order. */
+ * and packed per reference in file order.
+ * Environment switches, read by the library (measurement and test aids, not configuration):
+ *   PMIO_TIMING=1        seconds per stage on stderr (also pmio_bw_prefetch)
+ *   PMIO_ZLIB_ONLY=1     zlib's inflate / crc32 / uncompress instead of the library's own (A/B;
+ *                        read once per process)
+ *   PMIO_BATCH_BLOCKS=n  BGZF blocks per batch (default 128 per thread, 512..4096)
+ *   PMIO_SHARE_BYTES=n   inflated bytes per share (default 512 KiB; tests shrink it) */
 int  pmio_bam_load(const char *path, int mapq_criteria, int threads, pmio_bam **out);
 void pmio_bam_free(pmio_bam *b);
 int  pmio_bam_stats_get(const pmio_bam *b, pmio_bam_stats *s);
