@@ -359,7 +359,7 @@ def gpu_arm(args):
         dev.set_option("variant", args.variant)
     if args.tile_words:
         dev.set_option("tile_words", args.tile_words)
-    dev.set_option("path", {"auto": 0, "dense": 1, "events": 2}[args.path])
+    dev.set_option("path", {"auto": 0, "dense": 1, "events": 2, "lists": 3}[args.path])
     for kv in args.opt:
         k, v = kv.split("=")
         dev.set_option(k, int(v))
@@ -446,7 +446,7 @@ def gpu_arm(args):
                 dist.all_reduce(counters_tensor(ob))
             o_out = ob.fetch()
             ob.free()
-            dev.set_option("path", {"auto": 0, "dense": 1, "events": 2}[args.path])
+            dev.set_option("path", {"auto": 0, "dense": 1, "events": 2, "lists": 3}[args.path])
             other = {"path": t2["path"], "window_ms": float(np.mean(o_win[1:])),
                      "build_ms": float(np.mean(o_build[1:])), "pairs": t2["window_word_shift_pairs"],
                      "same": all(np.array_equal(np.asarray(a[k]), np.asarray(b2[k]))
@@ -606,7 +606,7 @@ def main():
     ap.add_argument("--variant", type=int, default=None, help="shift-window kernel variant (tuning)")
     ap.add_argument("--tile-words", type=int, default=0)
     ap.add_argument("--single-path", action="store_true", help="skip the cross-check pass of the other algorithm")
-    ap.add_argument("--path", default="auto", choices=["auto", "dense", "events"],
+    ap.add_argument("--path", default="auto", choices=["auto", "dense", "events", "lists"],
                     help="device algorithm: dense shift-window kernel or event-window kernels")
     ap.add_argument("--h2d-groups", type=int, default=4,
                     help="e2e arm: chromosome groups whose H2D overlaps the kernels (0 = no overlap)")

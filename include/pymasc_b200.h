@@ -109,10 +109,10 @@ typedef struct {
     uint32_t launches;  /* kernels launched by the execute                   */
     uint32_t window_launches;
     uint64_t window_word_shift_pairs; /* 32-bit word x shift pairs evaluated (dense path) */
-    uint32_t path;      /* algorithm the execute used: 1 dense shift-window, 2 event-window */
-    float ev_fwd_ms;    /* event path: forward-read kernel(s)                 */
-    float ev_rev_ms;    /* event path: reverse-read kernel(s)                 */
-    float ev_edge_ms;   /* event path: run-edge kernel(s) + finalize          */
+    uint32_t path;      /* algorithm the execute used: 1 dense shift-window, 2 event-window, 3 lists */
+    float ev_fwd_ms;    /* event / list path: forward-read kernel(s)          */
+    float ev_rev_ms;    /* event / list path: reverse-read kernel(s)          */
+    float ev_edge_ms;   /* event / list path: run-edge kernel(s) + finalize   */
 } pmb_timing;
 
 int  pmb_device_count(void);                 /* usable CUDA devices (0 on any error)   */
@@ -146,6 +146,14 @@ int  pmb_batch_execute(pmb_ctx *ctx, pmb_batch *b);
 int  pmb_batch_fetch(pmb_ctx *ctx, pmb_batch *b, pmb_chrom_out *o);
 int  pmb_batch_counters(pmb_ctx *ctx, pmb_batch *b, void **dev_ptr, uint64_t *n_int64,
                         uint32_t *stride);
+/* The list path (see "path" below) takes sorted reads and sorted, disjoint intervals -- what the
+ * reference's feed rules guarantee (ReadUnsortedError, mscc.pyx:351-366) and what a BigWig holds
+ * -- and verifies it on the device while it counts.  pmb_batch_fetch handles the other case by
+ * itself (the batch is recomputed on the event path).  A caller that reads the device counters
+ * WITHOUT a fetch (an all-reduce on pmb_batch_counters) calls pmb_batch_validate once after the
+ * batch's first execute: it waits for the stream and, if the inputs turned out unsorted, moves
+ * the batch to the event path and executes it again.  Later executes of the batch need no check. */
+int  pmb_batch_validate(pmb_ctx *ctx, pmb_batch *b);
 void pmb_batch_free(pmb_ctx *ctx, pmb_batch *b);
 int  pmb_get_timing(pmb_ctx *ctx, pmb_timing *t);
 
@@ -162,9 +170,13 @@ int  pmb_host_alloc(void **out, uint64_t bytes);
 void pmb_host_free(void *p);
 
 /* Options (0 = default).  "path": 0 auto, 1 dense shift-window kernel, 2 event-window
- * kernels -- two algorithms for the same counts (identical results); auto takes the
- * event path unless the inputs hold more than 4 events (reads + run edges) per 32-bit
- * word.  Tuning: "variant" (carry-save depth of the shift-window counters), "tile_words",
+ * kernels, 3 list kernels -- three algorithms for the same counts (identical results):
+ *   dense  every (bit position, shift) pair from bit arrays in shared memory; cost ~ bits x shifts
+ *   events one max_shift-bit window of a bit array per read / run edge;   cost ~ events x shifts/32
+ *   lists  no bit arrays: pairs of sorted list entries within max_shift;  cost ~ entries + pairs
+ * auto takes the list path while a forward read expects fewer than "list_pairs_limit"
+ * (default 24) reverse reads per 1024 shifts, else the event path unless the inputs hold more
+ * than 4 events (reads + run edges) per 32-bit word.  Tuning: "list_blocks_per_sm", "variant" (carry-save depth of the shift-window counters), "tile_words",
  * "grid_blocks", "block_warps", "event_tile_words", "event_blocks_per_sm".
  * Input copy: "async_h2d" (0/1, see pmb_batch_prepare), "h2d_groups" (1..64, default 4: at most that many),
  * "h2d_min_group_bytes" (default 16 MiB: no group smaller than that on average; 0 = always h2d_groups),

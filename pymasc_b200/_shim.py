@@ -60,6 +60,7 @@ EXPORTS = (
     "pmb_batch_prepare", "pmb_batch_execute", "pmb_batch_fetch", "pmb_batch_counters",
     "pmb_batch_free", "pmb_get_timing", "pmb_stream", "pmb_synchronize", "pmb_host_alloc",
     "pmb_host_free", "pmb_set_option", "pmb_pipe_probe", "pmb_set_stream", "pmb_device_count",
+    "pmb_batch_validate",
 )
 
 _lib = None
@@ -97,6 +98,8 @@ def load_library():
     L.pmb_batch_counters.argtypes = [vp, vp, vpp, ctypes.POINTER(ctypes.c_uint64),
                                      ctypes.POINTER(ctypes.c_uint32)]
     L.pmb_batch_counters.restype = ctypes.c_int
+    L.pmb_batch_validate.argtypes = [vp, vp]
+    L.pmb_batch_validate.restype = ctypes.c_int
     L.pmb_batch_free.argtypes = [vp, vp]
     L.pmb_batch_free.restype = None
     L.pmb_get_timing.argtypes = [vp, ctypes.POINTER(Timing)]
@@ -292,6 +295,11 @@ class Batch(object):
 
     def execute(self):
         self.dev._check(self.dev._L.pmb_batch_execute(self.dev._h, self._h))
+
+    def validate(self):
+        """After the first execute, before the device counters are read without a fetch (an
+        all-reduce): the list path's inputs turned out unsorted -> recompute on the event path."""
+        self.dev._check(self.dev._L.pmb_batch_validate(self.dev._h, self._h))
 
     def fetch(self):
         outs, arrays = self.dev._outputs(self.jobs)

@@ -16,6 +16,7 @@
 #include "pmb_probe.cuh"
 #include "pmb_window.cuh"
 #include "pmb_events.cuh"
+#include "pmb_lists.cuh"
 
 using namespace pmb;
 
@@ -35,7 +36,9 @@ struct pmb_ctx {
     int tile_words = 0;      // 0: automatic
     int grid_blocks = 0;     // 0: one per SM
     int block_warps = 16;
-    int path = 0;            // 0 auto, 1 dense shift-window, 2 event-window
+    int path = 0;            // 0 auto, 1 dense shift-window, 2 event-window, 3 lists
+    int list_blocks_per_sm = 0;
+    int list_pairs_limit = 0;    // auto: lists while the expected reverse reads per forward read and 1024 shifts stay below this
     int event_tile_words = 0;
     int event_blocks_per_sm = 0;
     int async_h2d = 0;       // prepare returns before the input copy has finished (see header)
@@ -118,7 +121,18 @@ struct pmb_batch {
     int* d_err = nullptr;
     uint32_t* d_long = nullptr; size_t long_cap = 0;   // [0] = count, [1..] = list
     // event-window path
-    int path = 1;                       // 1 dense, 2 events
+    int path = 1;                       // 1 dense, 2 events, 3 lists
+    // list path (pmb_lists.cuh): job table, entry prefixes (fwd | rev | intervals, n + 1 each),
+    // difference histograms [n][4][stride], edge products [n][2][stride] + direct lags [n][2]
+    bool list_ok = false;               // the inputs qualify for the list path
+    bool list_checked = false;          // an execute on the list path has found the inputs sorted
+    ListJob* d_listjobs = nullptr;
+    unsigned long long* d_list_prefix = nullptr;
+    unsigned long long* d_list_acc = nullptr; size_t list_acc_words = 0;
+    std::vector<unsigned long long> h_list_prefix;
+    std::vector<ListJob> h_listjobs;
+    uint64_t total_words = 0;           // body words of all jobs (tile-size choice of the dense path)
+    bool arrays_planned = false;        // the bit arrays of the dense / event path exist (layout + plan done)
     unsigned long long* d_aux = nullptr; size_t aux_words = 0;   // [n][2][stride] + [n][2]
     EventJob* d_evjobs = nullptr;
     uint32_t ev_total_tiles = 0, ev_tile_words = 0;
@@ -295,6 +309,8 @@ extern "C" int pmb_set_option(pmb_ctx* c, const char* name, int64_t value)
     else if (!strcmp(name, "block_warps")) c->block_warps = (int)value;
     else if (!strcmp(name, "path")) c->path = (int)value;
     else if (!strcmp(name, "event_tile_words")) c->event_tile_words = (int)value;
+    else if (!strcmp(name, "list_blocks_per_sm")) c->list_blocks_per_sm = (int)value;
+    else if (!strcmp(name, "list_pairs_limit")) c->list_pairs_limit = (int)value;
     else if (!strcmp(name, "event_blocks_per_sm")) c->event_blocks_per_sm = (int)value;
     else if (!strcmp(name, "async_h2d")) c->async_h2d = value != 0;
     else if (!strcmp(name, "h2d_growth_x10")) c->h2d_growth_x10 = (int)std::max<int64_t>(10, std::min<int64_t>(value, 100));
@@ -313,7 +329,7 @@ extern "C" int pmb_get_timing(pmb_ctx* c, pmb_timing* t)
         CU_TRY(c, cudaEventElapsedTime(&c->timing.build_ms, c->ev[0], c->ev[1]));
         CU_TRY(c, cudaEventElapsedTime(&c->timing.window_ms, c->ev[1], c->ev[2]));
         CU_TRY(c, cudaEventElapsedTime(&c->timing.total_ms, c->ev[0], c->ev[2]));
-        if (c->timing.path == 2) {
+        if (c->timing.path == 2 || c->timing.path == 3) {
             CU_TRY(c, cudaEventElapsedTime(&c->timing.ev_fwd_ms, c->ev[1], c->evk[0]));
             CU_TRY(c, cudaEventElapsedTime(&c->timing.ev_rev_ms, c->evk[0], c->evk[1]));
             CU_TRY(c, cudaEventElapsedTime(&c->timing.ev_edge_ms, c->evk[1], c->ev[2]));
@@ -358,6 +374,9 @@ extern "C" void pmb_batch_free(pmb_ctx* c, pmb_batch* b)
         if (b->d_tasks) cudaFreeAsync(b->d_tasks, c->stream);
         if (b->d_long64) cudaFreeAsync(b->d_long64, c->stream);
         if (b->d_runs) cudaFreeAsync(b->d_runs, c->stream);
+        if (b->d_listjobs) cudaFreeAsync(b->d_listjobs, c->stream);
+        if (b->d_list_prefix) cudaFreeAsync(b->d_list_prefix, c->stream);
+        if (b->d_list_acc) cudaFreeAsync(b->d_list_acc, c->stream);
         cudaStreamSynchronize(c->stream);
     }
     delete b;
@@ -607,6 +626,134 @@ static int plan_events(pmb_ctx* c, pmb_batch* b)
     return PMB_OK;
 }
 
+// Geometry of the bit arrays of the dense / event path (b->path says which): tile size, halos,
+// where every job's arrays start.  The packed inputs are laid out by prepare_impl.
+static int layout_arrays(pmb_ctx* c, pmb_batch* b)
+{
+    const uint32_t blocks = c->grid_blocks > 0 ? (uint32_t)c->grid_blocks : (uint32_t)c->num_sms;
+    b->halo_words = 4 * b->n_units + 4;
+    uint32_t T = 1024;
+    if (b->path == 2) {
+        T = 64;   // body granule only; the event kernels tile the whole array themselves
+        // windows reach 2*max_shift + read_len beyond the counted range (the stride-2 window of
+        // the reverse reads), plus the idle-lane / upper-neighbour words
+        b->halo_words = ((2 * b->max_shift + b->read_len + 192 + 31) / 32 + 3) & ~3u;
+    } else {
+        if (c->tile_words > 0) T = (uint32_t)c->tile_words;
+        else while (T > 64 && b->total_words / T < 8ull * blocks) T >>= 1;
+        if (T < 64 || (T & 63)) { c->err = "tile_words must be a multiple of 64"; return PMB_ERR_ARG; }
+    }
+    b->tile_words = T;
+    size_t bits_words = 0;
+    for (auto& j : b->jobs) {
+        uint64_t body = (uint64_t)(((j.hi + 31) >> 5) - j.origin_word);
+        j.n_tiles = (uint32_t)((body + T - 1) / T);
+        if (j.n_tiles == 0) j.n_tiles = 1;
+        j.body_words = (uint64_t)j.n_tiles * T;
+        j.array_words = 2 * (size_t)b->halo_words + j.body_words;
+        j.bits = bits_words;
+        if (b->path == 2) {     // F, R of all jobs first (one memset), then all M, then the derived arrays
+            if (!j.autocorr) bits_words += 2 * j.array_words;
+        } else {
+            bits_words += (size_t)arrays_of(j) * j.array_words;
+        }
+    }
+    if (b->path == 2) {
+        b->m_begin = bits_words;
+        for (auto& j : b->jobs)
+            if (j.owner >= 0) j.bits_m = b->jobs[j.owner].bits_m;
+            else if (j.autocorr || (j.mode & MODE_MSCC)) { j.bits_m = bits_words; bits_words += j.array_words; }
+        b->m_end = bits_words;
+        for (auto& j : b->jobs)
+            if (j.owner >= 0) j.bits_d = b->jobs[j.owner].bits_d;
+            else if (!j.autocorr && (j.mode & MODE_MSCC)) { j.bits_d = bits_words; bits_words += j.array_words; }
+        // M is gathered from the sorted intervals (the scatter kernels stay as the fallback)
+        b->gather_k = 0;
+        b->gather_m = b->read_len >= 2;   // rl 1: the second lag is negative
+        for (auto& j : b->jobs)
+            if (j.a.n_intervals >= (1ull << 31)) b->gather_m = false;
+        if (getenv("PMB_NO_GATHER")) b->gather_m = false;     // debug aid: always scatter M
+        b->edge_list_ok = true;
+        for (auto& j : b->jobs)
+            if ((uint64_t)j.array_words * 32 + 32ull * b->stride >= (1ull << 32)) b->edge_list_ok = false;
+        b->pack_reads = getenv("PMB_NO_PACK") == nullptr;      // debug aid: always scatter F, R
+        b->zero_words = b->gather_m ? b->m_begin : b->m_end;
+    }
+    b->bits_words = bits_words;
+    return PMB_OK;
+}
+
+// Device allocations and job / task tables of the dense or event path (after layout_arrays).
+static int plan_arrays(pmb_ctx* c, pmb_batch* b)
+{
+    const size_t n = b->jobs.size();
+    CU_TRY(c, cudaMallocAsync((void**)&b->d_bits_raw,
+                              (std::max<size_t>(b->bits_words, 4) + 2 * (size_t)EV_PAD_WORDS) * 4, c->stream));
+    b->d_bits = b->d_bits_raw + EV_PAD_WORDS;
+    // the pads are only ever read by TMA region overhang (never used); zero them once
+    CU_TRY(c, cudaMemsetAsync(b->d_bits_raw, 0, (size_t)EV_PAD_WORDS * 4, c->stream));
+    CU_TRY(c, cudaMemsetAsync(b->d_bits + std::max<size_t>(b->bits_words, 4), 0, (size_t)EV_PAD_WORDS * 4, c->stream));
+    uint64_t max_iv = 0;
+    for (auto& j : b->jobs) max_iv = std::max<uint64_t>(max_iv, j.a.n_intervals);
+    b->long_cap = (size_t)max_iv + 4;
+    CU_TRY(c, cudaMallocAsync((void**)&b->d_long, b->long_cap * 4, c->stream));
+    // window job tables: one per unit chunk (filled in execute)
+    b->d_jobs_count = (size_t)n * ((b->n_units + 63) / 64 + 1) * 3;
+    CU_TRY(c, cudaMallocAsync((void**)&b->d_jobs, b->d_jobs_count * sizeof(WindowJob), c->stream));
+    const int rc = b->path == 2 ? plan_events(c, b) : plan_windows(c, b);
+    if (rc == PMB_OK) b->arrays_planned = true;
+    return rc;
+}
+
+// List path: job table + the three entry prefixes (forward reads | reverse reads | intervals of
+// the jobs that own a track), accumulators.  No bit arrays.
+static int plan_lists(pmb_ctx* c, pmb_batch* b)
+{
+    const size_t n = b->jobs.size();
+    const size_t stride = b->stride;
+    b->list_acc_words = n * (6 * stride + 2);       // [n][4][stride] differences | [n][2][stride] edge products | [n][2] lags
+    CU_TRY(c, cudaMallocAsync((void**)&b->d_list_acc, b->list_acc_words * 8, c->stream));
+    CU_TRY(c, cudaMallocAsync((void**)&b->d_listjobs, n * sizeof(ListJob), c->stream));
+    CU_TRY(c, cudaMallocAsync((void**)&b->d_list_prefix, 3 * (n + 1) * 8, c->stream));
+    unsigned long long* diff0 = b->d_list_acc;
+    unsigned long long* aux0 = diff0 + n * 4 * stride;
+    unsigned long long* lag0 = aux0 + n * 2 * stride;
+    std::vector<ListJob>& table = b->h_listjobs;
+    std::vector<unsigned long long>& pre = b->h_list_prefix;
+    table.assign(n, ListJob{});
+    pre.assign(3 * (n + 1), 0);
+    for (size_t i = 0; i < n; i++) {
+        const JobPlan& j = b->jobs[i];
+        ListJob e{};
+        const bool mscc = !j.autocorr && (j.mode & MODE_MSCC);
+        if (!j.autocorr) {
+            e.fwd = b->d_in + j.in_fwd; e.n_fwd = (uint32_t)j.a.n_fwd;
+            e.rev = b->d_in + j.in_rev; e.n_rev = (uint32_t)j.a.n_rev;
+            e.flags = (j.mode & MODE_NCC ? EVF_NCC : 0) | (mscc ? EVF_MSCC : 0);
+        } else {
+            e.flags = EVF_AUTOCORR;
+        }
+        if (mscc || j.autocorr) {
+            e.begins = b->d_in + j.in_mb; e.ends = b->d_in + j.in_me; e.n_iv = (uint32_t)j.a.n_intervals;
+        }
+        const size_t io = j.owner >= 0 ? (size_t)j.owner : i;
+        if (j.owner >= 0) e.flags |= EVF_SHARED;
+        e.counters = b->d_counters + i * PMB_NCOUNTERS * stride;
+        e.totals = b->d_counters + n * PMB_NCOUNTERS * stride + 2 * i;
+        e.diff = diff0 + i * 4 * stride;
+        e.aux = aux0 + io * 2 * stride;
+        e.adirect = lag0 + 2 * io;
+        e.lo = j.lo; e.hi = j.hi; e.nbits = j.nbits;
+        table[i] = e;
+        pre[i + 1] = pre[i] + e.n_fwd;
+        pre[(n + 1) + i + 1] = pre[(n + 1) + i] + e.n_rev;
+        pre[2 * (n + 1) + i + 1] = pre[2 * (n + 1) + i] + ((mscc || j.autocorr) && j.owner < 0 ? e.n_iv : 0);
+    }
+    CU_TRY(c, cudaMemcpyAsync(b->d_listjobs, table.data(), n * sizeof(ListJob), cudaMemcpyHostToDevice, c->stream));
+    CU_TRY(c, cudaMemcpyAsync(b->d_list_prefix, pre.data(), pre.size() * 8, cudaMemcpyHostToDevice, c->stream));
+    return PMB_OK;
+}
+
 static int prepare_impl(pmb_ctx* c, const pmb_chrom_args* a, uint32_t n, pmb_batch** out, bool async)
 {
     if (!c || !a || !out || n == 0) return PMB_ERR_ARG;
@@ -672,75 +819,53 @@ static int prepare_impl(pmb_ctx* c, const pmb_chrom_args* a, uint32_t n, pmb_bat
         j.origin_word = (j.lo >> 5) & ~(int64_t)3;
         total_words += (uint64_t)(((j.hi + 31) >> 5) - j.origin_word);
     }
-    // Which algorithm?  The event-window path costs ~ (reads + run edges) x shifts/32, the dense
-    // shift-window path ~ words x shifts; both give identical counts.  auto: events unless the
-    // inputs are so dense that there are more than 4 events per 32-bit word.
+    // Which algorithm?  All three give identical counts.
+    //   lists  (3): cost ~ reads + run edges + PAIRS of entries within max_shift of each other
+    //   events (2): cost ~ (reads + run edges) x shifts/32 + a scan of the arrays
+    //   dense  (1): cost ~ words x shifts
+    // auto: lists while a forward read expects fewer than ~24 reverse reads per 1024 shifts,
+    // else events unless the inputs hold more than 4 events per 32-bit word.
     uint64_t total_events = 0;
+    double expect_pairs = 0, total_fwd = 0;
+    b->list_ok = b->read_len >= 2 && list_smem_bytes(b->max_shift, 4) <= 200 * 1024;
     for (uint32_t i = 0; i < n; i++) {
         total_events += a[i].n_fwd + a[i].n_rev + (b->jobs[i].owner < 0 ? 2 * a[i].n_intervals : 0);
         b->any_ncc |= (a[i].flags & PMB_FLAG_NCC) && !(a[i].flags & PMB_FLAG_AUTOCORR);
         b->any_mscc |= (a[i].flags & PMB_FLAG_MSCC) && !(a[i].flags & PMB_FLAG_AUTOCORR);
         b->any_autocorr |= (a[i].flags & PMB_FLAG_AUTOCORR) != 0;
+        if (a[i].n_fwd >= (1ull << 31) || a[i].n_rev >= (1ull << 31) || a[i].n_intervals >= (1ull << 31) ||
+            b->jobs[i].nbits + b->read_len + b->max_shift + 2 >= (1ull << 32))
+            b->list_ok = false;
+        if (!(a[i].flags & PMB_FLAG_AUTOCORR)) {
+            expect_pairs += (double)a[i].n_fwd * (double)a[i].n_rev * (double)b->n_shifts / (double)b->jobs[i].nbits;
+            total_fwd += (double)a[i].n_fwd;
+        }
     }
-    b->path = c->path == 1 || c->path == 2 ? c->path : (total_events <= 4 * total_words ? 2 : 1);
-    const uint32_t blocks = c->grid_blocks > 0 ? (uint32_t)c->grid_blocks : (uint32_t)c->num_sms;
-    uint32_t T = 1024;
-    if (b->path == 2) {
-        T = 64;   // body granule only; the event kernels tile the whole array themselves
-        // windows reach 2*max_shift + read_len beyond the counted range (the stride-2 window of
-        // the reverse reads), plus the idle-lane / upper-neighbour words
-        b->halo_words = ((2 * b->max_shift + b->read_len + 192 + 31) / 32 + 3) & ~3u;
-    } else {
-        if (c->tile_words > 0) T = (uint32_t)c->tile_words;
-        else while (T > 64 && total_words / T < 8ull * blocks) T >>= 1;
-        if (T < 64 || (T & 63)) { c->err = "tile_words must be a multiple of 64"; return PMB_ERR_ARG; }
-    }
-    b->tile_words = T;
+    if (getenv("PMB_NO_LISTS")) b->list_ok = false;         // debug aid
+    const double pairs_limit = (c->list_pairs_limit > 0 ? c->list_pairs_limit : 24) * ((b->n_shifts + 1023) / 1024);
+    if (c->path == 1 || c->path == 2) b->path = c->path;
+    else if (c->path == 3) {
+        if (!b->list_ok) { c->err = "the list path needs read_len >= 2, max_shift <= 12000 and fewer than 2^31 entries per list"; return PMB_ERR_ARG; }
+        b->path = 3;
+    } else if (b->list_ok && expect_pairs <= pairs_limit * (total_fwd + 1.0)) b->path = 3;
+    else b->path = total_events <= 4 * total_words ? 2 : 1;
+    b->total_words = total_words;
 
-    // pass 2: layout
-    size_t in_words = 0, bits_words = 0;
+    // pass 2: layout of the packed inputs on the device (the bit arrays: layout_arrays)
+    size_t in_words = 0;
     for (uint32_t i = 0; i < n; i++) {
         JobPlan& j = b->jobs[i];
-        uint64_t body = (uint64_t)(((j.hi + 31) >> 5) - j.origin_word);
-        j.n_tiles = (uint32_t)((body + T - 1) / T);
-        if (j.n_tiles == 0) j.n_tiles = 1;
-        j.body_words = (uint64_t)j.n_tiles * T;
-        j.array_words = 2 * (size_t)b->halo_words + j.body_words;
-        j.bits = bits_words;
-        if (b->path == 2) {     // F, R of all jobs first (one memset), then all M, then the derived arrays
-            if (!j.autocorr) bits_words += 2 * j.array_words;
-        } else {
-            bits_words += (size_t)arrays_of(j) * j.array_words;
-        }
         auto take = [&](uint64_t cnt) { size_t o = in_words; in_words += (cnt + 3) & ~3ull; return o; };
         if (!j.autocorr) { j.in_fwd = take(j.a.n_fwd); j.in_rev = take(j.a.n_rev); }
         if (j.owner >= 0) { j.in_mb = b->jobs[j.owner].in_mb; j.in_me = b->jobs[j.owner].in_me; }
         else if ((j.mode & MODE_MSCC) || j.autocorr) { j.in_mb = take(j.a.n_intervals); j.in_me = take(j.a.n_intervals); }
     }
     b->in_words = in_words;
-    if (b->path == 2) {
-        b->m_begin = bits_words;
-        for (auto& j : b->jobs)
-            if (j.owner >= 0) j.bits_m = b->jobs[j.owner].bits_m;
-            else if (j.autocorr || (j.mode & MODE_MSCC)) { j.bits_m = bits_words; bits_words += j.array_words; }
-        b->m_end = bits_words;
-        for (auto& j : b->jobs)
-            if (j.owner >= 0) j.bits_d = b->jobs[j.owner].bits_d;
-            else if (!j.autocorr && (j.mode & MODE_MSCC)) { j.bits_d = bits_words; bits_words += j.array_words; }
-        // M is gathered from the sorted intervals (the scatter kernels stay as the fallback)
-        b->gather_k = 0;
-        b->gather_m = b->read_len >= 2;   // rl 1: the second lag is negative
-        for (auto& j : b->jobs)
-            if (j.a.n_intervals >= (1ull << 31)) b->gather_m = false;
-        if (getenv("PMB_NO_GATHER")) b->gather_m = false;     // debug aid: always scatter M
-        b->edge_list_ok = true;
-        for (auto& j : b->jobs)
-            if ((uint64_t)j.array_words * 32 + 32ull * b->stride >= (1ull << 32)) b->edge_list_ok = false;
-        b->pack_reads = getenv("PMB_NO_PACK") == nullptr;      // debug aid: always scatter F, R
-        b->zero_words = b->gather_m ? b->m_begin : b->m_end;
-    }
-    b->bits_words = bits_words;
     b->counter_words = (size_t)n * PMB_NCOUNTERS * b->stride + (size_t)n * 2;
+    if (b->path != 3) {
+        int rc = layout_arrays(c, b);
+        if (rc != PMB_OK) return rc;
+    }
 
     CU_TRY(c, cudaMallocAsync((void**)&b->d_in, std::max<size_t>(in_words, 4) * 4, c->stream));
     // H2D of the packed inputs.  Synchronous mode: on the compute stream, complete when prepare
@@ -759,7 +884,7 @@ static int prepare_impl(pmb_ctx* c, const pmb_chrom_args* a, uint32_t n, pmb_bat
         // a group is only worth its extra launches when its copy takes a few hundred microseconds:
         // at most "h2d_groups" groups, and none smaller than ~16 MB on average
         uint32_t want = 1;
-        if (async && b->path == 2)
+        if (async && b->path != 1)
             want = c->h2d_min_group_bytes > 0
                        ? (uint32_t)std::min<size_t>((size_t)c->h2d_groups,
                                                     std::max<size_t>(1, total * 4 / (size_t)c->h2d_min_group_bytes))
@@ -767,7 +892,9 @@ static int prepare_impl(pmb_ctx* c, const pmb_chrom_args* a, uint32_t n, pmb_bat
         // Group sizes grow geometrically: the first group is small so the kernels start early,
         // and each later group may be larger because computing on a group takes ~2x as long
         // as copying it (so the copy of group g+1 hides behind the kernels of group g).
-        const double growth = c->h2d_growth_x10 / 10.0;
+        // (The list kernels are ~10x faster than the copy: equal groups, the last one's kernels
+        // are all that is left after the copy ends.)
+        const double growth = b->path == 3 ? 1.0 : c->h2d_growth_x10 / 10.0;
         std::vector<double> cum(want, 1.0);
         {
             double sum = 0, w = 1;
@@ -794,24 +921,10 @@ static int prepare_impl(pmb_ctx* c, const pmb_chrom_args* a, uint32_t n, pmb_bat
         // table uploads are small H2D copies on the compute stream, and behind 90 MB .. 1.2 GB of
         // inputs on the same copy engine they held the first kernel back by the whole input copy
         // (measured: 16 read sets, execute started 22 ms late; one genome, ~1 ms).
-        CU_TRY(c, cudaMallocAsync((void**)&b->d_bits_raw,
-                                  (std::max<size_t>(bits_words, 4) + 2 * (size_t)EV_PAD_WORDS) * 4, c->stream));
-        b->d_bits = b->d_bits_raw + EV_PAD_WORDS;
-        // the pads are only ever read by TMA region overhang (never used); zero them once
-        CU_TRY(c, cudaMemsetAsync(b->d_bits_raw, 0, (size_t)EV_PAD_WORDS * 4, c->stream));
-        CU_TRY(c, cudaMemsetAsync(b->d_bits + std::max<size_t>(bits_words, 4), 0, (size_t)EV_PAD_WORDS * 4, c->stream));
         CU_TRY(c, cudaMallocAsync((void**)&b->d_counters, b->counter_words * 8, c->stream));
         CU_TRY(c, cudaMallocAsync((void**)&b->d_err, 4 * (4 + 128), c->stream));
-        uint64_t max_iv = 0;
-        for (auto& j : b->jobs) max_iv = std::max<uint64_t>(max_iv, j.a.n_intervals);
-        b->long_cap = (size_t)max_iv + 4;
-        CU_TRY(c, cudaMallocAsync((void**)&b->d_long, b->long_cap * 4, c->stream));
-        // window job tables: one per unit chunk (filled in execute)
-        b->d_jobs_count = (size_t)n * ((b->n_units + 63) / 64 + 1) * 3;
-        CU_TRY(c, cudaMallocAsync((void**)&b->d_jobs, b->d_jobs_count * sizeof(WindowJob), c->stream));
-
         {
-            int rc = b->path == 2 ? plan_events(c, b) : plan_windows(c, b);
+            int rc = b->path == 3 ? plan_lists(c, b) : plan_arrays(c, b);
             if (rc != PMB_OK) return rc;
         }
         if (async) {
@@ -863,7 +976,7 @@ static int prepare_impl(pmb_ctx* c, const pmb_chrom_args* a, uint32_t n, pmb_bat
     }
     // synchronous mode: host arrays may be released by the caller; asynchronous mode: they are
     // still being read by the copy engine until the first execute of this batch has completed
-    if (!async || b->path != 2) CU_TRY(c, cudaStreamSynchronize(c->stream));
+    if (!async || b->path == 1) CU_TRY(c, cudaStreamSynchronize(c->stream));
     guard.armed = false;
     *out = b;
     return PMB_OK;
@@ -905,6 +1018,110 @@ static cudaError_t launch_window(pmb_ctx* c, int variant, const WindowParams& P,
         default: PMB_LAUNCH(V1);
     }
 #undef PMB_LAUNCH
+}
+
+// ------------------------------------------------------------------ batch: execute (list path)
+static void list_attributes()
+{
+    // once per process: the kernels' dynamic shared memory may exceed 48 KB for large max_shift
+    static bool done = false;
+    if (done) return;
+    const int cap = 200 * 1024;
+    cudaFuncSetAttribute(list_fwd_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, cap);
+    cudaFuncSetAttribute(list_fwd_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, cap);
+    cudaFuncSetAttribute(list_fwd_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, cap);
+    cudaFuncSetAttribute(list_rev_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, cap);
+    cudaFuncSetAttribute(list_rev_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, cap);
+    cudaFuncSetAttribute(list_edge_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, cap);
+    done = true;
+}
+
+static int execute_lists(pmb_ctx* c, pmb_batch* b)
+{
+    cudaStream_t st = c->stream;
+    const size_t n = b->jobs.size();
+    uint32_t launches = 0;
+    list_attributes();
+    CU_TRY(c, cudaEventRecord(c->ev[0], st));
+    {
+        ZeroSegs z{};
+        z.p[0] = (uint4*)b->d_counters;  z.n16[0] = b->counter_words * 8 / 16;
+        z.p[1] = (uint4*)b->d_list_acc;  z.n16[1] = b->list_acc_words * 8 / 16;
+        z.p[2] = (uint4*)b->d_err;       z.n16[2] = 4 * (4 + 128) / 16;
+        zero_segments_kernel<<<c->num_sms, 512, 0, st>>>(z);
+        launches++;
+    }
+    CU_TRY(c, cudaEventRecord(c->ev[1], st));
+    const bool grouped = b->h2d_pending && b->groups.size() > 1;
+    const size_t n_pass = grouped ? b->groups.size() : 1;
+    if (b->h2d_pending && !grouped)
+        for (auto& gr : b->groups) CU_TRY(c, cudaStreamWaitEvent(st, gr.done, 0));
+    ListParams P{};
+    P.jobs = b->d_listjobs;
+    P.max_shift = b->max_shift;
+    P.read_len = b->read_len;
+    P.stride = b->stride;
+    P.flags = b->d_err;
+    const uint32_t bps = c->list_blocks_per_sm > 0 ? (uint32_t)c->list_blocks_per_sm : 2;
+    const unsigned long long* pre = b->h_list_prefix.data();
+    auto grid_for = [&](unsigned long long items) {
+        return (unsigned)std::max<unsigned long long>(1, std::min<unsigned long long>((items + 2047) / 2048,
+                                                                                      (unsigned long long)c->num_sms * bps));
+    };
+    const size_t sm_f = list_smem_bytes(b->max_shift, b->any_mscc ? 4 : 1), sm_2 = list_smem_bytes(b->max_shift, 2);
+    for (size_t pass = 0; pass < n_pass; pass++) {
+        const uint32_t jl = grouped ? b->groups[pass].job_lo : 0, jh = grouped ? b->groups[pass].job_hi : (uint32_t)n;
+        if (grouped) CU_TRY(c, cudaStreamWaitEvent(st, b->groups[pass].done, 0));
+        for (int kind = 0; kind < 3; kind++) {      // forward reads | reverse reads | run edges
+            const unsigned long long* pk = pre + kind * (n + 1);
+            const unsigned long long items = pk[jh] - pk[jl];
+            if (items) {
+                P.prefix = b->d_list_prefix + kind * (n + 1);
+                P.job_lo = jl; P.job_hi = jh;
+                const unsigned grid = grid_for(items);
+                if (kind == 0) {
+                    if (b->any_ncc && b->any_mscc) list_fwd_kernel<true, true><<<grid, LIST_THREADS, sm_f, st>>>(P);
+                    else if (b->any_ncc) list_fwd_kernel<true, false><<<grid, LIST_THREADS, sm_f, st>>>(P);
+                    else list_fwd_kernel<false, true><<<grid, LIST_THREADS, sm_f, st>>>(P);
+                } else if (kind == 1) {
+                    if (b->any_mscc) list_rev_kernel<true><<<grid, LIST_THREADS, sm_2, st>>>(P);
+                    else list_rev_kernel<false><<<grid, LIST_THREADS, 0, st>>>(P);
+                } else {
+                    list_edge_kernel<<<grid, LIST_THREADS, sm_2, st>>>(P);
+                }
+                launches++;
+            }
+            if (kind < 2 && pass + 1 == n_pass) CU_TRY(c, cudaEventRecord(c->evk[kind], st));   // (per-kernel split: ungrouped passes only)
+        }
+    }
+    if (b->any_mscc || b->any_autocorr) {
+        list_finalize_kernel<<<(unsigned)n, 256, 0, st>>>(b->d_listjobs, b->stride, b->max_shift);
+        launches++;
+    }
+    CU_TRY(c, cudaGetLastError());
+    CU_TRY(c, cudaEventRecord(c->ev[2], st));
+    b->h2d_pending = false;
+    c->timing.launches = launches;
+    c->timing.window_launches = launches - 1;
+    c->timing.window_word_shift_pairs = 0;
+    c->timing.path = 3;
+    c->timing.build_ms = c->timing.window_ms = c->timing.total_ms = -1.f;
+    return PMB_OK;
+}
+
+// The list path found its inputs unsorted (or the intervals overlapping): the batch moves to
+// the event path for good -- bit arrays are planned now, from the inputs already in HBM -- and
+// is executed again.
+static int execute_events(pmb_ctx* c, pmb_batch* b);
+static int fallback_to_events(pmb_ctx* c, pmb_batch* b)
+{
+    b->path = 2;
+    if (!b->arrays_planned) {
+        int rc = layout_arrays(c, b);
+        if (rc == PMB_OK) rc = plan_arrays(c, b);
+        if (rc != PMB_OK) return rc;
+    }
+    return execute_events(c, b);
 }
 
 // ------------------------------------------------------------------ batch: execute (event path)
@@ -1143,7 +1360,7 @@ extern "C" int pmb_batch_execute(pmb_ctx* c, pmb_batch* b)
     if (!c || !b) return PMB_ERR_ARG;
     return guarded(c, [&]() -> int {
         CU_TRY(c, cudaSetDevice(c->device));
-        return b->path == 2 ? execute_events(c, b) : execute_dense(c, b);
+        return b->path == 3 ? execute_lists(c, b) : b->path == 2 ? execute_events(c, b) : execute_dense(c, b);
     });
 }
 
@@ -1264,23 +1481,64 @@ extern "C" int pmb_batch_counters(pmb_ctx* c, pmb_batch* b, void** dev_ptr, uint
     return PMB_OK;
 }
 
+// After an execute on the list path: has the device found the inputs unsorted / overlapping?  Then
+// the batch moves to the event path and is executed again (synchronises the stream).
+static int settle_path(pmb_ctx* c, pmb_batch* b)
+{
+    if (b->path != 3 || b->list_checked) return PMB_OK;
+    int* h_flags = (int*)((char*)c->h_stage + c->h_stage_bytes - 16);
+    CU_TRY(c, cudaMemcpyAsync(h_flags, b->d_err, 8, cudaMemcpyDeviceToHost, c->stream));
+    CU_TRY(c, cudaStreamSynchronize(c->stream));
+    if (h_flags[1] && !h_flags[0]) return fallback_to_events(c, b);
+    b->list_checked = true;     // the inputs are resident: what held for this execute holds for the next
+    return PMB_OK;
+}
+
+static int ensure_stage(pmb_ctx* c, size_t bytes)
+{
+    if (c->h_stage_bytes >= bytes) return PMB_OK;
+    if (c->h_stage) cudaFreeHost(c->h_stage);
+    c->h_stage = nullptr;
+    c->h_stage_bytes = 0;
+    CU_TRY(c, cudaHostAlloc(&c->h_stage, bytes, cudaHostAllocDefault));
+    c->h_stage_bytes = bytes;
+    return PMB_OK;
+}
+
+extern "C" int pmb_batch_validate(pmb_ctx* c, pmb_batch* b)
+{
+    if (!c || !b) return PMB_ERR_ARG;
+    return guarded(c, [&]() -> int {
+        CU_TRY(c, cudaSetDevice(c->device));
+        int rc = ensure_stage(c, b->counter_words * 8 + 32);
+        return rc == PMB_OK ? settle_path(c, b) : rc;
+    });
+}
+
 extern "C" int pmb_batch_fetch(pmb_ctx* c, pmb_batch* b, pmb_chrom_out* o)
 {
     if (!c || !b || !o) return PMB_ERR_ARG;
     CU_TRY(c, cudaSetDevice(c->device));
-    const size_t bytes = b->counter_words * 8 + 16;
-    if (c->h_stage_bytes < bytes) {
-        if (c->h_stage) cudaFreeHost(c->h_stage);
-        c->h_stage = nullptr;
-        c->h_stage_bytes = 0;
-        CU_TRY(c, cudaHostAlloc(&c->h_stage, bytes, cudaHostAllocDefault));
-        c->h_stage_bytes = bytes;
+    const size_t bytes = b->counter_words * 8 + 32;
+    {
+        int rc = ensure_stage(c, bytes);
+        if (rc != PMB_OK) return rc;
     }
     int64_t* h = (int64_t*)c->h_stage;
     int* h_err = (int*)((char*)c->h_stage + b->counter_words * 8);
     CU_TRY(c, cudaMemcpyAsync(h, b->d_counters, b->counter_words * 8, cudaMemcpyDeviceToHost, c->stream));
-    CU_TRY(c, cudaMemcpyAsync(h_err, b->d_err, 4, cudaMemcpyDeviceToHost, c->stream));
+    CU_TRY(c, cudaMemcpyAsync(h_err, b->d_err, 8, cudaMemcpyDeviceToHost, c->stream));
     CU_TRY(c, cudaStreamSynchronize(c->stream));
+    if (b->path == 3 && !b->list_checked && h_err[1] && !h_err[0]) {
+        // unsorted input on the list path: recompute on the event path, then read again
+        int rc = guarded(c, [&]() -> int { return fallback_to_events(c, b); });
+        if (rc != PMB_OK) return rc;
+        CU_TRY(c, cudaMemcpyAsync(h, b->d_counters, b->counter_words * 8, cudaMemcpyDeviceToHost, c->stream));
+        CU_TRY(c, cudaMemcpyAsync(h_err, b->d_err, 8, cudaMemcpyDeviceToHost, c->stream));
+        CU_TRY(c, cudaStreamSynchronize(c->stream));
+    } else if (b->path == 3) {
+        b->list_checked = true;
+    }
     if (*h_err) {
         c->err = "a read position or mappability interval lies beyond chrom_len + read_len + "
                  "max_shift + 100 bits";

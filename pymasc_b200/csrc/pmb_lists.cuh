@@ -1,0 +1,489 @@
+// pmb_lists.cuh -- the LIST path (sm_100a): the same per-shift counts as the shift-window and
+// event-window kernels, computed straight from the SORTED position and interval lists the host
+// hands over.  No bit array is ever built.
+//
+// Every count of the reference's loop (PyMaSC/core/bitarray/mscc.pyx:288-317) is a sum over
+// pairs of list entries that lie within max_shift of each other:
+//
+//   ncc[k]  = #{(p, q): q - p = k}                       p forward 5' end, q reverse 5' end   (:314)
+//   mscc[k] = the same pairs with M[p] and M[p+rl-1-k]                                        (:305)
+//   mfwd[k] = sum_p M[p] M[p+rl-1-k]    a step function of k per read: +1 where a mappable
+//             run enters the window, -1 where it leaves -> a DIFFERENCE histogram, prefix-
+//             summed once at the end                                                          (:303)
+//   mrev[k] = sum_q M[q-k] M[q+rl-1-2k] the product of two step functions (runs met at stride
+//             1 and at stride 2): merge the two run lists, again +1 / -1 per piece            (:304)
+//   dmp[k]  = A[rl-1-k], A[s] = sum_j Mc[j] M[j+s]: its second difference is a sum over pairs
+//             of run edges; two directly counted lags anchor it (as on the event path)        (:291-298)
+//
+// With 20 M reads on hg38 a forward read sees ~3 reverse reads and ~1 run edge inside its 1000
+// shifts, so a read costs a few histogram updates instead of a 1000-bit window per counter.
+// Histograms live in shared memory (ATOMS.POPC.INC: ~11 updates/clk/SM measured on B200,
+// profiles/r02_atom_probe.jsonl -- the cost is per instruction, whatever the bins), one copy
+// per CTA, flushed to the 64-bit global counters when the CTA changes chromosome.
+//
+// Mapping.  One THREAD per list entry.  A CTA owns a contiguous range of the batch's entries,
+// cut into per-chromosome segments; inside a segment every warp owns a contiguous sub-range and
+// walks it 32 entries at a time with warp-uniform cursors into the other lists: a gallop from
+// the cursor bounds the window, a per-lane binary search (6-7 L1-resident probes) finds each
+// entry's own start.  Warps meet only where the CTA changes chromosome.
+//
+// Preconditions, verified on the device (flag -> the host re-runs the batch on the event path):
+// reads sorted; intervals sorted and disjoint.  Exact integer arithmetic throughout; the
+// thread-for-thread CPU restatement of this file is oracle/list_model.py.
+#pragma once
+#include <stdint.h>
+#include <cuda_runtime.h>
+
+#include "pmb_events.cuh"   // EVF_*, C_*, block_scan_inplace
+
+namespace pmb {
+
+struct ListJob {
+    const uint32_t* fwd;
+    const uint32_t* rev;
+    const uint32_t* begins;         // the owner's intervals for a job that shares its track
+    const uint32_t* ends;
+    uint32_t n_fwd, n_rev, n_iv, flags;
+    unsigned long long* counters;   // [5][stride]
+    unsigned long long* totals;     // [2]
+    unsigned long long* diff;       // [4][stride]: mfwd +, mfwd -, mrev +, mrev -
+    unsigned long long* aux;        // [2][stride]: run-edge products (the owner's)
+    unsigned long long* adirect;    // [2]: the two directly counted lags (the owner's)
+    long long lo, hi;               // counted range, chromosome bits
+    unsigned long long nbits;
+};
+
+struct ListParams {
+    const ListJob* jobs;
+    const unsigned long long* prefix;   // [n_jobs + 1]: entries of this kernel's list before each job
+    uint32_t job_lo, job_hi;            // this launch covers these jobs (everything, or one H2D group)
+    uint32_t max_shift, read_len, stride;
+    int* flags;                         // [0] position beyond the array, [1] input not sorted / disjoint
+};
+
+constexpr int LIST_THREADS = 512;
+constexpr uint32_t LIST_NONE = 0xFFFFFFFFu;
+
+__host__ __device__ constexpr size_t list_smem_bytes(uint32_t max_shift, int n_hist)
+{
+    return (size_t)n_hist * (max_shift + 2) * 4;      // bins 0 .. max_shift and a dump bin
+}
+
+// ---------------------------------------------------------------- searches
+// number of a[0..n) that are < key: warp-cooperative 33-ary search (one probe per lane and round)
+__device__ __forceinline__ uint32_t warp_lower_bound(const uint32_t* __restrict__ a, uint32_t n, uint32_t key, int lane)
+{
+    uint32_t lo = 0, hi = n;                    // the answer lies in [lo, hi]
+    while (hi - lo >= 33) {
+        const uint32_t width = hi - lo;
+        const uint32_t pi = lo + (uint32_t)(((uint64_t)width * (lane + 1)) / 33);
+        const uint32_t cnt = __popc(__ballot_sync(0xFFFFFFFFu, __ldg(a + pi) < key));     // a prefix of the lanes
+        const uint32_t nlo = cnt ? lo + (uint32_t)(((uint64_t)width * cnt) / 33) + 1 : lo;
+        const uint32_t nhi = cnt < 32 ? lo + (uint32_t)(((uint64_t)width * (cnt + 1)) / 33) : hi;
+        lo = nlo; hi = nhi;
+    }
+    const uint32_t pi = lo + lane;
+    return lo + __popc(__ballot_sync(0xFFFFFFFFu, pi < hi && __ldg(a + pi) < key));
+}
+
+// first index in [lo, hi] with a[index] >= key, given a[< lo] < key and (hi == n or a[hi] >= key)
+__device__ __forceinline__ uint32_t lower_bound_in(const uint32_t* __restrict__ a, uint32_t lo, uint32_t hi, uint32_t key)
+{
+    while (lo < hi) {
+        const uint32_t mid = (lo + hi) >> 1;
+        if (__ldg(a + mid) < key) lo = mid + 1; else hi = mid;
+    }
+    return lo;
+}
+
+// warp-uniform: from a cursor with a[< cur] < every key of the group, an index `hi` with
+// hi == n or a[hi] >= key_max (doubling steps; one or two probes for evenly spread lists)
+__device__ __forceinline__ uint32_t gallop(const uint32_t* __restrict__ a, uint32_t n, uint32_t cur, uint32_t key_max)
+{
+    uint32_t step = 48;
+    for (;;) {
+        if (n - cur <= step) return n;
+        if (__ldg(a + cur + step) >= key_max) return cur + step;
+        cur += step;                            // everything up to here is below every later key, too
+        step <<= 1;
+    }
+}
+
+// per-thread lower bound over the whole array by doubling steps from `start` (run edges: the
+// answer lies a few entries from the thread's own interval)
+__device__ __forceinline__ uint32_t lower_bound_near(const uint32_t* __restrict__ a, uint32_t n, uint32_t start, long long key)
+{
+    if (key <= 0) return 0;
+    if (key > 0xFFFFFFFFll) return n;
+    const uint32_t k = (uint32_t)key;
+    uint32_t lo, hi;
+    if (start < n && __ldg(a + start) >= k) {   // answer in [0, start]
+        hi = start;
+        uint32_t step = 1;
+        for (;;) {
+            if (hi < step) { lo = 0; break; }
+            const uint32_t c = hi - step;
+            if (__ldg(a + c) < k) { lo = c + 1; break; }
+            hi = c;
+            step <<= 1;
+        }
+    } else {                                    // answer in (start, n]
+        lo = min(start + 1, n);
+        uint32_t step = 1;
+        for (;;) {
+            if (n - lo <= step) { hi = n; break; }
+            const uint32_t c = lo + step;
+            if (__ldg(a + c) >= k) { hi = c; break; }
+            lo = c + 1;
+            step <<= 1;
+        }
+    }
+    return lower_bound_in(a, lo, hi, k);
+}
+
+// ---------------------------------------------------------------- the CTA / segment / warp skeleton
+// body(job, J, w0, w1): called by every warp with its sub-range [w0, w1) of the job's entries
+// flush(job, J): called by the whole CTA (between barriers) when a segment ends
+template <class Body, class Flush>
+__device__ __forceinline__ void list_segments(const ListParams& P, int warp, int n_warps, Body&& body, Flush&& flush)
+{
+    const unsigned long long g0 = P.prefix[P.job_lo], g1 = P.prefix[P.job_hi];
+    const unsigned long long N = g1 - g0;
+    const unsigned long long c_lo = g0 + (N * blockIdx.x) / gridDim.x;
+    const unsigned long long c_hi = g0 + (N * (blockIdx.x + 1)) / gridDim.x;
+    if (c_lo >= c_hi) return;
+    uint32_t job = P.job_lo;
+    while (P.prefix[job + 1] <= c_lo) job++;
+    for (unsigned long long pos = c_lo; pos < c_hi; ++job) {
+        const unsigned long long jb = P.prefix[job], je = P.prefix[job + 1];
+        if (je <= pos) continue;                                // a job without entries
+        const unsigned long long seg_hi = c_hi < je ? c_hi : je;
+        const ListJob& J = P.jobs[job];
+        const uint32_t s0 = (uint32_t)(pos - jb), s1 = (uint32_t)(seg_hi - jb);
+        const uint32_t len = s1 - s0;
+        const uint32_t chunk = (((len + n_warps - 1) / n_warps) + 31u) & ~31u;
+        const unsigned long long w0 = (unsigned long long)s0 + (unsigned long long)warp * chunk;
+        if (w0 < s1) body(job, J, (uint32_t)w0, (uint32_t)min((unsigned long long)s1, w0 + chunk));
+        __syncthreads();
+        flush(job, J);
+        __syncthreads();
+        pos = seg_hi;
+    }
+}
+
+// add the non-zero bins of a shared-memory histogram to 64-bit global counters and clear them
+__device__ __forceinline__ void flush_hist(uint32_t* h, uint32_t n_bins, unsigned long long* dst)
+{
+    for (uint32_t i = threadIdx.x; i < n_bins; i += blockDim.x) {
+        const uint32_t v = h[i];
+        if (v) { atomicAdd(dst + i, (unsigned long long)v); h[i] = 0; }
+    }
+}
+
+// ---------------------------------------------------------------- forward reads: ncc, mscc, d(mfwd)
+template <bool NCC, bool MSCC>
+__global__ void __launch_bounds__(LIST_THREADS, 2) list_fwd_kernel(const ListParams P)
+{
+    extern __shared__ uint32_t lsm[];
+    const uint32_t D = P.max_shift, S2 = D + 2, DUMP = D + 1;
+    uint32_t* h_ncc = lsm;
+    uint32_t* h_mscc = lsm + S2;
+    uint32_t* h_fp = lsm + 2 * S2;
+    uint32_t* h_fm = lsm + 3 * S2;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, n_warps = blockDim.x >> 5;
+    for (uint32_t i = threadIdx.x; i < (MSCC ? 4 : 1) * S2; i += blockDim.x) lsm[i] = 0;
+    __syncthreads();
+    const uint32_t rl1 = P.read_len - 1;
+    bool bad_order = false, bad_range = false;
+
+    list_segments(P, warp, n_warps,
+        [&](uint32_t, const ListJob& J, uint32_t w0, uint32_t w1) {
+            const uint32_t* __restrict__ fwd = J.fwd;
+            const uint32_t* __restrict__ rev = J.rev;
+            const uint32_t* __restrict__ begins = J.begins;
+            const uint32_t* __restrict__ ends = J.ends;
+            const uint32_t nR = J.n_rev, nI = J.n_iv;
+            const bool job_ncc = NCC && (J.flags & EVF_NCC);
+            const bool job_mscc = MSCC && (J.flags & EVF_MSCC) && nI;
+            const long long lo = J.lo, hi = J.hi;
+            const unsigned long long nbits = J.nbits;
+            const uint32_t p_first = __ldg(fwd + w0);
+            uint32_t JR = warp_lower_bound(rev, nR, p_first, lane);                          // reverse reads below p
+            uint32_t CI = job_mscc ? warp_lower_bound(begins, nI, p_first + rl1, lane) : 0;  // runs beginning below p+rl-1
+            uint32_t tot = 0;
+            for (uint32_t base = w0; base < w1; base += 32) {
+                const uint32_t i = base + lane;
+                const uint32_t n_act = min(32u, w1 - base);
+                const bool act = lane < (int)n_act;
+                uint32_t p = __ldg(fwd + (act ? i : w1 - 1));
+                uint32_t pprev = __shfl_up_sync(0xFFFFFFFFu, p, 1);
+                if (lane == 0) pprev = base ? __ldg(fwd + base - 1) : LIST_NONE;
+                bad_order |= act && pprev != LIST_NONE && p < pprev;
+                bad_range |= act && p >= nbits;
+                const bool valid = act && p != pprev && (long long)p >= lo && (long long)p < hi && p < nbits;
+                tot += valid;
+                const uint32_t p_max = __shfl_sync(0xFFFFFFFFu, p, n_act - 1);
+                // this read's first reverse read: q >= p
+                const uint32_t HR = gallop(rev, nR, JR, p_max);
+                uint32_t j = lower_bound_in(rev, JR, HR, p);
+                JR = __shfl_sync(0xFFFFFFFFu, j, n_act - 1);
+                // mappable runs: c = last run that begins below x_top = p + rl - 1
+                const uint32_t x_top = p + rl1;
+                int c = -1;
+                bool mp = false;
+                if (job_mscc) {
+                    const uint32_t HI = gallop(begins, nI, CI, p_max + rl1);
+                    const uint32_t c1 = lower_bound_in(begins, CI, HI, x_top);
+                    CI = __shfl_sync(0xFFFFFFFFu, c1, n_act - 1);
+                    c = (int)c1 - 1;
+                    int cp = c;
+                    while (cp >= 0 && __ldg(begins + cp) >= p) cp--;
+                    mp = valid && cp >= 0 && p <= __ldg(ends + cp);                          // M[p]
+                }
+                if (!valid) continue;
+                // the run in the window that the next shifts can meet: x = x_top - k in (b, e]  <=>  k in [k1, k2]
+                uint32_t k1 = LIST_NONE, k2 = LIST_NONE;
+                auto load_run = [&]() {
+                    const uint32_t b = __ldg(begins + c), e = __ldg(ends + c);
+                    k2 = x_top - b - 1;
+                    k1 = x_top - min(e, x_top);
+                    if (e > b) {                        // the run enters the window at k1 and leaves after k2
+                        atomicAdd(h_fp + min(k1, DUMP), 1u);
+                        atomicAdd(h_fm + min(k2 + 1, DUMP), 1u);
+                    }
+                };
+                if (MSCC && mp && c >= 0) load_run(); else mp = false;
+                uint32_t qprev = LIST_NONE;
+                for (; j < nR; ++j) {
+                    const uint32_t q = __ldg(rev + j);
+                    const uint32_t k = q - p;
+                    if (k > D) break;
+                    if (q == qprev) continue;           // a bit is set once (mscc.pyx:416-418)
+                    qprev = q;
+                    if (job_ncc) atomicAdd(h_ncc + k, 1u);
+                    if (MSCC && mp) {
+                        while (k > k2 && c > 0) { c--; load_run(); }
+                        if (k >= k1 && k <= k2) atomicAdd(h_mscc + k, 1u);
+                    }
+                }
+                if (MSCC && mp)
+                    while (k2 < D && c > 0) { c--; load_run(); }      // the window's remaining runs
+            }
+            for (int o = 16; o; o >>= 1) tot += __shfl_xor_sync(0xFFFFFFFFu, tot, o);
+            if (lane == 0 && tot) atomicAdd(J.totals, (unsigned long long)tot);            // bit_array_num_bits_set
+        },
+        [&](uint32_t, const ListJob& J) {
+            if (NCC) flush_hist(h_ncc, D + 1, J.counters + (size_t)C_NCC * P.stride);
+            if (MSCC) {
+                flush_hist(h_mscc, D + 1, J.counters + (size_t)C_MSCC * P.stride);
+                flush_hist(h_fp, D + 1, J.diff);
+                flush_hist(h_fm, D + 1, J.diff + P.stride);
+                if (threadIdx.x == 0) { h_fp[DUMP] = 0; h_fm[DUMP] = 0; }
+            }
+        });
+    if (bad_range) atomicExch(P.flags, 1);
+    if (bad_order) atomicExch(P.flags + 1, 1);
+}
+
+// ---------------------------------------------------------------- reverse reads: d(mrev), strand total
+template <bool MSCC>
+__global__ void __launch_bounds__(LIST_THREADS, 2) list_rev_kernel(const ListParams P)
+{
+    extern __shared__ uint32_t lsm[];
+    const uint32_t D = P.max_shift, S2 = D + 2;
+    uint32_t* h_rp = lsm;
+    uint32_t* h_rm = lsm + S2;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, n_warps = blockDim.x >> 5;
+    if (MSCC) {
+        for (uint32_t i = threadIdx.x; i < 2 * S2; i += blockDim.x) lsm[i] = 0;
+        __syncthreads();
+    }
+    const uint32_t rl1 = P.read_len - 1;
+    bool bad_order = false, bad_range = false;
+
+    list_segments(P, warp, n_warps,
+        [&](uint32_t, const ListJob& J, uint32_t w0, uint32_t w1) {
+            const uint32_t* __restrict__ rev = J.rev;
+            const uint32_t* __restrict__ begins = J.begins;
+            const uint32_t* __restrict__ ends = J.ends;
+            const uint32_t nI = J.n_iv;
+            const bool job_mscc = MSCC && (J.flags & EVF_MSCC) && nI;
+            const long long lo = J.lo, hi = J.hi;
+            const unsigned long long nbits = J.nbits;
+            uint32_t CI = job_mscc ? warp_lower_bound(begins, nI, __ldg(rev + w0) + rl1, lane) : 0;
+            uint32_t tot = 0;
+            for (uint32_t base = w0; base < w1; base += 32) {
+                const uint32_t n_act = min(32u, w1 - base);
+                const bool act = lane < (int)n_act;
+                const uint32_t q = __ldg(rev + (act ? base + lane : w1 - 1));
+                uint32_t qprev = __shfl_up_sync(0xFFFFFFFFu, q, 1);
+                if (lane == 0) qprev = base ? __ldg(rev + base - 1) : LIST_NONE;
+                bad_order |= act && qprev != LIST_NONE && q < qprev;
+                bad_range |= act && q >= nbits;
+                const bool valid = act && q != qprev && q < nbits;
+                tot += valid && (long long)q >= lo && (long long)q < hi;
+                if (!job_mscc) continue;
+                const uint32_t t = q + rl1;
+                const uint32_t q_max = __shfl_sync(0xFFFFFFFFu, q, n_act - 1);
+                const uint32_t HI = gallop(begins, nI, CI, q_max + rl1);
+                const uint32_t c1 = lower_bound_in(begins, CI, HI, t);
+                CI = __shfl_sync(0xFFFFFFFFu, c1, n_act - 1);
+                // shifts whose j = q - k lies in the counted range
+                const long long ka_l = (long long)q - hi + 1, kb_l = (long long)q - lo;
+                const int ka = ka_l > 0 ? (int)min(ka_l, (long long)D + 1) : 0;
+                const int kb = kb_l < (long long)D ? (int)max(kb_l, -1ll) : (int)D;
+                int cB = (int)c1 - 1;                   // last run that begins below t = q + rl - 1
+                int cA = cB;                            // ... below q
+                while (cA >= 0 && __ldg(begins + cA) >= q) cA--;
+                if (!valid || ka > kb || cA < 0) continue;
+                // M[q-k]: run (b, e] <=> k in [a1, a2];  M[t-2k]: run (b, e] <=> k in [b1, b2]
+                uint32_t a1, a2, b1, b2;
+                auto load_a = [&]() {
+                    const uint32_t b = __ldg(begins + cA), e = __ldg(ends + cA);
+                    a1 = q - min(e, q); a2 = q - b - 1;
+                };
+                auto load_b = [&]() {
+                    const uint32_t b = __ldg(begins + cB), e = __ldg(ends + cB);
+                    b1 = (t - min(e, t) + 1) >> 1; b2 = (t - b - 1) >> 1;
+                };
+                load_a();
+                load_b();
+                for (;;) {
+                    if (a1 > (uint32_t)kb || b1 > (uint32_t)kb) break;
+                    const uint32_t s = max(max(a1, b1), (uint32_t)ka), e = min(min(a2, b2), (uint32_t)kb);
+                    if (s <= e) {                       // both mappable for k in [s, e]
+                        atomicAdd(h_rp + s, 1u);
+                        atomicAdd(h_rm + e + 1, 1u);
+                    }
+                    if (min(a2, b2) >= (uint32_t)kb) break;
+                    if (a2 <= b2) { if (cA == 0) break; cA--; load_a(); }
+                    else { if (cB == 0) break; cB--; load_b(); }
+                }
+            }
+            for (int o = 16; o; o >>= 1) tot += __shfl_xor_sync(0xFFFFFFFFu, tot, o);
+            if (lane == 0 && tot) atomicAdd(J.totals + 1, (unsigned long long)tot);
+        },
+        [&](uint32_t, const ListJob& J) {
+            if (MSCC) {
+                flush_hist(h_rp, D + 1, J.diff + 2 * (size_t)P.stride);
+                flush_hist(h_rm, D + 1, J.diff + 3 * (size_t)P.stride);
+                if (threadIdx.x == 0) h_rm[D + 1] = 0;
+            }
+        });
+    if (bad_range) atomicExch(P.flags, 1);
+    if (bad_order) atomicExch(P.flags + 1, 1);
+}
+
+// ---------------------------------------------------------------- mappable runs: edge products, direct lags
+// (entries = the intervals of the jobs that OWN a track; followers and NCC-only jobs have none)
+__global__ void __launch_bounds__(LIST_THREADS, 2) list_edge_kernel(const ListParams P)
+{
+    extern __shared__ uint32_t lsm[];
+    const uint32_t D = P.max_shift, S2 = D + 2;
+    uint32_t* h_plus = lsm;
+    uint32_t* h_minus = lsm + S2;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, n_warps = blockDim.x >> 5;
+    for (uint32_t i = threadIdx.x; i < 2 * S2; i += blockDim.x) lsm[i] = 0;
+    __syncthreads();
+    bool bad_order = false, bad_range = false;
+
+    list_segments(P, warp, n_warps,
+        [&](uint32_t, const ListJob& J, uint32_t w0, uint32_t w1) {
+            const uint32_t* __restrict__ begins = J.begins;
+            const uint32_t* __restrict__ ends = J.ends;
+            const uint32_t n = J.n_iv;
+            const bool autocorr = (J.flags & EVF_AUTOCORR) != 0;
+            const long long lo = J.lo, hi = J.hi;
+            const long long off = autocorr ? 0 : (long long)P.read_len - 1 - (long long)D;   // window start relative to an edge
+            const long long L0 = autocorr ? 0 : (long long)P.read_len - 1;
+            const long long L1 = autocorr ? 1 : (long long)P.read_len - 2;
+            const long long Lmax = L0 > L1 ? L0 : L1;
+            unsigned long long d0 = 0, d1 = 0;
+            for (uint32_t base = w0; base < w1; base += 32) {
+                const uint32_t i = base + lane;
+                if (i >= w1) continue;
+                const long long b = __ldg(begins + i), e = __ldg(ends + i);
+                bad_order |= b > e || (i + 1 < n && e > (long long)__ldg(begins + i + 1));
+                bad_range |= e > b && (unsigned long long)e >= J.nbits;
+                const long long s = max(b + 1, lo), t = min(e + 1, hi);     // the counted part of the run: [s, t)
+                if (s >= t) continue;
+                // run edges of M inside the windows of this run's two edges: [s + off, s + off + D] and [t + off, ...]
+                const long long w_hi = t + off + D;
+                for (uint32_t Jx = lower_bound_near(ends, n, i, s + off - 1); Jx < n; ++Jx) {
+                    const long long bj = __ldg(begins + Jx), ej = __ldg(ends + Jx);
+                    if (bj + 1 > w_hi) break;
+                    if (ej <= bj) continue;
+                    const long long ds0 = bj + 1 - (s + off), de0 = ej + 1 - (s + off);     // against the start edge
+                    const long long ds1 = bj + 1 - (t + off), de1 = ej + 1 - (t + off);     // against the end edge
+                    if (ds0 >= 0 && ds0 <= (long long)D) atomicAdd(h_plus + ds0, 1u);        // start . start
+                    if (de0 >= 0 && de0 <= (long long)D) atomicAdd(h_minus + de0, 1u);       // start . end
+                    if (ds1 >= 0 && ds1 <= (long long)D) atomicAdd(h_minus + ds1, 1u);       // end . start
+                    if (de1 >= 0 && de1 <= (long long)D) atomicAdd(h_plus + de1, 1u);        // end . end
+                }
+                // the two directly counted lags: overlap of this run with the runs at and above it, moved down
+                const long long A_lo = s, A_hi = t - 1;
+                for (uint32_t kk = i; kk < n; ++kk) {
+                    const long long B_lo = (long long)__ldg(begins + kk) + 1, B_hi = __ldg(ends + kk);
+                    if (B_lo - Lmax > A_hi) break;
+                    if (B_hi < B_lo) continue;
+                    const long long o0 = min(A_hi, B_hi - L0) - max(A_lo, B_lo - L0) + 1;
+                    if (o0 > 0) d0 += (unsigned long long)o0;
+                    const long long o1 = min(A_hi, B_hi - L1) - max(A_lo, B_lo - L1) + 1;
+                    if (o1 > 0) d1 += (unsigned long long)o1;
+                }
+            }
+            for (int o = 16; o; o >>= 1) {
+                d0 += __shfl_xor_sync(0xFFFFFFFFu, d0, o);
+                d1 += __shfl_xor_sync(0xFFFFFFFFu, d1, o);
+            }
+            if (lane == 0) {
+                if (d0) atomicAdd(J.adirect, d0);
+                if (d1) atomicAdd(J.adirect + 1, d1);
+            }
+        },
+        [&](uint32_t, const ListJob& J) {
+            flush_hist(h_plus, D + 1, J.aux);
+            flush_hist(h_minus, D + 1, J.aux + P.stride);
+        });
+    if (bad_range) atomicExch(P.flags, 1);
+    if (bad_order) atomicExch(P.flags + 1, 1);
+}
+
+// ---------------------------------------------------------------- finalize: prefix sums
+// One CTA per job: mfwd / mrev from their difference histograms, dmp from the edge products and
+// the two direct lags (the same double prefix sum as finalize_dmp_kernel).
+__global__ void __launch_bounds__(256) list_finalize_kernel(const ListJob* __restrict__ jobs, uint32_t stride,
+                                                            uint32_t max_shift)
+{
+    __shared__ long long part[256];
+    const ListJob& J = jobs[blockIdx.x];
+    if (!(J.flags & (EVF_MSCC | EVF_AUTOCORR))) return;       // uniform per CTA
+    const bool autocorr = (J.flags & EVF_AUTOCORR) != 0;
+    if (!autocorr) {
+        for (int which = 0; which < 2; ++which) {
+            long long* out = (long long*)(J.counters + (size_t)(which ? C_MREV : C_MFWD) * stride);
+            const long long* plus = (const long long*)(J.diff + (size_t)(2 * which) * stride);
+            const long long* minus = plus + stride;
+            for (uint32_t k = threadIdx.x; k <= max_shift; k += blockDim.x) out[k] = plus[k] - minus[k];
+            __syncthreads();
+            block_scan_inplace(out, max_shift + 1, part);
+        }
+    }
+    long long* out = (long long*)(J.counters + (size_t)C_DMP * stride);
+    const long long* plus = (const long long*)J.aux;
+    const long long* minus = plus + stride;
+    const long long a0 = (long long)J.adirect[0], a1 = (long long)J.adirect[1];
+    if (max_shift == 0) { if (threadIdx.x == 0) out[0] = a0; return; }
+    for (uint32_t k = threadIdx.x; k <= max_shift; k += blockDim.x) {
+        long long v;
+        if (k == 0) v = a0;
+        else if (k == 1) v = a1 - a0;
+        else { const uint32_t b = autocorr ? k - 1 : max_shift - (k - 1); v = -(plus[b] - minus[b]); }
+        out[k] = v;
+    }
+    __syncthreads();
+    block_scan_inplace(out + 1, max_shift, part);
+    block_scan_inplace(out, max_shift + 1, part);
+}
+
+}  // namespace pmb
