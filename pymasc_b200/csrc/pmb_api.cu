@@ -38,6 +38,7 @@ struct pmb_ctx {
     int block_warps = 16;
     int path = 0;            // 0 auto, 1 dense shift-window, 2 event-window, 3 lists
     int list_blocks_per_sm = 0;
+    bool list_attr_done = false; // the list kernels' shared-memory limit is raised on THIS device
     int list_pairs_limit = 0;    // auto: lists while the expected reverse reads per forward read and 1024 shifts stay below this
     int event_tile_words = 0;
     int event_blocks_per_sm = 0;
@@ -1021,11 +1022,11 @@ static cudaError_t launch_window(pmb_ctx* c, int variant, const WindowParams& P,
 }
 
 // ------------------------------------------------------------------ batch: execute (list path)
-static void list_attributes()
+static void list_attributes(pmb_ctx* c)
 {
-    // once per process: the kernels' dynamic shared memory may exceed 48 KB for large max_shift
-    static bool done = false;
-    if (done) return;
+    // once per context (the attribute is per device, and a process may drive several): the
+    // kernels' dynamic shared memory exceeds 48 KB for max_shift > ~3000
+    if (c->list_attr_done) return;
     const int cap = 200 * 1024;
     cudaFuncSetAttribute(list_fwd_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, cap);
     cudaFuncSetAttribute(list_fwd_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, cap);
@@ -1033,7 +1034,7 @@ static void list_attributes()
     cudaFuncSetAttribute(list_rev_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, cap);
     cudaFuncSetAttribute(list_rev_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, cap);
     cudaFuncSetAttribute(list_edge_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, cap);
-    done = true;
+    c->list_attr_done = true;
 }
 
 static int execute_lists(pmb_ctx* c, pmb_batch* b)
@@ -1041,7 +1042,7 @@ static int execute_lists(pmb_ctx* c, pmb_batch* b)
     cudaStream_t st = c->stream;
     const size_t n = b->jobs.size();
     uint32_t launches = 0;
-    list_attributes();
+    list_attributes(c);
     CU_TRY(c, cudaEventRecord(c->ev[0], st));
     {
         ZeroSegs z{};
