@@ -183,6 +183,44 @@ void pmb_host_free(void *p);
  * "h2d_growth_x10" (size ratio of consecutive groups in tenths, default 13). */
 int  pmb_set_option(pmb_ctx *ctx, const char *name, int64_t value);
 
+/*
+ * pmb_run_chrom_noalloc -- one chromosome through the list kernels WITHOUT any allocation.
+ * (No counterpart in the reference: added for callers
+ * that cannot call cudaMalloc -- code under CUDA graph capture, tight serving loops, harnesses
+ * that forbid it.)
+ *
+ * The list path's scratch (job table, difference histograms of mfwd / mrev, run-edge products,
+ * the two direct lags: ~197 KB) lives in a file-scope `static __device__` array of the library,
+ * sized for max_shift <= PMB_NOALLOC_MAX_SHIFT; every GPU that loads the library holds it until
+ * the process exits.  The call issues kernels on the context's stream and returns without
+ * waiting; it calls no cudaMalloc / cudaFree / cudaHostAlloc and copies nothing.
+ *
+ *   a      as for pmb_run_chrom, but fwd_pos / rev_pos / map_begin / map_end are DEVICE pointers
+ *          (4-byte aligned), and the lists must be what the reference's feed rules produce:
+ *          reads sorted, intervals sorted and disjoint (duplicates allowed).  Flags: PMB_FLAG_NCC,
+ *          PMB_FLAG_MSCC, or PMB_FLAG_AUTOCORR alone; read_len >= 2; PMB_FLAG_SAME_TRACK is refused.
+ *   d_out  DEVICE pointer, 8-byte aligned, to PMB_NOALLOC_OUT_INT64(max_shift) int64:
+ *            [PMB_NCOUNTERS][max_shift+1]  ncc, dmp, mfwd, mrev, mscc (vectors the flags do not
+ *                                          select are zero)
+ *            [2]                           fwd_total, rev_total
+ *            [1]                           status, two int32: low word != 0 -> a position or
+ *                                          interval lies beyond the bit array (PMB_ERR_RANGE of
+ *                                          the other entry points); high word != 0 -> the lists
+ *                                          are not sorted / disjoint and the counts are invalid
+ *                                          (use pmb_run_chrom, which handles such input)
+ *   out_int64  capacity of d_out in int64; less than PMB_NOALLOC_OUT_INT64(max_shift) is refused
+ * Returns PMB_ERR_ARG (text in pmb_last_error) for max_shift > PMB_NOALLOC_MAX_SHIFT and the
+ * other refusals above.  The first call on a context looks up the scratch array's device address
+ * (cudaGetSymbolAddress) and raises the kernels' shared-memory limit: make that call outside
+ * graph capture.
+ * ALL calls on one GPU share the scratch array, and it keeps the last call's contents: every call
+ * clears what it accumulates into (scratch and d_out) first, and calls that overlap on the GPU --
+ * two contexts / streams on one device -- race.  Calls on one context's stream are ordered.
+ */
+#define PMB_NOALLOC_MAX_SHIFT 4095
+#define PMB_NOALLOC_OUT_INT64(max_shift) (PMB_NCOUNTERS * ((uint64_t)(max_shift) + 1) + 3)
+int  pmb_run_chrom_noalloc(pmb_ctx *ctx, const pmb_chrom_args *a, int64_t *d_out, uint64_t out_int64);
+
 /* Integer-pipe calibration on the device: runs a dependent-free loop of `what`
  * (0 = POPC, 1 = LOP3, 2 = POPC+LOP3 interleaved, 3 = SHF, 4 = IADD3, 5 = POPC+IMAD)
  * and returns executed thread-level ops per second. */

@@ -60,7 +60,7 @@ EXPORTS = (
     "pmb_batch_prepare", "pmb_batch_execute", "pmb_batch_fetch", "pmb_batch_counters",
     "pmb_batch_free", "pmb_get_timing", "pmb_stream", "pmb_synchronize", "pmb_host_alloc",
     "pmb_host_free", "pmb_set_option", "pmb_pipe_probe", "pmb_set_stream", "pmb_device_count",
-    "pmb_batch_validate",
+    "pmb_batch_validate", "pmb_run_chrom_noalloc",
 )
 
 _lib = None
@@ -100,6 +100,8 @@ def load_library():
     L.pmb_batch_counters.restype = ctypes.c_int
     L.pmb_batch_validate.argtypes = [vp, vp]
     L.pmb_batch_validate.restype = ctypes.c_int
+    L.pmb_run_chrom_noalloc.argtypes = [vp, ctypes.POINTER(ChromArgs), vp, ctypes.c_uint64]
+    L.pmb_run_chrom_noalloc.restype = ctypes.c_int
     L.pmb_batch_free.argtypes = [vp, vp]
     L.pmb_batch_free.restype = None
     L.pmb_get_timing.argtypes = [vp, ctypes.POINTER(Timing)]
@@ -265,6 +267,25 @@ class Device(object):
         outs, arrays = self._outputs(jobs)
         self._check(self._L.pmb_run_batch(self._h, args, outs, len(jobs)))
         return self._collect(jobs, outs, arrays)
+
+    NOALLOC_MAX_SHIFT = 4095
+
+    @staticmethod
+    def noalloc_out_int64(max_shift):
+        return NCOUNTERS * (int(max_shift) + 1) + 3
+
+    def run_chrom_noalloc(self, chrom_len, read_len, max_shift, flags, d_fwd, n_fwd, d_rev, n_rev,
+                          d_begins, d_ends, n_intervals, d_out, out_int64, lo=0, hi=0):
+        """pmb_run_chrom_noalloc: DEVICE pointers (integers) in, counters into the caller's device
+        block; asynchronous on the context's stream, allocates nothing (see include/pymasc_b200.h)."""
+        a = ChromArgs()
+        a.chrom_len, a.read_len, a.max_shift, a.flags = int(chrom_len), int(read_len), int(max_shift), int(flags)
+        a.fwd_pos, a.n_fwd = d_fwd or None, int(n_fwd)
+        a.rev_pos, a.n_rev = d_rev or None, int(n_rev)
+        a.map_begin, a.map_end, a.n_intervals = d_begins or None, d_ends or None, int(n_intervals)
+        a.range_lo, a.range_hi = int(lo), int(hi)
+        self._check(self._L.pmb_run_chrom_noalloc(self._h, ctypes.byref(a), ctypes.c_void_p(int(d_out)),
+                                                  int(out_int64)))
 
     def prepare(self, jobs):
         return Batch(self, jobs)

@@ -39,6 +39,7 @@ struct pmb_ctx {
     int path = 0;            // 0 auto, 1 dense shift-window, 2 event-window, 3 lists
     int list_blocks_per_sm = 0;
     bool list_attr_done = false; // the list kernels' shared-memory limit is raised on THIS device
+    unsigned long long* noalloc_scratch = nullptr;   // device address of g_noalloc_scratch on this device
     int list_pairs_limit = 0;    // auto: lists while the expected reverse reads per forward read and 1024 shifts stay below this
     int event_tile_words = 0;
     int event_blocks_per_sm = 0;
@@ -1580,6 +1581,140 @@ extern "C" int pmb_run_batch(pmb_ctx* c, const pmb_chrom_args* a, pmb_chrom_out*
 extern "C" int pmb_run_chrom(pmb_ctx* c, const pmb_chrom_args* a, pmb_chrom_out* o)
 {
     return pmb_run_batch(c, a, o, 1);
+}
+
+// ------------------------------------------------------------------ one chromosome, no allocation
+// pmb_run_chrom_noalloc (include/pymasc_b200.h): the list kernels on one chromosome whose lists
+// are already in device memory, with every byte of scratch in the array below.  In HOST code the
+// array's name is only a stand-in for the symbol -- not a device address: the address comes from
+// cudaGetSymbolAddress, once per context, with the context's device current.  Device code names
+// the array directly (noalloc_setup_kernel).
+//   words [0, 32)    the job table: one ListJob
+//   words [32, 64)   entry prefixes of the three kernels: {0, n_fwd}, {0, n_rev}, {0, n_intervals}
+//   words [64, ...)  accumulators: [4][S] difference histograms | [2][S] edge products | [2] lags,
+//                    S = max_shift + 1 <= PMB_NOALLOC_MAX_SHIFT + 1
+constexpr size_t NOALLOC_TABLE_WORDS = 32, NOALLOC_PREFIX_WORDS = 32;
+constexpr size_t NOALLOC_ACC_WORDS = 6 * ((size_t)PMB_NOALLOC_MAX_SHIFT + 1) + 2;
+constexpr size_t NOALLOC_SCRATCH_WORDS = NOALLOC_TABLE_WORDS + NOALLOC_PREFIX_WORDS + NOALLOC_ACC_WORDS;
+static_assert(sizeof(ListJob) <= NOALLOC_TABLE_WORDS * 8, "job table slot too small");
+static __device__ __align__(256) unsigned long long g_noalloc_scratch[NOALLOC_SCRATCH_WORDS];
+
+// Writes the job table and the prefixes, and clears what the list kernels accumulate into: the
+// accumulators in the scratch array (they hold the previous call's sums) and the caller's output.
+__global__ void __launch_bounds__(512) noalloc_setup_kernel(ListJob J, unsigned long long n_fwd,
+                                                            unsigned long long n_rev, unsigned long long n_iv,
+                                                            unsigned long long* __restrict__ out, uint32_t n_out,
+                                                            uint32_t n_acc)
+{
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+        *reinterpret_cast<ListJob*>(g_noalloc_scratch) = J;
+        unsigned long long* pre = g_noalloc_scratch + NOALLOC_TABLE_WORDS;
+        pre[0] = 0; pre[1] = n_fwd; pre[2] = 0; pre[3] = n_rev; pre[4] = 0; pre[5] = n_iv;
+    }
+    unsigned long long* acc = g_noalloc_scratch + NOALLOC_TABLE_WORDS + NOALLOC_PREFIX_WORDS;
+    const uint32_t tid = blockIdx.x * blockDim.x + threadIdx.x, nth = gridDim.x * blockDim.x;
+    for (uint32_t i = tid; i < n_acc; i += nth) acc[i] = 0;
+    for (uint32_t i = tid; i < n_out; i += nth) out[i] = 0;
+}
+
+extern "C" int pmb_run_chrom_noalloc(pmb_ctx* c, const pmb_chrom_args* a, int64_t* d_out, uint64_t out_int64)
+{
+    if (!c) return PMB_ERR_ARG;
+    if (!a || !d_out) { c->err = "pmb_run_chrom_noalloc: null argument"; return PMB_ERR_ARG; }
+    if (a->max_shift > PMB_NOALLOC_MAX_SHIFT) {
+        c->err = "pmb_run_chrom_noalloc: max_shift " + std::to_string(a->max_shift) + " exceeds PMB_NOALLOC_MAX_SHIFT (" +
+                 std::to_string(PMB_NOALLOC_MAX_SHIFT) + "): the static scratch array holds no more; use pmb_run_chrom";
+        return PMB_ERR_ARG;
+    }
+    const uint32_t D = a->max_shift, S = D + 1;
+    if (out_int64 < PMB_NOALLOC_OUT_INT64(D)) {
+        c->err = "pmb_run_chrom_noalloc: d_out holds " + std::to_string(out_int64) + " int64, " +
+                 std::to_string(PMB_NOALLOC_OUT_INT64(D)) + " needed";
+        return PMB_ERR_ARG;
+    }
+    if (((uintptr_t)d_out & 7) || ((uintptr_t)a->fwd_pos & 3) || ((uintptr_t)a->rev_pos & 3) ||
+        ((uintptr_t)a->map_begin & 3) || ((uintptr_t)a->map_end & 3)) {
+        c->err = "pmb_run_chrom_noalloc: misaligned device pointer"; return PMB_ERR_ARG;
+    }
+    const bool autocorr = (a->flags & PMB_FLAG_AUTOCORR) != 0;
+    const bool ncc = !autocorr && (a->flags & PMB_FLAG_NCC), mscc = !autocorr && (a->flags & PMB_FLAG_MSCC);
+    if ((a->flags & PMB_FLAG_SAME_TRACK) || (!autocorr && !ncc && !mscc)) {
+        c->err = "pmb_run_chrom_noalloc: flags must be NCC and/or MSCC, or AUTOCORR alone"; return PMB_ERR_ARG;
+    }
+    if (a->read_len < 2) { c->err = "pmb_run_chrom_noalloc: read_len must be >= 2"; return PMB_ERR_ARG; }
+    const uint64_t nbits = a->chrom_len + a->read_len + a->max_shift + PMB_EXTRA_ALLOCATE_SIZE;
+    if (nbits + a->read_len + a->max_shift + 2 >= (1ull << 32) || a->n_fwd >= (1ull << 31) || a->n_rev >= (1ull << 31) ||
+        a->n_intervals >= (1ull << 31)) {
+        c->err = "pmb_run_chrom_noalloc: chromosome or list too long for 32-bit positions"; return PMB_ERR_ARG;
+    }
+    if ((!autocorr && ((a->n_fwd && !a->fwd_pos) || (a->n_rev && !a->rev_pos))) ||
+        ((mscc || autocorr) && a->n_intervals && (!a->map_begin || !a->map_end))) {
+        c->err = "pmb_run_chrom_noalloc: list pointer missing"; return PMB_ERR_ARG;
+    }
+    CU_TRY(c, cudaSetDevice(c->device));
+    if (!c->noalloc_scratch) {      // set-up, once per context: the array's address on THIS device
+        unsigned long long* p = nullptr;
+        CU_TRY(c, cudaGetSymbolAddress((void**)&p, g_noalloc_scratch));
+        if (!p) { c->err = "pmb_run_chrom_noalloc: cudaGetSymbolAddress returned no address"; return PMB_ERR_CUDA; }
+        c->noalloc_scratch = p;
+    }
+    list_attributes(c);
+    unsigned long long* scratch = c->noalloc_scratch;
+    unsigned long long* acc = scratch + NOALLOC_TABLE_WORDS + NOALLOC_PREFIX_WORDS;
+    unsigned long long* out = (unsigned long long*)d_out;
+
+    ListJob J{};
+    if (!autocorr) {
+        J.fwd = a->fwd_pos; J.n_fwd = (uint32_t)a->n_fwd;
+        J.rev = a->rev_pos; J.n_rev = (uint32_t)a->n_rev;
+        J.flags = (ncc ? EVF_NCC : 0) | (mscc ? EVF_MSCC : 0);
+    } else {
+        J.flags = EVF_AUTOCORR;
+    }
+    if (mscc || autocorr) { J.begins = a->map_begin; J.ends = a->map_end; J.n_iv = (uint32_t)a->n_intervals; }
+    J.counters = out;                               // [5][S]
+    J.totals = out + (size_t)PMB_NCOUNTERS * S;     // [2]
+    J.diff = acc;                                   // [4][S]
+    J.aux = acc + 4 * (size_t)S;                    // [2][S]
+    J.adirect = acc + 6 * (size_t)S;                // [2]
+    J.nbits = nbits;
+    J.lo = (long long)a->range_lo;
+    J.hi = a->range_hi ? (long long)std::min<uint64_t>(a->range_hi, nbits) : (long long)nbits;
+    if (J.lo > J.hi) J.lo = J.hi;
+
+    cudaStream_t st = c->stream;
+    noalloc_setup_kernel<<<c->num_sms, 512, 0, st>>>(J, J.n_fwd, J.n_rev, J.n_iv, out,
+                                                     (uint32_t)PMB_NOALLOC_OUT_INT64(D), (uint32_t)(6 * (size_t)S + 2));
+    ListParams P{};
+    P.jobs = reinterpret_cast<const ListJob*>(scratch);
+    P.job_lo = 0; P.job_hi = 1;
+    P.max_shift = D; P.read_len = a->read_len; P.stride = S;
+    P.flags = (int*)(out + (size_t)PMB_NCOUNTERS * S + 2);      // the status word of d_out: {range, unsorted}
+    const uint32_t bps = c->list_blocks_per_sm > 0 ? (uint32_t)c->list_blocks_per_sm : 2;
+    auto grid_for = [&](unsigned long long items) {
+        return (unsigned)std::max<unsigned long long>(1, std::min<unsigned long long>((items + 2047) / 2048,
+                                                                                      (unsigned long long)c->num_sms * bps));
+    };
+    const size_t sm_f = list_smem_bytes(D, mscc ? 4 : 1), sm_2 = list_smem_bytes(D, 2);
+    const unsigned long long* pre = scratch + NOALLOC_TABLE_WORDS;
+    if (J.n_fwd) {
+        P.prefix = pre;
+        if (ncc && mscc) list_fwd_kernel<true, true><<<grid_for(J.n_fwd), LIST_THREADS, sm_f, st>>>(P);
+        else if (ncc) list_fwd_kernel<true, false><<<grid_for(J.n_fwd), LIST_THREADS, sm_f, st>>>(P);
+        else list_fwd_kernel<false, true><<<grid_for(J.n_fwd), LIST_THREADS, sm_f, st>>>(P);
+    }
+    if (J.n_rev) {
+        P.prefix = pre + 2;
+        if (mscc) list_rev_kernel<true><<<grid_for(J.n_rev), LIST_THREADS, sm_2, st>>>(P);
+        else list_rev_kernel<false><<<grid_for(J.n_rev), LIST_THREADS, 0, st>>>(P);
+    }
+    if (J.n_iv) {
+        P.prefix = pre + 4;
+        list_edge_kernel<<<grid_for(J.n_iv), LIST_THREADS, sm_2, st>>>(P);
+    }
+    if (mscc || autocorr) list_finalize_kernel<<<1, 256, 0, st>>>(P.jobs, S, D);
+    CU_TRY(c, cudaGetLastError());
+    return PMB_OK;
 }
 
 // ------------------------------------------------------------------ pipe calibration
