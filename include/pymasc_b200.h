@@ -175,7 +175,7 @@ void pmb_host_free(void *p);
  *   events one max_shift-bit window of a bit array per read / run edge;   cost ~ events x shifts/32
  *   lists  no bit arrays: pairs of sorted list entries within max_shift;  cost ~ entries + pairs
  * auto takes the list path while a forward read expects fewer than "list_pairs_limit"
- * (default 24) reverse reads per 1024 shifts, else the event path unless the inputs hold more
+ * (default 64) reverse reads per 1024 shifts, else the event path unless the inputs hold more
  * than 4 events (reads + run edges) per 32-bit word.  Tuning: "list_blocks_per_sm", "variant" (carry-save depth of the shift-window counters), "tile_words",
  * "grid_blocks", "block_warps", "event_tile_words", "event_blocks_per_sm".
  * Input copy: "async_h2d" (0/1, see pmb_batch_prepare), "h2d_groups" (1..64, default 4: at most that many),

@@ -825,7 +825,8 @@ static int prepare_impl(pmb_ctx* c, const pmb_chrom_args* a, uint32_t n, pmb_bat
     //   lists  (3): cost ~ reads + run edges + PAIRS of entries within max_shift of each other
     //   events (2): cost ~ (reads + run edges) x shifts/32 + a scan of the arrays
     //   dense  (1): cost ~ words x shifts
-    // auto: lists while a forward read expects fewer than ~24 reverse reads per 1024 shifts,
+    // auto: lists while a forward read expects fewer than ~64 reverse reads per 1024 shifts
+    // (measured crossover ~75: profiles/r02_config4_chr1_paths.jsonl),
     // else events unless the inputs hold more than 4 events per 32-bit word.
     uint64_t total_events = 0;
     double expect_pairs = 0, total_fwd = 0;
@@ -844,7 +845,7 @@ static int prepare_impl(pmb_ctx* c, const pmb_chrom_args* a, uint32_t n, pmb_bat
         }
     }
     if (getenv("PMB_NO_LISTS")) b->list_ok = false;         // debug aid
-    const double pairs_limit = (c->list_pairs_limit > 0 ? c->list_pairs_limit : 24) * ((b->n_shifts + 1023) / 1024);
+    const double pairs_limit = (c->list_pairs_limit > 0 ? c->list_pairs_limit : 64) * ((b->n_shifts + 1023) / 1024);
     if (c->path == 1 || c->path == 2) b->path = c->path;
     else if (c->path == 3) {
         if (!b->list_ok) { c->err = "the list path needs read_len >= 2, max_shift <= 12000 and fewer than 2^31 entries per list"; return PMB_ERR_ARG; }
@@ -1064,7 +1065,7 @@ static int execute_lists(pmb_ctx* c, pmb_batch* b)
     P.read_len = b->read_len;
     P.stride = b->stride;
     P.flags = b->d_err;
-    const uint32_t bps = c->list_blocks_per_sm > 0 ? (uint32_t)c->list_blocks_per_sm : 2;
+    const uint32_t bps = c->list_blocks_per_sm > 0 ? (uint32_t)c->list_blocks_per_sm : (uint32_t)LIST_MIN_BLOCKS;
     const unsigned long long* pre = b->h_list_prefix.data();
     auto grid_for = [&](unsigned long long items) {
         return (unsigned)std::max<unsigned long long>(1, std::min<unsigned long long>((items + 2047) / 2048,
@@ -1690,7 +1691,7 @@ extern "C" int pmb_run_chrom_noalloc(pmb_ctx* c, const pmb_chrom_args* a, int64_
     P.job_lo = 0; P.job_hi = 1;
     P.max_shift = D; P.read_len = a->read_len; P.stride = S;
     P.flags = (int*)(out + (size_t)PMB_NCOUNTERS * S + 2);      // the status word of d_out: {range, unsorted}
-    const uint32_t bps = c->list_blocks_per_sm > 0 ? (uint32_t)c->list_blocks_per_sm : 2;
+    const uint32_t bps = c->list_blocks_per_sm > 0 ? (uint32_t)c->list_blocks_per_sm : (uint32_t)LIST_MIN_BLOCKS;
     auto grid_for = [&](unsigned long long items) {
         return (unsigned)std::max<unsigned long long>(1, std::min<unsigned long long>((items + 2047) / 2048,
                                                                                       (unsigned long long)c->num_sms * bps));

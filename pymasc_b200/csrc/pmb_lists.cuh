@@ -61,7 +61,14 @@ struct ListParams {
     int* flags;                         // [0] position beyond the array, [1] input not sorted / disjoint
 };
 
-constexpr int LIST_THREADS = 512;
+#ifndef PMB_LIST_THREADS
+#define PMB_LIST_THREADS 512
+#endif
+#ifndef PMB_LIST_MIN_BLOCKS
+#define PMB_LIST_MIN_BLOCKS 2
+#endif
+constexpr int LIST_THREADS = PMB_LIST_THREADS;
+constexpr int LIST_MIN_BLOCKS = PMB_LIST_MIN_BLOCKS;      // resident CTAs per SM the register budget is cut for
 constexpr uint32_t LIST_NONE = 0xFFFFFFFFu;
 
 __host__ __device__ constexpr size_t list_smem_bytes(uint32_t max_shift, int n_hist)
@@ -182,7 +189,7 @@ __device__ __forceinline__ void flush_hist(uint32_t* h, uint32_t n_bins, unsigne
 
 // ---------------------------------------------------------------- forward reads: ncc, mscc, d(mfwd)
 template <bool NCC, bool MSCC>
-__global__ void __launch_bounds__(LIST_THREADS, 2) list_fwd_kernel(const ListParams P)
+__global__ void __launch_bounds__(LIST_THREADS, LIST_MIN_BLOCKS) list_fwd_kernel(const ListParams P)
 {
     extern __shared__ uint32_t lsm[];
     const uint32_t D = P.max_shift, S2 = D + 2, DUMP = D + 1;
@@ -253,18 +260,25 @@ __global__ void __launch_bounds__(LIST_THREADS, 2) list_fwd_kernel(const ListPar
                     }
                 };
                 if (MSCC && mp && c >= 0) load_run(); else mp = false;
+                // pairs (p, q), q - p <= D.  The next reverse read is requested before this one is
+                // counted (the loads hit L1, but a dependent load per pair would serialise on its
+                // latency); past the end of the list a sentinel gives k > D.
                 uint32_t qprev = LIST_NONE;
-                for (; j < nR; ++j) {
-                    const uint32_t q = __ldg(rev + j);
+                uint32_t q = j < nR ? __ldg(rev + j) : LIST_NONE;
+                for (;;) {
                     const uint32_t k = q - p;
                     if (k > D) break;
-                    if (q == qprev) continue;           // a bit is set once (mscc.pyx:416-418)
-                    qprev = q;
-                    if (job_ncc) atomicAdd(h_ncc + k, 1u);
-                    if (MSCC && mp) {
-                        while (k > k2 && c > 0) { c--; load_run(); }
-                        if (k >= k1 && k <= k2) atomicAdd(h_mscc + k, 1u);
+                    ++j;
+                    const uint32_t qn = j < nR ? __ldg(rev + j) : LIST_NONE;
+                    if (q != qprev) {                   // a bit is set once (mscc.pyx:416-418)
+                        if (job_ncc) atomicAdd(h_ncc + k, 1u);
+                        if (MSCC && mp) {
+                            while (k > k2 && c > 0) { c--; load_run(); }
+                            if (k >= k1 && k <= k2) atomicAdd(h_mscc + k, 1u);
+                        }
                     }
+                    qprev = q;
+                    q = qn;
                 }
                 if (MSCC && mp)
                     while (k2 < D && c > 0) { c--; load_run(); }      // the window's remaining runs
@@ -287,7 +301,7 @@ __global__ void __launch_bounds__(LIST_THREADS, 2) list_fwd_kernel(const ListPar
 
 // ---------------------------------------------------------------- reverse reads: d(mrev), strand total
 template <bool MSCC>
-__global__ void __launch_bounds__(LIST_THREADS, 2) list_rev_kernel(const ListParams P)
+__global__ void __launch_bounds__(LIST_THREADS, LIST_MIN_BLOCKS) list_rev_kernel(const ListParams P)
 {
     extern __shared__ uint32_t lsm[];
     const uint32_t D = P.max_shift, S2 = D + 2;
@@ -376,7 +390,7 @@ __global__ void __launch_bounds__(LIST_THREADS, 2) list_rev_kernel(const ListPar
 
 // ---------------------------------------------------------------- mappable runs: edge products, direct lags
 // (entries = the intervals of the jobs that OWN a track; followers and NCC-only jobs have none)
-__global__ void __launch_bounds__(LIST_THREADS, 2) list_edge_kernel(const ListParams P)
+__global__ void __launch_bounds__(LIST_THREADS, LIST_MIN_BLOCKS) list_edge_kernel(const ListParams P)
 {
     extern __shared__ uint32_t lsm[];
     const uint32_t D = P.max_shift, S2 = D + 2;
