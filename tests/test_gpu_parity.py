@@ -639,3 +639,127 @@ def test_multi_device_engine_position_split_with_two_contexts():
     for g, w in zip(got, wants):
         for k in w:
             assert np.array_equal(np.asarray(g[k]), np.asarray(w[k])), k
+
+
+# ----------------------------------------------------------------- full size against the oracle
+def _density_workload(name, genome_reads, rl):
+    total = float(sum(L for _, L in synth.HG38))
+    L = dict(synth.HG38)[name]
+    return synth.workload(n_reads=int(genome_reads * L / total), chroms=[name], read_len=rl)[0]
+
+
+def test_whole_chr1_against_the_oracle_on_every_path_and_as_eight_shards(dev):
+    """BASELINE configs[1]/[2] at full chromosome size: all of hg38 chr1 (249 Mbp, the 20 M-read
+    genome's density, max_shift 1000) against cc_oracle -- every counter, every shift, on each of
+    the three device algorithms -- and again as the sum of the 8 ranks' position shards
+    (distributed.shard_jobs: what bench.py --gpus 8 and ShardedEngine run)."""
+    from pymasc_b200 import sharding
+    from pymasc_b200.distributed import shard_jobs
+    rl, D = 36, 1000
+    w = _density_workload("chr1", 20_000_000, rl)
+    want = cc_oracle.chrom_counts(w["length"], rl, D, w["fwd"], w["rev"], w["begins"], w["ends"])
+    job = _shim.Job(w["length"], rl, D, 3, w["fwd"], w["rev"], w["begins"], w["ends"])
+    try:
+        for path in PATHS:
+            dev.set_option("path", path)
+            got = dev.run_batch([job])[0]
+            assert dev.timing()["path"] == path
+            assert sorted(got) == sorted(want)
+            for k in want:
+                assert np.array_equal(np.asarray(got[k]), np.asarray(want[k])), (k, PATH_NAMES[path])
+    finally:
+        dev.set_option("path", 0)
+    parts = [dev.run_batch(shard_jobs([job], r, 8)) for r in range(8)]
+    merged = sharding.sum_outputs(parts)[0]
+    for k in want:
+        assert np.array_equal(np.asarray(merged[k]), np.asarray(want[k])), (k, "8 shards")
+
+
+def test_deep_library_chromosome_at_max_shift_5000_against_the_oracle(dev):
+    """BASELINE configs[3]'s shape: a 114 Mbp chromosome (chr13) at the 200 M-read library's
+    density, max_shift 5000 -- five 1024-shift column chunks per event kernel, ~137 reverse reads
+    inside every forward read's window on the list path -- against cc_oracle, paths 2 and 3, and
+    the path `auto` picks."""
+    rl, D = 36, 5000
+    w = _density_workload("chr13", 200_000_000, rl)
+    want = cc_oracle.chrom_counts(w["length"], rl, D, w["fwd"], w["rev"], w["begins"], w["ends"])
+    job = _shim.Job(w["length"], rl, D, 3, w["fwd"], w["rev"], w["begins"], w["ends"])
+    try:
+        for path in (2, 3, 0):
+            dev.set_option("path", path)
+            got = dev.run_batch([job])[0]
+            for k in want:
+                assert np.array_equal(np.asarray(got[k]), np.asarray(want[k])), (k, path)
+        assert dev.timing()["path"] == 3        # auto: ~28 pairs per read and 1024 shifts, under the limit of 64
+    finally:
+        dev.set_option("path", 0)
+
+
+def test_auto_picks_the_documented_path_and_counts_stay_exact_across_the_thresholds(dev):
+    """`path` 0 (what the product and bench.py run): lists while a forward read expects fewer
+    than 64 reverse reads per 1024 shifts, else events unless the inputs hold more than 4 events
+    per 32-bit word, else dense (include/pymasc_b200.h).  Inputs on both sides of each threshold;
+    the path the library reports is asserted and the counts are checked against the oracle."""
+    L, rl, D = 200000, 36, 1000
+    words = (L + rl + D + 100) // 32
+    rng = np.random.default_rng(77)
+
+    def reads(n, lo, hi):
+        return np.unique(rng.integers(lo, hi, size=int(n))).astype(np.uint32)
+
+    _, _, b, e = random_case(5, L, rl, 10)
+    cases = [   # (forward reads per word, reverse reads per word, read_len, expected path)
+        (0.05, 0.05, rl, 3),        # ChIP-seq density
+        (0.3, 1.8, rl, 3),          # ~56 pairs per read: still lists
+        (0.3, 2.4, rl, 2),          # ~75 pairs per read, 2.7 events per word: events
+        (0.3, 3.4, rl, 2),          # 3.7 events per word + run edges: just under 4
+        (2.2, 2.6, rl, 1),          # 4.8 events per word: dense
+        (0.05, 0.05, 1, 2),         # read_len 1: no list path
+    ]
+    try:
+        for f_pw, r_pw, rlen, expect in cases:
+            fwd = reads(f_pw * words * 1.02, 1, L)
+            rev = reads(r_pw * words * 1.02, rlen, L + rlen - 1)
+            dev.set_option("path", 0)
+            got = dev.run_batch([_shim.Job(L, rlen, D, 3, fwd, rev, b, e)])[0]
+            assert dev.timing()["path"] == expect, (f_pw, r_pw, rlen, fwd.size, rev.size)
+            want = cc_oracle.chrom_counts(L, rlen, D, fwd, rev, b, e)
+            for k in want:
+                assert np.array_equal(np.asarray(got[k]), np.asarray(want[k])), (k, f_pw, r_pw)
+    finally:
+        dev.set_option("path", 0)
+
+
+def test_unsorted_input_moves_a_list_batch_to_the_event_path(dev):
+    """The list path verifies sortedness on the device while it counts; unsorted reads or
+    overlapping intervals send the batch to the event path (fetch, or pmb_batch_validate for
+    callers that read the device counters without a fetch) -- same counts, path 2 reported."""
+    L, rl, D = 150000, 36, 300
+    fwd, rev, b, e = random_case(31, L, rl, 9000)
+    want = cc_oracle.chrom_counts(L, rl, D, fwd, rev, b, e)
+    perm = np.random.default_rng(1).permutation(fwd.size)
+    ob, oe = np.asarray([5000, 100, 4000], np.uint32), np.asarray([9000, 6000, 4500], np.uint32)
+    want_o = cc_oracle.chrom_counts(L, rl, D, fwd, rev, ob, oe)
+    try:
+        dev.set_option("path", 3)
+        got = dev.run_batch([_shim.Job(L, rl, D, 3, fwd, rev, b, e)])[0]
+        assert dev.timing()["path"] == 3
+        for jobs, w in (([_shim.Job(L, rl, D, 3, fwd[perm], rev, b, e)], want),
+                        ([_shim.Job(L, rl, D, 3, fwd, rev, ob, oe)], want_o)):
+            got = dev.run_batch(jobs)[0]
+            assert dev.timing()["path"] == 2
+            for k in w:
+                assert np.array_equal(np.asarray(got[k]), np.asarray(w[k])), k
+            batch = dev.prepare(jobs)           # the all-reduce route: execute, validate, then read
+            batch.execute()
+            assert dev.timing()["path"] == 3
+            batch.validate()
+            assert dev.timing()["path"] == 2
+            batch.execute()                     # later executes stay on the event path
+            assert dev.timing()["path"] == 2
+            got = batch.fetch()[0]
+            batch.free()
+            for k in w:
+                assert np.array_equal(np.asarray(got[k]), np.asarray(w[k])), k
+    finally:
+        dev.set_option("path", 0)
