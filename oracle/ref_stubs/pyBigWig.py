@@ -8,6 +8,7 @@ from ``X.bedGraph`` beside it, with chromosome sizes from any ``*.chrom.sizes`` 
 same directory.  It never decodes the binary BigWig format.
 """
 import glob
+import io
 import os
 
 
@@ -18,7 +19,7 @@ class _Track(object):
         if not os.path.exists(text):
             raise RuntimeError("pyBigWig stub: no bedGraph twin for %s" % path)
         self._by_chrom = {}
-        with open(text) as fh:
+        with io.open(text) as fh:      # (this module's own open() below is pyBigWig's)
             for line in fh:
                 if not line.strip() or line.startswith(("#", "track", "browser")):
                     continue
@@ -26,7 +27,7 @@ class _Track(object):
                 self._by_chrom.setdefault(chrom, []).append((int(start), int(end), float(value)))
         self._sizes = {}
         for sizes in glob.glob(os.path.join(os.path.dirname(path) or ".", "*.chrom.sizes")):
-            with open(sizes) as fh:
+            with io.open(sizes) as fh:
                 for line in fh:
                     parts = line.split()
                     if len(parts) >= 2:

@@ -58,6 +58,14 @@ class DeviceEngine(object):
         return self.device.run_batch(jobs)
 
 
+class _NoProgress(object):
+    """progress_bar=None: the reference creates its own terminal ProgressBar here
+    (mscc.pyx:140); per-shift ticks do not exist on the device, so nothing is drawn."""
+
+    def __getattr__(self, name):
+        return lambda *a, **k: None
+
+
 class _Pending(object):
     __slots__ = ("chrom", "fwd", "rev", "intervals", "fwd_len_sum", "rev_len_sum")
 
@@ -94,7 +102,11 @@ class CCBitArrayCalculator(object):
         self._bwfeeder = bwfeeder
         self._skip_ncc = bool(skip_ncc)
         self._logger_lock = logger_lock
-        self._progress = progress_bar           # accepted; per-shift ticks do not exist here
+        # mscc.pyx:140-142: a caller's hook (a ProgressHook posting to the report queue in `-p N`
+        # workers, utils/progress.py:173-200) gets the mappability bar of every chromosome and no
+        # per-shift bar ("bitarray progress stacks in multiprocessing")
+        self._progress = progress_bar if progress_bar else _NoProgress()
+        self._allow_bitarray_progress = progress_bar is None
         self._engine = engine if engine is not None else DeviceEngine()
 
         self._pending = []                      # closed chromosomes awaiting the device
@@ -117,6 +129,17 @@ class CCBitArrayCalculator(object):
         logger.info(msg)
         if self._logger_lock:
             self._logger_lock.release()
+
+    # ------------------------------------------------------------------ progress (mscc.pyx:151-159)
+    def _init_mappability_progress(self, chrom):
+        self._progress.enable_bar()
+        self._progress.reset_progress("@@@@@^" * 12, '^', ' ', chrom, self.ref2genomelen[chrom])
+
+    def _init_bitarray_progress(self, chrom):
+        if self._allow_bitarray_progress:
+            self._progress.reset_progress("xxxxxX" * 12, 'X', ' ', chrom, self._max_shift)
+        else:
+            self._progress.disable_bar()
 
     # ------------------------------------------------------------------ feeding (host)
     def _init_buff(self):
@@ -235,6 +258,11 @@ class CCBitArrayCalculator(object):
             arr = np.asarray(rows, dtype=np.int64).reshape(-1, 2)
             b, e = arr[:, 0], arr[:, 1]
         self._logging_info("Loading {} mappability to bit array...".format(chrom))
+        # mscc.pyx:342-347: the reference ticks once per interval while it fills the bit array;
+        # here the intervals arrive as arrays, so the bar goes from empty to full in one update
+        self._init_mappability_progress(chrom)
+        self._progress.update(self.ref2genomelen[chrom])
+        self._progress.clean()
         nbits = self.ref2genomelen[chrom] + self._array_extend_size
         if (isinstance(b, np.ndarray) and isinstance(e, np.ndarray) and b.dtype == np.uint32 and e.dtype == np.uint32
                 and b.flags.c_contiguous and e.flags.c_contiguous):     # the native readers' arrays: no conversions
@@ -311,6 +339,9 @@ class CCBitArrayCalculator(object):
 
     def _store(self, p, out):
         chrom, L = p.chrom, self.ref2genomelen[p.chrom]
+        # mscc.pyx:286, :317, :325: the per-shift bar -- one tick per finished chromosome here
+        self._init_bitarray_progress(chrom)
+        self._progress.update(self._max_shift)
         if not self._skip_ncc:
             self.forward_sum += out["fwd_total"]
             self.reverse_sum += out["rev_total"]
@@ -329,6 +360,7 @@ class CCBitArrayCalculator(object):
                            mappable_len=self._mappable_len_list(out["dmp"]))
             r.calc_cc()
             self.ref2mscc_result[chrom] = r
+        self._progress.clean()
 
     def _track_key(self, chrom):
         """Names the mappability track of a job for pymasc_b200.multifile: readers of the same
