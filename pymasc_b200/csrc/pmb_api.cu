@@ -38,6 +38,7 @@ struct pmb_ctx {
     int block_warps = 16;
     int path = 0;            // 0 auto, 1 dense shift-window, 2 event-window, 3 lists
     int list_blocks_per_sm = 0;
+    int check_selftest = 0;      // -DPMB_CHECKED builds: make every TMA range check of the event kernels fail (proves the chain)
     bool list_attr_done = false; // the list kernels' shared-memory limit is raised on THIS device
     unsigned long long* noalloc_scratch = nullptr;   // device address of g_noalloc_scratch on this device
     int list_pairs_limit = 0;    // auto: lists while the expected reverse reads per forward read and 1024 shifts stay below this
@@ -311,6 +312,7 @@ extern "C" int pmb_set_option(pmb_ctx* c, const char* name, int64_t value)
     else if (!strcmp(name, "block_warps")) c->block_warps = (int)value;
     else if (!strcmp(name, "path")) c->path = (int)value;
     else if (!strcmp(name, "event_tile_words")) c->event_tile_words = (int)value;
+    else if (!strcmp(name, "check_selftest")) c->check_selftest = (int)value;
     else if (!strcmp(name, "list_blocks_per_sm")) c->list_blocks_per_sm = (int)value;
     else if (!strcmp(name, "list_pairs_limit")) c->list_pairs_limit = (int)value;
     else if (!strcmp(name, "event_blocks_per_sm")) c->event_blocks_per_sm = (int)value;
@@ -1193,6 +1195,10 @@ static int execute_events(pmb_ctx* c, pmb_batch* b)
     P.max_shift = b->max_shift;
     P.read_len = b->read_len;
     P.stride = b->stride;
+    P.mem_lo = b->d_bits_raw;
+    P.mem_hi = b->d_bits + std::max<size_t>(b->bits_words, 4) + EV_PAD_WORDS;
+    P.chk = b->d_err;
+    if (c->check_selftest) P.mem_hi = P.mem_lo;
     const uint32_t n_cols_total = (b->n_shifts + 31) / 32;
     const uint32_t bps = c->event_blocks_per_sm > 0 ? (uint32_t)c->event_blocks_per_sm : 8;
     uint32_t window_launches = 0;
@@ -1541,6 +1547,10 @@ extern "C" int pmb_batch_fetch(pmb_ctx* c, pmb_batch* b, pmb_chrom_out* o)
         CU_TRY(c, cudaStreamSynchronize(c->stream));
     } else if (b->path == 3) {
         b->list_checked = true;
+    }
+    if (*h_err >= 1000) {       // a -DPMB_CHECKED build only (PMB_CHECK in the kernels)
+        c->err = "device-side check failed at source line " + std::to_string(*h_err - 1000);
+        return PMB_ERR_CUDA;
     }
     if (*h_err) {
         c->err = "a read position or mappability interval lies beyond chrom_len + read_len + "

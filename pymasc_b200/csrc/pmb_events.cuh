@@ -77,6 +77,9 @@ struct EventParams {
     uint32_t read_len;
     uint32_t stride;
     const int* gate;        // EV_EDGE: run only if *gate is set (fallback of edge_list_kernel); may be null
+    const uint32_t* mem_lo; // the bit-array allocation (pads included): every TMA source range lies inside
+    const uint32_t* mem_hi; //   (verified in a -DPMB_CHECKED build)
+    int* chk;               // the batch's error flag
 };
 
 #ifndef EV_SWITCH_ADD
@@ -335,6 +338,13 @@ __global__ void __launch_bounds__(32 * EV_WARPS) event_window_kernel(const Event
         return floor4((((N >> 1) - 1 - (G_last >> 1) - hmax) >> 5) + P.col0);               // Er, Or
     };
 
+    // (checked build: the source range of every bulk copy lies inside the bit-array allocation,
+    // the destination inside this warp's stage)
+    auto tma_load_1d = [&](uint32_t* dst, const uint32_t* src, uint32_t bytes, uint64_t* bar) {
+        PMB_CHECK(src >= P.mem_lo && src + bytes / 4 <= P.mem_hi && (bytes & 15u) == 0 && ((uintptr_t)src & 15u) == 0, P.chk);
+        PMB_CHECK(dst >= stage0 && dst + bytes / 4 <= stage0 + 2 * STAGE, P.chk);
+        pmb::tma_load_1d(dst, src, bytes, bar);
+    };
     // producer (thread 0): request the regions of one tile into one stage
     auto request = [&](uint32_t t, uint32_t job, int s) {
         const EventJob& J = P.jobs[job];

@@ -71,6 +71,8 @@ constexpr int LIST_THREADS = PMB_LIST_THREADS;
 constexpr int LIST_MIN_BLOCKS = PMB_LIST_MIN_BLOCKS;      // resident CTAs per SM the register budget is cut for
 constexpr uint32_t LIST_NONE = 0xFFFFFFFFu;
 
+// (PMB_CHECK: pmb_window.cuh -- bounds checks of every list index and histogram bin in a -DPMB_CHECKED build)
+
 __host__ __device__ constexpr size_t list_smem_bytes(uint32_t max_shift, int n_hist)
 {
     return (size_t)n_hist * (max_shift + 2) * 4;      // bins 0 .. max_shift and a dump bin
@@ -167,6 +169,7 @@ __device__ __forceinline__ void list_segments(const ListParams& P, int warp, int
         const unsigned long long seg_hi = c_hi < je ? c_hi : je;
         const ListJob& J = P.jobs[job];
         const uint32_t s0 = (uint32_t)(pos - jb), s1 = (uint32_t)(seg_hi - jb);
+        PMB_CHECK(job < P.job_hi && s0 < s1 && jb + s1 <= je, P.flags);
         const uint32_t len = s1 - s0;
         const uint32_t chunk = (((len + n_warps - 1) / n_warps) + 31u) & ~31u;
         const unsigned long long w0 = (unsigned long long)s0 + (unsigned long long)warp * chunk;
@@ -214,6 +217,7 @@ __global__ void __launch_bounds__(LIST_THREADS, LIST_MIN_BLOCKS) list_fwd_kernel
             const bool job_mscc = MSCC && (J.flags & EVF_MSCC) && nI;
             const long long lo = J.lo, hi = J.hi;
             const unsigned long long nbits = J.nbits;
+            PMB_CHECK(w0 < w1 && w1 <= J.n_fwd, P.flags);
             const uint32_t p_first = __ldg(fwd + w0);
             uint32_t JR = warp_lower_bound(rev, nR, p_first, lane);                          // reverse reads below p
             uint32_t CI = job_mscc ? warp_lower_bound(begins, nI, p_first + rl1, lane) : 0;  // runs beginning below p+rl-1
@@ -232,7 +236,9 @@ __global__ void __launch_bounds__(LIST_THREADS, LIST_MIN_BLOCKS) list_fwd_kernel
                 const uint32_t p_max = __shfl_sync(0xFFFFFFFFu, p, n_act - 1);
                 // this read's first reverse read: q >= p
                 const uint32_t HR = gallop(rev, nR, JR, p_max);
+                PMB_CHECK(JR <= HR && HR <= nR, P.flags);
                 uint32_t j = lower_bound_in(rev, JR, HR, p);
+                PMB_CHECK(j <= nR, P.flags);
                 JR = __shfl_sync(0xFFFFFFFFu, j, n_act - 1);
                 // mappable runs: c = last run that begins below x_top = p + rl - 1
                 const uint32_t x_top = p + rl1;
@@ -240,7 +246,9 @@ __global__ void __launch_bounds__(LIST_THREADS, LIST_MIN_BLOCKS) list_fwd_kernel
                 bool mp = false;
                 if (job_mscc) {
                     const uint32_t HI = gallop(begins, nI, CI, p_max + rl1);
+                    PMB_CHECK(CI <= HI && HI <= nI, P.flags);
                     const uint32_t c1 = lower_bound_in(begins, CI, HI, x_top);
+                    PMB_CHECK(c1 <= nI, P.flags);
                     CI = __shfl_sync(0xFFFFFFFFu, c1, n_act - 1);
                     c = (int)c1 - 1;
                     int cp = c;
@@ -251,6 +259,7 @@ __global__ void __launch_bounds__(LIST_THREADS, LIST_MIN_BLOCKS) list_fwd_kernel
                 // the run in the window that the next shifts can meet: x = x_top - k in (b, e]  <=>  k in [k1, k2]
                 uint32_t k1 = LIST_NONE, k2 = LIST_NONE;
                 auto load_run = [&]() {
+                    PMB_CHECK(c >= 0 && (uint32_t)c < nI, P.flags);
                     const uint32_t b = __ldg(begins + c), e = __ldg(ends + c);
                     k2 = x_top - b - 1;
                     k1 = x_top - min(e, x_top);
@@ -271,6 +280,7 @@ __global__ void __launch_bounds__(LIST_THREADS, LIST_MIN_BLOCKS) list_fwd_kernel
                     ++j;
                     const uint32_t qn = j < nR ? __ldg(rev + j) : LIST_NONE;
                     if (q != qprev) {                   // a bit is set once (mscc.pyx:416-418)
+                        PMB_CHECK(k <= D && j <= nR, P.flags);
                         if (job_ncc) atomicAdd(h_ncc + k, 1u);
                         if (MSCC && mp) {
                             while (k > k2 && c > 0) { c--; load_run(); }
@@ -324,6 +334,7 @@ __global__ void __launch_bounds__(LIST_THREADS, LIST_MIN_BLOCKS) list_rev_kernel
             const bool job_mscc = MSCC && (J.flags & EVF_MSCC) && nI;
             const long long lo = J.lo, hi = J.hi;
             const unsigned long long nbits = J.nbits;
+            PMB_CHECK(w0 < w1 && w1 <= J.n_rev, P.flags);
             uint32_t CI = job_mscc ? warp_lower_bound(begins, nI, __ldg(rev + w0) + rl1, lane) : 0;
             uint32_t tot = 0;
             for (uint32_t base = w0; base < w1; base += 32) {
@@ -340,7 +351,9 @@ __global__ void __launch_bounds__(LIST_THREADS, LIST_MIN_BLOCKS) list_rev_kernel
                 const uint32_t t = q + rl1;
                 const uint32_t q_max = __shfl_sync(0xFFFFFFFFu, q, n_act - 1);
                 const uint32_t HI = gallop(begins, nI, CI, q_max + rl1);
+                PMB_CHECK(CI <= HI && HI <= nI, P.flags);
                 const uint32_t c1 = lower_bound_in(begins, CI, HI, t);
+                PMB_CHECK(c1 <= nI, P.flags);
                 CI = __shfl_sync(0xFFFFFFFFu, c1, n_act - 1);
                 // shifts whose j = q - k lies in the counted range
                 const long long ka_l = (long long)q - hi + 1, kb_l = (long long)q - lo;
@@ -353,10 +366,12 @@ __global__ void __launch_bounds__(LIST_THREADS, LIST_MIN_BLOCKS) list_rev_kernel
                 // M[q-k]: run (b, e] <=> k in [a1, a2];  M[t-2k]: run (b, e] <=> k in [b1, b2]
                 uint32_t a1, a2, b1, b2;
                 auto load_a = [&]() {
+                    PMB_CHECK(cA >= 0 && (uint32_t)cA < nI, P.flags);
                     const uint32_t b = __ldg(begins + cA), e = __ldg(ends + cA);
                     a1 = q - min(e, q); a2 = q - b - 1;
                 };
                 auto load_b = [&]() {
+                    PMB_CHECK(cB >= 0 && (uint32_t)cB < nI, P.flags);
                     const uint32_t b = __ldg(begins + cB), e = __ldg(ends + cB);
                     b1 = (t - min(e, t) + 1) >> 1; b2 = (t - b - 1) >> 1;
                 };
@@ -366,6 +381,7 @@ __global__ void __launch_bounds__(LIST_THREADS, LIST_MIN_BLOCKS) list_rev_kernel
                     if (a1 > (uint32_t)kb || b1 > (uint32_t)kb) break;
                     const uint32_t s = max(max(a1, b1), (uint32_t)ka), e = min(min(a2, b2), (uint32_t)kb);
                     if (s <= e) {                       // both mappable for k in [s, e]
+                        PMB_CHECK(e <= D, P.flags);
                         atomicAdd(h_rp + s, 1u);
                         atomicAdd(h_rm + e + 1, 1u);
                     }
@@ -416,6 +432,7 @@ __global__ void __launch_bounds__(LIST_THREADS, LIST_MIN_BLOCKS) list_edge_kerne
             for (uint32_t base = w0; base < w1; base += 32) {
                 const uint32_t i = base + lane;
                 if (i >= w1) continue;
+                PMB_CHECK(i < n, P.flags);
                 const long long b = __ldg(begins + i), e = __ldg(ends + i);
                 bad_order |= b > e || (i + 1 < n && e > (long long)__ldg(begins + i + 1));
                 bad_range |= e > b && (unsigned long long)e >= J.nbits;
@@ -423,7 +440,9 @@ __global__ void __launch_bounds__(LIST_THREADS, LIST_MIN_BLOCKS) list_edge_kerne
                 if (s >= t) continue;
                 // run edges of M inside the windows of this run's two edges: [s + off, s + off + D] and [t + off, ...]
                 const long long w_hi = t + off + D;
-                for (uint32_t Jx = lower_bound_near(ends, n, i, s + off - 1); Jx < n; ++Jx) {
+                const uint32_t Jx0 = lower_bound_near(ends, n, i, s + off - 1);
+                PMB_CHECK(Jx0 <= n, P.flags);
+                for (uint32_t Jx = Jx0; Jx < n; ++Jx) {
                     const long long bj = __ldg(begins + Jx), ej = __ldg(ends + Jx);
                     if (bj + 1 > w_hi) break;
                     if (ej <= bj) continue;

@@ -65,6 +65,17 @@ struct WindowParams {
     uint32_t halo_words;   // 4U+4 for the units of this launch
 };
 
+// -DPMB_CHECKED: device-side bounds checks -- list indices and histogram bins (pmb_lists.cuh), TMA source
+// ranges of the event kernels (pmb_events.cuh) -- because compute-sanitizer
+// is closed on the B200 pool ( tools/checked_build.sh runs the GPU tests against such a build).  A
+// failed check leaves 1000 + its source line in the batch's error flag, which every fetch reads:
+// the call then fails with "device-side check failed at line N".  Compiled out otherwise.
+#ifdef PMB_CHECKED
+#define PMB_CHECK(cond, flag_ptr) do { if (!(cond)) atomicMax((flag_ptr), 1000 + __LINE__); } while (0)
+#else
+#define PMB_CHECK(cond, flag_ptr) ((void)0)
+#endif
+
 // ---------------------------------------------------------------- PTX helpers
 __device__ __forceinline__ uint32_t smem_u32(const void* p)
 {

@@ -763,3 +763,41 @@ def test_unsorted_input_moves_a_list_batch_to_the_event_path(dev):
                 assert np.array_equal(np.asarray(got[k]), np.asarray(w[k])), k
     finally:
         dev.set_option("path", 0)
+
+
+@pytest.mark.parametrize("groups", [1, 3])
+def test_repeated_executes_are_bit_identical(pdev, groups):
+    """Every count is an exact integer sum, so whatever order the atomics land in, two executes
+    of the same resident batch must agree bit for bit: a data race between warps, streams (the
+    grouped first execute runs on two) or kernels, or a read of memory an earlier execute left
+    behind, shows up as a difference (compute-sanitizer's racecheck / initcheck are closed on this
+    pool).  30 executes of a mixed batch per path, the first one grouped."""
+    dev = pdev
+    rl, D, S = 36, 700, _shim.FLAG_SAME_TRACK
+    jobs = []
+    for c, L in enumerate([180000, 52000, 240000, 9000]):
+        fwd, rev, b, e = random_case(900 + c, L, rl, L // 9)
+        jobs.append(_shim.Job(L, rl, D, 3 if c != 1 else 1, fwd, rev, b if c != 1 else None, e if c != 1 else None))
+        if c == 2:
+            fwd2, rev2, _, _ = random_case(950, L, rl, L // 14, with_track=False)
+            jobs.append(_shim.Job(L, rl, D, 3 | S, fwd2, rev2))
+    _, _, b, e = random_case(960, 70000, rl, 10)
+    jobs.append(_shim.Job(70000, rl, D, _shim.FLAG_AUTOCORR, None, None, b, e))
+    dev.set_option("h2d_groups", groups)
+    dev.set_option("async_h2d", 1)
+    try:
+        batch = dev.prepare(jobs)
+        first = None
+        for it in range(30):
+            batch.execute()
+            got = batch.fetch()
+            if first is None:
+                first = got
+                continue
+            for a, w in zip(got, first):
+                for k in w:
+                    assert np.array_equal(np.asarray(a[k]), np.asarray(w[k])), (k, it)
+        batch.free()
+    finally:
+        dev.set_option("async_h2d", 0)
+        dev.set_option("h2d_groups", 4)
