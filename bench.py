@@ -9,21 +9,36 @@ Workload (BASELINE.json configs[2]/[1]): synthetic hg38-shaped gen
 chromosomes with the real hg38 lengths, 20 M single-end 36 bp ChIP-like reads, synthetic
 36-mer mappability track (~79 % mappable, ~1.6 M intervals), max_shift 1000, NCC+MSCC
 (``--mode ncc``: NCC only, configs[1]).  One STEP = the whole correlation stage of that genome:
-bit-array build (scatter + interval fill) and the shift-window kernel for all chromosomes, and
-for N > 1 the NCCL all-reduce of the per-shift counters.  N ranks cut the genome into N equal
-position ranges (pymasc_b200/sharding.py), so total work is fixed: strong scaling.
+from the packed position / interval lists to every per-shift counter of every chromosome, and for
+N > 1 the all-reduce of the counters.  N ranks cut the genome into N position ranges
+(pymasc_b200/sharding.py), so total work is fixed: strong scaling.
+
+Three device algorithms give the same counters (include/pymasc_b200.h, "path"); `auto` -- what
+the product runs -- picks the list kernels for this workload.  The line says which path ran
+(config.path) and carries the other two, run on the same inputs, under `paths` with
+`counters_equal_*` (a full-size cross-check of three independent algorithms).
 
 metric   bit-position x shift evals/s: sum_chrom (L + read_len + max_shift + 100) x (max_shift+1)
-         evals per step / step time.
+         evals per step / step time (delivered evals: the counts are those of the reference's
+         bit-array loop, whatever the algorithm).
 value    inputs (packed uint32 positions / intervals) resident in HBM; device time by CUDA
          events on the launching stream, max over ranks.
-e2e      same step through the C ABI from pinned HOST arrays: H2D + build + window
-         (+ all-reduce) + D2H of the counters inside the timed region.
-roofline popc pipe (the kernel is an integer AND+popcount reduction, not HBM- or tensor-bound):
-         algorithmic popc32 = evals x P / 32 (P = 5 NCC+MSCC, 1 NCC) / window-kernel time,
-         against the POPC issue rate measured live on the device (pmb_pipe_probe).
+e2e      same step through the C ABI from pinned HOST arrays: H2D + kernels (+ all-reduce) +
+         D2H of the counters inside the timed region.  PCIe-bound (90 MB per step).
+roofline of the dominant kernel of the path that ran.  List path: `bound` hbm -- SURVEY 8(d)'s
+         algorithmic bytes (the bit arrays the reference streams, 3 x Lbits/8) over the forward-read
+         kernel's CUDA-event time against MEASURED_PEAKS.json, with the DRAM traffic measured by
+         ncu (profiles/r02_traffic_lists.json) and the shared-memory-atomic rate that really binds
+         it beside it.  paths.dense.roofline is the north-star figure: the shift-window kernel
+         against the POPC rate measured live (pmb_pipe_probe).
 cpu_baseline / --impl reference: the UNMODIFIED reference calculator compiled into oracle/_ref
-         (CCBitArrayCalculator, fed read by read as handler/read.py does), on a bounded sample.
+         (CCBitArrayCalculator, fed read by read as handler/read.py does) on ALL of chr21 of the
+         workload -- not a cache-resident prefix; the N = 1 line also runs that chromosome through
+         the CUDA path and compares every vector (gpu_matches_reference_on_sample).
+configs  BASELINE.json configs[3] (200 M reads, max_shift 5000, position ranges) and configs[4]
+         (16 read sets over one track, by chromosome) at THIS N, each with ms_per_step, e2e and an
+         oracle check on a sample (tools/bench_blocks.py); skipped past --budget-s.
+s_per_bam  (N = 1) the workload as BAM + BigWig files on disk -> result objects, seconds per stage.
 """
 import argparse
 import json
@@ -39,6 +54,7 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
 
+T_START = time.time()
 READ_LEN = 36
 MAX_SHIFT = 1000
 N_READS = 20_000_000
@@ -184,11 +200,14 @@ def build_workload(mode, chrom_indices=None):
 
 
 # ---------------------------------------------------------------------------- CPU arms
+REF_KEYS = ("ncc", "mscc", "mfwd", "mrev", "mappable_len", "fwd_total", "rev_total")
+
+
 def _ref_task(args):
-    """One worker task of the reference arm: a chromosome-shaped sample through the
-    unmodified reference calculator (feed read by read, then finishup).  Returns
-    (evals, seconds, ncc ccbins[:4]) -- runs in a spawned process like a CalcWorker."""
-    (name, L, fwd, rev, begins, ends, mode) = args
+    """One worker task of the reference arm: a chromosome through the unmodified reference
+    calculator (feed read by read, then finishup) -- runs in a spawned process like a CalcWorker
+    (handler/worker.py:68-104).  Returns (evals, seconds, every result vector of the chromosome)."""
+    (name, L, fwd, rev, begins, ends, mode, max_shift) = args
     if ROOT not in sys.path:
         sys.path.insert(0, ROOT)
     from oracle import ref_runner
@@ -197,12 +216,40 @@ def _ref_task(args):
         np.full(len(rev), READ_LEN))
     tracks = {name: (begins, ends)} if mode == "both" else None
     t0 = time.perf_counter()
-    calc = ref_runner.run_reference(MAX_SHIFT, READ_LEN, [name], [L], {name: (pos, ln, is_rev)},
-                                    tracks=tracks)
+    # popcnt=None: the build is chosen per worker process through PYMASC_REF_POPCNT
+    calc = ref_runner.run_reference(max_shift, READ_LEN, [name], [L], {name: (pos, ln, is_rev)},
+                                    tracks=tracks, popcnt=None)
     dt = time.perf_counter() - t0
     res = calc.get_result(name)
-    evals = (L + READ_LEN + MAX_SHIFT + 100) * (MAX_SHIFT + 1)
-    return evals, dt, [int(x) for x in res.chrom.ccbins[:4]]
+    evals = (L + READ_LEN + max_shift + 100) * (max_shift + 1)
+    vec = {"ncc": [int(x) for x in res.chrom.ccbins], "fwd_total": int(res.chrom.forward_sum),
+           "rev_total": int(res.chrom.reverse_sum)}
+    if mode == "both":
+        m = res.mappable_chrom
+        vec.update(mscc=[int(x) for x in m.ccbins], mfwd=[int(x) for x in m.forward_sum],
+                   mrev=[int(x) for x in m.reverse_sum], mappable_len=[None if x is None else int(x) for x in m.mappable_len])
+    return evals, dt, vec
+
+
+def device_vectors(dev, task):
+    """The same chromosome through the CUDA path, in the reference's result layout."""
+    from pymasc_b200 import _shim
+    (name, L, fwd, rev, begins, ends, mode, max_shift) = task
+    flags = _shim.FLAG_NCC | (_shim.FLAG_MSCC if mode == "both" else 0)
+    got = dev.run_batch([_shim.Job(L, READ_LEN, max_shift, flags, fwd, rev, begins, ends)])[0]
+    vec = {"ncc": got["ncc"].tolist(), "fwd_total": int(got["fwd_total"]), "rev_total": int(got["rev_total"])}
+    if mode == "both":
+        d = got["dmp"].tolist()       # popc(D_k) -> the reference's mappable_len list (mscc.pyx:271, :292-298)
+        n = min(READ_LEN, max_shift + 1)
+        ml = [None] * READ_LEN
+        ml[READ_LEN - n:READ_LEN] = d[:n][::-1]
+        vec.update(mscc=got["mscc"].tolist(), mfwd=got["mfwd"].tolist(), mrev=got["mrev"].tolist(),
+                   mappable_len=ml + d[2 * READ_LEN - 1:max_shift + 1])
+    return vec
+
+
+def whole_chromosome(chrom):
+    return (chrom["name"], int(chrom["length"]), chrom["fwd"], chrom["rev"], chrom["begins"], chrom["ends"])
 
 
 def sample_chromosome(chrom, length):
@@ -216,49 +263,54 @@ def sample_chromosome(chrom, length):
     return (chrom["name"], int(length), fwd, rev, b, e)
 
 
-def cpu_baseline_leg(workload, mode, sample_bp, check_device=None):
-    """Reference calculator on ONE core over a bounded sample (rank 0, N = 1 only)."""
+def cpu_baseline_leg(workload, mode, check_device=None, with_popcnt=True):
+    """Reference calculator on ONE core over ALL of chr21 of this workload at the workload's own
+    max_shift (46.7 Mbp: 5.8 MB per bit array, several arrays per shift -- not cache-resident;
+    BASELINE.md: "time chr1 and chr21 in full").  Rank 0, N = 1 only, after every timed region."""
     from oracle import ref_runner
     if not ref_runner.available():
         return {"value": None, "unit": UNIT, "cores": 0, "kind": "reference",
                 "sample": "oracle/_ref missing (build it where /root/reference exists)"}
     chrom = workload[20]   # chr21
-    task = sample_chromosome(chrom, min(sample_bp, chrom["length"]))
-    evals, dt, head = _ref_task(task + (mode,))
+    task = whole_chromosome(chrom) + (mode, MAX_SHIFT)
+    evals, dt, vec = _ref_task(task)
     out = {"value": evals / dt, "unit": UNIT, "cores": 1, "kind": "reference",
-           "seconds": round(dt, 2),
-           "sample": "first %d bp of %s of this workload (%d fwd + %d rev reads, %s intervals), all %d "
-                     "shifts, feed_*_read per read + finishup_calculation, %s" %
-                     (task[1], task[0], len(task[2]), len(task[3]),
+           "seconds": round(dt, 2), "same_config_as_gpu_arm": True,
+           "sample": "ALL of %s of this workload (%d bp, %d fwd + %d rev reads, %s intervals), all %d "
+                     "shifts, feed_*_read per read + finishup_calculation, %s; the genome is %.1fx this" %
+                     (task[0], task[1], len(task[2]), len(task[3]),
                       "no" if task[4] is None else len(task[4]), MAX_SHIFT + 1,
-                      "NCC+MSCC" if mode == "both" else "NCC")}
-    # SURVEY 8d: the same sample through the reference rebuilt with -mpopcnt (its setup.py does
+                      "NCC+MSCC" if mode == "both" else "NCC",
+                      sum(c["length"] for c in workload) / float(task[1]))}
+    # SURVEY 8d: the same chromosome through the reference rebuilt with -mpopcnt (its setup.py does
     # not pass it, so the stock build popcounts in software, external/bitcnt.h:26-44), in a
     # spawned interpreter because one process can import only one build of the package
-    if ref_runner.available(popcnt=True):
+    if with_popcnt and ref_runner.available(popcnt=True):
         import multiprocessing as mp
         os.environ["PYMASC_REF_POPCNT"] = "1"
         try:
             with mp.get_context("spawn").Pool(1) as pool:
-                ev2, dt2, head2 = pool.apply(_ref_task, (task + (mode,),))
+                ev2, dt2, vec2 = pool.apply(_ref_task, (task,))
         finally:
             os.environ.pop("PYMASC_REF_POPCNT", None)
         out["reference_plus_popcnt"] = {"value": ev2 / dt2, "unit": UNIT, "cores": 1, "seconds": round(dt2, 2),
                                         "flags": "-O3 -ffast-math -mpopcnt (oracle/_ref_popcnt)",
-                                        "same_counts": head2 == head}
-    if check_device is not None:   # the same sample through the CUDA path must agree
-        from pymasc_b200 import _shim
-        flags = _shim.FLAG_NCC | (_shim.FLAG_MSCC if mode == "both" else 0)
-        got = check_device.run_batch([_shim.Job(task[1], READ_LEN, MAX_SHIFT, flags, task[2],
-                                                task[3], task[4], task[5])])[0]
-        out["gpu_matches_reference_on_sample"] = [int(x) for x in got["ncc"][:4]] == head
+                                        "same_counts": vec2 == vec}
+    if check_device is not None:   # the same chromosome through the CUDA path must agree -- everywhere
+        got = device_vectors(check_device, task)
+        keys = [k for k in REF_KEYS if k in vec]
+        out["gpu_matches_reference_on_sample"] = all(got[k] == vec[k] for k in keys)
+        out["gpu_vs_reference_compared"] = "%s: every value of %s at all %d shifts" % (task[0], ", ".join(keys), MAX_SHIFT + 1)
     return out
 
 
 def reference_arm(args):
-    """--impl reference: the reference's own `-p N` scheme (one spawned process per task pulled
-    from a pool, handler/calc.py:163-192) on all host cores; each step = `cores` chromosome-
-    shaped samples of the workload."""
+    """--impl reference: the reference's own `-p N` scheme (spawned workers pulling one
+    chromosome each, handler/calc.py:163-192) on all host cores.  Each task is ALL of chr21 of the
+    workload (arrays of 5.8 MB: not cache-resident); what is bounded, so that K + W steps end
+    within a few minutes, is the number of SHIFTS per step -- the reference's cost per shift does
+    not depend on max_shift (ten whole-array passes per shift, mscc.pyx:288-317), so evals/s carry
+    over.  With a budget that allows it the step runs the workload's own max_shift."""
     import multiprocessing as mp
     from oracle import ref_runner
     mode = args.mode
@@ -268,45 +320,58 @@ def reference_arm(args):
     cores = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
     if args.ref_cores:
         cores = args.ref_cores
-    n_steps = args.steps + args.warmup
-    # size the sample so that the whole run stays within ~4 minutes: calibrate on 1 Mb
-    workload, _ = build_workload(mode, chrom_indices=list(range(24))[-min(24, cores):] if cores < 24 else None)
-    live = [c for c in workload if len(c["fwd"])]
-    ev, dt, _ = _ref_task(sample_chromosome(live[-1], 1_000_000) + (mode,))
-    per_bp = dt / 1_000_000
-    budget = min(25.0, 200.0 / max(1, n_steps))
-    sample_bp = int(max(2_000_000, min(40_000_000, budget / per_bp)))
-    tasks = []
-    for i in range(cores):
-        c = live[i % len(live)]
-        tasks.append(sample_chromosome(c, min(sample_bp, c["length"])) + (mode,))
+    workload, _ = build_workload(mode, chrom_indices=[20])
+    chr21 = whole_chromosome(workload[20])
     ctx = mp.get_context("spawn")
     times = []
     with ctx.Pool(processes=cores) as pool:
-        pool.map(_ref_task, [sample_chromosome(live[0], 200_000) + (mode,)] * cores)  # import warm-up
-        for s in range(n_steps):
+        # import warm-up + calibration under full load: every core runs all of chr21 at 16 and at
+        # 64 shifts; the difference is 48 shifts without the set-up (allocation, feed, track load)
+        t0 = time.perf_counter()
+        pool.map(_ref_task, [chr21 + (mode, 15)] * cores, chunksize=1)
+        t1 = time.perf_counter()
+        pool.map(_ref_task, [chr21 + (mode, 63)] * cores, chunksize=1)
+        t2 = time.perf_counter()
+        per_shift = max(1e-4, ((t2 - t1) - (t1 - t0)) / 48.0)
+        setup = max(0.0, (t1 - t0) - 16 * per_shift)
+        budget = min(40.0, 200.0 / max(1, args.steps)) - setup
+        shifts = int(max(32, min(MAX_SHIFT + 1, budget / per_shift)))
+        D = shifts - 1
+        tasks = [chr21 + (mode, D)] * cores
+        warm = [chr21 + (mode, 15)] * cores
+        for s in range(args.warmup):
+            pool.map(_ref_task, warm, chunksize=1)
+        for s in range(args.steps):
             t0 = time.perf_counter()
             res = pool.map(_ref_task, tasks, chunksize=1)
-            dt = time.perf_counter() - t0
-            if s >= args.warmup:
-                times.append((sum(r[0] for r in res), dt))
+            times.append((sum(r[0] for r in res), time.perf_counter() - t0))
     evals = sum(t[0] for t in times)
     secs = sum(t[1] for t in times)
     value = evals / secs
-    sample = ("%d tasks per step (one per core), each the first %d bp of a workload chromosome as a "
-              "stand-alone chromosome, all %d shifts, feed per read + finishup, %s" %
-              (cores, sample_bp, MAX_SHIFT + 1, "NCC+MSCC" if mode == "both" else "NCC"))
+    sample = ("%d tasks per step (one per core, spawned workers), each ALL of chr21 of the workload (%d bp, "
+              "%d fwd + %d rev reads%s) at %d of the %d shifts (max_shift %d; the reference's cost per shift "
+              "is constant), feed per read + finishup, %s; warm-up steps run 16 shifts" %
+              (cores, chr21[1], len(chr21[2]), len(chr21[3]),
+               ", %d intervals" % len(chr21[4]) if chr21[4] is not None else "", shifts, MAX_SHIFT + 1, D,
+               "NCC+MSCC" if mode == "both" else "NCC"))
     line = {
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * secs / max(1, len(times)),
         "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "u64",
         "data": "synthetic", "config": workload_config(mode),
         "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "reference",
-                         "sample": sample},
+                         "sample": sample, "shifts_per_step": shifts, "full_max_shift": shifts == MAX_SHIFT + 1},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
+        "whole_genome_correlation_stage_s_at_this_rate": sum(
+            (L + READ_LEN + MAX_SHIFT + 100) for L in genome_lengths()) * (MAX_SHIFT + 1) / value,
     }
     print(json.dumps(line))
+
+
+def genome_lengths():
+    from pymasc_b200 import synth
+    return [L for _, L in synth.HG38]
 
 
 def workload_config(mode):
@@ -378,13 +443,22 @@ def gpu_arm(args):
 
     with torch.cuda.stream(stream):
         # ---- resident-input arm
+        def reduce(b):
+            """Sum the per-shift counters of a batch over the ranks, in place on the device.  The
+            list path checks its inputs' order while it counts: the first reduce of a batch
+            settles that check first (pmb_batch_validate), later ones go straight through."""
+            if not getattr(b, "_validated", False):
+                b.validate()
+                b._validated = True
+                b._ctr = counters_tensor(b)
+            dist.all_reduce(b._ctr)
+
         batch = dev.prepare(jobs)
-        ctr = counters_tensor(batch) if world > 1 else None
 
         def step():
             batch.execute()
             if world > 1:
-                dist.all_reduce(ctr)
+                reduce(batch)
 
         for _ in range(args.warmup):
             step()
@@ -427,30 +501,34 @@ def gpu_arm(args):
             barrier()
             mine_ms = ev0.elapsed_time(ev1) / args.steps
             exec_only_ms = {"max": max_over_ranks(mine_ms), "min": -max_over_ranks(-mine_ms)}
-            dist.all_reduce(ctr)        # the last execute above left this rank's partial counts
+            reduce(batch)               # the last execute above left this rank's partial counts
         resident = batch.fetch()
         batch.free()
 
-        # ---- the other algorithm on the same inputs: must give identical counters; the dense
-        #      shift-window kernel is the one the popc-pipe roofline is quoted on
-        other = None
+        # ---- the other algorithms on the same inputs: identical counters are required; the dense
+        #      shift-window kernel is the one the popc-pipe roofline (north_star) is quoted on
+        others = {}
         if not args.single_path:
-            dev.set_option("path", 1 if used_path == 2 else 2)
-            ob = dev.prepare(jobs)
-            o_win, o_build = [], []
-            for _ in range(4):
-                ob.execute()
-                t2 = dev.timing()
-                o_win.append(t2["window_ms"]); o_build.append(t2["build_ms"])
-            if world > 1:
-                dist.all_reduce(counters_tensor(ob))
-            o_out = ob.fetch()
-            ob.free()
+            for op in (1, 2, 3):
+                if op == used_path:
+                    continue
+                dev.set_option("path", op)
+                ob = dev.prepare(jobs)
+                o_win, o_build, o_fwd = [], [], []
+                for _ in range(4):
+                    ob.execute()
+                    t2 = dev.timing()
+                    o_win.append(t2["window_ms"]); o_build.append(t2["build_ms"]); o_fwd.append(t2["ev_fwd_ms"])
+                if world > 1:
+                    reduce(ob)
+                o_out = ob.fetch()
+                ob.free()
+                others[op] = {"window_ms": float(np.mean(o_win[1:])), "build_ms": float(np.mean(o_build[1:])),
+                              "fwd_ms": float(np.mean(o_fwd[1:])), "pairs": t2["window_word_shift_pairs"],
+                              "launches": t2["launches"],
+                              "same": all(np.array_equal(np.asarray(a[k]), np.asarray(b2[k]))
+                                          for a, b2 in zip(resident, o_out) for k in a)}
             dev.set_option("path", {"auto": 0, "dense": 1, "events": 2, "lists": 3}[args.path])
-            other = {"path": t2["path"], "window_ms": float(np.mean(o_win[1:])),
-                     "build_ms": float(np.mean(o_build[1:])), "pairs": t2["window_word_shift_pairs"],
-                     "same": all(np.array_equal(np.asarray(a[k]), np.asarray(b2[k]))
-                                 for a, b2 in zip(resident, o_out) for k in a)}
 
         # ---- end-to-end arm: pinned host arrays in, counters on the host out
         def e2e_step():
@@ -458,7 +536,7 @@ def gpu_arm(args):
             try:
                 b.execute()
                 if world > 1:
-                    dist.all_reduce(counters_tensor(b))
+                    reduce(b)
                 return b.fetch()                       # D2H + sync
             finally:
                 b.free()
@@ -540,23 +618,67 @@ def gpu_arm(args):
                     "note": "latency/issue-bound today (see profiles/); evals/s of this path are "
                             "delivered evals: the counts equal the dense kernel's bit for bit"}
 
-        paths = {}
-        if used_path == 2:
+        def measured_traffic():
+            """DRAM bytes of every kernel of one list-path step, from the committed ncu capture
+            (profiles/r02_traffic_lists.json, written by tools/ncu_traffic.py from an
+            `ncu --set full` report of tools/list_prof.py) -- measured, per launch, N = 1."""
+            try:
+                with open(os.path.join(ROOT, "profiles", "r02_traffic_lists.json")) as fh:
+                    return json.load(fh)
+            except (OSError, ValueError):
+                return None
+
+        def lists_roofline(fwd_s, all_s):
+            """List kernels: no bit array exists.  Per SURVEY 8(d) the algorithmic bytes of a step
+            are the bit arrays the reference's path streams (2 or 3 x Lbits/8): `achieved` is those
+            bytes over the dominant kernel's time, i.e. DELIVERED bandwidth (the counts equal the
+            dense kernel's bit for bit).  What the kernels really read are the packed lists (90 MB);
+            they are bound by shared-memory atomics and dependent issue, not by HBM -- see `lists`."""
+            nbytes = (3 if mode == "both" else 2) * bits_bytes
+            tr = measured_traffic() if (world == 1 and mode == "both") else None
+            out = {"bound": "hbm", "kernel": "list_fwd_kernel",
+                   "achieved": nbytes / fwd_s / 1e9, "peak": hbm_peak, "unit": "GB/s",
+                   "frac": nbytes / fwd_s / 1e9 / hbm_peak, "peak_source": peak_src,
+                   "algorithmic_bytes": nbytes, "kernel_ms": fwd_s * 1e3, "all_list_kernels_ms": all_s * 1e3,
+                   "whole_step_frac": nbytes / (ms_per_step * 1e-3) / 1e9 / hbm_peak,
+                   "traffic": tr["kernels"]["list_fwd_kernel"]["dram_bytes"] if tr else None,
+                   "traffic_whole_step": tr["step_dram_bytes"] if tr else None,
+                   "traffic_source": tr["source"] if tr else None,
+                   "lists": {"input_bytes": int(h2d), "input_gbs_over_all_kernels": h2d / all_s / 1e9,
+                             "note": "delivered evals: the path reads the sorted lists, never the bit arrays; "
+                                     "DRAM traffic is far BELOW the algorithmic bytes"}}
+            if tr and "shared_atomic_instr" in tr["kernels"]["list_fwd_kernel"]:
+                n_at = tr["kernels"]["list_fwd_kernel"]["shared_atomic_instr"]
+                peak_at = tr.get("atoms_warp_instr_per_s_peak")
+                out["lists"].update(fwd_shared_atomic_warp_instr=n_at, fwd_atomic_instr_per_s=n_at / fwd_s,
+                                    atomic_peak_instr_per_s=peak_at,
+                                    atomic_frac=(n_at / fwd_s / peak_at) if peak_at else None,
+                                    atomic_peak_source=tr.get("atoms_peak_source"))
+            return out
+
+        names = {1: "dense", 2: "events", 3: "lists"}
+        mine = {"window_ms": win_s * 1e3, "build_ms": float(np.mean(build_ms)),
+                "launches_per_step": int(launches_per_step)}
+        if used_path == 3:
+            roof = lists_roofline(float(np.mean(fwd_ms)) * 1e-3, win_s)
+            roof.update(rev_kernel_ms=float(np.mean(rev_ms)), edge_and_finalize_ms=float(np.mean(edge_ms)),
+                        zero_ms=float(np.mean(build_ms)), kernel_launches_per_step=int(launches_per_step))
+        elif used_path == 2:
             roof = events_roofline(float(np.mean(fwd_ms)) * 1e-3, win_s)
             roof.update(rev_kernel_ms=float(np.mean(rev_ms)), edge_kernel_ms=float(np.mean(edge_ms)),
                         build_ms=float(np.mean(build_ms)), kernel_launches_per_step=int(win_launches))
-            paths["events"] = {"window_ms": win_s * 1e3, "build_ms": float(np.mean(build_ms))}
-            if other:
-                paths["dense"] = {"window_ms": other["window_ms"], "build_ms": other["build_ms"],
-                                  "roofline": dense_roofline(other["window_ms"] * 1e-3, other["pairs"]),
-                                  "counters_equal_events_path": other["same"]}
         else:
             roof = dense_roofline(win_s, pairs)
             roof.update(build_ms=float(np.mean(build_ms)), kernel_launches_per_step=int(win_launches))
-            paths["dense"] = {"window_ms": win_s * 1e3, "build_ms": float(np.mean(build_ms))}
-            if other:
-                paths["events"] = {"window_ms": other["window_ms"], "build_ms": other["build_ms"],
-                                   "counters_equal_dense_path": other["same"]}
+        paths = {names[used_path]: mine}
+        for op, o in others.items():
+            entry = {"window_ms": o["window_ms"], "build_ms": o["build_ms"], "launches_per_step": o["launches"],
+                     "counters_equal_%s_path" % names[used_path]: o["same"]}
+            if op == 1:     # north_star: the dense kernel's popc-pipe roofline is always reported
+                entry["roofline"] = dense_roofline(o["window_ms"] * 1e-3, o["pairs"])
+            if op == 2:
+                entry["roofline"] = events_roofline(o["fwd_ms"] * 1e-3, o["window_ms"] * 1e-3)
+            paths[names[op]] = entry
         line = {
             "metric": METRIC, "value": evals_total / (ms_per_step * 1e-3), "unit": UNIT,
             "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_per_step,
@@ -564,13 +686,15 @@ def gpu_arm(args):
             "data": "synthetic", "config": dict(workload_config(mode),
                                                 parallelism="position ranges x%d + NCCL all-reduce" % world
                                                 if world > 1 else "1 GPU",
-                                                path="events" if used_path == 2 else "dense"),
+                                                path=names[used_path]),
             "e2e": {"value": evals_total / (e2e_ms * 1e-3), "unit": UNIT, "ms_per_step": e2e_ms,
                     "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
                     "api": "pmb_batch_prepare/execute/fetch via ctypes (pymasc_b200._shim)",
                     "h2d": ("pipelined: up to %d chromosome groups (none under 16 MiB) on a copy stream"
                             % args.h2d_groups)
-                           if args.h2d_groups > 0 else "copy, then compute"},
+                           if args.h2d_groups > 0 else "copy, then compute",
+                    "pcie_floor_ms": h2d / 55e9 * 1e3,
+                    "note": "PCIe-bound: the step's inputs cross the bus once per step"},
             "gpu_launches": int(launches_per_step * args.steps),
             "launches_per_step": int(launches_per_step),
             "clocks": clocks,
@@ -580,11 +704,42 @@ def gpu_arm(args):
             "resident_equals_e2e": bool(same),
             "synthetic_generation_s": round(gen_s, 1),
         }
+    # ---- the other BASELINE configs at this N, and the "s per BAM" half of the metric
+    blocks = {}
+    if not args.no_configs:
+        sys.path.insert(0, os.path.join(ROOT, "tools"))
+        import bench_blocks
+        comm = {"reduce": reduce, "barrier": barrier, "max_over_ranks": max_over_ranks,
+                "all_true": lambda ok: max_over_ranks(0.0 if ok else 1.0) == 0.0}
+        for key, fn, est_s in (("configs[3]", bench_blocks.deep_library_block, 60.0),
+                               ("configs[4]", bench_blocks.multi_file_block, 60.0)):
+            spent = max_over_ranks(time.time() - T_START)       # one decision for all ranks
+            if spent + est_s > args.budget_s:
+                blocks[key] = {"skipped": "time budget: %.0f s spent of %.0f" % (spent, args.budget_s)}
+                continue
+            with torch.cuda.stream(stream):
+                blocks[key] = fn(dev, stream, world, rank, comm, steps=max(3, min(args.steps, 5)))
+    if rank == 0:
+        line["configs"] = blocks
         if world == 1 and not args.no_cpu_baseline:
             dev.set_stream(None)
-            line["cpu_baseline"] = cpu_baseline_leg(workload, mode, args.cpu_sample_bp, check_device=dev)
+            line["cpu_baseline"] = cpu_baseline_leg(workload, mode, check_device=dev)
         else:
             line["cpu_baseline"] = None
+        if world == 1 and not args.no_bam and time.time() - T_START + 60.0 <= args.budget_s + 120.0:
+            sys.path.insert(0, os.path.join(ROOT, "tools"))
+            import bench_blocks
+            dev.set_stream(None)
+            bam = bench_blocks.s_per_bam_block(workload, MAX_SHIFT)
+            cb = line.get("cpu_baseline") or {}
+            if cb.get("value"):
+                cores = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
+                bam["reference_correlation_stage_s"] = {
+                    "one_core": evals_total / cb["value"], "all_%d_cores_if_p_N_scaled_perfectly" % cores:
+                    evals_total / cb["value"] / cores,
+                    "source": "cpu_baseline of this line (all of chr21 on one core), scaled by evals; "
+                              "`bench.py --impl reference` measures the -p N rate on all cores"}
+            line["s_per_bam"] = bam
         sys.stdout.flush()
         os.dup2(real_stdout, 1)
         print(json.dumps(line), flush=True)
@@ -613,7 +768,10 @@ def main():
     ap.add_argument("--opt", action="append", default=[], help="pmb_set_option name=value (tuning)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-clocks", action="store_true", help="do not poll NVML during the timed region (diagnostic)")
-    ap.add_argument("--cpu-sample-bp", type=int, default=20_000_000)
+    ap.add_argument("--no-configs", action="store_true", help="skip the configs[3] / configs[4] blocks")
+    ap.add_argument("--no-bam", action="store_true", help="skip the s-per-BAM block (N = 1 only)")
+    ap.add_argument("--budget-s", type=float, default=200.0,
+                    help="wall-clock budget: a configs block that would start later than this is skipped")
     ap.add_argument("--ref-cores", type=int, default=0)
     args = ap.parse_args()
     args.warmup = max(args.warmup, 0)
