@@ -389,7 +389,6 @@ def gpu_arm(args):
     import torch
     import torch.distributed as dist
     from pymasc_b200 import _shim, sharding, synth
-    from pymasc_b200.distributed import counters_tensor
 
     world = env_int("WORLD_SIZE", 1)
     rank = env_int("RANK", 0)
@@ -443,15 +442,20 @@ def gpu_arm(args):
 
     with torch.cuda.stream(stream):
         # ---- resident-input arm
+        if world > 1:
+            # the C ABI's own communicator (pmb_comm_init): rank 0's id travels through torch.distributed,
+            # which this script otherwise uses for the barrier and the max-over-ranks of the timings only
+            idt = torch.zeros(_shim.Device.COMM_ID_BYTES, dtype=torch.uint8, device="cuda")
+            if rank == 0:
+                idt.copy_(torch.frombuffer(bytearray(_shim.Device.comm_get_id()), dtype=torch.uint8))
+            dist.broadcast(idt, src=0)
+            dev.comm_init(idt.cpu().numpy().tobytes(), rank, world)
+
         def reduce(b):
-            """Sum the per-shift counters of a batch over the ranks, in place on the device.  The
-            list path checks its inputs' order while it counts: the first reduce of a batch
-            settles that check first (pmb_batch_validate), later ones go straight through."""
-            if not getattr(b, "_validated", False):
-                b.validate()
-                b._validated = True
-                b._ctr = counters_tensor(b)
-            dist.all_reduce(b._ctr)
+            """pmb_allreduce: in-place NCCL sum of the batch's device counter block over the ranks,
+            on the context's stream.  The first reduce of a batch also settles the ranks' status
+            words (range errors, the list path's order check); later ones are asynchronous."""
+            b.allreduce()
 
         batch = dev.prepare(jobs)
 

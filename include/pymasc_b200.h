@@ -184,6 +184,36 @@ void pmb_host_free(void *p);
 int  pmb_set_option(pmb_ctx *ctx, const char *name, int64_t value);
 
 /*
+ * The collective for position shards (the reference has no counterpart: its
+ * `-p N` workers exchange pickled results through a multiprocessing.Queue,
+ * PyMaSC/handler/calc.py:163-235).  Every rank runs the SAME job list with its own range_lo /
+ * range_hi (see pymasc_b200/sharding.py), so the counter blocks share one layout and one
+ * ncclAllReduce(int64, sum) over NVLink completes every per-shift vector on every rank.
+ * NCCL is bound at run time (a copy already in the process, else libnccl.so.2, or $PMB_NCCL_LIB).
+ *
+ *   one process per GPU (torchrun, MPI):  rank 0 calls pmb_comm_get_id and hands the
+ *       PMB_COMM_ID_BYTES to the other ranks by any side channel; every rank calls pmb_comm_init.
+ *   one process, n GPUs:  pmb_comm_init_all over n contexts on n different devices.
+ *   pmb_allreduce(ctxs, batches, n): after pmb_batch_execute on every rank, in-place sum of the
+ *       counter blocks (what pmb_batch_counters exposes, plus two status words) on each context's
+ *       stream; n = 1 in a process per GPU, n = all contexts in one process.  pmb_batch_fetch then
+ *       returns the complete vectors on every rank.  The FIRST all-reduce of a batch also agrees
+ *       on the ranks' status and waits for the result once: a position beyond the array on any
+ *       rank -> PMB_ERR_RANGE on every rank; lists that one rank found unsorted -> every rank
+ *       recomputes its share and the reduce is repeated.  Later all-reduces of the same batch
+ *       (repeated executes) are asynchronous.
+ *   A rank that fails BEFORE the collective (pmb_batch_prepare / execute returned an error) must
+ *   not simply leave: the others would wait in NCCL.  Agree on the local status first (the
+ *   Python engines do, pymasc_b200/distributed.py).
+ */
+#define PMB_COMM_ID_BYTES 128
+int  pmb_comm_get_id(void *id_out);                                  /* ncclGetUniqueId                 */
+int  pmb_comm_init(pmb_ctx *ctx, const void *id, int rank, int world);
+int  pmb_comm_init_all(pmb_ctx **ctxs, int n);
+int  pmb_allreduce(pmb_ctx **ctxs, pmb_batch **batches, int n);
+void pmb_comm_destroy(pmb_ctx *ctx);                                 /* also done by pmb_destroy        */
+
+/*
  * pmb_run_chrom_noalloc -- one chromosome through the list kernels WITHOUT any allocation.
  * (No counterpart in the reference: added for callers
  * that cannot call cudaMalloc -- code under CUDA graph capture, tight serving loops, harnesses

@@ -60,7 +60,8 @@ EXPORTS = (
     "pmb_batch_prepare", "pmb_batch_execute", "pmb_batch_fetch", "pmb_batch_counters",
     "pmb_batch_free", "pmb_get_timing", "pmb_stream", "pmb_synchronize", "pmb_host_alloc",
     "pmb_host_free", "pmb_set_option", "pmb_pipe_probe", "pmb_set_stream", "pmb_device_count",
-    "pmb_batch_validate", "pmb_run_chrom_noalloc",
+    "pmb_batch_validate", "pmb_run_chrom_noalloc", "pmb_comm_get_id", "pmb_comm_init", "pmb_comm_init_all",
+    "pmb_allreduce", "pmb_comm_destroy",
 )
 
 _lib = None
@@ -100,6 +101,16 @@ def load_library():
     L.pmb_batch_counters.restype = ctypes.c_int
     L.pmb_batch_validate.argtypes = [vp, vp]
     L.pmb_batch_validate.restype = ctypes.c_int
+    L.pmb_comm_get_id.argtypes = [vp]
+    L.pmb_comm_get_id.restype = ctypes.c_int
+    L.pmb_comm_init.argtypes = [vp, vp, ctypes.c_int, ctypes.c_int]
+    L.pmb_comm_init.restype = ctypes.c_int
+    L.pmb_comm_init_all.argtypes = [vpp, ctypes.c_int]
+    L.pmb_comm_init_all.restype = ctypes.c_int
+    L.pmb_allreduce.argtypes = [vpp, vpp, ctypes.c_int]
+    L.pmb_allreduce.restype = ctypes.c_int
+    L.pmb_comm_destroy.argtypes = [vp]
+    L.pmb_comm_destroy.restype = None
     L.pmb_run_chrom_noalloc.argtypes = [vp, ctypes.POINTER(ChromArgs), vp, ctypes.c_uint64]
     L.pmb_run_chrom_noalloc.restype = ctypes.c_int
     L.pmb_batch_free.argtypes = [vp, vp]
@@ -268,6 +279,41 @@ class Device(object):
         self._check(self._L.pmb_run_batch(self._h, args, outs, len(jobs)))
         return self._collect(jobs, outs, arrays)
 
+    # ---- the collective (include/pymasc_b200.h: pmb_comm_*, pmb_allreduce)
+    COMM_ID_BYTES = 128
+
+    @staticmethod
+    def comm_get_id():
+        """128 bytes that name a new communicator (rank 0 creates them, every rank gets a copy)."""
+        buf = ctypes.create_string_buffer(Device.COMM_ID_BYTES)
+        L = load_library()
+        if L.pmb_comm_get_id(buf) != PMB_OK:
+            raise DeviceError("pmb_comm_get_id failed: %s" % L.pmb_last_error(None).decode())
+        return buf.raw
+
+    def comm_init(self, comm_id, rank, world):
+        buf = ctypes.create_string_buffer(bytes(comm_id), Device.COMM_ID_BYTES)
+        self._check(self._L.pmb_comm_init(self._h, buf, int(rank), int(world)))
+        self.comm_rank, self.comm_world = int(rank), int(world)
+
+    @staticmethod
+    def comm_init_all(devices):
+        """One communicator over the contexts of one process (one per device)."""
+        n = len(devices)
+        arr = (ctypes.c_void_p * n)(*[d._h.value for d in devices])
+        devices[0]._check(devices[0]._L.pmb_comm_init_all(arr, n))
+        for i, d in enumerate(devices):
+            d.comm_rank, d.comm_world = i, n
+
+    @staticmethod
+    def allreduce(batches):
+        """In-place sum of the batches' device counter blocks over their contexts' communicator
+        (one batch in a process per GPU; all of them in a single process)."""
+        n = len(batches)
+        ctxs = (ctypes.c_void_p * n)(*[b.dev._h.value for b in batches])
+        bs = (ctypes.c_void_p * n)(*[b._h.value for b in batches])
+        batches[0].dev._check(batches[0].dev._L.pmb_allreduce(ctxs, bs, n))
+
     NOALLOC_MAX_SHIFT = 4095
 
     @staticmethod
@@ -316,6 +362,10 @@ class Batch(object):
 
     def execute(self):
         self.dev._check(self.dev._L.pmb_batch_execute(self.dev._h, self._h))
+
+    def allreduce(self):
+        """Sum this batch's device counters over the ranks of the context's communicator."""
+        Device.allreduce([self])
 
     def validate(self):
         """After the first execute, before the device counters are read without a fetch (an

@@ -2,6 +2,8 @@
 // Host-side planning + launches for the bit-array build and shift-window kernels.
 // sm_100a only; there is no CPU path in this library.
 #include <cuda_runtime.h>
+#include <dlfcn.h>
+#include <nccl.h>      // types only: the library is bound at run time (nccl_api below), not linked
 #include <stdint.h>
 #include <stdio.h>
 #include <stdlib.h>
@@ -40,6 +42,8 @@ struct pmb_ctx {
     int list_blocks_per_sm = 0;
     int check_selftest = 0;      // -DPMB_CHECKED builds: make every TMA range check of the event kernels fail (proves the chain)
     bool list_attr_done = false; // the list kernels' shared-memory limit is raised on THIS device
+    ncclComm_t comm = nullptr;   // pmb_comm_init / pmb_comm_init_all
+    int comm_rank = 0, comm_world = 1;
     unsigned long long* noalloc_scratch = nullptr;   // device address of g_noalloc_scratch on this device
     int list_pairs_limit = 0;    // auto: lists while the expected reverse reads per forward read and 1024 shifts stay below this
     int event_tile_words = 0;
@@ -128,6 +132,7 @@ struct pmb_batch {
     // list path (pmb_lists.cuh): job table, entry prefixes (fwd | rev | intervals, n + 1 each),
     // difference histograms [n][4][stride], edge products [n][2][stride] + direct lags [n][2]
     bool list_ok = false;               // the inputs qualify for the list path
+    bool reduce_checked = false;        // the first all-reduce of the batch has agreed on the ranks' status words
     bool list_checked = false;          // an execute on the list path has found the inputs sorted
     ListJob* d_listjobs = nullptr;
     unsigned long long* d_list_prefix = nullptr;
@@ -250,9 +255,11 @@ extern "C" int pmb_device_count(void)
     return cudaGetDeviceCount(&n) == cudaSuccess ? n : 0;
 }
 
+extern "C" void pmb_comm_destroy(pmb_ctx* c);
 extern "C" void pmb_destroy(pmb_ctx* c)
 {
     if (!c) return;
+    pmb_comm_destroy(c);
     cudaSetDevice(c->device);
     if (c->stream) cudaStreamSynchronize(c->stream);
     for (auto& ev : c->ev)
@@ -926,7 +933,7 @@ static int prepare_impl(pmb_ctx* c, const pmb_chrom_args* a, uint32_t n, pmb_bat
         // table uploads are small H2D copies on the compute stream, and behind 90 MB .. 1.2 GB of
         // inputs on the same copy engine they held the first kernel back by the whole input copy
         // (measured: 16 read sets, execute started 22 ms late; one genome, ~1 ms).
-        CU_TRY(c, cudaMallocAsync((void**)&b->d_counters, b->counter_words * 8, c->stream));
+        CU_TRY(c, cudaMallocAsync((void**)&b->d_counters, (b->counter_words + 2) * 8, c->stream));   // + the all-reduce's status words
         CU_TRY(c, cudaMallocAsync((void**)&b->d_err, 4 * (4 + 128), c->stream));
         {
             int rc = b->path == 3 ? plan_lists(c, b) : plan_arrays(c, b);
@@ -1592,6 +1599,208 @@ extern "C" int pmb_run_batch(pmb_ctx* c, const pmb_chrom_args* a, pmb_chrom_out*
 extern "C" int pmb_run_chrom(pmb_ctx* c, const pmb_chrom_args* a, pmb_chrom_out* o)
 {
     return pmb_run_batch(c, a, o, 1);
+}
+
+// ------------------------------------------------------------------ the collective (NCCL over NVLink)
+// Position shards add up: every rank carries the same job list, so the counter blocks
+// have one layout and ONE ncclAllReduce(int64, sum) of the whole block completes the result on
+// every rank.  NCCL is bound at run time: a copy already loaded into the process (torch brings
+// one) is preferred, else libnccl.so.2 from the loader's path, or $PMB_NCCL_LIB -- the library
+// itself links no NCCL, so single-GPU hosts need none.
+struct NcclApi {
+    void* handle = nullptr;
+    ncclResult_t (*GetUniqueId)(ncclUniqueId*) = nullptr;
+    ncclResult_t (*CommInitRank)(ncclComm_t*, int, ncclUniqueId, int) = nullptr;
+    ncclResult_t (*CommInitAll)(ncclComm_t*, int, const int*) = nullptr;
+    ncclResult_t (*CommDestroy)(ncclComm_t) = nullptr;
+    ncclResult_t (*AllReduce)(const void*, void*, size_t, ncclDataType_t, ncclRedOp_t, ncclComm_t, cudaStream_t) = nullptr;
+    ncclResult_t (*GroupStart)() = nullptr;
+    ncclResult_t (*GroupEnd)() = nullptr;
+    const char* (*GetErrorString)(ncclResult_t) = nullptr;
+    std::string error;
+};
+
+static NcclApi* nccl_api()
+{
+    static NcclApi api;
+    static bool tried = false;
+    if (tried) return &api;
+    tried = true;
+    const char* env = getenv("PMB_NCCL_LIB");
+    void* h = nullptr;
+    if (env && *env) h = dlopen(env, RTLD_NOW | RTLD_GLOBAL);
+    if (!h) h = dlopen("libnccl.so.2", RTLD_NOW | RTLD_NOLOAD);      // the process's own copy, if it has one
+    if (!h) h = dlopen("libnccl.so.2", RTLD_NOW | RTLD_GLOBAL);
+    if (!h) h = dlopen("libnccl.so", RTLD_NOW | RTLD_GLOBAL);
+    if (!h) { api.error = std::string("NCCL not found (libnccl.so.2; set PMB_NCCL_LIB): ") + (dlerror() ? dlerror() : ""); return &api; }
+    api.handle = h;
+    bool ok = true;
+    auto sym = [&](const char* name) { void* p = dlsym(h, name); if (!p) { ok = false; api.error = std::string("NCCL symbol missing: ") + name; } return p; };
+    api.GetUniqueId = (decltype(api.GetUniqueId))sym("ncclGetUniqueId");
+    api.CommInitRank = (decltype(api.CommInitRank))sym("ncclCommInitRank");
+    api.CommInitAll = (decltype(api.CommInitAll))sym("ncclCommInitAll");
+    api.CommDestroy = (decltype(api.CommDestroy))sym("ncclCommDestroy");
+    api.AllReduce = (decltype(api.AllReduce))sym("ncclAllReduce");
+    api.GroupStart = (decltype(api.GroupStart))sym("ncclGroupStart");
+    api.GroupEnd = (decltype(api.GroupEnd))sym("ncclGroupEnd");
+    api.GetErrorString = (decltype(api.GetErrorString))sym("ncclGetErrorString");
+    if (!ok) api.handle = nullptr;
+    return &api;
+}
+
+#define NCCL_TRY(ctx, api, call)                                                                  \
+    do {                                                                                          \
+        ncclResult_t r__ = (call);                                                                \
+        if (r__ != ncclSuccess) {                                                                 \
+            (ctx)->err = std::string(#call) + " failed: " + (api)->GetErrorString(r__);           \
+            return PMB_ERR_CUDA;                                                                  \
+        }                                                                                         \
+    } while (0)
+
+extern "C" int pmb_comm_get_id(void* id_out)
+{
+    if (!id_out) return PMB_ERR_ARG;
+    NcclApi* api = nccl_api();
+    if (!api->handle) { g_create_error = api->error; return PMB_ERR_CUDA; }
+    ncclUniqueId id;
+    if (api->GetUniqueId(&id) != ncclSuccess) { g_create_error = "ncclGetUniqueId failed"; return PMB_ERR_CUDA; }
+    memcpy(id_out, &id, sizeof id);
+    return PMB_OK;
+}
+
+extern "C" int pmb_comm_init(pmb_ctx* c, const void* id_in, int rank, int world)
+{
+    if (!c) return PMB_ERR_ARG;
+    if (!id_in || world < 1 || rank < 0 || rank >= world) { c->err = "pmb_comm_init: bad rank / world / id"; return PMB_ERR_ARG; }
+    if (c->comm) { c->err = "pmb_comm_init: the context already has a communicator"; return PMB_ERR_ARG; }
+    NcclApi* api = nccl_api();
+    if (!api->handle) { c->err = api->error; return PMB_ERR_CUDA; }
+    CU_TRY(c, cudaSetDevice(c->device));
+    ncclUniqueId id;
+    memcpy(&id, id_in, sizeof id);
+    NCCL_TRY(c, api, api->CommInitRank(&c->comm, world, id, rank));
+    c->comm_rank = rank;
+    c->comm_world = world;
+    return PMB_OK;
+}
+
+extern "C" int pmb_comm_init_all(pmb_ctx** ctxs, int n)
+{
+    if (!ctxs || n < 1 || !ctxs[0]) return PMB_ERR_ARG;
+    pmb_ctx* c0 = ctxs[0];
+    NcclApi* api = nccl_api();
+    if (!api->handle) { c0->err = api->error; return PMB_ERR_CUDA; }
+    std::vector<int> devs(n);
+    std::vector<ncclComm_t> comms(n, nullptr);
+    for (int i = 0; i < n; i++) {
+        if (!ctxs[i] || ctxs[i]->comm) { c0->err = "pmb_comm_init_all: null context or communicator already set"; return PMB_ERR_ARG; }
+        devs[i] = ctxs[i]->device;
+        for (int k = 0; k < i; k++)
+            if (devs[k] == devs[i]) { c0->err = "pmb_comm_init_all: one context per device"; return PMB_ERR_ARG; }
+    }
+    NCCL_TRY(c0, api, api->CommInitAll(comms.data(), n, devs.data()));
+    for (int i = 0; i < n; i++) { ctxs[i]->comm = comms[i]; ctxs[i]->comm_rank = i; ctxs[i]->comm_world = n; }
+    return PMB_OK;
+}
+
+extern "C" void pmb_comm_destroy(pmb_ctx* c)
+{
+    if (!c || !c->comm) return;
+    NcclApi* api = nccl_api();
+    cudaSetDevice(c->device);
+    cudaStreamSynchronize(c->stream);
+    if (api->handle) api->CommDestroy(c->comm);
+    c->comm = nullptr;
+    c->comm_world = 1;
+    c->comm_rank = 0;
+}
+
+// the rank's status (range error, inputs unsorted) as two int64 behind the counters: summed with them
+__global__ void status_words_kernel(const int* __restrict__ flags, unsigned long long* __restrict__ tail, int checked)
+{
+    tail[0] = (flags[0] != 0) ? 1ull : 0ull;
+    tail[1] = (!checked && flags[1] != 0) ? 1ull : 0ull;
+}
+
+static int allreduce_enqueue(NcclApi* api, pmb_ctx** ctxs, pmb_batch** bs, int n)
+{
+    for (int i = 0; i < n; i++) {
+        pmb_ctx* c = ctxs[i];
+        CU_TRY(c, cudaSetDevice(c->device));
+        status_words_kernel<<<1, 1, 0, c->stream>>>(bs[i]->d_err, bs[i]->d_counters + bs[i]->counter_words,
+                                                    bs[i]->path != 3 || bs[i]->list_checked ? 1 : 0);
+        CU_TRY(c, cudaGetLastError());
+    }
+    if (n > 1) NCCL_TRY(ctxs[0], api, api->GroupStart());
+    for (int i = 0; i < n; i++) {
+        pmb_ctx* c = ctxs[i];
+        if (n > 1) cudaSetDevice(c->device);
+        NCCL_TRY(c, api, api->AllReduce(bs[i]->d_counters, bs[i]->d_counters, bs[i]->counter_words + 2, ncclInt64, ncclSum,
+                                        c->comm, c->stream));
+    }
+    if (n > 1) NCCL_TRY(ctxs[0], api, api->GroupEnd());
+    return PMB_OK;
+}
+
+// In-place sum of the counter blocks over the communicator, on each context's stream.  The FIRST
+// all-reduce of a batch also agrees on the ranks' status (it waits for the result once): a
+// position out of range on any rank fails the call on every rank; inputs that the list path found
+// unsorted on any rank make every rank recompute its share (that rank on the event path) and
+// reduce again.  Later all-reduces of the batch are asynchronous.
+extern "C" int pmb_allreduce(pmb_ctx** ctxs, pmb_batch** bs, int n)
+{
+    if (!ctxs || !bs || n < 1 || !ctxs[0]) return PMB_ERR_ARG;
+    pmb_ctx* c0 = ctxs[0];
+    return guarded(c0, [&]() -> int {
+        NcclApi* api = nccl_api();
+        if (!api->handle) { c0->err = api->error; return PMB_ERR_CUDA; }
+        for (int i = 0; i < n; i++) {
+            if (!ctxs[i] || !bs[i] || !ctxs[i]->comm) { c0->err = "pmb_allreduce: context without a communicator (pmb_comm_init)"; return PMB_ERR_ARG; }
+            if (bs[i]->counter_words != bs[0]->counter_words) { c0->err = "pmb_allreduce: the batches' job lists differ"; return PMB_ERR_ARG; }
+        }
+        int rc = allreduce_enqueue(api, ctxs, bs, n);
+        if (rc != PMB_OK) return rc;
+        bool all_checked = true;
+        for (int i = 0; i < n; i++) all_checked = all_checked && bs[i]->reduce_checked;
+        if (all_checked) return PMB_OK;
+        // first reduce: read the summed status words (the same on every rank)
+        unsigned long long st[2] = {0, 0};
+        for (int i = 0; i < n; i++) {
+            pmb_ctx* c = ctxs[i];
+            CU_TRY(c, cudaSetDevice(c->device));
+            unsigned long long s[2];
+            CU_TRY(c, cudaMemcpyAsync(s, bs[i]->d_counters + bs[i]->counter_words, 16, cudaMemcpyDeviceToHost, c->stream));
+            CU_TRY(c, cudaStreamSynchronize(c->stream));
+            st[0] = s[0]; st[1] = s[1];
+        }
+        if (st[0]) {
+            for (int i = 0; i < n; i++)
+                ctxs[i]->err = "a read position or mappability interval lies beyond chrom_len + read_len + max_shift + 100 bits "
+                               "(on at least one rank)";
+            return PMB_ERR_RANGE;
+        }
+        if (st[1]) {        // some rank's lists were unsorted: every rank recomputes (the sum overwrote its share)
+            for (int i = 0; i < n; i++) {
+                pmb_ctx* c = ctxs[i];
+                CU_TRY(c, cudaSetDevice(c->device));
+                int h_flags[2] = {0, 0};
+                int rc2;
+                if (bs[i]->path == 3 && !bs[i]->list_checked) {
+                    // (the flags were cleared by nothing since the execute: still the rank's own)
+                    CU_TRY(c, cudaMemcpy(h_flags, bs[i]->d_err, 8, cudaMemcpyDeviceToHost));
+                    rc2 = h_flags[1] ? fallback_to_events(c, bs[i]) : pmb_batch_execute(c, bs[i]);
+                } else {
+                    rc2 = pmb_batch_execute(c, bs[i]);
+                }
+                if (rc2 != PMB_OK) return rc2;
+                bs[i]->list_checked = true;
+            }
+            for (int i = 0; i < n; i++) bs[i]->reduce_checked = true;
+            return allreduce_enqueue(api, ctxs, bs, n);
+        }
+        for (int i = 0; i < n; i++) { bs[i]->reduce_checked = true; bs[i]->list_checked = true; }
+        return PMB_OK;
+    });
 }
 
 // ------------------------------------------------------------------ one chromosome, no allocation

@@ -491,6 +491,7 @@ __global__ void __launch_bounds__(256) list_finalize_kernel(const ListJob* __res
     __shared__ long long part[256];
     const ListJob& J = jobs[blockIdx.x];
     if (!(J.flags & (EVF_MSCC | EVF_AUTOCORR))) return;       // uniform per CTA
+    if (J.lo >= J.hi) return;       // a chromosome outside this rank's position range: every vector stays zero
     const bool autocorr = (J.flags & EVF_AUTOCORR) != 0;
     if (!autocorr) {
         for (int which = 0; which < 2; ++which) {

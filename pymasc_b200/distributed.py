@@ -4,10 +4,13 @@
 of the process group feeds the same reads (or at least closes the same chromosomes) and calls
 ``run(jobs)`` with the same job list; each rank counts its position shard of every chromosome
 (``sharding.plan_weighted``), the (max_shift+1)-long int64 count vectors are summed across ranks with a
-single ``all_reduce`` -- NCCL over NVLink/NVSwitch when the local engine is a device, on the
-device counter block itself (no host round trip) -- and every rank returns the full result.
+single all-reduce -- ``pmb_allreduce`` of the C ABI (NCCL over NVLink/NVSwitch) when the local
+engine is a device, on the device counter block itself (no host round trip) -- and every rank
+returns the full result.
 
-torch is used for the process group only; the counts come from libpymasc_b200.so.
+torch.distributed is used for the rendezvous only (rank / world, carrying the communicator id,
+agreeing that no rank failed before the collective); counts and their sum come from
+libpymasc_b200.so.
 """
 import numpy as np
 
@@ -91,25 +94,62 @@ class ShardedEngine(object):
             return self._run_device(mine)
         return self._run_host(mine)
 
-    # NCCL path: reduce the device counter block in place, then one D2H
-    def _run_device(self, mine):
+    def _agree(self, failed, device=None):
+        """Has ANY rank failed so far?  (A rank that raises before the collective would leave the
+        others waiting in it: everyone learns of the failure here and raises instead.)"""
         import torch
+        where = ("cuda:%d" % device) if device is not None and self._dist.get_backend(self._group) == "nccl" else "cpu"
+        t = torch.tensor([1 if failed else 0], dtype=torch.int32, device=where)
+        self._dist.all_reduce(t, op=self._dist.ReduceOp.MAX, group=self._group)
+        return bool(int(t.item()))
+
+    def _ensure_comm(self, dev):
+        """The context's NCCL communicator (pmb_comm_init): rank 0 of the group creates the id,
+        torch.distributed carries its 128 bytes to the others -- the only use of torch here."""
+        if getattr(dev, "comm_world", 1) == self.world and getattr(dev, "_comm_group", None) is self._group:
+            return
+        import torch
+        backend = self._dist.get_backend(self._group)
+        where = ("cuda:%d" % dev.ordinal) if backend == "nccl" else "cpu"
+        t = torch.zeros(_shim.Device.COMM_ID_BYTES, dtype=torch.uint8, device=where)
+        if self.rank == 0:
+            t.copy_(torch.frombuffer(bytearray(_shim.Device.comm_get_id()), dtype=torch.uint8))
+        src = self._dist.get_global_rank(self._group, 0) if self._group is not None else 0
+        self._dist.broadcast(t, src=src, group=self._group)
+        dev.comm_init(bytes(t.cpu().numpy().tobytes()), self.rank, self.world)
+        dev._comm_group = self._group
+
+    # NCCL path: the device counter blocks are summed in place through the C ABI (pmb_allreduce),
+    # then one D2H.  A position out of range on any rank raises PositionOutOfRange on every rank.
+    def _run_device(self, mine):
         dev = self.local
-        with torch.cuda.device(dev.ordinal):
-            dev.set_stream(torch.cuda.current_stream().cuda_stream)
+        self._ensure_comm(dev)
+        batch, err = None, None
+        try:
             batch = dev.prepare(mine)
-            try:
-                batch.execute()
-                self._dist.all_reduce(counters_tensor(batch), group=self._group)
-                return batch.fetch()
-            finally:
+            batch.execute()
+        except Exception as e:      # noqa: BLE001 -- raised below, once every rank knows
+            err = e
+        try:
+            if self._agree(err is not None, dev.ordinal):
+                raise err if err is not None else _shim.DeviceError(
+                    "another rank failed before the all-reduce; this rank's counts are discarded")
+            batch.allreduce()
+            return batch.fetch()
+        finally:
+            if batch is not None:
                 batch.free()
-                dev.set_stream(None)
 
     # host path (gloo): used by the CPU tests of the sharding logic
     def _run_host(self, mine):
         import torch
-        outs = self.local.run(mine)
+        outs, err = None, None
+        try:
+            outs = self.local.run(mine)
+        except Exception as e:      # noqa: BLE001
+            err = e
+        if self._agree(err is not None):
+            raise err if err is not None else RuntimeError("another rank failed before the all-reduce")
         flat, index = [], []
         for i, o in enumerate(outs):
             for k in sorted(o):

@@ -16,10 +16,11 @@ built once.
 ``split="position"`` is the other decomposition of SURVEY.md 8(e), for deep libraries whose
 largest chromosome is too much for one GPU's share (BASELINE configs[3]): every device counts
 one position range of the concatenated genome with halos rebuilt from the clipped inputs
-(pymasc_b200.sharding), and the per-device count vectors -- (max_shift+1) int64 per counter and
-chromosome, ~1 MB per device -- are summed on the host after the D2H.  (One process per GPU
-with an NCCL all-reduce of the device counter blocks is ``pymasc_b200.distributed.ShardedEngine``;
-in one process the host sum is cheaper than setting up a communicator.)
+(pymasc_b200.sharding), and the per-device counter blocks -- (max_shift+1) int64 per counter and
+chromosome, ~1 MB per device -- are summed in place by ``pmb_allreduce`` (one NCCL communicator
+over the process's contexts, ``pmb_comm_init_all``); device 0's block is then the only D2H.
+(Several contexts on ONE device -- the single-GPU tests -- cannot form a communicator and are
+summed on the host.  One process per GPU is ``pymasc_b200.distributed.ShardedEngine``.)
 """
 import os
 import threading
@@ -74,6 +75,7 @@ class MultiDeviceEngine(object):
                 raise _shim.DeviceError("no CUDA device visible -- pymasc_b200 has no CPU fallback")
         self._specs = list(devices)
         self._engines = [None] * len(self._specs)
+        self._comm_ready = False
         self.last_placement = None
         self.last_device_ms = None      # per device: CUDA-event time of its execute (None for test engines)
 
@@ -99,13 +101,21 @@ class MultiDeviceEngine(object):
         errors = []
         self.last_device_ms = [None] * n_dev
 
+        # position ranges on distinct devices: counters stay on the devices and are all-reduced
+        on_device = by_position and all(not hasattr(sp, "run") for sp in self._specs) and \
+            len(set(int(sp) for sp in self._specs)) == n_dev
+        batches = [None] * n_dev
+
         def work(k):
             idx = placement[k]
             if not idx:
                 return
             try:
                 eng = self._engine(k)
-                if by_position:
+                if on_device:
+                    batches[k] = eng.device.prepare(shards[k])
+                    batches[k].execute()
+                elif by_position:
                     parts[k] = eng.run(shards[k])
                 else:
                     for i, out in zip(idx, eng.run([jobs[i] for i in idx])):
@@ -121,8 +131,19 @@ class MultiDeviceEngine(object):
         work(0)
         for t in threads:
             t.join()
-        if errors:
-            raise errors[0]
+        try:
+            if errors:
+                raise errors[0]
+            if on_device:
+                if not self._comm_ready:
+                    _shim.Device.comm_init_all([self._engine(k).device for k in range(n_dev)])
+                    self._comm_ready = True
+                _shim.Device.allreduce(batches)
+                return batches[0].fetch()
+        finally:
+            for b in batches:
+                if b is not None:
+                    b.free()
         if by_position:
             from .sharding import sum_outputs
             return sum_outputs(parts)
@@ -133,6 +154,7 @@ class MultiDeviceEngine(object):
             if isinstance(e, _DeviceRunner):
                 e.close()
         self._engines = [None] * len(self._specs)
+        self._comm_ready = False
 
 
 class _DeviceRunner(object):
