@@ -25,6 +25,7 @@ import numpy as np
 
 from . import _shim
 from .exceptions import PositionOutOfRange, ReadUnsortedError
+from .result import mscc_cc, ncc_cc
 from .result import (
     BothChromResult, BothGenomeWideResult, EmptyMSCCResult, EmptyNCCResult, MSCCGenomeWideResult,
     MSCCResult, NCCGenomeWideResult, NCCResult,
@@ -349,7 +350,8 @@ class CCBitArrayCalculator(object):
                           forward_sum=out["fwd_total"], reverse_sum=out["rev_total"],
                           forward_read_len_sum=p.fwd_len_sum, reverse_read_len_sum=p.rev_len_sum,
                           ccbins=_ints(out["ncc"]))
-            r.calc_cc()
+            # calc_cc()'s curve, computed from the vector itself (result.ncc_cc: bit-identical)
+            r.cc = ncc_cc(out["fwd_total"], out["rev_total"], np.asarray(out["ncc"]), L, self._max_shift)
             self.ref2ncc_result[chrom] = r
         if p.intervals is not None:
             r = MSCCResult(max_shift=self._max_shift, read_len=self._read_len, genomelen=L,
@@ -358,7 +360,8 @@ class CCBitArrayCalculator(object):
                            forward_read_len_sum=p.fwd_len_sum, reverse_read_len_sum=p.rev_len_sum,
                            ccbins=_ints(out["mscc"]),
                            mappable_len=self._mappable_len_list(out["dmp"]))
-            r.calc_cc()
+            r.cc = mscc_cc(np.asarray(out["mfwd"]), np.asarray(out["mrev"]), np.asarray(out["mscc"]),
+                           np.asarray(out["dmp"]), self._read_len, self._max_shift)
             self.ref2mscc_result[chrom] = r
         self._progress.clean()
 

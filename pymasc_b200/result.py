@@ -22,6 +22,64 @@ from typing import Any, Dict, Optional
 
 import numpy as np
 
+def _normalised_cc(forward_sum, reverse_sum, ccbins, totlen, denom):
+    bins = np.array(ccbins, dtype=np.int64)
+    if bins.sum() == 0:
+        return np.full_like(bins, np.nan, dtype=np.float64)
+
+    def body():
+        fmean = forward_sum / totlen
+        rmean = reverse_sum / totlen
+        fvar = fmean * (1 - fmean)
+        rvar = rmean * (1 - rmean)
+        prod = fmean * rmean
+        geo = (fvar * rvar) ** 0.5
+        return (bins / denom - prod) / geo
+
+    try:
+        with np.errstate(divide="raise", invalid="raise"):
+            return body()
+    except (FloatingPointError, ZeroDivisionError):
+        with np.errstate(divide="ignore", invalid="ignore"):
+            return body()
+
+
+
+# ---------------------------------------------------------------------------- cc from the count vectors
+# SURVEY.md 8(f) row 4 (`calc_cc`, PyMaSC/result.py:42-118): the calculator holds the per-shift
+# counts as int64 numpy vectors when they come back from the device, while the result classes
+# keep them as Python lists (the reference's field type) and `calc_cc()` converts every list
+# back to an array -- four conversions of max_shift+1 Python ints per chromosome, most of the
+# host time of a finished batch.  These two functions compute the same float64 curve straight
+# from the vectors, in calc_cc's own operation order (bit-identical: tests/test_calculator_host.py),
+# so the calculator assigns `result.cc` instead of calling `result.calc_cc()`.  It stays on the
+# host: max_shift+1 float64 values per chromosome give a device nothing to do.
+def ncc_cc(forward_sum, reverse_sum, ccbins, genomelen, max_shift):
+    """NCCResult.calc_cc (PyMaSC/result.py:82-89) from an int64 vector."""
+    shifts = np.arange(max_shift + 1, dtype=np.float64)
+    return _normalised_cc(float(forward_sum), float(reverse_sum), ccbins[:max_shift + 1], genomelen,
+                          genomelen - shifts)
+
+
+def mappable_len_array(dmp, read_len, max_shift):
+    """float64 form of the reference's mappable_len list (mscc.pyx:271, :292-298; unset slots NaN,
+    as np.array(list_with_None, dtype=float64) gives them)."""
+    S = max_shift + 1
+    n = min(read_len, S)
+    ml = np.full(read_len, np.nan)
+    ml[read_len - n:read_len] = dmp[:n][::-1]
+    return np.concatenate((ml, np.asarray(dmp[2 * read_len - 1:S], dtype=np.float64)))
+
+
+def mscc_cc(forward_sum, reverse_sum, ccbins, dmp, read_len, max_shift):
+    """MSCCResult.calc_cc (PyMaSC/result.py:104-118) from int64 vectors; `dmp` = popc(D_k) by shift."""
+    n = max_shift + 1
+    ml = mappable_len_array(dmp, read_len, max_shift)
+    tot = np.concatenate((ml[:read_len][::-1], ml[1:]))[:n]
+    return _normalised_cc(np.asarray(forward_sum[:n], dtype=np.float64), np.asarray(reverse_sum[:n], dtype=np.float64),
+                          ccbins[:n], tot, tot)
+
+
 try:  # inside PyMaSC: hand back the reference's own types
     if os.environ.get("PYMASC_B200_MIRROR_RESULTS"):  # tests: force the mirrors
         raise ImportError("mirrors forced")
@@ -33,27 +91,6 @@ try:  # inside PyMaSC: hand back the reference's own types
     USING_REFERENCE_TYPES = True
 except Exception:  # stand-alone mirrors
     USING_REFERENCE_TYPES = False
-
-    def _normalised_cc(forward_sum, reverse_sum, ccbins, totlen, denom):
-        bins = np.array(ccbins, dtype=np.int64)
-        if bins.sum() == 0:
-            return np.full_like(bins, np.nan, dtype=np.float64)
-
-        def body():
-            fmean = forward_sum / totlen
-            rmean = reverse_sum / totlen
-            fvar = fmean * (1 - fmean)
-            rvar = rmean * (1 - rmean)
-            prod = fmean * rmean
-            geo = (fvar * rvar) ** 0.5
-            return (bins / denom - prod) / geo
-
-        try:
-            with np.errstate(divide="raise", invalid="raise"):
-                return body()
-        except (FloatingPointError, ZeroDivisionError):
-            with np.errstate(divide="ignore", invalid="ignore"):
-                return body()
 
     @dataclass
     class NCCResult:

@@ -101,6 +101,13 @@ for label, target, with_track in (("fixture_ncc", CalculationTarget.NCC, False),
     assert type(whole).__module__ == ref_result.__name__          # the reference's own result classes
     chrom = calc.get_result("chr1")
     assert isinstance(chrom, ref_result.BothChromResult)
+    # the calculator assigns .cc from the count vectors; the reference's own calc_cc() on the same
+    # objects must give the same float64 values bit for bit (PyMaSC/result.py:82-118)
+    import numpy as np
+    for res in list(whole.chroms.values()) + list(getattr(whole, "mappable_chroms", {}).values()):
+        cc0 = np.array(res.cc, dtype=np.float64, copy=True)
+        res.calc_cc()
+        assert np.array_equal(cc0, np.asarray(res.cc, dtype=np.float64), equal_nan=True), type(res).__name__
     if bwfeeder is not None:
         bwfeeder.close()
     out[label] = {"whole": helpers.snapshot_whole(whole), "progress": hook.calls,

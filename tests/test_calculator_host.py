@@ -152,3 +152,33 @@ def test_default_engine_fails_loudly_without_a_gpu():
     calc.feed_reverse_read("a", 30, 20)
     with pytest.raises(DeviceError):
         calc.finishup_calculation()
+
+
+def test_cc_from_the_count_vectors_is_bit_identical_to_calc_cc():
+    """The calculator assigns result.cc from the int64 vectors (pymasc_b200.result.ncc_cc / mscc_cc)
+    instead of calling calc_cc() on the list fields (PyMaSC/result.py:82-118): same float64 values,
+    bit for bit -- NaN curves for all-zero counts, division by a zero mappable length, and the None
+    slots of a mappable_len list when max_shift < 2 read_len - 1 included."""
+    import numpy as np
+    from pymasc_b200 import result as R
+    rng = np.random.default_rng(5)
+    for rl, D in ((36, 300), (36, 50), (36, 20), (5, 3), (101, 1300)):
+        S = D + 1
+        for zero in (False, True):
+            ncc = np.zeros(S, np.int64) if zero else rng.integers(0, 5000, S).astype(np.int64)
+            mscc = np.zeros(S, np.int64) if zero else rng.integers(0, 4000, S).astype(np.int64)
+            mfwd = rng.integers(1, 90000, S).astype(np.int64)
+            mrev = rng.integers(1, 90000, S).astype(np.int64)
+            dmp = rng.integers(100000, 900000, S).astype(np.int64)
+            dmp[rng.integers(0, S, 3)] = 0                        # division by zero somewhere
+            L = 1000000
+            n = R.NCCResult(max_shift=D, read_len=rl, genomelen=L, forward_sum=41234, reverse_sum=40111,
+                            forward_read_len_sum=1, reverse_read_len_sum=1, ccbins=ncc.tolist())
+            n.calc_cc()
+            assert np.array_equal(R.ncc_cc(41234, 40111, ncc, L, D), n.cc, equal_nan=True)
+            calc = CCBitArrayCalculator(D, rl, ["c"], [L], engine=OracleEngine())
+            m = R.MSCCResult(max_shift=D, read_len=rl, genomelen=L, forward_sum=mfwd.tolist(), reverse_sum=mrev.tolist(),
+                             forward_read_len_sum=1, reverse_read_len_sum=1, ccbins=mscc.tolist(),
+                             mappable_len=calc._mappable_len_list(dmp))
+            m.calc_cc()
+            assert np.array_equal(R.mscc_cc(mfwd, mrev, mscc, dmp, rl, D), m.cc, equal_nan=True)

@@ -1,6 +1,7 @@
 """Where the end-to-end step goes: host wall time of prepare / execute / fetch / free on the
 bench workload, for copy-then-compute and for the pipelined input copy, next to the bare
-PCIe time of the same bytes.  Run on the GPU box: python tools/e2e_breakdown.py"""
+PCIe time of the same bytes.  Run on the GPU box: python tools/e2e_breakdown.py [world]
+(world > 1: rank 0's share of the `world` position ranges -- the per-rank fixed cost of an N-GPU step)"""
 import json
 import os
 import sys
@@ -17,12 +18,13 @@ def main():
     import torch
     from pymasc_b200 import _shim, sharding, synth
     lengths = [L for _, L in synth.HG38]
-    pieces = sharding.plan(lengths, bench.READ_LEN, bench.MAX_SHIFT, 1)[0]
+    world = int(sys.argv[1]) if len(sys.argv) > 1 else 1
+    pieces = sharding.plan(lengths, bench.READ_LEN, bench.MAX_SHIFT, world)[0]
     workload, _ = bench.build_workload("both")
     jobs = sharding.jobs_for_rank(workload, pieces, bench.READ_LEN, bench.MAX_SHIFT)
     nbytes = bench.pinned_pack(jobs)
     dev = _shim.Device(0)
-    out = {"h2d_bytes": nbytes}
+    out = {"h2d_bytes": nbytes, "world": world}
 
     # bare PCIe: one pinned buffer of the same size
     src = torch.empty(nbytes, dtype=torch.uint8).pin_memory()
@@ -63,6 +65,7 @@ def main():
     for _ in range(100):
         dev._marshal(jobs)
     out["marshal_ms"] = round((time.perf_counter() - t0) * 10, 3)
+    out["device_timing_last"] = dev.timing()
     print(json.dumps(out))
 
 
