@@ -220,7 +220,7 @@ void pmb_comm_destroy(pmb_ctx *ctx);                                 /* also don
  * that forbid it.)
  *
  * The list path's scratch (job table, difference histograms of mfwd / mrev, run-edge products,
- * the two direct lags: ~197 KB) lives in a file-scope `static __device__` array of the library,
+ * the two direct lags: ~257 KB) lives in a file-scope `static __device__` array of the library,
  * sized for max_shift <= PMB_NOALLOC_MAX_SHIFT; every GPU that loads the library holds it until
  * the process exits.  The call issues kernels on the context's stream and returns without
  * waiting; it calls no cudaMalloc / cudaFree / cudaHostAlloc and copies nothing.

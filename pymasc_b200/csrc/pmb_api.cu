@@ -132,6 +132,8 @@ struct pmb_batch {
     // list path (pmb_lists.cuh): job table, entry prefixes (fwd | rev | intervals, n + 1 each),
     // difference histograms [n][4][stride], edge products [n][2][stride] + direct lags [n][2]
     bool list_ok = false;               // the inputs qualify for the list path
+    size_t list_acc_copy = 0;           // words of ONE copy of the list accumulators (there are two, see ListJob)
+    uint32_t list_execs = 0;            // executes so far on the list path: execute k uses copy k & 1
     bool reduce_checked = false;        // the first all-reduce of the batch has agreed on the ranks' status words
     bool list_checked = false;          // an execute on the list path has found the inputs sorted
     ListJob* d_listjobs = nullptr;
@@ -722,13 +724,20 @@ static int plan_lists(pmb_ctx* c, pmb_batch* b)
 {
     const size_t n = b->jobs.size();
     const size_t stride = b->stride;
-    b->list_acc_words = n * (6 * stride + 2);       // [n][4][stride] differences | [n][2][stride] edge products | [n][2] lags
+    // two copies of [n][LA_N][stride] + [n][2] totals | [n][2][stride] run-edge products + [n][2] lags
+    const size_t job_acc = LA_N * stride + 2, job_aux = 2 * stride + 2;
+    b->list_acc_copy = n * (job_acc + job_aux);
+    b->list_acc_words = 2 * b->list_acc_copy;
     CU_TRY(c, cudaMallocAsync((void**)&b->d_list_acc, b->list_acc_words * 8, c->stream));
+    // cleared ONCE: from then on the finalize of every execute clears the copy the next one uses.
+    // The outputs are written, not added to -- but a job outside this rank's range is never written.
+    CU_TRY(c, cudaMemsetAsync(b->d_list_acc, 0, b->list_acc_words * 8, c->stream));
+    CU_TRY(c, cudaMemsetAsync(b->d_counters, 0, (b->counter_words + 2) * 8, c->stream));
+    CU_TRY(c, cudaMemsetAsync(b->d_err, 0, 4 * (4 + 128), c->stream));
     CU_TRY(c, cudaMallocAsync((void**)&b->d_listjobs, n * sizeof(ListJob), c->stream));
     CU_TRY(c, cudaMallocAsync((void**)&b->d_list_prefix, 3 * (n + 1) * 8, c->stream));
-    unsigned long long* diff0 = b->d_list_acc;
-    unsigned long long* aux0 = diff0 + n * 4 * stride;
-    unsigned long long* lag0 = aux0 + n * 2 * stride;
+    unsigned long long* acc0 = b->d_list_acc;
+    unsigned long long* aux0 = acc0 + n * job_acc;
     std::vector<ListJob>& table = b->h_listjobs;
     std::vector<unsigned long long>& pre = b->h_list_prefix;
     table.assign(n, ListJob{});
@@ -751,9 +760,8 @@ static int plan_lists(pmb_ctx* c, pmb_batch* b)
         if (j.owner >= 0) e.flags |= EVF_SHARED;
         e.counters = b->d_counters + i * PMB_NCOUNTERS * stride;
         e.totals = b->d_counters + n * PMB_NCOUNTERS * stride + 2 * i;
-        e.diff = diff0 + i * 4 * stride;
-        e.aux = aux0 + io * 2 * stride;
-        e.adirect = lag0 + 2 * io;
+        e.acc = acc0 + i * job_acc;
+        e.aux = aux0 + io * job_aux;
         e.lo = j.lo; e.hi = j.hi; e.nbits = j.nbits;
         table[i] = e;
         pre[i + 1] = pre[i] + e.n_fwd;
@@ -1055,15 +1063,9 @@ static int execute_lists(pmb_ctx* c, pmb_batch* b)
     uint32_t launches = 0;
     list_attributes(c);
     CU_TRY(c, cudaEventRecord(c->ev[0], st));
-    {
-        ZeroSegs z{};
-        z.p[0] = (uint4*)b->d_counters;  z.n16[0] = b->counter_words * 8 / 16;
-        z.p[1] = (uint4*)b->d_list_acc;  z.n16[1] = b->list_acc_words * 8 / 16;
-        z.p[2] = (uint4*)b->d_err;       z.n16[2] = 4 * (4 + 128) / 16;
-        zero_segments_kernel<<<c->num_sms, 512, 0, st>>>(z);
-        launches++;
-    }
-    CU_TRY(c, cudaEventRecord(c->ev[1], st));
+    CU_TRY(c, cudaEventRecord(c->ev[1], st));     // (no build stage: nothing is zeroed or built per execute)
+    const uint32_t parity = b->list_execs & 1u;
+    b->list_execs++;
     const bool grouped = b->h2d_pending && b->groups.size() > 1;
     const size_t n_pass = grouped ? b->groups.size() : 1;
     if (b->h2d_pending && !grouped)
@@ -1073,7 +1075,11 @@ static int execute_lists(pmb_ctx* c, pmb_batch* b)
     P.max_shift = b->max_shift;
     P.read_len = b->read_len;
     P.stride = b->stride;
-    P.flags = b->d_err;
+    P.flags = b->d_err + 2 * parity;
+    P.acc_off = parity ? b->list_acc_copy : 0;
+    P.acc_other = parity ? 0 : b->list_acc_copy;
+    P.flags_other = b->d_err + 2 * (parity ^ 1u);
+    P.status_tail = b->d_counters + b->counter_words;
     const uint32_t bps = c->list_blocks_per_sm > 0 ? (uint32_t)c->list_blocks_per_sm : (uint32_t)LIST_MIN_BLOCKS;
     const unsigned long long* pre = b->h_list_prefix.data();
     auto grid_for = [&](unsigned long long items) {
@@ -1106,15 +1112,14 @@ static int execute_lists(pmb_ctx* c, pmb_batch* b)
             if (kind < 2 && pass + 1 == n_pass) CU_TRY(c, cudaEventRecord(c->evk[kind], st));   // (per-kernel split: ungrouped passes only)
         }
     }
-    if (b->any_mscc || b->any_autocorr) {
-        list_finalize_kernel<<<(unsigned)n, 256, 0, st>>>(b->d_listjobs, b->stride, b->max_shift);
-        launches++;
-    }
+    P.job_lo = 0; P.job_hi = (uint32_t)n;
+    list_finalize_kernel<<<dim3((unsigned)n, 4), 256, 0, st>>>(P);
+    launches++;
     CU_TRY(c, cudaGetLastError());
     CU_TRY(c, cudaEventRecord(c->ev[2], st));
     b->h2d_pending = false;
     c->timing.launches = launches;
-    c->timing.window_launches = launches - 1;
+    c->timing.window_launches = launches;
     c->timing.window_word_shift_pairs = 0;
     c->timing.path = 3;
     c->timing.build_ms = c->timing.window_ms = c->timing.total_ms = -1.f;
@@ -1497,13 +1502,20 @@ extern "C" int pmb_batch_counters(pmb_ctx* c, pmb_batch* b, void** dev_ptr, uint
     return PMB_OK;
 }
 
+// The flags of the batch's LAST execute: the list path alternates between two pairs (see ListJob),
+// the other paths clear and use the first.
+static int* batch_flags(pmb_batch* b)
+{
+    return b->d_err + (b->path == 3 && b->list_execs ? 2 * ((b->list_execs - 1) & 1u) : 0);
+}
+
 // After an execute on the list path: has the device found the inputs unsorted / overlapping?  Then
 // the batch moves to the event path and is executed again (synchronises the stream).
 static int settle_path(pmb_ctx* c, pmb_batch* b)
 {
     if (b->path != 3 || b->list_checked) return PMB_OK;
     int* h_flags = (int*)((char*)c->h_stage + c->h_stage_bytes - 16);
-    CU_TRY(c, cudaMemcpyAsync(h_flags, b->d_err, 8, cudaMemcpyDeviceToHost, c->stream));
+    CU_TRY(c, cudaMemcpyAsync(h_flags, batch_flags(b), 8, cudaMemcpyDeviceToHost, c->stream));
     CU_TRY(c, cudaStreamSynchronize(c->stream));
     if (h_flags[1] && !h_flags[0]) return fallback_to_events(c, b);
     b->list_checked = true;     // the inputs are resident: what held for this execute holds for the next
@@ -1543,14 +1555,14 @@ extern "C" int pmb_batch_fetch(pmb_ctx* c, pmb_batch* b, pmb_chrom_out* o)
     int64_t* h = (int64_t*)c->h_stage;
     int* h_err = (int*)((char*)c->h_stage + b->counter_words * 8);
     CU_TRY(c, cudaMemcpyAsync(h, b->d_counters, b->counter_words * 8, cudaMemcpyDeviceToHost, c->stream));
-    CU_TRY(c, cudaMemcpyAsync(h_err, b->d_err, 8, cudaMemcpyDeviceToHost, c->stream));
+    CU_TRY(c, cudaMemcpyAsync(h_err, batch_flags(b), 8, cudaMemcpyDeviceToHost, c->stream));
     CU_TRY(c, cudaStreamSynchronize(c->stream));
     if (b->path == 3 && !b->list_checked && h_err[1] && !h_err[0]) {
         // unsorted input on the list path: recompute on the event path, then read again
         int rc = guarded(c, [&]() -> int { return fallback_to_events(c, b); });
         if (rc != PMB_OK) return rc;
         CU_TRY(c, cudaMemcpyAsync(h, b->d_counters, b->counter_words * 8, cudaMemcpyDeviceToHost, c->stream));
-        CU_TRY(c, cudaMemcpyAsync(h_err, b->d_err, 8, cudaMemcpyDeviceToHost, c->stream));
+        CU_TRY(c, cudaMemcpyAsync(h_err, batch_flags(b), 8, cudaMemcpyDeviceToHost, c->stream));
         CU_TRY(c, cudaStreamSynchronize(c->stream));
     } else if (b->path == 3) {
         b->list_checked = true;
@@ -1727,9 +1739,10 @@ static int allreduce_enqueue(NcclApi* api, pmb_ctx** ctxs, pmb_batch** bs, int n
     for (int i = 0; i < n; i++) {
         pmb_ctx* c = ctxs[i];
         CU_TRY(c, cudaSetDevice(c->device));
-        status_words_kernel<<<1, 1, 0, c->stream>>>(bs[i]->d_err, bs[i]->d_counters + bs[i]->counter_words,
-                                                    bs[i]->path != 3 || bs[i]->list_checked ? 1 : 0);
-        CU_TRY(c, cudaGetLastError());
+        if (bs[i]->path != 3) {     // (the list path's finalize kernel has written the words already)
+            status_words_kernel<<<1, 1, 0, c->stream>>>(bs[i]->d_err, bs[i]->d_counters + bs[i]->counter_words, 1);
+            CU_TRY(c, cudaGetLastError());
+        }
     }
     if (n > 1) NCCL_TRY(ctxs[0], api, api->GroupStart());
     for (int i = 0; i < n; i++) {
@@ -1787,7 +1800,7 @@ extern "C" int pmb_allreduce(pmb_ctx** ctxs, pmb_batch** bs, int n)
                 int rc2;
                 if (bs[i]->path == 3 && !bs[i]->list_checked) {
                     // (the flags were cleared by nothing since the execute: still the rank's own)
-                    CU_TRY(c, cudaMemcpy(h_flags, bs[i]->d_err, 8, cudaMemcpyDeviceToHost));
+                    CU_TRY(c, cudaMemcpy(h_flags, batch_flags(bs[i]), 8, cudaMemcpyDeviceToHost));
                     rc2 = h_flags[1] ? fallback_to_events(c, bs[i]) : pmb_batch_execute(c, bs[i]);
                 } else {
                     rc2 = pmb_batch_execute(c, bs[i]);
@@ -1811,10 +1824,10 @@ extern "C" int pmb_allreduce(pmb_ctx** ctxs, pmb_batch** bs, int n)
 // the array directly (noalloc_setup_kernel).
 //   words [0, 32)    the job table: one ListJob
 //   words [32, 64)   entry prefixes of the three kernels: {0, n_fwd}, {0, n_rev}, {0, n_intervals}
-//   words [64, ...)  accumulators: [4][S] difference histograms | [2][S] edge products | [2] lags,
-//                    S = max_shift + 1 <= PMB_NOALLOC_MAX_SHIFT + 1
+//   words [64, ...)  accumulators (ONE copy, cleared by every call): [6][S] pair and difference histograms |
+//                    [2] strand totals | [2][S] run-edge products | [2] lags,  S = max_shift + 1 <= PMB_NOALLOC_MAX_SHIFT + 1
 constexpr size_t NOALLOC_TABLE_WORDS = 32, NOALLOC_PREFIX_WORDS = 32;
-constexpr size_t NOALLOC_ACC_WORDS = 6 * ((size_t)PMB_NOALLOC_MAX_SHIFT + 1) + 2;
+constexpr size_t NOALLOC_ACC_WORDS = (LA_N + 2) * ((size_t)PMB_NOALLOC_MAX_SHIFT + 1) + 4;
 constexpr size_t NOALLOC_SCRATCH_WORDS = NOALLOC_TABLE_WORDS + NOALLOC_PREFIX_WORDS + NOALLOC_ACC_WORDS;
 static_assert(sizeof(ListJob) <= NOALLOC_TABLE_WORDS * 8, "job table slot too small");
 static __device__ __align__(256) unsigned long long g_noalloc_scratch[NOALLOC_SCRATCH_WORDS];
@@ -1894,9 +1907,8 @@ extern "C" int pmb_run_chrom_noalloc(pmb_ctx* c, const pmb_chrom_args* a, int64_
     if (mscc || autocorr) { J.begins = a->map_begin; J.ends = a->map_end; J.n_iv = (uint32_t)a->n_intervals; }
     J.counters = out;                               // [5][S]
     J.totals = out + (size_t)PMB_NCOUNTERS * S;     // [2]
-    J.diff = acc;                                   // [4][S]
-    J.aux = acc + 4 * (size_t)S;                    // [2][S]
-    J.adirect = acc + 6 * (size_t)S;                // [2]
+    J.acc = acc;                                    // [LA_N][S] + [2]
+    J.aux = acc + (size_t)LA_N * S + 2;             // [2][S] + [2]
     J.nbits = nbits;
     J.lo = (long long)a->range_lo;
     J.hi = a->range_hi ? (long long)std::min<uint64_t>(a->range_hi, nbits) : (long long)nbits;
@@ -1904,12 +1916,15 @@ extern "C" int pmb_run_chrom_noalloc(pmb_ctx* c, const pmb_chrom_args* a, int64_
 
     cudaStream_t st = c->stream;
     noalloc_setup_kernel<<<c->num_sms, 512, 0, st>>>(J, J.n_fwd, J.n_rev, J.n_iv, out,
-                                                     (uint32_t)PMB_NOALLOC_OUT_INT64(D), (uint32_t)(6 * (size_t)S + 2));
+                                                     (uint32_t)PMB_NOALLOC_OUT_INT64(D), (uint32_t)((LA_N + 2) * (size_t)S + 4));
     ListParams P{};
     P.jobs = reinterpret_cast<const ListJob*>(scratch);
     P.job_lo = 0; P.job_hi = 1;
     P.max_shift = D; P.read_len = a->read_len; P.stride = S;
     P.flags = (int*)(out + (size_t)PMB_NCOUNTERS * S + 2);      // the status word of d_out: {range, unsorted}
+    P.acc_off = P.acc_other = 0;                                // one copy: the set-up kernel above clears it
+    P.flags_other = nullptr;
+    P.status_tail = nullptr;
     const uint32_t bps = c->list_blocks_per_sm > 0 ? (uint32_t)c->list_blocks_per_sm : (uint32_t)LIST_MIN_BLOCKS;
     auto grid_for = [&](unsigned long long items) {
         return (unsigned)std::max<unsigned long long>(1, std::min<unsigned long long>((items + 2047) / 2048,
@@ -1932,7 +1947,7 @@ extern "C" int pmb_run_chrom_noalloc(pmb_ctx* c, const pmb_chrom_args* a, int64_
         P.prefix = pre + 4;
         list_edge_kernel<<<grid_for(J.n_iv), LIST_THREADS, sm_2, st>>>(P);
     }
-    if (mscc || autocorr) list_finalize_kernel<<<1, 256, 0, st>>>(P.jobs, S, D);
+    list_finalize_kernel<<<dim3(1, 4), 256, 0, st>>>(P);
     CU_TRY(c, cudaGetLastError());
     return PMB_OK;
 }

@@ -38,17 +38,25 @@
 
 namespace pmb {
 
+// Accumulators.  The list kernels ADD into per-job accumulators, the finalize kernel turns them
+// into the job's output vectors with plain stores.  There are two copies of every accumulator
+// (and of the flags), used by alternate executes of a batch: the finalize of execute k, once it
+// has read copy k & 1, clears copy (k+1) & 1 -- dirty since execute k-1, which nobody reads any
+// more -- so a step needs no zeroing pass and no kernel ever clears what another still reads.
+//   acc  [LA_N][stride] | [2] strand totals        per job
+//   aux  [2][stride] run-edge products | [2] lags  per job that OWNS its track (followers point at it)
+enum { LA_NCC = 0, LA_MSCC = 1, LA_FP = 2, LA_FM = 3, LA_RP = 4, LA_RM = 5, LA_N = 6 };
+
 struct ListJob {
     const uint32_t* fwd;
     const uint32_t* rev;
     const uint32_t* begins;         // the owner's intervals for a job that shares its track
     const uint32_t* ends;
     uint32_t n_fwd, n_rev, n_iv, flags;
-    unsigned long long* counters;   // [5][stride]
-    unsigned long long* totals;     // [2]
-    unsigned long long* diff;       // [4][stride]: mfwd +, mfwd -, mrev +, mrev -
-    unsigned long long* aux;        // [2][stride]: run-edge products (the owner's)
-    unsigned long long* adirect;    // [2]: the two directly counted lags (the owner's)
+    unsigned long long* counters;   // out: [5][stride]
+    unsigned long long* totals;     // out: [2]
+    unsigned long long* acc;        // copy 0 of this job's accumulators
+    unsigned long long* aux;        // copy 0 of the (owner's) run-edge products and lags
     long long lo, hi;               // counted range, chromosome bits
     unsigned long long nbits;
 };
@@ -58,7 +66,12 @@ struct ListParams {
     const unsigned long long* prefix;   // [n_jobs + 1]: entries of this kernel's list before each job
     uint32_t job_lo, job_hi;            // this launch covers these jobs (everything, or one H2D group)
     uint32_t max_shift, read_len, stride;
-    int* flags;                         // [0] position beyond the array, [1] input not sorted / disjoint
+    int* flags;                         // this execute's: [0] position beyond the array, [1] input not sorted / disjoint
+    unsigned long long acc_off;         // words from copy 0 to this execute's copy of the accumulators
+    // finalize only
+    unsigned long long acc_other;       // ... to the copy the NEXT execute uses (cleared here); == acc_off: clear nothing
+    int* flags_other;                   // the next execute's flags (cleared here), or null
+    unsigned long long* status_tail;    // [2] status words behind the counter block (pmb_allreduce), or null
 };
 
 #ifndef PMB_LIST_THREADS
@@ -294,14 +307,15 @@ __global__ void __launch_bounds__(LIST_THREADS, LIST_MIN_BLOCKS) list_fwd_kernel
                     while (k2 < D && c > 0) { c--; load_run(); }      // the window's remaining runs
             }
             for (int o = 16; o; o >>= 1) tot += __shfl_xor_sync(0xFFFFFFFFu, tot, o);
-            if (lane == 0 && tot) atomicAdd(J.totals, (unsigned long long)tot);            // bit_array_num_bits_set
+            if (lane == 0 && tot) atomicAdd(J.acc + P.acc_off + (size_t)LA_N * P.stride, (unsigned long long)tot);   // bit_array_num_bits_set
         },
         [&](uint32_t, const ListJob& J) {
-            if (NCC) flush_hist(h_ncc, D + 1, J.counters + (size_t)C_NCC * P.stride);
+            unsigned long long* acc = J.acc + P.acc_off;
+            if (NCC) flush_hist(h_ncc, D + 1, acc + (size_t)LA_NCC * P.stride);
             if (MSCC) {
-                flush_hist(h_mscc, D + 1, J.counters + (size_t)C_MSCC * P.stride);
-                flush_hist(h_fp, D + 1, J.diff);
-                flush_hist(h_fm, D + 1, J.diff + P.stride);
+                flush_hist(h_mscc, D + 1, acc + (size_t)LA_MSCC * P.stride);
+                flush_hist(h_fp, D + 1, acc + (size_t)LA_FP * P.stride);
+                flush_hist(h_fm, D + 1, acc + (size_t)LA_FM * P.stride);
                 if (threadIdx.x == 0) { h_fp[DUMP] = 0; h_fm[DUMP] = 0; }
             }
         });
@@ -391,12 +405,12 @@ __global__ void __launch_bounds__(LIST_THREADS, LIST_MIN_BLOCKS) list_rev_kernel
                 }
             }
             for (int o = 16; o; o >>= 1) tot += __shfl_xor_sync(0xFFFFFFFFu, tot, o);
-            if (lane == 0 && tot) atomicAdd(J.totals + 1, (unsigned long long)tot);
+            if (lane == 0 && tot) atomicAdd(J.acc + P.acc_off + (size_t)LA_N * P.stride + 1, (unsigned long long)tot);
         },
         [&](uint32_t, const ListJob& J) {
             if (MSCC) {
-                flush_hist(h_rp, D + 1, J.diff + 2 * (size_t)P.stride);
-                flush_hist(h_rm, D + 1, J.diff + 3 * (size_t)P.stride);
+                flush_hist(h_rp, D + 1, J.acc + P.acc_off + (size_t)LA_RP * P.stride);
+                flush_hist(h_rm, D + 1, J.acc + P.acc_off + (size_t)LA_RM * P.stride);
                 if (threadIdx.x == 0) h_rm[D + 1] = 0;
             }
         });
@@ -470,54 +484,130 @@ __global__ void __launch_bounds__(LIST_THREADS, LIST_MIN_BLOCKS) list_edge_kerne
                 d1 += __shfl_xor_sync(0xFFFFFFFFu, d1, o);
             }
             if (lane == 0) {
-                if (d0) atomicAdd(J.adirect, d0);
-                if (d1) atomicAdd(J.adirect + 1, d1);
+                unsigned long long* lags = J.aux + P.acc_off + 2 * (size_t)P.stride;
+                if (d0) atomicAdd(lags, d0);
+                if (d1) atomicAdd(lags + 1, d1);
             }
         },
         [&](uint32_t, const ListJob& J) {
-            flush_hist(h_plus, D + 1, J.aux);
-            flush_hist(h_minus, D + 1, J.aux + P.stride);
+            flush_hist(h_plus, D + 1, J.aux + P.acc_off);
+            flush_hist(h_minus, D + 1, J.aux + P.acc_off + P.stride);
         });
     if (bad_range) atomicExch(P.flags, 1);
     if (bad_order) atomicExch(P.flags + 1, 1);
 }
 
-// ---------------------------------------------------------------- finalize: prefix sums
-// One CTA per job: mfwd / mrev from their difference histograms, dmp from the edge products and
-// the two direct lags (the same double prefix sum as finalize_dmp_kernel).
-__global__ void __launch_bounds__(256) list_finalize_kernel(const ListJob* __restrict__ jobs, uint32_t stride,
-                                                            uint32_t max_shift)
+// ---------------------------------------------------------------- finalize: accumulators -> outputs
+// Inclusive prefix sum of a[0..n) in place by one CTA of 256 threads: every thread owns a
+// contiguous chunk, the 256 chunk sums are scanned by warp shuffles (a serial pass of one thread
+// over them cost 4 us per scan: the whole kernel was latency, 27 us whatever the batch).
+__device__ __forceinline__ long long shfl_up_ll(long long v, int d)
 {
-    __shared__ long long part[256];
-    const ListJob& J = jobs[blockIdx.x];
-    if (!(J.flags & (EVF_MSCC | EVF_AUTOCORR))) return;       // uniform per CTA
-    if (J.lo >= J.hi) return;       // a chromosome outside this rank's position range: every vector stays zero
+    const int lo = __shfl_up_sync(0xFFFFFFFFu, (int)(unsigned long long)v, d);
+    const int hi = __shfl_up_sync(0xFFFFFFFFu, (int)((unsigned long long)v >> 32), d);
+    return (long long)(((unsigned long long)(unsigned)hi << 32) | (unsigned)lo);
+}
+__device__ __forceinline__ void block_scan_fast(long long* a, uint32_t n, long long* warp_sums /* [8] shared */)
+{
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const uint32_t chunk = (n + blockDim.x - 1) / blockDim.x;
+    const uint32_t lo = min(n, threadIdx.x * chunk), hi = min(n, lo + chunk);
+    long long sum = 0;
+    for (uint32_t i = lo; i < hi; ++i) sum += a[i];
+    long long inc = sum;                                  // inclusive scan over the warp
+    for (int d = 1; d < 32; d <<= 1) {
+        const long long t = shfl_up_ll(inc, d);
+        if (lane >= d) inc += t;
+    }
+    if (lane == 31) warp_sums[warp] = inc;
+    __syncthreads();
+    long long run = inc - sum;                            // exclusive prefix inside the warp
+    for (int w = 0; w < warp; ++w) run += warp_sums[w];
+    for (uint32_t i = lo; i < hi; ++i) { run += a[i]; a[i] = run; }
+    __syncthreads();
+}
+
+// grid (n_jobs, 4): part 0 ncc, mscc, strand totals (copies) | 1 mfwd | 2 mrev (prefix sums of their
+// difference histograms) | 3 dmp (double prefix sum of the run-edge products, anchored by the two
+// direct lags).  Outputs are written with plain stores; then the part clears the accumulators the
+// NEXT execute adds into (see ListJob).  A job outside this rank's position range is left alone:
+// its outputs were zeroed when the batch was prepared and nothing ever adds to it.
+__global__ void __launch_bounds__(256) list_finalize_kernel(const ListParams P)
+{
+    __shared__ long long warp_sums[8];
+    const ListJob& J = P.jobs[blockIdx.x];
+    const uint32_t part = blockIdx.y, stride = P.stride, D = P.max_shift, S = D + 1;
+    if (blockIdx.x == 0 && part == 0 && threadIdx.x == 0) {
+        if (P.status_tail) {            // this rank's status words, summed with the counters by pmb_allreduce
+            P.status_tail[0] = P.flags[0] != 0 ? 1ull : 0ull;
+            P.status_tail[1] = P.flags[1] != 0 ? 1ull : 0ull;
+        }
+        if (P.flags_other) { P.flags_other[0] = 0; P.flags_other[1] = 0; }
+    }
+    if (J.lo >= J.hi) return;
     const bool autocorr = (J.flags & EVF_AUTOCORR) != 0;
-    if (!autocorr) {
-        for (int which = 0; which < 2; ++which) {
-            long long* out = (long long*)(J.counters + (size_t)(which ? C_MREV : C_MFWD) * stride);
-            const long long* plus = (const long long*)(J.diff + (size_t)(2 * which) * stride);
+    const bool mscc = (J.flags & EVF_MSCC) != 0;
+    const bool clear = P.acc_other != P.acc_off;
+    const long long* acc = (const long long*)(J.acc + P.acc_off);
+    unsigned long long* acc_next = J.acc + P.acc_other;
+    auto zero = [&](unsigned long long* p, uint32_t n) {
+        if (clear) for (uint32_t i = threadIdx.x; i < n; i += blockDim.x) p[i] = 0;
+    };
+    if (part == 0) {
+        if (!autocorr) {
+            if (J.flags & EVF_NCC)
+                for (uint32_t k = threadIdx.x; k < S; k += blockDim.x) J.counters[(size_t)C_NCC * stride + k] = acc[(size_t)LA_NCC * stride + k];
+            if (mscc)
+                for (uint32_t k = threadIdx.x; k < S; k += blockDim.x) J.counters[(size_t)C_MSCC * stride + k] = acc[(size_t)LA_MSCC * stride + k];
+            if (threadIdx.x < 2) J.totals[threadIdx.x] = acc[(size_t)LA_N * stride + threadIdx.x];
+        }
+        zero(acc_next + (size_t)LA_NCC * stride, S);
+        zero(acc_next + (size_t)LA_MSCC * stride, S);
+        zero(acc_next + (size_t)LA_N * stride, 2);
+        return;
+    }
+    if (part == 1 || part == 2) {
+        const int lp = part == 1 ? LA_FP : LA_RP;
+        if (mscc && !autocorr) {
+            long long* out = (long long*)(J.counters + (size_t)(part == 1 ? C_MFWD : C_MREV) * stride);
+            const long long* plus = acc + (size_t)lp * stride;
             const long long* minus = plus + stride;
-            for (uint32_t k = threadIdx.x; k <= max_shift; k += blockDim.x) out[k] = plus[k] - minus[k];
+            for (uint32_t k = threadIdx.x; k < S; k += blockDim.x) out[k] = plus[k] - minus[k];
             __syncthreads();
-            block_scan_inplace(out, max_shift + 1, part);
+            block_scan_fast(out, S, warp_sums);
+        }
+        zero(acc_next + (size_t)lp * stride, S);
+        zero(acc_next + (size_t)(lp + 1) * stride, S);
+        return;
+    }
+    // part 3: dmp
+    if (mscc || autocorr) {
+        long long* out = (long long*)(J.counters + (size_t)C_DMP * stride);
+        const long long* plus = (const long long*)(J.aux + P.acc_off);
+        const long long* minus = plus + stride;
+        const long long a0 = plus[2 * (size_t)stride], a1 = plus[2 * (size_t)stride + 1];
+        if (D == 0) {
+            if (threadIdx.x == 0) out[0] = a0;
+        } else {
+            // out[0] = A0, out[1] = A1 - A0, out[k+1] = -C[b(k)]; two scans: first differences, then dmp
+            for (uint32_t k = threadIdx.x; k <= D; k += blockDim.x) {
+                long long v;
+                if (k == 0) v = a0;
+                else if (k == 1) v = a1 - a0;
+                else { const uint32_t b = autocorr ? k - 1 : D - (k - 1); v = -(plus[b] - minus[b]); }
+                out[k] = v;
+            }
+            __syncthreads();
+            block_scan_fast(out + 1, D, warp_sums);
+            block_scan_fast(out, D + 1, warp_sums);
         }
     }
-    long long* out = (long long*)(J.counters + (size_t)C_DMP * stride);
-    const long long* plus = (const long long*)J.aux;
-    const long long* minus = plus + stride;
-    const long long a0 = (long long)J.adirect[0], a1 = (long long)J.adirect[1];
-    if (max_shift == 0) { if (threadIdx.x == 0) out[0] = a0; return; }
-    for (uint32_t k = threadIdx.x; k <= max_shift; k += blockDim.x) {
-        long long v;
-        if (k == 0) v = a0;
-        else if (k == 1) v = a1 - a0;
-        else { const uint32_t b = autocorr ? k - 1 : max_shift - (k - 1); v = -(plus[b] - minus[b]); }
-        out[k] = v;
+    if (!(J.flags & EVF_SHARED)) {      // the owner clears the run-edge accumulators its followers read, too
+        unsigned long long* aux_next = J.aux + P.acc_other;
+        zero(aux_next, S);
+        zero(aux_next + stride, S);
+        zero(aux_next + 2 * (size_t)stride, 2);
     }
-    __syncthreads();
-    block_scan_inplace(out + 1, max_shift, part);
-    block_scan_inplace(out, max_shift + 1, part);
 }
 
 }  // namespace pmb
