@@ -176,7 +176,9 @@ void pmb_host_free(void *p);
  *   lists  no bit arrays: pairs of sorted list entries within max_shift;  cost ~ entries + pairs
  * auto takes the list path while a forward read expects fewer than "list_pairs_limit"
  * (default 64) reverse reads per 1024 shifts, else the event path unless the inputs hold more
- * than 4 events (reads + run edges) per 32-bit word.  Tuning: "list_blocks_per_sm", "variant" (carry-save depth of the shift-window counters), "tile_words",
+ * than 4 events (reads + run edges) per 32-bit word.  Tuning: "list_blocks_per_sm", "list_concurrent"
+ * (-1 auto / 0 / 1: the reverse and edge list kernels beside the forward kernel on a second stream; auto does
+ * so below 8 M list entries, where a launch is mostly ramp and tail), "variant" (carry-save depth of the shift-window counters), "tile_words",
  * "grid_blocks", "block_warps", "event_tile_words", "event_blocks_per_sm".
  * Input copy: "async_h2d" (0/1, see pmb_batch_prepare), "h2d_groups" (1..64, default 4: at most that many),
  * "h2d_min_group_bytes" (default 16 MiB: no group smaller than that on average; 0 = always h2d_groups),

@@ -40,6 +40,7 @@ struct pmb_ctx {
     int block_warps = 16;
     int path = 0;            // 0 auto, 1 dense shift-window, 2 event-window, 3 lists
     int list_blocks_per_sm = 0;
+    int list_concurrent = -1;    // reverse + edge list kernels beside the forward kernel on the side stream: -1 auto, 0, 1
     int check_selftest = 0;      // -DPMB_CHECKED builds: make every TMA range check of the event kernels fail (proves the chain)
     bool list_attr_done = false; // the list kernels' shared-memory limit is raised on THIS device
     ncclComm_t comm = nullptr;   // pmb_comm_init / pmb_comm_init_all
@@ -322,6 +323,7 @@ extern "C" int pmb_set_option(pmb_ctx* c, const char* name, int64_t value)
     else if (!strcmp(name, "path")) c->path = (int)value;
     else if (!strcmp(name, "event_tile_words")) c->event_tile_words = (int)value;
     else if (!strcmp(name, "check_selftest")) c->check_selftest = (int)value;
+    else if (!strcmp(name, "list_concurrent")) c->list_concurrent = (int)value;
     else if (!strcmp(name, "list_blocks_per_sm")) c->list_blocks_per_sm = (int)value;
     else if (!strcmp(name, "list_pairs_limit")) c->list_pairs_limit = (int)value;
     else if (!strcmp(name, "event_blocks_per_sm")) c->event_blocks_per_sm = (int)value;
@@ -1087,30 +1089,45 @@ static int execute_lists(pmb_ctx* c, pmb_batch* b)
                                                                                       (unsigned long long)c->num_sms * bps));
     };
     const size_t sm_f = list_smem_bytes(b->max_shift, b->any_mscc ? 4 : 1), sm_2 = list_smem_bytes(b->max_shift, 2);
+    // The three list kernels do not depend on each other.  On long lists each fills the GPU by
+    // itself and they run back to back (clean per-kernel times); on short ones -- a rank's share
+    // of a genome cut into 4 or 8 ranges -- a launch is mostly ramp and tail, so the reverse and
+    // edge kernels run beside the forward kernel on the side stream.
+    const unsigned long long all_entries = pre[n] + pre[(n + 1) + n] + pre[2 * (n + 1) + n];
+    const bool concurrent = !grouped && (c->list_concurrent < 0 ? all_entries < 8000000ull : c->list_concurrent != 0);
+    if (concurrent) {
+        CU_TRY(c, cudaEventRecord(c->ev_side, st));
+        CU_TRY(c, cudaStreamWaitEvent(c->side_stream, c->ev_side, 0));
+    }
     for (size_t pass = 0; pass < n_pass; pass++) {
         const uint32_t jl = grouped ? b->groups[pass].job_lo : 0, jh = grouped ? b->groups[pass].job_hi : (uint32_t)n;
         if (grouped) CU_TRY(c, cudaStreamWaitEvent(st, b->groups[pass].done, 0));
         for (int kind = 0; kind < 3; kind++) {      // forward reads | reverse reads | run edges
             const unsigned long long* pk = pre + kind * (n + 1);
             const unsigned long long items = pk[jh] - pk[jl];
+            cudaStream_t ks = (concurrent && kind > 0) ? c->side_stream : st;
             if (items) {
                 P.prefix = b->d_list_prefix + kind * (n + 1);
                 P.job_lo = jl; P.job_hi = jh;
                 const unsigned grid = grid_for(items);
                 if (kind == 0) {
-                    if (b->any_ncc && b->any_mscc) list_fwd_kernel<true, true><<<grid, LIST_THREADS, sm_f, st>>>(P);
-                    else if (b->any_ncc) list_fwd_kernel<true, false><<<grid, LIST_THREADS, sm_f, st>>>(P);
-                    else list_fwd_kernel<false, true><<<grid, LIST_THREADS, sm_f, st>>>(P);
+                    if (b->any_ncc && b->any_mscc) list_fwd_kernel<true, true><<<grid, LIST_THREADS, sm_f, ks>>>(P);
+                    else if (b->any_ncc) list_fwd_kernel<true, false><<<grid, LIST_THREADS, sm_f, ks>>>(P);
+                    else list_fwd_kernel<false, true><<<grid, LIST_THREADS, sm_f, ks>>>(P);
                 } else if (kind == 1) {
-                    if (b->any_mscc) list_rev_kernel<true><<<grid, LIST_THREADS, sm_2, st>>>(P);
-                    else list_rev_kernel<false><<<grid, LIST_THREADS, 0, st>>>(P);
+                    if (b->any_mscc) list_rev_kernel<true><<<grid, LIST_THREADS, sm_2, ks>>>(P);
+                    else list_rev_kernel<false><<<grid, LIST_THREADS, 0, ks>>>(P);
                 } else {
-                    list_edge_kernel<<<grid, LIST_THREADS, sm_2, st>>>(P);
+                    list_edge_kernel<<<grid, LIST_THREADS, sm_2, ks>>>(P);
                 }
                 launches++;
             }
-            if (kind < 2 && pass + 1 == n_pass) CU_TRY(c, cudaEventRecord(c->evk[kind], st));   // (per-kernel split: ungrouped passes only)
+            if (kind < 2 && pass + 1 == n_pass) CU_TRY(c, cudaEventRecord(c->evk[kind], st));   // (per-kernel split: back-to-back passes only)
         }
+    }
+    if (concurrent) {
+        CU_TRY(c, cudaEventRecord(c->ev_side, c->side_stream));
+        CU_TRY(c, cudaStreamWaitEvent(st, c->ev_side, 0));
     }
     P.job_lo = 0; P.job_hi = (uint32_t)n;
     list_finalize_kernel<<<dim3((unsigned)n, 4), 256, 0, st>>>(P);
