@@ -96,14 +96,26 @@ uint64_t    pmio_bam_ref_len(const pmio_bam *b, uint32_t i);
  * pointers to get the count only). */
 int  pmio_bam_reads(pmio_bam *b, uint32_t i, const uint32_t **pos, const uint32_t **qlen,
                     const uint8_t **is_reverse, uint64_t *n);
-/* The same reads reduced by the calculator's feed rules (mscc.pyx:370-418), for coordinate-
- * sorted files only (PMIO_ERR_ARG otherwise): sorted unique forward 5' positions (consecutive
+/* The same reads reduced by the calculator's feed rules (mscc.pyx:370-418), for a reference
+ * whose own reads are coordinate sorted (pmio_bam_ref_sorted; PMIO_ERR_ARG otherwise): sorted unique forward 5' positions (consecutive
  * repeats dropped) and sorted unique reverse 5' ends pos + qlen - 1, each with the summed query
  * length of the reads that set a bit first; first/last leftmost position fed. */
 int  pmio_bam_packed(const pmio_bam *b, uint32_t i, const uint32_t **fwd, uint64_t *n_fwd,
                      uint64_t *fwd_len_sum, const uint32_t **rev, uint64_t *n_rev,
                      uint64_t *rev_len_sum, uint32_t *first_pos, uint32_t *last_pos);
-/* Query-length histogram for the read-length estimator, ascending by length. */
+/* Coordinate order as the reference sees it: it checks order only on reads that survive the
+ * chromosome filter (handler/calc.py:143-144 -> _check_pos, mscc.pyx:351-366), so the file-wide
+ * `sorted` flag of pmio_bam_stats is not enough.
+ *   pmio_bam_ref_sorted: 1 when the accepted reads of reference i have non-decreasing positions in
+ *       file order (whatever other references lie between them), else 0.
+ *   pmio_bam_ref_order:  the reference ids in the order their reads appear in the file, consecutive
+ *       repeats merged (a reference listed twice was left and revisited); *overflow = 1 when the
+ *       list was cut at 4 M entries (a hopelessly unsorted file). */
+int  pmio_bam_ref_sorted(const pmio_bam *b, uint32_t i);
+int  pmio_bam_ref_order(const pmio_bam *b, const int32_t **refs, uint64_t *n, int *overflow);
+/* Query-length histogram for the read-length estimator (records without a CIGAR have no query
+ * length and are not counted), in the order the lengths first occur in the file -- the order the
+ * reference's MODE estimator breaks ties by (core/readlen.pyx:81). */
 int  pmio_bam_readlen_hist(const pmio_bam *b, const uint32_t **lengths, const uint64_t **counts,
                            uint32_t *n);
 

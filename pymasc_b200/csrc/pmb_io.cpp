@@ -241,7 +241,7 @@ extern "C" uint32_t pmio_crc32(const uint8_t* data, uint64_t len, int use_zlib)
 // (cache-line aligned, like the other per-thread structs below: neighbours are written by
 // different threads once per record)
 struct alignas(128) pmio_chunk {
-    struct Run { int32_t ref; size_t begin; uint32_t first_pos, last_pos; };
+    struct Run { int32_t ref; size_t begin; uint32_t first_pos, last_pos; bool sorted = true; };
     std::vector<uint32_t> pos, qlen;
     std::vector<uint8_t> rev;
     std::vector<Run> runs;
@@ -259,8 +259,15 @@ struct pmio_bam {
     std::vector<std::vector<uint32_t>> pos, qlen;
     std::vector<std::vector<uint8_t>> rev;
     std::vector<uint8_t> materialised;
-    std::vector<uint32_t> hist_len;
+    std::vector<uint32_t> hist_len;             // in the order the lengths first occur in the file
     std::vector<uint64_t> hist_cnt;
+    // coordinate order per reference (the reference checks it only on reads that survive the
+    // chromosome filter, handler/calc.py:143-144 -> mscc.pyx:351-366): ref_ok[i] = the accepted
+    // reads of reference i have non-decreasing positions in file order; run_refs = the references
+    // in the order their reads appear, consecutive repeats merged
+    std::vector<uint8_t> ref_ok;
+    std::vector<int32_t> run_refs;
+    bool run_overflow = false;
     pmio_bam_stats st{};
     // per reference, the reads reduced by the calculator's feed rules (mscc.pyx:370-418)
     struct alignas(128) Packed {
@@ -298,6 +305,7 @@ struct BamHeaderParser {
                 const size_t nr = b->names.size();
                 b->segs.resize(nr); b->counts.assign(nr, 0);
                 b->first_pos.assign(nr, 0); b->last_pos.assign(nr, 0);
+                b->ref_ok.assign(nr, 1);
                 b->pos.resize(nr); b->qlen.resize(nr); b->rev.resize(nr);
                 b->materialised.assign(nr, 0);
                 stage = 2;
@@ -321,6 +329,7 @@ struct alignas(128) ShareStats {
     pmio_bam_stats st{};
     std::vector<uint64_t> hist_small = std::vector<uint64_t>(512, 0);
     std::map<uint32_t, uint64_t> hist;
+    std::vector<uint32_t> first_seen;   // the share's lengths in the order they first occur (MODE ties, readlen.pyx:81)
     bool sorted = true;         // within every run
     bool incomplete = false;    // stopped at a record that runs past the end of the batch
     const char* err = nullptr;
@@ -330,6 +339,7 @@ struct alignas(128) ShareStats {
         st = pmio_bam_stats{};
         std::fill(hist_small.begin(), hist_small.end(), 0);
         hist.clear();
+        first_seen.clear();
         sorted = true;
         err = nullptr;
     }
@@ -374,15 +384,16 @@ size_t parse_share(const uint8_t* p, size_t start, size_t limit, size_t end, uin
             if (op == 0 || op == 1 || op == 4 || op == 7 || op == 8) ql += c >> 4;
         }
         const bool good = !(flag & 0x4) && !(flag & 0x400) && (int)mq >= mapq;
-        // estimate_readlen's counter (readlen.pyx:150-156): read2 is NOT excluded there
-        if (good) {
-            if (ql < ss.hist_small.size()) ss.hist_small[ql]++;
-            else ss.hist[ql]++;
+        // estimate_readlen's counter (readlen.pyx:150-156): read2 is NOT excluded there.  A record
+        // without a CIGAR has no query length (pysam's infer_query_length() gives None): not counted
+        if (good && n_cig) {
+            if (ql < ss.hist_small.size()) { if (ss.hist_small[ql]++ == 0) ss.first_seen.push_back(ql); }
+            else if (ss.hist[ql]++ == 0) ss.first_seen.push_back(ql);
         }
         if ((flag & 0x80) || !good || ql == 0) continue;        // handler/read.py:62-90, :132-143
         const uint32_t p1 = (uint32_t)(pos0 + 1);
         if (out.runs.empty() || out.runs.back().ref != ref) out.runs.push_back({ref, out.pos.size(), p1, p1});
-        else if (p1 < out.runs.back().last_pos) ss.sorted = false;
+        else if (p1 < out.runs.back().last_pos) { ss.sorted = false; out.runs.back().sorted = false; }
         out.runs.back().last_pos = p1;
         out.pos.push_back(p1);
         out.qlen.push_back(ql);
@@ -443,10 +454,15 @@ struct BamMerger {
     int32_t cur_ref = -1;
     uint32_t last_pos = 0;
     std::vector<uint8_t> seen;
+    std::vector<uint32_t> len_order;    // lengths in file order of first occurrence
     bool sorted = true;
 
     void take(const pmio_chunk& c, const ShareStats& ss)
     {
+        for (uint32_t ql : ss.first_seen) {
+            const bool known = ql < hist_small.size() ? hist_small[ql] != 0 : hist.count(ql) != 0;
+            if (!known) len_order.push_back(ql);
+        }
         pmio_bam_stats& st = b->st;
         st.n_records += ss.st.n_records; st.n_with_ref += ss.st.n_with_ref; st.n_unmapped += ss.st.n_unmapped;
         st.n_paired += ss.st.n_paired; st.n_read2 += ss.st.n_read2; st.n_accepted += ss.st.n_accepted;
@@ -462,9 +478,12 @@ struct BamMerger {
                 seen[r.ref] = 1;
                 cur_ref = r.ref;
                 last_pos = 0;
+                if (b->run_refs.size() < (1u << 22)) b->run_refs.push_back(r.ref);
+                else b->run_overflow = true;
             }
             if (r.first_pos < last_pos) sorted = false;
             last_pos = r.last_pos;
+            if (!r.sorted || (b->counts[r.ref] && r.first_pos < b->last_pos[r.ref])) b->ref_ok[r.ref] = 0;
             if (b->counts[r.ref] == 0) b->first_pos[r.ref] = r.first_pos;
             b->last_pos[r.ref] = r.last_pos;
             b->counts[r.ref] += end - r.begin;
@@ -777,13 +796,13 @@ static int bam_load_impl(const char* path, int mapq_criteria, int threads, pmio_
     b->st.sorted = merger.sorted ? 1 : 0;
     for (size_t l = 0; l < merger.hist_small.size(); l++)
         if (merger.hist_small[l]) merger.hist[(uint32_t)l] += merger.hist_small[l];
-    for (auto& kv : merger.hist) { b->hist_len.push_back(kv.first); b->hist_cnt.push_back(kv.second); }
+    for (uint32_t ql : merger.len_order) { b->hist_len.push_back(ql); b->hist_cnt.push_back(merger.hist[ql]); }
     // packed form per reference, references spread over the threads (longest first)
-    if (b->st.sorted) {
+    {   // (every reference whose own reads are in order, whatever the rest of the file looks like)
         b->packed.resize(b->names.size());
         std::vector<size_t> order;
         for (size_t i = 0; i < b->names.size(); i++)
-            if (b->counts[i]) order.push_back(i);
+            if (b->counts[i] && b->ref_ok[i]) order.push_back(i);
         std::sort(order.begin(), order.end(), [&](size_t x, size_t y) { return b->counts[x] > b->counts[y]; });
         std::atomic<size_t> next{0};
         std::atomic<bool> oom{false};
@@ -858,7 +877,7 @@ extern "C" int pmio_bam_packed(const pmio_bam* b, uint32_t i, const uint32_t** f
                                uint64_t* rev_len_sum, uint32_t* first_pos, uint32_t* last_pos)
 {
     if (!b || i >= b->names.size()) return fail(PMIO_ERR_ARG, "reference index out of range");
-    if (!b->st.sorted) return fail(PMIO_ERR_ARG, "reads are not coordinate sorted");
+    if (!b->ref_ok[i]) return fail(PMIO_ERR_ARG, "the reads of this reference are not coordinate sorted");
     const pmio_bam::Packed& k = b->packed[i];
     if (fwd) *fwd = k.fwd.data();
     if (n_fwd) *n_fwd = k.fwd.size();
@@ -868,6 +887,21 @@ extern "C" int pmio_bam_packed(const pmio_bam* b, uint32_t i, const uint32_t** f
     if (rev_len_sum) *rev_len_sum = k.rev_len_sum;
     if (first_pos) *first_pos = b->first_pos[i];
     if (last_pos) *last_pos = b->last_pos[i];
+    return PMIO_OK;
+}
+
+extern "C" int pmio_bam_ref_sorted(const pmio_bam* b, uint32_t i)
+{
+    if (!b || i >= b->names.size()) return fail(PMIO_ERR_ARG, "reference index out of range");
+    return b->ref_ok[i] ? 1 : 0;
+}
+
+extern "C" int pmio_bam_ref_order(const pmio_bam* b, const int32_t** refs, uint64_t* n, int* overflow)
+{
+    if (!b) return fail(PMIO_ERR_ARG, "null argument");
+    if (refs) *refs = b->run_refs.data();
+    if (n) *n = b->run_refs.size();
+    if (overflow) *overflow = b->run_overflow ? 1 : 0;
     return PMIO_OK;
 }
 

@@ -30,6 +30,7 @@ LIB_PATH = os.environ.get("PYMASC_IO_LIB") or os.path.join(_HERE, "libpymasc_io.
 EXPORTS = (
     "pmio_last_error", "pmio_inflate_raw", "pmio_inflate_raw2", "pmio_crc32", "pmio_bam_load", "pmio_bam_free", "pmio_bam_stats_get", "pmio_bam_n_refs",
     "pmio_bam_ref_name", "pmio_bam_ref_len", "pmio_bam_reads", "pmio_bam_packed", "pmio_bam_readlen_hist",
+    "pmio_bam_ref_sorted", "pmio_bam_ref_order",
     "pmio_bw_open", "pmio_bw_close", "pmio_bw_n_chroms", "pmio_bw_chrom_name", "pmio_bw_chrom_len",
     "pmio_bw_intervals", "pmio_bw_prefetch",
 )
@@ -77,6 +78,10 @@ def load_library():
     u64p = ctypes.POINTER(ctypes.c_uint64)
     L.pmio_bam_packed.argtypes = [vp, ctypes.c_uint32, u32pp, u64p, u64p, u32pp, u64p, u64p,
                                   ctypes.POINTER(ctypes.c_uint32), ctypes.POINTER(ctypes.c_uint32)]
+    L.pmio_bam_ref_sorted.argtypes = [vp, ctypes.c_uint32]
+    L.pmio_bam_ref_sorted.restype = ctypes.c_int
+    L.pmio_bam_ref_order.argtypes = [vp, ctypes.POINTER(ctypes.POINTER(ctypes.c_int32)), u64p, ctypes.POINTER(ctypes.c_int)]
+    L.pmio_bam_ref_order.restype = ctypes.c_int
     L.pmio_bam_readlen_hist.argtypes = [vp, u32pp, ctypes.POINTER(ctypes.POINTER(ctypes.c_uint64)),
                                         ctypes.POINTER(ctypes.c_uint32)]
     L.pmio_bw_open.argtypes = [ctypes.c_char_p, vpp]
@@ -212,6 +217,12 @@ class BamFile(object):
             L.pmio_bam_reads(h, i, None, None, None, ctypes.byref(cnt))
             if cnt.value:
                 self._counts[name] = int(cnt.value)
+        # order as the reference sees it (per chromosome, and the sequence of chromosomes in the file)
+        self.ref_sorted = {name: bool(L.pmio_bam_ref_sorted(h, i)) for i, name in enumerate(self.references)}
+        ro, rn, rov = ctypes.POINTER(ctypes.c_int32)(), ctypes.c_uint64(), ctypes.c_int()
+        L.pmio_bam_ref_order(h, ctypes.byref(ro), ctypes.byref(rn), ctypes.byref(rov))
+        self.ref_order = [self.references[i] for i in _copy(ro, rn.value, np.int64).tolist()]
+        self.ref_order_overflow = bool(rov.value)
         self.reads = _LazyReads(self)
         hl, hc, hn = ctypes.POINTER(ctypes.c_uint32)(), ctypes.POINTER(ctypes.c_uint64)(), ctypes.c_uint32()
         L.pmio_bam_readlen_hist(h, ctypes.byref(hl), ctypes.byref(hc), ctypes.byref(hn))
@@ -233,11 +244,12 @@ class BamFile(object):
     def packed(self, chrom):
         """The chromosome's reads after the feed rules of mscc.pyx:370-418: dict of ``fwd``
         (sorted unique forward 5' positions, uint32), ``fwd_len_sum``, ``rev`` (sorted unique
-        reverse 5' ends), ``rev_len_sum``, ``first_pos``, ``last_pos``.  Sorted files only."""
-        if not self.sorted:
-            raise ReadUnsortedError
+        reverse 5' ends), ``rev_len_sum``, ``first_pos``, ``last_pos``.  The chromosome's own
+        reads must be in coordinate order."""
         if chrom not in self._counts:
             raise KeyError(chrom)
+        if not self.ref_sorted[chrom]:
+            raise ReadUnsortedError
         f, r = ctypes.POINTER(ctypes.c_uint32)(), ctypes.POINTER(ctypes.c_uint32)()
         nf, nr, fs, rs = ctypes.c_uint64(), ctypes.c_uint64(), ctypes.c_uint64(), ctypes.c_uint64()
         p0, p1 = ctypes.c_uint32(), ctypes.c_uint32()
@@ -271,15 +283,15 @@ def _estimate(counter, esttype):
     """The five estimators of core/readlen.pyx:22-86 over a {query length: reads} counter.
     MEAN rounds the weighted mean (Python ``round``); MEDIAN is the lower-half boundary of the
     cumulative counts, the rounded midpoint of two lengths when an even total splits exactly
-    between them; MODE is the most frequent length (the reference breaks a tie by the order in
-    which lengths first occur in the file, this one by taking the longer)."""
+    between them; MODE is the most frequent length, ties broken like the reference: by the order in
+    which the lengths first occur in the file (the counter is built in that order)."""
     lengths, counts = _counter_arrays(counter)
     if esttype == "MIN":
         return int(lengths[0])
     if esttype == "MAX":
         return int(lengths[-1])
-    if esttype == "MODE":
-        return int(lengths[len(counts) - 1 - int(np.argmax(counts[::-1]))])
+    if esttype == "MODE":       # readlen.pyx:81, literally: a stable sort by count, ties in first-seen order
+        return int([k for k, v in sorted(counter.items(), key=lambda x: x[1])][-1])
     total = int(counts.sum())
     if esttype == "MEAN":
         return int(round(int((lengths * counts).sum()) / float(total)))
@@ -309,15 +321,26 @@ def estimate_readlen(path, esttype="MEDIAN", mapq_criteria=1, threads=0):
 
 def feed_bam(calc, bam, only=None):
     """Feed every accepted read of `bam` to a calculator, one ``feed_packed`` per chromosome in
-    file order (handler/calc.py:140-153), raising ReadUnsortedError as the per-read loop would.
-    `only`: a set of chromosome names; reads elsewhere are skipped (handler/calc.py:143-144)."""
-    if not bam.sorted:
+    the order the chromosomes appear in the file (handler/calc.py:140-153).
+    `only`: a set of chromosome names; reads elsewhere are skipped BEFORE any order check, as the
+    reference does (handler/calc.py:143-144 skips, then ``_check_pos``, mscc.pyx:351-366): a file
+    that is unsorted only inside an excluded chromosome feeds fine; a selected chromosome whose
+    reads go backwards, or that is left for another selected chromosome and revisited, raises
+    ReadUnsortedError."""
+    if bam.ref_order_overflow:
         raise ReadUnsortedError
-    # chromosomes appear in a sorted file in header order; the per-read rules (duplicates,
-    # read-length sums) were applied natively while decoding
-    for chrom in bam.reads:
-        if only is None or chrom in only:
-            calc.feed_packed(chrom, **bam.packed(chrom))
+    order = []
+    for chrom in bam.ref_order:
+        if only is not None and chrom not in only:
+            continue
+        if order and order[-1] == chrom:
+            continue                    # only excluded chromosomes lay in between
+        if chrom in order or not bam.ref_sorted[chrom]:
+            raise ReadUnsortedError
+        order.append(chrom)
+    # the per-read rules (duplicates, read-length sums) were applied natively while decoding
+    for chrom in order:
+        calc.feed_packed(chrom, **bam.packed(chrom))
 
 
 # ------------------------------------------------------------------------------------- BigWig

@@ -100,7 +100,7 @@ def synthetic_records():
                                      l_seq=40 if not cigar else None))
             ql = sum(n_ for n_, op in cigar if op in "MIS=X")
             good = not flag & 0x4 and not flag & 0x400 and mapq >= 20
-            if good:
+            if good and cigar:                    # no CIGAR, no query length: not in the estimator's counter
                 hist[ql] = hist.get(ql, 0) + 1
             if good and not flag & 0x80 and ql:
                 want[chrom].append((pos, ql, bool(flag & 16)))
@@ -140,6 +140,7 @@ def test_synthetic_bam_flags_cigars_and_block_boundaries(tmp_path, monkeypatch, 
         got = list(zip(r["pos"].tolist(), r["readlen"].tolist(), r["is_reverse"].tolist()))
         assert got == want[chrom]
     assert bam.readlen_counter == hist
+    assert list(bam.readlen_counter) == list(hist)      # lengths in first-seen order (MODE ties, readlen.pyx:81)
     st = bam.stats
     assert st["n_records"] == 4501 and st["n_with_ref"] == 4500
     assert st["n_unmapped"] == sum(1 for i in range(3000) if i % 11 == 2) + sum(1 for i in range(1500) if i % 11 == 2)
@@ -161,6 +162,73 @@ def test_unsorted_bam_is_reported_and_refused(tmp_path):
             W.bam_record(0, 20, 30, 0, [(36, "M")])]
     W.write_bam(path, [("c1", 1000), ("c2", 1000)], recs)
     assert not io_native.BamFile(path, 1).sorted
+
+
+def test_order_is_checked_per_selected_chromosome_like_the_reference(tmp_path):
+    """The reference skips reads of excluded chromosomes BEFORE `_check_pos` (handler/calc.py:143-144,
+    mscc.pyx:351-366) and feeds chromosomes in file order: a file that is unsorted only inside an
+    excluded chromosome feeds fine; a selected chromosome that goes backwards, or is revisited after
+    another SELECTED chromosome, raises; chromosomes are fed in the order they first appear."""
+    M = [(36, "M")]
+
+    class Recorder(object):
+        def __init__(self):
+            self.fed = []
+
+        def feed_packed(self, chrom, **kw):
+            self.fed.append((chrom, kw["fwd"].tolist()))
+
+    refs = [("c1", 1000), ("c2", 1000), ("c3", 1000)]
+    path = str(tmp_path / "order.bam")
+    # c3 first (header order differs from file order), c2 unsorted inside, c1 clean
+    recs = [W.bam_record(2, 5, 30, 0, M), W.bam_record(2, 9, 30, 0, M),
+            W.bam_record(1, 100, 30, 0, M), W.bam_record(1, 50, 30, 0, M),
+            W.bam_record(0, 7, 30, 0, M)]
+    W.write_bam(path, refs, recs)
+    bam = io_native.BamFile(path, 1)
+    assert not bam.sorted and bam.ref_order == ["c3", "c2", "c1"]
+    assert bam.ref_sorted == {"c1": True, "c2": False, "c3": True}
+    with pytest.raises(ReadUnsortedError):
+        io_native.feed_bam(Recorder(), bam)
+    rec = Recorder()
+    io_native.feed_bam(rec, bam, only={"c1", "c3"})                 # c2 excluded: no error, file order
+    assert rec.fed == [("c3", [6, 10]), ("c1", [8])]
+    with pytest.raises(ReadUnsortedError):
+        bam.packed("c2")
+    # c1 ... c2 ... c1: revisited -- unless c2 is excluded, then c1 simply continues
+    recs = [W.bam_record(0, 10, 30, 0, M), W.bam_record(1, 10, 30, 0, M), W.bam_record(0, 20, 30, 0, M)]
+    W.write_bam(path, refs, recs)
+    bam = io_native.BamFile(path, 1)
+    assert bam.ref_order == ["c1", "c2", "c1"] and bam.ref_sorted["c1"]
+    with pytest.raises(ReadUnsortedError):
+        io_native.feed_bam(Recorder(), bam)
+    rec = Recorder()
+    io_native.feed_bam(rec, bam, only={"c1"})
+    assert rec.fed == [("c1", [11, 21])]
+    # ... but not if c1 went backwards across the excluded stretch
+    recs = [W.bam_record(0, 30, 30, 0, M), W.bam_record(1, 10, 30, 0, M), W.bam_record(0, 20, 30, 0, M)]
+    W.write_bam(path, refs, recs)
+    bam = io_native.BamFile(path, 1)
+    with pytest.raises(ReadUnsortedError):
+        io_native.feed_bam(Recorder(), bam, only={"c1"})
+
+
+def test_mode_estimate_breaks_ties_by_first_occurrence_like_the_reference(tmp_path):
+    """core/readlen.pyx:81: `[k for k, v in sorted(c.items(), key=lambda x: x[1])][-1]` -- a stable
+    sort by count over a dict in insertion order: among equally frequent lengths the one that
+    first occurs LAST in the file wins.  Records without a CIGAR are not counted at all."""
+    path = str(tmp_path / "mode.bam")
+    lens = [50, 36, 50, 36, 75, 75, 40]                   # 50, 36, 75 twice each; first seen 50, 36, 75
+    recs = [W.bam_record(0, 10 * i, 30, 0, [(n, "M")]) for i, n in enumerate(lens)]
+    recs.append(W.bam_record(0, 500, 30, 0, [], l_seq=20))   # no CIGAR
+    W.write_bam(path, [("c1", 10000)], recs)
+    bam = io_native.BamFile(path, 1)
+    assert list(bam.readlen_counter.items()) == [(50, 2), (36, 2), (75, 2), (40, 1)]
+    assert io_native.estimate_readlen(bam, "MODE", 1) == 75
+    assert io_native.estimate_readlen(bam, "MIN", 1) == 36      # (0 before: CIGAR-less records counted as length 0)
+    lens = [75, 36, 50, 36, 75, 50]                       # first seen 75, 36, 50 -> 50
+    W.write_bam(path, [("c1", 10000)], [W.bam_record(0, 10 * i, 30, 0, [(n, "M")]) for i, n in enumerate(lens)])
+    assert io_native.estimate_readlen(io_native.BamFile(path, 1), "MODE", 1) == 50
 
 
 def test_bam_errors(tmp_path):
