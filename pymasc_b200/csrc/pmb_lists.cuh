@@ -530,8 +530,8 @@ __device__ __forceinline__ void block_scan_fast(long long* a, uint32_t n, long l
 // grid (n_jobs, 4): part 0 ncc, mscc, strand totals (copies) | 1 mfwd | 2 mrev (prefix sums of their
 // difference histograms) | 3 dmp (double prefix sum of the run-edge products, anchored by the two
 // direct lags).  Outputs are written with plain stores; then the part clears the accumulators the
-// NEXT execute adds into (see ListJob).  A job outside this rank's position range is left alone:
-// its outputs were zeroed when the batch was prepared and nothing ever adds to it.
+// NEXT execute adds into (see ListJob).  A job outside this rank's position range has its vectors
+// written as zero (nothing adds to it, but an in-place all-reduce overwrites them).
 __global__ void __launch_bounds__(256) list_finalize_kernel(const ListParams P)
 {
     __shared__ long long warp_sums[8];
@@ -544,7 +544,22 @@ __global__ void __launch_bounds__(256) list_finalize_kernel(const ListParams P)
         }
         if (P.flags_other) { P.flags_other[0] = 0; P.flags_other[1] = 0; }
     }
-    if (J.lo >= J.hi) return;
+    if (J.lo >= J.hi) {
+        // A chromosome outside this rank's position range: nothing was added for it, its vectors are
+        // zero -- and have to be WRITTEN as zero: an in-place all-reduce (pmb_allreduce) leaves the
+        // other ranks' sums in them, which the next execute + reduce of the batch would add again.
+        if (part == 0) {
+            for (uint32_t k = threadIdx.x; k < S; k += blockDim.x) {
+                J.counters[(size_t)C_NCC * stride + k] = 0;
+                J.counters[(size_t)C_MSCC * stride + k] = 0;
+            }
+            if (threadIdx.x < 2) J.totals[threadIdx.x] = 0;
+        } else {
+            const int which = part == 1 ? C_MFWD : part == 2 ? C_MREV : C_DMP;
+            for (uint32_t k = threadIdx.x; k < S; k += blockDim.x) J.counters[(size_t)which * stride + k] = 0;
+        }
+        return;
+    }
     const bool autocorr = (J.flags & EVF_AUTOCORR) != 0;
     const bool mscc = (J.flags & EVF_MSCC) != 0;
     const bool clear = P.acc_other != P.acc_off;

@@ -79,3 +79,41 @@ def test_one_process_per_gpu_sharded_engine_under_torchrun():
         assert x["unsorted_equal"] is True, x
         assert x["range_error"] == "raised", x
         assert x["equal_after_error"] is True, x
+
+
+@pytest.mark.skipif(n_devices() < 2, reason="needs two GPUs")
+def test_repeated_execute_and_allreduce_of_resident_batches():
+    """What bench.py's resident arm does at N > 1: the SAME batch is executed and all-reduced in
+    place again and again.  The reduce leaves the sum in every rank's counter block -- also in the
+    vectors of chromosomes outside the rank's range, which the next execute must not build on."""
+    from pymasc_b200.distributed import shard_jobs
+    rl, D = 36, 500
+    n = 2
+    jobs, wants = [], []
+    for c, L in enumerate([300000, 60000, 200000, 90000]):
+        fwd, rev, b, e = case(900 + c, L, rl, L // 10)
+        flags = 3 if c != 1 else 1
+        jobs.append(_shim.Job(L, rl, D, flags, fwd, rev, b if flags & 2 else None, e if flags & 2 else None))
+        wants.append(cc_oracle.chrom_counts(L, rl, D, fwd, rev, b if flags & 2 else None, e if flags & 2 else None))
+    devs = [_shim.Device(k) for k in range(n)]
+    try:
+        _shim.Device.comm_init_all(devs)
+        for path in (3, 2):
+            batches = []
+            for k, d in enumerate(devs):
+                d.set_option("path", path)
+                batches.append(d.prepare(shard_jobs(jobs, k, n)))
+            for it in range(4):
+                for b_ in batches:
+                    b_.execute()
+                _shim.Device.allreduce(batches)
+                for b_ in batches:
+                    got = b_.fetch()
+                    for g, w in zip(got, wants):
+                        for key in w:
+                            assert np.array_equal(np.asarray(g[key]), np.asarray(w[key])), (key, it, path)
+            for b_ in batches:
+                b_.free()
+    finally:
+        for d in devs:
+            d.close()
