@@ -725,6 +725,13 @@ def gpu_arm(args):
                 blocks[key] = fn(dev, stream, world, rank, comm, steps=max(3, min(args.steps, 5)))
     if rank == 0:
         line["configs"] = blocks
+        # one flag for every full-size consistency check of this run (a False here voids the numbers)
+        checks = [bool(same)] + [bool(o["same"]) for o in others.values()] + \
+                 [bool(v["resident_equals_e2e"]) and bool(v["counters_equal_oracle_on_sample"])
+                  for v in blocks.values() if "ms_per_step" in v]
+        line["parity_ok"] = all(checks)
+        if not line["parity_ok"]:
+            sys.stderr.write("bench.py: PARITY CHECK FAILED (resident / e2e / other paths / oracle sample disagree)\n")
         if world == 1 and not args.no_cpu_baseline:
             dev.set_stream(None)
             line["cpu_baseline"] = cpu_baseline_leg(workload, mode, check_device=dev)
