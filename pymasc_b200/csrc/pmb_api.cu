@@ -42,6 +42,7 @@ struct pmb_ctx {
     int list_blocks_per_sm = 0;
     int list_concurrent = -1;    // reverse + edge list kernels beside the forward kernel on the side stream: -1 auto, 0, 1
     int check_selftest = 0;      // -DPMB_CHECKED builds: make every TMA range check of the event kernels fail (proves the chain)
+    bool event_attr_done = false; // the event kernels' shared-memory limit is raised on THIS device
     bool list_attr_done = false; // the list kernels' shared-memory limit is raised on THIS device
     ncclComm_t comm = nullptr;   // pmb_comm_init / pmb_comm_init_all
     int comm_rank = 0, comm_world = 1;
@@ -1235,7 +1236,6 @@ static int execute_events(pmb_ctx* c, pmb_batch* b)
     do {                                                                                            \
         auto k = event_window_kernel<KIND, NCC, MSCC>;                                              \
         const size_t sm = event_smem_bytes<KIND>();                                                 \
-        CU_TRY(c, cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));   \
         for (uint32_t col0 = 0; col0 < n_cols_total; col0 += 32) {                                  \
             P.col0 = col0;                                                                          \
             P.n_cols = std::min(32u, n_cols_total - col0);                                          \
@@ -1243,6 +1243,15 @@ static int execute_events(pmb_ctx* c, pmb_batch* b)
             window_launches++;                                                                      \
         }                                                                                           \
     } while (0)
+    if (!c->event_attr_done) {      // once per context (the attribute is per device), not before every launch
+#define PMB_EV_ATTR(KIND, NCC, MSCC)                                                                                    \
+    CU_TRY(c, cudaFuncSetAttribute(event_window_kernel<KIND, NCC, MSCC>, cudaFuncAttributeMaxDynamicSharedMemorySize,   \
+                                   (int)event_smem_bytes<KIND>()))
+        PMB_EV_ATTR(EV_FWD, true, true); PMB_EV_ATTR(EV_FWD, true, false); PMB_EV_ATTR(EV_FWD, false, true);
+        PMB_EV_ATTR(EV_REV, false, true); PMB_EV_ATTR(EV_EDGE, false, true);
+#undef PMB_EV_ATTR
+        c->event_attr_done = true;
+    }
     for (size_t pass = 0; pass < n_pass; pass++) {
         const pmb_batch::Group& G = grouped ? b->groups[pass] : whole;
         // odd groups run on the side stream: a group's kernel tails then overlap the next

@@ -37,3 +37,50 @@ def test_inflate_bench_compares_the_decoders(tmp_path):
     for kind in ("literal_heavy", "match_heavy"):
         assert all(line[kind][k] > 0 for k in ("own", "own_two_streams", "zlib", "crc32_clmul", "crc32_zlib"))
     assert line["literal_heavy"]["compression_ratio"] < 4 < line["match_heavy"]["compression_ratio"]
+
+
+def test_ncu_traffic_sums_dram_bytes_per_kernel(tmp_path):
+    """tools/ncu_traffic.py turns `ncu --page raw --csv` into the measured-traffic file bench.py
+    reports as roofline.traffic (no typed-in constants): units are honoured, launches summed."""
+    hdr = ["ID", "Kernel Name", "dram__bytes_read.sum", "dram__bytes_write.sum",
+           "smsp__inst_executed_op_shared_atom.sum", "smsp__inst_executed.sum", "gpu__time_duration.sum"]
+    units = ["", "", "Mbyte", "Kbyte", "inst", "inst", "us"]
+    rows = [["0", "void pmb::list_fwd_kernel<1, 1>(pmb::ListParams)", "91.5", "3,684.0", "11063486", "279181269", "441.0"],
+            ["1", "void pmb::list_rev_kernel<1>(pmb::ListParams)", "51.8", "149.76", "2540866", "113168051", "190.3"],
+            ["2", "void pmb::list_fwd_kernel<1, 1>(pmb::ListParams)", "1.5", "0", "10", "100", "9.0"]]
+    src = tmp_path / "raw.csv"
+    with open(src, "w") as fh:
+        for r in (hdr, units) + tuple(rows):
+            fh.write(",".join('"%s"' % x for x in r) + "\n")
+    out = tmp_path / "traffic.json"
+    r = subprocess.run([sys.executable, "tools/ncu_traffic.py", str(src), str(out), "9.8e10"], cwd=ROOT,
+                       capture_output=True, text=True, timeout=120)
+    assert r.returncode == 0, r.stderr[-2000:]
+    d = json.load(open(out))
+    fwd = d["kernels"]["list_fwd_kernel"]
+    assert fwd["launches"] == 2 and abs(fwd["dram_bytes"] - (91.5e6 + 3684.0e3 + 1.5e6)) < 1
+    assert fwd["shared_atomic_instr"] == 11063496 and abs(fwd["duration_us"] - 450.0) < 1e-9
+    assert abs(d["step_dram_bytes"] - (fwd["dram_bytes"] + 51.8e6 + 149.76e3)) < 1
+    assert d["atoms_warp_instr_per_s_peak"] == 9.8e10
+
+
+def test_bench_blocks_generate_in_parallel_what_synth_generates(tmp_path):
+    """tools/bench_blocks.generate (spawned workers, longest first) returns exactly the arrays
+    pymasc_b200.synth produces in-process, in task order."""
+    sys.path.insert(0, os.path.join(ROOT, "tools"))
+    import numpy as np
+    import bench_blocks
+    from pymasc_b200 import synth
+    tasks = [(20, 3000, 20260101, True), (21, 2500, 20260201, False), (23, 1000, 20260101, True)]
+    got = bench_blocks.generate(tasks, procs=2)
+    assert [g[0] for g in got] == [20, 21, 23]
+    for (ci, n, seed, wt), (gi, gseed, fwd, rev, b, e) in zip(tasks, got):
+        L = synth.HG38[ci][1]
+        f2, r2 = synth.chip_reads(ci, L, n, 36, seed=seed)
+        assert gseed == seed and np.array_equal(fwd, f2) and np.array_equal(rev, r2)
+        if wt:
+            b2, e2 = synth.mappability(ci, L)
+            assert np.array_equal(b, b2) and np.array_equal(e, e2)
+        else:
+            assert b is None and e is None
+    assert sum(bench_blocks.reads_per_chrom(20_000_000)) > 19_900_000
