@@ -5,6 +5,7 @@ device can be opened, the calls here raise -- there is deliberately no CPU fallb
 """
 import ctypes
 import os
+import struct
 
 import numpy as np
 
@@ -156,7 +157,9 @@ class Job(object):
     keys may be merged into a FLAG_SAME_TRACK run (pymasc_b200.multifile)."""
 
     __slots__ = ("chrom_len", "read_len", "max_shift", "flags", "fwd_pos", "rev_pos",
-                 "map_begins", "map_ends", "lo", "hi", "track_key")
+                 "map_begins", "map_ends", "lo", "hi", "track_key", "_rec")
+
+    _FMT = struct.Struct("<QIIIIQQQQQQQQQ")            # pmb_chrom_args, include/pymasc_b200.h
 
     def __init__(self, chrom_len, read_len, max_shift, flags, fwd_pos=None, rev_pos=None,
                  map_begins=None, map_ends=None, lo=0, hi=0):
@@ -166,6 +169,24 @@ class Job(object):
         self.map_begins, self.map_ends = _as_u32(map_begins), _as_u32(map_ends)
         self.lo, self.hi = int(lo), int(hi)
         self.track_key = None
+
+    def __setattr__(self, name, value):
+        object.__setattr__(self, name, value)
+        if name != "_rec":
+            object.__setattr__(self, "_rec", None)      # the packed record below is stale
+
+    def record(self):
+        """This job as the 96 bytes of a pmb_chrom_args (cached until a field is assigned: a
+        caller that runs the same jobs again -- resident arrays, another step -- pays nothing).
+        The arrays are borrowed: the job keeps them alive."""
+        rec = self._rec
+        if rec is None:
+            f, r, b, e = self.fwd_pos, self.rev_pos, self.map_begins, self.map_ends
+            ptr = lambda a: a.__array_interface__["data"][0] if a.size else 0     # noqa: E731
+            rec = self._FMT.pack(self.chrom_len, self.read_len, self.max_shift, self.flags, 0, ptr(f), f.size,
+                                 ptr(r), r.size, ptr(b), ptr(e), b.size, self.lo, self.hi)
+            object.__setattr__(self, "_rec", rec)
+        return rec
 
 
 class Device(object):
@@ -216,17 +237,18 @@ class Device(object):
         self._check(self._L.pmb_set_stream(self._h, ctypes.c_void_p(int(stream) if stream else None)))
 
     # ---- argument marshalling
+    # (one struct.pack_into per job: a dozen ctypes field assignments and four `.ctypes.data`
+    # look-ups per job were a third of the host time of a 24-chromosome step)
+    _OUT_FMT = struct.Struct("<qqQQQQQ")              # pmb_chrom_out: totals, then ncc, mscc, mfwd, mrev, dmp
+    _OUT_ORDER = ("ncc", "mscc", "mfwd", "mrev", "dmp")
+
     @staticmethod
     def _marshal(jobs):
         n = len(jobs)
-        args = (ChromArgs * n)()
-        for a, j in zip(args, jobs):
-            a.chrom_len, a.read_len, a.max_shift, a.flags = j.chrom_len, j.read_len, j.max_shift, j.flags
-            a.fwd_pos, a.n_fwd = j.fwd_pos.ctypes.data, j.fwd_pos.size
-            a.rev_pos, a.n_rev = j.rev_pos.ctypes.data, j.rev_pos.size
-            a.map_begin, a.map_end = j.map_begins.ctypes.data, j.map_ends.ctypes.data
-            a.n_intervals = j.map_begins.size
-            a.range_lo, a.range_hi = j.lo, j.hi
+        buf = bytearray(b"".join([j.record() for j in jobs]))
+        assert len(buf) == n * ctypes.sizeof(ChromArgs)
+        args = (ChromArgs * n).from_buffer(buf)
+        args._keep = buf
         return args
 
     @staticmethod
@@ -234,7 +256,6 @@ class Device(object):
         """Output structs over ONE int64 block (a view per counter): per-array allocations and
         .ctypes lookups cost more host time than the D2H copy itself."""
         n = len(jobs)
-        outs = (ChromOut * n)()
         names = []
         total = 0
         for j in jobs:
@@ -246,17 +267,24 @@ class Device(object):
             names.append(ks)
             total += len(ks) * (j.max_shift + 1)
         block = np.empty(max(total, 1), np.int64)
-        base = block.ctypes.data
+        base = block.__array_interface__["data"][0]
+        size = Device._OUT_FMT.size
+        assert size == ctypes.sizeof(ChromOut)
+        buf = bytearray(n * size)
+        pack = Device._OUT_FMT.pack_into
         arrays = []
         off = 0
-        for o, j, ks in zip(outs, jobs, names):
+        for i, (j, ks) in enumerate(zip(jobs, names)):
             S = j.max_shift + 1
-            d = {}
+            d, p = {}, {}
             for k in ks:
                 d[k] = block[off:off + S]
-                setattr(o, k, base + 8 * off)
+                p[k] = base + 8 * off
                 off += S
+            pack(buf, i * size, 0, 0, *[p.get(k, 0) for k in Device._OUT_ORDER])
             arrays.append(d)
+        outs = (ChromOut * n).from_buffer(buf)
+        outs._keep = (buf, block)
         return outs, arrays
 
     @staticmethod
