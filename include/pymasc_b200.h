@@ -182,7 +182,9 @@ void pmb_host_free(void *p);
  * "grid_blocks", "block_warps", "event_tile_words", "event_blocks_per_sm".
  * Input copy: "async_h2d" (0/1, see pmb_batch_prepare), "h2d_groups" (1..64, default 4: at most that many),
  * "h2d_min_group_bytes" (default 16 MiB: no group smaller than that on average; 0 = always h2d_groups),
- * "h2d_growth_x10" (size ratio of consecutive groups in tenths, default 13). */
+ * "h2d_growth_x10" (size ratio of consecutive groups in tenths, default 13; the list path uses equal groups, up to
+ * twice "h2d_groups" of them at half the minimum size: its kernels outrun the copy).
+ * Debug: "check_selftest" (a -DPMB_CHECKED build only: makes every bounds check of the event kernels fail). */
 int  pmb_set_option(pmb_ctx *ctx, const char *name, int64_t value);
 
 /*

@@ -907,11 +907,16 @@ static int prepare_impl(pmb_ctx* c, const pmb_chrom_args* a, uint32_t n, pmb_bat
         // a group is only worth its extra launches when its copy takes a few hundred microseconds:
         // at most "h2d_groups" groups, and none smaller than ~16 MB on average
         uint32_t want = 1;
-        if (async && b->path != 1)
+        if (async && b->path != 1) {
+            // (list path: its kernels run ~3x faster than the copy, so what is exposed is the LAST
+            // group's kernels after the copy has ended: twice the groups at half the size)
+            const size_t max_groups = (size_t)c->h2d_groups * (b->path == 3 ? 2 : 1);
+            const size_t min_bytes = (size_t)c->h2d_min_group_bytes / (b->path == 3 ? 2 : 1);
             want = c->h2d_min_group_bytes > 0
-                       ? (uint32_t)std::min<size_t>((size_t)c->h2d_groups,
-                                                    std::max<size_t>(1, total * 4 / (size_t)c->h2d_min_group_bytes))
-                       : (uint32_t)c->h2d_groups;
+                       ? (uint32_t)std::min<size_t>(max_groups, std::max<size_t>(1, total * 4 / std::max<size_t>(min_bytes, 1)))
+                       : (uint32_t)max_groups;
+            want = std::min<uint32_t>(want, 64);
+        }
         // Group sizes grow geometrically: the first group is small so the kernels start early,
         // and each later group may be larger because computing on a group takes ~2x as long
         // as copying it (so the copy of group g+1 hides behind the kernels of group g).
