@@ -25,8 +25,8 @@ def dev():
 
 
 def check_job(dev, L, rl, D, fwd, rev, b=None, e=None, flags=None, lo=0, hi=0):
-    """Both device algorithms -- the dense shift-window kernel (path 1) and the event-window
-    kernels (path 2) -- against the oracle, bit for bit."""
+    """All three device algorithms -- the dense shift-window kernel (path 1), the event-window
+    kernels (path 2) and the list kernels (path 3) -- against the oracle, bit for bit."""
     if flags is None:
         flags = _shim.FLAG_NCC | (_shim.FLAG_MSCC if b is not None else 0)
     mscc = bool(flags & _shim.FLAG_MSCC)
