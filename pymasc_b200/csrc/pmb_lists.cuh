@@ -33,6 +33,7 @@
 #pragma once
 #include <stdint.h>
 #include <cuda_runtime.h>
+#include <type_traits>
 
 #include "pmb_events.cuh"   // EVF_*, C_*, block_scan_inplace
 
@@ -203,6 +204,23 @@ __device__ __forceinline__ void flush_hist(uint32_t* h, uint32_t n_bins, unsigne
     }
 }
 
+// Shared-memory histogram updates by 32-bit shared-space address.  With generic pointers the
+// compiler rebuilt the address of every update inside the pair loop (S2UR SR_CgaCtaId, ULEA, LEA:
+// the shared window of the CTA) and branched around each atomicAdd; the loop was 36 SASS
+// instructions per pair.
+__device__ __forceinline__ uint32_t smem_addr(const void* p)
+{
+    uint32_t a;     // (volatile: the compiler may not redo the conversion where the address is used -- it did, per pair)
+    asm volatile("{ .reg .u64 t;\n\tcvta.to.shared.u64 t, %1;\n\tcvt.u32.u64 %0, t; }" : "=r"(a) : "l"(p));
+    return a;
+}
+// ++[addr]; callers that count conditionally pass the address of a dump bin instead of branching
+// around the update (ptxas does not predicate ATOMS: every condition became BSSY / BRA / BSYNC,
+// and an update costs one issue slot whatever the number of lanes that take part)
+__device__ __forceinline__ void smem_inc(uint32_t addr)
+{
+    asm volatile("red.shared.add.u32 [%0], 1;" :: "r"(addr) : "memory");
+}
 // ---------------------------------------------------------------- forward reads: ncc, mscc, d(mfwd)
 template <bool NCC, bool MSCC>
 __global__ void __launch_bounds__(LIST_THREADS, LIST_MIN_BLOCKS) list_fwd_kernel(const ListParams P)
@@ -218,6 +236,11 @@ __global__ void __launch_bounds__(LIST_THREADS, LIST_MIN_BLOCKS) list_fwd_kernel
     __syncthreads();
     const uint32_t rl1 = P.read_len - 1;
     bool bad_order = false, bad_range = false;
+    const uint32_t s_ncc = smem_addr(h_ncc), s_mscc = smem_addr(h_mscc), s_fp = smem_addr(h_fp), s_fm = smem_addr(h_fm);
+    const uint32_t s_dump = s_ncc + 4u * DUMP;          // (the pair histograms' own dump bins are never flushed)
+    uint32_t Dr;                                        // max_shift in a register (not re-read from the constant bank per pair)
+    asm volatile("mov.u32 %0, %1;" : "=r"(Dr) : "r"(D));
+    (void)s_ncc; (void)s_mscc; (void)s_fp; (void)s_fm; (void)s_dump; (void)Dr;
 
     list_segments(P, warp, n_warps,
         [&](uint32_t, const ListJob& J, uint32_t w0, uint32_t w1) {
@@ -228,6 +251,8 @@ __global__ void __launch_bounds__(LIST_THREADS, LIST_MIN_BLOCKS) list_fwd_kernel
             const uint32_t nR = J.n_rev, nI = J.n_iv;
             const bool job_ncc = NCC && (J.flags & EVF_NCC);
             const bool job_mscc = MSCC && (J.flags & EVF_MSCC) && nI;
+            const uint32_t r_last = nR ? __ldg(rev + nR - 1) : 0;       // (windows that end below it never meet the list's end)
+            (void)r_last; (void)job_ncc;
             const long long lo = J.lo, hi = J.hi;
             const unsigned long long nbits = J.nbits;
             PMB_CHECK(w0 < w1 && w1 <= J.n_fwd, P.flags);
@@ -239,7 +264,7 @@ __global__ void __launch_bounds__(LIST_THREADS, LIST_MIN_BLOCKS) list_fwd_kernel
                 const uint32_t i = base + lane;
                 const uint32_t n_act = min(32u, w1 - base);
                 const bool act = lane < (int)n_act;
-                uint32_t p = __ldg(fwd + (act ? i : w1 - 1));
+                const uint32_t p = __ldg(fwd + (act ? i : w1 - 1));
                 uint32_t pprev = __shfl_up_sync(0xFFFFFFFFu, p, 1);
                 if (lane == 0) pprev = base ? __ldg(fwd + base - 1) : LIST_NONE;
                 bad_order |= act && pprev != LIST_NONE && p < pprev;
@@ -268,50 +293,67 @@ __global__ void __launch_bounds__(LIST_THREADS, LIST_MIN_BLOCKS) list_fwd_kernel
                     while (cp >= 0 && __ldg(begins + cp) >= p) cp--;
                     mp = valid && cp >= 0 && p <= __ldg(ends + cp);                          // M[p]
                 }
+                // every window of the group ends before the list does (whatever the input: no read of
+                // the loop below can pass rev[n_rev - 1]) -> no bounds checks in the pair loop
+                const bool fast = __all_sync(0xFFFFFFFFu, !valid || (j < nR && r_last > p && r_last - p > D));
                 if (!valid) continue;
-                // the run in the window that the next shifts can meet: x = x_top - k in (b, e]  <=>  k in [k1, k2]
-                uint32_t k1 = LIST_NONE, k2 = LIST_NONE;
+                // the run in the window that the next shifts can meet: x = x_top - k in (b, e]  <=>  k - k1 <= span
+                // (no run, or an empty one: k1 = NONE, span = 0 -- no k passes); k2w: the last shift of
+                // the run while runs are left below it, else NONE (nothing more to walk to)
+                uint32_t k1 = LIST_NONE, span = 0, k2w = LIST_NONE;
                 auto load_run = [&]() {
                     PMB_CHECK(c >= 0 && (uint32_t)c < nI, P.flags);
                     const uint32_t b = __ldg(begins + c), e = __ldg(ends + c);
-                    k2 = x_top - b - 1;
+                    const uint32_t k2 = x_top - b - 1;
                     k1 = x_top - min(e, x_top);
+                    span = k2 - k1;
+                    k2w = c > 0 ? k2 : LIST_NONE;
                     if (e > b) {                        // the run enters the window at k1 and leaves after k2
-                        atomicAdd(h_fp + min(k1, DUMP), 1u);
-                        atomicAdd(h_fm + min(k2 + 1, DUMP), 1u);
+                        smem_inc(s_fp + 4u * min(k1, DUMP));
+                        smem_inc(s_fm + 4u * min(k2 + 1, DUMP));
+                    } else {
+                        k1 = LIST_NONE; span = 0;
                     }
                 };
                 if (MSCC && mp && c >= 0) load_run(); else mp = false;
-                // pairs (p, q), q - p <= D.  The next reverse read is requested before this one is
-                // counted (the loads hit L1, but a dependent load per pair would serialise on its
-                // latency); past the end of the list a sentinel gives k > D.
-                uint32_t qprev = LIST_NONE;
-                uint32_t q = j < nR ? __ldg(rev + j) : LIST_NONE;
-                for (;;) {
-                    const uint32_t k = q - p;
-                    if (k > D) break;
-                    ++j;
-                    const uint32_t qn = j < nR ? __ldg(rev + j) : LIST_NONE;
-                    if (q != qprev) {                   // a bit is set once (mscc.pyx:416-418)
+                // pairs (p, q), p <= q <= p + D.  Of equal reverse reads the LAST is counted (a bit is
+                // set once, mscc.pyx:416-418): the test is against the entry loaded for the next round.
+                // A pair that does not count goes to the dump bin.  `checked`: the list may end inside
+                // this group's windows.
+                auto pair_loop = [&](auto checked) {
+                    bool more = !checked.value || j < nR;
+                    uint32_t q = more ? __ldg(rev + j) : 0u;
+                    uint32_t k = q - p;                 // (unsigned: an unsorted list cannot index outside the bins)
+                    while (more && k <= Dr) {
+                        ++j;
+                        const bool last = checked.value && j >= nR;
+                        const uint32_t qn = last ? ~q : __ldg(rev + j);
+                        const uint32_t k4 = 4u * k;
+                        const bool once = q != qn;
                         PMB_CHECK(k <= D && j <= nR, P.flags);
-                        if (job_ncc) atomicAdd(h_ncc + k, 1u);
-                        if (MSCC && mp) {
-                            while (k > k2 && c > 0) { c--; load_run(); }
-                            if (k >= k1 && k <= k2) atomicAdd(h_mscc + k, 1u);
+                        if (NCC) smem_inc(once ? s_ncc + k4 : s_dump);
+                        if (MSCC) {
+                            while (k > k2w) { c--; load_run(); }
+                            smem_inc(once && k - k1 <= span ? s_mscc + k4 : s_dump);
                         }
+                        q = qn;
+                        k = q - p;
+                        more = !last;
                     }
-                    qprev = q;
-                    q = qn;
-                }
+                };
+                if (fast) pair_loop(std::false_type{}); else pair_loop(std::true_type{});
                 if (MSCC && mp)
-                    while (k2 < D && c > 0) { c--; load_run(); }      // the window's remaining runs
+                    while (k2w < D) { c--; load_run(); }              // the window's remaining runs
             }
             for (int o = 16; o; o >>= 1) tot += __shfl_xor_sync(0xFFFFFFFFu, tot, o);
             if (lane == 0 && tot) atomicAdd(J.acc + P.acc_off + (size_t)LA_N * P.stride, (unsigned long long)tot);   // bit_array_num_bits_set
         },
         [&](uint32_t, const ListJob& J) {
             unsigned long long* acc = J.acc + P.acc_off;
-            if (NCC) flush_hist(h_ncc, D + 1, acc + (size_t)LA_NCC * P.stride);
+            if (NCC) {
+                if (J.flags & EVF_NCC) flush_hist(h_ncc, D + 1, acc + (size_t)LA_NCC * P.stride);
+                else for (uint32_t i = threadIdx.x; i <= D; i += blockDim.x) h_ncc[i] = 0;     // (the pair loop counts for every job)
+            }
             if (MSCC) {
                 flush_hist(h_mscc, D + 1, acc + (size_t)LA_MSCC * P.stride);
                 flush_hist(h_fp, D + 1, acc + (size_t)LA_FP * P.stride);
@@ -338,6 +380,9 @@ __global__ void __launch_bounds__(LIST_THREADS, LIST_MIN_BLOCKS) list_rev_kernel
     }
     const uint32_t rl1 = P.read_len - 1;
     bool bad_order = false, bad_range = false;
+    const uint32_t s_rp = smem_addr(h_rp), s_rm = smem_addr(h_rm);
+    const uint32_t s_dump = s_rp + 4u * (D + 1);        // (bin D+1 of h_rp is never flushed)
+    (void)s_rp; (void)s_rm; (void)s_dump;
 
     list_segments(P, warp, n_warps,
         [&](uint32_t, const ListJob& J, uint32_t w0, uint32_t w1) {
@@ -394,10 +439,11 @@ __global__ void __launch_bounds__(LIST_THREADS, LIST_MIN_BLOCKS) list_rev_kernel
                 for (;;) {
                     if (a1 > (uint32_t)kb || b1 > (uint32_t)kb) break;
                     const uint32_t s = max(max(a1, b1), (uint32_t)ka), e = min(min(a2, b2), (uint32_t)kb);
-                    if (s <= e) {                       // both mappable for k in [s, e]
-                        PMB_CHECK(e <= D, P.flags);
-                        atomicAdd(h_rp + s, 1u);
-                        atomicAdd(h_rm + e + 1, 1u);
+                    {                                   // both mappable for k in [s, e]; else: the dump bin
+                        const bool both = s <= e;
+                        PMB_CHECK(!both || e <= D, P.flags);
+                        smem_inc(both ? s_rp + 4u * s : s_dump);
+                        smem_inc(both ? s_rm + 4u * e + 4u : s_dump);
                     }
                     if (min(a2, b2) >= (uint32_t)kb) break;
                     if (a2 <= b2) { if (cA == 0) break; cA--; load_a(); }
