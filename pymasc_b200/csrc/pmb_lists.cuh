@@ -132,6 +132,30 @@ __device__ __forceinline__ uint32_t gallop(const uint32_t* __restrict__ a, uint3
     }
 }
 
+// The search every group makes: first index >= cur with a[index] >= key, given a[< cur] < key and
+// a warp-uniform cursor.  The answer nearly always lies within the next 63 entries (a group of 32
+// reads meets about as many entries of the other list), so those are searched without a loop:
+// six probes at fixed offsets from one base address.  If any lane finds all 63 below its key --
+// or the list ends inside the window -- the warp bounds the range by galloping and searches that.
+// (key_max: the largest key of the group.  Unsorted input gives wrong but in-bounds answers.)
+__device__ __forceinline__ uint32_t cursor_lower_bound(const uint32_t* __restrict__ a, uint32_t n, uint32_t cur,
+                                                       uint32_t key, uint32_t key_max)
+{
+    uint32_t off = 63;
+    if (cur + 63 <= n) {
+        const uint32_t* __restrict__ b = a + cur;
+        off = 0;
+#pragma unroll
+        for (uint32_t s = 32; s; s >>= 1)
+            if (__ldg(b + off + (s - 1)) < key) off += s;
+    }
+    if (__any_sync(0xFFFFFFFFu, off == 63)) {
+        const uint32_t hi = gallop(a, n, cur, key_max);
+        return lower_bound_in(a, cur, hi, key);
+    }
+    return cur + off;
+}
+
 // per-thread lower bound over the whole array by doubling steps from `start` (run edges: the
 // answer lies a few entries from the thread's own interval)
 __device__ __forceinline__ uint32_t lower_bound_near(const uint32_t* __restrict__ a, uint32_t n, uint32_t start, long long key)
@@ -238,9 +262,7 @@ __global__ void __launch_bounds__(LIST_THREADS, LIST_MIN_BLOCKS) list_fwd_kernel
     bool bad_order = false, bad_range = false;
     const uint32_t s_ncc = smem_addr(h_ncc), s_mscc = smem_addr(h_mscc), s_fp = smem_addr(h_fp), s_fm = smem_addr(h_fm);
     const uint32_t s_dump = s_ncc + 4u * DUMP;          // (the pair histograms' own dump bins are never flushed)
-    uint32_t Dr;                                        // max_shift in a register (not re-read from the constant bank per pair)
-    asm volatile("mov.u32 %0, %1;" : "=r"(Dr) : "r"(D));
-    (void)s_ncc; (void)s_mscc; (void)s_fp; (void)s_fm; (void)s_dump; (void)Dr;
+    (void)s_ncc; (void)s_mscc; (void)s_fp; (void)s_fm; (void)s_dump;
 
     list_segments(P, warp, n_warps,
         [&](uint32_t, const ListJob& J, uint32_t w0, uint32_t w1) {
@@ -255,6 +277,9 @@ __global__ void __launch_bounds__(LIST_THREADS, LIST_MIN_BLOCKS) list_fwd_kernel
             (void)r_last; (void)job_ncc;
             const long long lo = J.lo, hi = J.hi;
             const unsigned long long nbits = J.nbits;
+            // max_shift as a value that has to live in a register: as a kernel parameter it was re-read
+            // from the constant bank for every pair (LDCU + IMAD.U32); nbits < 2^32, so this adds 0
+            const uint32_t Dr = D + (uint32_t)(nbits >> 32);
             PMB_CHECK(w0 < w1 && w1 <= J.n_fwd, P.flags);
             const uint32_t p_first = __ldg(fwd + w0);
             uint32_t JR = warp_lower_bound(rev, nR, p_first, lane);                          // reverse reads below p
@@ -273,9 +298,7 @@ __global__ void __launch_bounds__(LIST_THREADS, LIST_MIN_BLOCKS) list_fwd_kernel
                 tot += valid;
                 const uint32_t p_max = __shfl_sync(0xFFFFFFFFu, p, n_act - 1);
                 // this read's first reverse read: q >= p
-                const uint32_t HR = gallop(rev, nR, JR, p_max);
-                PMB_CHECK(JR <= HR && HR <= nR, P.flags);
-                uint32_t j = lower_bound_in(rev, JR, HR, p);
+                uint32_t j = cursor_lower_bound(rev, nR, JR, p, p_max);
                 PMB_CHECK(j <= nR, P.flags);
                 JR = __shfl_sync(0xFFFFFFFFu, j, n_act - 1);
                 // mappable runs: c = last run that begins below x_top = p + rl - 1
@@ -283,9 +306,7 @@ __global__ void __launch_bounds__(LIST_THREADS, LIST_MIN_BLOCKS) list_fwd_kernel
                 int c = -1;
                 bool mp = false;
                 if (job_mscc) {
-                    const uint32_t HI = gallop(begins, nI, CI, p_max + rl1);
-                    PMB_CHECK(CI <= HI && HI <= nI, P.flags);
-                    const uint32_t c1 = lower_bound_in(begins, CI, HI, x_top);
+                    const uint32_t c1 = cursor_lower_bound(begins, nI, CI, x_top, p_max + rl1);
                     PMB_CHECK(c1 <= nI, P.flags);
                     CI = __shfl_sync(0xFFFFFFFFu, c1, n_act - 1);
                     c = (int)c1 - 1;
@@ -409,9 +430,7 @@ __global__ void __launch_bounds__(LIST_THREADS, LIST_MIN_BLOCKS) list_rev_kernel
                 if (!job_mscc) continue;
                 const uint32_t t = q + rl1;
                 const uint32_t q_max = __shfl_sync(0xFFFFFFFFu, q, n_act - 1);
-                const uint32_t HI = gallop(begins, nI, CI, q_max + rl1);
-                PMB_CHECK(CI <= HI && HI <= nI, P.flags);
-                const uint32_t c1 = lower_bound_in(begins, CI, HI, t);
+                const uint32_t c1 = cursor_lower_bound(begins, nI, CI, t, q_max + rl1);
                 PMB_CHECK(c1 <= nI, P.flags);
                 CI = __shfl_sync(0xFFFFFFFFu, c1, n_act - 1);
                 // shifts whose j = q - k lies in the counted range
