@@ -486,11 +486,13 @@ def gpu_arm(args):
 
         # ---- per-kernel times of the same step (library CUDA events on the same stream)
         win_ms, build_ms, fwd_ms, rev_ms, edge_ms = [], [], [], [], []
+        dev.set_option("kernel_timing", 1)      # (list path: events between the kernels, off in the timed steps above)
         for _ in range(max(3, min(args.steps, 10))):
             batch.execute()
             t = dev.timing()
             win_ms.append(t["window_ms"]); build_ms.append(t["build_ms"])
             fwd_ms.append(t["ev_fwd_ms"]); rev_ms.append(t["ev_rev_ms"]); edge_ms.append(t["ev_edge_ms"])
+        dev.set_option("kernel_timing", 0)
         pairs = t["window_word_shift_pairs"]
         win_launches = t["window_launches"]
         used_path = t["path"]

@@ -110,7 +110,7 @@ typedef struct {
     uint32_t window_launches;
     uint64_t window_word_shift_pairs; /* 32-bit word x shift pairs evaluated (dense path) */
     uint32_t path;      /* algorithm the execute used: 1 dense shift-window, 2 event-window, 3 lists */
-    float ev_fwd_ms;    /* event / list path: forward-read kernel(s)          */
+    float ev_fwd_ms;    /* event / list path: forward-read kernel(s)   (list path: with option "kernel_timing" 1) */
     float ev_rev_ms;    /* event / list path: reverse-read kernel(s)          */
     float ev_edge_ms;   /* event / list path: run-edge kernel(s) + finalize   */
 } pmb_timing;
@@ -178,7 +178,11 @@ void pmb_host_free(void *p);
  * (default 64) reverse reads per 1024 shifts, else the event path unless the inputs hold more
  * than 4 events (reads + run edges) per 32-bit word.  Tuning: "list_blocks_per_sm", "list_concurrent"
  * (-1 auto / 0 / 1: the reverse and edge list kernels beside the forward kernel on a second stream; auto does
- * so below 8 M list entries, where a launch is mostly ramp and tail), "variant" (carry-save depth of the shift-window counters), "tile_words",
+ * so below 8 M list entries, where a launch is mostly ramp and tail), "list_edge_items" (intervals per CTA of the
+ * list path's run-edge kernel at least, default 512), "kernel_timing" (list path, 0/1, default 0: with 1 an execute
+ * records events between its kernels, so that pmb_get_timing splits the time by kernel -- ev_fwd_ms, ev_rev_ms,
+ * ev_edge_ms, zero otherwise -- at ~8 us per step: a kernel then cannot start under the tail of the one before),
+ * "variant" (carry-save depth of the shift-window counters), "tile_words",
  * "grid_blocks", "block_warps", "event_tile_words", "event_blocks_per_sm".
  * Input copy: "async_h2d" (0/1, see pmb_batch_prepare), "h2d_groups" (1..64, default 4: at most that many),
  * "h2d_min_group_bytes" (default 16 MiB: no group smaller than that on average; 0 = always h2d_groups),

@@ -41,6 +41,10 @@ struct pmb_ctx {
     int path = 0;            // 0 auto, 1 dense shift-window, 2 event-window, 3 lists
     int list_blocks_per_sm = 0;
     int list_concurrent = -1;    // reverse + edge list kernels beside the forward kernel on the side stream: -1 auto, 0, 1
+    bool timing_split = true;    // the last execute recorded the events between its kernels
+    int kernel_timing = 0;       // list path: 1 = events between the kernels of an execute (pmb_get_timing's per-kernel split; they
+                                 // keep a kernel from starting under the tail of the one before: +8 us per step); 0: start and end only
+    int list_edge_items = 0;     // list path: intervals per CTA of the run-edge kernel at least (0: 512)
     int check_selftest = 0;      // -DPMB_CHECKED builds: make every TMA range check of the event kernels fail (proves the chain)
     bool event_attr_done = false; // the event kernels' shared-memory limit is raised on THIS device
     bool list_attr_done = false; // the list kernels' shared-memory limit is raised on THIS device
@@ -326,6 +330,8 @@ extern "C" int pmb_set_option(pmb_ctx* c, const char* name, int64_t value)
     else if (!strcmp(name, "check_selftest")) c->check_selftest = (int)value;
     else if (!strcmp(name, "list_concurrent")) c->list_concurrent = (int)value;
     else if (!strcmp(name, "list_blocks_per_sm")) c->list_blocks_per_sm = (int)value;
+    else if (!strcmp(name, "kernel_timing")) c->kernel_timing = value != 0;
+    else if (!strcmp(name, "list_edge_items")) c->list_edge_items = (int)value;
     else if (!strcmp(name, "list_pairs_limit")) c->list_pairs_limit = (int)value;
     else if (!strcmp(name, "event_blocks_per_sm")) c->event_blocks_per_sm = (int)value;
     else if (!strcmp(name, "async_h2d")) c->async_h2d = value != 0;
@@ -345,7 +351,7 @@ extern "C" int pmb_get_timing(pmb_ctx* c, pmb_timing* t)
         CU_TRY(c, cudaEventElapsedTime(&c->timing.build_ms, c->ev[0], c->ev[1]));
         CU_TRY(c, cudaEventElapsedTime(&c->timing.window_ms, c->ev[1], c->ev[2]));
         CU_TRY(c, cudaEventElapsedTime(&c->timing.total_ms, c->ev[0], c->ev[2]));
-        if (c->timing.path == 2 || c->timing.path == 3) {
+        if (c->timing.path == 2 || (c->timing.path == 3 && c->timing_split)) {
             CU_TRY(c, cudaEventElapsedTime(&c->timing.ev_fwd_ms, c->ev[1], c->evk[0]));
             CU_TRY(c, cudaEventElapsedTime(&c->timing.ev_rev_ms, c->evk[0], c->evk[1]));
             CU_TRY(c, cudaEventElapsedTime(&c->timing.ev_edge_ms, c->evk[1], c->ev[2]));
@@ -1070,6 +1076,7 @@ static int execute_lists(pmb_ctx* c, pmb_batch* b)
     const size_t n = b->jobs.size();
     uint32_t launches = 0;
     list_attributes(c);
+    const bool split = c->kernel_timing != 0;
     CU_TRY(c, cudaEventRecord(c->ev[0], st));
     CU_TRY(c, cudaEventRecord(c->ev[1], st));     // (no build stage: nothing is zeroed or built per execute)
     const uint32_t parity = b->list_execs & 1u;
@@ -1090,8 +1097,11 @@ static int execute_lists(pmb_ctx* c, pmb_batch* b)
     P.status_tail = b->d_counters + b->counter_words;
     const uint32_t bps = c->list_blocks_per_sm > 0 ? (uint32_t)c->list_blocks_per_sm : (uint32_t)LIST_MIN_BLOCKS;
     const unsigned long long* pre = b->h_list_prefix.data();
-    auto grid_for = [&](unsigned long long items) {
-        return (unsigned)std::max<unsigned long long>(1, std::min<unsigned long long>((items + 2047) / 2048,
+    // CTAs of at least 2048 reads -- but 512 intervals: a thread of the run-edge kernel spends its time
+    // in dependent loads, so a short interval list (a rank's share) is better spread over all SMs
+    const unsigned long long edge_items = c->list_edge_items > 0 ? (unsigned long long)c->list_edge_items : 512ull;
+    auto grid_for = [&](unsigned long long items, unsigned long long per_cta) {
+        return (unsigned)std::max<unsigned long long>(1, std::min<unsigned long long>((items + per_cta - 1) / per_cta,
                                                                                       (unsigned long long)c->num_sms * bps));
     };
     const size_t sm_f = list_smem_bytes(b->max_shift, b->any_mscc ? 4 : 1), sm_2 = list_smem_bytes(b->max_shift, 2);
@@ -1115,7 +1125,7 @@ static int execute_lists(pmb_ctx* c, pmb_batch* b)
             if (items) {
                 P.prefix = b->d_list_prefix + kind * (n + 1);
                 P.job_lo = jl; P.job_hi = jh;
-                const unsigned grid = grid_for(items);
+                const unsigned grid = grid_for(items, kind == 2 ? edge_items : 2048ull);
                 if (kind == 0) {
                     if (b->any_ncc && b->any_mscc) list_fwd_kernel<true, true><<<grid, LIST_THREADS, sm_f, ks>>>(P);
                     else if (b->any_ncc) list_fwd_kernel<true, false><<<grid, LIST_THREADS, sm_f, ks>>>(P);
@@ -1128,7 +1138,7 @@ static int execute_lists(pmb_ctx* c, pmb_batch* b)
                 }
                 launches++;
             }
-            if (kind < 2 && pass + 1 == n_pass) CU_TRY(c, cudaEventRecord(c->evk[kind], st));   // (per-kernel split: back-to-back passes only)
+            if (split && kind < 2 && pass + 1 == n_pass) CU_TRY(c, cudaEventRecord(c->evk[kind], st));   // (per-kernel split: back-to-back passes only)
         }
     }
     if (concurrent) {
@@ -1145,7 +1155,9 @@ static int execute_lists(pmb_ctx* c, pmb_batch* b)
     c->timing.window_launches = launches;
     c->timing.window_word_shift_pairs = 0;
     c->timing.path = 3;
+    c->timing_split = split;
     c->timing.build_ms = c->timing.window_ms = c->timing.total_ms = -1.f;
+    c->timing.ev_fwd_ms = c->timing.ev_rev_ms = c->timing.ev_edge_ms = 0.f;
     return PMB_OK;
 }
 

@@ -37,6 +37,7 @@ def main():
     jobs = [_shim.Job(w["length"], rl, D, flags, w["fwd"], w["rev"], w.get("begins"), w.get("ends")) for w in wl]
     dev = _shim.Device(0)
     dev.set_option("path", {"auto": 0, "dense": 1, "events": 2, "lists": 3}[args.path])
+    dev.set_option("kernel_timing", 1)      # per-kernel events (off by default: they cost a few us per step)
     for kv in args.opt:
         k, v = kv.split("=")
         dev.set_option(k, int(v))

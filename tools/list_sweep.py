@@ -66,6 +66,7 @@ def child(directory, max_shift, execs, opts):
         jobs.append(j)
     dev = _shim.Device(0)
     dev.set_option("path", 3)
+    dev.set_option("kernel_timing", 1)      # per-kernel events (off by default; --opts kernel_timing=0 for the plain step)
     for kv in opts:
         k, v = kv.split("=")
         dev.set_option(k, int(v))
