@@ -138,8 +138,9 @@ __device__ __forceinline__ uint32_t gallop(const uint32_t* __restrict__ a, uint3
 // six probes at fixed offsets from one base address.  If any lane finds all 63 below its key --
 // or the list ends inside the window -- the warp bounds the range by galloping and searches that.
 // (key_max: the largest key of the group.  Unsorted input gives wrong but in-bounds answers.)
-__device__ __forceinline__ uint32_t cursor_lower_bound(const uint32_t* __restrict__ a, uint32_t n, uint32_t cur,
-                                                       uint32_t key, uint32_t key_max)
+// (in two steps, so that a caller with two independent searches can issue both probe chains
+// before either vote: the probes are dependent L1 hits, the chains overlap)
+__device__ __forceinline__ uint32_t cursor_window(const uint32_t* __restrict__ a, uint32_t n, uint32_t cur, uint32_t key)
 {
     uint32_t off = 63;
     if (cur + 63 <= n) {
@@ -149,11 +150,21 @@ __device__ __forceinline__ uint32_t cursor_lower_bound(const uint32_t* __restric
         for (uint32_t s = 32; s; s >>= 1)
             if (__ldg(b + off + (s - 1)) < key) off += s;
     }
+    return off;
+}
+__device__ __forceinline__ uint32_t cursor_resolve(const uint32_t* __restrict__ a, uint32_t n, uint32_t cur,
+                                                   uint32_t key, uint32_t key_max, uint32_t off)
+{
     if (__any_sync(0xFFFFFFFFu, off == 63)) {
         const uint32_t hi = gallop(a, n, cur, key_max);
         return lower_bound_in(a, cur, hi, key);
     }
     return cur + off;
+}
+__device__ __forceinline__ uint32_t cursor_lower_bound(const uint32_t* __restrict__ a, uint32_t n, uint32_t cur,
+                                                       uint32_t key, uint32_t key_max)
+{
+    return cursor_resolve(a, n, cur, key, key_max, cursor_window(a, n, cur, key));
 }
 
 // per-thread lower bound over the whole array by doubling steps from `start` (run edges: the
@@ -297,16 +308,18 @@ __global__ void __launch_bounds__(LIST_THREADS, LIST_MIN_BLOCKS) list_fwd_kernel
                 const bool valid = act && p != pprev && (long long)p >= lo && (long long)p < hi && p < nbits;
                 tot += valid;
                 const uint32_t p_max = __shfl_sync(0xFFFFFFFFu, p, n_act - 1);
-                // this read's first reverse read: q >= p
-                uint32_t j = cursor_lower_bound(rev, nR, JR, p, p_max);
+                // this read's first reverse read: q >= p; the mappable runs: c = last run that begins
+                // below x_top = p + rl - 1 (both searches' probes are issued before either is resolved)
+                const uint32_t x_top = p + rl1;
+                const uint32_t off_r = cursor_window(rev, nR, JR, p);
+                const uint32_t off_i = job_mscc ? cursor_window(begins, nI, CI, x_top) : 0u;
+                uint32_t j = cursor_resolve(rev, nR, JR, p, p_max, off_r);
                 PMB_CHECK(j <= nR, P.flags);
                 JR = __shfl_sync(0xFFFFFFFFu, j, n_act - 1);
-                // mappable runs: c = last run that begins below x_top = p + rl - 1
-                const uint32_t x_top = p + rl1;
                 int c = -1;
                 bool mp = false;
                 if (job_mscc) {
-                    const uint32_t c1 = cursor_lower_bound(begins, nI, CI, x_top, p_max + rl1);
+                    const uint32_t c1 = cursor_resolve(begins, nI, CI, x_top, p_max + rl1, off_i);
                     PMB_CHECK(c1 <= nI, P.flags);
                     CI = __shfl_sync(0xFFFFFFFFu, c1, n_act - 1);
                     c = (int)c1 - 1;
