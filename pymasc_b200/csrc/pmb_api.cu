@@ -44,6 +44,7 @@ struct pmb_ctx {
     bool timing_split = true;    // the last execute recorded the events between its kernels
     int kernel_timing = 0;       // list path: 1 = events between the kernels of an execute (pmb_get_timing's per-kernel split; they
                                  // keep a kernel from starting under the tail of the one before: +8 us per step); 0: start and end only
+    int list_pair_cap = 0;       // list path: forward reads between flushes of the packed pair histogram (0: 65535; tests shrink it)
     int list_edge_items = 0;     // list path: intervals per CTA of the run-edge kernel at least (0: 512)
     int check_selftest = 0;      // -DPMB_CHECKED builds: make every TMA range check of the event kernels fail (proves the chain)
     bool event_attr_done = false; // the event kernels' shared-memory limit is raised on THIS device
@@ -332,6 +333,7 @@ extern "C" int pmb_set_option(pmb_ctx* c, const char* name, int64_t value)
     else if (!strcmp(name, "list_blocks_per_sm")) c->list_blocks_per_sm = (int)value;
     else if (!strcmp(name, "kernel_timing")) c->kernel_timing = value != 0;
     else if (!strcmp(name, "list_edge_items")) c->list_edge_items = (int)value;
+    else if (!strcmp(name, "list_pair_cap")) c->list_pair_cap = (int)value;
     else if (!strcmp(name, "list_pairs_limit")) c->list_pairs_limit = (int)value;
     else if (!strcmp(name, "event_blocks_per_sm")) c->event_blocks_per_sm = (int)value;
     else if (!strcmp(name, "async_h2d")) c->async_h2d = value != 0;
@@ -856,7 +858,7 @@ static int prepare_impl(pmb_ctx* c, const pmb_chrom_args* a, uint32_t n, pmb_bat
     // else events unless the inputs hold more than 4 events per 32-bit word.
     uint64_t total_events = 0;
     double expect_pairs = 0, total_fwd = 0;
-    b->list_ok = b->read_len >= 2 && list_smem_bytes(b->max_shift, 4) <= 200 * 1024;
+    b->list_ok = b->read_len >= 2 && list_smem_bytes(b->max_shift, list_fwd_hists(true)) <= 200 * 1024;
     for (uint32_t i = 0; i < n; i++) {
         total_events += a[i].n_fwd + a[i].n_rev + (b->jobs[i].owner < 0 ? 2 * a[i].n_intervals : 0);
         b->any_ncc |= (a[i].flags & PMB_FLAG_NCC) && !(a[i].flags & PMB_FLAG_AUTOCORR);
@@ -1090,6 +1092,7 @@ static int execute_lists(pmb_ctx* c, pmb_batch* b)
     P.max_shift = b->max_shift;
     P.read_len = b->read_len;
     P.stride = b->stride;
+    P.pair_cap = c->list_pair_cap > 0 ? (uint32_t)c->list_pair_cap : LIST_PAIR_CAP;
     P.flags = b->d_err + 2 * parity;
     P.acc_off = parity ? b->list_acc_copy : 0;
     P.acc_other = parity ? 0 : b->list_acc_copy;
@@ -1104,7 +1107,7 @@ static int execute_lists(pmb_ctx* c, pmb_batch* b)
         return (unsigned)std::max<unsigned long long>(1, std::min<unsigned long long>((items + per_cta - 1) / per_cta,
                                                                                       (unsigned long long)c->num_sms * bps));
     };
-    const size_t sm_f = list_smem_bytes(b->max_shift, b->any_mscc ? 4 : 1), sm_2 = list_smem_bytes(b->max_shift, 2);
+    const size_t sm_f = list_smem_bytes(b->max_shift, list_fwd_hists(b->any_mscc)), sm_2 = list_smem_bytes(b->max_shift, 2);
     // The three list kernels do not depend on each other.  On long lists each fills the GPU by
     // itself and they run back to back (clean per-kernel times); on short ones -- a rank's share
     // of a genome cut into 4 or 8 ranges -- a launch is mostly ramp and tail, so the reverse and
@@ -1964,6 +1967,7 @@ extern "C" int pmb_run_chrom_noalloc(pmb_ctx* c, const pmb_chrom_args* a, int64_
     P.jobs = reinterpret_cast<const ListJob*>(scratch);
     P.job_lo = 0; P.job_hi = 1;
     P.max_shift = D; P.read_len = a->read_len; P.stride = S;
+    P.pair_cap = LIST_PAIR_CAP;
     P.flags = (int*)(out + (size_t)PMB_NCOUNTERS * S + 2);      // the status word of d_out: {range, unsorted}
     P.acc_off = P.acc_other = 0;                                // one copy: the set-up kernel above clears it
     P.flags_other = nullptr;
@@ -1973,7 +1977,7 @@ extern "C" int pmb_run_chrom_noalloc(pmb_ctx* c, const pmb_chrom_args* a, int64_
         return (unsigned)std::max<unsigned long long>(1, std::min<unsigned long long>((items + 2047) / 2048,
                                                                                       (unsigned long long)c->num_sms * bps));
     };
-    const size_t sm_f = list_smem_bytes(D, mscc ? 4 : 1), sm_2 = list_smem_bytes(D, 2);
+    const size_t sm_f = list_smem_bytes(D, list_fwd_hists(mscc)), sm_2 = list_smem_bytes(D, 2);
     const unsigned long long* pre = scratch + NOALLOC_TABLE_WORDS;
     if (J.n_fwd) {
         P.prefix = pre;

@@ -67,6 +67,7 @@ struct ListParams {
     const unsigned long long* prefix;   // [n_jobs + 1]: entries of this kernel's list before each job
     uint32_t job_lo, job_hi;            // this launch covers these jobs (everything, or one H2D group)
     uint32_t max_shift, read_len, stride;
+    uint32_t pair_cap;                  // forward kernel: reads between two flushes of the packed pair histogram (<= LIST_PAIR_CAP)
     int* flags;                         // this execute's: [0] position beyond the array, [1] input not sorted / disjoint
     unsigned long long acc_off;         // words from copy 0 to this execute's copy of the accumulators
     // finalize only
@@ -91,6 +92,8 @@ __host__ __device__ constexpr size_t list_smem_bytes(uint32_t max_shift, int n_h
 {
     return (size_t)n_hist * (max_shift + 2) * 4;      // bins 0 .. max_shift and a dump bin
 }
+__host__ __device__ constexpr int list_fwd_hists(bool mscc) { return mscc ? 3 : 1; }   // pairs | d(mfwd) plus, minus
+constexpr unsigned LIST_PAIR_CAP = 65535;             // forward reads between two flushes of the packed pair histogram
 
 // ---------------------------------------------------------------- searches
 // number of a[0..n) that are < key: warp-cooperative 33-ary search (one probe per lane and round)
@@ -202,8 +205,11 @@ __device__ __forceinline__ uint32_t lower_bound_near(const uint32_t* __restrict_
 // ---------------------------------------------------------------- the CTA / segment / warp skeleton
 // body(job, J, w0, w1): called by every warp with its sub-range [w0, w1) of the job's entries
 // flush(job, J): called by the whole CTA (between barriers) when a segment ends
+// seg_cap: a segment never holds more entries than this (the forward kernel's packed pair
+// histogram counts in 16 bits between flushes)
 template <class Body, class Flush>
-__device__ __forceinline__ void list_segments(const ListParams& P, int warp, int n_warps, Body&& body, Flush&& flush)
+__device__ __forceinline__ void list_segments(const ListParams& P, int warp, int n_warps, Body&& body, Flush&& flush,
+                                              unsigned long long seg_cap = ~0ull)
 {
     const unsigned long long g0 = P.prefix[P.job_lo], g1 = P.prefix[P.job_hi];
     const unsigned long long N = g1 - g0;
@@ -212,10 +218,11 @@ __device__ __forceinline__ void list_segments(const ListParams& P, int warp, int
     if (c_lo >= c_hi) return;
     uint32_t job = P.job_lo;
     while (P.prefix[job + 1] <= c_lo) job++;
-    for (unsigned long long pos = c_lo; pos < c_hi; ++job) {
+    for (unsigned long long pos = c_lo; pos < c_hi;) {
         const unsigned long long jb = P.prefix[job], je = P.prefix[job + 1];
-        if (je <= pos) continue;                                // a job without entries
-        const unsigned long long seg_hi = c_hi < je ? c_hi : je;
+        if (je <= pos) { ++job; continue; }                     // a job without entries, or done with
+        unsigned long long seg_hi = c_hi < je ? c_hi : je;
+        if (seg_hi - pos > seg_cap) seg_hi = pos + seg_cap;
         const ListJob& J = P.jobs[job];
         const uint32_t s0 = (uint32_t)(pos - jb), s1 = (uint32_t)(seg_hi - jb);
         PMB_CHECK(job < P.job_hi && s0 < s1 && jb + s1 <= je, P.flags);
@@ -256,24 +263,29 @@ __device__ __forceinline__ void smem_inc(uint32_t addr)
 {
     asm volatile("red.shared.add.u32 [%0], 1;" :: "r"(addr) : "memory");
 }
+__device__ __forceinline__ void smem_add(uint32_t addr, uint32_t v)
+{
+    asm volatile("red.shared.add.u32 [%0], %1;" :: "r"(addr), "r"(v) : "memory");
+}
 // ---------------------------------------------------------------- forward reads: ncc, mscc, d(mfwd)
 template <bool NCC, bool MSCC>
 __global__ void __launch_bounds__(LIST_THREADS, LIST_MIN_BLOCKS) list_fwd_kernel(const ListParams P)
 {
     extern __shared__ uint32_t lsm[];
     const uint32_t D = P.max_shift, S2 = D + 2, DUMP = D + 1;
-    uint32_t* h_ncc = lsm;
-    uint32_t* h_mscc = lsm + S2;
-    uint32_t* h_fp = lsm + 2 * S2;
-    uint32_t* h_fm = lsm + 3 * S2;
+    // MSCC: ncc and mscc of a shift share one 32-bit bin (low / high half), so a pair costs ONE
+    // update; a read adds at most 1 to a bin, and a segment is cut after LIST_PAIR_CAP reads
+    uint32_t* h_pair = lsm;
+    uint32_t* h_fp = lsm + S2;
+    uint32_t* h_fm = lsm + 2 * S2;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, n_warps = blockDim.x >> 5;
-    for (uint32_t i = threadIdx.x; i < (MSCC ? 4 : 1) * S2; i += blockDim.x) lsm[i] = 0;
+    for (uint32_t i = threadIdx.x; i < (uint32_t)list_fwd_hists(MSCC) * S2; i += blockDim.x) lsm[i] = 0;
     __syncthreads();
     const uint32_t rl1 = P.read_len - 1;
     bool bad_order = false, bad_range = false;
-    const uint32_t s_ncc = smem_addr(h_ncc), s_mscc = smem_addr(h_mscc), s_fp = smem_addr(h_fp), s_fm = smem_addr(h_fm);
-    const uint32_t s_dump = s_ncc + 4u * DUMP;          // (the pair histograms' own dump bins are never flushed)
-    (void)s_ncc; (void)s_mscc; (void)s_fp; (void)s_fm; (void)s_dump;
+    const uint32_t s_pair = smem_addr(h_pair), s_fp = smem_addr(h_fp), s_fm = smem_addr(h_fm);
+    const uint32_t s_dump = s_pair + 4u * DUMP;         // (the pair histogram's own dump bin is never flushed)
+    (void)s_fp; (void)s_fm; (void)s_dump;
 
     list_segments(P, warp, n_warps,
         [&](uint32_t, const ListJob& J, uint32_t w0, uint32_t w1) {
@@ -358,6 +370,7 @@ __global__ void __launch_bounds__(LIST_THREADS, LIST_MIN_BLOCKS) list_fwd_kernel
                     bool more = !checked.value || j < nR;
                     uint32_t q = more ? __ldg(rev + j) : 0u;
                     uint32_t k = q - p;                 // (unsigned: an unsorted list cannot index outside the bins)
+#pragma unroll 2
                     while (more && k <= Dr) {
                         ++j;
                         const bool last = checked.value && j >= nR;
@@ -365,10 +378,11 @@ __global__ void __launch_bounds__(LIST_THREADS, LIST_MIN_BLOCKS) list_fwd_kernel
                         const uint32_t k4 = 4u * k;
                         const bool once = q != qn;
                         PMB_CHECK(k <= D && j <= nR, P.flags);
-                        if (NCC) smem_inc(once ? s_ncc + k4 : s_dump);
                         if (MSCC) {
                             while (k > k2w) { c--; load_run(); }
-                            smem_inc(once && k - k1 <= span ? s_mscc + k4 : s_dump);
+                            smem_add(s_pair + k4, once ? (k - k1 <= span ? 0x10001u : 1u) : 0u);
+                        } else {
+                            smem_inc(once ? s_pair + k4 : s_dump);
                         }
                         q = qn;
                         k = q - p;
@@ -384,17 +398,24 @@ __global__ void __launch_bounds__(LIST_THREADS, LIST_MIN_BLOCKS) list_fwd_kernel
         },
         [&](uint32_t, const ListJob& J) {
             unsigned long long* acc = J.acc + P.acc_off;
-            if (NCC) {
-                if (J.flags & EVF_NCC) flush_hist(h_ncc, D + 1, acc + (size_t)LA_NCC * P.stride);
-                else for (uint32_t i = threadIdx.x; i <= D; i += blockDim.x) h_ncc[i] = 0;     // (the pair loop counts for every job)
-            }
+            const bool keep_ncc = NCC && (J.flags & EVF_NCC);     // (the pair loop counts for every job)
             if (MSCC) {
-                flush_hist(h_mscc, D + 1, acc + (size_t)LA_MSCC * P.stride);
+                for (uint32_t i = threadIdx.x; i <= D; i += blockDim.x) {
+                    const uint32_t v = h_pair[i];
+                    if (!v) continue;
+                    if (keep_ncc) atomicAdd(acc + (size_t)LA_NCC * P.stride + i, (unsigned long long)(v & 0xFFFFu));
+                    if (v >> 16) atomicAdd(acc + (size_t)LA_MSCC * P.stride + i, (unsigned long long)(v >> 16));
+                    h_pair[i] = 0;
+                }
                 flush_hist(h_fp, D + 1, acc + (size_t)LA_FP * P.stride);
                 flush_hist(h_fm, D + 1, acc + (size_t)LA_FM * P.stride);
                 if (threadIdx.x == 0) { h_fp[DUMP] = 0; h_fm[DUMP] = 0; }
+            } else if (keep_ncc) {
+                flush_hist(h_pair, D + 1, acc + (size_t)LA_NCC * P.stride);
+            } else {
+                for (uint32_t i = threadIdx.x; i <= D; i += blockDim.x) h_pair[i] = 0;
             }
-        });
+        }, MSCC ? (unsigned long long)min(max(P.pair_cap, 1u), LIST_PAIR_CAP) : ~0ull);
     if (bad_range) atomicExch(P.flags, 1);
     if (bad_order) atomicExch(P.flags + 1, 1);
 }

@@ -730,6 +730,35 @@ def test_auto_picks_the_documented_path_and_counts_stay_exact_across_the_thresho
         dev.set_option("path", 0)
 
 
+@pytest.mark.parametrize("cap", [1, 37, 1000])
+def test_list_pair_histogram_is_flushed_before_its_16_bit_halves_can_overflow(dev, cap):
+    """List path, NCC+MSCC: ncc and mscc of a shift share one 32-bit shared-memory bin (low / high
+    half), a read adds at most 1 to a bin, and a CTA's segment is cut after 65535 reads
+    (pmb_lists.cuh, LIST_PAIR_CAP).  The cut is exercised here with a tiny cap (option
+    "list_pair_cap"): same counts as the oracle whatever the cap, pile-ups on one shift
+    included (every forward read has its partner at distance 150)."""
+    L, rl, D = 400000, 36, 300
+    fwd, rev, b, e = random_case(4242 + cap, L, rl, 60000)
+    rev = np.unique(np.concatenate([rev, fwd[fwd + 150 < L + rl - 1] + 150])).astype(np.uint32)
+    want = cc_oracle.chrom_counts(L, rl, D, fwd, rev, b, e)
+    assert int(want["ncc"][150]) >= fwd.size - 200          # the pile-up is there
+    try:
+        dev.set_option("path", 3)
+        dev.set_option("list_pair_cap", cap)
+        jobs = [_shim.Job(L, rl, D, 3, fwd, rev, b, e), _shim.Job(L, rl, D, 2, fwd, rev, b, e),
+                _shim.Job(L, rl, D, 1, fwd, rev)]
+        outs = dev.run_batch(jobs)
+        assert dev.timing()["path"] == 3
+        for k in want:
+            assert np.array_equal(np.asarray(outs[0][k]), np.asarray(want[k])), k
+        for k in ("mscc", "mfwd", "mrev", "dmp"):
+            assert np.array_equal(np.asarray(outs[1][k]), np.asarray(want[k])), k
+        assert np.array_equal(np.asarray(outs[2]["ncc"]), np.asarray(want["ncc"]))
+    finally:
+        dev.set_option("list_pair_cap", 0)
+        dev.set_option("path", 0)
+
+
 def test_unsorted_input_moves_a_list_batch_to_the_event_path(dev):
     """The list path verifies sortedness on the device while it counts; unsorted reads or
     overlapping intervals send the batch to the event path (fetch, or pmb_batch_validate for
