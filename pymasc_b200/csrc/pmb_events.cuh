@@ -908,7 +908,6 @@ __global__ void __launch_bounds__(256) edge_list_kernel(const DeriveTask* __rest
     }
     const DeriveTask& T = tasks[lo_t];
     const uint32_t* __restrict__ M = T.M;
-    const long long W = T.array_words;
     const uint32_t nI = T.n_intervals;
     for (uint32_t i = threadIdx.x; i < 2 * 32 * EV_HIST_STRIDE; i += blockDim.x) hist[i] = 0;
     __syncthreads();

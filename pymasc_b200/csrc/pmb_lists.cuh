@@ -298,7 +298,7 @@ __global__ void __launch_bounds__(LIST_THREADS, LIST_MIN_BLOCKS) list_fwd_kernel
             const bool job_mscc = MSCC && (J.flags & EVF_MSCC) && nI;
             const uint32_t r_last = nR ? __ldg(rev + nR - 1) : 0;       // (windows that end below it never meet the list's end)
             (void)r_last; (void)job_ncc;
-            const long long lo = J.lo, hi = J.hi;
+            const uint32_t lo32 = (uint32_t)J.lo, hi32 = (uint32_t)J.hi;         // 0 <= lo <= hi <= nbits < 2^32
             const unsigned long long nbits = J.nbits;
             // max_shift as a value that has to live in a register: as a kernel parameter it was re-read
             // from the constant bank for every pair (LDCU + IMAD.U32); nbits < 2^32, so this adds 0
@@ -317,7 +317,7 @@ __global__ void __launch_bounds__(LIST_THREADS, LIST_MIN_BLOCKS) list_fwd_kernel
                 if (lane == 0) pprev = base ? __ldg(fwd + base - 1) : LIST_NONE;
                 bad_order |= act && pprev != LIST_NONE && p < pprev;
                 bad_range |= act && p >= nbits;
-                const bool valid = act && p != pprev && (long long)p >= lo && (long long)p < hi && p < nbits;
+                const bool valid = act && p != pprev && p >= lo32 && p < hi32;       // (hi <= nbits < 2^32)
                 tot += valid;
                 const uint32_t p_max = __shfl_sync(0xFFFFFFFFu, p, n_act - 1);
                 // this read's first reverse read: q >= p; the mappable runs: c = last run that begins
@@ -446,7 +446,7 @@ __global__ void __launch_bounds__(LIST_THREADS, LIST_MIN_BLOCKS) list_rev_kernel
             const uint32_t* __restrict__ ends = J.ends;
             const uint32_t nI = J.n_iv;
             const bool job_mscc = MSCC && (J.flags & EVF_MSCC) && nI;
-            const long long lo = J.lo, hi = J.hi;
+            const uint32_t lo32 = (uint32_t)J.lo, hi32 = (uint32_t)J.hi;         // 0 <= lo <= hi <= nbits < 2^32
             const unsigned long long nbits = J.nbits;
             PMB_CHECK(w0 < w1 && w1 <= J.n_rev, P.flags);
             uint32_t CI = job_mscc ? warp_lower_bound(begins, nI, __ldg(rev + w0) + rl1, lane) : 0;
@@ -460,7 +460,7 @@ __global__ void __launch_bounds__(LIST_THREADS, LIST_MIN_BLOCKS) list_rev_kernel
                 bad_order |= act && qprev != LIST_NONE && q < qprev;
                 bad_range |= act && q >= nbits;
                 const bool valid = act && q != qprev && q < nbits;
-                tot += valid && (long long)q >= lo && (long long)q < hi;
+                tot += valid && q >= lo32 && q < hi32;
                 if (!job_mscc) continue;
                 const uint32_t t = q + rl1;
                 const uint32_t q_max = __shfl_sync(0xFFFFFFFFu, q, n_act - 1);
@@ -468,13 +468,12 @@ __global__ void __launch_bounds__(LIST_THREADS, LIST_MIN_BLOCKS) list_rev_kernel
                 PMB_CHECK(c1 <= nI, P.flags);
                 CI = __shfl_sync(0xFFFFFFFFu, c1, n_act - 1);
                 // shifts whose j = q - k lies in the counted range
-                const long long ka_l = (long long)q - hi + 1, kb_l = (long long)q - lo;
-                const int ka = ka_l > 0 ? (int)min(ka_l, (long long)D + 1) : 0;
-                const int kb = kb_l < (long long)D ? (int)max(kb_l, -1ll) : (int)D;
+                const uint32_t ka = q >= hi32 ? min(q - hi32 + 1u, D + 1u) : 0u;
+                const uint32_t kb = min(q - lo32, D);                  // (for q >= lo, checked below)
                 int cB = (int)c1 - 1;                   // last run that begins below t = q + rl - 1
                 int cA = cB;                            // ... below q
                 while (cA >= 0 && __ldg(begins + cA) >= q) cA--;
-                if (!valid || ka > kb || cA < 0) continue;
+                if (!valid || q < lo32 || ka > kb || cA < 0) continue;
                 // M[q-k]: run (b, e] <=> k in [a1, a2];  M[t-2k]: run (b, e] <=> k in [b1, b2]
                 uint32_t a1, a2, b1, b2;
                 auto load_a = [&]() {
@@ -490,15 +489,15 @@ __global__ void __launch_bounds__(LIST_THREADS, LIST_MIN_BLOCKS) list_rev_kernel
                 load_a();
                 load_b();
                 for (;;) {
-                    if (a1 > (uint32_t)kb || b1 > (uint32_t)kb) break;
-                    const uint32_t s = max(max(a1, b1), (uint32_t)ka), e = min(min(a2, b2), (uint32_t)kb);
+                    if (a1 > kb || b1 > kb) break;
+                    const uint32_t s = max(max(a1, b1), ka), e = min(min(a2, b2), kb);
                     {                                   // both mappable for k in [s, e]; else: the dump bin
                         const bool both = s <= e;
                         PMB_CHECK(!both || e <= D, P.flags);
                         smem_inc(both ? s_rp + 4u * s : s_dump);
                         smem_inc(both ? s_rm + 4u * e + 4u : s_dump);
                     }
-                    if (min(a2, b2) >= (uint32_t)kb) break;
+                    if (min(a2, b2) >= kb) break;
                     if (a2 <= b2) { if (cA == 0) break; cA--; load_a(); }
                     else { if (cB == 0) break; cB--; load_b(); }
                 }
