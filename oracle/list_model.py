@@ -8,6 +8,10 @@ list kernel adds to the histograms, so that the formulas (run -> shift ranges, c
 difference histograms and their prefix sums, the dump bin) can be checked against cc_oracle.c
 on the CPU (tests/test_list_model.py) before the kernels ever see a GPU.
 
+What the model does not restate is how the kernels are shaped for the machine: of equal reverse
+reads the kernel counts the LAST (the model the first -- a bit is set once either way), ncc and
+mscc of a shift share one 32-bit bin there, and its searches look at a window after a cursor.
+
 Inputs follow include/pymasc_b200.h: sorted forward 5' positions, sorted reverse 5' ends,
 sorted disjoint BigWig intervals (bits begin+1 .. end), counted range [lo, hi).
 """
