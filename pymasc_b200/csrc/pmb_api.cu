@@ -865,7 +865,7 @@ static int prepare_impl(pmb_ctx* c, const pmb_chrom_args* a, uint32_t n, pmb_bat
         b->any_mscc |= (a[i].flags & PMB_FLAG_MSCC) && !(a[i].flags & PMB_FLAG_AUTOCORR);
         b->any_autocorr |= (a[i].flags & PMB_FLAG_AUTOCORR) != 0;
         if (a[i].n_fwd >= (1ull << 31) || a[i].n_rev >= (1ull << 31) || a[i].n_intervals >= (1ull << 31) ||
-            b->jobs[i].nbits + b->read_len + b->max_shift + 2 >= (1ull << 32))
+            b->jobs[i].nbits + 2ull * (b->read_len + b->max_shift) + 64 >= (1ull << 32))   // (distances modulo 2^32 in the list kernels)
             b->list_ok = false;
         if (!(a[i].flags & PMB_FLAG_AUTOCORR)) {
             expect_pairs += (double)a[i].n_fwd * (double)a[i].n_rev * (double)b->n_shifts / (double)b->jobs[i].nbits;
@@ -876,7 +876,7 @@ static int prepare_impl(pmb_ctx* c, const pmb_chrom_args* a, uint32_t n, pmb_bat
     const double pairs_limit = (c->list_pairs_limit > 0 ? c->list_pairs_limit : 64) * ((b->n_shifts + 1023) / 1024);
     if (c->path == 1 || c->path == 2) b->path = c->path;
     else if (c->path == 3) {
-        if (!b->list_ok) { c->err = "the list path needs read_len >= 2, max_shift <= 12000 and fewer than 2^31 entries per list"; return PMB_ERR_ARG; }
+        if (!b->list_ok) { c->err = "the list path needs read_len >= 2, max_shift <= 17000 and fewer than 2^31 entries per list"; return PMB_ERR_ARG; }
         b->path = 3;
     } else if (b->list_ok && expect_pairs <= pairs_limit * (total_fwd + 1.0)) b->path = 3;
     else b->path = total_events <= 4 * total_words ? 2 : 1;
@@ -1922,7 +1922,7 @@ extern "C" int pmb_run_chrom_noalloc(pmb_ctx* c, const pmb_chrom_args* a, int64_
     }
     if (a->read_len < 2) { c->err = "pmb_run_chrom_noalloc: read_len must be >= 2"; return PMB_ERR_ARG; }
     const uint64_t nbits = a->chrom_len + a->read_len + a->max_shift + PMB_EXTRA_ALLOCATE_SIZE;
-    if (nbits + a->read_len + a->max_shift + 2 >= (1ull << 32) || a->n_fwd >= (1ull << 31) || a->n_rev >= (1ull << 31) ||
+    if (nbits + 2ull * (a->read_len + a->max_shift) + 64 >= (1ull << 32) || a->n_fwd >= (1ull << 31) || a->n_rev >= (1ull << 31) ||
         a->n_intervals >= (1ull << 31)) {
         c->err = "pmb_run_chrom_noalloc: chromosome or list too long for 32-bit positions"; return PMB_ERR_ARG;
     }

@@ -170,38 +170,6 @@ __device__ __forceinline__ uint32_t cursor_lower_bound(const uint32_t* __restric
     return cursor_resolve(a, n, cur, key, key_max, cursor_window(a, n, cur, key));
 }
 
-// per-thread lower bound over the whole array by doubling steps from `start` (run edges: the
-// answer lies a few entries from the thread's own interval)
-__device__ __forceinline__ uint32_t lower_bound_near(const uint32_t* __restrict__ a, uint32_t n, uint32_t start, long long key)
-{
-    if (key <= 0) return 0;
-    if (key > 0xFFFFFFFFll) return n;
-    const uint32_t k = (uint32_t)key;
-    uint32_t lo, hi;
-    if (start < n && __ldg(a + start) >= k) {   // answer in [0, start]
-        hi = start;
-        uint32_t step = 1;
-        for (;;) {
-            if (hi < step) { lo = 0; break; }
-            const uint32_t c = hi - step;
-            if (__ldg(a + c) < k) { lo = c + 1; break; }
-            hi = c;
-            step <<= 1;
-        }
-    } else {                                    // answer in (start, n]
-        lo = min(start + 1, n);
-        uint32_t step = 1;
-        for (;;) {
-            if (n - lo <= step) { hi = n; break; }
-            const uint32_t c = lo + step;
-            if (__ldg(a + c) >= k) { hi = c; break; }
-            lo = c + 1;
-            step <<= 1;
-        }
-    }
-    return lower_bound_in(a, lo, hi, k);
-}
-
 // ---------------------------------------------------------------- the CTA / segment / warp skeleton
 // body(job, J, w0, w1): called by every warp with its sub-range [w0, w1) of the job's entries
 // flush(job, J): called by the whole CTA (between barriers) when a segment ends
@@ -528,6 +496,8 @@ __global__ void __launch_bounds__(LIST_THREADS, LIST_MIN_BLOCKS) list_edge_kerne
     for (uint32_t i = threadIdx.x; i < 2 * S2; i += blockDim.x) lsm[i] = 0;
     __syncthreads();
     bool bad_order = false, bad_range = false;
+    const uint32_t s_plus = smem_addr(h_plus), s_minus = smem_addr(h_minus);
+    const uint32_t s_dump = s_plus + 4u * (D + 1);      // (bin D+1 of h_plus is never flushed)
 
     list_segments(P, warp, n_warps,
         [&](uint32_t, const ListJob& J, uint32_t w0, uint32_t w1) {
@@ -537,9 +507,9 @@ __global__ void __launch_bounds__(LIST_THREADS, LIST_MIN_BLOCKS) list_edge_kerne
             const bool autocorr = (J.flags & EVF_AUTOCORR) != 0;
             const long long lo = J.lo, hi = J.hi;
             const long long off = autocorr ? 0 : (long long)P.read_len - 1 - (long long)D;   // window start relative to an edge
-            const long long L0 = autocorr ? 0 : (long long)P.read_len - 1;
-            const long long L1 = autocorr ? 1 : (long long)P.read_len - 2;
-            const long long Lmax = L0 > L1 ? L0 : L1;
+            const uint32_t L0 = autocorr ? 0u : P.read_len - 1u;         // (read_len >= 2 on this path)
+            const uint32_t L1 = autocorr ? 1u : P.read_len - 2u;
+            const uint32_t Lmax = L0 > L1 ? L0 : L1;
             unsigned long long d0 = 0, d1 = 0;
             for (uint32_t base = w0; base < w1; base += 32) {
                 const uint32_t i = base + lane;
@@ -551,30 +521,45 @@ __global__ void __launch_bounds__(LIST_THREADS, LIST_MIN_BLOCKS) list_edge_kerne
                 const long long s = max(b + 1, lo), t = min(e + 1, hi);     // the counted part of the run: [s, t)
                 if (s >= t) continue;
                 // run edges of M inside the windows of this run's two edges: [s + off, s + off + D] and [t + off, ...]
-                const long long w_hi = t + off + D;
-                const uint32_t Jx0 = lower_bound_near(ends, n, i, s + off - 1);
-                PMB_CHECK(Jx0 <= n, P.flags);
-                for (uint32_t Jx = Jx0; Jx < n; ++Jx) {
-                    const long long bj = __ldg(begins + Jx), ej = __ldg(ends + Jx);
-                    if (bj + 1 > w_hi) break;
+                // From here on 32-bit arithmetic: the list path is not taken for a chromosome within
+                // 2 (max_shift + read_len) of 2^32 bits (pmb_api.cu, list_ok), so the sums below fit, and a
+                // distance taken modulo 2^32 is in the window iff it is <= D as an unsigned number (neither
+                // a negative nor a huge true distance can wrap into [0, D]).
+                const uint32_t w_hi = (uint32_t)(t + off + (long long)D);           // >= 1: off + D >= 0
+                const uint32_t key = (uint32_t)max(s + off - 1, 0ll);
+                // the first run whose end reaches the start edge's window: ends[Jx] >= s + off - 1.  It lies a
+                // run or two from this one -- walked to, one entry at a time (never more steps than the loop
+                // below then makes)
+                uint32_t Jx = i;
+                while (Jx > 0 && __ldg(ends + Jx - 1) >= key) --Jx;
+                if (Jx == i)
+                    while (Jx < n && __ldg(ends + Jx) < key) ++Jx;
+                const uint32_t base0 = (uint32_t)s + (uint32_t)off, base1 = (uint32_t)t + (uint32_t)off;
+                for (; Jx < n; ++Jx) {
+                    const uint32_t bj = __ldg(begins + Jx), ej = __ldg(ends + Jx);
+                    if (bj + 1u > w_hi) break;
                     if (ej <= bj) continue;
-                    const long long ds0 = bj + 1 - (s + off), de0 = ej + 1 - (s + off);     // against the start edge
-                    const long long ds1 = bj + 1 - (t + off), de1 = ej + 1 - (t + off);     // against the end edge
-                    if (ds0 >= 0 && ds0 <= (long long)D) atomicAdd(h_plus + ds0, 1u);        // start . start
-                    if (de0 >= 0 && de0 <= (long long)D) atomicAdd(h_minus + de0, 1u);       // start . end
-                    if (ds1 >= 0 && ds1 <= (long long)D) atomicAdd(h_minus + ds1, 1u);       // end . start
-                    if (de1 >= 0 && de1 <= (long long)D) atomicAdd(h_plus + de1, 1u);        // end . end
+                    const uint32_t ds0 = bj + 1u - base0, de0 = ej + 1u - base0;     // against the start edge
+                    const uint32_t ds1 = bj + 1u - base1, de1 = ej + 1u - base1;     // against the end edge
+                    smem_inc(ds0 <= D ? s_plus + 4u * ds0 : s_dump);                // start . start
+                    smem_inc(de0 <= D ? s_minus + 4u * de0 : s_dump);               // start . end
+                    smem_inc(ds1 <= D ? s_minus + 4u * ds1 : s_dump);               // end . start
+                    smem_inc(de1 <= D ? s_plus + 4u * de1 : s_dump);                // end . end
                 }
                 // the two directly counted lags: overlap of this run with the runs at and above it, moved down
-                const long long A_lo = s, A_hi = t - 1;
+                const uint32_t A_lo = (uint32_t)s, A_hi = (uint32_t)t - 1u;
                 for (uint32_t kk = i; kk < n; ++kk) {
-                    const long long B_lo = (long long)__ldg(begins + kk) + 1, B_hi = __ldg(ends + kk);
-                    if (B_lo - Lmax > A_hi) break;
+                    const uint32_t B_lo = __ldg(begins + kk) + 1u, B_hi = __ldg(ends + kk);
+                    if (B_lo > A_hi + Lmax) break;
                     if (B_hi < B_lo) continue;
-                    const long long o0 = min(A_hi, B_hi - L0) - max(A_lo, B_lo - L0) + 1;
-                    if (o0 > 0) d0 += (unsigned long long)o0;
-                    const long long o1 = min(A_hi, B_hi - L1) - max(A_lo, B_lo - L1) + 1;
-                    if (o1 > 0) d1 += (unsigned long long)o1;
+                    if (B_hi >= L0) {
+                        const uint32_t top = min(A_hi, B_hi - L0), bot = max(A_lo, B_lo > L0 ? B_lo - L0 : 0u);
+                        if (top >= bot) d0 += top - bot + 1u;
+                    }
+                    if (B_hi >= L1) {
+                        const uint32_t top = min(A_hi, B_hi - L1), bot = max(A_lo, B_lo > L1 ? B_lo - L1 : 0u);
+                        if (top >= bot) d1 += top - bot + 1u;
+                    }
                 }
             }
             for (int o = 16; o; o >>= 1) {
