@@ -84,3 +84,61 @@ def test_bench_blocks_generate_in_parallel_what_synth_generates(tmp_path):
         else:
             assert b is None and e is None
     assert sum(bench_blocks.reads_per_chrom(20_000_000)) > 19_900_000
+
+
+def test_ncu_summary_and_launch_list_tools(tmp_path):
+    """tools/ncu_summary.py (selected metrics per launch of an `ncu --page raw --csv` export) and
+    tools/ncu_launches.py (per-kernel totals and shares of a `--metrics gpu__time_duration.sum`
+    launch list): the text summaries under profiles/ are their output."""
+    hdr = ["ID", "Kernel Name", "gpu__time_duration.sum", "smsp__inst_executed.sum", "dram__bytes_read.sum"]
+    units = ["", "", "us", "inst", "Mbyte"]
+    rows = [["0", "void pmb::list_fwd_kernel<1, 1>(pmb::ListParams)", "300.0", "181017628", "92.0"],
+            ["1", "pmb::list_finalize_kernel(pmb::ListParams)", "100.0", "347590", "1.6"]]
+    raw = tmp_path / "raw.csv"
+    with open(raw, "w") as fh:
+        for r in (hdr, units) + tuple(rows):
+            fh.write(",".join('"%s"' % x for x in r) + "\n")
+    r = subprocess.run([sys.executable, "tools/ncu_summary.py", str(raw)], cwd=ROOT, capture_output=True, text=True, timeout=120)
+    assert r.returncode == 0, r.stderr[-2000:]
+    assert "== void list_fwd_kernel<1, 1>(ListParams)   (75.0 % of the captured kernels' time)" in r.stdout
+    assert "smsp__inst_executed.sum" in r.stdout and "181017628 inst" in r.stdout
+    assert "(25.0 %" in r.stdout
+
+    launches = tmp_path / "launches.csv"
+    with open(launches, "w") as fh:
+        fh.write("==PROF== Connected to process 1\n")
+        fh.write('"ID","Process ID","Process Name","Host Name","Kernel Name","Context","Stream","Block Size","Grid Size",'
+                 '"Device","CC","Section Name","Metric Name","Metric Unit","Metric Value"\n')
+        for i, (name, ns) in enumerate([("void list_fwd_kernel<1, 1>(ListParams)", "300000"),
+                                        ("void list_rev_kernel<1>(ListParams)", "100,000"),
+                                        ("void list_fwd_kernel<1, 1>(ListParams)", "100000"),
+                                        ("void probe_kernel<0>(unsigned int *)", "999000")]):
+            fh.write('"%d","1","python","h","%s","1","7","(512, 1, 1)","(296, 1, 1)","0","10.0","s",'
+                     '"gpu__time_duration.sum","ns","%s"\n' % (i, name, ns))
+    r = subprocess.run([sys.executable, "tools/ncu_launches.py", str(launches)], cwd=ROOT, capture_output=True, text=True, timeout=120)
+    assert r.returncode == 0, r.stderr[-2000:]
+    lines = {l.split()[0]: l.split() for l in r.stdout.splitlines() if not l.startswith("#")}
+    assert lines["list_fwd_kernel<1,"][2:] == ["2", "400.0", "200.00", "0.800"]
+    assert lines["list_rev_kernel<1>"][1:] == ["1", "100.0", "100.00", "0.200"]
+    assert lines["probe_kernel<0>"][-1] == "-"
+
+
+def test_list_sweep_caches_the_bench_workload_once(tmp_path):
+    """tools/list_sweep.py: the workload every (library, options) child loads is the bench
+    workload (synth.workload's seed), cut to a rank's share on request."""
+    sys.path.insert(0, os.path.join(ROOT, "tools"))
+    import numpy as np
+    import list_sweep
+    from pymasc_b200 import synth
+    list_sweep.save_workload(str(tmp_path), 200000, ["chr21", "chr22"], 2)
+    meta = json.load(open(tmp_path / "meta.json"))
+    assert [m["name"] for m in meta] == ["chr21", "chr22"]
+    total = sum(m["length"] for m in meta)
+    assert meta[0]["hi"] == meta[0]["length"] and meta[0]["hi"] + meta[1]["hi"] == total // 2
+    want = {w["name"]: w for w in synth.workload(n_reads=200000, chroms=["chr21", "chr22"])}
+    # (read counts are allotted against the whole genome by the tool, as bench.py does)
+    n21 = max(8, int(round(200000 * dict(synth.HG38)["chr21"] / float(sum(L for _, L in synth.HG38)))))
+    fwd, rev = synth.chip_reads([n for n, _ in synth.HG38].index("chr21"), dict(synth.HG38)["chr21"], n21, 36)
+    assert np.array_equal(np.load(tmp_path / "chr21_fwd.npy"), fwd)
+    assert np.array_equal(np.load(tmp_path / "chr21_rev.npy"), rev)
+    assert np.array_equal(np.load(tmp_path / "chr22_begins.npy"), want["chr22"]["begins"])
