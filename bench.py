@@ -132,8 +132,8 @@ class ClockSampler(object):
         return {"sm_mhz": float(np.median(sm)), "sm_min_mhz": float(min(sm)), "sm_max_mhz": float(self.max_sm),
                 "power_w_max": max(x[2] for x in self.samples), "samples": len(sm),
                 "reasons": [name for bit, name in self.REASONS if mask & bit],
-                "source": "nvml, polled (start / every 20 ms / end) over the same K steps repeated back to back "
-                          "right after the timed ones: queries inside the timed region perturb it"}
+                "source": "nvml, polled (start / every 20 ms / end) over the same steps repeated back to back right "
+                          "after the timed ones, as many as fill 0.25 s: queries inside the timed region perturb it"}
 
 
 def pinned_u32(a):
@@ -474,14 +474,31 @@ def gpu_arm(args):
         ev1.record(stream)
         # Clocks: NVML queries take a driver lock that stalls submission / NCCL progress (measured:
         # two queries inside the region added 0.45 ms to every 2.4 ms step at N=2), so they are
-        # taken over the SAME steps run again back to back, the device never going idle between.
+        # taken over the SAME steps run again back to back, the device never going idle between --
+        # and, K steps of this workload being a few milliseconds, over as many of them as fill
+        # a quarter of a second (the same count on every rank: it derives from the max over ranks).
         sampler = ClockSampler(local).start() if (rank == 0 and not args.no_clocks) else None
         for _ in range(args.steps):
             step()
-        clocks = sampler.stop() if sampler else None      # steps are enqueued, the device is still in them
         barrier()
         dev_ms = max_over_ranks(ev0.elapsed_time(ev1))
         ms_per_step = dev_ms / args.steps
+        clock_steps = args.steps
+        if not args.no_clocks:
+            more = int(min(4000, max(0.0, 250.0 / max(ms_per_step, 1e-3) - args.steps)))
+            for _ in range(more):
+                step()
+            clock_steps += more
+            if sampler is not None:     # the steps are only enqueued: keep sampling while the device works through them
+                ev_c = torch.cuda.Event()
+                ev_c.record(stream)
+                t_c = time.perf_counter()
+                while not ev_c.query() and time.perf_counter() - t_c < 1.0:
+                    time.sleep(0.005)
+        clocks = sampler.stop() if sampler else None      # (the last sample: right behind the last step)
+        if clocks is not None:
+            clocks["steps_sampled_over"] = clock_steps
+        barrier()
         launches_per_step = dev.timing()["launches"]
 
         # ---- per-kernel times of the same step (library CUDA events on the same stream)
