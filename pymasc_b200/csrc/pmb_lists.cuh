@@ -17,15 +17,19 @@
 //
 // With 20 M reads on hg38 a forward read sees ~3 reverse reads and ~1 run edge inside its 1000
 // shifts, so a read costs a few histogram updates instead of a 1000-bit window per counter.
-// Histograms live in shared memory (ATOMS.POPC.INC: ~11 updates/clk/SM measured on B200,
+// Histograms live in shared memory (ATOMS: ~11 updates/clk/SM measured on B200,
 // profiles/r02_atom_probe.jsonl -- the cost is per instruction, whatever the bins), one copy
-// per CTA, flushed to the 64-bit global counters when the CTA changes chromosome.
+// per CTA, flushed to the 64-bit global counters when the CTA changes chromosome.  The inner
+// loops are shaped against the SASS: shared-space addresses converted once,
+// conditions that select the value added or a dump bin instead of branching around an update,
+// ncc and mscc of a shift in one 32-bit bin.
 //
 // Mapping.  One THREAD per list entry.  A CTA owns a contiguous range of the batch's entries,
 // cut into per-chromosome segments; inside a segment every warp owns a contiguous sub-range and
-// walks it 32 entries at a time with warp-uniform cursors into the other lists: a gallop from
-// the cursor bounds the window, a per-lane binary search (6-7 L1-resident probes) finds each
-// entry's own start.  Warps meet only where the CTA changes chromosome.
+// walks it 32 entries at a time with warp-uniform cursors into the other lists: each entry's own
+// start is searched in the 63 entries after the cursor (six probes at fixed offsets; a gallop and
+// a binary search only where a vote says the window may be too short).  Warps meet only where the
+// CTA changes chromosome.
 //
 // Preconditions, verified on the device (flag -> the host re-runs the batch on the event path):
 // reads sorted; intervals sorted and disjoint.  Exact integer arithmetic throughout; the
