@@ -179,7 +179,8 @@ void pmb_host_free(void *p);
  * than 4 events (reads + run edges) per 32-bit word.  Tuning: "list_blocks_per_sm", "list_concurrent"
  * (-1 auto / 0 / 1: the reverse and edge list kernels beside the forward kernel on a second stream; auto does
  * so below 8 M list entries, where a launch is mostly ramp and tail), "list_edge_items" (intervals per CTA of the
- * list path's run-edge kernel at least, default 512), "kernel_timing" (list path, 0/1, default 0: with 1 an execute
+ * list path's run-edge kernel at least, default 512), "list_pair_cap" (forward reads between two flushes of the
+ * forward list kernel's packed ncc | mscc bins, default and maximum 65535: tests shrink it), "kernel_timing" (list path, 0/1, default 0: with 1 an execute
  * records events between its kernels, so that pmb_get_timing splits the time by kernel -- ev_fwd_ms, ev_rev_ms,
  * ev_edge_ms, zero otherwise -- at ~8 us per step: a kernel then cannot start under the tail of the one before),
  * "variant" (carry-save depth of the shift-window counters), "tile_words",
